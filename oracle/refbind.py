@@ -1,0 +1,146 @@
+"""ctypes binding for oracle/_ref/libpbrtref.so — the UNMODIFIED reference hot path (see
+oracle/ref/ref_api.h).  TEST INFRASTRUCTURE ONLY: imported by tests/, by the golden-vector generator
+(tests/golden/make_golden.py) and by bench.py's cpu_baseline / --impl reference legs.  Never by the
+product path."""
+import ctypes as C
+import os
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "_ref", "libpbrtref.so")
+
+REF_HIT = np.dtype([("prim", "<i4"), ("t", "<f4"), ("uv", "<f4", 2), ("p", "<f4", 3)])
+REF_CNT = np.dtype([("prim_tests", "<u4"), ("interior_visits", "<u4"), ("leaf_visits", "<u4")])
+
+
+class TreeInfo(C.Structure):
+    _fields_ = [("node_count", C.c_uint32), ("node_stride", C.c_uint32), ("n_indices", C.c_uint32),
+                ("n_directions", C.c_uint32), ("n_prims", C.c_uint32), ("bounds", C.c_float * 6)]
+
+
+def available():
+    return os.path.exists(LIB_PATH)
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        L = C.CDLL(LIB_PATH)
+        L.ref_scene_create.restype = C.c_void_p
+        L.ref_scene_create.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int]
+        L.ref_scene_destroy.argtypes = [C.c_void_p]
+        L.ref_scene_num_prims.argtypes = [C.c_void_p]
+        L.ref_loopsubdiv.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_void_p),
+                                     C.POINTER(C.c_int), C.POINTER(C.c_void_p), C.POINTER(C.c_int)]
+        L.ref_free.argtypes = [C.c_void_p]
+        L.ref_accel_create.restype = C.c_void_p
+        L.ref_accel_create.argtypes = [C.c_void_p, C.c_char_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.ref_accel_destroy.argtypes = [C.c_void_p]
+        L.ref_accel_info.argtypes = [C.c_void_p, C.POINTER(TreeInfo)]
+        L.ref_accel_export.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.ref_intersect.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_int]
+        L.ref_intersect_p.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_int]
+        L.ref_prim_intersect.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_uint64, C.c_void_p]
+        L.ref_prim_intersect_p.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_uint64, C.c_void_p]
+        _lib = L
+    return _lib
+
+
+def _p(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+class RefScene:
+    """vector<shared_ptr<Primitive>>: one GeometricPrimitive per triangle, then the spheres."""
+
+    def __init__(self, P, indices, uv=None, spheres=None):
+        self.P = np.ascontiguousarray(P, np.float32).reshape(-1, 3)
+        self.idx = np.ascontiguousarray(indices, np.int32).reshape(-1, 3)
+        self.uv = None if uv is None else np.ascontiguousarray(uv, np.float32).reshape(-1, 2)
+        self.spheres = None if spheres is None else np.ascontiguousarray(spheres, np.float32).reshape(-1, 4)
+        ns = 0 if self.spheres is None else len(self.spheres)
+        self.h = lib().ref_scene_create(_p(self.P), len(self.P), _p(self.idx), len(self.idx), _p(self.uv),
+                                        _p(self.spheres), ns)
+        self.n_prims = lib().ref_scene_num_prims(self.h)
+
+    def prim_intersect(self, prim, rays):
+        rays = np.ascontiguousarray(rays, np.float32).reshape(-1, 8)
+        hits = np.zeros(len(rays), REF_HIT)
+        lib().ref_prim_intersect(self.h, int(prim), _p(rays), len(rays), _p(hits))
+        return hits
+
+    def prim_intersect_p(self, prim, rays):
+        rays = np.ascontiguousarray(rays, np.float32).reshape(-1, 8)
+        occ = np.zeros(len(rays), np.uint8)
+        lib().ref_prim_intersect_p(self.h, int(prim), _p(rays), len(rays), _p(occ))
+        return occ
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            lib().ref_scene_destroy(self.h)
+            self.h = None
+
+
+def loopsubdiv(P, indices, n_levels):
+    P = np.ascontiguousarray(P, np.float32).reshape(-1, 3)
+    idx = np.ascontiguousarray(indices, np.int32).reshape(-1)
+    oP, oI = C.c_void_p(), C.c_void_p()
+    nv, nt = C.c_int(), C.c_int()
+    rc = lib().ref_loopsubdiv(_p(P), len(P), _p(idx), len(idx), n_levels, C.byref(oP), C.byref(nv), C.byref(oI),
+                              C.byref(nt))
+    if rc != 0:
+        raise RuntimeError("ref_loopsubdiv failed")
+    outP = np.ctypeslib.as_array(C.cast(oP, C.POINTER(C.c_float)), (nv.value, 3)).copy()
+    outI = np.ctypeslib.as_array(C.cast(oI, C.POINTER(C.c_int)), (nt.value, 3)).copy()
+    lib().ref_free(oP)
+    lib().ref_free(oI)
+    return outP, outI
+
+
+class RefAccel:
+    """The reference's own accelerator built by its Create*Accelerator from a ParamSet."""
+
+    def __init__(self, scene, kind, int_params=None, float_params=None):
+        self.scene = scene
+        self.kind = kind
+        ip = int_params or {}
+        fp = float_params or {}
+        inames = (C.c_char_p * (len(ip) + 1))(*[k.encode() for k in ip], None)
+        ivals = (C.c_int * max(1, len(ip)))(*ip.values())
+        fnames = (C.c_char_p * (len(fp) + 1))(*[k.encode() for k in fp], None)
+        fvals = (C.c_float * max(1, len(fp)))(*fp.values())
+        self.h = lib().ref_accel_create(scene.h, kind.encode(), inames, ivals, fnames, fvals)
+        if not self.h:
+            raise ValueError("unknown accelerator kind %r" % kind)
+
+    def export(self):
+        ti = TreeInfo()
+        lib().ref_accel_info(self.h, C.byref(ti))
+        nodes = np.zeros((ti.node_count, ti.node_stride // 4), np.uint32)
+        idx = np.zeros(ti.n_indices, np.uint32)
+        dirs = np.zeros((ti.n_directions, 3), np.float32)
+        lib().ref_accel_export(self.h, _p(nodes), _p(idx), _p(dirs))
+        return dict(kind=self.kind, nodes=nodes, indices=idx, directions=dirs,
+                    bounds=np.array(list(ti.bounds), np.float32), n_prims=ti.n_prims)
+
+    def intersect(self, rays, counters=False, n_threads=1):
+        rays = np.ascontiguousarray(rays, np.float32).reshape(-1, 8)
+        hits = np.zeros(len(rays), REF_HIT)
+        cnt = np.zeros(len(rays), REF_CNT) if counters else None
+        lib().ref_intersect(self.h, _p(rays), len(rays), _p(hits), _p(cnt), n_threads)
+        return (hits, cnt) if counters else hits
+
+    def intersect_p(self, rays, counters=False, n_threads=1):
+        rays = np.ascontiguousarray(rays, np.float32).reshape(-1, 8)
+        occ = np.zeros(len(rays), np.uint8)
+        cnt = np.zeros(len(rays), REF_CNT) if counters else None
+        lib().ref_intersect_p(self.h, _p(rays), len(rays), _p(occ), _p(cnt), n_threads)
+        return (occ, cnt) if counters else occ
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            lib().ref_accel_destroy(self.h)
+            self.h = None
