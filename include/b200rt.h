@@ -1,0 +1,146 @@
+/*
+ * b200rt.h — C ABI of the B200-native ray-intersection engine (libb200rt.so).
+ *
+ * This is the drop-in boundary for ONE hot path of jhoobergs/Thesis-pbrt-v3:
+ *   Aggregate::Intersect / IntersectP over the flattened BVH / kd-tree / RBSP(/Kd) node arrays
+ *   plus the watertight Triangle::Intersect, batched over ray arrays.
+ *
+ * Each entry point cites the reference interface it replaces (paths relative to the reference
+ * tree).  Conventions: plain pointers and sizes only; every call returns 0 on success or a
+ * B200RT_E* code (never throws across the ABI; b200rt_last_error() has the text); the caller keeps
+ * ownership of every host buffer it passes in; a scene is immutable after creation; intersect
+ * calls are thread-safe on distinct streams.  There is NO CPU fallback: without a CUDA device every
+ * compute entry point fails with B200RT_ENODEVICE.
+ */
+#ifndef B200RT_H
+#define B200RT_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200RT_VERSION 1
+
+enum {
+    B200RT_OK = 0,
+    B200RT_EINVAL = 1,     /* bad argument / malformed tree */
+    B200RT_ENODEVICE = 2,  /* no CUDA device (there is no CPU path) */
+    B200RT_ECUDA = 3,      /* CUDA runtime error, see b200rt_last_error() */
+    B200RT_EUNSUPPORTED = 4, /* e.g. tree deeper than the reference's 64-entry stack */
+    B200RT_ENOMEM = 5
+};
+
+/* Accelerator kinds = the `Accelerator "<name>"` strings of MakeAccelerator (src/core/api.cpp:790-1015). */
+typedef enum {
+    B200RT_BVH = 0,    /* "bvh"    src/accelerators/bvh.cpp          (32-byte LinearBVHNode) */
+    B200RT_KDTREE = 1, /* "kdtree" src/accelerators/kdtreeaccel.cpp  (8-byte KdAccelNode)    */
+    B200RT_RBSP = 2,   /* "rbsp"   src/accelerators/rbsp.cpp         (8-byte RBSPNode)       */
+    B200RT_RBSPKD = 3  /* "rbspkd" src/accelerators/rbspKd.cpp       (RBSP + axis<3 kd path) */
+} b200rt_kind;
+
+/* Ray = the fields of pbrt::Ray the hot path reads (src/core/geometry.h:1176-1203): 32 bytes. */
+typedef struct {
+    float o[3];
+    float tMax; /* Ray::tMax (mutable in the reference; the shrunk value is returned in b200rt_hit::t) */
+    float d[3];
+    float time; /* carried, unused by triangles */
+} b200rt_ray;
+
+/* Closest-hit record, 20 bytes.  Replaces the (bool, ray.tMax, SurfaceInteraction) triple of
+ * Aggregate::Intersect (src/core/primitive.h:49-56); b0,b1,b2 are Triangle::Intersect's barycentrics
+ * (src/shapes/triangle.cpp:266-270) from which the shading stage rebuilds the SurfaceInteraction. */
+#define B200RT_MISS 0xFFFFFFFFu
+typedef struct {
+    uint32_t prim; /* ORIGINAL primitive number (index into the prims vector handed to the
+                      accelerator, i.e. primNumMapping[slot] for the BVH), B200RT_MISS if none */
+    float t;       /* ray.tMax after the call (unchanged input tMax on a miss) */
+    float b0, b1, b2;
+} b200rt_hit;
+
+/* Scene description: the host-built flattened tree in the REFERENCE'S OWN node format plus
+ * world-space triangles in original primitive order.  The library re-lays both out for HBM. */
+typedef struct {
+    uint32_t kind;         /* b200rt_kind */
+    const void *nodes;     /* BVH: node_count x 32 B (bvh.cpp:123-152); others: node_count x 8 B
+                              (kdtreeaccel.cpp:43-160, rbsp.cpp:15-135) */
+    uint32_t node_count;
+    const uint32_t *prim_indices; /* BVH: primNumMapping[slot] -> original prim (bvh.cpp:227,322),
+                                     n_indices == n_prims.  kd/RBSP: primitiveIndices
+                                     (genericBSP.h:187). */
+    uint32_t n_indices;
+    const float *directions; /* RBSP/RBSPKd: M x 3 split normals (RBSPShared.h:29-74); else NULL */
+    uint32_t n_directions;   /* M (3 for kd) */
+    float bounds[6];         /* kd/RBSP root bounds pMin.xyz pMax.xyz (genericBSP.h:190); BVH: ignored */
+    const float *tri_verts;  /* n_prims x 9 floats: world-space p0,p1,p2 (TriangleMesh::p, triangle.h:50-69) */
+    const float *tri_uvs;    /* n_prims x 6 floats or NULL (default (0,0),(1,0),(1,1), triangle.h:109-121);
+                                only used for the degenerate-triangle rejection of triangle.cpp:302-315 */
+    uint32_t n_prims;
+} b200rt_scene_desc;
+
+typedef struct b200rt_scene b200rt_scene;
+
+/* Per-launch traversal counters (optional instrumented kernels; = the reference's per-ray
+ * GeneralStats, src/core/geometry.h:1078-1173, summed over the batch). */
+typedef struct {
+    uint64_t rays;
+    uint64_t nodes_fetched;  /* BVH: nodes whose box was tested; kd/RBSP: loop iterations (kdtreeaccel.cpp:401) */
+    uint64_t nodes_passed;   /* BVH: boxes passed (bvh.cpp:368); kd/RBSP: interior nodes */
+    uint64_t leaf_visits;
+    uint64_t prim_tests;     /* GeometricPrimitive::Intersect(P) calls (primitive.cpp:118-126) */
+    uint64_t index_reads;    /* primitiveIndices reads in multi-prim kd/RBSP leaves */
+} b200rt_counters;
+
+/* ---- device / lifetime -------------------------------------------------------------------- */
+int b200rt_init(int device);              /* cudaSetDevice + context warm-up; replaces nothing (pbrtInit has no device) */
+const char *b200rt_last_error(void);      /* thread-local text of the last failure */
+int b200rt_version(void);
+
+/* MakeAccelerator(name, prims, paramSet) (src/core/api.cpp:790) AFTER the host builder ran:
+ * copies the tree + triangles to HBM in the device layout. */
+int b200rt_scene_create(const b200rt_scene_desc *desc, b200rt_scene **out);
+void b200rt_scene_destroy(b200rt_scene *scene);
+/* Aggregate::WorldBound() (src/core/primitive.h:53; bvh.cpp:187, genericBSP.h:97). */
+int b200rt_scene_bounds(const b200rt_scene *scene, float out_bounds[6]);
+
+/* Aggregate::Intersect over a batch (bvh.cpp:354, kdtreeaccel.cpp:381, rbsp.cpp:405, rbspKd.cpp).
+ * rays/hits may each be host or device pointers (detected per pointer); with host pointers the
+ * copies are part of the call.  stream: a cudaStream_t or NULL for the default stream.
+ * The call is synchronous w.r.t. host buffers, asynchronous for device buffers. */
+int b200rt_intersect_closest(b200rt_scene *scene, const b200rt_ray *rays, uint64_t n, b200rt_hit *hits,
+                             void *stream);
+/* Aggregate::IntersectP over a batch (bvh.cpp:398, kdtreeaccel.cpp:454, rbsp.cpp:479): occluded[i] = 0/1. */
+int b200rt_intersect_any(b200rt_scene *scene, const b200rt_ray *rays, uint64_t n, uint8_t *occluded,
+                         void *stream);
+/* Instrumented variants (slower; counters accumulate into *counters, a HOST struct). */
+int b200rt_intersect_closest_counted(b200rt_scene *scene, const b200rt_ray *rays, uint64_t n,
+                                     b200rt_hit *hits, b200rt_counters *counters, void *stream);
+int b200rt_intersect_any_counted(b200rt_scene *scene, const b200rt_ray *rays, uint64_t n,
+                                 uint8_t *occluded, b200rt_counters *counters, void *stream);
+/* Number of kernel launches issued by this library since b200rt_init (bench.py's gpu_launches). */
+uint64_t b200rt_launch_count(void);
+
+/* ---- host builders (C++; node-for-node restatement of the reference's builders) ------------ */
+/* BVHAccel::BVHAccel / iterativeBuild / flattenBVHTree (bvh.cpp:155-352) on triangle bounds.
+ * Params = CreateBVHAccelerator's (bvh.cpp:529-535): maxnodeprims 4, intersectcost 8, traversalcost 1.
+ * Outputs malloc'ed arrays the caller frees with b200rt_free. */
+int b200rt_build_bvh(const float *tri_verts, uint32_t n_prims, int max_node_prims, int isect_cost,
+                     int traversal_cost, void **out_nodes, uint32_t *out_node_count,
+                     uint32_t **out_prim_order);
+/* KdTreeAccel::buildTree (kdtreeaccel.cpp:208-379); params of CreateKdTreeAccelerator (:523-545):
+ * intersectcost 80, traversalcost 1, emptybonus 0, maxprims 1, maxdepth -1. */
+int b200rt_build_kdtree(const float *tri_verts, uint32_t n_prims, int isect_cost, int traversal_cost,
+                        float empty_bonus, int max_prims, int max_depth, void **out_nodes,
+                        uint32_t *out_node_count, uint32_t **out_prim_indices, uint32_t *out_n_indices,
+                        float out_bounds[6]);
+void b200rt_free(void *p);
+
+/* ---- wavefront driver (SamplerIntegrator::Render restructured, src/core/integrator.cpp:230-360
+ *      + PathIntegrator::Li, src/integrators/path.cpp:64-204) ---------------------------------
+ * See b200rt_wavefront.h. */
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200RT_H */

@@ -1,0 +1,492 @@
+/*
+ * oracle.c — CPU restatement of the reference's ray-intersection hot path.
+ *
+ * TEST INFRASTRUCTURE ONLY.  Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline /
+ * --impl reference legs may load this; the product (libb200rt.so) never does.
+ *
+ * Parity status: PINNED.  Every function below is checked bit-for-bit against the unmodified
+ * reference compiled from /root/reference (oracle/_ref/libpbrtref.so, recipe oracle/ref/Makefile)
+ * by tests/test_oracle_vs_ref.py, and against the committed golden vectors that the same library
+ * produced (tests/golden/, generator tests/golden/make_golden.py).
+ *
+ * Each function cites the reference file:line it restates (paths relative to /root/reference/src).
+ * All arithmetic is IEEE binary32 with no contraction (build: gcc -O2 -ffp-contract=off, baseline
+ * x86-64, like the reference's Release build) except the double-precision edge-function fallback.
+ */
+#include <math.h>
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+
+typedef struct { float o[3]; float tMax; float d[3]; float time; } orc_ray;
+typedef struct { uint32_t prim; float t, b0, b1, b2; } orc_hit;
+typedef struct {
+    uint64_t rays, nodes_fetched, nodes_passed, leaf_visits, prim_tests, index_reads;
+} orc_counters;
+#define ORC_MISS 0xFFFFFFFFu
+
+/* pbrt.h:201-204,289-291 */
+static const float MachineEpsilon = 5.9604644775390625e-08f; /* 2^-24 = numeric_limits<float>::epsilon()*0.5 */
+static inline float orc_gamma(int n) { return (n * MachineEpsilon) / (1 - n * MachineEpsilon); }
+
+/* Default UVs of Triangle::GetUVs (shapes/triangle.h:109-121). */
+static const float kDefaultUV[6] = {0, 0, 1, 0, 1, 1};
+
+/* ------------------------------------------------------------------------------------------ */
+/* Triangle::Intersect tail, shapes/triangle.cpp:294-315 (same in IntersectP only under an alpha
+ * mask, :533-556, which the engine rejects at upload): the hit is "bogus" when the UV
+ * parameterisation is degenerate (or dpdu x dpdv == 0) AND the geometric normal is zero.
+ * Depends on the triangle only, not on the ray, so the engine precomputes it per triangle. */
+int orc_tri_is_degenerate(const float *v /*9*/, const float *uv /*6 or NULL*/) {
+    if (!uv) uv = kDefaultUV;
+    const float *p0 = v, *p1 = v + 3, *p2 = v + 6;
+    float duv02[2] = {uv[0] - uv[4], uv[1] - uv[5]};
+    float duv12[2] = {uv[2] - uv[4], uv[3] - uv[5]};
+    float dp02[3], dp12[3];
+    for (int i = 0; i < 3; ++i) { dp02[i] = p0[i] - p2[i]; dp12[i] = p1[i] - p2[i]; }
+    float determinant = duv02[0] * duv12[1] - duv02[1] * duv12[0];
+    int degenerateUV = fabsf(determinant) < 1e-8; /* float < double comparison, as in the reference */
+    float dpdu[3] = {0, 0, 0}, dpdv[3] = {0, 0, 0};
+    if (!degenerateUV) {
+        float invdet = 1 / determinant;
+        for (int i = 0; i < 3; ++i) {
+            /* (duv12[1] * dp02 - duv02[1] * dp12) * invdet ; (-duv12[0] * dp02 + duv02[0] * dp12) * invdet */
+            dpdu[i] = (duv12[1] * dp02[i] - duv02[1] * dp12[i]) * invdet;
+            dpdv[i] = (-duv12[0] * dp02[i] + duv02[0] * dp12[i]) * invdet;
+        }
+    }
+    int need = degenerateUV;
+    if (!need) {
+        /* Cross() is evaluated in double (core/geometry.h:1289-1297) then narrowed. */
+        double ax = dpdu[0], ay = dpdu[1], az = dpdu[2], bx = dpdv[0], by = dpdv[1], bz = dpdv[2];
+        float cx = (float)((ay * bz) - (az * by));
+        float cy = (float)((az * bx) - (ax * bz));
+        float cz = (float)((ax * by) - (ay * bx));
+        float l2 = cx * cx + cy * cy + cz * cz;
+        need = (l2 == 0);
+    }
+    if (!need) return 0;
+    float e0[3], e1[3];
+    for (int i = 0; i < 3; ++i) { e0[i] = p2[i] - p0[i]; e1[i] = p1[i] - p0[i]; }
+    double ax = e0[0], ay = e0[1], az = e0[2], bx = e1[0], by = e1[1], bz = e1[2];
+    float nx = (float)((ay * bz) - (az * by));
+    float ny = (float)((az * bx) - (ax * bz));
+    float nz = (float)((ax * by) - (ay * bx));
+    float l2 = nx * nx + ny * ny + nz * nz;
+    return l2 == 0;
+}
+
+/* MaxComponent(Abs(Vector3f(a,b,c))) (core/geometry.h:1333-1335) = std::max(x, std::max(y, z)) with
+ * std::max(a,b) = (a < b) ? b : a (differs from fmaxf for NaN operands, so the exact form is kept). */
+static inline float orc_stdmax(float a, float b) { return (a < b) ? b : a; }
+static inline float orc_max3abs(float x, float y, float z) {
+    return orc_stdmax(fabsf(x), orc_stdmax(fabsf(y), fabsf(z)));
+}
+
+/* Triangle::Intersect, shapes/triangle.cpp:188-292 (identical arithmetic in IntersectP :428-530).
+ * v = p0,p1,p2 world space.  Returns 1 and writes t,b0,b1,b2 on a hit. */
+static int tri_isect(const float o[3], const float dir[3], float rayTMax, const float *v, float *tOut,
+                     float *b0o, float *b1o, float *b2o) {
+    float p0t[3], p1t[3], p2t[3];
+    for (int i = 0; i < 3; ++i) {
+        p0t[i] = v[i] - o[i];
+        p1t[i] = v[3 + i] - o[i];
+        p2t[i] = v[6 + i] - o[i];
+    }
+    float ax = fabsf(dir[0]), ay = fabsf(dir[1]), az = fabsf(dir[2]);
+    int kz = (ax > ay) ? ((ax > az) ? 0 : 2) : ((ay > az) ? 1 : 2);
+    int kx = kz + 1; if (kx == 3) kx = 0;
+    int ky = kx + 1; if (ky == 3) ky = 0;
+    float d[3] = {dir[kx], dir[ky], dir[kz]};
+    float q0[3] = {p0t[kx], p0t[ky], p0t[kz]};
+    float q1[3] = {p1t[kx], p1t[ky], p1t[kz]};
+    float q2[3] = {p2t[kx], p2t[ky], p2t[kz]};
+    float Sx = -d[0] / d[2];
+    float Sy = -d[1] / d[2];
+    float Sz = 1.f / d[2];
+    q0[0] += Sx * q0[2]; q0[1] += Sy * q0[2];
+    q1[0] += Sx * q1[2]; q1[1] += Sy * q1[2];
+    q2[0] += Sx * q2[2]; q2[1] += Sy * q2[2];
+    float e0 = q1[0] * q2[1] - q1[1] * q2[0];
+    float e1 = q2[0] * q0[1] - q2[1] * q0[0];
+    float e2 = q0[0] * q1[1] - q0[1] * q1[0];
+    if (e0 == 0.0f || e1 == 0.0f || e2 == 0.0f) {
+        double p2txp1ty = (double)q2[0] * (double)q1[1];
+        double p2typ1tx = (double)q2[1] * (double)q1[0];
+        e0 = (float)(p2typ1tx - p2txp1ty);
+        double p0txp2ty = (double)q0[0] * (double)q2[1];
+        double p0typ2tx = (double)q0[1] * (double)q2[0];
+        e1 = (float)(p0typ2tx - p0txp2ty);
+        double p1txp0ty = (double)q1[0] * (double)q0[1];
+        double p1typ0tx = (double)q1[1] * (double)q0[0];
+        e2 = (float)(p1typ0tx - p1txp0ty);
+    }
+    if ((e0 < 0 || e1 < 0 || e2 < 0) && (e0 > 0 || e1 > 0 || e2 > 0)) return 0;
+    float det = e0 + e1 + e2;
+    if (det == 0) return 0;
+    q0[2] *= Sz; q1[2] *= Sz; q2[2] *= Sz;
+    float tScaled = e0 * q0[2] + e1 * q1[2] + e2 * q2[2];
+    if (det < 0 && (tScaled >= 0 || tScaled < rayTMax * det)) return 0;
+    else if (det > 0 && (tScaled <= 0 || tScaled > rayTMax * det)) return 0;
+    float invDet = 1 / det;
+    float b0 = e0 * invDet, b1 = e1 * invDet, b2 = e2 * invDet;
+    float t = tScaled * invDet;
+    float maxZt = orc_max3abs(q0[2], q1[2], q2[2]);
+    float deltaZ = orc_gamma(3) * maxZt;
+    float maxXt = orc_max3abs(q0[0], q1[0], q2[0]);
+    float maxYt = orc_max3abs(q0[1], q1[1], q2[1]);
+    float deltaX = orc_gamma(5) * (maxXt + maxZt);
+    float deltaY = orc_gamma(5) * (maxYt + maxZt);
+    float deltaE = 2 * (orc_gamma(2) * maxXt * maxYt + deltaY * maxXt + deltaX * maxYt);
+    float maxE = orc_max3abs(e0, e1, e2);
+    float deltaT = 3 * (orc_gamma(3) * maxE * maxZt + deltaE * maxZt + deltaZ * maxE) * fabsf(invDet);
+    if (t <= deltaT) return 0;
+    *tOut = t; *b0o = b0; *b1o = b1; *b2o = b2;
+    return 1;
+}
+
+/* Public single-triangle entry (exact form). degenerate = orc_tri_is_degenerate() result. */
+int orc_triangle(const orc_ray *r, const float *v, int degenerate, float *t, float *b0, float *b1, float *b2) {
+    if (!tri_isect(r->o, r->d, r->tMax, v, t, b0, b1, b2)) return 0;
+    return degenerate ? 0 : 1; /* triangle.cpp:309-315 */
+}
+
+/* ------------------------------------------------------------------------------------------ */
+typedef struct {
+    const float *verts;      /* n_prims x 9, original primitive order */
+    const uint8_t *degen;    /* n_prims, orc_tri_is_degenerate flags */
+    uint32_t n_prims;
+} orc_prims;
+
+/* GeometricPrimitive::Intersect, core/primitive.cpp:123-139: on a hit r.tMax = tHit. */
+static inline int prim_intersect(const orc_prims *P, uint32_t prim, orc_ray *r, orc_hit *h, orc_counters *c) {
+    float t, b0, b1, b2;
+    if (c) c->prim_tests++;
+    if (!tri_isect(r->o, r->d, r->tMax, P->verts + 9 * (size_t)prim, &t, &b0, &b1, &b2)) return 0;
+    if (P->degen && P->degen[prim]) return 0;
+    r->tMax = t;
+    h->prim = prim; h->t = t; h->b0 = b0; h->b1 = b1; h->b2 = b2;
+    return 1;
+}
+/* GeometricPrimitive::IntersectP, core/primitive.cpp:118-121. */
+static inline int prim_intersect_p(const orc_prims *P, uint32_t prim, const orc_ray *r, orc_counters *c) {
+    float t, b0, b1, b2;
+    if (c) c->prim_tests++;
+    if (!tri_isect(r->o, r->d, r->tMax, P->verts + 9 * (size_t)prim, &t, &b0, &b1, &b2)) return 0;
+    if (P->degen && P->degen[prim]) return 0;
+    return 1;
+}
+
+/* ---------------------------------- BVH ---------------------------------------------------- */
+/* LinearBVHNode, accelerators/bvh.cpp:123-152: 32 bytes. */
+typedef struct {
+    float bmin[3], bmax[3];
+    int32_t offset;    /* primitivesOffset (leaf) / secondChildOffset (interior) */
+    uint32_t word;     /* axis in bits 0-1 (3 = leaf), nPrims << 2 */
+} orc_bvh_node;
+
+/* Bounds3::IntersectP(ray, invDir, dirIsNeg), core/geometry.h:1754-1780. */
+static inline int slab_bvh(const orc_bvh_node *n, const orc_ray *r, const float invDir[3], const int neg[3]) {
+    const float *b[2] = {n->bmin, n->bmax};
+    const float k = 1 + 2 * orc_gamma(3);
+    float tMin = (b[neg[0]][0] - r->o[0]) * invDir[0];
+    float tMax = (b[1 - neg[0]][0] - r->o[0]) * invDir[0];
+    float tyMin = (b[neg[1]][1] - r->o[1]) * invDir[1];
+    float tyMax = (b[1 - neg[1]][1] - r->o[1]) * invDir[1];
+    tMax *= k;
+    tyMax *= k;
+    if (tMin > tyMax || tyMin > tMax) return 0;
+    if (tyMin > tMin) tMin = tyMin;
+    if (tyMax < tMax) tMax = tyMax;
+    float tzMin = (b[neg[2]][2] - r->o[2]) * invDir[2];
+    float tzMax = (b[1 - neg[2]][2] - r->o[2]) * invDir[2];
+    tzMax *= k;
+    if (tMin > tzMax || tzMin > tMax) return 0;
+    if (tzMin > tMin) tMin = tzMin;
+    if (tzMax < tMax) tMax = tzMax;
+    return (tMin < r->tMax) && (tMax > 0);
+}
+
+/* BVHAccel::Intersect, accelerators/bvh.cpp:354-396.  prim_order[slot] = original prim number. */
+static void bvh_closest_one(const orc_bvh_node *nodes, const uint32_t *prim_order, const orc_prims *P, orc_ray *r,
+                            orc_hit *h, orc_counters *c) {
+    h->prim = ORC_MISS; h->t = r->tMax; h->b0 = h->b1 = h->b2 = 0;
+    if (!nodes) return;
+    float invDir[3] = {1 / r->d[0], 1 / r->d[1], 1 / r->d[2]};
+    int neg[3] = {invDir[0] < 0, invDir[1] < 0, invDir[2] < 0};
+    int toVisit = 0, cur = 0;
+    int stack[64];
+    for (;;) {
+        const orc_bvh_node *n = &nodes[cur];
+        if (c) c->nodes_fetched++;
+        if (slab_bvh(n, r, invDir, neg)) {
+            if (c) c->nodes_passed++;
+            if ((n->word & 3) == 3) {
+                if (c) c->leaf_visits++;
+                uint32_t np = n->word >> 2;
+                for (uint32_t i = 0; i < np; ++i) prim_intersect(P, prim_order[n->offset + i], r, h, c);
+                if (toVisit == 0) break;
+                cur = stack[--toVisit];
+            } else {
+                if (neg[n->word & 3]) { stack[toVisit++] = cur + 1; cur = n->offset; }
+                else { stack[toVisit++] = n->offset; cur = cur + 1; }
+            }
+        } else {
+            if (toVisit == 0) break;
+            cur = stack[--toVisit];
+        }
+    }
+}
+/* BVHAccel::IntersectP, accelerators/bvh.cpp:398-437. */
+static int bvh_any_one(const orc_bvh_node *nodes, const uint32_t *prim_order, const orc_prims *P, const orc_ray *r,
+                       orc_counters *c) {
+    if (!nodes) return 0;
+    float invDir[3] = {1.f / r->d[0], 1.f / r->d[1], 1.f / r->d[2]};
+    int neg[3] = {invDir[0] < 0, invDir[1] < 0, invDir[2] < 0};
+    int toVisit = 0, cur = 0;
+    int stack[64];
+    for (;;) {
+        const orc_bvh_node *n = &nodes[cur];
+        if (c) c->nodes_fetched++;
+        if (slab_bvh(n, r, invDir, neg)) {
+            if (c) c->nodes_passed++;
+            if ((n->word & 3) == 3) {
+                if (c) c->leaf_visits++;
+                uint32_t np = n->word >> 2;
+                for (uint32_t i = 0; i < np; ++i)
+                    if (prim_intersect_p(P, prim_order[n->offset + i], r, c)) return 1;
+                if (toVisit == 0) break;
+                cur = stack[--toVisit];
+            } else {
+                if (neg[n->word & 3]) { stack[toVisit++] = cur + 1; cur = n->offset; }
+                else { stack[toVisit++] = n->offset; cur = cur + 1; }
+            }
+        } else {
+            if (toVisit == 0) break;
+            cur = stack[--toVisit];
+        }
+    }
+    return 0;
+}
+
+/* ---------------------------------- kd / RBSP / RBSPKd -------------------------------------- */
+typedef struct { uint32_t w0, w1; } orc_bsp_node; /* kdtreeaccel.cpp:146-159, rbsp.cpp:121-134 */
+typedef struct {
+    int kind;                 /* 1 kd, 2 rbsp, 3 rbspkd */
+    const orc_bsp_node *nodes;
+    const uint32_t *indices;  /* primitiveIndices */
+    const float *directions;  /* M x 3 */
+    uint32_t M;
+    float bounds[6];
+} orc_bsp_tree;
+
+/* Bounds3::IntersectP(ray,&t0,&t1), core/geometry.h:1730-1751. */
+static inline int root_clip(const float b[6], const orc_ray *r, float *hitt0, float *hitt1) {
+    float t0 = 0, t1 = r->tMax;
+    for (int i = 0; i < 3; ++i) {
+        float invRayDir = 1 / r->d[i];
+        float tNear = (b[i] - r->o[i]) * invRayDir;
+        float tFar = (b[3 + i] - r->o[i]) * invRayDir;
+        if (tNear > tFar) { float s = tNear; tNear = tFar; tFar = s; }
+        tFar *= 1 + 2 * orc_gamma(3);
+        t0 = tNear > t0 ? tNear : t0;
+        t1 = tFar < t1 ? tFar : t1;
+        if (t0 > t1) return 0;
+    }
+    *hitt0 = t0; *hitt1 = t1;
+    return 1;
+}
+/* genericBSP.cpp:11-22: getBitOffset(M) = 32 - clz(M) ; mask = (1<<off)-1. */
+static inline uint32_t bit_offset(int kind, uint32_t M) { return kind == 1 ? 2u : 32u - (uint32_t)__builtin_clz(M); }
+
+/* intersectInterior: kdtreeaccel.cpp:95-104 + geometry.h:1833-1835 (kd);
+ * rbsp.cpp:68-80 + geometry.h:1837-1843 (rbsp); rbspKd.cpp:68-92 (axis<3 fast path). */
+static inline float interior(const orc_bsp_tree *T, const orc_ray *r, const float invDir[3], uint32_t axis, float split,
+                             int *belowFirst) {
+    if (T->kind == 1 || (T->kind == 3 && axis < 3)) {
+        float tPlane = (split - r->o[axis]) * invDir[axis];
+        *belowFirst = (r->o[axis] < split) || (r->o[axis] == split && r->d[axis] <= 0);
+        return tPlane;
+    }
+    const float *dv = T->directions + 3 * axis;
+    /* Dot(), core/geometry.h:1264-1267: v1.x*v2.x + v1.y*v2.y + v1.z*v2.z */
+    float projectedO = dv[0] * r->o[0] + dv[1] * r->o[1] + dv[2] * r->o[2];
+    float inverseProjectedD = 1 / (dv[0] * r->d[0] + dv[1] * r->d[1] + dv[2] * r->d[2]);
+    *belowFirst = (projectedO < split) || (projectedO == split && inverseProjectedD <= 0);
+    return (split - projectedO) * inverseProjectedD;
+}
+
+typedef struct { uint32_t node; float tMin, tMax; } orc_todo; /* genericBSP.h:195-199 */
+
+/* KdTreeAccel::Intersect kdtreeaccel.cpp:381-452; RBSP::Intersect rbsp.cpp:405-477; RBSPKd same loop. */
+static void bsp_closest_one(const orc_bsp_tree *T, const orc_prims *P, orc_ray *r, orc_hit *h, orc_counters *c) {
+    h->prim = ORC_MISS; h->t = r->tMax; h->b0 = h->b1 = h->b2 = 0;
+    float tMin, tMax;
+    if (!root_clip(T->bounds, r, &tMin, &tMax)) return;
+    float invDir[3] = {1 / r->d[0], 1 / r->d[1], 1 / r->d[2]};
+    const uint32_t off = bit_offset(T->kind, T->M), mask = (1u << off) - 1u;
+    const uint32_t leafTag = T->kind == 1 ? 3u : T->M;
+    orc_todo todo[64];
+    uint32_t todoPos = 0, cur = 0;
+    for (;;) {
+        if (r->tMax < tMin) break;
+        if (c) c->nodes_fetched++;
+        const orc_bsp_node n = T->nodes[cur];
+        uint32_t axis = n.w1 & mask;
+        if (axis != leafTag) {
+            if (c) c->nodes_passed++;
+            float split; memcpy(&split, &n.w0, 4);
+            int belowFirst;
+            float tPlane = interior(T, r, invDir, axis, split, &belowFirst);
+            uint32_t above = n.w1 >> off, first, second;
+            if (belowFirst) { first = cur + 1; second = above; } else { first = above; second = cur + 1; }
+            if (tPlane > tMax || tPlane <= 0) cur = first;
+            else if (tPlane < tMin) cur = second;
+            else {
+                todo[todoPos].node = second; todo[todoPos].tMin = tPlane; todo[todoPos].tMax = tMax; ++todoPos;
+                cur = first; tMax = tPlane;
+            }
+        } else {
+            if (c) c->leaf_visits++;
+            uint32_t np = n.w1 >> off;
+            if (np == 1) prim_intersect(P, n.w0, r, h, c);
+            else for (uint32_t i = 0; i < np; ++i) {
+                if (c) c->index_reads++;
+                prim_intersect(P, T->indices[n.w0 + i], r, h, c);
+            }
+            if (todoPos > 0) { --todoPos; cur = todo[todoPos].node; tMin = todo[todoPos].tMin; tMax = todo[todoPos].tMax; }
+            else break;
+        }
+    }
+}
+/* KdTreeAccel::IntersectP kdtreeaccel.cpp:454-521; RBSP::IntersectP rbsp.cpp:479-547. No tMax<tMin bail-out. */
+static int bsp_any_one(const orc_bsp_tree *T, const orc_prims *P, const orc_ray *r, orc_counters *c) {
+    float tMin, tMax;
+    if (!root_clip(T->bounds, r, &tMin, &tMax)) return 0;
+    float invDir[3] = {1 / r->d[0], 1 / r->d[1], 1 / r->d[2]};
+    const uint32_t off = bit_offset(T->kind, T->M), mask = (1u << off) - 1u;
+    const uint32_t leafTag = T->kind == 1 ? 3u : T->M;
+    orc_todo todo[64];
+    uint32_t todoPos = 0, cur = 0;
+    for (;;) {
+        if (c) c->nodes_fetched++;
+        const orc_bsp_node n = T->nodes[cur];
+        uint32_t axis = n.w1 & mask;
+        if (axis == leafTag) {
+            if (c) c->leaf_visits++;
+            uint32_t np = n.w1 >> off;
+            if (np == 1) { if (prim_intersect_p(P, n.w0, r, c)) return 1; }
+            else for (uint32_t i = 0; i < np; ++i) {
+                if (c) c->index_reads++;
+                if (prim_intersect_p(P, T->indices[n.w0 + i], r, c)) return 1;
+            }
+            if (todoPos > 0) { --todoPos; cur = todo[todoPos].node; tMin = todo[todoPos].tMin; tMax = todo[todoPos].tMax; }
+            else break;
+        } else {
+            if (c) c->nodes_passed++;
+            float split; memcpy(&split, &n.w0, 4);
+            int belowFirst;
+            float tPlane = interior(T, r, invDir, axis, split, &belowFirst);
+            uint32_t above = n.w1 >> off, first, second;
+            if (belowFirst) { first = cur + 1; second = above; } else { first = above; second = cur + 1; }
+            if (tPlane > tMax || tPlane <= 0) cur = first;
+            else if (tPlane < tMin) cur = second;
+            else {
+                todo[todoPos].node = second; todo[todoPos].tMin = tPlane; todo[todoPos].tMax = tMax; ++todoPos;
+                cur = first; tMax = tPlane;
+            }
+        }
+    }
+    return 0;
+}
+
+/* ---------------------------------- batch entry points -------------------------------------- */
+#include <pthread.h>
+static void add_counters(orc_counters *dst, const orc_counters *src) {
+    dst->nodes_fetched += src->nodes_fetched; dst->nodes_passed += src->nodes_passed;
+    dst->leaf_visits += src->leaf_visits; dst->prim_tests += src->prim_tests; dst->index_reads += src->index_reads;
+}
+
+typedef struct {
+    int kind, any, want;
+    const void *nodes; const uint32_t *indices;
+    orc_prims P; orc_bsp_tree T;
+    const orc_ray *rays; uint64_t begin, end;
+    orc_hit *hits; uint8_t *occluded;
+    orc_counters *per_ray; orc_counters total;
+} orc_job;
+
+static void *run_job(void *arg) {
+    orc_job *j = (orc_job *)arg;
+    memset(&j->total, 0, sizeof(j->total));
+    for (uint64_t i = j->begin; i < j->end; ++i) {
+        orc_counters c; memset(&c, 0, sizeof(c));
+        orc_counters *cp = j->want ? &c : 0;
+        if (j->any) {
+            j->occluded[i] = (uint8_t)(j->kind == 0
+                ? bvh_any_one((const orc_bvh_node *)j->nodes, j->indices, &j->P, &j->rays[i], cp)
+                : bsp_any_one(&j->T, &j->P, &j->rays[i], cp));
+        } else {
+            orc_ray r = j->rays[i];
+            if (j->kind == 0) bvh_closest_one((const orc_bvh_node *)j->nodes, j->indices, &j->P, &r, &j->hits[i], cp);
+            else bsp_closest_one(&j->T, &j->P, &r, &j->hits[i], cp);
+        }
+        if (j->want) { c.rays = 1; add_counters(&j->total, &c); if (j->per_ray) j->per_ray[i] = c; }
+    }
+    return 0;
+}
+
+/* kind 0: nodes = orc_bvh_node[], indices = prim_order.  kind 1/2/3: orc_bsp_node[], primitiveIndices.
+ * counters (nullable) is a single accumulated struct; per_ray (nullable) gets one struct per ray. */
+static void run_batch(int any, int kind, const void *nodes, const uint32_t *indices, const float *directions,
+                      uint32_t M, const float bounds[6], const float *verts, const uint8_t *degen, uint32_t n_prims,
+                      const orc_ray *rays, uint64_t n, orc_hit *hits, uint8_t *occluded, orc_counters *counters,
+                      orc_counters *per_ray, int n_threads) {
+    if (n_threads < 1) n_threads = 1;
+    if (n_threads > 256) n_threads = 256;
+    orc_job *jobs = (orc_job *)calloc((size_t)n_threads, sizeof(orc_job));
+    pthread_t *th = (pthread_t *)calloc((size_t)n_threads, sizeof(pthread_t));
+    uint64_t chunk = (n + (uint64_t)n_threads - 1) / (uint64_t)n_threads;
+    for (int t = 0; t < n_threads; ++t) {
+        orc_job *j = &jobs[t];
+        j->kind = kind; j->any = any; j->want = counters || per_ray;
+        j->nodes = nodes; j->indices = indices;
+        j->P.verts = verts; j->P.degen = degen; j->P.n_prims = n_prims;
+        if (kind != 0) {
+            j->T.kind = kind; j->T.nodes = (const orc_bsp_node *)nodes; j->T.indices = indices;
+            j->T.directions = directions; j->T.M = M;
+            memcpy(j->T.bounds, bounds, sizeof(j->T.bounds));
+        }
+        j->rays = rays; j->hits = hits; j->occluded = occluded; j->per_ray = per_ray;
+        j->begin = (uint64_t)t * chunk < n ? (uint64_t)t * chunk : n;
+        j->end = j->begin + chunk < n ? j->begin + chunk : n;
+        if (n_threads == 1) run_job(j); else pthread_create(&th[t], 0, run_job, j);
+    }
+    orc_counters tot; memset(&tot, 0, sizeof(tot));
+    for (int t = 0; t < n_threads; ++t) {
+        if (n_threads > 1) pthread_join(th[t], 0);
+        add_counters(&tot, &jobs[t].total);
+    }
+    if (counters) { tot.rays = n; *counters = tot; }
+    free(jobs); free(th);
+}
+
+void orc_intersect_closest(int kind, const void *nodes, const uint32_t *indices, const float *directions, uint32_t M,
+                           const float bounds[6], const float *verts, const uint8_t *degen, uint32_t n_prims,
+                           const orc_ray *rays, uint64_t n, orc_hit *hits, orc_counters *counters,
+                           orc_counters *per_ray, int n_threads) {
+    run_batch(0, kind, nodes, indices, directions, M, bounds, verts, degen, n_prims, rays, n, hits, 0, counters,
+              per_ray, n_threads);
+}
+void orc_intersect_any(int kind, const void *nodes, const uint32_t *indices, const float *directions, uint32_t M,
+                       const float bounds[6], const float *verts, const uint8_t *degen, uint32_t n_prims,
+                       const orc_ray *rays, uint64_t n, uint8_t *occluded, orc_counters *counters,
+                       orc_counters *per_ray, int n_threads) {
+    run_batch(1, kind, nodes, indices, directions, M, bounds, verts, degen, n_prims, rays, n, 0, occluded, counters,
+              per_ray, n_threads);
+}
+
+void orc_degenerate_flags(const float *verts, const float *uvs, uint32_t n_prims, uint8_t *out) {
+    for (uint32_t i = 0; i < n_prims; ++i)
+        out[i] = (uint8_t)orc_tri_is_degenerate(verts + 9 * (size_t)i, uvs ? uvs + 6 * (size_t)i : 0);
+}
