@@ -145,7 +145,8 @@ static int tri_isect(const float o[3], const float dir[3], float rayTMax, const 
     return 1;
 }
 
-/* Public single-triangle entry (exact form). degenerate = orc_tri_is_degenerate() result. */
+/* Public single-triangle entry. degenerate = orc_tri_is_degenerate() result; pass 0 for the
+ * IntersectP semantics (no tail). */
 int orc_triangle(const orc_ray *r, const float *v, int degenerate, float *t, float *b0, float *b1, float *b2) {
     if (!tri_isect(r->o, r->d, r->tMax, v, t, b0, b1, b2)) return 0;
     return degenerate ? 0 : 1; /* triangle.cpp:309-315 */
@@ -173,7 +174,8 @@ static inline int prim_intersect_p(const orc_prims *P, uint32_t prim, const orc_
     float t, b0, b1, b2;
     if (c) c->prim_tests++;
     if (!tri_isect(r->o, r->d, r->tMax, P->verts + 9 * (size_t)prim, &t, &b0, &b1, &b2)) return 0;
-    if (P->degen && P->degen[prim]) return 0;
+    /* NOTE: no degenerate-triangle rejection here: Triangle::IntersectP only has it inside the
+     * alpha-mask branch (triangle.cpp:533-556), unlike Triangle::Intersect (:309-315). */
     return 1;
 }
 

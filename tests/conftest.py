@@ -1,0 +1,45 @@
+import os
+import sys
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "thesis-pbrt-v3_b200"))
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box)")
+
+
+def load_golden(name):
+    z = np.load(os.path.join(GOLDEN, name))
+    return {k: z[k] for k in z.files}
+
+
+def golden_tree(g):
+    return dict(kind=str(g["kind"]), nodes=g["nodes"], indices=g["indices"], directions=g["directions"],
+                bounds=g["bounds"], n_prims=len(g["tri_verts"]))
+
+
+SMALL = ["bvh", "kdtree", "rbsp3", "rbsp7", "rbsp13", "rbspkd13"]
+
+
+@pytest.fixture(scope="session")
+def built_lib():
+    """Builds (if needed) and loads libb200rt.so; the build is a no-op when the .so is current."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("b200rt_build", os.path.join(ROOT, "thesis-pbrt-v3_b200", "build.py"))
+    m = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(m)
+    if not os.path.exists(m.OUT) or (os.path.exists("/usr/local/cuda/bin/nvcc") and not m.up_to_date()):
+        m.build()
+    import b200rt
+    return b200rt
+
+
+@pytest.fixture(scope="session")
+def gpu(built_lib):
+    built_lib.init(0)
+    return built_lib

@@ -1,0 +1,262 @@
+"""Scene instantiation for the configs of BASELINE.json.
+
+* killeroo-simple (reference scenes/killeroo-simple): the loop-subdivided killeroo comes from the
+  committed fixture tests/golden/killeroo_mesh.npz (generated from the reference's own
+  scenes/geometry/killeroo.pbrt by tests/golden/make_golden.py through the reference's
+  LoopSubdivide); transforms, ground quads, camera and film follow the scene file.  The sphere area
+  light (scenes/killeroo-simple:20-24) is not a triangle and is left out of the aggregate.
+* sponza / museum / conference: their geometry is NOT in the reference tree, so these
+  are documented PROCEDURAL STAND-INS (fixed seed, stated triangle count); every number reported on
+  them says so.  Cameras/lights follow the scene templates (scenes/sponza:1-2,16).
+
+Everything here is host-side numpy; output = world-space triangle soup (n,9) float32 + camera."""
+import os
+import numpy as np
+
+_GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "..", "tests", "golden")
+
+
+# ---- tiny mesh toolkit -----------------------------------------------------------------------
+def _grid(nu, nv):
+    """Index list (two triangles per cell) of an (nu+1) x (nv+1) vertex grid."""
+    i, j = np.meshgrid(np.arange(nu), np.arange(nv), indexing="ij")
+    a = (i * (nv + 1) + j).ravel()
+    b, c, d = a + (nv + 1), a + (nv + 1) + 1, a + 1
+    return np.stack([np.stack([a, b, c], 1), np.stack([a, c, d], 1)], 1).reshape(-1, 3)
+
+
+def _surface(fn, nu, nv):
+    u, v = np.meshgrid(np.linspace(0, 1, nu + 1), np.linspace(0, 1, nv + 1), indexing="ij")
+    P = fn(u.ravel(), v.ravel())
+    return np.asarray(P, np.float64).reshape(-1, 3)[_grid(nu, nv)].reshape(-1, 9)
+
+
+def _box(lo, hi, n=1):
+    lo, hi = np.asarray(lo, float), np.asarray(hi, float)
+    out = []
+    for ax in range(3):
+        a, b = (ax + 1) % 3, (ax + 2) % 3
+        for side in (lo[ax], hi[ax]):
+            def f(u, v, ax=ax, a=a, b=b, side=side):
+                P = np.zeros((len(u), 3))
+                P[:, ax] = side
+                P[:, a] = lo[a] + u * (hi[a] - lo[a])
+                P[:, b] = lo[b] + v * (hi[b] - lo[b])
+                return P
+            out.append(_surface(f, n, n))
+    return np.concatenate(out)
+
+
+def _lathe(profile, cx, cz, y0, nseg, nring):
+    """Surface of revolution around the vertical axis; profile(v) -> (radius, height)."""
+    def f(u, v):
+        r, h = profile(v)
+        ang = 2 * np.pi * u
+        return np.stack([cx + r * np.cos(ang), y0 + h, cz + r * np.sin(ang)], 1)
+    return _surface(f, nseg, nring)
+
+
+def look_at_camera(eye, look, up, fov_deg, xres, yres):
+    """Perspective camera of the scene files (pbrt LookAt + `Camera "perspective" "float fov"`):
+    fov spans the SHORTER image axis (reference src/cameras/perspective.cpp:240-262)."""
+    eye, look, up = (np.asarray(a, np.float64) for a in (eye, look, up))
+    d = look - eye
+    d /= np.linalg.norm(d)
+    right = np.cross(up / np.linalg.norm(up), d)
+    right /= np.linalg.norm(right)
+    newup = np.cross(d, right)
+    aspect = xres / yres
+    t = np.tan(np.radians(fov_deg) / 2)
+    sx, sy = (aspect, 1.0) if aspect > 1 else (1.0, 1 / aspect)
+    return dict(eye=eye.astype(np.float32), dir=d.astype(np.float32), right=(right * t * sx).astype(np.float32),
+                up=(newup * t * sy).astype(np.float32), xres=int(xres), yres=int(yres))
+
+
+def camera_rays(cam, spp=1, seed=0, x0=0, x1=None, y0=0, y1=None):
+    """(n,8) float32 primary rays, row-major over the pixel window, spp jittered samples per pixel."""
+    x1 = cam["xres"] if x1 is None else x1
+    y1 = cam["yres"] if y1 is None else y1
+    rng = np.random.default_rng(seed)
+    px, py = np.meshgrid(np.arange(x0, x1), np.arange(y0, y1), indexing="xy")
+    px = np.repeat(px.ravel(), spp).astype(np.float64)
+    py = np.repeat(py.ravel(), spp).astype(np.float64)
+    jx, jy = (rng.random(len(px)), rng.random(len(px))) if spp > 1 or seed else (0.5, 0.5)
+    sx = 1 - 2 * (px + jx) / cam["xres"]   # pbrt's screen x grows to the left of `right` = up x dir
+    sy = 1 - 2 * (py + jy) / cam["yres"]
+    d = cam["dir"][None, :] + sx[:, None] * cam["right"][None, :] + sy[:, None] * cam["up"][None, :]
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    r = np.zeros((len(px), 8), np.float32)
+    r[:, 0:3] = cam["eye"]
+    r[:, 3] = np.inf
+    r[:, 4:7] = d
+    return r
+
+
+def random_rays(bounds, n, seed=12345):
+    """Rrand of SURVEY.md §8(d): origins uniform in the root bounds, directions uniform on the sphere."""
+    rng = np.random.default_rng(seed)
+    lo, hi = np.asarray(bounds[:3], np.float64), np.asarray(bounds[3:], np.float64)
+    o = lo + rng.random((n, 3)) * (hi - lo)
+    z = 1 - 2 * rng.random(n)
+    phi = 2 * np.pi * rng.random(n)
+    s = np.sqrt(np.maximum(0, 1 - z * z))
+    d = np.stack([s * np.cos(phi), s * np.sin(phi), z], 1)
+    r = np.zeros((n, 8), np.float32)
+    r[:, 0:3] = o
+    r[:, 3] = np.inf
+    r[:, 4:7] = d
+    return r
+
+
+# ---- killeroo-simple -------------------------------------------------------------------------
+def _rot_z(deg):
+    c, s = np.cos(np.radians(deg)), np.sin(np.radians(deg))
+    return np.array([[c, -s, 0, 0], [s, c, 0, 0], [0, 0, 1, 0], [0, 0, 0, 1]], float)
+
+
+def _translate(x, y, z):
+    m = np.eye(4)
+    m[:3, 3] = (x, y, z)
+    return m
+
+
+def _scale(x, y, z):
+    return np.diag([x, y, z, 1.0])
+
+
+def _xform(m, P):
+    return P @ m[:3, :3].T + m[:3, 3]
+
+
+def killeroo_mesh():
+    f = os.path.join(_GOLDEN, "killeroo_mesh.npz")
+    z = np.load(f)
+    return z["P"].astype(np.float64), z["idx"].astype(np.int64)
+
+
+def killeroo_simple(xres=700, yres=700):
+    """scenes/killeroo-simple: 2 killeroos (2 x 33 264 tris) + 2 ground quads (4 tris) = 66 532
+    triangles; camera LookAt 400 20 30 / 0 63 -110 / 0 0 1, fov 39, 700x700."""
+    P, idx = killeroo_mesh()
+    tris = []
+    # AttributeBegin Translate 0 0 -140 : two quads (scenes/killeroo-simple:27-35)
+    q1 = np.array([[-1000, -1000, 0], [1000, -1000, 0], [1000, 1000, 0], [-1000, 1000, 0]], float)
+    q2 = np.array([[-400, -1000, -1000], [-400, 1000, -1000], [-400, 1000, 1000], [-400, -1000, 1000]], float)
+    for q in (q1, q2):
+        qw = _xform(_translate(0, 0, -140), q)
+        tris.append(qw[[0, 1, 2, 2, 3, 0]].reshape(-1, 9))
+    # Scale .5 .5 .5 ; Rotate -60 0 0 1 ; Translate 100 200 -140 ; killeroo ; Translate -200 0 0 ; killeroo (:38-49)
+    ctm = _scale(.5, .5, .5) @ _rot_z(-60) @ _translate(100, 200, -140)
+    tris.append(_xform(ctm, P)[idx].reshape(-1, 9))
+    ctm = ctm @ _translate(-200, 0, 0)
+    tris.append(_xform(ctm, P)[idx].reshape(-1, 9))
+    tv = np.concatenate(tris).astype(np.float32) + np.float32(0)
+    # LookAt 400 20 30  0 63 -110  0 0 1 ; Rotate -5 0 0 1 precedes Camera and rolls the view slightly: ignored
+    cam = look_at_camera((400, 20, 30), (0, 63, -110), (0, 0, 1), 39, xres, yres)
+    return dict(name="killeroo-simple", tri_verts=tv, camera=cam, light=np.array([150, 120, 20], np.float32),
+                note="reference geometry (fixture); sphere area light replaced by a point light at its centre")
+
+
+# ---- procedural stand-ins --------------------------------------------------------------------
+def sponza_standin(seed=7, detail=1.0, xres=700, yres=700):
+    """Procedural atrium standing in for Crytek Sponza (geometry absent from the reference tree).
+    Two-storey colonnaded nave, arches, drapes, vases, displaced floor/walls, roof beams.
+    detail=1.0 gives ~262 k triangles.  Camera and point light from scenes/sponza:1-2,16."""
+    rng = np.random.default_rng(seed)
+    k = float(np.sqrt(detail))
+    n = lambda x: max(2, int(round(x * k)))
+    parts = []
+    X0, X1, Z0, Z1, H = -1.0, 1.0, -0.45, 0.45, 0.8
+    zc = 0.22  # column rows at z = +-zc
+    # floor with bumpy tiles
+    def floor(u, v):
+        x, z = X0 + u * (X1 - X0), Z0 + v * (Z1 - Z0)
+        y = 0.004 * np.sin(40 * x) * np.sin(40 * z)
+        return np.stack([x, y, z], 1)
+    parts.append(_surface(floor, n(220), n(100)))
+    # outer walls with brick relief, two long + two short
+    def wall_long(zpos, sgn):
+        def f(u, v):
+            x, y = X0 + u * (X1 - X0), v * H
+            z = zpos + sgn * 0.003 * np.sign(np.sin(60 * x + 3 * np.floor(y * 25))) * (np.sin(25 * np.pi * y) > 0)
+            return np.stack([x, y, z], 1)
+        return f
+    parts.append(_surface(wall_long(Z0, 1), n(180), n(70)))
+    parts.append(_surface(wall_long(Z1, -1), n(180), n(70)))
+    def wall_short(xpos):
+        def f(u, v):
+            z, y = Z0 + u * (Z1 - Z0), v * H
+            return np.stack([np.full_like(z, xpos), y, z], 1)
+        return f
+    parts.append(_surface(wall_short(X0), n(60), n(50)))
+    parts.append(_surface(wall_short(X1), n(60), n(50)))
+    # ceiling + gallery floors
+    parts.append(_box((X0, H, Z0), (X1, H + 0.02, Z1), n(24)))
+    for s in (-1, 1):
+        z0, z1 = (Z0, -zc) if s < 0 else (zc, Z1)
+        parts.append(_box((X0, 0.38, z0), (X1, 0.40, z1), n(30)))
+    # columns (two storeys, both sides) with entasis + fluting
+    ncol = 10
+    xs = np.linspace(X0 + 0.12, X1 - 0.12, ncol)
+    def col_profile(h, r0):
+        def p(v):
+            r = r0 * (1 - 0.15 * v) * (1 + 0.25 * np.exp(-((v - 0.02) / 0.03) ** 2) + 0.3 * np.exp(-((v - 0.98) / 0.03) ** 2))
+            return r, v * h
+        return p
+    for y0, h, r0 in ((0.0, 0.38, 0.028), (0.40, 0.36, 0.022)):
+        for x in xs:
+            for z in (-zc, zc):
+                parts.append(_lathe(col_profile(h, r0), x, z, y0, n(28), n(36)))
+    # arches between columns (half tori), both storeys
+    def arch(xa, xb, z, ytop, rt):
+        cx, R = 0.5 * (xa + xb), 0.5 * (xb - xa)
+        def f(u, v):
+            a, b = np.pi * u, 2 * np.pi * v
+            rr = R + rt * np.cos(b)
+            return np.stack([cx + rr * np.cos(a), ytop - R + rr * np.sin(a) * 0.6, z + rt * np.sin(b)], 1)
+        return _surface(f, n(20), n(8))
+    for ytop in (0.38, 0.76):
+        for i in range(ncol - 1):
+            for z in (-zc, zc):
+                parts.append(arch(xs[i], xs[i + 1], z, ytop + 0.04, 0.012))
+    # drapes hanging between upper columns
+    for i in range(0, ncol - 1, 2):
+        ph = rng.random() * 6
+        z = zc if i % 4 == 0 else -zc
+        def drape(u, v, i=i, ph=ph, z=z):
+            x = xs[i] + u * (xs[i + 1] - xs[i])
+            y = 0.70 - 0.28 * v - 0.03 * np.sin(np.pi * u)
+            zz = z + 0.02 * np.sin(18 * u + ph) * (0.3 + v)
+            return np.stack([x, y, zz], 1)
+        parts.append(_surface(drape, n(64), n(64)))
+    # vases along the nave
+    def vase_profile(v):
+        r = 0.02 + 0.025 * np.sin(np.pi * v) ** 2 + 0.01 * (v > 0.9)
+        return r, 0.10 * v
+    for x in np.linspace(X0 + 0.3, X1 - 0.3, 6):
+        for z in (-0.09, 0.09):
+            parts.append(_lathe(vase_profile, x, z, 0.0, n(32), n(24)))
+    # roof beams
+    for x in np.linspace(X0 + 0.1, X1 - 0.1, 12):
+        parts.append(_box((x - 0.012, H - 0.05, Z0), (x + 0.012, H, Z1), n(4)))
+    # lion-head-like blobs on the end wall
+    def blob(cx, cy, cz, r):
+        def f(u, v):
+            th, ph = np.pi * v, 2 * np.pi * u
+            rr = r * (1 + 0.15 * np.sin(5 * ph) * np.sin(4 * th))
+            return np.stack([cx + rr * np.sin(th) * np.cos(ph), cy + rr * np.cos(th), cz + rr * np.sin(th) * np.sin(ph)], 1)
+        return _surface(f, n(40), n(30))
+    for zz in (-0.2, 0.0, 0.2):
+        parts.append(blob(X1 - 0.03, 0.3, zz, 0.04))
+    tv = np.concatenate(parts).astype(np.float32) + np.float32(0)
+    cam = look_at_camera((-0.7, 0.45, 0.05), (0, 0.25, 0), (0, 1, 0), 42, xres, yres)
+    return dict(name="sponza-standin", tri_verts=tv, camera=cam, light=np.array([0, .5, 0], np.float32),
+                note="PROCEDURAL STAND-IN for scenes/sponza (geometry absent from the reference tree), seed=%d detail=%g, %d triangles"
+                     % (seed, detail, len(tv)))
+
+
+def soup(n, seed=1, extent=10.0, size=0.5):
+    """Random triangle soup (unit tests)."""
+    rng = np.random.default_rng(seed)
+    c = rng.uniform(-extent, extent, (n, 1, 3))
+    return (c + rng.normal(0, size, (n, 3, 3))).reshape(-1, 9).astype(np.float32) + np.float32(0)

@@ -1,0 +1,44 @@
+"""Builds libb200rt.so (CUDA kernels + C ABI + host builders) for sm_100a, in-tree.
+
+    python thesis-pbrt-v3_b200/build.py [--force] [--verbose]
+
+-fmad=false and IEEE division are part of the parity contract (csrc/rt_math.cuh)."""
+import os
+import subprocess
+import sys
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+CSRC = os.path.join(HERE, "csrc")
+OUT = os.path.join(HERE, "b200rt", "libb200rt.so")
+SOURCES = ["b200rt.cu", "wavefront.cu", "build_bvh.cpp", "build_kd.cpp"]
+NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-fmad=false",
+         "--shared", "-Xcompiler", "-fPIC,-ffp-contract=off,-fno-fast-math", "-cudart", "static"]
+
+
+def sources():
+    return [os.path.join(CSRC, s) for s in SOURCES if os.path.exists(os.path.join(CSRC, s))]
+
+
+def up_to_date():
+    if not os.path.exists(OUT):
+        return False
+    t = os.path.getmtime(OUT)
+    deps = [os.path.join(CSRC, f) for f in os.listdir(CSRC)] + [os.path.join(HERE, "..", "include", "b200rt.h"),
+                                                                 os.path.join(HERE, "..", "include", "b200rt_wavefront.h")]
+    return all(os.path.getmtime(d) <= t for d in deps if os.path.exists(d))
+
+
+def build(force=False, verbose=False):
+    if not force and up_to_date():
+        return OUT
+    cmd = [NVCC] + FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", OUT] + sources()
+    if verbose:
+        print(" ".join(cmd))
+    subprocess.check_call(cmd)
+    return OUT
+
+
+if __name__ == "__main__":
+    build(force="--force" in sys.argv, verbose="--verbose" in sys.argv)
+    print(OUT)

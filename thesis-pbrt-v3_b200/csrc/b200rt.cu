@@ -1,0 +1,410 @@
+// libb200rt.so — C ABI (include/b200rt.h): scene upload + batched Intersect / IntersectP.
+//
+// Replaces, for ray batches, Scene::Intersect / IntersectP -> Aggregate::Intersect / IntersectP
+// (reference src/core/scene.cpp:45-55 -> src/accelerators/{bvh,kdtreeaccel,rbsp,rbspKd}.cpp).
+// There is no CPU path in this file: every compute entry point needs a CUDA device.
+#include <cuda_runtime.h>
+#include <atomic>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <new>
+#include <vector>
+#include "rt_kernels.cuh"
+
+using namespace b200rt;
+
+// ---- error plumbing ---------------------------------------------------------------------------
+static thread_local char g_err[512] = "";
+static int fail(int code, const char *fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return code;
+}
+#define CU(call)                                                                                   \
+    do {                                                                                           \
+        cudaError_t e_ = (call);                                                                   \
+        if (e_ != cudaSuccess)                                                                     \
+            return fail(e_ == cudaErrorNoDevice || e_ == cudaErrorInsufficientDriver ? B200RT_ENODEVICE : B200RT_ECUDA, \
+                        "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+    } while (0)
+
+static std::atomic<uint64_t> g_launches{0};
+static int g_sm_count = 148;
+
+extern "C" const char *b200rt_last_error(void) { return g_err; }
+extern "C" int b200rt_version(void) { return B200RT_VERSION; }
+extern "C" uint64_t b200rt_launch_count(void) { return g_launches.load(); }
+
+extern "C" int b200rt_init(int device) {
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0)
+        return fail(B200RT_ENODEVICE, "no CUDA device (%s); b200rt has no CPU fallback",
+                    e == cudaSuccess ? "device count 0" : cudaGetErrorString(e));
+    if (device < 0 || device >= n) return fail(B200RT_EINVAL, "device %d out of range [0,%d)", device, n);
+    CU(cudaSetDevice(device));
+    CU(cudaFree(0));
+    cudaDeviceProp p;
+    CU(cudaGetDeviceProperties(&p, device));
+    g_sm_count = p.multiProcessorCount;
+    return B200RT_OK;
+}
+
+// ---- scene ------------------------------------------------------------------------------------
+struct b200rt_scene {
+    int kind = 0;
+    int device = 0;
+    BvhView bvh{};
+    BspView bsp{};
+    void *d_nodes = nullptr;
+    uint32_t *d_indices = nullptr;
+    float4 *d_tris = nullptr;
+    float bounds[6] = {0, 0, 0, 0, 0, 0};
+    uint32_t n_prims = 0;
+    bool empty = false;  // zero primitives: every ray misses (bvh.cpp:355 `if (!nodes) return false`)
+    // staging for host-pointer calls
+    std::mutex mu;
+    void *d_stage_in = nullptr, *d_stage_out = nullptr;
+    size_t stage_in_bytes = 0, stage_out_bytes = 0;
+    Counters *d_counters = nullptr;
+};
+
+// Triangle::Intersect's tail (triangle.cpp:294-315) rejects EVERY hit on a triangle whose UV
+// parameterisation is degenerate (or dpdu x dpdv == 0) and whose geometric normal is zero.  It
+// depends on the triangle only, so it becomes a per-triangle flag computed once at upload, in the
+// same float/double arithmetic (host compiler: no contraction for these expressions, see build.py).
+static bool tri_tail_rejects(const float *v, const float *uv) {
+    static const float kDefault[6] = {0, 0, 1, 0, 1, 1};  // Triangle::GetUVs, triangle.h:109-121
+    if (!uv) uv = kDefault;
+    const float *p0 = v, *p1 = v + 3, *p2 = v + 6;
+    volatile float duv02x = uv[0] - uv[4], duv02y = uv[1] - uv[5];
+    volatile float duv12x = uv[2] - uv[4], duv12y = uv[3] - uv[5];
+    float dp02[3], dp12[3];
+    for (int i = 0; i < 3; ++i) { dp02[i] = p0[i] - p2[i]; dp12[i] = p1[i] - p2[i]; }
+    volatile float m0 = duv02x * duv12y, m1 = duv02y * duv12x;
+    const float determinant = m0 - m1;
+    const bool degenerateUV = std::fabs(determinant) < 1e-8;
+    bool need = degenerateUV;
+    if (!need) {
+        const float invdet = 1 / determinant;
+        float dpdu[3], dpdv[3];
+        for (int i = 0; i < 3; ++i) {
+            volatile float a = duv12y * dp02[i], b = duv02y * dp12[i];
+            volatile float du = a - b;
+            dpdu[i] = du * invdet;
+            volatile float c = -duv12x * dp02[i], d = duv02x * dp12[i];
+            volatile float dv = c + d;
+            dpdv[i] = dv * invdet;
+        }
+        // Cross() in double then narrowed (geometry.h:1287-1293); products of two floats are exact in double
+        const double ax = dpdu[0], ay = dpdu[1], az = dpdu[2], bx = dpdv[0], by = dpdv[1], bz = dpdv[2];
+        const float cx = (float)((ay * bz) - (az * by)), cy = (float)((az * bx) - (ax * bz)),
+                    cz = (float)((ax * by) - (ay * bx));
+        volatile float xx = cx * cx, yy = cy * cy, zz = cz * cz;
+        volatile float s = xx + yy;
+        need = (s + zz) == 0;
+    }
+    if (!need) return false;
+    float e0[3], e1[3];
+    for (int i = 0; i < 3; ++i) { e0[i] = p2[i] - p0[i]; e1[i] = p1[i] - p0[i]; }
+    const double ax = e0[0], ay = e0[1], az = e0[2], bx = e1[0], by = e1[1], bz = e1[2];
+    const float nx = (float)((ay * bz) - (az * by)), ny = (float)((az * bx) - (ax * bz)),
+                nz = (float)((ax * by) - (ay * bx));
+    volatile float xx = nx * nx, yy = ny * ny, zz = nz * nz;
+    volatile float s = xx + yy;
+    return (s + zz) == 0;
+}
+
+static void fill_record(float4 *rec, const float *v, uint32_t prim, uint32_t flags) {
+    rec[0] = make_float4(v[0], v[1], v[2], 0.f);
+    rec[1] = make_float4(v[3], v[4], v[5], 0.f);
+    rec[2] = make_float4(v[6], v[7], v[8], 0.f);
+    std::memcpy(&rec[0].w, &prim, 4);
+    std::memcpy(&rec[1].w, &flags, 4);
+}
+
+struct RefBvhNode {  // LinearBVHNode, bvh.cpp:123-152
+    float lo[3], hi[3];
+    int32_t offset;
+    uint32_t word;
+};
+
+static int build_bvh_scene(const b200rt_scene_desc *d, b200rt_scene *s) {
+    const RefBvhNode *ref = (const RefBvhNode *)d->nodes;
+    const uint32_t N = d->node_count;
+    if (d->n_indices != d->n_prims) return fail(B200RT_EINVAL, "BVH: n_indices (%u) must equal n_prims (%u)", d->n_indices, d->n_prims);
+    // pass 1: validate + number the interior nodes (depth-first order = array order)
+    std::vector<uint32_t> wide(N, 0xFFFFFFFFu);
+    uint32_t nInterior = 0;
+    for (uint32_t i = 0; i < N; ++i) {
+        const bool leaf = (ref[i].word & 3u) == 3u;
+        if (leaf) {
+            const uint64_t np = ref[i].word >> 2, off = (uint32_t)ref[i].offset;
+            if (np == 0 || ref[i].offset < 0 || off + np > d->n_prims)
+                return fail(B200RT_EINVAL, "BVH leaf %u: primitive range [%lld,+%llu) outside %u prims", i, (long long)ref[i].offset, (unsigned long long)np, d->n_prims);
+        } else {
+            if (i + 1 >= N || ref[i].offset <= (int32_t)i + 1 || (uint32_t)ref[i].offset >= N)
+                return fail(B200RT_EINVAL, "BVH interior node %u: bad child offsets (second=%d, nodes=%u)", i, ref[i].offset, N);
+            wide[i] = nInterior++;
+        }
+    }
+    // depth check (the reference's traversal stack holds 64 entries, bvh.cpp:362)
+    {
+        std::vector<uint32_t> depth(N, 0);
+        uint32_t maxDepth = 0;
+        depth[0] = 0;
+        for (uint32_t i = 0; i < N; ++i) {
+            if ((ref[i].word & 3u) != 3u) {
+                depth[i + 1] = depth[i] + 1;
+                depth[ref[i].offset] = depth[i] + 1;
+                if (depth[i] + 1 > maxDepth) maxDepth = depth[i] + 1;
+            }
+        }
+        if (maxDepth > 64) return fail(B200RT_EUNSUPPORTED, "BVH depth %u exceeds the reference's 64-entry traversal stack", maxDepth);
+    }
+    // triangles in slot order, flagged at leaf ends
+    std::vector<float4> recs((size_t)3 * d->n_prims);
+    std::vector<uint8_t> last(d->n_prims, 0);
+    for (uint32_t i = 0; i < N; ++i)
+        if ((ref[i].word & 3u) == 3u) last[(uint32_t)ref[i].offset + (ref[i].word >> 2) - 1] = 1;
+    last[d->n_prims - 1] = 1;  // a leaf walk can never run past the array, whatever the input tree says
+    for (uint32_t slot = 0; slot < d->n_prims; ++slot) {
+        const uint32_t prim = d->prim_indices[slot];
+        if (prim >= d->n_prims) return fail(B200RT_EINVAL, "BVH prim_indices[%u] = %u out of range", slot, prim);
+        const float *v = d->tri_verts + 9 * (size_t)prim;
+        uint32_t flags = last[slot] ? B200RT_TRI_LAST : 0u;
+        if (tri_tail_rejects(v, d->tri_uvs ? d->tri_uvs + 6 * (size_t)prim : nullptr)) flags |= B200RT_TRI_DEGENERATE;
+        fill_record(&recs[3 * (size_t)slot], v, prim, flags);
+    }
+    auto ref_of = [&](uint32_t i) -> uint32_t {
+        return (ref[i].word & 3u) == 3u ? (B200RT_LEAF_BIT | (uint32_t)ref[i].offset) : wide[i];
+    };
+    std::vector<BvhNode2> nodes(nInterior ? nInterior : 1);
+    std::memset(nodes.data(), 0, nodes.size() * sizeof(BvhNode2));
+    for (uint32_t i = 0; i < N; ++i) {
+        if ((ref[i].word & 3u) == 3u) continue;
+        const RefBvhNode &c0 = ref[i + 1], &c1 = ref[ref[i].offset];
+        BvhNode2 &w = nodes[wide[i]];
+        w.a = make_float4(c0.lo[0], c0.lo[1], c0.lo[2], c0.hi[0]);
+        w.b = make_float4(c0.hi[1], c0.hi[2], c1.lo[0], c1.lo[1]);
+        w.c = make_float4(c1.lo[2], c1.hi[0], c1.hi[1], c1.hi[2]);
+        w.m = make_uint4(ref_of(i + 1), ref_of((uint32_t)ref[i].offset), ref[i].word & 3u, ref[i].word >> 2);
+    }
+    CU(cudaMalloc(&s->d_nodes, nodes.size() * sizeof(BvhNode2)));
+    CU(cudaMemcpy(s->d_nodes, nodes.data(), nodes.size() * sizeof(BvhNode2), cudaMemcpyHostToDevice));
+    CU(cudaMalloc(&s->d_tris, recs.size() * sizeof(float4)));
+    CU(cudaMemcpy(s->d_tris, recs.data(), recs.size() * sizeof(float4), cudaMemcpyHostToDevice));
+    s->bvh.nodes = (const BvhNode2 *)s->d_nodes;
+    s->bvh.tris = s->d_tris;
+    for (int k = 0; k < 3; ++k) { s->bvh.root[k] = ref[0].lo[k]; s->bvh.root[3 + k] = ref[0].hi[k]; }
+    s->bvh.rootRef = ref_of(0);
+    std::memcpy(s->bounds, s->bvh.root, sizeof(s->bounds));
+    return B200RT_OK;
+}
+
+static int build_bsp_scene(const b200rt_scene_desc *d, b200rt_scene *s) {
+    const uint2 *ref = (const uint2 *)d->nodes;
+    const uint32_t N = d->node_count;
+    const int kind = (int)d->kind;
+    uint32_t M = 3;
+    if (kind != B200RT_KDTREE) {
+        M = d->n_directions;
+        if (!d->directions || M < 1 || M > 13) return fail(B200RT_EINVAL, "RBSP: need 1..13 directions (got %u)", M);
+    }
+    const uint32_t off = kind == B200RT_KDTREE ? 2u : 32u - (uint32_t)__builtin_clz(M);  // genericBSP.cpp:11-22
+    const uint32_t mask = (1u << off) - 1u, leafTag = kind == B200RT_KDTREE ? 3u : M;
+    // validate + depth (todo stack of 64, kdtreeaccel.cpp:391)
+    std::vector<uint32_t> depth(N, 0);
+    uint32_t maxDepth = 0;
+    for (uint32_t i = 0; i < N; ++i) {
+        const uint32_t axis = ref[i].y & mask;
+        if (axis == leafTag) {
+            const uint64_t np = ref[i].y >> off;
+            if (np == 1) { if (ref[i].x >= d->n_prims) return fail(B200RT_EINVAL, "leaf %u: primitive %u out of range", i, ref[i].x); }
+            else if (np > 1 && (uint64_t)ref[i].x + np > d->n_indices) return fail(B200RT_EINVAL, "leaf %u: index range out of bounds", i);
+        } else {
+            const uint32_t above = ref[i].y >> off;
+            if (axis >= M || i + 1 >= N || above <= i + 1 || above >= N)
+                return fail(B200RT_EINVAL, "interior node %u: bad axis/children (axis=%u above=%u nodes=%u)", i, axis, above, N);
+            depth[i + 1] = depth[above] = depth[i] + 1;
+            if (depth[i] + 1 > maxDepth) maxDepth = depth[i] + 1;
+        }
+    }
+    if (maxDepth > 64) return fail(B200RT_EUNSUPPORTED, "tree depth %u exceeds the reference's 64-entry todo stack", maxDepth);
+    for (uint32_t i = 0; i < d->n_indices; ++i)
+        if (d->prim_indices[i] >= d->n_prims) return fail(B200RT_EINVAL, "prim_indices[%u] out of range", i);
+    std::vector<float4> recs((size_t)3 * d->n_prims);
+    for (uint32_t p = 0; p < d->n_prims; ++p) {
+        const float *v = d->tri_verts + 9 * (size_t)p;
+        uint32_t flags = tri_tail_rejects(v, d->tri_uvs ? d->tri_uvs + 6 * (size_t)p : nullptr) ? B200RT_TRI_DEGENERATE : 0u;
+        fill_record(&recs[3 * (size_t)p], v, p, flags);
+    }
+    CU(cudaMalloc(&s->d_nodes, (size_t)N * 8));
+    CU(cudaMemcpy(s->d_nodes, ref, (size_t)N * 8, cudaMemcpyHostToDevice));
+    CU(cudaMalloc(&s->d_indices, std::max<size_t>(1, d->n_indices) * 4));
+    if (d->n_indices) CU(cudaMemcpy(s->d_indices, d->prim_indices, (size_t)d->n_indices * 4, cudaMemcpyHostToDevice));
+    CU(cudaMalloc(&s->d_tris, std::max<size_t>(1, recs.size()) * sizeof(float4)));
+    if (!recs.empty()) CU(cudaMemcpy(s->d_tris, recs.data(), recs.size() * sizeof(float4), cudaMemcpyHostToDevice));
+    s->bsp.nodes = (const uint2 *)s->d_nodes;
+    s->bsp.indices = s->d_indices;
+    s->bsp.tris = s->d_tris;
+    std::memcpy(s->bsp.bounds, d->bounds, sizeof(s->bsp.bounds));
+    std::memset(s->bsp.dirs, 0, sizeof(s->bsp.dirs));
+    if (kind == B200RT_KDTREE) { s->bsp.dirs[0] = s->bsp.dirs[4] = s->bsp.dirs[8] = 1.f; }
+    else std::memcpy(s->bsp.dirs, d->directions, sizeof(float) * 3 * M);
+    s->bsp.M = M; s->bsp.bitOffset = off; s->bsp.bitMask = mask; s->bsp.leafTag = leafTag; s->bsp.kind = kind;
+    std::memcpy(s->bounds, d->bounds, sizeof(s->bounds));
+    return B200RT_OK;
+}
+
+extern "C" int b200rt_scene_create(const b200rt_scene_desc *d, b200rt_scene **out) {
+    if (!d || !out) return fail(B200RT_EINVAL, "null argument");
+    *out = nullptr;
+    if (d->kind > B200RT_RBSPKD) return fail(B200RT_EINVAL, "unknown accelerator kind %u", d->kind);
+    if (d->n_prims && !d->tri_verts) return fail(B200RT_EINVAL, "tri_verts is null");
+    if (d->node_count && !d->nodes) return fail(B200RT_EINVAL, "nodes is null");
+    if (d->n_indices && !d->prim_indices) return fail(B200RT_EINVAL, "prim_indices is null");
+    int dev = 0;
+    CU(cudaGetDevice(&dev));
+    b200rt_scene *s = new (std::nothrow) b200rt_scene;
+    if (!s) return fail(B200RT_ENOMEM, "out of host memory");
+    s->kind = (int)d->kind;
+    s->device = dev;
+    s->n_prims = d->n_prims;
+    int rc = B200RT_OK;
+    if (d->node_count == 0 || d->n_prims == 0) s->empty = true;
+    else rc = d->kind == B200RT_BVH ? build_bvh_scene(d, s) : build_bsp_scene(d, s);
+    if (rc == B200RT_OK) {
+        cudaError_t e = cudaMalloc(&s->d_counters, sizeof(Counters));
+        if (e != cudaSuccess) rc = fail(B200RT_ECUDA, "cudaMalloc(counters): %s", cudaGetErrorString(e));
+    }
+    if (rc != B200RT_OK) { b200rt_scene_destroy(s); return rc; }
+    *out = s;
+    return B200RT_OK;
+}
+
+extern "C" void b200rt_scene_destroy(b200rt_scene *s) {
+    if (!s) return;
+    cudaFree(s->d_nodes); cudaFree(s->d_indices); cudaFree(s->d_tris);
+    cudaFree(s->d_stage_in); cudaFree(s->d_stage_out); cudaFree(s->d_counters);
+    delete s;
+}
+
+extern "C" int b200rt_scene_bounds(const b200rt_scene *s, float out[6]) {
+    if (!s || !out) return fail(B200RT_EINVAL, "null argument");
+    std::memcpy(out, s->bounds, sizeof(s->bounds));
+    return B200RT_OK;
+}
+
+// ---- launches -----------------------------------------------------------------------------------
+static bool is_device_ptr(const void *p) {
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return false; }
+    return a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged;
+}
+
+template <bool ANY, bool COUNT>
+static void launch_kind(const b200rt_scene *s, const float4 *rays, uint64_t n, b200rt_hit *hits, uint8_t *occ,
+                        Counters *cnt, cudaStream_t st) {
+    const uint64_t blocks64 = (n + B200RT_BLOCK - 1) / B200RT_BLOCK;
+    const unsigned blocks = (unsigned)std::min<uint64_t>(blocks64, (uint64_t)g_sm_count * 64);
+    switch (s->kind) {
+        case B200RT_BVH: trace_kernel<B200RT_BVH, ANY, COUNT><<<blocks, B200RT_BLOCK, 0, st>>>(s->bvh, s->bsp, rays, n, hits, occ, cnt); break;
+        case B200RT_KDTREE: trace_kernel<B200RT_KDTREE, ANY, COUNT><<<blocks, B200RT_BLOCK, 0, st>>>(s->bvh, s->bsp, rays, n, hits, occ, cnt); break;
+        case B200RT_RBSP: trace_kernel<B200RT_RBSP, ANY, COUNT><<<blocks, B200RT_BLOCK, 0, st>>>(s->bvh, s->bsp, rays, n, hits, occ, cnt); break;
+        default: trace_kernel<B200RT_RBSPKD, ANY, COUNT><<<blocks, B200RT_BLOCK, 0, st>>>(s->bvh, s->bsp, rays, n, hits, occ, cnt); break;
+    }
+    g_launches.fetch_add(1);
+}
+
+// Fills the result for an empty scene (every ray misses) without touching a tree.
+__global__ void miss_kernel(const float4 *__restrict__ rays, uint64_t n, b200rt_hit *hits, uint8_t *occ) {
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    if (occ) occ[i] = 0;
+    if (hits) {
+        b200rt_hit h;
+        h.prim = B200RT_MISS; h.t = rays[2 * i].w; h.b0 = h.b1 = h.b2 = 0.f;
+        hits[i] = h;
+    }
+}
+
+static int ensure(void **p, size_t *have, size_t want) {
+    if (*have >= want) return B200RT_OK;
+    cudaFree(*p);
+    *p = nullptr; *have = 0;
+    CU(cudaMalloc(p, want));
+    *have = want;
+    return B200RT_OK;
+}
+
+static int run(b200rt_scene *s, const b200rt_ray *rays, uint64_t n, b200rt_hit *hits, uint8_t *occ, bool any,
+               b200rt_counters *counters, void *stream) {
+    if (!s) return fail(B200RT_EINVAL, "null scene");
+    if (n == 0) { if (counters) std::memset(counters, 0, sizeof(*counters)); return B200RT_OK; }
+    if (!rays || (any ? !occ : !hits)) return fail(B200RT_EINVAL, "null ray/result buffer");
+    cudaStream_t st = (cudaStream_t)stream;
+    const bool rays_dev = is_device_ptr(rays);
+    const void *outp = any ? (const void *)occ : (const void *)hits;
+    const bool out_dev = is_device_ptr(outp);
+    const size_t out_elem = any ? 1 : sizeof(b200rt_hit);
+    std::unique_lock<std::mutex> lock(s->mu, std::defer_lock);
+    const float4 *d_rays = (const float4 *)rays;
+    void *d_out = (void *)outp;
+    if (!rays_dev || !out_dev || counters) lock.lock();
+    if (!rays_dev) {
+        int rc = ensure(&s->d_stage_in, &s->stage_in_bytes, n * sizeof(b200rt_ray));
+        if (rc) return rc;
+        CU(cudaMemcpyAsync(s->d_stage_in, rays, n * sizeof(b200rt_ray), cudaMemcpyHostToDevice, st));
+        d_rays = (const float4 *)s->d_stage_in;
+    }
+    if (!out_dev) {
+        int rc = ensure(&s->d_stage_out, &s->stage_out_bytes, n * out_elem);
+        if (rc) return rc;
+        d_out = s->d_stage_out;
+    }
+    if (counters) CU(cudaMemsetAsync(s->d_counters, 0, sizeof(Counters), st));
+    if (s->empty) {
+        miss_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(d_rays, n, any ? nullptr : (b200rt_hit *)d_out, any ? (uint8_t *)d_out : nullptr);
+        g_launches.fetch_add(1);
+    } else if (any) {
+        if (counters) launch_kind<true, true>(s, d_rays, n, nullptr, (uint8_t *)d_out, s->d_counters, st);
+        else launch_kind<true, false>(s, d_rays, n, nullptr, (uint8_t *)d_out, nullptr, st);
+    } else {
+        if (counters) launch_kind<false, true>(s, d_rays, n, (b200rt_hit *)d_out, nullptr, s->d_counters, st);
+        else launch_kind<false, false>(s, d_rays, n, (b200rt_hit *)d_out, nullptr, nullptr, st);
+    }
+    CU(cudaGetLastError());
+    if (!out_dev) CU(cudaMemcpyAsync((void *)outp, d_out, n * out_elem, cudaMemcpyDeviceToHost, st));
+    if (counters) {
+        Counters c;
+        CU(cudaMemcpyAsync(&c, s->d_counters, sizeof(c), cudaMemcpyDeviceToHost, st));
+        CU(cudaStreamSynchronize(st));
+        counters->rays = s->empty ? n : c.rays; counters->nodes_fetched = c.nodes_fetched; counters->nodes_passed = c.nodes_passed;
+        counters->leaf_visits = c.leaf_visits; counters->prim_tests = c.prim_tests; counters->index_reads = c.index_reads;
+    } else if (!rays_dev || !out_dev) {
+        CU(cudaStreamSynchronize(st));
+    }
+    return B200RT_OK;
+}
+
+extern "C" int b200rt_intersect_closest(b200rt_scene *s, const b200rt_ray *rays, uint64_t n, b200rt_hit *hits, void *stream) {
+    return run(s, rays, n, hits, nullptr, false, nullptr, stream);
+}
+extern "C" int b200rt_intersect_any(b200rt_scene *s, const b200rt_ray *rays, uint64_t n, uint8_t *occ, void *stream) {
+    return run(s, rays, n, nullptr, occ, true, nullptr, stream);
+}
+extern "C" int b200rt_intersect_closest_counted(b200rt_scene *s, const b200rt_ray *rays, uint64_t n, b200rt_hit *hits,
+                                                b200rt_counters *c, void *stream) {
+    if (!c) return fail(B200RT_EINVAL, "null counters");
+    return run(s, rays, n, hits, nullptr, false, c, stream);
+}
+extern "C" int b200rt_intersect_any_counted(b200rt_scene *s, const b200rt_ray *rays, uint64_t n, uint8_t *occ,
+                                            b200rt_counters *c, void *stream) {
+    if (!c) return fail(B200RT_EINVAL, "null counters");
+    return run(s, rays, n, nullptr, occ, true, c, stream);
+}
