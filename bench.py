@@ -1,0 +1,389 @@
+#!/usr/bin/env python
+"""bench.py — the measurement contract of this repo.
+
+    python bench.py --gpus N --steps K --warmup W            (one rank per GPU under torchrun for N>1)
+    python bench.py --impl reference --gpus N --steps K --warmup W
+
+Metric (BASELINE.json): Mrays/s (closest-hit + shadow any-hit) per GPU and frame time.
+Workload (configs[1]): sponza (PROCEDURAL STAND-IN — the geometry is absent from the reference tree),
+BVHAccel, path integrator maxdepth 5, wavefront closest-hit + shadow rays; the scene template's own
+700x700 film at 64 spp (reference scenes/sponza:4,10).
+
+A step = one whole frame: every rank renders its tiles (tile t -> rank t % N of the reference's 16x16
+tile grid) through the wavefront driver, then the film is gathered to rank 0 over NCCL.
+  value   = rays traced by all ranks (closest + shadow) / max-over-ranks device time     [Mrays/s]
+  e2e     = the same ray queues pushed through the C ABI from pinned HOST buffers, copies timed
+  roofline= closest-hit kernel: algorithmic bytes / CUDA-event kernel time vs HBM peak
+  cpu_baseline = the reference's own Intersect/IntersectP (oracle/_ref) on the host cores, bounded sample
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "thesis-pbrt-v3_b200"))
+
+METRIC = "Mrays/s (closest-hit + shadow any-hit), whole frame, all GPUs"
+UNIT = "Mrays/s"
+XRES, YRES, SPP, MAXDEPTH = 700, 700, 64, 5
+LIGHT_I = (1.0, 1.0, 1.0)
+KD = (0.5, 0.5, 0.5)
+
+
+def workload_name(spp=SPP):
+    return ("sponza-standin(procedural, seed 7) BVHAccel(sweep-SAH) path maxdepth %d, %dx%d @ %d spp, point light, "
+            "matte; wavefront closest+shadow queues" % (MAXDEPTH, XRES, YRES, spp))
+
+
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+# ---- clocks sampling during the timed region ----------------------------------------------------
+class ClockSampler:
+    Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._pump, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for ln in self.proc.stdout:
+            self.lines.append(ln.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.12)
+        self.proc.terminate()
+        self.t.join(timeout=2)
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 6:
+                continue
+            try:
+                sm.append(float(f[0]))
+                mx = float(f[1])
+            except ValueError:
+                continue
+            for k, nm in enumerate(names):
+                if f[2 + k].lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+# ---- host-side (numpy) wavefront used ONLY by the reference arm to produce the same kind of ray queues
+def numpy_queues(intersect, cam, light, spp, maxdepth, seed, tri_verts, x0, x1, y0, y1):
+    """Camera / bounce / shadow queues of the path integrator for a pixel window, with `intersect`
+    answering closest-hit queries.  Returns [(kind, rays)], kind in {"closest", "shadow"}."""
+    from b200rt import scenes
+    rng = np.random.default_rng(seed)
+    rays = scenes.camera_rays(cam, spp=spp, seed=seed + 1, x0=x0, x1=x1, y0=y0, y1=y1)
+    out = []
+    tv = tri_verts.reshape(-1, 3, 3)
+    for depth in range(maxdepth + 1):
+        out.append(("closest", rays))
+        if depth == maxdepth or len(rays) == 0:
+            break
+        prim, t = intersect(rays)
+        m = prim >= 0
+        o, d, t, prim = rays[m, 0:3], rays[m, 4:7], t[m], prim[m]
+        p = o + t[:, None] * d
+        v = tv[prim]
+        n = np.cross(v[:, 0] - v[:, 2], v[:, 1] - v[:, 2])
+        n /= np.maximum(np.linalg.norm(n, axis=1, keepdims=True), 1e-30)
+        n = np.where((np.sum(n * -d, 1) < 0)[:, None], -n, n)
+        eps = 1e-4 * np.maximum(1.0, np.abs(p).max(1, keepdims=True))
+        wl = light[None, :] - p
+        lit = np.sum(n * wl, 1) > 0
+        so = p[lit] + n[lit] * eps[lit]
+        sh = np.zeros((lit.sum(), 8), np.float32)
+        sh[:, 0:3], sh[:, 4:7], sh[:, 3] = so, light[None, :] - so, 1 - 1e-4
+        out.append(("shadow", sh))
+        u0, u1 = rng.random(len(p)), rng.random(len(p))
+        r, ph = np.sqrt(u0), 2 * np.pi * u1
+        a = np.where(np.abs(n[:, :1]) > 0.9, np.array([[0, 1, 0]]), np.array([[1, 0, 0]]))
+        s = np.cross(a, n)
+        s /= np.linalg.norm(s, axis=1, keepdims=True)
+        tt = np.cross(n, s)
+        wi = s * (r * np.cos(ph))[:, None] + tt * (r * np.sin(ph))[:, None] + n * np.sqrt(np.maximum(0, 1 - u0))[:, None]
+        nr = np.zeros((len(p), 8), np.float32)
+        nr[:, 0:3], nr[:, 4:7], nr[:, 3] = p + n * eps, wi, np.inf
+        rays = nr
+    return out
+
+
+def build_reference_accel(tri_verts):
+    """The reference's own BVHAccel on the same triangles (oracle/_ref), or the oracle port."""
+    from oracle import refbind as rb, orcbind as ob
+    n = len(tri_verts)
+    if rb.available():
+        sc = rb.RefScene(tri_verts.reshape(-1, 3), np.arange(3 * n, dtype=np.int32).reshape(-1, 3))
+        acc = rb.RefAccel(sc, "bvh")
+        return "reference", acc, (lambda r, th: acc.intersect(r, n_threads=th)), (lambda r, th: acc.intersect_p(r, n_threads=th))
+    import b200rt
+    tree = b200rt.build_bvh(tri_verts)
+    acc = ob.OracleAccel(tree, tri_verts)
+    return "port", acc, (lambda r, th: acc.intersect(r, n_threads=th)), (lambda r, th: acc.intersect_p(r, n_threads=th))
+
+
+def time_cpu(queues, isect, isect_p, threads):
+    t0 = time.perf_counter()
+    n = 0
+    for kind, rays in queues:
+        if len(rays) == 0:
+            continue
+        (isect if kind == "closest" else isect_p)(rays, threads)
+        n += len(rays)
+    return n, time.perf_counter() - t0
+
+
+# ---- reference arm ------------------------------------------------------------------------------
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from b200rt import scenes
+    sc = scenes.sponza_standin()
+    tv = sc["tri_verts"]
+    threads = os.cpu_count() or 1
+    kind, acc, isect, isect_p = build_reference_accel(tv)
+    cam = sc["camera"]
+
+    def closest(r):
+        h = isect(r, threads)
+        return (h["prim"].astype(np.int64) if kind == "reference"
+                else np.where(h["prim"] == 0xFFFFFFFF, -1, h["prim"].astype(np.int64))), h["t"]
+    # bounded sample of the workload: a centred 256x256 window at 2 spp -> ~0.6 M rays per step
+    w = 128
+    queues = numpy_queues(closest, cam, sc["light"], 2, MAXDEPTH, 1, tv, XRES // 2 - w, XRES // 2 + w, YRES // 2 - w, YRES // 2 + w)
+    for _ in range(args.warmup):
+        time_cpu(queues, isect, isect_p, threads)
+    tot_n, tot_t = 0, 0.0
+    for _ in range(args.steps):
+        n, t = time_cpu(queues, isect, isect_p, threads)
+        tot_n += n
+        tot_t += t
+    v = tot_n / tot_t / 1e6
+    sample = "%d rays/step: path queues (closest+shadow, maxdepth %d) of a centred %dx%d window at 2 spp" % (
+        tot_n // max(1, args.steps), MAXDEPTH, 2 * w, 2 * w)
+    line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": 1e3 * tot_t / max(1, args.steps), "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": workload_name(), "l2": "n/a (CPU)"},
+            "cpu_baseline": {"value": v, "unit": UNIT, "cores": threads, "kind": kind, "sample": sample},
+            "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+# ---- our arm ------------------------------------------------------------------------------------
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200rt", choices=["b200rt", "reference"])
+    ap.add_argument("--spp", type=int, default=SPP)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+
+    import torch
+    import torch.distributed as dist
+    import b200rt
+    from b200rt import scenes, wavefront as wf
+    from b200rt.film import FilmGather
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    b200rt.init(local)
+    dev = torch.device("cuda", local)
+    torch.zeros(1, device=dev)
+    stream = torch.cuda.current_stream().cuda_stream
+
+    sc = scenes.sponza_standin()
+    tv = sc["tri_verts"]
+    accel = b200rt.MakeAccelerator("bvh", tv)
+    integ = b200rt.WavefrontPathIntegrator(sc["camera"], spp=args.spp, maxdepth=MAXDEPTH, light_pos=sc["light"],
+                                           light_I=LIGHT_I, kd=KD, rank=rank, world=world, seed=1)
+    film = torch.zeros(integ.shape, dtype=torch.float32, device=dev)
+    gather = FilmGather(XRES, YRES, 16, rank, world, dev)
+
+    def step():
+        film.zero_()
+        st = integ.render_ptr(accel, film.data_ptr(), stream)
+        gather.gather(film)
+        return st
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(3, args.warmup)):
+        st = step()
+    barrier()
+    clocks = ClockSampler(local)
+    if rank == 0:
+        clocks.start()
+    launches0 = b200rt.launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    agg = {"closest_rays": 0, "shadow_rays": 0, "camera_rays": 0, "ms_closest": 0.0, "ms_any": 0.0, "launches": 0,
+           "launches_closest": 0, "launches_any": 0}
+    for _ in range(args.steps):
+        st = step()
+        for k in agg:
+            agg[k] += st[k]
+    e1.record()
+    barrier()
+    ms = e0.elapsed_time(e1)
+    launches = b200rt.launch_count() - launches0
+    clk = clocks.stop() if rank == 0 else None
+    t = torch.tensor([ms, float(agg["closest_rays"]), float(agg["shadow_rays"]), agg["ms_closest"], agg["ms_any"],
+                      float(launches)], dtype=torch.float64, device=dev)
+    if world > 1:
+        tmax = t.clone()
+        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+        tsum = t.clone()
+        dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
+    else:
+        tmax, tsum = t, t
+    ms_max = float(tmax[0])
+    rays_total = float(tsum[1] + tsum[2])
+    value = rays_total / (ms_max * 1e-3) / 1e6
+
+    line = None
+    if rank == 0:
+        # ---- roofline of the dominant kernel (closest-hit BVH trace) on rank 0's own launches ----
+        wf.keep_queues(accel, True)
+        step()
+        torch.cuda.synchronize()
+        wf.keep_queues(accel, False)
+        peak, peak_src = load_peaks()
+        nq = 2 * (MAXDEPTH + 1)
+        alg_bytes_closest, n_closest_kept, fetch, tests, rays_c = 0.0, 0, 0, 0, 0
+        kept = {}
+        for q in range(nq):
+            n = wf.queue_count(accel, q)
+            if n == 0:
+                continue
+            buf = torch.empty((n, 8), dtype=torch.float32, device=dev)
+            wf.queue_rays(accel, q, buf.data_ptr())
+            kept[q] = buf
+        from oracle import orcbind as ob
+        orc = ob.OracleAccel(accel.tree, tv)
+        checked = True
+        for q, buf in kept.items():
+            if q % 2 == 0:  # closest queues: exact traversal counters from the instrumented kernel
+                host = buf.cpu().numpy()
+                _, c = accel.Intersect(host, counters=True)
+                fetch += c["nodes_fetched"]; tests += c["prim_tests"]; rays_c += c["rays"]
+                if q in (0, 2):  # counters cross-checked against the CPU oracle on a bounded sample
+                    smp = host[:: max(1, len(host) // 100000)][:100000]
+                    _, cg = accel.Intersect(smp, counters=True)
+                    _, co = orc.intersect(smp, counters=True, n_threads=os.cpu_count() or 1)
+                    checked &= all(cg[f] == int(co[f]) for f in ("nodes_fetched", "nodes_passed", "prim_tests"))
+        # B_ray = 32 (ray in) + 20 (hit out) + 32 * N_fetch + 36 * N_tri   (BVH closest)
+        b_ray = 32 + 20 + 32.0 * fetch / max(1, rays_c) + 36.0 * tests / max(1, rays_c)
+        n_launch_closest = agg["launches_closest"]
+        closest_rays_rank0 = agg["closest_rays"]
+        avg_ms = agg["ms_closest"] / max(1, n_launch_closest)
+        achieved = (b_ray * closest_rays_rank0 / max(1, n_launch_closest)) / (avg_ms * 1e-3) / 1e9 if avg_ms > 0 else 0.0
+        roofline = {"bound": "hbm", "kernel": "trace_kernel<BVH,closest>", "achieved": achieved, "peak": peak,
+                    "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                    "bytes_per_ray": b_ray, "n_fetch_per_ray": fetch / max(1, rays_c), "n_tri_per_ray": tests / max(1, rays_c),
+                    "avg_launch_ms": avg_ms, "launches": n_launch_closest,
+                    "closest_kernel_mrays_s": closest_rays_rank0 / max(1e-9, agg["ms_closest"]) / 1e3,
+                    "any_kernel_mrays_s": agg["shadow_rays"] / max(1e-9, agg["ms_any"]) / 1e3,
+                    "kernel_share_of_step": (agg["ms_closest"] + agg["ms_any"]) / ms,
+                    "counters_checked_vs_oracle": bool(checked),
+                    "note": "node+triangle arrays (~40 MB) are L2-resident; HBM fraction understates memory-system load"}
+        # ---- e2e: the same queues through the C ABI from pinned host memory -------------------
+        hq = {q: b.cpu().pin_memory() for q, b in kept.items()}
+        outs = {q: (torch.empty((len(b), 5), dtype=torch.int32).pin_memory() if q % 2 == 0
+                    else torch.empty(len(b), dtype=torch.uint8).pin_memory()) for q, b in hq.items()}
+
+        def e2e_pass():
+            for q, b in hq.items():
+                if q % 2 == 0:
+                    accel.intersect_ptr(b.data_ptr(), len(b), outs[q].data_ptr(), stream)
+                else:
+                    accel.intersect_p_ptr(b.data_ptr(), len(b), outs[q].data_ptr(), stream)
+        for _ in range(3):
+            e2e_pass()
+        torch.cuda.synchronize()
+        a, b_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        reps = 3
+        for _ in range(reps):
+            e2e_pass()
+        b_.record()
+        torch.cuda.synchronize()
+        e2e_ms = a.elapsed_time(b_) / reps
+        n_e2e = sum(len(b) for b in hq.values())
+        h2d = sum(len(b) * 32 for b in hq.values())
+        d2h = sum(len(b) * (20 if q % 2 == 0 else 1) for q, b in hq.items())
+        e2e = {"value": n_e2e / (e2e_ms * 1e-3) / 1e6, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+               "rays_per_step": n_e2e, "ms_per_step": e2e_ms,
+               "what": "b200rt_intersect_closest/any on the frame's last-batch ray queues, pinned HOST rays in, HOST hits out"}
+        # ---- cpu_baseline: the reference's own code on the host cores, bounded sample ----------
+        cpu = None
+        if not args.no_cpu_baseline:
+            threads = os.cpu_count() or 1
+            kind, racc, isect, isect_p = build_reference_accel(tv)
+            budget = 3_000_000
+            total = sum(len(b) for b in hq.values())
+            stride = max(1, total // budget)
+            sample = [("closest" if q % 2 == 0 else "shadow", b.numpy()[::stride]) for q, b in hq.items()]
+            time_cpu(sample[:1], isect, isect_p, threads)
+            n, tsec = time_cpu(sample, isect, isect_p, threads)
+            cpu = {"value": n / tsec / 1e6, "unit": UNIT, "cores": threads, "kind": kind,
+                   "sample": "every %d-th ray of the last batch's %d queues (%d rays), %s BVHAccel::Intersect/IntersectP"
+                             % (stride, len(hq), n, "reference's own" if kind == "reference" else "oracle port of the")}
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup),
+                "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+                "dtype": "f32", "data": "synthetic",
+                "config": {"workload": workload_name(args.spp), "triangles": int(len(tv)),
+                           "l2": "ray/hit queues are ~0.5 GB per wavefront batch (> 126 MB L2) and rewritten every step",
+                           "parallelism": "tiles%%%d" % world, "rays_per_frame": rays_total / args.steps},
+                "frame_ms": ms_max / args.steps, "clocks": clk, "e2e": e2e, "gpu_launches": int(float(tsum[5])),
+                "roofline": roofline, "cpu_baseline": cpu}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,80 @@
+/*
+ * b200rt_wavefront.h — C ABI of the wavefront path-tracing driver.
+ *
+ * Restructures the reference's per-tile, per-pixel, per-sample loop
+ *   SamplerIntegrator::Render            src/core/integrator.cpp:230-360
+ *   PathIntegrator::Li                   src/integrators/path.cpp:64-204
+ *   UniformSampleOneLight/EstimateDirect src/core/integrator.cpp:86-217
+ *   VisibilityTester::Unoccluded         src/core/light.cpp:59-64
+ * into device-resident ray batches: camera rays -> closest-hit queue -> shade -> (shadow any-hit
+ * queue, bounce closest-hit queue) -> ... up to maxdepth, with warp-ballot queue compaction.
+ *
+ * Shading subset (what the config scenes' templates need around the traversal): perspective camera
+ * (src/cameras/perspective.cpp), one point light (src/lights/point.cpp), Lambertian "matte" material
+ * (src/materials/matte.cpp), box pixel filter, Russian roulette of path.cpp:190-199.  Samples come
+ * from a counter-based hash of (pixel, sample, dimension), so the image does not depend on the
+ * execution order, the batch size or the number of GPUs.
+ *
+ * Image tiles are the reference's 16x16 tile grid (integrator.cpp:237-239); a rank renders the tiles
+ * with `tile_index % world == rank`.
+ */
+#ifndef B200RT_WAVEFRONT_H
+#define B200RT_WAVEFRONT_H
+#include "b200rt.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct {
+    float eye[3];
+    float dir[3];    /* unit view direction */
+    float right[3];  /* screen-x half extent at distance 1 (already scaled by tan(fov/2) and aspect) */
+    float up[3];     /* screen-y half extent at distance 1 */
+    uint32_t xres, yres;
+} b200rt_camera;
+
+typedef struct {
+    b200rt_camera camera;
+    uint32_t spp;        /* Sampler "pixelsamples" */
+    uint32_t max_depth;  /* Integrator "path" "maxdepth" (path.cpp:110) */
+    float light_pos[3];  /* LightSource "point" "from" */
+    float light_I[3];    /* "I" */
+    float kd[3];         /* Material "matte" "Kd" */
+    uint32_t tile_size;  /* 16 in the reference (integrator.cpp:237) */
+    uint32_t rank, world; /* this process renders tiles t with t % world == rank */
+    uint32_t seed;
+    uint32_t max_batch;  /* paths in flight per wavefront (0 = default 1<<22) */
+} b200rt_render_desc;
+
+typedef struct {
+    uint64_t camera_rays;   /* = paths started */
+    uint64_t closest_rays;  /* rays through Aggregate::Intersect (camera + bounce) */
+    uint64_t shadow_rays;   /* rays through Aggregate::IntersectP */
+    uint64_t launches;      /* kernels launched by this call */
+    float ms_closest;       /* CUDA-event time inside the closest-hit kernels */
+    float ms_any;           /* ... inside the any-hit kernels */
+    float ms_total;         /* whole call on the stream */
+    uint32_t n_tiles;       /* tiles rendered by this rank */
+    uint32_t launches_closest, launches_any; /* traversal-kernel launches behind ms_closest / ms_any */
+} b200rt_render_stats;
+
+/* Number of tiles / pixels rank `rank` of `world` owns for this camera and tile size. */
+int b200rt_render_tiles(const b200rt_render_desc *desc, uint32_t *n_tiles, uint64_t *n_pixels);
+
+/* Renders this rank's tiles.  film: DEVICE or HOST buffer of xres*yres*4 floats (sum R, sum G,
+ * sum B, sum weight per pixel — Film's Pixel accumulators, src/core/film.h:85-92); pixels of other
+ * ranks' tiles are left untouched.  stats may be NULL. */
+int b200rt_render(b200rt_scene *scene, const b200rt_render_desc *desc, float *film, b200rt_render_stats *stats,
+                  void *stream);
+
+/* Dumps the ray queues of the LAST b200rt_render batch of this scene (the real closest/shadow mix)
+ * for kernel benchmarking: queue q = 2*depth (closest) or 2*depth+1 (shadow).  Pass rays = NULL to
+ * query the count.  rays: HOST or DEVICE buffer of *n b200rt_ray. */
+int b200rt_render_queue(b200rt_scene *scene, uint32_t queue, b200rt_ray *rays, uint64_t *n);
+int b200rt_render_keep_queues(b200rt_scene *scene, int keep); /* enable recording (off by default) */
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -11,5 +11,7 @@ checks can run), but every compute call raises B200RTError without a CUDA device
 from .api import (B200RTError, B200Accel, MakeAccelerator, RAY_DTYPE, HIT_DTYPE, MISS, lib, lib_path,
                   build_bvh, build_kdtree, make_rays, init, launch_count, KINDS)
 
-__all__ = ["B200RTError", "B200Accel", "MakeAccelerator", "RAY_DTYPE", "HIT_DTYPE", "MISS", "lib", "lib_path",
+from .wavefront import WavefrontPathIntegrator, film_to_rgb  # noqa: E402
+
+__all__ = ["WavefrontPathIntegrator", "film_to_rgb", "B200RTError", "B200Accel", "MakeAccelerator", "RAY_DTYPE", "HIT_DTYPE", "MISS", "lib", "lib_path",
            "build_bvh", "build_kdtree", "make_rays", "init", "launch_count", "KINDS"]

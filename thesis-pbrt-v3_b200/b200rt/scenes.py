@@ -158,10 +158,10 @@ def killeroo_simple(xres=700, yres=700):
 
 
 # ---- procedural stand-ins --------------------------------------------------------------------
-def sponza_standin(seed=7, detail=1.0, xres=700, yres=700):
+def sponza_standin(seed=7, detail=0.885, xres=700, yres=700):
     """Procedural atrium standing in for Crytek Sponza (geometry absent from the reference tree).
     Two-storey colonnaded nave, arches, drapes, vases, displaced floor/walls, roof beams.
-    detail=1.0 gives ~262 k triangles.  Camera and point light from scenes/sponza:1-2,16."""
+    the default detail gives ~262 k triangles.  Camera and point light from scenes/sponza:1-2,16."""
     rng = np.random.default_rng(seed)
     k = float(np.sqrt(detail))
     n = lambda x: max(2, int(round(x * k)))

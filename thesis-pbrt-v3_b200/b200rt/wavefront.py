@@ -1,0 +1,107 @@
+"""Host mirror of the reference's integrator entry for the hot path: `Integrator::Render(scene)`
+(src/core/integrator.h:57, SamplerIntegrator::Render src/core/integrator.cpp:230-360) with the
+"path" integrator's parameters (src/integrators/path.cpp:206-240), over include/b200rt_wavefront.h."""
+import ctypes as C
+import numpy as np
+from . import api
+
+
+class Camera(C.Structure):
+    _fields_ = [("eye", C.c_float * 3), ("dir", C.c_float * 3), ("right", C.c_float * 3), ("up", C.c_float * 3),
+                ("xres", C.c_uint32), ("yres", C.c_uint32)]
+
+
+class RenderDesc(C.Structure):
+    _fields_ = [("camera", Camera), ("spp", C.c_uint32), ("max_depth", C.c_uint32), ("light_pos", C.c_float * 3),
+                ("light_I", C.c_float * 3), ("kd", C.c_float * 3), ("tile_size", C.c_uint32), ("rank", C.c_uint32),
+                ("world", C.c_uint32), ("seed", C.c_uint32), ("max_batch", C.c_uint32)]
+
+
+class RenderStats(C.Structure):
+    _fields_ = [("camera_rays", C.c_uint64), ("closest_rays", C.c_uint64), ("shadow_rays", C.c_uint64),
+                ("launches", C.c_uint64), ("ms_closest", C.c_float), ("ms_any", C.c_float), ("ms_total", C.c_float),
+                ("n_tiles", C.c_uint32), ("launches_closest", C.c_uint32), ("launches_any", C.c_uint32)]
+
+
+_bound = False
+
+
+def _lib():
+    global _bound
+    L = api.lib()
+    if not _bound:
+        L.b200rt_render.argtypes = [C.c_void_p, C.POINTER(RenderDesc), C.c_void_p, C.POINTER(RenderStats), C.c_void_p]
+        L.b200rt_render_tiles.argtypes = [C.POINTER(RenderDesc), C.POINTER(C.c_uint32), C.POINTER(C.c_uint64)]
+        L.b200rt_render_keep_queues.argtypes = [C.c_void_p, C.c_int]
+        L.b200rt_render_queue.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.POINTER(C.c_uint64)]
+        _bound = True
+    return L
+
+
+class WavefrontPathIntegrator:
+    """Integrator "path" "integer maxdepth" [...] restructured as a wavefront (see module docstring).
+
+    render(accel) -> film (yres, xres, 4) float32 = per-pixel (sum R, sum G, sum B, sum weight) for
+    this rank's tiles (tile t belongs to rank t % world); stats as a dict."""
+
+    def __init__(self, camera, spp=8, maxdepth=5, light_pos=(0, 0, 0), light_I=(1, 1, 1), kd=(.5, .5, .5),
+                 rank=0, world=1, seed=0, tile_size=16, max_batch=0):
+        d = RenderDesc()
+        for k in ("eye", "dir", "right", "up"):
+            setattr(d.camera, k, (C.c_float * 3)(*[float(x) for x in camera[k]]))
+        d.camera.xres, d.camera.yres = int(camera["xres"]), int(camera["yres"])
+        d.spp, d.max_depth = int(spp), int(maxdepth)
+        d.light_pos = (C.c_float * 3)(*[float(x) for x in light_pos])
+        d.light_I = (C.c_float * 3)(*[float(x) for x in light_I])
+        d.kd = (C.c_float * 3)(*[float(x) for x in kd])
+        d.tile_size, d.rank, d.world, d.seed, d.max_batch = tile_size, rank, world, seed, max_batch
+        self.desc = d
+
+    @property
+    def shape(self):
+        return (self.desc.camera.yres, self.desc.camera.xres, 4)
+
+    def tiles(self):
+        n, px = C.c_uint32(), C.c_uint64()
+        api._check(_lib().b200rt_render_tiles(C.byref(self.desc), C.byref(n), C.byref(px)))
+        return n.value, px.value
+
+    def render_ptr(self, accel, film_ptr, stream=None):
+        """film_ptr: device (or host) pointer to xres*yres*4 floats, accumulated into."""
+        st = RenderStats()
+        api._check(_lib().b200rt_render(accel._h, C.byref(self.desc), film_ptr, C.byref(st), stream))
+        return {f: getattr(st, f) for f, _ in RenderStats._fields_}
+
+    def Render(self, accel, stream=None):
+        film = np.zeros(self.shape, np.float32)
+        stats = self.render_ptr(accel, film.ctypes.data_as(C.c_void_p), stream)
+        return film, stats
+
+
+def keep_queues(accel, keep=True):
+    api._check(_lib().b200rt_render_keep_queues(accel._h, int(keep)))
+
+
+def queue_count(accel, q):
+    n = C.c_uint64()
+    api._check(_lib().b200rt_render_queue(accel._h, q, None, C.byref(n)))
+    return n.value
+
+
+def queue_rays(accel, q, ptr=None):
+    """Rays of queue q (2*depth = closest, 2*depth+1 = shadow) of the last rendered batch.  With
+    ptr=None returns a host (n,8) array; else copies into the given device pointer."""
+    n = C.c_uint64(queue_count(accel, q))
+    if ptr is not None:
+        api._check(_lib().b200rt_render_queue(accel._h, q, ptr, C.byref(n)))
+        return n.value
+    out = np.zeros((n.value, 8), np.float32)
+    if n.value:
+        api._check(_lib().b200rt_render_queue(accel._h, q, out.ctypes.data_as(C.c_void_p), C.byref(n)))
+    return out
+
+
+def film_to_rgb(film):
+    """Film::WriteImage normalisation (src/core/film.cpp:266-305): rgb = sum / weight."""
+    w = np.maximum(film[..., 3:4], 1e-20)
+    return np.where(film[..., 3:4] > 0, film[..., :3] / w, 0.0).astype(np.float32)

@@ -12,6 +12,7 @@
 #include <new>
 #include <vector>
 #include "rt_kernels.cuh"
+#include "scene_internal.h"
 
 using namespace b200rt;
 
@@ -32,8 +33,16 @@ static int fail(int code, const char *fmt, ...) {
                         "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
     } while (0)
 
-static std::atomic<uint64_t> g_launches{0};
-static int g_sm_count = 148;
+int b200rt::set_error(int code, const char *fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return code;
+}
+
+std::atomic<uint64_t> g_launches{0};
+int g_sm_count = 148;
 
 extern "C" const char *b200rt_last_error(void) { return g_err; }
 extern "C" int b200rt_version(void) { return B200RT_VERSION; }
@@ -53,25 +62,6 @@ extern "C" int b200rt_init(int device) {
     g_sm_count = p.multiProcessorCount;
     return B200RT_OK;
 }
-
-// ---- scene ------------------------------------------------------------------------------------
-struct b200rt_scene {
-    int kind = 0;
-    int device = 0;
-    BvhView bvh{};
-    BspView bsp{};
-    void *d_nodes = nullptr;
-    uint32_t *d_indices = nullptr;
-    float4 *d_tris = nullptr;
-    float bounds[6] = {0, 0, 0, 0, 0, 0};
-    uint32_t n_prims = 0;
-    bool empty = false;  // zero primitives: every ray misses (bvh.cpp:355 `if (!nodes) return false`)
-    // staging for host-pointer calls
-    std::mutex mu;
-    void *d_stage_in = nullptr, *d_stage_out = nullptr;
-    size_t stage_in_bytes = 0, stage_out_bytes = 0;
-    Counters *d_counters = nullptr;
-};
 
 // Triangle::Intersect's tail (triangle.cpp:294-315) rejects EVERY hit on a triangle whose UV
 // parameterisation is degenerate (or dpdu x dpdv == 0) and whose geometric normal is zero.  It
@@ -198,6 +188,13 @@ static int build_bvh_scene(const b200rt_scene_desc *d, b200rt_scene *s) {
     CU(cudaMemcpy(s->d_nodes, nodes.data(), nodes.size() * sizeof(BvhNode2), cudaMemcpyHostToDevice));
     CU(cudaMalloc(&s->d_tris, recs.size() * sizeof(float4)));
     CU(cudaMemcpy(s->d_tris, recs.data(), recs.size() * sizeof(float4), cudaMemcpyHostToDevice));
+    {   // original-primitive-order copy for the shading stage (hit.prim indexes this)
+        std::vector<float4> byPrim((size_t)3 * d->n_prims);
+        for (uint32_t slot = 0; slot < d->n_prims; ++slot)
+            std::memcpy(&byPrim[3 * (size_t)d->prim_indices[slot]], &recs[3 * (size_t)slot], 3 * sizeof(float4));
+        CU(cudaMalloc(&s->d_prim_tris, byPrim.size() * sizeof(float4)));
+        CU(cudaMemcpy(s->d_prim_tris, byPrim.data(), byPrim.size() * sizeof(float4), cudaMemcpyHostToDevice));
+    }
     s->bvh.nodes = (const BvhNode2 *)s->d_nodes;
     s->bvh.tris = s->d_tris;
     for (int k = 0; k < 3; ++k) { s->bvh.root[k] = ref[0].lo[k]; s->bvh.root[3 + k] = ref[0].hi[k]; }
@@ -252,6 +249,7 @@ static int build_bsp_scene(const b200rt_scene_desc *d, b200rt_scene *s) {
     s->bsp.nodes = (const uint2 *)s->d_nodes;
     s->bsp.indices = s->d_indices;
     s->bsp.tris = s->d_tris;
+    s->d_prim_tris = s->d_tris;
     std::memcpy(s->bsp.bounds, d->bounds, sizeof(s->bsp.bounds));
     std::memset(s->bsp.dirs, 0, sizeof(s->bsp.dirs));
     if (kind == B200RT_KDTREE) { s->bsp.dirs[0] = s->bsp.dirs[4] = s->bsp.dirs[8] = 1.f; }
@@ -289,6 +287,8 @@ extern "C" int b200rt_scene_create(const b200rt_scene_desc *d, b200rt_scene **ou
 
 extern "C" void b200rt_scene_destroy(b200rt_scene *s) {
     if (!s) return;
+    b200rt_wavefront_release(s);
+    if (s->d_prim_tris != s->d_tris) cudaFree(s->d_prim_tris);
     cudaFree(s->d_nodes); cudaFree(s->d_indices); cudaFree(s->d_tris);
     cudaFree(s->d_stage_in); cudaFree(s->d_stage_out); cudaFree(s->d_counters);
     delete s;
@@ -308,15 +308,15 @@ static bool is_device_ptr(const void *p) {
 }
 
 template <bool ANY, bool COUNT>
-static void launch_kind(const b200rt_scene *s, const float4 *rays, uint64_t n, b200rt_hit *hits, uint8_t *occ,
-                        Counters *cnt, cudaStream_t st) {
+static void launch_kind(const b200rt_scene *s, const float4 *rays, uint64_t n, const uint32_t *n_dev, b200rt_hit *hits,
+                        uint8_t *occ, Counters *cnt, cudaStream_t st) {
     const uint64_t blocks64 = (n + B200RT_BLOCK - 1) / B200RT_BLOCK;
     const unsigned blocks = (unsigned)std::min<uint64_t>(blocks64, (uint64_t)g_sm_count * 64);
     switch (s->kind) {
-        case B200RT_BVH: trace_kernel<B200RT_BVH, ANY, COUNT><<<blocks, B200RT_BLOCK, 0, st>>>(s->bvh, s->bsp, rays, n, hits, occ, cnt); break;
-        case B200RT_KDTREE: trace_kernel<B200RT_KDTREE, ANY, COUNT><<<blocks, B200RT_BLOCK, 0, st>>>(s->bvh, s->bsp, rays, n, hits, occ, cnt); break;
-        case B200RT_RBSP: trace_kernel<B200RT_RBSP, ANY, COUNT><<<blocks, B200RT_BLOCK, 0, st>>>(s->bvh, s->bsp, rays, n, hits, occ, cnt); break;
-        default: trace_kernel<B200RT_RBSPKD, ANY, COUNT><<<blocks, B200RT_BLOCK, 0, st>>>(s->bvh, s->bsp, rays, n, hits, occ, cnt); break;
+        case B200RT_BVH: trace_kernel<B200RT_BVH, ANY, COUNT><<<blocks, B200RT_BLOCK, 0, st>>>(s->bvh, s->bsp, rays, n, n_dev, hits, occ, cnt); break;
+        case B200RT_KDTREE: trace_kernel<B200RT_KDTREE, ANY, COUNT><<<blocks, B200RT_BLOCK, 0, st>>>(s->bvh, s->bsp, rays, n, n_dev, hits, occ, cnt); break;
+        case B200RT_RBSP: trace_kernel<B200RT_RBSP, ANY, COUNT><<<blocks, B200RT_BLOCK, 0, st>>>(s->bvh, s->bsp, rays, n, n_dev, hits, occ, cnt); break;
+        default: trace_kernel<B200RT_RBSPKD, ANY, COUNT><<<blocks, B200RT_BLOCK, 0, st>>>(s->bvh, s->bsp, rays, n, n_dev, hits, occ, cnt); break;
     }
     g_launches.fetch_add(1);
 }
@@ -331,6 +331,23 @@ __global__ void miss_kernel(const float4 *__restrict__ rays, uint64_t n, b200rt_
         h.prim = B200RT_MISS; h.t = rays[2 * i].w; h.b0 = h.b1 = h.b2 = 0.f;
         hits[i] = h;
     }
+}
+
+int b200rt::launch_trace(const b200rt_scene *s, const float4 *rays, uint64_t n, const uint32_t *n_dev, b200rt_hit *hits,
+                         uint8_t *occ, bool any, Counters *counters, cudaStream_t st) {
+    if (n == 0) return B200RT_OK;
+    if (s->empty) {
+        miss_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(rays, n, any ? nullptr : hits, any ? occ : nullptr);
+        g_launches.fetch_add(1);
+    } else if (any) {
+        if (counters) launch_kind<true, true>(s, rays, n, n_dev, nullptr, occ, counters, st);
+        else launch_kind<true, false>(s, rays, n, n_dev, nullptr, occ, nullptr, st);
+    } else {
+        if (counters) launch_kind<false, true>(s, rays, n, n_dev, hits, nullptr, counters, st);
+        else launch_kind<false, false>(s, rays, n, n_dev, hits, nullptr, nullptr, st);
+    }
+    CU(cudaGetLastError());
+    return B200RT_OK;
 }
 
 static int ensure(void **p, size_t *have, size_t want) {
@@ -368,15 +385,10 @@ static int run(b200rt_scene *s, const b200rt_ray *rays, uint64_t n, b200rt_hit *
         d_out = s->d_stage_out;
     }
     if (counters) CU(cudaMemsetAsync(s->d_counters, 0, sizeof(Counters), st));
-    if (s->empty) {
-        miss_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(d_rays, n, any ? nullptr : (b200rt_hit *)d_out, any ? (uint8_t *)d_out : nullptr);
-        g_launches.fetch_add(1);
-    } else if (any) {
-        if (counters) launch_kind<true, true>(s, d_rays, n, nullptr, (uint8_t *)d_out, s->d_counters, st);
-        else launch_kind<true, false>(s, d_rays, n, nullptr, (uint8_t *)d_out, nullptr, st);
-    } else {
-        if (counters) launch_kind<false, true>(s, d_rays, n, (b200rt_hit *)d_out, nullptr, s->d_counters, st);
-        else launch_kind<false, false>(s, d_rays, n, (b200rt_hit *)d_out, nullptr, nullptr, st);
+    {
+        int rc = launch_trace(s, d_rays, n, nullptr, any ? nullptr : (b200rt_hit *)d_out, any ? (uint8_t *)d_out : nullptr, any,
+                              counters ? s->d_counters : nullptr, st);
+        if (rc) return rc;
     }
     CU(cudaGetLastError());
     if (!out_dev) CU(cudaMemcpyAsync((void *)outp, d_out, n * out_elem, cudaMemcpyDeviceToHost, st));

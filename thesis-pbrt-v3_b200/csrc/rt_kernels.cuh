@@ -236,8 +236,10 @@ __device__ __forceinline__ bool bsp_trace(const BspView &S, RayCtx &r, HitRec &h
 template <int KIND, bool ANY, bool COUNT>
 __global__ void __launch_bounds__(B200RT_BLOCK)
 trace_kernel(const __grid_constant__ BvhView bvh, const __grid_constant__ BspView bsp, const float4 *__restrict__ rays,
-             uint64_t n, b200rt_hit *__restrict__ hits, uint8_t *__restrict__ occluded, Counters *counters) {
+             uint64_t n, const uint32_t *__restrict__ n_dev, b200rt_hit *__restrict__ hits,
+             uint8_t *__restrict__ occluded, Counters *counters) {
     LocalCount cnt;
+    if (n_dev) { const uint64_t m = *n_dev; n = m < n ? m : n; }
     const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
     for (uint64_t base = (uint64_t)blockIdx.x * blockDim.x; base < n; base += stride) {
         const uint64_t i = base + threadIdx.x;

@@ -1,0 +1,35 @@
+// Internal: the scene object behind the opaque b200rt_scene handle, shared by b200rt.cu and wavefront.cu.
+#pragma once
+#include <mutex>
+#include "rt_kernels.cuh"
+
+struct b200rt_scene {
+    int kind = 0;
+    int device = 0;
+    b200rt::BvhView bvh{};
+    b200rt::BspView bsp{};
+    void *d_nodes = nullptr;
+    uint32_t *d_indices = nullptr;
+    float4 *d_tris = nullptr;       // traversal order (BVH: leaf slots; kd/RBSP: original primitive order)
+    float4 *d_prim_tris = nullptr;  // original primitive order, for the shading stage (== d_tris for kd/RBSP)
+    float bounds[6] = {0, 0, 0, 0, 0, 0};
+    uint32_t n_prims = 0;
+    bool empty = false;  // zero primitives: every ray misses (bvh.cpp:355 `if (!nodes) return false`)
+    // staging for host-pointer calls
+    std::mutex mu;
+    void *d_stage_in = nullptr, *d_stage_out = nullptr;
+    size_t stage_in_bytes = 0, stage_out_bytes = 0;
+    b200rt::Counters *d_counters = nullptr;
+};
+
+
+// frees the wavefront workspace attached to a scene (wavefront.cu)
+void b200rt_wavefront_release(const b200rt_scene *s);
+
+namespace b200rt {
+// Launches the traversal kernel on device-resident buffers.  n_dev (nullable): device-side ray count
+// (queue sizes produced by the wavefront stages) — the kernel traces min(n, *n_dev) rays.
+int launch_trace(const b200rt_scene *s, const float4 *rays, uint64_t n, const uint32_t *n_dev, b200rt_hit *hits,
+                 uint8_t *occ, bool any, Counters *counters, cudaStream_t st);
+int set_error(int code, const char *fmt, ...);
+}  // namespace b200rt

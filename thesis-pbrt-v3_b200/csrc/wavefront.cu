@@ -1,0 +1,492 @@
+// Wavefront path-tracing driver (include/b200rt_wavefront.h).
+//
+// SamplerIntegrator::Render's tile/pixel/sample loops (reference src/core/integrator.cpp:230-360)
+// and PathIntegrator::Li's bounce loop (src/integrators/path.cpp:64-204) restructured into
+// device-resident ray queues.  Per wavefront step:
+//   closest-hit queue --trace--> hits --shade--> { shadow queue --any-hit--> resolve , next closest queue }
+// Queue sizes live on the device (no host round trip inside a batch); queues are compacted with
+// warp ballots + one atomic per warp.
+#include <cuda_runtime.h>
+#include <algorithm>
+#include <atomic>
+#include <cstring>
+#include <vector>
+#include "../../include/b200rt_wavefront.h"
+#include "scene_internal.h"
+
+using namespace b200rt;
+
+extern std::atomic<uint64_t> g_launches;
+extern int g_sm_count;
+
+#define WCU(call)                                                                                   \
+    do {                                                                                            \
+        cudaError_t e_ = (call);                                                                    \
+        if (e_ != cudaSuccess)                                                                      \
+            return set_error(B200RT_ECUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+    } while (0)
+
+namespace {
+
+constexpr float kPi = 3.14159265358979323846f;
+constexpr float kInvPi = 0.31830988618379067154f;
+constexpr float kShadowEpsilon = 0.0001f;  // pbrt.h:204
+constexpr float kGamma7 = rt_gamma(7);
+
+struct Tiling {
+    uint32_t xres, yres, tile, ntx, nty, rank, world, spp;
+    uint32_t n_tiles_rank;      // tiles owned by this rank
+    uint64_t n_paths_rank;      // n_tiles_rank * tile^2 * spp (incl. slots outside the image on edge tiles)
+};
+
+struct WfParams {
+    b200rt_camera cam;
+    Tiling tl;
+    float light_pos[3], light_I[3], kd[3];
+    uint32_t max_depth, seed;
+};
+
+// ---- counter-based sampler: value = hash(seed, pixel, sample, dimension) ------------------------
+__device__ __forceinline__ uint32_t mix32(uint32_t x) {
+    x ^= x >> 16; x *= 0x7feb352dU; x ^= x >> 15; x *= 0x846ca68bU; x ^= x >> 16;
+    return x;
+}
+__device__ __forceinline__ float rnd(uint32_t seed, uint32_t pixel, uint32_t sample, uint32_t dim) {
+    uint32_t h = mix32(seed ^ 0x9e3779b9U);
+    h = mix32(h ^ pixel);
+    h = mix32(h + sample * 0x85ebca6bU);
+    h = mix32(h ^ (dim * 0xc2b2ae35U + 0x27d4eb2fU));
+    return (h >> 8) * 5.9604644775390625e-08f;  // [0,1)
+}
+
+// path slot -> (pixel x, y, sample); false when the slot lies outside the image (edge tiles)
+__device__ __forceinline__ bool path_pixel(const Tiling &t, uint64_t gpath, uint32_t &x, uint32_t &y, uint32_t &s) {
+    const uint32_t tp = t.tile * t.tile;
+    const uint64_t pixOrd = gpath / t.spp;
+    s = (uint32_t)(gpath % t.spp);
+    const uint32_t tileOrd = (uint32_t)(pixOrd / tp), inTile = (uint32_t)(pixOrd % tp);
+    const uint32_t tileIdx = t.rank + tileOrd * t.world;  // tiles t with t % world == rank
+    const uint32_t tx = tileIdx % t.ntx, ty = tileIdx / t.ntx;
+    x = tx * t.tile + inTile % t.tile;
+    y = ty * t.tile + inTile / t.tile;
+    return ty < t.nty && x < t.xres && y < t.yres;
+}
+
+// warp-aggregated queue append: one atomic per warp (ballot + popc + shuffle)
+__device__ __forceinline__ uint32_t warp_append(bool pred, uint32_t *counter) {
+    const unsigned m = __ballot_sync(0xFFFFFFFFu, pred);
+    if (m == 0) return 0;
+    const int lane = threadIdx.x & 31, leader = __ffs(m) - 1;
+    uint32_t base = 0;
+    if (lane == leader) base = atomicAdd(counter, (uint32_t)__popc(m));
+    base = __shfl_sync(0xFFFFFFFFu, base, leader);
+    return base + __popc(m & ((1u << lane) - 1u));
+}
+
+// NextFloatUp / NextFloatDown, pbrt.h:207-253
+__device__ __forceinline__ float next_up(float v) {
+    if (isinf(v) && v > 0.f) return v;
+    if (v == -0.f) v = 0.f;
+    uint32_t ui = __float_as_uint(v);
+    if (v >= 0) ++ui; else --ui;
+    return __uint_as_float(ui);
+}
+__device__ __forceinline__ float next_down(float v) {
+    if (isinf(v) && v < 0.f) return v;
+    if (v == 0.f) v = -0.f;
+    uint32_t ui = __float_as_uint(v);
+    if (v > 0) --ui; else ++ui;
+    return __uint_as_float(ui);
+}
+// OffsetRayOrigin, src/core/geometry.h:1782-1802
+__device__ __forceinline__ float3 offset_ray_origin(float3 p, float3 pError, float3 n, float3 w) {
+    const float d = fabsf(n.x) * pError.x + fabsf(n.y) * pError.y + fabsf(n.z) * pError.z;
+    float3 off = make_float3(d * n.x, d * n.y, d * n.z);
+    if (w.x * n.x + w.y * n.y + w.z * n.z < 0) { off.x = -off.x; off.y = -off.y; off.z = -off.z; }
+    float3 po = make_float3(p.x + off.x, p.y + off.y, p.z + off.z);
+    if (off.x > 0) po.x = next_up(po.x); else if (off.x < 0) po.x = next_down(po.x);
+    if (off.y > 0) po.y = next_up(po.y); else if (off.y < 0) po.y = next_down(po.y);
+    if (off.z > 0) po.z = next_up(po.z); else if (off.z < 0) po.z = next_down(po.z);
+    return po;
+}
+
+// ---- stage kernels ------------------------------------------------------------------------------
+// Camera rays for path slots [batchStart, batchStart + nSlots) (PerspectiveCamera::GenerateRay,
+// src/cameras/perspective.cpp:97-143, pinhole; pixel sample = box filter footprint).
+__global__ void k_camera(const __grid_constant__ WfParams P, uint64_t batchStart, uint32_t nSlots, float4 *rays,
+                         uint32_t *qPath, uint32_t *count, float4 *beta, float4 *L) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    bool active = false;
+    uint32_t x = 0, y = 0, s = 0;
+    if (i < nSlots) {
+        active = path_pixel(P.tl, batchStart + i, x, y, s);
+        beta[i] = make_float4(1.f, 1.f, 1.f, 0.f);
+        L[i] = make_float4(0.f, 0.f, 0.f, active ? 1.f : 0.f);
+    }
+    const uint32_t slot = warp_append(active, count);
+    if (!active) return;
+    const uint32_t pix = y * P.cam.xres + x;
+    const float fx = (x + rnd(P.seed, pix, s, 0)) / P.cam.xres, fy = (y + rnd(P.seed, pix, s, 1)) / P.cam.yres;
+    const float sx = 1.f - 2.f * fx, sy = 1.f - 2.f * fy;
+    float dx = P.cam.dir[0] + sx * P.cam.right[0] + sy * P.cam.up[0];
+    float dy = P.cam.dir[1] + sx * P.cam.right[1] + sy * P.cam.up[1];
+    float dz = P.cam.dir[2] + sx * P.cam.right[2] + sy * P.cam.up[2];
+    const float inv = 1.f / sqrtf(dx * dx + dy * dy + dz * dz);
+    rays[2 * (size_t)slot] = make_float4(P.cam.eye[0], P.cam.eye[1], P.cam.eye[2], __int_as_float(0x7f800000));
+    rays[2 * (size_t)slot + 1] = make_float4(dx * inv, dy * inv, dz * inv, 0.f);
+    qPath[slot] = i;
+}
+
+// Shade one wavefront (PathIntegrator::Li body for one bounce, path.cpp:89-199; direct lighting =
+// UniformSampleOneLight with one point light, integrator.cpp:86-217; matte BSDF, reflection.h
+// LambertianReflection; CosineSampleHemisphere, sampling.h).
+__global__ void k_shade(const __grid_constant__ WfParams P, uint32_t depth, uint64_t batchStart,
+                        const uint32_t *__restrict__ nCur, const float4 *__restrict__ rays,
+                        const uint32_t *__restrict__ qPath, const b200rt_hit *__restrict__ hits,
+                        const float4 *__restrict__ primTris, float4 *beta, float4 *nextRays, uint32_t *nextPath,
+                        uint32_t *nNext, float4 *shRays, uint32_t *shPath, float4 *shContrib, uint32_t *nShadow) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t n = *nCur;
+    bool wantShadow = false, wantNext = false;
+    float3 so = make_float3(0, 0, 0), sd = so, no = so, nd = so, contrib = so;
+    uint32_t path = 0;
+    if (i < n) {
+        const b200rt_hit h = hits[i];
+        if (h.prim != B200RT_MISS && depth < P.max_depth) {  // path.cpp:110
+            path = qPath[i];
+            const float4 ro = rays[2 * (size_t)i], rd = rays[2 * (size_t)i + 1];
+            const float4 a = __ldg(primTris + 3 * (size_t)h.prim), b = __ldg(primTris + 3 * (size_t)h.prim + 1),
+                         c = __ldg(primTris + 3 * (size_t)h.prim + 2);
+            // pHit, pError (triangle.cpp:318-326)
+            const float3 p = make_float3(h.b0 * a.x + h.b1 * b.x + h.b2 * c.x, h.b0 * a.y + h.b1 * b.y + h.b2 * c.y,
+                                         h.b0 * a.z + h.b1 * b.z + h.b2 * c.z);
+            const float3 pe = make_float3(kGamma7 * (fabsf(h.b0 * a.x) + fabsf(h.b1 * b.x) + fabsf(h.b2 * c.x)),
+                                          kGamma7 * (fabsf(h.b0 * a.y) + fabsf(h.b1 * b.y) + fabsf(h.b2 * c.y)),
+                                          kGamma7 * (fabsf(h.b0 * a.z) + fabsf(h.b1 * b.z) + fabsf(h.b2 * c.z)));
+            // geometric normal = Normalize(Cross(dp02, dp12)) (triangle.cpp:346)
+            const float3 e0 = make_float3(a.x - c.x, a.y - c.y, a.z - c.z), e1 = make_float3(b.x - c.x, b.y - c.y, b.z - c.z);
+            float3 ng = make_float3(e0.y * e1.z - e0.z * e1.y, e0.z * e1.x - e0.x * e1.z, e0.x * e1.y - e0.y * e1.x);
+            const float nl = sqrtf(ng.x * ng.x + ng.y * ng.y + ng.z * ng.z);
+            if (nl > 0.f) {
+                ng.x /= nl; ng.y /= nl; ng.z /= nl;
+                const float3 wo = make_float3(-rd.x, -rd.y, -rd.z);
+                const float side = (ng.x * wo.x + ng.y * wo.y + ng.z * wo.z) < 0.f ? -1.f : 1.f;
+                const float3 nf = make_float3(side * ng.x, side * ng.y, side * ng.z);  // wo's hemisphere
+                const float4 bt = beta[path];
+                // -- direct lighting: PointLight::Sample_Li (point.cpp:44-53) + matte f * |cos|
+                const float3 wl = make_float3(P.light_pos[0] - p.x, P.light_pos[1] - p.y, P.light_pos[2] - p.z);
+                const float d2 = wl.x * wl.x + wl.y * wl.y + wl.z * wl.z;
+                if (d2 > 0.f) {
+                    const float invd = 1.f / sqrtf(d2);
+                    const float cosl = (nf.x * wl.x + nf.y * wl.y + nf.z * wl.z) * invd;
+                    if (cosl > 0.f) {  // SameHemisphere(wo, wi) for a reflective Lambertian lobe
+                        const float g = cosl * kInvPi / d2;
+                        contrib = make_float3(bt.x * P.kd[0] * P.light_I[0] * g, bt.y * P.kd[1] * P.light_I[1] * g,
+                                              bt.z * P.kd[2] * P.light_I[2] * g);
+                        if (contrib.x > 0.f || contrib.y > 0.f || contrib.z > 0.f) {
+                            // Interaction::SpawnRayTo (interaction.h:68-72)
+                            so = offset_ray_origin(p, pe, ng, wl);
+                            sd = make_float3(P.light_pos[0] - so.x, P.light_pos[1] - so.y, P.light_pos[2] - so.z);
+                            wantShadow = true;
+                        }
+                    }
+                }
+                // -- BSDF sample: CosineSampleHemisphere via ConcentricSampleDisk (sampling.cpp)
+                uint32_t x, y, s;
+                path_pixel(P.tl, batchStart + path, x, y, s);
+                const uint32_t pix = y * P.cam.xres + x, dim = 2 + 3 * depth;
+                const float u0 = 2.f * rnd(P.seed, pix, s, dim) - 1.f, u1 = 2.f * rnd(P.seed, pix, s, dim + 1) - 1.f;
+                float dxl = 0.f, dyl = 0.f;
+                if (u0 != 0.f || u1 != 0.f) {
+                    float r, th;
+                    if (fabsf(u0) > fabsf(u1)) { r = u0; th = (kPi / 4.f) * (u1 / u0); }
+                    else { r = u1; th = (kPi / 2.f) - (kPi / 4.f) * (u0 / u1); }
+                    dxl = r * cosf(th); dyl = r * sinf(th);
+                }
+                const float dzl = sqrtf(fmaxf(0.f, 1.f - dxl * dxl - dyl * dyl));
+                // CoordinateSystem(nf, &s, &t) (geometry.h)
+                float3 ss;
+                if (fabsf(nf.x) > fabsf(nf.y)) { const float il = 1.f / sqrtf(nf.x * nf.x + nf.z * nf.z); ss = make_float3(-nf.z * il, 0.f, nf.x * il); }
+                else { const float il = 1.f / sqrtf(nf.y * nf.y + nf.z * nf.z); ss = make_float3(0.f, nf.z * il, -nf.y * il); }
+                const float3 ts = make_float3(nf.y * ss.z - nf.z * ss.y, nf.z * ss.x - nf.x * ss.z, nf.x * ss.y - nf.y * ss.x);
+                const float3 wi = make_float3(ss.x * dxl + ts.x * dyl + nf.x * dzl, ss.y * dxl + ts.y * dyl + nf.y * dzl,
+                                              ss.z * dxl + ts.z * dyl + nf.z * dzl);
+                if (dzl > 0.f) {
+                    // beta *= f * |cos| / pdf = Kd (path.cpp:151)
+                    float3 nb = make_float3(bt.x * P.kd[0], bt.y * P.kd[1], bt.z * P.kd[2]);
+                    bool alive = nb.x > 0.f || nb.y > 0.f || nb.z > 0.f;
+                    // Russian roulette (path.cpp:190-199): bounces > 3 and max(beta) < rrThreshold = 1
+                    const float mx = fmaxf(nb.x, fmaxf(nb.y, nb.z));
+                    if (alive && mx < 1.f && depth > 3) {
+                        const float q = fmaxf(.05f, 1.f - mx);
+                        if (rnd(P.seed, pix, s, dim + 2) < q) alive = false;
+                        else { const float k = 1.f / (1.f - q); nb.x *= k; nb.y *= k; nb.z *= k; }
+                    }
+                    if (alive) {
+                        beta[path] = make_float4(nb.x, nb.y, nb.z, 0.f);
+                        no = offset_ray_origin(p, pe, ng, wi);  // Interaction::SpawnRay (interaction.h:64-67)
+                        nd = wi;
+                        wantNext = true;
+                    }
+                }
+            }
+        }
+    }
+    const uint32_t sj = warp_append(wantShadow, nShadow);
+    if (wantShadow) {
+        shRays[2 * (size_t)sj] = make_float4(so.x, so.y, so.z, 1.f - kShadowEpsilon);
+        shRays[2 * (size_t)sj + 1] = make_float4(sd.x, sd.y, sd.z, 0.f);
+        shPath[sj] = path;
+        shContrib[sj] = make_float4(contrib.x, contrib.y, contrib.z, 0.f);
+    }
+    const uint32_t nj = warp_append(wantNext, nNext);
+    if (wantNext) {
+        nextRays[2 * (size_t)nj] = make_float4(no.x, no.y, no.z, __int_as_float(0x7f800000));
+        nextRays[2 * (size_t)nj + 1] = make_float4(nd.x, nd.y, nd.z, 0.f);
+        nextPath[nj] = path;
+    }
+}
+
+// VisibilityTester::Unoccluded (light.cpp:59-64): add the light sample when the shadow ray is free.
+__global__ void k_shadow_resolve(const uint32_t *__restrict__ nShadow, const uint8_t *__restrict__ occluded,
+                                 const uint32_t *__restrict__ shPath, const float4 *__restrict__ shContrib, float4 *L) {
+    const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= *nShadow || occluded[j]) return;
+    const float4 c = shContrib[j];
+    float4 l = L[shPath[j]];  // one shadow ray per path per bounce: single writer
+    l.x += c.x; l.y += c.y; l.z += c.z;
+    L[shPath[j]] = l;
+}
+
+// FilmTile::AddSample with the box filter (film.h:130-169): each pixel sums its own samples, in
+// sample order (deterministic), into (sum R, sum G, sum B, sum weight).
+__global__ void k_film(const __grid_constant__ WfParams P, uint64_t batchStart, uint32_t nPixels, const float4 *__restrict__ L,
+                       float4 *film) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nPixels) return;
+    uint32_t x, y, s;
+    if (!path_pixel(P.tl, batchStart + (uint64_t)i * P.tl.spp, x, y, s)) return;
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (uint32_t k = 0; k < P.tl.spp; ++k) {
+        const float4 l = L[(size_t)i * P.tl.spp + k];
+        acc.x += l.x; acc.y += l.y; acc.z += l.z; acc.w += l.w;
+    }
+    float4 f = film[(size_t)y * P.cam.xres + x];
+    f.x += acc.x; f.y += acc.y; f.z += acc.z; f.w += acc.w;
+    film[(size_t)y * P.cam.xres + x] = f;
+}
+
+struct Workspace {
+    size_t cap = 0;
+    float4 *rays[2] = {nullptr, nullptr}, *shRays = nullptr, *shContrib = nullptr, *beta = nullptr, *L = nullptr;
+    uint32_t *qPath[2] = {nullptr, nullptr}, *shPath = nullptr, *counts = nullptr;
+    b200rt_hit *hits = nullptr;
+    uint8_t *occ = nullptr;
+    float4 *film = nullptr;
+    size_t film_px = 0;
+    // recorded queues of the last batch (b200rt_render_keep_queues)
+    bool keep = false;
+    std::vector<float4 *> kept;
+    std::vector<uint32_t> keptCount;
+    size_t keptCap = 0;
+};
+
+void free_ws(Workspace *w) {
+    for (int k = 0; k < 2; ++k) { cudaFree(w->rays[k]); cudaFree(w->qPath[k]); }
+    cudaFree(w->shRays); cudaFree(w->shContrib); cudaFree(w->beta); cudaFree(w->L); cudaFree(w->shPath);
+    cudaFree(w->counts); cudaFree(w->hits); cudaFree(w->occ); cudaFree(w->film);
+    for (float4 *p : w->kept) cudaFree(p);
+    *w = Workspace();
+}
+
+int tiling_of(const b200rt_render_desc *d, Tiling *t) {
+    if (!d || d->camera.xres == 0 || d->camera.yres == 0 || d->spp == 0 || d->world == 0 || d->rank >= d->world)
+        return set_error(B200RT_EINVAL, "bad render description (resolution/spp/rank/world)");
+    t->xres = d->camera.xres; t->yres = d->camera.yres;
+    t->tile = d->tile_size ? d->tile_size : 16;
+    t->ntx = (t->xres + t->tile - 1) / t->tile;
+    t->nty = (t->yres + t->tile - 1) / t->tile;
+    t->rank = d->rank; t->world = d->world; t->spp = d->spp;
+    const uint32_t total = t->ntx * t->nty;
+    t->n_tiles_rank = total > t->rank ? (total - t->rank + t->world - 1) / t->world : 0;
+    t->n_paths_rank = (uint64_t)t->n_tiles_rank * t->tile * t->tile * t->spp;
+    return B200RT_OK;
+}
+
+}  // namespace
+
+// the workspace hangs off the scene handle
+struct b200rt_wavefront_ws : Workspace {};
+static std::mutex g_ws_mu;
+static std::vector<std::pair<const b200rt_scene *, Workspace *>> g_ws;
+static Workspace *ws_of(const b200rt_scene *s) {
+    std::lock_guard<std::mutex> g(g_ws_mu);
+    for (auto &p : g_ws) if (p.first == s) return p.second;
+    g_ws.emplace_back(s, new Workspace());
+    return g_ws.back().second;
+}
+void b200rt_wavefront_release(const b200rt_scene *s) {
+    std::lock_guard<std::mutex> g(g_ws_mu);
+    for (size_t i = 0; i < g_ws.size(); ++i)
+        if (g_ws[i].first == s) { free_ws(g_ws[i].second); delete g_ws[i].second; g_ws.erase(g_ws.begin() + i); return; }
+}
+
+extern "C" int b200rt_render_tiles(const b200rt_render_desc *d, uint32_t *n_tiles, uint64_t *n_pixels) {
+    Tiling t;
+    int rc = tiling_of(d, &t);
+    if (rc) return rc;
+    if (n_tiles) *n_tiles = t.n_tiles_rank;
+    if (n_pixels) {
+        uint64_t px = 0;
+        for (uint32_t k = 0; k < t.n_tiles_rank; ++k) {
+            const uint32_t idx = t.rank + k * t.world, tx = idx % t.ntx, ty = idx / t.ntx;
+            px += (uint64_t)std::min(t.tile, t.xres - tx * t.tile) * std::min(t.tile, t.yres - ty * t.tile);
+        }
+        *n_pixels = px;
+    }
+    return B200RT_OK;
+}
+
+extern "C" int b200rt_render_keep_queues(b200rt_scene *s, int keep) {
+    if (!s) return set_error(B200RT_EINVAL, "null scene");
+    ws_of(s)->keep = keep != 0;
+    return B200RT_OK;
+}
+
+extern "C" int b200rt_render_queue(b200rt_scene *s, uint32_t q, b200rt_ray *rays, uint64_t *n) {
+    if (!s || !n) return set_error(B200RT_EINVAL, "null argument");
+    Workspace *w = ws_of(s);
+    if (q >= w->kept.size()) { *n = 0; return B200RT_OK; }
+    const uint64_t have = w->keptCount[q];
+    if (!rays) { *n = have; return B200RT_OK; }
+    const uint64_t m = std::min<uint64_t>(have, *n);
+    WCU(cudaMemcpy(rays, w->kept[q], m * sizeof(b200rt_ray), cudaMemcpyDefault));
+    *n = m;
+    return B200RT_OK;
+}
+
+extern "C" int b200rt_render(b200rt_scene *s, const b200rt_render_desc *d, float *film, b200rt_render_stats *stats,
+                             void *stream) {
+    if (!s || !d || !film) return set_error(B200RT_EINVAL, "null argument");
+    WfParams P;
+    std::memset(&P, 0, sizeof(P));
+    int rc = tiling_of(d, &P.tl);
+    if (rc) return rc;
+    P.cam = d->camera;
+    std::memcpy(P.light_pos, d->light_pos, 12); std::memcpy(P.light_I, d->light_I, 12); std::memcpy(P.kd, d->kd, 12);
+    P.max_depth = d->max_depth; P.seed = d->seed;
+    if (d->max_depth > 64) return set_error(B200RT_EINVAL, "max_depth %u too large", d->max_depth);
+    cudaStream_t st = (cudaStream_t)stream;
+    Workspace *w = ws_of(s);
+    const uint32_t tp = P.tl.tile * P.tl.tile;
+    const uint64_t unit = (uint64_t)tp * P.tl.spp;  // batches hold whole tiles so a pixel's samples never split
+    uint64_t want = d->max_batch ? d->max_batch : (1u << 22);
+    uint64_t cap = std::max<uint64_t>(unit, want / unit * unit);
+    cap = std::min<uint64_t>(cap, std::max<uint64_t>(unit, P.tl.n_paths_rank));
+    if (cap > 0x7fffffffull) return set_error(B200RT_EINVAL, "batch too large");
+    const uint32_t nCounts = 2 * (d->max_depth + 2);
+    if (w->cap < cap) {
+        const bool keep = w->keep;
+        free_ws(w);
+        w->keep = keep;
+        for (int k = 0; k < 2; ++k) { WCU(cudaMalloc(&w->rays[k], cap * 32)); WCU(cudaMalloc(&w->qPath[k], cap * 4)); }
+        WCU(cudaMalloc(&w->shRays, cap * 32)); WCU(cudaMalloc(&w->shContrib, cap * 16)); WCU(cudaMalloc(&w->shPath, cap * 4));
+        WCU(cudaMalloc(&w->beta, cap * 16)); WCU(cudaMalloc(&w->L, cap * 16));
+        WCU(cudaMalloc(&w->hits, cap * sizeof(b200rt_hit))); WCU(cudaMalloc(&w->occ, cap));
+        WCU(cudaMalloc(&w->counts, 4 * 2 * 66));
+        w->cap = cap;
+    }
+    const size_t npx = (size_t)P.tl.xres * P.tl.yres;
+    cudaPointerAttributes pa;
+    bool film_dev = cudaPointerGetAttributes(&pa, film) == cudaSuccess &&
+                    (pa.type == cudaMemoryTypeDevice || pa.type == cudaMemoryTypeManaged);
+    cudaGetLastError();
+    float4 *d_film = (float4 *)film;
+    if (!film_dev) {
+        if (w->film_px < npx) { cudaFree(w->film); w->film = nullptr; WCU(cudaMalloc(&w->film, npx * 16)); w->film_px = npx; }
+        WCU(cudaMemcpyAsync(w->film, film, npx * 16, cudaMemcpyHostToDevice, st));
+        d_film = w->film;
+    }
+    if (w->keep) {
+        const size_t nq = 2 * (size_t)(d->max_depth + 1);
+        if (w->kept.size() != nq || w->keptCap < cap) {
+            for (float4 *p : w->kept) cudaFree(p);
+            w->kept.assign(nq, nullptr);
+            for (size_t q = 0; q < nq; ++q) WCU(cudaMalloc(&w->kept[q], cap * 32));
+            w->keptCap = cap;
+        }
+        w->keptCount.assign(nq, 0);
+    }
+    std::vector<cudaEvent_t> evs;
+    auto ev = [&]() { cudaEvent_t e; cudaEventCreate(&e); cudaEventRecord(e, st); evs.push_back(e); return e; };
+    struct Span { cudaEvent_t a, b; bool any; };
+    std::vector<Span> spans;
+    const uint64_t launches0 = g_launches.load();
+    uint64_t nClosest = 0, nShadow = 0, nCamera = 0;
+    std::vector<uint32_t> hostCounts(nCounts);
+    cudaEvent_t t0 = ev();
+    const unsigned TB = 256;
+    for (uint64_t start = 0; start < P.tl.n_paths_rank; start += cap) {
+        const uint32_t nSlots = (uint32_t)std::min<uint64_t>(cap, P.tl.n_paths_rank - start);
+        const unsigned gridSlots = (nSlots + TB - 1) / TB;
+        WCU(cudaMemsetAsync(w->counts, 0, 4 * nCounts, st));
+        // counts[2*depth] = closest queue size at depth, counts[2*depth+1] = shadow queue size at depth
+        k_camera<<<gridSlots, TB, 0, st>>>(P, start, nSlots, w->rays[0], w->qPath[0], w->counts, w->beta, w->L);
+        g_launches.fetch_add(1);
+        int cur = 0;
+        for (uint32_t depth = 0; depth <= d->max_depth; ++depth) {
+            if (w->keep) WCU(cudaMemcpyAsync(w->kept[2 * depth], w->rays[cur], (size_t)nSlots * 32, cudaMemcpyDeviceToDevice, st));
+            cudaEvent_t a = ev();
+            rc = launch_trace(s, w->rays[cur], nSlots, w->counts + 2 * depth, w->hits, nullptr, false, nullptr, st);
+            if (rc) return rc;
+            spans.push_back({a, ev(), false});
+            if (depth == d->max_depth) break;  // path.cpp:110: the last intersection is found, then the path ends
+            k_shade<<<gridSlots, TB, 0, st>>>(P, depth, start, w->counts + 2 * depth, w->rays[cur], w->qPath[cur], w->hits,
+                                              s->d_prim_tris, w->beta, w->rays[cur ^ 1], w->qPath[cur ^ 1],
+                                              w->counts + 2 * (depth + 1), w->shRays, w->shPath, w->shContrib,
+                                              w->counts + 2 * depth + 1);
+            g_launches.fetch_add(1);
+            if (w->keep) WCU(cudaMemcpyAsync(w->kept[2 * depth + 1], w->shRays, (size_t)nSlots * 32, cudaMemcpyDeviceToDevice, st));
+            a = ev();
+            rc = launch_trace(s, w->shRays, nSlots, w->counts + 2 * depth + 1, nullptr, w->occ, true, nullptr, st);
+            if (rc) return rc;
+            spans.push_back({a, ev(), true});
+            k_shadow_resolve<<<gridSlots, TB, 0, st>>>(w->counts + 2 * depth + 1, w->occ, w->shPath, w->shContrib, w->L);
+            g_launches.fetch_add(1);
+            cur ^= 1;
+        }
+        const uint32_t nPix = nSlots / P.tl.spp;
+        k_film<<<(nPix + TB - 1) / TB, TB, 0, st>>>(P, start, nPix, w->L, d_film);
+        g_launches.fetch_add(1);
+        WCU(cudaMemcpyAsync(hostCounts.data(), w->counts, 4 * nCounts, cudaMemcpyDeviceToHost, st));
+        WCU(cudaStreamSynchronize(st));
+        nCamera += hostCounts[0];
+        for (uint32_t depth = 0; depth <= d->max_depth; ++depth) {
+            nClosest += hostCounts[2 * depth];
+            if (depth < d->max_depth) nShadow += hostCounts[2 * depth + 1];
+            if (w->keep) {
+                w->keptCount[2 * depth] = hostCounts[2 * depth];
+                if (depth < d->max_depth) w->keptCount[2 * depth + 1] = hostCounts[2 * depth + 1];
+            }
+        }
+    }
+    if (!film_dev) WCU(cudaMemcpyAsync(film, d_film, npx * 16, cudaMemcpyDeviceToHost, st));
+    cudaEvent_t t1 = ev();
+    WCU(cudaStreamSynchronize(st));
+    WCU(cudaGetLastError());
+    if (stats) {
+        std::memset(stats, 0, sizeof(*stats));
+        stats->camera_rays = nCamera; stats->closest_rays = nClosest; stats->shadow_rays = nShadow;
+        stats->launches = g_launches.load() - launches0;
+        stats->n_tiles = P.tl.n_tiles_rank;
+        for (const Span &sp : spans) (sp.any ? stats->launches_any : stats->launches_closest) += 1;
+        for (const Span &sp : spans) {
+            float ms = 0;
+            cudaEventElapsedTime(&ms, sp.a, sp.b);
+            (sp.any ? stats->ms_any : stats->ms_closest) += ms;
+        }
+        cudaEventElapsedTime(&stats->ms_total, t0, t1);
+    }
+    for (cudaEvent_t e : evs) cudaEventDestroy(e);
+    return B200RT_OK;
+}
