@@ -43,6 +43,13 @@ int b200rt::set_error(int code, const char *fmt, ...) {
 
 std::atomic<uint64_t> g_launches{0};
 int g_sm_count = 148;
+#define B200RT_PC_SLOTS 256
+// tuning knobs (read once in b200rt_init): B200RT_KERNEL=baseline selects the one-ray-per-thread kernel
+// for A/B measurements; B200RT_THRESH = busy-lane count below which a persistent warp refills.
+static int g_use_baseline = 0;
+static uint32_t g_thresh = 14;
+static int g_pblocks[4][2];  // resident persistent blocks per SM, [kind][any]
+static int g_persist_bsp = 1;
 
 extern "C" const char *b200rt_last_error(void) { return g_err; }
 extern "C" int b200rt_version(void) { return B200RT_VERSION; }
@@ -60,6 +67,15 @@ extern "C" int b200rt_init(int device) {
     cudaDeviceProp p;
     CU(cudaGetDeviceProperties(&p, device));
     g_sm_count = p.multiProcessorCount;
+    if (const char *e = getenv("B200RT_KERNEL")) g_use_baseline = std::strcmp(e, "baseline") == 0;
+    if (const char *e = getenv("B200RT_THRESH")) g_thresh = (uint32_t)atoi(e);
+    if (const char *e = getenv("B200RT_PERSIST_BSP")) g_persist_bsp = atoi(e);
+#define OCC(k, a, fn) CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_pblocks[k][a], fn, B200RT_PBLOCK, 0))
+    OCC(B200RT_BVH, 0, bvh_persistent_kernel<false>); OCC(B200RT_BVH, 1, bvh_persistent_kernel<true>);
+    OCC(B200RT_KDTREE, 0, (bsp_persistent_kernel<B200RT_KDTREE, false>)); OCC(B200RT_KDTREE, 1, (bsp_persistent_kernel<B200RT_KDTREE, true>));
+    OCC(B200RT_RBSP, 0, (bsp_persistent_kernel<B200RT_RBSP, false>)); OCC(B200RT_RBSP, 1, (bsp_persistent_kernel<B200RT_RBSP, true>));
+    OCC(B200RT_RBSPKD, 0, (bsp_persistent_kernel<B200RT_RBSPKD, false>)); OCC(B200RT_RBSPKD, 1, (bsp_persistent_kernel<B200RT_RBSPKD, true>));
+#undef OCC
     return B200RT_OK;
 }
 
@@ -278,6 +294,8 @@ extern "C" int b200rt_scene_create(const b200rt_scene_desc *d, b200rt_scene **ou
     else rc = d->kind == B200RT_BVH ? build_bvh_scene(d, s) : build_bsp_scene(d, s);
     if (rc == B200RT_OK) {
         cudaError_t e = cudaMalloc(&s->d_counters, sizeof(Counters));
+        if (e == cudaSuccess) e = cudaMalloc(&s->d_pc, B200RT_PC_SLOTS * sizeof(PersistCounters));
+        if (e == cudaSuccess) e = cudaMemset(s->d_pc, 0, B200RT_PC_SLOTS * sizeof(PersistCounters));
         if (e != cudaSuccess) rc = fail(B200RT_ECUDA, "cudaMalloc(counters): %s", cudaGetErrorString(e));
     }
     if (rc != B200RT_OK) { b200rt_scene_destroy(s); return rc; }
@@ -290,7 +308,7 @@ extern "C" void b200rt_scene_destroy(b200rt_scene *s) {
     b200rt_wavefront_release(s);
     if (s->d_prim_tris != s->d_tris) cudaFree(s->d_prim_tris);
     cudaFree(s->d_nodes); cudaFree(s->d_indices); cudaFree(s->d_tris);
-    cudaFree(s->d_stage_in); cudaFree(s->d_stage_out); cudaFree(s->d_counters);
+    cudaFree(s->d_stage_in); cudaFree(s->d_stage_out); cudaFree(s->d_counters); cudaFree(s->d_pc);
     delete s;
 }
 
@@ -339,6 +357,36 @@ int b200rt::launch_trace(const b200rt_scene *s, const float4 *rays, uint64_t n, 
     if (s->empty) {
         miss_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(rays, n, any ? nullptr : hits, any ? occ : nullptr);
         g_launches.fetch_add(1);
+    } else if (!counters && !g_use_baseline && (s->kind == B200RT_BVH || g_persist_bsp)) {
+        // production path: persistent warps (rt_persist.cuh); <= 2^30 rays per launch
+        const uint64_t kMax = 1ull << 30;
+        for (uint64_t off = 0; off < n; off += kMax) {
+            const uint64_t m = std::min<uint64_t>(kMax, n - off);
+            if (n_dev && off) return fail(B200RT_EINVAL, "device-side ray counts need n <= 2^30");
+            PersistCounters *pc = s->d_pc + (s->pc_next.fetch_add(1) % B200RT_PC_SLOTS);
+            const int perSM = std::max(1, g_pblocks[s->kind][any ? 1 : 0]);
+            const uint64_t maxBlocks = (uint64_t)g_sm_count * perSM, wpb = B200RT_PBLOCK / 32;
+            // big queues: 128-ray chunks (one atomic per 128 rays); small ones: 32-ray chunks so that
+            // every resident warp gets work
+            const uint32_t chunk = m >= maxBlocks * wpb * 128 * 4 ? 128u : 32u;
+            const unsigned blocks = (unsigned)std::min<uint64_t>((m + chunk * wpb - 1) / (chunk * wpb), maxBlocks);
+            b200rt_hit *ho = any ? nullptr : hits + off;
+            uint8_t *oo = any ? occ + off : nullptr;
+            const float4 *ri = rays + 2 * off;
+#define PL(fn, view) fn<<<blocks, B200RT_PBLOCK, 0, st>>>(view, ri, m, n_dev, ho, oo, pc, g_thresh, chunk)
+            switch (s->kind * 2 + (any ? 1 : 0)) {
+                case B200RT_BVH * 2: PL(bvh_persistent_kernel<false>, s->bvh); break;
+                case B200RT_BVH * 2 + 1: PL(bvh_persistent_kernel<true>, s->bvh); break;
+                case B200RT_KDTREE * 2: PL((bsp_persistent_kernel<B200RT_KDTREE, false>), s->bsp); break;
+                case B200RT_KDTREE * 2 + 1: PL((bsp_persistent_kernel<B200RT_KDTREE, true>), s->bsp); break;
+                case B200RT_RBSP * 2: PL((bsp_persistent_kernel<B200RT_RBSP, false>), s->bsp); break;
+                case B200RT_RBSP * 2 + 1: PL((bsp_persistent_kernel<B200RT_RBSP, true>), s->bsp); break;
+                case B200RT_RBSPKD * 2: PL((bsp_persistent_kernel<B200RT_RBSPKD, false>), s->bsp); break;
+                default: PL((bsp_persistent_kernel<B200RT_RBSPKD, true>), s->bsp); break;
+            }
+#undef PL
+            g_launches.fetch_add(1);
+        }
     } else if (any) {
         if (counters) launch_kind<true, true>(s, rays, n, n_dev, nullptr, occ, counters, st);
         else launch_kind<true, false>(s, rays, n, n_dev, nullptr, occ, nullptr, st);

@@ -1,0 +1,360 @@
+// Persistent-warp traversal kernels (sm_100a): the production path of b200rt_intersect_closest/any.
+//
+// Why (ncu, profiles/r01_ncu_full_v1_summary.txt): the one-ray-per-thread baseline kernel is
+// ISSUE-bound (issue slots 75-80 % busy, 2-3 eligible warps per issue, DRAM < 2 %) while only 8-10 of
+// 32 lanes execute each instruction on path-traced ray queues.  So the levers are (1) lanes per
+// instruction and (2) instructions per traversal step, not bytes:
+//   * persistent warps: a warp keeps running and REFILLS idle lanes with new rays as soon as fewer
+//     than `thresh` lanes are still traversing (ballot + popc + one chunked atomic per warp), instead
+//     of waiting for the slowest ray of a fixed 32-ray packet;
+//   * while-while scheduling: all lanes first walk interior nodes until each holds a leaf (or is
+//     done), then all lanes run the (much longer) triangle code together, instead of paying
+//     interior + leaf code on every iteration of one mixed loop;
+//   * a branch-free slab test (2 x FMNMX3 per box) that is bit-identical to the reference's
+//     sequential test for every ray whose 1/d.x is finite; the rare other rays take the reference's
+//     literal sequence (slab_geom).
+//
+// Results are bit-identical to the baseline kernel and to the reference: same node order (near child
+// first by dirIsNeg[axis], far child re-tested against the CURRENT ray.tMax when popped, bvh.cpp:367),
+// leaf primitives in array order, strict comparisons.
+#pragma once
+#include "rt_kernels.cuh"
+
+namespace b200rt {
+
+#define B200RT_DONE 0x7FFFFFFFu  // "no node": an interior ref that no tree can contain
+#define B200RT_PBLOCK 128
+
+// Bounds3::IntersectP(ray, invDir, dirIsNeg) (geometry.h:1754-1780) for rays with finite 1/d.x and
+// finite origin.  Equivalence with the sequential form: comparisons with NaN are false there, so a
+// NaN entry value acts as -inf and a NaN exit value as +inf — exactly what fmaxf/fminf do by
+// ignoring a NaN operand; NaNs come only from 0*inf on an axis with d == 0, and on the x axis they
+// are sticky in the reference (the ray misses), which is why such rays do not come here.  The
+// pairwise early-outs test every (entry_a, exit_b) pair with a != b; same-axis pairs can only fail
+// when that exit is < 0, which the final `tMax > 0` rejects as well.  x*k is monotone, so
+// min(a*k, b*k, c*k) == min(a, b, c)*k bit for bit.
+__device__ __forceinline__ bool slab_fast(const RayCtx &r, float lox, float loy, float loz, float hix, float hiy,
+                                          float hiz, float &tEntry) {
+    const float t0x = (lox - r.ox) * r.ix, t0y = (loy - r.oy) * r.iy, t0z = (loz - r.oz) * r.iz;
+    const float t1x = (hix - r.ox) * r.ix, t1y = (hiy - r.oy) * r.iy, t1z = (hiz - r.oz) * r.iz;
+    const float en = fmaxf(fmaxf(t0x, t0y), t0z);
+    const float ex = fminf(fminf(t1x, t1y), t1z) * kSlabK;
+    tEntry = en;
+    return en <= ex && ex > 0;
+}
+
+// 256-bit read-only load (sm_100: LDG.E.256): one request instead of two LDG.128 — halves the L1
+// data-pipe wavefronts of the scattered node fetch, which is what bounds the kernel once the lanes are
+// kept busy (ncu l1tex__data_pipe_lsu_wavefronts 86 % of peak, profiles/r01_ncu_full_v3_vote_summary.txt).
+__device__ __forceinline__ void ldg256(const void *p, float4 &lo, float4 &hi) {
+    asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=f"(lo.x), "=f"(lo.y), "=f"(lo.z), "=f"(lo.w), "=f"(hi.x), "=f"(hi.y), "=f"(hi.z), "=f"(hi.w)
+                 : "l"(p));
+}
+
+struct PersistCounters {  // one slot per in-flight launch, zeroed by the last warp to leave
+    unsigned int next;    // next unclaimed ray
+    unsigned int exited;  // warps that have left the kernel
+};
+
+// Warp-level work queue: a warp claims `chunk` consecutive rays with one global atomic and hands
+// them to its idle lanes by ballot rank (work stealing at warp granularity: fast warps simply claim
+// more chunks).  Returns this lane's new ray index, or 0xFFFFFFFF if it gets none this round.
+struct WarpQueue {
+    uint32_t next = 0, end = 0;
+    bool drained = false;  // the global queue has no more rays
+};
+__device__ __forceinline__ uint32_t warp_claim(WarpQueue &q, PersistCounters *pc, uint32_t n, uint32_t chunk,
+                                               unsigned idleMask, bool laneIdle, int lane) {
+    const unsigned FULL = 0xFFFFFFFFu;
+    const uint32_t want = __popc(idleMask);
+    if (q.end == q.next) {  // the remainder of a chunk (< 32 rays) is handed out before a new claim
+        uint32_t base = 0;
+        if (lane == 0) base = atomicAdd(&pc->next, chunk);
+        base = __shfl_sync(FULL, base, 0);
+        if (base >= n) { q.drained = true; q.next = q.end = 0; }
+        else { q.next = base; q.end = base + chunk < n ? base + chunk : n; }
+    }
+    const uint32_t avail = q.end - q.next;
+    const uint32_t rank = __popc(idleMask & ((1u << lane) - 1u));
+    const uint32_t idx = (laneIdle && rank < avail) ? q.next + rank : 0xFFFFFFFFu;
+    q.next += want < avail ? want : avail;
+    return idx;
+}
+// the last warp out re-arms the counter slot for the next launch that uses it
+__device__ __forceinline__ void warp_exit(PersistCounters *pc, int lane) {
+    if (lane == 0) {
+        const unsigned total = gridDim.x * (blockDim.x >> 5);
+        __threadfence();
+        if (atomicAdd(&pc->exited, 1u) == total - 1) { pc->next = 0; pc->exited = 0; __threadfence(); }
+    }
+}
+
+template <bool ANY>
+__global__ void __launch_bounds__(B200RT_PBLOCK)
+bvh_persistent_kernel(const __grid_constant__ BvhView S, const float4 *__restrict__ rays, uint64_t n64,
+                      const uint32_t *__restrict__ n_dev, b200rt_hit *__restrict__ hits,
+                      uint8_t *__restrict__ occluded, PersistCounters *pc, uint32_t thresh,
+                      uint32_t chunk /* rays a warp claims per global atomic */) {
+    uint32_t n = (uint32_t)n64;
+    if (n_dev) { const uint32_t m = *n_dev; n = m < n ? m : n; }
+    const unsigned FULL = 0xFFFFFFFFu;
+    const int lane = threadIdx.x & 31;
+
+    // per-lane traversal state
+    RayCtx r;
+    HitRec h;
+    uint32_t cur = B200RT_DONE, rayIdx = 0;
+    bool nx = false, ny = false, nz = false, slow = false, hit = false;
+    bool live = false;  // this lane holds a ray whose result has not been written yet
+    uint32_t negMask = 0;
+    uint2 stack[64];  // (node ref, entry distance of its box): one 8-byte local store / load per push / pop
+    int sp = 0;
+    WarpQueue wq;
+
+    for (;;) {
+        // ---- refill idle lanes (warp-uniform control flow) -------------------------------------
+        const unsigned idle = __ballot_sync(FULL, cur == B200RT_DONE);
+        if (idle && !wq.drained) {
+            const uint32_t got = warp_claim(wq, pc, n, chunk, idle, cur == B200RT_DONE, lane);
+            if (got != 0xFFFFFFFFu) {
+                rayIdx = got;
+                ray_setup(r, __ldg(rays + 2 * (size_t)rayIdx), __ldg(rays + 2 * (size_t)rayIdx + 1));
+                nx = r.ix < 0; ny = r.iy < 0; nz = r.iz < 0;  // dirIsNeg (bvh.cpp:359)
+                negMask = (nx ? 1u : 0u) | (ny ? 2u : 0u) | (nz ? 4u : 0u);
+                slow = !(fabsf(r.ix) <= 3.402823466e+38f) || !(fabsf(r.iy) <= 3.402823466e+38f) ||
+                       !(fabsf(r.iz) <= 3.402823466e+38f) || !(fabsf(r.ox) <= 3.402823466e+38f) ||
+                       !(fabsf(r.oy) <= 3.402823466e+38f) || !(fabsf(r.oz) <= 3.402823466e+38f);
+                h.prim = B200RT_MISS; h.t = r.tMax; h.b0 = h.b1 = h.b2 = 0.f;
+                hit = false;
+                sp = 0;
+                // root box (node 0 of the reference): literal sequence, once per ray
+                float te;
+                const bool ok = slab_geom(r, nx ? S.root[3] : S.root[0], ny ? S.root[4] : S.root[1],
+                                          nz ? S.root[5] : S.root[2], nx ? S.root[0] : S.root[3],
+                                          ny ? S.root[1] : S.root[4], nz ? S.root[2] : S.root[5], te);
+                if (ok && te < r.tMax) { cur = S.rootRef; live = true; }
+                else {  // misses everything
+                    if (ANY) occluded[rayIdx] = 0;
+                    else {
+                        b200rt_hit o; o.prim = B200RT_MISS; o.t = h.t; o.b0 = o.b1 = o.b2 = 0.f;
+                        hits[rayIdx] = o;
+                    }
+                }
+            }
+        }
+        if (__ballot_sync(FULL, cur != B200RT_DONE) == 0) {
+            if (wq.drained) break;
+            continue;
+        }
+        // ---- vote-scheduled traversal until too few lanes are busy -------------------------------
+        // Each round the warp runs ONE kind of step, the one more lanes are waiting for: an interior
+        // step (fetch a 64-byte node, two slab tests, order, push/pop) or a primitive step (one
+        // triangle of the lane's current leaf).  Lanes in the other state wait; they become the
+        // majority within a few rounds.  Every lane still sees its own nodes and primitives in the
+        // reference's order, so results do not depend on the schedule.
+        for (;;) {
+            const unsigned mI = __ballot_sync(FULL, !(cur & B200RT_LEAF_BIT) && cur != B200RT_DONE);
+            const unsigned mL = __ballot_sync(FULL, (cur & B200RT_LEAF_BIT) != 0);
+            const uint32_t nI = __popc(mI), nL = __popc(mL);
+            if (nI + nL == 0 || (!wq.drained && nI + nL < thresh)) break;
+            if (nI >= nL) {
+                if (!(cur & B200RT_LEAF_BIT) && cur != B200RT_DONE) {
+                    const BvhNode2 *nd = S.nodes + cur;
+                    float4 a, b, c, mf;
+                    ldg256(&nd->a, a, b);
+                    ldg256(&nd->c, c, mf);
+                    const uint4 m = make_uint4(__float_as_uint(mf.x), __float_as_uint(mf.y), __float_as_uint(mf.z), 0u);
+                    float t0, t1;
+                    bool g0, g1;
+                    const float l0x = nx ? a.w : a.x, l0y = ny ? b.x : a.y, l0z = nz ? b.y : a.z;
+                    const float h0x = nx ? a.x : a.w, h0y = ny ? a.y : b.x, h0z = nz ? a.z : b.y;
+                    const float l1x = nx ? c.y : b.z, l1y = ny ? c.z : b.w, l1z = nz ? c.w : c.x;
+                    const float h1x = nx ? b.z : c.y, h1y = ny ? b.w : c.z, h1z = nz ? c.x : c.w;
+                    if (!slow) {
+                        g0 = slab_fast(r, l0x, l0y, l0z, h0x, h0y, h0z, t0);
+                        g1 = slab_fast(r, l1x, l1y, l1z, h1x, h1y, h1z, t1);
+                    } else {
+                        g0 = slab_geom(r, l0x, l0y, l0z, h0x, h0y, h0z, t0);
+                        g1 = slab_geom(r, l1x, l1y, l1z, h1x, h1y, h1z, t1);
+                    }
+                    const bool p0 = g0 && t0 < r.tMax, p1 = g1 && t1 < r.tMax;
+                    // near = second child when dirIsNeg[axis] (bvh.cpp:382-388)
+                    const bool negAxis = (negMask >> m.z) & 1u;
+                    const uint32_t nearRef = negAxis ? m.y : m.x, farRef = negAxis ? m.x : m.y;
+                    const bool hitNear = negAxis ? p1 : p0, hitFar = negAxis ? p0 : p1;
+                    if (hitNear) {
+                        if (hitFar) {
+                            stack[sp++] = make_uint2(farRef, __float_as_uint(negAxis ? t0 : t1));
+                        }
+                        cur = nearRef;
+                    } else if (hitFar) cur = farRef;
+                    else {
+                        // pop: the reference re-tests the far box against the CURRENT ray.tMax (bvh.cpp:367)
+                        cur = B200RT_DONE;
+                        while (sp > 0) {
+                            const uint2 e = stack[--sp];
+                            if (ANY || __uint_as_float(e.y) < r.tMax) { cur = e.x; break; }
+                        }
+                    }
+                }
+            } else {
+                if (cur & B200RT_LEAF_BIT) {
+                    // next primitive of the leaf, in array order (bvh.cpp:372-375 / 412-418)
+                    const float4 *rec = S.tris + 3 * (size_t)(cur & ~B200RT_LEAF_BIT);
+                    const float4 v0 = __ldg(rec), v1 = __ldg(rec + 1), v2 = __ldg(rec + 2);
+                    bool stop = false;
+                    if (prim_closest<ANY>(r, v0, v1, v2, h)) {
+                        hit = true;
+                        if (ANY) stop = true;
+                    }
+                    if (stop) cur = B200RT_DONE;
+                    else if (__float_as_uint(v1.w) & B200RT_TRI_LAST) {
+                        cur = B200RT_DONE;
+                        while (sp > 0) {
+                            const uint2 e = stack[--sp];
+                            if (ANY || __uint_as_float(e.y) < r.tMax) { cur = e.x; break; }
+                        }
+                    } else cur += 1;
+                }
+            }
+            if (live && cur == B200RT_DONE) {  // ray finished (in either kind of step): write its result
+                live = false;
+                if (ANY) occluded[rayIdx] = hit ? 1 : 0;
+                else {
+                    b200rt_hit o; o.prim = h.prim; o.t = h.t; o.b0 = h.b0; o.b1 = h.b1; o.b2 = h.b2;
+                    hits[rayIdx] = o;
+                }
+            }
+        }
+    }
+    warp_exit(pc, lane);
+}
+
+// ---- kd-tree / RBSP / RBSPKd ---------------------------------------------------------------------
+// Same persistent-warp + vote skeleton over the reference's 8-byte nodes (kdtreeaccel.cpp:381-521,
+// rbsp.cpp:405-547, rbspKd.cpp).  Lane states: walking interior nodes (cheap step: one 8-byte fetch, a
+// plane distance, a push at most), or iterating the primitives of a leaf (expensive step: one
+// triangle).  Interior steps are cheap, so a lane takes up to B200RT_BSP_STEPS of them per vote.
+#define B200RT_BSP_STEPS 4
+#define B200RT_ST_DONE 0u
+#define B200RT_ST_NODE 1u
+#define B200RT_ST_LEAF 2u
+
+template <int KIND, bool ANY>
+__global__ void __launch_bounds__(B200RT_PBLOCK)
+bsp_persistent_kernel(const __grid_constant__ BspView S, const float4 *__restrict__ rays, uint64_t n64,
+                      const uint32_t *__restrict__ n_dev, b200rt_hit *__restrict__ hits,
+                      uint8_t *__restrict__ occluded, PersistCounters *pc, uint32_t thresh, uint32_t chunk) {
+    uint32_t n = (uint32_t)n64;
+    if (n_dev) { const uint32_t m = *n_dev; n = m < n ? m : n; }
+    const unsigned FULL = 0xFFFFFFFFu;
+    const int lane = threadIdx.x & 31;
+    const uint32_t off = KIND == B200RT_KDTREE ? 2u : S.bitOffset;
+    const uint32_t mask = KIND == B200RT_KDTREE ? 3u : S.bitMask;
+    const uint32_t leafTag = KIND == B200RT_KDTREE ? 3u : S.leafTag;
+
+    RayCtx r;
+    HitRec h;
+    uint32_t state = B200RT_ST_DONE, rayIdx = 0;
+    uint32_t cur = 0;            // node index (ST_NODE)
+    uint32_t li = 0, lend = 0;   // ST_LEAF: next / end position; single-primitive leaves use lend = li + 1
+    bool lsingle = false;        // ST_LEAF: li is the primitive itself (onePrimitive), not an index position
+    float tMin = 0, tMax = 0;
+    bool hit = false;
+    uint4 todo[64];              // (node, tMin, tMax, -): one 16-byte local store / load per push / pop
+    int todoPos = 0;
+    WarpQueue wq;
+
+    for (;;) {
+        const unsigned idle = __ballot_sync(FULL, state == B200RT_ST_DONE);
+        if (idle && !wq.drained) {
+            const uint32_t got = warp_claim(wq, pc, n, chunk, idle, state == B200RT_ST_DONE, lane);
+            if (got != 0xFFFFFFFFu) {
+                rayIdx = got;
+                ray_setup(r, __ldg(rays + 2 * (size_t)rayIdx), __ldg(rays + 2 * (size_t)rayIdx + 1));
+                h.prim = B200RT_MISS; h.t = r.tMax; h.b0 = h.b1 = h.b2 = 0.f;
+                hit = false;
+                todoPos = 0;
+                cur = 0;
+                if (root_clip(r, S.bounds, tMin, tMax)) state = B200RT_ST_NODE;  // kdtreeaccel.cpp:385
+                else {
+                    if (ANY) occluded[rayIdx] = 0;
+                    else {
+                        b200rt_hit o; o.prim = B200RT_MISS; o.t = h.t; o.b0 = o.b1 = o.b2 = 0.f;
+                        hits[rayIdx] = o;
+                    }
+                }
+            }
+        }
+        if (__ballot_sync(FULL, state != B200RT_ST_DONE) == 0) {
+            if (wq.drained) break;
+            continue;
+        }
+        for (;;) {
+            const unsigned mN = __ballot_sync(FULL, state == B200RT_ST_NODE);
+            const unsigned mL = __ballot_sync(FULL, state == B200RT_ST_LEAF);
+            const uint32_t nN = __popc(mN), nL = __popc(mL);
+            if (nN + nL == 0 || (!wq.drained && nN + nL < thresh)) break;
+            bool finished = false;
+            if (nN >= nL) {
+#pragma unroll 1
+                for (int k = 0; k < B200RT_BSP_STEPS && state == B200RT_ST_NODE; ++k) {
+                    if (!ANY && r.tMax < tMin) { finished = true; break; }  // kdtreeaccel.cpp:400 (closest-hit only)
+                    const uint2 nd = __ldg(S.nodes + cur);
+                    const uint32_t axis = nd.y & mask;
+                    if (axis != leafTag) {
+                        bool belowFirst;
+                        const float tPlane = bsp_interior<KIND>(S, r, axis, __uint_as_float(nd.x), belowFirst);
+                        const uint32_t above = nd.y >> off;
+                        const uint32_t first = belowFirst ? cur + 1 : above, second = belowFirst ? above : cur + 1;
+                        if (tPlane > tMax || tPlane <= 0) cur = first;
+                        else if (tPlane < tMin) cur = second;
+                        else {
+                            todo[todoPos++] = make_uint4(second, __float_as_uint(tPlane), __float_as_uint(tMax), 0u);
+                            cur = first;
+                            tMax = tPlane;
+                        }
+                    } else {
+                        const uint32_t np = nd.y >> off;
+                        if (np == 0) {
+                            if (todoPos > 0) {
+                                const uint4 e = todo[--todoPos];
+                                cur = e.x; tMin = __uint_as_float(e.y); tMax = __uint_as_float(e.z);
+                            } else finished = true;
+                        } else {
+                            state = B200RT_ST_LEAF;
+                            lsingle = np == 1;
+                            li = nd.x; lend = nd.x + np;  // np == 1: li IS the primitive (kdtreeaccel.cpp:112-118)
+                        }
+                    }
+                    if (finished) break;
+                }
+            } else if (state == B200RT_ST_LEAF) {
+                const uint32_t p = lsingle ? li : __ldg(S.indices + li);
+                if (prim_closest<ANY>(r, S.tris + 3 * (size_t)p, h)) {
+                    hit = true;
+                    if (ANY) finished = true;
+                }
+                if (!finished && ++li == lend) {
+                    if (todoPos > 0) {
+                        const uint4 e = todo[--todoPos];
+                        cur = e.x; tMin = __uint_as_float(e.y); tMax = __uint_as_float(e.z);
+                        state = B200RT_ST_NODE;
+                    } else finished = true;
+                }
+            }
+            if (finished) {
+                state = B200RT_ST_DONE;
+                if (ANY) occluded[rayIdx] = hit ? 1 : 0;
+                else {
+                    b200rt_hit o; o.prim = h.prim; o.t = h.t; o.b0 = h.b0; o.b1 = h.b1; o.b2 = h.b2;
+                    hits[rayIdx] = o;
+                }
+            }
+        }
+    }
+    warp_exit(pc, lane);
+}
+
+}  // namespace b200rt

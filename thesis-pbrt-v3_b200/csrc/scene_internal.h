@@ -1,7 +1,8 @@
 // Internal: the scene object behind the opaque b200rt_scene handle, shared by b200rt.cu and wavefront.cu.
 #pragma once
 #include <mutex>
-#include "rt_kernels.cuh"
+#include <atomic>
+#include "rt_persist.cuh"
 
 struct b200rt_scene {
     int kind = 0;
@@ -20,6 +21,10 @@ struct b200rt_scene {
     void *d_stage_in = nullptr, *d_stage_out = nullptr;
     size_t stage_in_bytes = 0, stage_out_bytes = 0;
     b200rt::Counters *d_counters = nullptr;
+    // persistent kernels: ring of work-counter slots (one per in-flight launch; each slot is re-armed by
+    // the last warp of the launch that used it)
+    b200rt::PersistCounters *d_pc = nullptr;
+    mutable std::atomic<uint32_t> pc_next{0};
 };
 
 
