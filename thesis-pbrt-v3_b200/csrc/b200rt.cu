@@ -50,6 +50,8 @@ static int g_use_baseline = 0;
 static uint32_t g_thresh = 14;
 static int g_pblocks[4][2];  // resident persistent blocks per SM, [kind][any]
 static int g_persist_bsp = 1;
+#define B200RT_PIPE_CHUNK_MAX (1024u * 1024u)
+static uint32_t g_pipe_chunk = 256u * 1024u;  // rays per pipeline stage (B200RT_PIPE_CHUNK overrides, <= 1 Mi)
 
 extern "C" const char *b200rt_last_error(void) { return g_err; }
 extern "C" int b200rt_version(void) { return B200RT_VERSION; }
@@ -69,6 +71,7 @@ extern "C" int b200rt_init(int device) {
     g_sm_count = p.multiProcessorCount;
     if (const char *e = getenv("B200RT_KERNEL")) g_use_baseline = std::strcmp(e, "baseline") == 0;
     if (const char *e = getenv("B200RT_THRESH")) g_thresh = (uint32_t)atoi(e);
+    if (const char *e = getenv("B200RT_PIPE_CHUNK")) g_pipe_chunk = std::min<uint32_t>(B200RT_PIPE_CHUNK_MAX, std::max(1024, atoi(e)));
     if (const char *e = getenv("B200RT_PERSIST_BSP")) g_persist_bsp = atoi(e);
 #define OCC(k, a, fn) CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_pblocks[k][a], fn, B200RT_PBLOCK, 0))
     OCC(B200RT_BVH, 0, bvh_persistent_kernel<false>); OCC(B200RT_BVH, 1, bvh_persistent_kernel<true>);
@@ -309,6 +312,12 @@ extern "C" void b200rt_scene_destroy(b200rt_scene *s) {
     if (s->d_prim_tris != s->d_tris) cudaFree(s->d_prim_tris);
     cudaFree(s->d_nodes); cudaFree(s->d_indices); cudaFree(s->d_tris);
     cudaFree(s->d_stage_in); cudaFree(s->d_stage_out); cudaFree(s->d_counters); cudaFree(s->d_pc);
+    for (auto &l : s->lanes) {
+        cudaFree(l.d_in); cudaFree(l.d_out);
+        if (l.done) cudaEventDestroy(l.done);
+        if (l.st) cudaStreamDestroy(l.st);
+    }
+    if (s->ev_start) cudaEventDestroy(s->ev_start);
     delete s;
 }
 
@@ -407,6 +416,40 @@ static int ensure(void **p, size_t *have, size_t want) {
     return B200RT_OK;
 }
 
+// Host-buffer batches: chunked 3-stage pipeline (H2D | trace | D2H) over three streams.
+
+static int run_pipelined(b200rt_scene *s, const b200rt_ray *rays, uint64_t n, void *out, bool any, cudaStream_t user) {
+    const size_t out_elem = any ? 1 : sizeof(b200rt_hit);
+    if (!s->lanes_ready) {
+        for (auto &l : s->lanes) {
+            CU(cudaStreamCreateWithFlags(&l.st, cudaStreamNonBlocking));
+            CU(cudaEventCreateWithFlags(&l.done, cudaEventDisableTiming));
+            CU(cudaMalloc(&l.d_in, (size_t)B200RT_PIPE_CHUNK_MAX * sizeof(b200rt_ray)));
+            CU(cudaMalloc(&l.d_out, (size_t)B200RT_PIPE_CHUNK_MAX * sizeof(b200rt_hit)));
+        }
+        CU(cudaEventCreateWithFlags(&s->ev_start, cudaEventDisableTiming));
+        s->lanes_ready = true;
+    }
+    CU(cudaEventRecord(s->ev_start, user));
+    for (auto &l : s->lanes) CU(cudaStreamWaitEvent(l.st, s->ev_start, 0));
+    int k = 0;
+    for (uint64_t off = 0; off < n; off += g_pipe_chunk, k = (k + 1) % 3) {
+        b200rt_scene::Lane &l = s->lanes[k];
+        const uint64_t m = std::min<uint64_t>(g_pipe_chunk, n - off);
+        CU(cudaMemcpyAsync(l.d_in, rays + off, m * sizeof(b200rt_ray), cudaMemcpyHostToDevice, l.st));
+        int rc = launch_trace(s, (const float4 *)l.d_in, m, nullptr, any ? nullptr : (b200rt_hit *)l.d_out,
+                              any ? (uint8_t *)l.d_out : nullptr, any, nullptr, l.st);
+        if (rc) return rc;
+        CU(cudaMemcpyAsync((char *)out + off * out_elem, l.d_out, m * out_elem, cudaMemcpyDeviceToHost, l.st));
+    }
+    for (auto &l : s->lanes) {
+        CU(cudaEventRecord(l.done, l.st));
+        CU(cudaStreamWaitEvent(user, l.done, 0));
+    }
+    CU(cudaStreamSynchronize(user));
+    return B200RT_OK;
+}
+
 static int run(b200rt_scene *s, const b200rt_ray *rays, uint64_t n, b200rt_hit *hits, uint8_t *occ, bool any,
                b200rt_counters *counters, void *stream) {
     if (!s) return fail(B200RT_EINVAL, "null scene");
@@ -421,6 +464,8 @@ static int run(b200rt_scene *s, const b200rt_ray *rays, uint64_t n, b200rt_hit *
     const float4 *d_rays = (const float4 *)rays;
     void *d_out = (void *)outp;
     if (!rays_dev || !out_dev || counters) lock.lock();
+    if (!rays_dev && !out_dev && !counters && n > g_pipe_chunk)
+        return run_pipelined(s, rays, n, (void *)outp, any, st);
     if (!rays_dev) {
         int rc = ensure(&s->d_stage_in, &s->stage_in_bytes, n * sizeof(b200rt_ray));
         if (rc) return rc;

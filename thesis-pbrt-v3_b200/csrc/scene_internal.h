@@ -21,6 +21,16 @@ struct b200rt_scene {
     void *d_stage_in = nullptr, *d_stage_out = nullptr;
     size_t stage_in_bytes = 0, stage_out_bytes = 0;
     b200rt::Counters *d_counters = nullptr;
+    // host-pointer calls are pipelined in chunks over B200RT_LANES streams: H2D of chunk i+1 overlaps the
+    // kernel of chunk i and the D2H of chunk i-1 (both copy engines + SMs busy at once)
+    struct Lane {
+        cudaStream_t st = nullptr;
+        void *d_in = nullptr, *d_out = nullptr;
+        cudaEvent_t done = nullptr;
+    };
+    Lane lanes[3];
+    cudaEvent_t ev_start = nullptr;
+    bool lanes_ready = false;
     // persistent kernels: ring of work-counter slots (one per in-flight launch; each slot is re-armed by
     // the last warp of the launch that used it)
     b200rt::PersistCounters *d_pc = nullptr;
