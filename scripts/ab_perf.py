@@ -51,11 +51,18 @@ def main():
     queues[100] = torch.from_numpy(scenes.camera_rays(cam)).cuda()
     queues[102] = torch.from_numpy(scenes.random_rays(acc.WorldBound(), 1 << 22)).cuda()
     configs = [("baseline", None)] + [("persist", t) for t in threshes]
+    # extra env sweeps: B200RT_AB_EXTRA="NAME=VAL,NAME=VAL;NAME=VAL" -> one persistent config per ';' group
+    extra = [g for g in os.environ.get("B200RT_AB_EXTRA", "").split(";") if g]
+    configs += [("persist", g) for g in extra]
     results = {}
     ref_out = {}
     for name, t in configs:
         os.environ["B200RT_KERNEL"] = "baseline" if name == "baseline" else "persistent"
-        if t is not None:
+        if isinstance(t, str):
+            for kv in t.split(","):
+                k, v = kv.split("=")
+                os.environ[k] = v
+        elif t is not None:
             os.environ["B200RT_THRESH"] = str(t)
         b200rt.init(0)
         tot_c = tot_a = 0.0
@@ -76,7 +83,7 @@ def main():
                 else: tot_c += ms
         nc = sum(len(b) for q, b in queues.items() if q < 100 and q % 2 == 0)
         na = sum(len(b) for q, b in queues.items() if q < 100 and q % 2 == 1)
-        print("%-9s thresh %-4s | path queues: closest %7.3f ms = %6.0f Mrays/s | any %7.3f ms = %6.0f Mrays/s | camera %6.0f | random %6.0f Mrays/s"
+        print("%-9s %-28s | path queues: closest %7.3f ms = %6.0f Mrays/s | any %7.3f ms = %6.0f Mrays/s | camera %6.0f | random %6.0f Mrays/s"
               % (name, t, tot_c, nc / tot_c / 1e3, tot_a, na / max(tot_a, 1e-9) / 1e3,
                  results[(name, t, 100)][0] / results[(name, t, 100)][1] / 1e3,
                  results[(name, t, 102)][0] / results[(name, t, 102)][1] / 1e3), flush=True)

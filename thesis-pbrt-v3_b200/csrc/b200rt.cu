@@ -50,6 +50,7 @@ static int g_use_baseline = 0;
 static uint32_t g_thresh = 14;
 static int g_pblocks[4][2];  // resident persistent blocks per SM, [kind][any]
 static int g_persist_bsp = 1;
+static uint32_t g_bvh_steps = 4;
 #define B200RT_PIPE_CHUNK_MAX (1024u * 1024u)
 static uint32_t g_pipe_chunk = 256u * 1024u;  // rays per pipeline stage (B200RT_PIPE_CHUNK overrides, <= 1 Mi)
 
@@ -72,8 +73,14 @@ extern "C" int b200rt_init(int device) {
     if (const char *e = getenv("B200RT_KERNEL")) g_use_baseline = std::strcmp(e, "baseline") == 0;
     if (const char *e = getenv("B200RT_THRESH")) g_thresh = (uint32_t)atoi(e);
     if (const char *e = getenv("B200RT_PIPE_CHUNK")) g_pipe_chunk = std::min<uint32_t>(B200RT_PIPE_CHUNK_MAX, std::max(1024, atoi(e)));
+    if (const char *e = getenv("B200RT_BVH_STEPS")) g_bvh_steps = std::max(1, atoi(e));
     if (const char *e = getenv("B200RT_PERSIST_BSP")) g_persist_bsp = atoi(e);
-#define OCC(k, a, fn) CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_pblocks[k][a], fn, B200RT_PBLOCK, 0))
+    // the persistent kernels use no shared memory: give the whole 256 KB array to L1 (node working set)
+    int carve = 0;
+    if (const char *e = getenv("B200RT_CARVEOUT")) carve = atoi(e);
+#define OCC(k, a, fn)                                                                                        \
+    if (carve >= 0) CU(cudaFuncSetAttribute(fn, cudaFuncAttributePreferredSharedMemoryCarveout, carve)); \
+    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_pblocks[k][a], fn, B200RT_PBLOCK, 0))
     OCC(B200RT_BVH, 0, bvh_persistent_kernel<false>); OCC(B200RT_BVH, 1, bvh_persistent_kernel<true>);
     OCC(B200RT_KDTREE, 0, (bsp_persistent_kernel<B200RT_KDTREE, false>)); OCC(B200RT_KDTREE, 1, (bsp_persistent_kernel<B200RT_KDTREE, true>));
     OCC(B200RT_RBSP, 0, (bsp_persistent_kernel<B200RT_RBSP, false>)); OCC(B200RT_RBSP, 1, (bsp_persistent_kernel<B200RT_RBSP, true>));
@@ -383,9 +390,10 @@ int b200rt::launch_trace(const b200rt_scene *s, const float4 *rays, uint64_t n, 
             uint8_t *oo = any ? occ + off : nullptr;
             const float4 *ri = rays + 2 * off;
 #define PL(fn, view) fn<<<blocks, B200RT_PBLOCK, 0, st>>>(view, ri, m, n_dev, ho, oo, pc, g_thresh, chunk)
+#define PLB(fn, view) fn<<<blocks, B200RT_PBLOCK, 0, st>>>(view, ri, m, n_dev, ho, oo, pc, g_thresh, chunk, g_bvh_steps)
             switch (s->kind * 2 + (any ? 1 : 0)) {
-                case B200RT_BVH * 2: PL(bvh_persistent_kernel<false>, s->bvh); break;
-                case B200RT_BVH * 2 + 1: PL(bvh_persistent_kernel<true>, s->bvh); break;
+                case B200RT_BVH * 2: PLB(bvh_persistent_kernel<false>, s->bvh); break;
+                case B200RT_BVH * 2 + 1: PLB(bvh_persistent_kernel<true>, s->bvh); break;
                 case B200RT_KDTREE * 2: PL((bsp_persistent_kernel<B200RT_KDTREE, false>), s->bsp); break;
                 case B200RT_KDTREE * 2 + 1: PL((bsp_persistent_kernel<B200RT_KDTREE, true>), s->bsp); break;
                 case B200RT_RBSP * 2: PL((bsp_persistent_kernel<B200RT_RBSP, false>), s->bsp); break;
@@ -394,6 +402,7 @@ int b200rt::launch_trace(const b200rt_scene *s, const float4 *rays, uint64_t n, 
                 default: PL((bsp_persistent_kernel<B200RT_RBSPKD, true>), s->bsp); break;
             }
 #undef PL
+#undef PLB
             g_launches.fetch_add(1);
         }
     } else if (any) {

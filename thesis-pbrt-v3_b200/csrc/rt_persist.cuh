@@ -95,7 +95,8 @@ __global__ void __launch_bounds__(B200RT_PBLOCK)
 bvh_persistent_kernel(const __grid_constant__ BvhView S, const float4 *__restrict__ rays, uint64_t n64,
                       const uint32_t *__restrict__ n_dev, b200rt_hit *__restrict__ hits,
                       uint8_t *__restrict__ occluded, PersistCounters *pc, uint32_t thresh,
-                      uint32_t chunk /* rays a warp claims per global atomic */) {
+                      uint32_t chunk /* rays a warp claims per global atomic */,
+                      uint32_t steps /* interior steps a lane may take per vote */) {
     uint32_t n = (uint32_t)n64;
     if (n_dev) { const uint32_t m = *n_dev; n = m < n ? m : n; }
     const unsigned FULL = 0xFFFFFFFFu;
@@ -159,7 +160,8 @@ bvh_persistent_kernel(const __grid_constant__ BvhView S, const float4 *__restric
             const uint32_t nI = __popc(mI), nL = __popc(mL);
             if (nI + nL == 0 || (!wq.drained && nI + nL < thresh)) break;
             if (nI >= nL) {
-                if (!(cur & B200RT_LEAF_BIT) && cur != B200RT_DONE) {
+#pragma unroll 1
+                for (uint32_t k = 0; k < steps && !(cur & B200RT_LEAF_BIT) && cur != B200RT_DONE; ++k) {
                     const BvhNode2 *nd = S.nodes + cur;
                     float4 a, b, c, mf;
                     ldg256(&nd->a, a, b);
