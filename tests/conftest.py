@@ -43,3 +43,14 @@ def built_lib():
 def gpu(built_lib):
     built_lib.init(0)
     return built_lib
+
+
+FEET = ["bvh", "rbsp3", "rbsp7", "rbsp9", "rbsp13", "rbspkd13"]
+
+
+def feet_tree(g, name):
+    """Reference-built tree `name` of tests/golden/ref_feet.npz (BASELINE config 4) in the dict form
+    B200Accel / OracleAccel take."""
+    kind = "bvh" if name == "bvh" else ("rbspkd" if name.startswith("rbspkd") else "rbsp")
+    return dict(kind=kind, nodes=g[name + "_nodes"], indices=g[name + "_indices"], directions=g[name + "_directions"],
+                bounds=g[name + "_bounds"], n_prims=len(g["tri_verts"]))

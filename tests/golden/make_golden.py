@@ -10,6 +10,9 @@ Outputs (tests/golden/):
                          the reference's memory), 4096 rays, and the reference's own Intersect /
                          IntersectP results + per-ray counters.  kinds: bvh, kdtree, rbsp3, rbsp7,
                          rbsp13, rbspkd13.
+  ref_feet.npz           BASELINE config 4: the feet crop of scenes/killeroo-feet, reference-built BVH and
+                         RBSP (3/7/9/13 directions) + RBSPKd(13) trees, the crop's camera rays + secondary
+                         rays, and the reference's own answers per accelerator.
   ref_triangle.npz       Triangle.Watertight / Reintersect / BadCases style single-triangle cases
                          (reference src/tests/shapes.cpp:28-205,544-559) with the reference's answers.
 """
@@ -141,7 +144,63 @@ def gen_triangle():
     np.savez_compressed(os.path.join(OUT, "ref_triangle.npz"), tris=tris, rays=rays, hit=hit, t=t, uv=uv, occ=occ)
 
 
+def gen_feet():
+    """BASELINE config 4 (scenes/killeroo-feet + scripts/run_rbsps.sh): the feet crop of one killeroo,
+    RBSP with nbDirections 3/7/9/13 (+ RBSPKd 13) against the BVH on the SAME rays.  To keep the
+    fixture small only the triangles seen through the crop window (plus a margin) are kept."""
+    sys.path.insert(0, os.path.join(ROOT, "thesis-pbrt-v3_b200"))
+    from b200rt import scenes
+    sc = scenes.killeroo_feet()
+    tv_all, cam = sc["tri_verts"], sc["camera"]
+    n_all = len(tv_all)
+    full = rb.RefScene(tv_all.reshape(-1, 3), np.arange(3 * n_all, dtype=np.int32).reshape(-1, 3))
+    bvh_full = rb.RefAccel(full, "bvh")
+    x0, x1, y0, y1 = sc["crop"]
+    probe = scenes.camera_rays(dict(cam, xres=cam["xres"] // 8, yres=cam["yres"] // 8), x0=x0 // 8, x1=x1 // 8, y0=y0 // 8, y1=y1 // 8)
+    h = bvh_full.intersect(probe, n_threads=8)
+    pts = h["p"][h["prim"] >= 0]
+    c = tv_all.reshape(-1, 3, 3).mean(1)
+    keep = np.sort(np.argsort(np.linalg.norm(c - pts.mean(0), axis=1))[:4096])  # the 4096 triangles around the feet
+    tv = np.ascontiguousarray(tv_all[keep])
+    n = len(tv)
+    print("killeroo-feet: %d of %d triangles kept, %d/%d probe rays hit" % (n, n_all, len(pts), len(probe)))
+    P, idx = tv.reshape(-1, 3), np.arange(3 * n, dtype=np.int32).reshape(-1, 3)
+    rsc = rb.RefScene(P, idx)
+    # rays: the crop window's camera rays on a coarse grid + path-like rays leaving the surface
+    rng = np.random.default_rng(21)
+    hh = rb.RefAccel(rsc, "bvh").intersect(probe, n_threads=8)
+    m = hh["prim"] >= 0
+    cam_r = np.concatenate([probe[m], probe[~m][:: max(1, (~m).sum() // 1024)]])  # every hitting ray + ~1024 missing ones
+    o = hh["p"][m][:4096]
+    d = rng.normal(size=o.shape)
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    sec = np.zeros((len(o), 8), np.float32)
+    sec[:, 0:3], sec[:, 4:7], sec[:, 3] = o + 1e-3 * d, d, np.inf
+    sec[::3, 3] = rng.uniform(1, 60, len(sec[::3]))
+    rays = np.concatenate([cam_r, sec]).astype(np.float32)
+    out = dict(tri_verts=tv, rays=rays)
+    import time
+    for name, kind, ip in [("bvh", "bvh", {}), ("rbsp3", "rbsp", {"nbDirections": 3}), ("rbsp7", "rbsp", {"nbDirections": 7}),
+                           ("rbsp9", "rbsp", {"nbDirections": 9}), ("rbsp13", "rbsp", {"nbDirections": 13}),
+                           ("rbspkd13", "rbspkd", {"nbDirections": 13})]:
+        t0 = time.time()
+        acc = rb.RefAccel(rsc, kind, ip)
+        tb = time.time() - t0
+        ex = acc.export()
+        hits = acc.intersect(rays, n_threads=8)
+        occ = acc.intersect_p(rays, n_threads=8)
+        for k in ("nodes", "indices", "directions", "bounds"):
+            out["%s_%s" % (name, k)] = ex[k]
+        out["%s_prim" % name], out["%s_t" % name], out["%s_occ" % name] = hits["prim"], hits["t"], occ
+        print("  %-9s build %.1fs nodes %d indices %d hits %d occ %d" % (name, tb, len(ex["nodes"]), len(ex["indices"]),
+                                                                      int((hits["prim"] >= 0).sum()), int(occ.sum())))
+    np.savez_compressed(os.path.join(OUT, "ref_feet.npz"), **out)
+    print("ref_feet.npz: %.1f MB" % (os.path.getsize(os.path.join(OUT, "ref_feet.npz")) / 1e6))
+
+
 if __name__ == "__main__":
-    gen_killeroo()
-    gen_small()
-    gen_triangle()
+    which = sys.argv[1:] or ["killeroo", "small", "triangle", "feet"]
+    if "killeroo" in which: gen_killeroo()
+    if "small" in which: gen_small()
+    if "triangle" in which: gen_triangle()
+    if "feet" in which: gen_feet()

@@ -3,7 +3,7 @@ reference goldens, and through size-independent properties at full size.
 Bar: primitive ids, t and barycentrics BIT-EXACT; any-hit exact; counters exact."""
 import numpy as np
 import pytest
-from conftest import load_golden, golden_tree, SMALL
+from conftest import load_golden, golden_tree, SMALL, FEET, feet_tree
 from oracle import orcbind as ob
 
 pytestmark = pytest.mark.gpu
@@ -39,6 +39,25 @@ def test_golden_small(gpu, name):
     assert np.array_equal(occ2, g["occluded"])
     assert cp["prim_tests"] == int(g["cntp_tests"].sum())
     assert cp["leaf_visits"] == int(g["cntp_leaf"].sum())
+
+
+@pytest.mark.parametrize("name", FEET)
+def test_golden_feet(gpu, name):
+    """BASELINE config 4 (scenes/killeroo-feet + scripts/run_rbsps.sh): reference-built RBSP 3/7/9/13,
+    RBSPKd 13 and BVH over the feet crop, compared with the reference's own answers on the same rays."""
+    g = load_golden("ref_feet.npz")
+    acc = gpu.B200Accel(feet_tree(g, name), g["tri_verts"])
+    hits = acc.Intersect(g["rays"])
+    ref_prim = np.where(g[name + "_prim"] < 0, gpu.MISS, g[name + "_prim"]).astype(np.uint32)
+    assert np.array_equal(hits["prim"], ref_prim)
+    assert np.array_equal(hits["t"].view(np.uint32), g[name + "_t"].view(np.uint32))
+    assert np.array_equal(acc.IntersectP(g["rays"]), g[name + "_occ"])
+    # the instrumented (one-ray-per-thread) kernels agree with the persistent production kernels
+    h2, c = acc.Intersect(g["rays"], counters=True)
+    _same_hits(h2, hits)
+    o2, _ = acc.IntersectP(g["rays"], counters=True)
+    assert np.array_equal(o2, g[name + "_occ"])
+    assert c["rays"] == len(g["rays"])
 
 
 def test_golden_triangles(gpu):

@@ -2,7 +2,7 @@
 (tests/golden/make_golden.py), and the host builders against the reference-built trees."""
 import numpy as np
 import pytest
-from conftest import load_golden, golden_tree, SMALL
+from conftest import load_golden, golden_tree, SMALL, FEET, feet_tree
 from oracle import orcbind as ob
 
 
@@ -74,3 +74,18 @@ def test_rbsp3_equals_kdtree_hits():
         assert np.array_equal(a["hit_prim"], b["hit_prim"])
         assert np.array_equal(a["hit_t"], b["hit_t"])
         assert np.array_equal(a["occluded"], b["occluded"])
+
+
+@pytest.mark.parametrize("name", FEET)
+def test_oracle_matches_reference_feet(name):
+    """BASELINE config 4 (scenes/killeroo-feet, scripts/run_rbsps.sh): RBSP 3/7/9/13 + RBSPKd and the BVH
+    on the same rays, trees and answers from the unmodified reference."""
+    g = load_golden("ref_feet.npz")
+    acc = ob.OracleAccel(feet_tree(g, name), g["tri_verts"])
+    hits = acc.intersect(g["rays"], n_threads=4)
+    ref_prim = np.where(g[name + "_prim"] < 0, ob.MISS, g[name + "_prim"]).astype(np.uint32)
+    assert np.array_equal(hits["prim"], ref_prim)
+    assert np.array_equal(hits["t"].view(np.uint32), g[name + "_t"].view(np.uint32))
+    assert np.array_equal(acc.intersect_p(g["rays"], n_threads=4), g[name + "_occ"])
+    # cross-accelerator agreement on identical rays (SURVEY.md §4): same t as the BVH
+    assert np.array_equal(g[name + "_t"], g["bvh_t"])

@@ -134,6 +134,28 @@ def killeroo_mesh():
     return z["P"].astype(np.float64), z["idx"].astype(np.int64)
 
 
+def _killeroo_camera(xres, yres):
+    """LookAt 400 20 30  0 63 -110  0 0 1 ; Rotate -5 0 0 1 ; Camera "perspective" fov 39
+    (scenes/killeroo-simple:1-3, scenes/killeroo-feet:1-3).  The CTM at `Camera` is LookAt * Rotate(-5, z)
+    = world-to-camera, i.e. the world turns by -5 deg about z before the LookAt: the same view as a
+    LookAt whose eye and target are turned by +5 deg about the world z axis (up = z is invariant)."""
+    r = _rot_z(5.0)
+    eye, look = _xform(r, np.array([[400.0, 20, 30]]))[0], _xform(r, np.array([[0.0, 63, -110]]))[0]
+    return look_at_camera(eye, look, (0, 0, 1), 39, xres, yres)
+
+
+def killeroo_feet(xres=5000, yres=5000):
+    """scenes/killeroo-feet (BASELINE config 4, scripts/run_rbsps.sh): one killeroo translated by
+    (-200, 100, -100) (33 264 triangles), distant light along the view direction, 5000x5000 film with
+    crop window [.3 .5] x [.4 .8] -> pixels x in [1500, 2500), y in [2000, 4000)."""
+    P, idx = killeroo_mesh()
+    tv = _xform(_translate(-200, 100, -100), P)[idx].reshape(-1, 9).astype(np.float32) + np.float32(0)
+    cam = _killeroo_camera(xres, yres)
+    crop = (int(np.ceil(.3 * xres)), int(np.ceil(.5 * xres)), int(np.ceil(.4 * yres)), int(np.ceil(.8 * yres)))
+    return dict(name="killeroo-feet", tri_verts=tv, camera=cam, crop=crop,
+                light_dir=np.array([400 - 0, 20 - 63, 30 + 110], np.float32))
+
+
 def killeroo_simple(xres=700, yres=700):
     """scenes/killeroo-simple: 2 killeroos (2 x 33 264 tris) + 2 ground quads (4 tris) = 66 532
     triangles; camera LookAt 400 20 30 / 0 63 -110 / 0 0 1, fov 39, 700x700."""
@@ -151,8 +173,7 @@ def killeroo_simple(xres=700, yres=700):
     ctm = ctm @ _translate(-200, 0, 0)
     tris.append(_xform(ctm, P)[idx].reshape(-1, 9))
     tv = np.concatenate(tris).astype(np.float32) + np.float32(0)
-    # LookAt 400 20 30  0 63 -110  0 0 1 ; Rotate -5 0 0 1 precedes Camera and rolls the view slightly: ignored
-    cam = look_at_camera((400, 20, 30), (0, 63, -110), (0, 0, 1), 39, xres, yres)
+    cam = _killeroo_camera(xres, yres)
     return dict(name="killeroo-simple", tri_verts=tv, camera=cam, light=np.array([150, 120, 20], np.float32),
                 note="reference geometry (fixture); sphere area light replaced by a point light at its centre")
 
