@@ -21,7 +21,7 @@
 extern "C" {
 #endif
 
-#define B200RT_VERSION 1
+#define B200RT_VERSION 2
 
 enum {
     B200RT_OK = 0,
@@ -77,6 +77,16 @@ typedef struct {
     const float *tri_uvs;    /* n_prims x 6 floats or NULL (default (0,0),(1,0),(1,1), triangle.h:109-121);
                                 only used for the degenerate-triangle rejection of triangle.cpp:302-315 */
     uint32_t n_prims;
+    /* Non-triangle primitives in the aggregate (Sphere::Intersect / IntersectP, src/shapes/sphere.cpp:49-156,
+     * 158-215; killeroo-simple's area light and scenes/simple put spheres next to the triangles).
+     * prim_kind: NULL (all triangles) or n_prims bytes, 0 = triangle, 1 = FULL sphere (zmin/zmax/phimax at
+     * their defaults; partial spheres are rejected with B200RT_EUNSUPPORTED by the caller's shim).  The k-th
+     * sphere primitive (in primitive order) uses sphere_params[16*k .. 16*k+15] = WorldToObject rows 0..2 of
+     * the shape's transform (affine 3x4, row-major), radius, 3 unused floats.  tri_verts rows of sphere
+     * primitives are ignored.  A sphere hit reports b0 = b1 = b2 = 0. */
+    const uint8_t *prim_kind;
+    const float *sphere_params;
+    uint32_t n_spheres;
 } b200rt_scene_desc;
 
 typedef struct b200rt_scene b200rt_scene;

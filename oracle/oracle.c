@@ -152,17 +152,140 @@ int orc_triangle(const orc_ray *r, const float *v, int degenerate, float *t, flo
     return degenerate ? 0 : 1; /* triangle.cpp:309-315 */
 }
 
+/* ---------------------------------- Sphere ------------------------------------------------- */
+/* NextFloatUp / NextFloatDown, core/pbrt.h:207-253. */
+static inline float next_up(float v) {
+    if (isinf(v) && v > 0.f) return v;
+    if (v == -0.f) v = 0.f;
+    uint32_t ui; memcpy(&ui, &v, 4);
+    if (v >= 0) ++ui; else --ui;
+    memcpy(&v, &ui, 4);
+    return v;
+}
+static inline float next_down(float v) {
+    if (isinf(v) && v < 0.f) return v;
+    if (v == 0.f) v = -0.f;
+    uint32_t ui; memcpy(&ui, &v, 4);
+    if (v > 0) --ui; else ++ui;
+    memcpy(&v, &ui, 4);
+    return v;
+}
+/* EFloat, core/efloat.h:48-214 (release build: no vPrecise). */
+typedef struct { float v, low, high; } efloat;
+static inline float f_min4(float a, float b, float c, float d) {  /* std::min(std::min(a,b), std::min(c,d)) */
+    float x = (b < a) ? b : a, y = (d < c) ? d : c;
+    return (y < x) ? y : x;
+}
+static inline float f_max4(float a, float b, float c, float d) {
+    float x = (a < b) ? b : a, y = (c < d) ? d : c;
+    return (x < y) ? y : x;
+}
+static inline efloat ef_make(float v, float err) { /* efloat.h:52-69 */
+    efloat r; r.v = v;
+    if (err == 0.) r.low = r.high = v;
+    else { r.low = next_down(v - err); r.high = next_up(v + err); }
+    return r;
+}
+static inline efloat ef_add(efloat a, efloat b) { /* :76-88 */
+    efloat r; r.v = a.v + b.v; r.low = next_down(a.low + b.low); r.high = next_up(a.high + b.high); return r;
+}
+static inline efloat ef_sub(efloat a, efloat b) { /* :100-110 */
+    efloat r; r.v = a.v - b.v; r.low = next_down(a.low - b.high); r.high = next_up(a.high - b.low); return r;
+}
+static inline efloat ef_mul(efloat a, efloat b) { /* :111-126 */
+    efloat r; r.v = a.v * b.v;
+    float p0 = a.low * b.low, p1 = a.high * b.low, p2 = a.low * b.high, p3 = a.high * b.high;
+    r.low = next_down(f_min4(p0, p1, p2, p3));
+    r.high = next_up(f_max4(p0, p1, p2, p3));
+    return r;
+}
+static inline efloat ef_div(efloat a, efloat b) { /* :127-149 */
+    efloat r; r.v = a.v / b.v;
+    if (b.low < 0 && b.high > 0) { r.low = -INFINITY; r.high = INFINITY; }
+    else {
+        float d0 = a.low / b.low, d1 = a.high / b.low, d2 = a.low / b.high, d3 = a.high / b.high;
+        r.low = next_down(f_min4(d0, d1, d2, d3));
+        r.high = next_up(f_max4(d0, d1, d2, d3));
+    }
+    return r;
+}
+/* Sphere parameters: 16 floats = WorldToObject rows 0..2 (affine 3x4, row-major), radius, 3 pad.
+ * FULL spheres only (zMin = -radius, zMax = radius, phiMax = 360): then the clipping tests of
+ * sphere.cpp:86-103 can never fire and hit / tHit depend on the EFloat quadratic alone.
+ * Sphere::Intersect sphere.cpp:49-81 / IntersectP :158-190; returns 1 and *tHit on a hit. */
+static int sphere_isect(const float *sp, const float o[3], const float d[3], float rayTMax, float *tHit) {
+    const float *m0 = sp, *m1 = sp + 4, *m2 = sp + 8;
+    const float radius = sp[12];
+    const float g3 = orc_gamma(3);
+    /* Transform::operator()(Point3f, Vector3f *pError), transform.h:278-300 (affine: wp == 1) */
+    float ox = m0[0] * o[0] + m0[1] * o[1] + m0[2] * o[2] + m0[3];
+    float oy = m1[0] * o[0] + m1[1] * o[1] + m1[2] * o[2] + m1[3];
+    float oz = m2[0] * o[0] + m2[1] * o[1] + m2[2] * o[2] + m2[3];
+    float oex = g3 * (fabsf(m0[0] * o[0]) + fabsf(m0[1] * o[1]) + fabsf(m0[2] * o[2]) + fabsf(m0[3]));
+    float oey = g3 * (fabsf(m1[0] * o[0]) + fabsf(m1[1] * o[1]) + fabsf(m1[2] * o[2]) + fabsf(m1[3]));
+    float oez = g3 * (fabsf(m2[0] * o[0]) + fabsf(m2[1] * o[1]) + fabsf(m2[2] * o[2]) + fabsf(m2[3]));
+    /* Transform::operator()(Vector3f, Vector3f *absError), transform.h:337-352 */
+    float dex = g3 * (fabsf(m0[0] * d[0]) + fabsf(m0[1] * d[1]) + fabsf(m0[2] * d[2]));
+    float dey = g3 * (fabsf(m1[0] * d[0]) + fabsf(m1[1] * d[1]) + fabsf(m1[2] * d[2]));
+    float dez = g3 * (fabsf(m2[0] * d[0]) + fabsf(m2[1] * d[1]) + fabsf(m2[2] * d[2]));
+    float dx = m0[0] * d[0] + m0[1] * d[1] + m0[2] * d[2];
+    float dy = m1[0] * d[0] + m1[1] * d[1] + m1[2] * d[2];
+    float dz = m2[0] * d[0] + m2[1] * d[1] + m2[2] * d[2];
+    /* Transform::operator()(Ray, oError, dError), transform.h:382-394 */
+    float lengthSquared = dx * dx + dy * dy + dz * dz;
+    if (lengthSquared > 0) {
+        float dt = (fabsf(dx) * oex + fabsf(dy) * oey + fabsf(dz) * oez) / lengthSquared;
+        ox += dx * dt; oy += dy * dt; oz += dz * dt;
+    }
+    /* sphere.cpp:60-65 */
+    efloat eox = ef_make(ox, oex), eoy = ef_make(oy, oey), eoz = ef_make(oz, oez);
+    efloat edx = ef_make(dx, dex), edy = ef_make(dy, dey), edz = ef_make(dz, dez);
+    efloat a = ef_add(ef_add(ef_mul(edx, edx), ef_mul(edy, edy)), ef_mul(edz, edz));
+    efloat b = ef_mul(ef_make(2.f, 0.f), ef_add(ef_add(ef_mul(edx, eox), ef_mul(edy, eoy)), ef_mul(edz, eoz)));
+    efloat er = ef_make(radius, 0.f);
+    efloat c = ef_sub(ef_add(ef_add(ef_mul(eox, eox), ef_mul(eoy, eoy)), ef_mul(eoz, eoz)), ef_mul(er, er));
+    /* Quadratic(EFloat...), efloat.h:267-285 */
+    double discrim = (double)b.v * (double)b.v - 4. * (double)a.v * (double)c.v;
+    if (discrim < 0.) return 0;
+    double rootDiscrim = sqrt(discrim);
+    efloat frd = ef_make((float)rootDiscrim, (float)(MachineEpsilon * rootDiscrim));
+    efloat q;
+    if (b.v < 0) q = ef_mul(ef_make(-.5f, 0.f), ef_sub(b, frd));
+    else q = ef_mul(ef_make(-.5f, 0.f), ef_add(b, frd));
+    efloat t0 = ef_div(q, a), t1 = ef_div(c, q);
+    if (t0.v > t1.v) { efloat s = t0; t0 = t1; t1 = s; }
+    /* sphere.cpp:72-81 */
+    if (t0.high > rayTMax || t1.low <= 0) return 0;
+    efloat tShapeHit = t0;
+    if (tShapeHit.low <= 0) {
+        tShapeHit = t1;
+        if (tShapeHit.high > rayTMax) return 0;
+    }
+    *tHit = tShapeHit.v;
+    return 1;
+}
+int orc_sphere(const orc_ray *r, const float *params /*16*/, float *t) { return sphere_isect(params, r->o, r->d, r->tMax, t); }
+
 /* ------------------------------------------------------------------------------------------ */
 typedef struct {
     const float *verts;      /* n_prims x 9, original primitive order */
     const uint8_t *degen;    /* n_prims, orc_tri_is_degenerate flags */
     uint32_t n_prims;
+    const uint8_t *kind;     /* nullable: 0 triangle, 1 sphere */
+    const uint32_t *sphere_of; /* prim -> index into spheres (valid where kind == 1) */
+    const float *spheres;    /* n_spheres x 16 */
 } orc_prims;
 
 /* GeometricPrimitive::Intersect, core/primitive.cpp:123-139: on a hit r.tMax = tHit. */
 static inline int prim_intersect(const orc_prims *P, uint32_t prim, orc_ray *r, orc_hit *h, orc_counters *c) {
     float t, b0, b1, b2;
     if (c) c->prim_tests++;
+    if (P->kind && P->kind[prim]) {
+        if (!sphere_isect(P->spheres + 16 * (size_t)P->sphere_of[prim], r->o, r->d, r->tMax, &t)) return 0;
+        r->tMax = t;
+        h->prim = prim; h->t = t; h->b0 = h->b1 = h->b2 = 0.f; /* no barycentrics on a sphere */
+        return 1;
+    }
     if (!tri_isect(r->o, r->d, r->tMax, P->verts + 9 * (size_t)prim, &t, &b0, &b1, &b2)) return 0;
     if (P->degen && P->degen[prim]) return 0;
     r->tMax = t;
@@ -173,6 +296,7 @@ static inline int prim_intersect(const orc_prims *P, uint32_t prim, orc_ray *r, 
 static inline int prim_intersect_p(const orc_prims *P, uint32_t prim, const orc_ray *r, orc_counters *c) {
     float t, b0, b1, b2;
     if (c) c->prim_tests++;
+    if (P->kind && P->kind[prim]) return sphere_isect(P->spheres + 16 * (size_t)P->sphere_of[prim], r->o, r->d, r->tMax, &t);
     if (!tri_isect(r->o, r->d, r->tMax, P->verts + 9 * (size_t)prim, &t, &b0, &b1, &b2)) return 0;
     /* NOTE: no degenerate-triangle rejection here: Triangle::IntersectP only has it inside the
      * alpha-mask branch (triangle.cpp:533-556), unlike Triangle::Intersect (:309-315). */
@@ -443,7 +567,13 @@ static void *run_job(void *arg) {
 static void run_batch(int any, int kind, const void *nodes, const uint32_t *indices, const float *directions,
                       uint32_t M, const float bounds[6], const float *verts, const uint8_t *degen, uint32_t n_prims,
                       const orc_ray *rays, uint64_t n, orc_hit *hits, uint8_t *occluded, orc_counters *counters,
-                      orc_counters *per_ray, int n_threads) {
+                      orc_counters *per_ray, int n_threads, const uint8_t *prim_kind, const float *spheres) {
+    uint32_t *sphere_of = 0;
+    if (prim_kind) {
+        sphere_of = (uint32_t *)calloc(n_prims ? n_prims : 1, sizeof(uint32_t));
+        uint32_t k = 0;
+        for (uint32_t i = 0; i < n_prims; ++i) if (prim_kind[i]) sphere_of[i] = k++;
+    }
     if (n_threads < 1) n_threads = 1;
     if (n_threads > 256) n_threads = 256;
     orc_job *jobs = (orc_job *)calloc((size_t)n_threads, sizeof(orc_job));
@@ -454,6 +584,7 @@ static void run_batch(int any, int kind, const void *nodes, const uint32_t *indi
         j->kind = kind; j->any = any; j->want = counters || per_ray;
         j->nodes = nodes; j->indices = indices;
         j->P.verts = verts; j->P.degen = degen; j->P.n_prims = n_prims;
+        j->P.kind = prim_kind; j->P.sphere_of = sphere_of; j->P.spheres = spheres;
         if (kind != 0) {
             j->T.kind = kind; j->T.nodes = (const orc_bsp_node *)nodes; j->T.indices = indices;
             j->T.directions = directions; j->T.M = M;
@@ -470,22 +601,22 @@ static void run_batch(int any, int kind, const void *nodes, const uint32_t *indi
         add_counters(&tot, &jobs[t].total);
     }
     if (counters) { tot.rays = n; *counters = tot; }
-    free(jobs); free(th);
+    free(jobs); free(th); free(sphere_of);
 }
 
 void orc_intersect_closest(int kind, const void *nodes, const uint32_t *indices, const float *directions, uint32_t M,
                            const float bounds[6], const float *verts, const uint8_t *degen, uint32_t n_prims,
                            const orc_ray *rays, uint64_t n, orc_hit *hits, orc_counters *counters,
-                           orc_counters *per_ray, int n_threads) {
+                           orc_counters *per_ray, int n_threads, const uint8_t *prim_kind, const float *spheres) {
     run_batch(0, kind, nodes, indices, directions, M, bounds, verts, degen, n_prims, rays, n, hits, 0, counters,
-              per_ray, n_threads);
+              per_ray, n_threads, prim_kind, spheres);
 }
 void orc_intersect_any(int kind, const void *nodes, const uint32_t *indices, const float *directions, uint32_t M,
                        const float bounds[6], const float *verts, const uint8_t *degen, uint32_t n_prims,
                        const orc_ray *rays, uint64_t n, uint8_t *occluded, orc_counters *counters,
-                       orc_counters *per_ray, int n_threads) {
+                       orc_counters *per_ray, int n_threads, const uint8_t *prim_kind, const float *spheres) {
     run_batch(1, kind, nodes, indices, directions, M, bounds, verts, degen, n_prims, rays, n, 0, occluded, counters,
-              per_ray, n_threads);
+              per_ray, n_threads, prim_kind, spheres);
 }
 
 void orc_degenerate_flags(const float *verts, const float *uvs, uint32_t n_prims, uint8_t *out) {

@@ -28,12 +28,14 @@ def lib():
             build()
         L = C.CDLL(LIB_PATH)
         common = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p,
-                  C.c_uint32, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
+                  C.c_uint32, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
         L.orc_intersect_closest.argtypes = common
         L.orc_intersect_any.argtypes = common
         L.orc_degenerate_flags.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]
         L.orc_triangle.argtypes = [C.c_void_p, C.c_void_p, C.c_int] + [C.c_void_p] * 4
         L.orc_triangle.restype = C.c_int
+        L.orc_sphere.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        L.orc_sphere.restype = C.c_int
         _lib = L
     return _lib
 
@@ -54,7 +56,11 @@ class OracleAccel:
     """Reference-format tree (dict from refbind.RefAccel.export() or b200rt builders) + triangles
     in original primitive order; runs the restated Intersect / IntersectP loops."""
 
-    def __init__(self, tree, tri_verts, tri_uvs=None):
+    def __init__(self, tree, tri_verts, tri_uvs=None, prim_kind=None, spheres=None):
+        """prim_kind: optional (n_prims,) uint8, 1 = sphere; spheres: (n_spheres, 16) float32 = WorldToObject
+        rows 0..2 (3x4), radius, 3 pad — the k-th sphere primitive uses row k."""
+        self.prim_kind = None if prim_kind is None else np.ascontiguousarray(prim_kind, np.uint8)
+        self.spheres = None if spheres is None else np.ascontiguousarray(spheres, np.float32).reshape(-1, 16)
         self.kind = KIND[tree["kind"]]
         self.nodes = np.ascontiguousarray(tree["nodes"], np.uint32)
         self.indices = np.ascontiguousarray(tree["indices"], np.uint32)
@@ -70,7 +76,8 @@ class OracleAccel:
         cnt = np.zeros(1, COUNTERS) if counters else None
         pr = np.zeros(len(rays), COUNTERS) if per_ray else None
         fn(self.kind, _p(self.nodes), _p(self.indices), _p(self.directions), self.M, _p(self.bounds), _p(self.verts),
-           _p(self.degen), len(self.verts), _p(rays), len(rays), _p(out), _p(cnt), _p(pr), n_threads)
+           _p(self.degen), len(self.verts), _p(rays), len(rays), _p(out), _p(cnt), _p(pr), n_threads,
+           _p(self.prim_kind), _p(self.spheres))
         res = [out]
         if counters:
             res.append(cnt[0])
@@ -94,3 +101,23 @@ def triangle(ray, verts, degenerate=False):
     o = [C.c_float() for _ in range(4)]
     hit = lib().orc_triangle(_p(r), _p(v), int(degenerate), *[C.byref(x) for x in o])
     return (bool(hit),) + tuple(x.value for x in o)
+
+
+def sphere_params(centers_radii):
+    """(n,4) (cx,cy,cz,radius) -> (n,16) sphere parameter rows for a pure-Translate ObjectToWorld
+    (scenes/killeroo-simple:20-24): WorldToObject = Translate(-c)."""
+    cr = np.asarray(centers_radii, np.float32).reshape(-1, 4)
+    out = np.zeros((len(cr), 16), np.float32)
+    out[:, 0] = out[:, 5] = out[:, 10] = 1
+    out[:, 3], out[:, 7], out[:, 11] = -cr[:, 0], -cr[:, 1], -cr[:, 2]
+    out[:, 12] = cr[:, 3]
+    return out
+
+
+def sphere(ray, params):
+    """Single Sphere::Intersect; returns (hit, t)."""
+    r = np.ascontiguousarray(ray, np.float32).reshape(8)
+    sp = np.ascontiguousarray(params, np.float32).reshape(16)
+    t = C.c_float()
+    hit = lib().orc_sphere(_p(r), _p(sp), C.byref(t))
+    return bool(hit), t.value

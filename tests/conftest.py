@@ -54,3 +54,18 @@ def feet_tree(g, name):
     kind = "bvh" if name == "bvh" else ("rbspkd" if name.startswith("rbspkd") else "rbsp")
     return dict(kind=kind, nodes=g[name + "_nodes"], indices=g[name + "_indices"], directions=g[name + "_directions"],
                 bounds=g[name + "_bounds"], n_prims=len(g["tri_verts"]))
+
+
+def spheres_scene(g, name):
+    """tests/golden/ref_spheres.npz -> (tree, tri_verts padded to all prims, prim_kind, sphere rows)."""
+    nt, ns = len(g["tri_verts"]), len(g["spheres"])
+    kind = "bvh" if name == "bvh" else ("kdtree" if name == "kdtree" else "rbsp")
+    tree = dict(kind=kind, nodes=g[name + "_nodes"], indices=g[name + "_indices"], directions=g[name + "_directions"],
+                bounds=g[name + "_bounds"], n_prims=nt + ns)
+    verts = np.concatenate([g["tri_verts"], np.zeros((ns, 9), np.float32)])
+    prim_kind = np.concatenate([np.zeros(nt, np.uint8), np.ones(ns, np.uint8)])
+    cr = g["spheres"]
+    rows = np.zeros((ns, 16), np.float32)  # WorldToObject = Translate(-c) (pure-Translate ObjectToWorld), radius
+    rows[:, 0] = rows[:, 5] = rows[:, 10] = 1
+    rows[:, 3], rows[:, 7], rows[:, 11], rows[:, 12] = -cr[:, 0], -cr[:, 1], -cr[:, 2], cr[:, 3]
+    return tree, verts, prim_kind, rows

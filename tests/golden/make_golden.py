@@ -13,6 +13,8 @@ Outputs (tests/golden/):
   ref_feet.npz           BASELINE config 4: the feet crop of scenes/killeroo-feet, reference-built BVH and
                          RBSP (3/7/9/13 directions) + RBSPKd(13) trees, the crop's camera rays + secondary
                          rays, and the reference's own answers per accelerator.
+  ref_spheres.npz        300 triangles + 4 full spheres in ONE aggregate (BVH, kd-tree, RBSP-7 built by the
+                         reference) and the reference's answers — pins Sphere::Intersect/IntersectP (a16).
   ref_triangle.npz       Triangle.Watertight / Reintersect / BadCases style single-triangle cases
                          (reference src/tests/shapes.cpp:28-205,544-559) with the reference's answers.
 """
@@ -144,6 +146,42 @@ def gen_triangle():
     np.savez_compressed(os.path.join(OUT, "ref_triangle.npz"), tris=tris, rays=rays, hit=hit, t=t, uv=uv, occ=occ)
 
 
+def gen_spheres():
+    """Spheres inside the aggregate (scenes/killeroo-simple:19-25 puts its area-light
+    sphere next to the triangles): a 300-triangle soup + 4 full spheres (pure Translate, one of them the
+    killeroo-simple light's size), reference-built BVH / kd-tree / RBSP-7 over all 304 primitives, and
+    the reference's answers.  Primitive order: triangles first, then the spheres."""
+    n = 300
+    P = soup(n, 17)
+    idx = np.arange(3 * n, dtype=np.int32).reshape(-1, 3)
+    tv = P[idx].reshape(-1, 9)
+    cr = np.array([[1.5, 12.0, 2.0, 3.0], [-4, -3, 5, 1.0], [6, -7, -2, 2.5], [0.25, 0.5, -8, 0.125]], np.float32)
+    sc = rb.RefScene(P, idx, spheres=cr)
+    rays = rays_for(np.array([-10, -10, -10, 10, 10, 10], np.float32), 4096, 9)
+    rng = np.random.default_rng(4)
+    aim = np.zeros((2048, 8), np.float32)  # rays aimed at the spheres, from outside and from inside
+    k = rng.integers(0, len(cr), len(aim))
+    aim[:, 0:3] = cr[k, :3] + rng.normal(size=(len(aim), 3)) * cr[k, 3:4] * rng.choice([0.5, 4.0], size=(len(aim), 1))
+    tgt = cr[k, :3] + rng.normal(size=(len(aim), 3)) * cr[k, 3:4] * 0.8
+    aim[:, 4:7] = tgt - aim[:, 0:3]
+    aim[:, 3] = np.inf
+    aim[::5, 3] = rng.uniform(0.2, 1.5, len(aim[::5]))
+    rays = np.concatenate([rays, aim]).astype(np.float32)
+    out = dict(tri_verts=tv, spheres=cr, rays=rays)
+    for name, kind, ip in [("bvh", "bvh", {}), ("kdtree", "kdtree", {}), ("rbsp7", "rbsp", {"nbDirections": 7})]:
+        acc = rb.RefAccel(sc, kind, ip)
+        ex = acc.export()
+        hits, cnt = acc.intersect(rays, counters=True)
+        occ = acc.intersect_p(rays)
+        for f in ("nodes", "indices", "directions", "bounds"):
+            out["%s_%s" % (name, f)] = ex[f]
+        out["%s_prim" % name], out["%s_t" % name], out["%s_occ" % name] = hits["prim"], hits["t"], occ
+        out["%s_tests" % name] = cnt["prim_tests"]
+        print("  spheres/%-7s nodes %d hits %d (on spheres %d) occ %d" % (name, len(ex["nodes"]), int((hits["prim"] >= 0).sum()),
+                                                                        int((hits["prim"] >= n).sum()), int(occ.sum())))
+    np.savez_compressed(os.path.join(OUT, "ref_spheres.npz"), **out)
+
+
 def gen_feet():
     """BASELINE config 4 (scenes/killeroo-feet + scripts/run_rbsps.sh): the feet crop of one killeroo,
     RBSP with nbDirections 3/7/9/13 (+ RBSPKd 13) against the BVH on the SAME rays.  To keep the
@@ -199,7 +237,8 @@ def gen_feet():
 
 
 if __name__ == "__main__":
-    which = sys.argv[1:] or ["killeroo", "small", "triangle", "feet"]
+    which = sys.argv[1:] or ["killeroo", "small", "triangle", "feet", "spheres"]
+    if "spheres" in which: gen_spheres()
     if "killeroo" in which: gen_killeroo()
     if "small" in which: gen_small()
     if "triangle" in which: gen_triangle()

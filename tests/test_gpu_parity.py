@@ -60,6 +60,26 @@ def test_golden_feet(gpu, name):
     assert c["rays"] == len(g["rays"])
 
 
+@pytest.mark.parametrize("name", ["bvh", "kdtree", "rbsp7"])
+def test_golden_spheres(gpu, name):
+    """Spheres in the aggregate (a16): reference-built trees over 300 triangles + 4 spheres."""
+    from conftest import spheres_scene
+    g = load_golden("ref_spheres.npz")
+    tree, verts, kind, rows = spheres_scene(g, name)
+    acc = gpu.B200Accel(tree, verts, prim_kind=kind, spheres=rows)
+    hits = acc.Intersect(g["rays"])
+    ref_prim = np.where(g[name + "_prim"] < 0, gpu.MISS, g[name + "_prim"]).astype(np.uint32)
+    assert np.array_equal(hits["prim"], ref_prim)
+    assert np.array_equal(hits["t"].view(np.uint32), g[name + "_t"].view(np.uint32))
+    assert np.array_equal(acc.IntersectP(g["rays"]), g[name + "_occ"])
+    h2, c = acc.Intersect(g["rays"], counters=True)   # instrumented one-ray-per-thread kernels
+    _same_hits(h2, hits)
+    assert c["prim_tests"] == int(g[name + "_tests"].sum())
+    # malformed sphere tables are rejected
+    with pytest.raises(gpu.B200RTError):
+        gpu.B200Accel(tree, verts, prim_kind=kind, spheres=rows[:2])
+
+
 def test_golden_triangles(gpu):
     """Single-triangle scenes: watertight vertex/edge rays, 1e+-8 coordinates, BadCases, degenerates."""
     g = load_golden("ref_triangle.npz")

@@ -89,3 +89,19 @@ def test_oracle_matches_reference_feet(name):
     assert np.array_equal(acc.intersect_p(g["rays"], n_threads=4), g[name + "_occ"])
     # cross-accelerator agreement on identical rays: same t as the BVH
     assert np.array_equal(g[name + "_t"], g["bvh_t"])
+
+
+@pytest.mark.parametrize("name", ["bvh", "kdtree", "rbsp7"])
+def test_oracle_matches_reference_spheres(name):
+    """Sphere::Intersect / IntersectP (SURVEY.md §8 a16) inside reference-built aggregates."""
+    from conftest import spheres_scene
+    g = load_golden("ref_spheres.npz")
+    tree, verts, kind, rows = spheres_scene(g, name)
+    acc = ob.OracleAccel(tree, verts, prim_kind=kind, spheres=rows)
+    hits, per = acc.intersect(g["rays"], per_ray=True)
+    ref_prim = np.where(g[name + "_prim"] < 0, ob.MISS, g[name + "_prim"]).astype(np.uint32)
+    assert np.array_equal(hits["prim"], ref_prim)
+    assert np.array_equal(hits["t"].view(np.uint32), g[name + "_t"].view(np.uint32))
+    assert (hits["prim"][hits["prim"] != ob.MISS] >= len(g["tri_verts"])).sum() > 1000   # plenty of sphere hits
+    assert np.array_equal(acc.intersect_p(g["rays"]), g[name + "_occ"])
+    assert np.array_equal(per["prim_tests"], g[name + "_tests"])

@@ -22,7 +22,8 @@ class SceneDesc(C.Structure):
     _fields_ = [("kind", C.c_uint32), ("nodes", C.c_void_p), ("node_count", C.c_uint32),
                 ("prim_indices", C.c_void_p), ("n_indices", C.c_uint32), ("directions", C.c_void_p),
                 ("n_directions", C.c_uint32), ("bounds", C.c_float * 6), ("tri_verts", C.c_void_p),
-                ("tri_uvs", C.c_void_p), ("n_prims", C.c_uint32)]
+                ("tri_uvs", C.c_void_p), ("n_prims", C.c_uint32), ("prim_kind", C.c_void_p),
+                ("sphere_params", C.c_void_p), ("n_spheres", C.c_uint32)]
 
 
 class CountersStruct(C.Structure):
@@ -141,9 +142,13 @@ class B200Accel:
     """Aggregate over a device-resident tree.  Mirrors pbrt's Aggregate (src/core/primitive.h:49-56,
     188-198) for ray BATCHES: WorldBound(), Intersect(rays) -> hits, IntersectP(rays) -> occluded."""
 
-    def __init__(self, tree, tri_verts, tri_uvs=None):
+    def __init__(self, tree, tri_verts, tri_uvs=None, prim_kind=None, spheres=None):
+        """prim_kind: optional (n_prims,) uint8 with 1 = full sphere; spheres: (n_spheres,16) float32 rows
+        (WorldToObject 3x4, radius, pad) — see b200rt_scene_desc in include/b200rt.h."""
         self.tree = tree
         v = np.ascontiguousarray(tri_verts, np.float32).reshape(-1, 9)
+        pk = None if prim_kind is None else np.ascontiguousarray(prim_kind, np.uint8)
+        sp = None if spheres is None else np.ascontiguousarray(spheres, np.float32).reshape(-1, 16)
         uv = None if tri_uvs is None else np.ascontiguousarray(tri_uvs, np.float32).reshape(-1, 6)
         nodes = np.ascontiguousarray(tree["nodes"], np.uint32)
         idx = np.ascontiguousarray(tree["indices"], np.uint32)
@@ -156,6 +161,7 @@ class B200Accel:
         d.directions, d.n_directions = _p(dirs), 0 if dirs is None else len(dirs)
         d.bounds = (C.c_float * 6)(*[float(x) for x in np.asarray(tree["bounds"], np.float32)])
         d.tri_verts, d.tri_uvs, d.n_prims = _p(v), _p(uv), len(v)
+        d.prim_kind, d.sphere_params, d.n_spheres = _p(pk), _p(sp), 0 if sp is None else len(sp)
         h = C.c_void_p()
         _check(lib().b200rt_scene_create(C.byref(d), C.byref(h)))
         self._h = h

@@ -1,7 +1,7 @@
 """Ray-set files: little-endian header {magic u32, version u32, n u64, flags u32, pad u32}
 followed by n x 8 float32 (ox, oy, oz, tMax, dx, dy, dz, time) — the b200rt_ray record.  Used to hand
-identical ray sets (camera rays R0, wavefront queues R1..Rk, random rays Rrand) to the GPU path, the
-oracle and the compiled reference."""
+identical ray sets (camera rays R0, wavefront queues R1..Rk, random rays Rrand) to the GPU path and to
+the CPU checkers."""
 import struct
 import numpy as np
 

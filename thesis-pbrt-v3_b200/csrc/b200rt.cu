@@ -143,6 +143,33 @@ static void fill_record(float4 *rec, const float *v, uint32_t prim, uint32_t fla
     std::memcpy(&rec[1].w, &flags, 4);
 }
 
+// prim -> index of its sphere parameter row (valid where prim_kind[prim] != 0); validates the counts
+static int sphere_table(const b200rt_scene_desc *d, std::vector<uint32_t> &sphereOf) {
+    sphereOf.assign(d->n_prims, 0);
+    uint32_t k = 0;
+    if (d->prim_kind)
+        for (uint32_t i = 0; i < d->n_prims; ++i) {
+            if (d->prim_kind[i] > 1) return fail(B200RT_EUNSUPPORTED, "prim_kind[%u] = %u: only triangles (0) and full spheres (1)", i, d->prim_kind[i]);
+            if (d->prim_kind[i]) sphereOf[i] = k++;
+        }
+    if (k != d->n_spheres) return fail(B200RT_EINVAL, "prim_kind marks %u spheres but n_spheres = %u", k, d->n_spheres);
+    if (k && !d->sphere_params) return fail(B200RT_EINVAL, "sphere_params is null");
+    return B200RT_OK;
+}
+static int upload_spheres(const b200rt_scene_desc *d, b200rt_scene *s) {
+    if (!d->n_spheres) return B200RT_OK;
+    CU(cudaMalloc(&s->d_spheres, (size_t)d->n_spheres * 64));
+    CU(cudaMemcpy(s->d_spheres, d->sphere_params, (size_t)d->n_spheres * 64, cudaMemcpyHostToDevice));
+    return B200RT_OK;
+}
+static void fill_sphere_record(float4 *rec, uint32_t prim, uint32_t flags, uint32_t sphereIdx) {
+    rec[0] = rec[1] = rec[2] = make_float4(0.f, 0.f, 0.f, 0.f);
+    flags |= B200RT_PRIM_SPHERE;
+    std::memcpy(&rec[0].w, &prim, 4);
+    std::memcpy(&rec[1].w, &flags, 4);
+    std::memcpy(&rec[2].w, &sphereIdx, 4);
+}
+
 struct RefBvhNode {  // LinearBVHNode, bvh.cpp:123-152
     float lo[3], hi[3];
     int32_t offset;
@@ -182,6 +209,8 @@ static int build_bvh_scene(const b200rt_scene_desc *d, b200rt_scene *s) {
         }
         if (maxDepth > 64) return fail(B200RT_EUNSUPPORTED, "BVH depth %u exceeds the reference's 64-entry traversal stack", maxDepth);
     }
+    std::vector<uint32_t> sphereOf;
+    { int rc = sphere_table(d, sphereOf); if (rc) return rc; }
     // triangles in slot order, flagged at leaf ends
     std::vector<float4> recs((size_t)3 * d->n_prims);
     std::vector<uint8_t> last(d->n_prims, 0);
@@ -193,6 +222,7 @@ static int build_bvh_scene(const b200rt_scene_desc *d, b200rt_scene *s) {
         if (prim >= d->n_prims) return fail(B200RT_EINVAL, "BVH prim_indices[%u] = %u out of range", slot, prim);
         const float *v = d->tri_verts + 9 * (size_t)prim;
         uint32_t flags = last[slot] ? B200RT_TRI_LAST : 0u;
+        if (d->prim_kind && d->prim_kind[prim]) { fill_sphere_record(&recs[3 * (size_t)slot], prim, flags, sphereOf[prim]); continue; }
         if (tri_tail_rejects(v, d->tri_uvs ? d->tri_uvs + 6 * (size_t)prim : nullptr)) flags |= B200RT_TRI_DEGENERATE;
         fill_record(&recs[3 * (size_t)slot], v, prim, flags);
     }
@@ -221,8 +251,10 @@ static int build_bvh_scene(const b200rt_scene_desc *d, b200rt_scene *s) {
         CU(cudaMalloc(&s->d_prim_tris, byPrim.size() * sizeof(float4)));
         CU(cudaMemcpy(s->d_prim_tris, byPrim.data(), byPrim.size() * sizeof(float4), cudaMemcpyHostToDevice));
     }
+    { int rc = upload_spheres(d, s); if (rc) return rc; }
     s->bvh.nodes = (const BvhNode2 *)s->d_nodes;
     s->bvh.tris = s->d_tris;
+    s->bvh.spheres = s->d_spheres;
     for (int k = 0; k < 3; ++k) { s->bvh.root[k] = ref[0].lo[k]; s->bvh.root[3 + k] = ref[0].hi[k]; }
     s->bvh.rootRef = ref_of(0);
     std::memcpy(s->bounds, s->bvh.root, sizeof(s->bounds));
@@ -260,8 +292,11 @@ static int build_bsp_scene(const b200rt_scene_desc *d, b200rt_scene *s) {
     if (maxDepth > 64) return fail(B200RT_EUNSUPPORTED, "tree depth %u exceeds the reference's 64-entry todo stack", maxDepth);
     for (uint32_t i = 0; i < d->n_indices; ++i)
         if (d->prim_indices[i] >= d->n_prims) return fail(B200RT_EINVAL, "prim_indices[%u] out of range", i);
+    std::vector<uint32_t> sphereOf;
+    { int rc = sphere_table(d, sphereOf); if (rc) return rc; }
     std::vector<float4> recs((size_t)3 * d->n_prims);
     for (uint32_t p = 0; p < d->n_prims; ++p) {
+        if (d->prim_kind && d->prim_kind[p]) { fill_sphere_record(&recs[3 * (size_t)p], p, 0u, sphereOf[p]); continue; }
         const float *v = d->tri_verts + 9 * (size_t)p;
         uint32_t flags = tri_tail_rejects(v, d->tri_uvs ? d->tri_uvs + 6 * (size_t)p : nullptr) ? B200RT_TRI_DEGENERATE : 0u;
         fill_record(&recs[3 * (size_t)p], v, p, flags);
@@ -272,9 +307,11 @@ static int build_bsp_scene(const b200rt_scene_desc *d, b200rt_scene *s) {
     if (d->n_indices) CU(cudaMemcpy(s->d_indices, d->prim_indices, (size_t)d->n_indices * 4, cudaMemcpyHostToDevice));
     CU(cudaMalloc(&s->d_tris, std::max<size_t>(1, recs.size()) * sizeof(float4)));
     if (!recs.empty()) CU(cudaMemcpy(s->d_tris, recs.data(), recs.size() * sizeof(float4), cudaMemcpyHostToDevice));
+    { int rc = upload_spheres(d, s); if (rc) return rc; }
     s->bsp.nodes = (const uint2 *)s->d_nodes;
     s->bsp.indices = s->d_indices;
     s->bsp.tris = s->d_tris;
+    s->bsp.spheres = s->d_spheres;
     s->d_prim_tris = s->d_tris;
     std::memcpy(s->bsp.bounds, d->bounds, sizeof(s->bsp.bounds));
     std::memset(s->bsp.dirs, 0, sizeof(s->bsp.dirs));
@@ -317,7 +354,7 @@ extern "C" void b200rt_scene_destroy(b200rt_scene *s) {
     if (!s) return;
     b200rt_wavefront_release(s);
     if (s->d_prim_tris != s->d_tris) cudaFree(s->d_prim_tris);
-    cudaFree(s->d_nodes); cudaFree(s->d_indices); cudaFree(s->d_tris);
+    cudaFree(s->d_nodes); cudaFree(s->d_indices); cudaFree(s->d_tris); cudaFree(s->d_spheres);
     cudaFree(s->d_stage_in); cudaFree(s->d_stage_out); cudaFree(s->d_counters); cudaFree(s->d_pc);
     for (auto &l : s->lanes) {
         cudaFree(l.d_in); cudaFree(l.d_out);

@@ -29,7 +29,8 @@ struct __align__(16) BvhNode2 {
 
 struct BvhView {
     const BvhNode2 *nodes;
-    const float4 *tris;  // 3 x float4 per slot: (p0, primId) (p1, flags) (p2, 0)
+    const float4 *tris;  // 3 x float4 per slot: (p0, primId) (p1, flags) (p2, sphere index)
+    const float4 *spheres;  // 4 x float4 per sphere: WorldToObject rows 0..2, (radius, -, -, -)
     float root[6];       // nodes[0].bounds of the reference tree
     uint32_t rootRef;
 };
@@ -40,6 +41,7 @@ struct BspView {
     const uint2 *nodes;
     const uint32_t *indices;
     const float4 *tris;  // 3 x float4 per ORIGINAL primitive
+    const float4 *spheres;
     float bounds[6];
     float dirs[13 * 3];  // RBSPShared.h:29-74, M <= 13
     uint32_t M, bitOffset, bitMask, leafTag;
@@ -63,8 +65,16 @@ struct HitRec {
 // ANY = GeometricPrimitive::IntersectP (:118-121): Triangle::IntersectP has NO degenerate-triangle
 // rejection outside its alpha-mask branch (triangle.cpp:533-556), unlike Intersect (:309-315).
 template <bool ANY>
-__device__ __forceinline__ bool prim_closest(RayCtx &r, const float4 v0, const float4 v1, const float4 v2, HitRec &h) {
+__device__ __forceinline__ bool prim_closest(RayCtx &r, const float4 v0, const float4 v1, const float4 v2, HitRec &h,
+                                             const float4 *spheres) {
     float t, b0, b1, b2;
+    if (__float_as_uint(v1.w) & B200RT_PRIM_SPHERE) {  // Sphere::Intersect / IntersectP (sphere.cpp:49, 158)
+        if (!sphere_test(spheres + 4 * (size_t)__float_as_uint(v2.w), r.ox, r.oy, r.oz, r.dx, r.dy, r.dz, r.tMax, t))
+            return false;
+        r.tMax = t;
+        h.prim = __float_as_uint(v0.w); h.t = t; h.b0 = h.b1 = h.b2 = 0.f;  // no barycentrics on a sphere
+        return true;
+    }
     if (!tri_test(r, v0, v1, v2, t, b0, b1, b2)) return false;
     if (!ANY && (__float_as_uint(v1.w) & B200RT_TRI_DEGENERATE)) return false;
     r.tMax = t;
@@ -73,8 +83,8 @@ __device__ __forceinline__ bool prim_closest(RayCtx &r, const float4 v0, const f
 }
 
 template <bool ANY>
-__device__ __forceinline__ bool prim_closest(RayCtx &r, const float4 *rec, HitRec &h) {
-    return prim_closest<ANY>(r, __ldg(rec), __ldg(rec + 1), __ldg(rec + 2), h);
+__device__ __forceinline__ bool prim_closest(RayCtx &r, const float4 *rec, HitRec &h, const float4 *spheres) {
+    return prim_closest<ANY>(r, __ldg(rec), __ldg(rec + 1), __ldg(rec + 2), h, spheres);
 }
 
 // ---- BVH --------------------------------------------------------------------------------------
@@ -103,7 +113,7 @@ __device__ __forceinline__ bool bvh_trace(const BvhView &S, RayCtx &r, HitRec &h
             for (;;) {
                 if (COUNT) cnt.tests++;
                 const float4 v0 = __ldg(rec), v1 = __ldg(rec + 1), v2 = __ldg(rec + 2);
-                if (prim_closest<ANY>(r, v0, v1, v2, h)) {
+                if (prim_closest<ANY>(r, v0, v1, v2, h, S.spheres)) {
                     hit = true;
                     if (ANY) return true;
                 }
@@ -213,12 +223,12 @@ __device__ __forceinline__ bool bsp_trace(const BspView &S, RayCtx &r, HitRec &h
             const uint32_t np = n.y >> off;
             if (np == 1) {
                 if (COUNT) cnt.tests++;
-                if (prim_closest<ANY>(r, S.tris + 3 * (size_t)n.x, h)) { hit = true; if (ANY) return true; }
+                if (prim_closest<ANY>(r, S.tris + 3 * (size_t)n.x, h, S.spheres)) { hit = true; if (ANY) return true; }
             } else {
                 for (uint32_t i = 0; i < np; ++i) {
                     if (COUNT) { cnt.tests++; cnt.idx++; }
                     const uint32_t p = __ldg(S.indices + n.x + i);
-                    if (prim_closest<ANY>(r, S.tris + 3 * (size_t)p, h)) { hit = true; if (ANY) return true; }
+                    if (prim_closest<ANY>(r, S.tris + 3 * (size_t)p, h, S.spheres)) { hit = true; if (ANY) return true; }
                 }
             }
             if (todoPos > 0) {

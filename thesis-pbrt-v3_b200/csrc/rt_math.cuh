@@ -15,6 +15,7 @@ namespace b200rt {
 
 #define B200RT_TRI_LAST 1u        // v1.w bit 0: last record of its BVH leaf
 #define B200RT_TRI_DEGENERATE 2u  // v1.w bit 1: Triangle::Intersect's tail rejects every hit (triangle.cpp:309-315)
+#define B200RT_PRIM_SPHERE 4u     // v1.w bit 2: the record is a sphere; v2.w = index into the sphere parameter array
 
 // gamma(n) = n*eps / (1 - n*eps) evaluated in float with eps = 2^-24 (pbrt.h:289-291).
 __host__ __device__ constexpr float rt_gamma(int n) {
@@ -167,6 +168,104 @@ __device__ __forceinline__ bool tri_test(const RayCtx &r, const float4 v0, const
     const float deltaT = 3 * (kGamma3 * maxE * maxZt + deltaE * maxZt + deltaZ * maxE) * fabsf(invDet);
     if (t <= deltaT) return false;
     tOut = t; b0o = b0; b1o = b1; b2o = b2;
+    return true;
+}
+
+// ---- Sphere (src/shapes/sphere.cpp:49-81, 158-190), full spheres only -----------------------------
+// NextFloatUp / NextFloatDown, pbrt.h:207-253
+__device__ __forceinline__ float next_up(float v) {
+    if (isinf(v) && v > 0.f) return v;
+    if (v == -0.f) v = 0.f;
+    uint32_t ui = __float_as_uint(v);
+    if (v >= 0) ++ui; else --ui;
+    return __uint_as_float(ui);
+}
+__device__ __forceinline__ float next_down(float v) {
+    if (isinf(v) && v < 0.f) return v;
+    if (v == 0.f) v = -0.f;
+    uint32_t ui = __float_as_uint(v);
+    if (v > 0) --ui; else ++ui;
+    return __uint_as_float(ui);
+}
+// EFloat (src/core/efloat.h:48-214, release build): value + conservative interval
+struct EFloat { float v, low, high; };
+__device__ __forceinline__ float std_min(float a, float b) { return (b < a) ? b : a; }
+__device__ __forceinline__ EFloat ef_make(float v, float err) {
+    EFloat r; r.v = v;
+    if (err == 0.f) r.low = r.high = v;
+    else { r.low = next_down(v - err); r.high = next_up(v + err); }
+    return r;
+}
+__device__ __forceinline__ EFloat ef_add(EFloat a, EFloat b) {
+    EFloat r; r.v = a.v + b.v; r.low = next_down(a.low + b.low); r.high = next_up(a.high + b.high); return r;
+}
+__device__ __forceinline__ EFloat ef_sub(EFloat a, EFloat b) {
+    EFloat r; r.v = a.v - b.v; r.low = next_down(a.low - b.high); r.high = next_up(a.high - b.low); return r;
+}
+__device__ __forceinline__ EFloat ef_mul(EFloat a, EFloat b) {
+    EFloat r; r.v = a.v * b.v;
+    const float p0 = a.low * b.low, p1 = a.high * b.low, p2 = a.low * b.high, p3 = a.high * b.high;
+    r.low = next_down(std_min(std_min(p0, p1), std_min(p2, p3)));
+    r.high = next_up(std_max(std_max(p0, p1), std_max(p2, p3)));
+    return r;
+}
+__device__ __forceinline__ EFloat ef_div(EFloat a, EFloat b) {
+    EFloat r; r.v = a.v / b.v;
+    if (b.low < 0 && b.high > 0) { r.low = -__int_as_float(0x7f800000); r.high = __int_as_float(0x7f800000); }
+    else {
+        const float d0 = a.low / b.low, d1 = a.high / b.low, d2 = a.low / b.high, d3 = a.high / b.high;
+        r.low = next_down(std_min(std_min(d0, d1), std_min(d2, d3)));
+        r.high = next_up(std_max(std_max(d0, d1), std_max(d2, d3)));
+    }
+    return r;
+}
+// sp: 4 x float4 = WorldToObject rows 0..2 (affine), (radius, -, -, -).  Transform of the ray with
+// error bounds: transform.h:278-300, 337-352, 382-394; quadratic: efloat.h:267-285.  For a FULL sphere
+// the clipping tests of sphere.cpp:86-103 cannot fire, so hit and tHit follow from the quadratic alone.
+// noinline: cold path (one light sphere among 10^5 triangles) kept out of the traversal loops.
+static __device__ __noinline__ bool sphere_test(const float4 *sp, float ox_, float oy_, float oz_, float dx_, float dy_,
+                                         float dz_, float rayTMax, float &tHit) {
+    const float4 m0 = __ldg(sp), m1 = __ldg(sp + 1), m2 = __ldg(sp + 2);
+    const float radius = __ldg(sp + 3).x;
+    float ox = m0.x * ox_ + m0.y * oy_ + m0.z * oz_ + m0.w;
+    float oy = m1.x * ox_ + m1.y * oy_ + m1.z * oz_ + m1.w;
+    float oz = m2.x * ox_ + m2.y * oy_ + m2.z * oz_ + m2.w;
+    const float oex = kGamma3 * (fabsf(m0.x * ox_) + fabsf(m0.y * oy_) + fabsf(m0.z * oz_) + fabsf(m0.w));
+    const float oey = kGamma3 * (fabsf(m1.x * ox_) + fabsf(m1.y * oy_) + fabsf(m1.z * oz_) + fabsf(m1.w));
+    const float oez = kGamma3 * (fabsf(m2.x * ox_) + fabsf(m2.y * oy_) + fabsf(m2.z * oz_) + fabsf(m2.w));
+    const float dex = kGamma3 * (fabsf(m0.x * dx_) + fabsf(m0.y * dy_) + fabsf(m0.z * dz_));
+    const float dey = kGamma3 * (fabsf(m1.x * dx_) + fabsf(m1.y * dy_) + fabsf(m1.z * dz_));
+    const float dez = kGamma3 * (fabsf(m2.x * dx_) + fabsf(m2.y * dy_) + fabsf(m2.z * dz_));
+    const float dx = m0.x * dx_ + m0.y * dy_ + m0.z * dz_;
+    const float dy = m1.x * dx_ + m1.y * dy_ + m1.z * dz_;
+    const float dz = m2.x * dx_ + m2.y * dy_ + m2.z * dz_;
+    const float lengthSquared = dx * dx + dy * dy + dz * dz;
+    if (lengthSquared > 0) {
+        const float dt = (fabsf(dx) * oex + fabsf(dy) * oey + fabsf(dz) * oez) / lengthSquared;
+        ox += dx * dt; oy += dy * dt; oz += dz * dt;
+    }
+    const EFloat eox = ef_make(ox, oex), eoy = ef_make(oy, oey), eoz = ef_make(oz, oez);
+    const EFloat edx = ef_make(dx, dex), edy = ef_make(dy, dey), edz = ef_make(dz, dez);
+    const EFloat a = ef_add(ef_add(ef_mul(edx, edx), ef_mul(edy, edy)), ef_mul(edz, edz));
+    const EFloat b = ef_mul(ef_make(2.f, 0.f), ef_add(ef_add(ef_mul(edx, eox), ef_mul(edy, eoy)), ef_mul(edz, eoz)));
+    const EFloat er = ef_make(radius, 0.f);
+    const EFloat c = ef_sub(ef_add(ef_add(ef_mul(eox, eox), ef_mul(eoy, eoy)), ef_mul(eoz, eoz)), ef_mul(er, er));
+    const double discrim = (double)b.v * (double)b.v - 4. * (double)a.v * (double)c.v;
+    if (discrim < 0.) return false;
+    const double rootDiscrim = sqrt(discrim);
+    const EFloat frd = ef_make((float)rootDiscrim, (float)((double)5.9604644775390625e-08f * rootDiscrim));
+    EFloat q;
+    if (b.v < 0) q = ef_mul(ef_make(-.5f, 0.f), ef_sub(b, frd));
+    else q = ef_mul(ef_make(-.5f, 0.f), ef_add(b, frd));
+    EFloat t0 = ef_div(q, a), t1 = ef_div(c, q);
+    if (t0.v > t1.v) { const EFloat s = t0; t0 = t1; t1 = s; }
+    if (t0.high > rayTMax || t1.low <= 0) return false;
+    EFloat tShapeHit = t0;
+    if (tShapeHit.low <= 0) {
+        tShapeHit = t1;
+        if (tShapeHit.high > rayTMax) return false;
+    }
+    tHit = tShapeHit.v;
     return true;
 }
 

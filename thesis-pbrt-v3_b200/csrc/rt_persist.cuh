@@ -91,7 +91,7 @@ __device__ __forceinline__ void warp_exit(PersistCounters *pc, int lane) {
 }
 
 template <bool ANY>
-__global__ void __launch_bounds__(B200RT_PBLOCK)
+__global__ void __launch_bounds__(B200RT_PBLOCK, 8)
 bvh_persistent_kernel(const __grid_constant__ BvhView S, const float4 *__restrict__ rays, uint64_t n64,
                       const uint32_t *__restrict__ n_dev, b200rt_hit *__restrict__ hits,
                       uint8_t *__restrict__ occluded, PersistCounters *pc, uint32_t thresh,
@@ -206,7 +206,7 @@ bvh_persistent_kernel(const __grid_constant__ BvhView S, const float4 *__restric
                     const float4 *rec = S.tris + 3 * (size_t)(cur & ~B200RT_LEAF_BIT);
                     const float4 v0 = __ldg(rec), v1 = __ldg(rec + 1), v2 = __ldg(rec + 2);
                     bool stop = false;
-                    if (prim_closest<ANY>(r, v0, v1, v2, h)) {
+                    if (prim_closest<ANY>(r, v0, v1, v2, h, S.spheres)) {
                         hit = true;
                         if (ANY) stop = true;
                     }
@@ -244,7 +244,7 @@ bvh_persistent_kernel(const __grid_constant__ BvhView S, const float4 *__restric
 #define B200RT_ST_LEAF 2u
 
 template <int KIND, bool ANY>
-__global__ void __launch_bounds__(B200RT_PBLOCK)
+__global__ void __launch_bounds__(B200RT_PBLOCK, 8)
 bsp_persistent_kernel(const __grid_constant__ BspView S, const float4 *__restrict__ rays, uint64_t n64,
                       const uint32_t *__restrict__ n_dev, b200rt_hit *__restrict__ hits,
                       uint8_t *__restrict__ occluded, PersistCounters *pc, uint32_t thresh, uint32_t chunk) {
@@ -334,7 +334,7 @@ bsp_persistent_kernel(const __grid_constant__ BspView S, const float4 *__restric
                 }
             } else if (state == B200RT_ST_LEAF) {
                 const uint32_t p = lsingle ? li : __ldg(S.indices + li);
-                if (prim_closest<ANY>(r, S.tris + 3 * (size_t)p, h)) {
+                if (prim_closest<ANY>(r, S.tris + 3 * (size_t)p, h, S.spheres)) {
                     hit = true;
                     if (ANY) finished = true;
                 }

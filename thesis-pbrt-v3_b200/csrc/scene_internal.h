@@ -12,6 +12,7 @@ struct b200rt_scene {
     void *d_nodes = nullptr;
     uint32_t *d_indices = nullptr;
     float4 *d_tris = nullptr;       // traversal order (BVH: leaf slots; kd/RBSP: original primitive order)
+    float4 *d_spheres = nullptr;    // 4 x float4 per sphere primitive (rt_math.cuh sphere_test)
     float4 *d_prim_tris = nullptr;  // original primitive order, for the shading stage (== d_tris for kd/RBSP)
     float bounds[6] = {0, 0, 0, 0, 0, 0};
     uint32_t n_prims = 0;

@@ -83,21 +83,6 @@ __device__ __forceinline__ uint32_t warp_append(bool pred, uint32_t *counter) {
     return base + __popc(m & ((1u << lane) - 1u));
 }
 
-// NextFloatUp / NextFloatDown, pbrt.h:207-253
-__device__ __forceinline__ float next_up(float v) {
-    if (isinf(v) && v > 0.f) return v;
-    if (v == -0.f) v = 0.f;
-    uint32_t ui = __float_as_uint(v);
-    if (v >= 0) ++ui; else --ui;
-    return __uint_as_float(ui);
-}
-__device__ __forceinline__ float next_down(float v) {
-    if (isinf(v) && v < 0.f) return v;
-    if (v == 0.f) v = -0.f;
-    uint32_t ui = __float_as_uint(v);
-    if (v > 0) --ui; else ++ui;
-    return __uint_as_float(ui);
-}
 // OffsetRayOrigin, src/core/geometry.h:1782-1802
 __device__ __forceinline__ float3 offset_ray_origin(float3 p, float3 pError, float3 n, float3 w) {
     const float d = fabsf(n.x) * pError.x + fabsf(n.y) * pError.y + fabsf(n.z) * pError.z;
@@ -154,7 +139,7 @@ __global__ void k_shade(const __grid_constant__ WfParams P, uint32_t depth, uint
         const b200rt_hit h = hits[i];
         if (h.prim != B200RT_MISS && depth < P.max_depth) {  // path.cpp:110
             path = qPath[i];
-            const float4 ro = rays[2 * (size_t)i], rd = rays[2 * (size_t)i + 1];
+            const float4 rd = rays[2 * (size_t)i + 1];
             const float4 a = __ldg(primTris + 3 * (size_t)h.prim), b = __ldg(primTris + 3 * (size_t)h.prim + 1),
                          c = __ldg(primTris + 3 * (size_t)h.prim + 2);
             // pHit, pError (triangle.cpp:318-326)
@@ -167,7 +152,8 @@ __global__ void k_shade(const __grid_constant__ WfParams P, uint32_t depth, uint
             const float3 e0 = make_float3(a.x - c.x, a.y - c.y, a.z - c.z), e1 = make_float3(b.x - c.x, b.y - c.y, b.z - c.z);
             float3 ng = make_float3(e0.y * e1.z - e0.z * e1.y, e0.z * e1.x - e0.x * e1.z, e0.x * e1.y - e0.y * e1.x);
             const float nl = sqrtf(ng.x * ng.x + ng.y * ng.y + ng.z * ng.z);
-            if (nl > 0.f) {
+            // a sphere primitive (killeroo-simple's emitter: matte Kd = 0) ends the path: nothing to reflect
+            if (nl > 0.f && !(__float_as_uint(b.w) & B200RT_PRIM_SPHERE)) {
                 ng.x /= nl; ng.y /= nl; ng.z /= nl;
                 const float3 wo = make_float3(-rd.x, -rd.y, -rd.z);
                 const float side = (ng.x * wo.x + ng.y * wo.y + ng.z * wo.z) < 0.f ? -1.f : 1.f;
