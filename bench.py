@@ -225,6 +225,8 @@ def main():
     torch.cuda.set_device(local)
     if world > 1:
         import datetime
+        # NCCL's banner ("NCCL version ...") goes to stdout by default; stdout carries exactly one JSON line
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local), timeout=datetime.timedelta(seconds=180))
     b200rt.init(local)
     dev = torch.device("cuda", local)
