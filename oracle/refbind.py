@@ -25,10 +25,11 @@ def available():
 _lib = None
 
 
-def lib():
-    global _lib
-    if _lib is None:
-        L = C.CDLL(LIB_PATH)
+def bind(path):
+    """Declares the ref_api.h prototypes on the shared library at `path` (libpbrtref.so, or the host-plugin
+    test library tests/hostplugin builds on top of the same objects)."""
+    if True:
+        L = C.CDLL(path)
         L.ref_scene_create.restype = C.c_void_p
         L.ref_scene_create.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int]
         L.ref_scene_destroy.argtypes = [C.c_void_p]
@@ -45,7 +46,13 @@ def lib():
         L.ref_intersect_p.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_int]
         L.ref_prim_intersect.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_uint64, C.c_void_p]
         L.ref_prim_intersect_p.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_uint64, C.c_void_p]
-        _lib = L
+    return L
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        _lib = bind(LIB_PATH)
     return _lib
 
 
@@ -56,31 +63,32 @@ def _p(a):
 class RefScene:
     """vector<shared_ptr<Primitive>>: one GeometricPrimitive per triangle, then the spheres."""
 
-    def __init__(self, P, indices, uv=None, spheres=None):
+    def __init__(self, P, indices, uv=None, spheres=None, L=None):
+        self.L = L or lib()
         self.P = np.ascontiguousarray(P, np.float32).reshape(-1, 3)
         self.idx = np.ascontiguousarray(indices, np.int32).reshape(-1, 3)
         self.uv = None if uv is None else np.ascontiguousarray(uv, np.float32).reshape(-1, 2)
         self.spheres = None if spheres is None else np.ascontiguousarray(spheres, np.float32).reshape(-1, 4)
         ns = 0 if self.spheres is None else len(self.spheres)
-        self.h = lib().ref_scene_create(_p(self.P), len(self.P), _p(self.idx), len(self.idx), _p(self.uv),
+        self.h = self.L.ref_scene_create(_p(self.P), len(self.P), _p(self.idx), len(self.idx), _p(self.uv),
                                         _p(self.spheres), ns)
-        self.n_prims = lib().ref_scene_num_prims(self.h)
+        self.n_prims = self.L.ref_scene_num_prims(self.h)
 
     def prim_intersect(self, prim, rays):
         rays = np.ascontiguousarray(rays, np.float32).reshape(-1, 8)
         hits = np.zeros(len(rays), REF_HIT)
-        lib().ref_prim_intersect(self.h, int(prim), _p(rays), len(rays), _p(hits))
+        self.L.ref_prim_intersect(self.h, int(prim), _p(rays), len(rays), _p(hits))
         return hits
 
     def prim_intersect_p(self, prim, rays):
         rays = np.ascontiguousarray(rays, np.float32).reshape(-1, 8)
         occ = np.zeros(len(rays), np.uint8)
-        lib().ref_prim_intersect_p(self.h, int(prim), _p(rays), len(rays), _p(occ))
+        self.L.ref_prim_intersect_p(self.h, int(prim), _p(rays), len(rays), _p(occ))
         return occ
 
     def __del__(self):
         if getattr(self, "h", None):
-            lib().ref_scene_destroy(self.h)
+            self.L.ref_scene_destroy(self.h)
             self.h = None
 
 
@@ -112,17 +120,18 @@ class RefAccel:
         ivals = (C.c_int * max(1, len(ip)))(*ip.values())
         fnames = (C.c_char_p * (len(fp) + 1))(*[k.encode() for k in fp], None)
         fvals = (C.c_float * max(1, len(fp)))(*fp.values())
-        self.h = lib().ref_accel_create(scene.h, kind.encode(), inames, ivals, fnames, fvals)
+        self.L = scene.L
+        self.h = self.L.ref_accel_create(scene.h, kind.encode(), inames, ivals, fnames, fvals)
         if not self.h:
             raise ValueError("unknown accelerator kind %r" % kind)
 
     def export(self):
         ti = TreeInfo()
-        lib().ref_accel_info(self.h, C.byref(ti))
+        self.L.ref_accel_info(self.h, C.byref(ti))
         nodes = np.zeros((ti.node_count, ti.node_stride // 4), np.uint32)
         idx = np.zeros(ti.n_indices, np.uint32)
         dirs = np.zeros((ti.n_directions, 3), np.float32)
-        lib().ref_accel_export(self.h, _p(nodes), _p(idx), _p(dirs))
+        self.L.ref_accel_export(self.h, _p(nodes), _p(idx), _p(dirs))
         return dict(kind=self.kind, nodes=nodes, indices=idx, directions=dirs,
                     bounds=np.array(list(ti.bounds), np.float32), n_prims=ti.n_prims)
 
@@ -130,17 +139,17 @@ class RefAccel:
         rays = np.ascontiguousarray(rays, np.float32).reshape(-1, 8)
         hits = np.zeros(len(rays), REF_HIT)
         cnt = np.zeros(len(rays), REF_CNT) if counters else None
-        lib().ref_intersect(self.h, _p(rays), len(rays), _p(hits), _p(cnt), n_threads)
+        self.L.ref_intersect(self.h, _p(rays), len(rays), _p(hits), _p(cnt), n_threads)
         return (hits, cnt) if counters else hits
 
     def intersect_p(self, rays, counters=False, n_threads=1):
         rays = np.ascontiguousarray(rays, np.float32).reshape(-1, 8)
         occ = np.zeros(len(rays), np.uint8)
         cnt = np.zeros(len(rays), REF_CNT) if counters else None
-        lib().ref_intersect_p(self.h, _p(rays), len(rays), _p(occ), _p(cnt), n_threads)
+        self.L.ref_intersect_p(self.h, _p(rays), len(rays), _p(occ), _p(cnt), n_threads)
         return (occ, cnt) if counters else occ
 
     def __del__(self):
         if getattr(self, "h", None):
-            lib().ref_accel_destroy(self.h)
+            self.L.ref_accel_destroy(self.h)
             self.h = None

@@ -1,0 +1,143 @@
+"""The C++ drop-in (`Accelerator "b200"`, thesis-pbrt-v3_b200/host/b200accel.cpp) driven through the REFERENCE'S
+OWN Primitive interface, side by side with the reference's own accelerators built over the same
+vector<shared_ptr<Primitive>> in the same process (tests/hostplugin builds the combined library into
+oracle/_ref/, which travels to the GPU box).  Bar: isect.primitive, ray.tMax, SurfaceInteraction::uv and ::p
+bit-identical; IntersectP identical."""
+import ctypes as C
+import os
+import subprocess
+import numpy as np
+import pytest
+from conftest import ROOT
+
+HOSTLIB = os.path.join(ROOT, "oracle", "_ref", "libpbrt_b200host.so")
+
+
+@pytest.fixture(scope="module")
+def host(built_lib):
+    if os.path.isdir("/root/reference/src") and os.path.exists("/usr/bin/make"):
+        subprocess.check_call(["make", "-s", "-C", os.path.join(ROOT, "oracle", "ref"), "-j8"])
+        subprocess.check_call(["make", "-s", "-C", os.path.join(ROOT, "tests", "hostplugin")])
+    if not os.path.exists(HOSTLIB):
+        pytest.skip("oracle/_ref/libpbrt_b200host.so not built (needs /root/reference)")
+    from oracle import refbind as rb
+    L = rb.bind(HOSTLIB)
+    L.plugin_accel_create.restype = C.c_void_p
+    L.plugin_accel_create.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    L.plugin_is_current.argtypes = [C.c_void_p]
+    L.plugin_world_bound.argtypes = [C.c_void_p, C.c_void_p]
+    L.plugin_intersect_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]
+    L.plugin_intersect_p_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]
+    return rb, L
+
+
+class PluginAccel:
+    """`Accelerator "b200" "string tree" tree "string builder" builder + the reference's own parameter names`."""
+
+    def __init__(self, rb, L, scene, tree, builder="reference", int_params=None):
+        ip = int_params or {}
+        inames = (C.c_char_p * (len(ip) + 1))(*[k.encode() for k in ip], None)
+        ivals = (C.c_int * max(1, len(ip)))(*ip.values())
+        self.rb, self.L, self.scene = rb, L, scene
+        self.h = L.plugin_accel_create(scene.h, tree.encode(), builder.encode(), inames, ivals, None, None)
+
+    def intersect(self, rays):   # per-ray Aggregate::Intersect through the reference harness
+        hits = np.zeros(len(rays), self.rb.REF_HIT)
+        self.L.ref_intersect(self.h, rays.ctypes.data, len(rays), hits.ctypes.data, None, 1)
+        return hits
+
+    def intersect_p(self, rays):
+        occ = np.zeros(len(rays), np.uint8)
+        self.L.ref_intersect_p(self.h, rays.ctypes.data, len(rays), occ.ctypes.data, None, 1)
+        return occ
+
+    def intersect_batch(self, rays):
+        hits = np.zeros(len(rays), self.rb.REF_HIT)
+        assert self.L.plugin_intersect_batch(self.h, rays.ctypes.data, len(rays), hits.ctypes.data) == 0
+        return hits
+
+    def intersect_p_batch(self, rays):
+        occ = np.zeros(len(rays), np.uint8)
+        assert self.L.plugin_intersect_p_batch(self.h, rays.ctypes.data, len(rays), occ.ctypes.data) == 0
+        return occ
+
+
+def _scene(rb, L, n_tris=1500, seed=3, spheres=True):
+    from b200rt import scenes
+    v = scenes.soup(n_tris, seed=seed).reshape(-1, 3)
+    idx = np.arange(len(v), dtype=np.int32).reshape(-1, 3)
+    rng = np.random.default_rng(seed)
+    uv = rng.random((len(v), 2), dtype=np.float32)
+    sp = np.array([[0, 0, 0, 2.5], [6, -3, 2, 1.25]], np.float32) if spheres else None
+    return rb.RefScene(v, idx, uv=uv, spheres=sp, L=L)
+
+
+def _rays(n, seed):
+    from b200rt import scenes
+    r = scenes.random_rays([-12, -12, -12, 12, 12, 12], n, seed=seed)
+    r[n // 2:, 3] = 9.0   # finite tMax half (shadow-style)
+    return np.ascontiguousarray(r, np.float32)
+
+
+def _same(a, b):
+    assert np.array_equal(a["prim"], b["prim"])
+    for f in ("t", "uv", "p"):
+        assert np.array_equal(a[f].view(np.uint32), b[f].view(np.uint32)), f
+
+
+def test_host_library_exports(host):
+    rb, L = host
+    for s in ("plugin_accel_create", "plugin_intersect_batch", "plugin_intersect_p_batch", "ref_intersect",
+              "ref_accel_create", "b200rt_scene_create"):
+        assert hasattr(L, s), s
+
+
+def test_no_device_means_null_like_an_unknown_accelerator(host):
+    """Without a CUDA device CreateB200Accelerator reports through Error() and returns nullptr, which is what
+    MakeAccelerator does for a name it does not know (api.cpp:1011-1014); there is no CPU path inside."""
+    rb, L = host
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a device is present")
+    sc = _scene(rb, L, n_tris=50)
+    assert PluginAccel(rb, L, sc, "bvh").h is None
+
+
+CASES = [("bvh", "reference", {}, "bvh"), ("bvh", "reference", {"maxnodeprims": 1}, "bvh"),
+         ("kdtree", "reference", {}, "kdtree"), ("rbsp", "reference", {"nbDirections": 7}, "rbsp"),
+         ("rbspkd", "reference", {"nbDirections": 13}, "rbspkd")]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("tree,builder,ip,refkind", CASES)
+def test_plugin_matches_reference_accelerator(host, gpu, tree, builder, ip, refkind):
+    rb, L = host
+    sc = _scene(rb, L)
+    ref = rb.RefAccel(sc, refkind, int_params=ip)
+    acc = PluginAccel(rb, L, sc, tree, builder, ip)
+    assert acc.h, "CreateB200Accelerator returned nullptr"
+    assert L.plugin_is_current(acc.h) == 1
+    b = np.zeros(6, np.float32)
+    L.plugin_world_bound(acc.h, b.ctypes.data)
+    assert np.array_equal(b, ref.export()["bounds"])
+    rays = _rays(6000, seed=11)
+    want, want_p = ref.intersect(rays), ref.intersect_p(rays)
+    assert (want["prim"] >= 0).sum() > 500 and (want["prim"] >= len(sc.idx)).sum() > 20   # triangles and spheres
+    _same(acc.intersect_batch(rays), want)
+    assert np.array_equal(acc.intersect_p_batch(rays), want_p)
+    # the per-ray virtual interface (batch of one per call)
+    _same(acc.intersect(rays[:400]), want[:400])
+    assert np.array_equal(acc.intersect_p(rays[:400]), want_p[:400])
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("tree", ["bvh", "kdtree"])
+def test_plugin_with_this_repos_builders(host, gpu, tree):
+    rb, L = host
+    sc = _scene(rb, L, spheres=False)
+    ref = rb.RefAccel(sc, tree)
+    acc = PluginAccel(rb, L, sc, tree, "b200")
+    assert acc.h
+    rays = _rays(4000, seed=5)
+    _same(acc.intersect_batch(rays), ref.intersect(rays))
+    assert np.array_equal(acc.intersect_p_batch(rays), ref.intersect_p(rays))
