@@ -1,0 +1,133 @@
+// Shim TU: drives the reference's OWN renderer — SamplerIntegrator::Render (core/integrator.cpp:230-360) with
+// PathIntegrator::Li (integrators/path.cpp:64-204), PerspectiveCamera, Film + BoxFilter, RandomSampler /
+// HaltonSampler, PointLight, MatteMaterial and the reference's accelerators — over a programmatically built
+// scene (no parser, no image libraries: core/imageio.cpp is not compiled, the two functions Film needs from it
+// are defined here and capture the pixels instead of writing a file).  TEST INFRASTRUCTURE ONLY.
+#include "std_first.h"
+#include "ref_internal.h"
+#define private public
+#define protected public
+#include "core/primitive.h"
+#undef private
+#undef protected
+#include "core/api.h"
+#include "core/camera.h"
+#include "core/film.h"
+#include "core/imageio.h"
+#include "core/light.h"
+#include "core/parallel.h"
+#include "core/paramset.h"
+#include "core/scene.h"
+#include "core/spectrum.h"
+#include "core/stats.h"
+#include "cameras/perspective.h"
+#include "filters/box.h"
+#include "integrators/path.h"
+#include "lights/point.h"
+#include "materials/matte.h"
+#include "samplers/halton.h"
+#include "samplers/random.h"
+#include "textures/constant.h"
+
+namespace pbrt {
+static std::mutex g_imgMutex;
+static std::vector<float> g_lastImage;
+static Point2i g_lastRes;
+// core/imageio.h:55 — Film::WriteImage (film.cpp:266-305) ends here with the final RGB pixels.
+void WriteImage(const std::string &, const Float *rgb, const Bounds2i &outputBounds, const Point2i &) {
+    std::lock_guard<std::mutex> l(g_imgMutex);
+    Vector2i res = outputBounds.Diagonal();
+    g_lastRes = Point2i(res.x, res.y);
+    g_lastImage.assign(rgb, rgb + 3 * (size_t)res.x * res.y);
+}
+std::unique_ptr<RGBSpectrum[]> ReadImage(const std::string &, Point2i *) { return nullptr; }
+}  // namespace pbrt
+using namespace pbrt;
+
+namespace {
+// Counts the calls that reach the aggregate (what Scene::Intersect/IntersectP count, scene.cpp:41-52).
+struct CountingAggregate : public Aggregate {
+    std::shared_ptr<Primitive> inner;
+    mutable std::atomic<uint64_t> nClosest{0}, nAny{0};
+    explicit CountingAggregate(std::shared_ptr<Primitive> p) : inner(std::move(p)) {}
+    Bounds3f WorldBound() const override { return inner->WorldBound(); }
+    bool Intersect(const Ray &r, SurfaceInteraction *si) const override {
+        nClosest.fetch_add(1, std::memory_order_relaxed);
+        return inner->Intersect(r, si);
+    }
+    bool IntersectP(const Ray &r) const override {
+        nAny.fetch_add(1, std::memory_order_relaxed);
+        return inner->IntersectP(r);
+    }
+};
+}  // namespace
+
+// cam: eye[3], look[3], up[3], fov — exactly a scene file's `LookAt` + `Camera "perspective" "float fov"`.
+// sampler: "random" | "halton".  out_rgb: yres*xres*3 floats (Film::WriteImage's buffer).  Returns 0 on success.
+extern "C" int ref_render(ref_scene *s, const char *accel_kind, const float *cam, int xres, int yres, int spp,
+                          int maxdepth, const float *light_pos, const float *light_I, const float *kd,
+                          const char *sampler_name, int n_threads, const char *tmp_prefix, float *out_rgb,
+                          uint64_t *n_closest, uint64_t *n_shadow) {
+    PbrtOptions.quiet = true;
+    PbrtOptions.nThreads = n_threads;
+    // material: Material "matte" "rgb Kd" (materials/matte.cpp:44-60), sigma 0
+    Float rgb[3] = {kd[0], kd[1], kd[2]};
+    auto Kd = std::make_shared<ConstantTexture<Spectrum>>(Spectrum::FromRGB(rgb));
+    auto sigma = std::make_shared<ConstantTexture<Float>>(0.f);
+    auto matte = std::make_shared<MatteMaterial>(Kd, sigma, nullptr);
+    MediumInterface mi;
+    std::vector<std::shared_ptr<Primitive>> prims;
+    for (auto &p : s->prims) {
+        auto *gp = static_cast<GeometricPrimitive *>(p.get());
+        prims.push_back(std::make_shared<GeometricPrimitive>(gp->shape, matte, nullptr, mi));
+    }
+    ParamSet ps;
+    std::shared_ptr<Primitive> accel;
+    {
+        ref_scene tmp;
+        tmp.prims = prims;
+        const char *none[] = {nullptr};
+        ref_accel *a = ref_accel_create(&tmp, accel_kind, none, nullptr, none, nullptr);
+        if (!a) return 1;
+        accel = a->agg;
+        delete a;
+    }
+    auto counting = std::make_shared<CountingAggregate>(accel);
+    // LightSource "point" "point from" "rgb I" (lights/point.cpp:81-89)
+    Float li[3] = {light_I[0], light_I[1], light_I[2]};
+    Transform l2w = Translate(Vector3f(light_pos[0], light_pos[1], light_pos[2]));
+    std::vector<std::shared_ptr<Light>> lights;
+    lights.push_back(std::make_shared<PointLight>(l2w, mi, Spectrum::FromRGB(li)));
+    Scene scene(counting, lights);
+
+    // Film "image" + PixelFilter "box" (film.cpp:307-351, filters/box.cpp) — defaults of every thesis template
+    std::unique_ptr<Filter> filter(new BoxFilter(Vector2f(0.5f, 0.5f)));
+    std::string fname = std::string(tmp_prefix) + ".exr";
+    Film *film = new Film(Point2i(xres, yres), Bounds2f(Point2f(0, 0), Point2f(1, 1)), std::move(filter), 35.f, fname, 1.f);
+    // LookAt + Camera "perspective" (api.cpp:1338-1370 pbrtCamera; cameras/perspective.cpp:231-279)
+    Transform w2c = LookAt(Point3f(cam[0], cam[1], cam[2]), Point3f(cam[3], cam[4], cam[5]), Vector3f(cam[6], cam[7], cam[8]));
+    Transform c2w = Inverse(w2c);
+    AnimatedTransform ac2w(&c2w, 0.f, &c2w, 1.f);
+    Float frame = Float(xres) / Float(yres);
+    Bounds2f screen;
+    if (frame > 1.f) { screen.pMin = Point2f(-frame, -1.f); screen.pMax = Point2f(frame, 1.f); }
+    else { screen.pMin = Point2f(-1.f, -1.f / frame); screen.pMax = Point2f(1.f, 1.f / frame); }
+    std::shared_ptr<const Camera> camera(new PerspectiveCamera(ac2w, screen, 0.f, 1.f, 0.f, 1e6f, cam[9], film, nullptr));
+    std::shared_ptr<Sampler> sampler;
+    if (std::string(sampler_name) == "halton") sampler.reset(new HaltonSampler(spp, film->GetSampleBounds()));
+    else sampler.reset(new RandomSampler(spp));
+    PathIntegrator integ(maxdepth, camera, sampler, film->GetSampleBounds(), 1.f, "spatial");
+
+    if (n_threads != 1) ParallelInit();
+    integ.Render(scene);     // -> film->WriteImage() -> the WriteImage above
+    if (n_threads != 1) ParallelCleanup();
+    {
+        std::lock_guard<std::mutex> l(g_imgMutex);
+        if (g_lastRes.x != xres || g_lastRes.y != yres) return 2;
+        std::memcpy(out_rgb, g_lastImage.data(), sizeof(float) * g_lastImage.size());
+    }
+    if (n_closest) *n_closest = counting->nClosest.load();
+    if (n_shadow) *n_shadow = counting->nAny.load();
+    // film is owned (and deleted) by the Camera (core/camera.cpp)
+    return 0;
+}

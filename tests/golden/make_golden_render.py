@@ -1,0 +1,58 @@
+"""Generates tests/golden/ref_render.npz: images rendered by the REFERENCE'S OWN renderer
+(SamplerIntegrator::Render + PathIntegrator::Li + Film/BoxFilter + RandomSampler + PointLight + MatteMaterial +
+BVHAccel, compiled from /root/reference by oracle/ref/Makefile; driver oracle/ref/ref_render.cpp), plus the
+number of rays that reached Aggregate::Intersect / IntersectP.  Run in the build container:
+
+    python tests/golden/make_golden_render.py
+"""
+import os
+import sys
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "thesis-pbrt-v3_b200"))
+from oracle import refbind as rb   # noqa: E402
+from b200rt import scenes          # noqa: E402
+
+CASES = {
+    # BASELINE config 1: scenes/killeroo-simple geometry + camera (point light at the sphere light's centre)
+    "killeroo": dict(scene="killeroo_simple", res=128, spp=256, maxdepth=5, I=(50000.0,) * 3, kd=(.5, .5, .5)),
+    # BASELINE config 2: the sponza stand-in the bench renders
+    "sponza": dict(scene="sponza_standin", res=96, spp=256, maxdepth=5, I=(1.0,) * 3, kd=(.5, .5, .5)),
+}
+
+
+def lookat_of(name):
+    """eye, look, up, fov of the scene templates (scenes/killeroo-simple:1-3, scenes/sponza:1-3)."""
+    if name == "killeroo_simple":
+        r = scenes._rot_z(5.0)
+        eye = scenes._xform(r, np.array([[400.0, 20, 30]]))[0]
+        look = scenes._xform(r, np.array([[0.0, 63, -110]]))[0]
+        return eye, look, (0, 0, 1), 39.0
+    return (-0.7, .45, .05), (0, .25, 0), (0, 1, 0), 42.0
+
+
+def main():
+    path = os.path.join(ROOT, "tests", "golden", "ref_render.npz")
+    out = dict(np.load(path)) if os.path.exists(path) else {}
+    for key, c in CASES.items():
+        if sys.argv[1:] and key not in sys.argv[1:]:
+            continue
+        sc = getattr(scenes, c["scene"])(xres=c["res"], yres=c["res"])
+        tv = sc["tri_verts"]
+        S = rb.RefScene(tv.reshape(-1, 3), np.arange(3 * len(tv), dtype=np.int32).reshape(-1, 3))
+        eye, look, up, fov = lookat_of(c["scene"])
+        img, nc, ns = rb.render(S, "bvh", eye, look, up, fov, c["res"], c["res"], c["spp"], c["maxdepth"], sc["light"],
+                                c["I"], c["kd"], sampler="random", n_threads=0)
+        print(key, "mean", img.mean(), "closest", nc, "shadow", ns)
+        out[key + "_rgb"] = img
+        out[key + "_rays"] = np.array([nc, ns], np.uint64)
+        out[key + "_params"] = np.array([c["res"], c["spp"], c["maxdepth"]], np.int32)
+        out[key + "_I"] = np.array(c["I"], np.float32)
+        out[key + "_kd"] = np.array(c["kd"], np.float32)
+    np.savez_compressed(path, **out)
+
+
+if __name__ == "__main__":
+    main()

@@ -81,7 +81,7 @@ def camera_rays(cam, spp=1, seed=0, x0=0, x1=None, y0=0, y1=None):
     px = np.repeat(px.ravel(), spp).astype(np.float64)
     py = np.repeat(py.ravel(), spp).astype(np.float64)
     jx, jy = (rng.random(len(px)), rng.random(len(px))) if spp > 1 or seed else (0.5, 0.5)
-    sx = 1 - 2 * (px + jx) / cam["xres"]   # pbrt's screen x grows to the left of `right` = up x dir
+    sx = 2 * (px + jx) / cam["xres"] - 1   # raster x grows along camera +x = `right` = up x dir (perspective.cpp:61-66; pinned by tests/golden/ref_render.npz)
     sy = 1 - 2 * (py + jy) / cam["yres"]
     d = cam["dir"][None, :] + sx[:, None] * cam["right"][None, :] + sy[:, None] * cam["up"][None, :]
     d /= np.linalg.norm(d, axis=1, keepdims=True)

@@ -112,7 +112,7 @@ __global__ void k_camera(const __grid_constant__ WfParams P, uint64_t batchStart
     if (!active) return;
     const uint32_t pix = y * P.cam.xres + x;
     const float fx = (x + rnd(P.seed, pix, s, 0)) / P.cam.xres, fy = (y + rnd(P.seed, pix, s, 1)) / P.cam.yres;
-    const float sx = 1.f - 2.f * fx, sy = 1.f - 2.f * fy;
+    const float sx = 2.f * fx - 1.f, sy = 1.f - 2.f * fy;  // raster x grows along camera +x, raster y downwards (camera.h ScreenToRaster)
     float dx = P.cam.dir[0] + sx * P.cam.right[0] + sy * P.cam.up[0];
     float dy = P.cam.dir[1] + sx * P.cam.right[1] + sy * P.cam.up[1];
     float dz = P.cam.dir[2] + sx * P.cam.right[2] + sy * P.cam.up[2];
