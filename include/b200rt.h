@@ -21,7 +21,7 @@
 extern "C" {
 #endif
 
-#define B200RT_VERSION 2
+#define B200RT_VERSION 3
 
 enum {
     B200RT_OK = 0,
@@ -37,7 +37,12 @@ typedef enum {
     B200RT_BVH = 0,    /* "bvh"    src/accelerators/bvh.cpp          (32-byte LinearBVHNode) */
     B200RT_KDTREE = 1, /* "kdtree" src/accelerators/kdtreeaccel.cpp  (8-byte KdAccelNode)    */
     B200RT_RBSP = 2,   /* "rbsp"   src/accelerators/rbsp.cpp         (8-byte RBSPNode)       */
-    B200RT_RBSPKD = 3  /* "rbspkd" src/accelerators/rbspKd.cpp       (RBSP + axis<3 kd path) */
+    B200RT_RBSPKD = 3, /* "rbspkd" src/accelerators/rbspKd.cpp       (RBSP + axis<3 kd path) */
+    /* General BSP families: every node carries its own split normal (20-byte nodes).  One traversal serves all
+     * of the thesis's builders of that node format: "bsppaper", "bspcluster", "bsprandom", "bsparbitrary",
+     * "bsp*withkd" (api.cpp:847-1010) build BSPNode trees; "bsppaperkd" and the "*fastkd" ones BSPKdNode trees. */
+    B200RT_BSP = 4,    /* src/accelerators/BSP.cpp:27-163   over BSPNode   (BSP.h:122-184)   */
+    B200RT_BSPKD = 5   /* src/accelerators/BSPKd.cpp:25-169 over BSPKdNode (BSPKd.h:11-174)  */
 } b200rt_kind;
 
 /* Ray = the fields of pbrt::Ray the hot path reads (src/core/geometry.h:1176-1203): 32 bytes. */
@@ -63,8 +68,9 @@ typedef struct {
  * world-space triangles in original primitive order.  The library re-lays both out for HBM. */
 typedef struct {
     uint32_t kind;         /* b200rt_kind */
-    const void *nodes;     /* BVH: node_count x 32 B (bvh.cpp:123-152); others: node_count x 8 B
-                              (kdtreeaccel.cpp:43-160, rbsp.cpp:15-135) */
+    const void *nodes;     /* BVH: node_count x 32 B (bvh.cpp:123-152); kd/RBSP(/Kd): node_count x 8 B
+                              (kdtreeaccel.cpp:43-160, rbsp.cpp:15-135); BSP/BSPKd: node_count x 20 B
+                              (split|prim|offset, flags, splitAxis.xyz — BSP.h:170-183, BSPKd.h:161-173) */
     uint32_t node_count;
     const uint32_t *prim_indices; /* BVH: primNumMapping[slot] -> original prim (bvh.cpp:227,322),
                                      n_indices == n_prims.  kd/RBSP: primitiveIndices

@@ -526,6 +526,107 @@ static int bsp_any_one(const orc_bsp_tree *T, const orc_prims *P, const orc_ray 
     return 0;
 }
 
+
+/* ------------------- general BSP / BSPKd (20-byte nodes with an explicit split normal) ------------------- */
+/* BSPNode (BSP.h:122-184): w0 = split | onePrimitive | primitiveIndicesOffset; w1 = flags: bit 0 = leaf, the rest
+ * = aboveChild << 1 or nPrims << 1 (BSP.h:13-55); splitAxis = 3 floats.
+ * BSPKdNode (BSPKd.h:11-174): w1 low 3 bits: 0..2 = kd node on that axis, 3 = leaf, 4 = general node; the rest =
+ * aboveChild << 3 or nPrims << 3. */
+typedef struct { uint32_t w0, w1; float axis[3]; } orc_gbsp_node;
+typedef struct { int kind; /* 4 BSP, 5 BSPKd */ const orc_gbsp_node *nodes; const uint32_t *indices; float bounds[6]; } orc_gbsp_tree;
+
+static inline int gbsp_is_leaf(int kind, uint32_t w1) { return kind == 4 ? (w1 & 1u) == 1u : (w1 & 7u) == 3u; }
+static inline uint32_t gbsp_shift(int kind) { return kind == 4 ? 1u : 3u; }
+/* treeIntersectInterior (BSP.h:57-67) / BSPKdNode::intersectInterior (BSPKd.h:52-72) + planeDistance
+ * (geometry.h:1833-1843); Dot = x*x' + y*y' + z*z' left to right. */
+static inline float gbsp_interior(int kind, const orc_gbsp_node *n, const orc_ray *r, const float invDir[3], int *belowFirst) {
+    float split; memcpy(&split, &n->w0, 4);
+    if (kind == 5 && (n->w1 & 7u) < 4u) {
+        uint32_t axis = n->w1 & 7u;
+        *belowFirst = (r->o[axis] < split) || (r->o[axis] == split && r->d[axis] <= 0);
+        return (split - r->o[axis]) * invDir[axis];
+    }
+    float projectedO = n->axis[0] * r->o[0] + n->axis[1] * r->o[1] + n->axis[2] * r->o[2];
+    float inverseProjectedD = 1 / (n->axis[0] * r->d[0] + n->axis[1] * r->d[1] + n->axis[2] * r->d[2]);
+    *belowFirst = (projectedO < split) || (projectedO == split && inverseProjectedD <= 0);
+    return (split - projectedO) * inverseProjectedD;
+}
+/* BSP::Intersect BSP.cpp:27-95; BSPKd::Intersect BSPKd.cpp:25-98 */
+static void gbsp_closest_one(const orc_gbsp_tree *T, const orc_prims *P, orc_ray *r, orc_hit *h, orc_counters *c) {
+    h->prim = ORC_MISS; h->t = r->tMax; h->b0 = h->b1 = h->b2 = 0;
+    float tMin, tMax;
+    if (!root_clip(T->bounds, r, &tMin, &tMax)) return;
+    float invDir[3] = {1 / r->d[0], 1 / r->d[1], 1 / r->d[2]};
+    const uint32_t off = gbsp_shift(T->kind);
+    orc_todo todo[64];
+    uint32_t todoPos = 0, cur = 0;
+    for (;;) {
+        if (r->tMax < tMin) break;
+        if (c) c->nodes_fetched++;
+        const orc_gbsp_node *n = &T->nodes[cur];
+        if (!gbsp_is_leaf(T->kind, n->w1)) {
+            if (c) c->nodes_passed++;
+            int belowFirst;
+            float tPlane = gbsp_interior(T->kind, n, r, invDir, &belowFirst);
+            uint32_t above = n->w1 >> off, first, second;
+            if (belowFirst) { first = cur + 1; second = above; } else { first = above; second = cur + 1; }
+            if (tPlane > tMax || tPlane <= 0) cur = first;
+            else if (tPlane < tMin) cur = second;
+            else {
+                todo[todoPos].node = second; todo[todoPos].tMin = tPlane; todo[todoPos].tMax = tMax; ++todoPos;
+                cur = first; tMax = tPlane;
+            }
+        } else {
+            if (c) c->leaf_visits++;
+            uint32_t np = n->w1 >> off;
+            if (np == 1) prim_intersect(P, n->w0, r, h, c);
+            else for (uint32_t i = 0; i < np; ++i) {
+                if (c) c->index_reads++;
+                prim_intersect(P, T->indices[n->w0 + i], r, h, c);
+            }
+            if (todoPos > 0) { --todoPos; cur = todo[todoPos].node; tMin = todo[todoPos].tMin; tMax = todo[todoPos].tMax; }
+            else break;
+        }
+    }
+}
+/* BSP::IntersectP BSP.cpp:97-163; BSPKd::IntersectP BSPKd.cpp:100-169 (no tMax < tMin bail-out) */
+static int gbsp_any_one(const orc_gbsp_tree *T, const orc_prims *P, const orc_ray *r, orc_counters *c) {
+    float tMin, tMax;
+    if (!root_clip(T->bounds, r, &tMin, &tMax)) return 0;
+    float invDir[3] = {1 / r->d[0], 1 / r->d[1], 1 / r->d[2]};
+    const uint32_t off = gbsp_shift(T->kind);
+    orc_todo todo[64];
+    uint32_t todoPos = 0, cur = 0;
+    for (;;) {
+        if (c) c->nodes_fetched++;
+        const orc_gbsp_node *n = &T->nodes[cur];
+        if (gbsp_is_leaf(T->kind, n->w1)) {
+            if (c) c->leaf_visits++;
+            uint32_t np = n->w1 >> off;
+            if (np == 1) { if (prim_intersect_p(P, n->w0, r, c)) return 1; }
+            else for (uint32_t i = 0; i < np; ++i) {
+                if (c) c->index_reads++;
+                if (prim_intersect_p(P, T->indices[n->w0 + i], r, c)) return 1;
+            }
+            if (todoPos > 0) { --todoPos; cur = todo[todoPos].node; tMin = todo[todoPos].tMin; tMax = todo[todoPos].tMax; }
+            else break;
+        } else {
+            if (c) c->nodes_passed++;
+            int belowFirst;
+            float tPlane = gbsp_interior(T->kind, n, r, invDir, &belowFirst);
+            uint32_t above = n->w1 >> off, first, second;
+            if (belowFirst) { first = cur + 1; second = above; } else { first = above; second = cur + 1; }
+            if (tPlane > tMax || tPlane <= 0) cur = first;
+            else if (tPlane < tMin) cur = second;
+            else {
+                todo[todoPos].node = second; todo[todoPos].tMin = tPlane; todo[todoPos].tMax = tMax; ++todoPos;
+                cur = first; tMax = tPlane;
+            }
+        }
+    }
+    return 0;
+}
+
 /* ---------------------------------- batch entry points -------------------------------------- */
 #include <pthread.h>
 static void add_counters(orc_counters *dst, const orc_counters *src) {
@@ -536,7 +637,7 @@ static void add_counters(orc_counters *dst, const orc_counters *src) {
 typedef struct {
     int kind, any, want;
     const void *nodes; const uint32_t *indices;
-    orc_prims P; orc_bsp_tree T;
+    orc_prims P; orc_bsp_tree T; orc_gbsp_tree G;
     const orc_ray *rays; uint64_t begin, end;
     orc_hit *hits; uint8_t *occluded;
     orc_counters *per_ray; orc_counters total;
@@ -551,10 +652,12 @@ static void *run_job(void *arg) {
         if (j->any) {
             j->occluded[i] = (uint8_t)(j->kind == 0
                 ? bvh_any_one((const orc_bvh_node *)j->nodes, j->indices, &j->P, &j->rays[i], cp)
+                : j->kind >= 4 ? gbsp_any_one(&j->G, &j->P, &j->rays[i], cp)
                 : bsp_any_one(&j->T, &j->P, &j->rays[i], cp));
         } else {
             orc_ray r = j->rays[i];
             if (j->kind == 0) bvh_closest_one((const orc_bvh_node *)j->nodes, j->indices, &j->P, &r, &j->hits[i], cp);
+            else if (j->kind >= 4) gbsp_closest_one(&j->G, &j->P, &r, &j->hits[i], cp);
             else bsp_closest_one(&j->T, &j->P, &r, &j->hits[i], cp);
         }
         if (j->want) { c.rays = 1; add_counters(&j->total, &c); if (j->per_ray) j->per_ray[i] = c; }
@@ -563,6 +666,7 @@ static void *run_job(void *arg) {
 }
 
 /* kind 0: nodes = orc_bvh_node[], indices = prim_order.  kind 1/2/3: orc_bsp_node[], primitiveIndices.
+ * kind 4/5: orc_gbsp_node[] (20 B), primitiveIndices.
  * counters (nullable) is a single accumulated struct; per_ray (nullable) gets one struct per ray. */
 static void run_batch(int any, int kind, const void *nodes, const uint32_t *indices, const float *directions,
                       uint32_t M, const float bounds[6], const float *verts, const uint8_t *degen, uint32_t n_prims,
@@ -585,7 +689,10 @@ static void run_batch(int any, int kind, const void *nodes, const uint32_t *indi
         j->nodes = nodes; j->indices = indices;
         j->P.verts = verts; j->P.degen = degen; j->P.n_prims = n_prims;
         j->P.kind = prim_kind; j->P.sphere_of = sphere_of; j->P.spheres = spheres;
-        if (kind != 0) {
+        if (kind >= 4) {
+            j->G.kind = kind; j->G.nodes = (const orc_gbsp_node *)nodes; j->G.indices = indices;
+            memcpy(j->G.bounds, bounds, sizeof(j->G.bounds));
+        } else if (kind != 0) {
             j->T.kind = kind; j->T.nodes = (const orc_bsp_node *)nodes; j->T.indices = indices;
             j->T.directions = directions; j->T.M = M;
             memcpy(j->T.bounds, bounds, sizeof(j->T.bounds));

@@ -12,7 +12,7 @@ HIT = np.dtype([("prim", "<u4"), ("t", "<f4"), ("b0", "<f4"), ("b1", "<f4"), ("b
 COUNTERS = np.dtype([("rays", "<u8"), ("nodes_fetched", "<u8"), ("nodes_passed", "<u8"), ("leaf_visits", "<u8"),
                      ("prim_tests", "<u8"), ("index_reads", "<u8")])
 MISS = 0xFFFFFFFF
-KIND = {"bvh": 0, "kdtree": 1, "rbsp": 2, "rbspkd": 3}
+KIND = {"bvh": 0, "kdtree": 1, "rbsp": 2, "rbspkd": 3, "bsp": 4, "bspkd": 5}
 
 _lib = None
 

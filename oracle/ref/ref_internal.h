@@ -26,4 +26,5 @@ ref_accel *ref_make_bvh(ref_scene *, const pbrt::ParamSet &);
 ref_accel *ref_make_kd(ref_scene *, const pbrt::ParamSet &);
 ref_accel *ref_make_rbsp(ref_scene *, const pbrt::ParamSet &);
 ref_accel *ref_make_rbspkd(ref_scene *, const pbrt::ParamSet &);
+ref_accel *ref_make_bsp(ref_scene *, const char *kind, const pbrt::ParamSet &);
 #endif

@@ -105,7 +105,7 @@ extern "C" ref_accel *ref_accel_create(ref_scene *s, const char *kind, const cha
     if (k == "kdtree") return ref_make_kd(s, ps);
     if (k == "rbsp") return ref_make_rbsp(s, ps);
     if (k == "rbspkd") return ref_make_rbspkd(s, ps);
-    return nullptr;
+    return ref_make_bsp(s, kind, ps);
 }
 extern "C" void ref_accel_destroy(ref_accel *a) { delete a; }
 extern "C" int ref_accel_info(const ref_accel *a, ref_tree_info *ti) { return a->info(a, ti); }

@@ -136,7 +136,9 @@ class RefAccel:
         idx = np.zeros(ti.n_indices, np.uint32)
         dirs = np.zeros((ti.n_directions, 3), np.float32)
         self.L.ref_accel_export(self.h, _p(nodes), _p(idx), _p(dirs))
-        return dict(kind=self.kind, nodes=nodes, indices=idx, directions=dirs,
+        # the general-BSP builder families share two node formats (BSP.h:122-184 / BSPKd.h:11-174)
+        kind = {"bsppaper": "bsp", "bspcluster": "bsp", "bsppaperkd": "bspkd", "bspclusterfastkd": "bspkd"}.get(self.kind, self.kind)
+        return dict(kind=kind, nodes=nodes, indices=idx, directions=dirs,
                     bounds=np.array(list(ti.bounds), np.float32), n_prims=ti.n_prims)
 
     def intersect(self, rays, counters=False, n_threads=1):

@@ -23,7 +23,7 @@ def golden_tree(g):
                 bounds=g["bounds"], n_prims=len(g["tri_verts"]))
 
 
-SMALL = ["bvh", "kdtree", "rbsp3", "rbsp7", "rbsp13", "rbspkd13"]
+SMALL = ["bvh", "kdtree", "rbsp3", "rbsp7", "rbsp13", "rbspkd13", "bsppaper", "bsppaperkd", "bspcluster", "bspclusterfastkd"]
 
 
 @pytest.fixture(scope="session")

@@ -68,17 +68,25 @@ def rays_for(bounds, n, seed):
     return r
 
 
-def gen_small():
+SMALL_CASES = [("bvh", "bvh", {}), ("kdtree", "kdtree", {}), ("rbsp3", "rbsp", {"nbDirections": 3}),
+               ("rbsp7", "rbsp", {"nbDirections": 7}), ("rbsp13", "rbsp", {"nbDirections": 13}),
+               ("rbspkd13", "rbspkd", {"nbDirections": 13})]
+# General-BSP families: Ize-et-al "paper" planes (deterministic) and k-means-of-normals
+# clusters (seeded by std::random_device in the reference, F9 — the fixture pins the tree that was built).
+BSP_CASES = [("bsppaper", "bsppaper", {}), ("bsppaperkd", "bsppaperkd", {}),
+             ("bspcluster", "bspcluster", {"nbDirections": 5}), ("bspclusterfastkd", "bspclusterfastkd", {"nbDirections": 5})]
+
+
+def gen_small(cases=SMALL_CASES):
     n = 600
     P = soup(n, 11)
     idx = np.arange(3 * n, dtype=np.int32).reshape(-1, 3)
     tv = P[idx].reshape(-1, 9)
     sc = rb.RefScene(P, idx)
-    for name, kind, ip in [("bvh", "bvh", {}), ("kdtree", "kdtree", {}), ("rbsp3", "rbsp", {"nbDirections": 3}),
-                           ("rbsp7", "rbsp", {"nbDirections": 7}), ("rbsp13", "rbsp", {"nbDirections": 13}),
-                           ("rbspkd13", "rbspkd", {"nbDirections": 13})]:
+    for name, kind, ip in cases:
         acc = rb.RefAccel(sc, kind, ip)
         ex = acc.export()
+        kind = ex["kind"]
         rays = rays_for(np.array([-10, -10, -10, 10, 10, 10], np.float32), 4096, 5)
         hits, cnt = acc.intersect(rays, counters=True)
         occ, cntp = acc.intersect_p(rays, counters=True)
@@ -241,5 +249,6 @@ if __name__ == "__main__":
     if "spheres" in which: gen_spheres()
     if "killeroo" in which: gen_killeroo()
     if "small" in which: gen_small()
+    if "bsp" in which: gen_small(BSP_CASES)
     if "triangle" in which: gen_triangle()
     if "feet" in which: gen_feet()

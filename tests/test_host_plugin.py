@@ -105,7 +105,8 @@ def test_no_device_means_null_like_an_unknown_accelerator(host):
 
 CASES = [("bvh", "reference", {}, "bvh"), ("bvh", "reference", {"maxnodeprims": 1}, "bvh"),
          ("kdtree", "reference", {}, "kdtree"), ("rbsp", "reference", {"nbDirections": 7}, "rbsp"),
-         ("rbspkd", "reference", {"nbDirections": 13}, "rbspkd")]
+         ("rbspkd", "reference", {"nbDirections": 13}, "rbspkd"),
+         ("bsppaper", "reference", {}, "bsppaper"), ("bsppaperkd", "reference", {}, "bsppaperkd")]
 
 
 @pytest.mark.gpu

@@ -8,7 +8,7 @@ MISS = 0xFFFFFFFF
 RAY_DTYPE = np.dtype([("o", "<f4", 3), ("tMax", "<f4"), ("d", "<f4", 3), ("time", "<f4")])
 HIT_DTYPE = np.dtype([("prim", "<u4"), ("t", "<f4"), ("b0", "<f4"), ("b1", "<f4"), ("b2", "<f4")])
 COUNTERS_FIELDS = ["rays", "nodes_fetched", "nodes_passed", "leaf_visits", "prim_tests", "index_reads"]
-KINDS = {"bvh": 0, "kdtree": 1, "rbsp": 2, "rbspkd": 3}
+KINDS = {"bvh": 0, "kdtree": 1, "rbsp": 2, "rbspkd": 3, "bsp": 4, "bspkd": 5}
 ERRORS = {1: "EINVAL", 2: "ENODEVICE", 3: "ECUDA", 4: "EUNSUPPORTED", 5: "ENOMEM"}
 
 

@@ -48,7 +48,7 @@ int g_sm_count = 148;
 // for A/B measurements; B200RT_THRESH = busy-lane count below which a persistent warp refills.
 static int g_use_baseline = 0;
 static uint32_t g_thresh = 14;
-static int g_pblocks[4][2];  // resident persistent blocks per SM, [kind][any]
+static int g_pblocks[6][2];  // resident persistent blocks per SM, [kind][any]
 static int g_persist_bsp = 1;
 static uint32_t g_bvh_steps = 4;
 #define B200RT_PIPE_CHUNK_MAX (1024u * 1024u)
@@ -85,6 +85,8 @@ extern "C" int b200rt_init(int device) {
     OCC(B200RT_KDTREE, 0, (bsp_persistent_kernel<B200RT_KDTREE, false>)); OCC(B200RT_KDTREE, 1, (bsp_persistent_kernel<B200RT_KDTREE, true>));
     OCC(B200RT_RBSP, 0, (bsp_persistent_kernel<B200RT_RBSP, false>)); OCC(B200RT_RBSP, 1, (bsp_persistent_kernel<B200RT_RBSP, true>));
     OCC(B200RT_RBSPKD, 0, (bsp_persistent_kernel<B200RT_RBSPKD, false>)); OCC(B200RT_RBSPKD, 1, (bsp_persistent_kernel<B200RT_RBSPKD, true>));
+    OCC(B200RT_BSP, 0, (bsp_persistent_kernel<B200RT_BSP, false>)); OCC(B200RT_BSP, 1, (bsp_persistent_kernel<B200RT_BSP, true>));
+    OCC(B200RT_BSPKD, 0, (bsp_persistent_kernel<B200RT_BSPKD, false>)); OCC(B200RT_BSPKD, 1, (bsp_persistent_kernel<B200RT_BSPKD, true>));
 #undef OCC
     return B200RT_OK;
 }
@@ -261,29 +263,41 @@ static int build_bvh_scene(const b200rt_scene_desc *d, b200rt_scene *s) {
     return B200RT_OK;
 }
 
+struct RefWideNode {  // BSPNode (BSP.h:170-183) / BSPKdNode (BSPKd.h:161-173): 20 bytes
+    uint32_t w0, w1;
+    float axis[3];
+};
+
 static int build_bsp_scene(const b200rt_scene_desc *d, b200rt_scene *s) {
-    const uint2 *ref = (const uint2 *)d->nodes;
-    const uint32_t N = d->node_count;
     const int kind = (int)d->kind;
+    const bool wideKind = kind == B200RT_BSP || kind == B200RT_BSPKD;
+    const uint2 *ref = (const uint2 *)d->nodes;
+    const RefWideNode *refW = (const RefWideNode *)d->nodes;
+    const uint32_t N = d->node_count;
     uint32_t M = 3;
-    if (kind != B200RT_KDTREE) {
+    if (kind == B200RT_RBSP || kind == B200RT_RBSPKD) {
         M = d->n_directions;
         if (!d->directions || M < 1 || M > 13) return fail(B200RT_EINVAL, "RBSP: need 1..13 directions (got %u)", M);
     }
-    const uint32_t off = kind == B200RT_KDTREE ? 2u : 32u - (uint32_t)__builtin_clz(M);  // genericBSP.cpp:11-22
-    const uint32_t mask = (1u << off) - 1u, leafTag = kind == B200RT_KDTREE ? 3u : M;
+    const uint32_t off = kind == B200RT_KDTREE ? 2u : kind == B200RT_BSP ? 1u : kind == B200RT_BSPKD ? 3u
+                         : 32u - (uint32_t)__builtin_clz(M);  // genericBSP.cpp:11-22
+    const uint32_t mask = (1u << off) - 1u, leafTag = kind == B200RT_KDTREE ? 3u : kind == B200RT_BSP ? 1u : kind == B200RT_BSPKD ? 3u : M;
+    auto w0 = [&](uint32_t i) { return wideKind ? refW[i].w0 : ref[i].x; };
+    auto w1 = [&](uint32_t i) { return wideKind ? refW[i].w1 : ref[i].y; };
     // validate + depth (todo stack of 64, kdtreeaccel.cpp:391)
     std::vector<uint32_t> depth(N, 0);
     uint32_t maxDepth = 0;
     for (uint32_t i = 0; i < N; ++i) {
-        const uint32_t axis = ref[i].y & mask;
+        const uint32_t axis = w1(i) & mask;
         if (axis == leafTag) {
-            const uint64_t np = ref[i].y >> off;
-            if (np == 1) { if (ref[i].x >= d->n_prims) return fail(B200RT_EINVAL, "leaf %u: primitive %u out of range", i, ref[i].x); }
-            else if (np > 1 && (uint64_t)ref[i].x + np > d->n_indices) return fail(B200RT_EINVAL, "leaf %u: index range out of bounds", i);
+            const uint64_t np = w1(i) >> off;
+            if (np == 1) { if (w0(i) >= d->n_prims) return fail(B200RT_EINVAL, "leaf %u: primitive %u out of range", i, w0(i)); }
+            else if (np > 1 && (uint64_t)w0(i) + np > d->n_indices) return fail(B200RT_EINVAL, "leaf %u: index range out of bounds", i);
         } else {
-            const uint32_t above = ref[i].y >> off;
-            if (axis >= M || i + 1 >= N || above <= i + 1 || above >= N)
+            const uint32_t above = w1(i) >> off;
+            // BSP: the tag is one bit; BSPKd: 0..2 = kd axis, 4 = general node (BSPKd.h:13,36-45)
+            const bool axisOk = kind == B200RT_BSP ? true : kind == B200RT_BSPKD ? (axis < 3 || axis == 4) : axis < M;
+            if (!axisOk || i + 1 >= N || above <= i + 1 || above >= N)
                 return fail(B200RT_EINVAL, "interior node %u: bad axis/children (axis=%u above=%u nodes=%u)", i, axis, above, N);
             depth[i + 1] = depth[above] = depth[i] + 1;
             if (depth[i] + 1 > maxDepth) maxDepth = depth[i] + 1;
@@ -301,8 +315,21 @@ static int build_bsp_scene(const b200rt_scene_desc *d, b200rt_scene *s) {
         uint32_t flags = tri_tail_rejects(v, d->tri_uvs ? d->tri_uvs + 6 * (size_t)p : nullptr) ? B200RT_TRI_DEGENERATE : 0u;
         fill_record(&recs[3 * (size_t)p], v, p, flags);
     }
-    CU(cudaMalloc(&s->d_nodes, (size_t)N * 8));
-    CU(cudaMemcpy(s->d_nodes, ref, (size_t)N * 8, cudaMemcpyHostToDevice));
+    if (wideKind) {  // 20-byte reference nodes -> aligned 32-byte records (rt_kernels.cuh bsp_fetch)
+        std::vector<float4> wide((size_t)2 * N);
+        for (uint32_t i = 0; i < N; ++i) {
+            float4 lo = make_float4(0.f, 0.f, refW[i].axis[0], refW[i].axis[1]);
+            std::memcpy(&lo.x, &refW[i].w0, 4);
+            std::memcpy(&lo.y, &refW[i].w1, 4);
+            wide[2 * (size_t)i] = lo;
+            wide[2 * (size_t)i + 1] = make_float4(refW[i].axis[2], 0.f, 0.f, 0.f);
+        }
+        CU(cudaMalloc(&s->d_nodes, wide.size() * sizeof(float4)));
+        CU(cudaMemcpy(s->d_nodes, wide.data(), wide.size() * sizeof(float4), cudaMemcpyHostToDevice));
+    } else {
+        CU(cudaMalloc(&s->d_nodes, (size_t)N * 8));
+        CU(cudaMemcpy(s->d_nodes, ref, (size_t)N * 8, cudaMemcpyHostToDevice));
+    }
     CU(cudaMalloc(&s->d_indices, std::max<size_t>(1, d->n_indices) * 4));
     if (d->n_indices) CU(cudaMemcpy(s->d_indices, d->prim_indices, (size_t)d->n_indices * 4, cudaMemcpyHostToDevice));
     CU(cudaMalloc(&s->d_tris, std::max<size_t>(1, recs.size()) * sizeof(float4)));
@@ -315,7 +342,7 @@ static int build_bsp_scene(const b200rt_scene_desc *d, b200rt_scene *s) {
     s->d_prim_tris = s->d_tris;
     std::memcpy(s->bsp.bounds, d->bounds, sizeof(s->bsp.bounds));
     std::memset(s->bsp.dirs, 0, sizeof(s->bsp.dirs));
-    if (kind == B200RT_KDTREE) { s->bsp.dirs[0] = s->bsp.dirs[4] = s->bsp.dirs[8] = 1.f; }
+    if (kind == B200RT_KDTREE || wideKind) { s->bsp.dirs[0] = s->bsp.dirs[4] = s->bsp.dirs[8] = 1.f; }
     else std::memcpy(s->bsp.dirs, d->directions, sizeof(float) * 3 * M);
     s->bsp.M = M; s->bsp.bitOffset = off; s->bsp.bitMask = mask; s->bsp.leafTag = leafTag; s->bsp.kind = kind;
     std::memcpy(s->bounds, d->bounds, sizeof(s->bounds));
@@ -325,7 +352,7 @@ static int build_bsp_scene(const b200rt_scene_desc *d, b200rt_scene *s) {
 extern "C" int b200rt_scene_create(const b200rt_scene_desc *d, b200rt_scene **out) {
     if (!d || !out) return fail(B200RT_EINVAL, "null argument");
     *out = nullptr;
-    if (d->kind > B200RT_RBSPKD) return fail(B200RT_EINVAL, "unknown accelerator kind %u", d->kind);
+    if (d->kind > B200RT_BSPKD) return fail(B200RT_EINVAL, "unknown accelerator kind %u", d->kind);
     if (d->n_prims && !d->tri_verts) return fail(B200RT_EINVAL, "tri_verts is null");
     if (d->node_count && !d->nodes) return fail(B200RT_EINVAL, "nodes is null");
     if (d->n_indices && !d->prim_indices) return fail(B200RT_EINVAL, "prim_indices is null");
@@ -387,7 +414,9 @@ static void launch_kind(const b200rt_scene *s, const float4 *rays, uint64_t n, c
         case B200RT_BVH: trace_kernel<B200RT_BVH, ANY, COUNT><<<blocks, B200RT_BLOCK, 0, st>>>(s->bvh, s->bsp, rays, n, n_dev, hits, occ, cnt); break;
         case B200RT_KDTREE: trace_kernel<B200RT_KDTREE, ANY, COUNT><<<blocks, B200RT_BLOCK, 0, st>>>(s->bvh, s->bsp, rays, n, n_dev, hits, occ, cnt); break;
         case B200RT_RBSP: trace_kernel<B200RT_RBSP, ANY, COUNT><<<blocks, B200RT_BLOCK, 0, st>>>(s->bvh, s->bsp, rays, n, n_dev, hits, occ, cnt); break;
-        default: trace_kernel<B200RT_RBSPKD, ANY, COUNT><<<blocks, B200RT_BLOCK, 0, st>>>(s->bvh, s->bsp, rays, n, n_dev, hits, occ, cnt); break;
+        case B200RT_RBSPKD: trace_kernel<B200RT_RBSPKD, ANY, COUNT><<<blocks, B200RT_BLOCK, 0, st>>>(s->bvh, s->bsp, rays, n, n_dev, hits, occ, cnt); break;
+        case B200RT_BSP: trace_kernel<B200RT_BSP, ANY, COUNT><<<blocks, B200RT_BLOCK, 0, st>>>(s->bvh, s->bsp, rays, n, n_dev, hits, occ, cnt); break;
+        default: trace_kernel<B200RT_BSPKD, ANY, COUNT><<<blocks, B200RT_BLOCK, 0, st>>>(s->bvh, s->bsp, rays, n, n_dev, hits, occ, cnt); break;
     }
     g_launches.fetch_add(1);
 }
@@ -436,7 +465,11 @@ int b200rt::launch_trace(const b200rt_scene *s, const float4 *rays, uint64_t n, 
                 case B200RT_RBSP * 2: PL((bsp_persistent_kernel<B200RT_RBSP, false>), s->bsp); break;
                 case B200RT_RBSP * 2 + 1: PL((bsp_persistent_kernel<B200RT_RBSP, true>), s->bsp); break;
                 case B200RT_RBSPKD * 2: PL((bsp_persistent_kernel<B200RT_RBSPKD, false>), s->bsp); break;
-                default: PL((bsp_persistent_kernel<B200RT_RBSPKD, true>), s->bsp); break;
+                case B200RT_RBSPKD * 2 + 1: PL((bsp_persistent_kernel<B200RT_RBSPKD, true>), s->bsp); break;
+                case B200RT_BSP * 2: PL((bsp_persistent_kernel<B200RT_BSP, false>), s->bsp); break;
+                case B200RT_BSP * 2 + 1: PL((bsp_persistent_kernel<B200RT_BSP, true>), s->bsp); break;
+                case B200RT_BSPKD * 2: PL((bsp_persistent_kernel<B200RT_BSPKD, false>), s->bsp); break;
+                default: PL((bsp_persistent_kernel<B200RT_BSPKD, true>), s->bsp); break;
             }
 #undef PL
 #undef PLB

@@ -6,6 +6,8 @@
 //   kd-tree : KdTreeAccel::Intersect / IntersectP         src/accelerators/kdtreeaccel.cpp:381-521
 //   RBSP    : RBSP::Intersect / IntersectP                src/accelerators/rbsp.cpp:405-547
 //   RBSPKd  : same loop, intersectInterior with kd path   src/accelerators/rbspKd.cpp:68-92
+//   BSP     : BSP::Intersect / IntersectP                 src/accelerators/BSP.cpp:27-163   (20-byte nodes)
+//   BSPKd   : BSPKd::Intersect / IntersectP               src/accelerators/BSPKd.cpp:25-169 (20-byte nodes)
 #pragma once
 #include "rt_math.cuh"
 #include "../../include/b200rt.h"
@@ -37,8 +39,11 @@ struct BvhView {
 
 // kd / RBSP: the reference's own 8-byte nodes (w0 = split | onePrimitive | indicesOffset,
 // w1 = axis bits + aboveChild/nPrims) + primitiveIndices + triangles in original primitive order.
+// BSP / BSPKd: the reference's 20-byte nodes widened to one aligned 32-byte record
+// (w0, flags, axis.x, axis.y | axis.z, 0, 0, 0) so that a node is ONE 256-bit load (a 20-byte stride would
+// straddle 32-byte sectors on 3 of every 8 nodes).
 struct BspView {
-    const uint2 *nodes;
+    const uint2 *nodes;   // kd / RBSP(/Kd): 8-byte nodes; BSP / BSPKd: 32-byte records (read through bsp_fetch)
     const uint32_t *indices;
     const float4 *tris;  // 3 x float4 per ORIGINAL primitive
     const float4 *spheres;
@@ -188,6 +193,64 @@ __device__ __forceinline__ float bsp_interior(const BspView &S, const RayCtx &r,
     return (split - projectedO) * inverseProjectedD;
 }
 
+// One decoded tree node of any of the BSP-like kinds.
+struct BspStep {
+    uint32_t w0;       // leaf: onePrimitive / primitiveIndicesOffset
+    uint32_t payload;  // leaf: nPrims; interior: aboveChild
+    float tPlane;      // interior
+    bool leaf, belowFirst;
+};
+template <int KIND>
+struct BspCodec {  // bit layout of the flags word
+    static constexpr bool wide = KIND == B200RT_BSP || KIND == B200RT_BSPKD;
+};
+
+// Fetch + decode node `cur` and, for an interior node, intersect its split plane.
+//   kd / RBSP / RBSPKd : kdtreeaccel.cpp:43-104, rbsp.cpp:15-80, rbspKd.cpp:68-92 (axis field `off` bits wide)
+//   BSP                : BSP.h:13-67 (bit 0 = leaf, payload << 1), treeIntersectInterior
+//   BSPKd              : BSPKd.h:13-72 (low 3 bits: 0..2 kd axis, 3 leaf, 4 general; payload << 3)
+template <int KIND>
+__device__ __forceinline__ BspStep bsp_fetch(const BspView &S, const RayCtx &r, uint32_t cur, uint32_t off, uint32_t mask,
+                                             uint32_t leafTag) {
+    BspStep st;
+    if (!BspCodec<KIND>::wide) {
+        const uint2 n = __ldg(S.nodes + cur);
+        const uint32_t axis = n.y & mask;
+        st.w0 = n.x;
+        st.payload = n.y >> off;
+        st.leaf = axis == leafTag;
+        st.tPlane = 0.f; st.belowFirst = false;
+        if (!st.leaf) st.tPlane = bsp_interior<KIND>(S, r, axis, __uint_as_float(n.x), st.belowFirst);
+        return st;
+    }
+    float4 lo, hi;
+    asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=f"(lo.x), "=f"(lo.y), "=f"(lo.z), "=f"(lo.w), "=f"(hi.x), "=f"(hi.y), "=f"(hi.z), "=f"(hi.w)
+                 : "l"(reinterpret_cast<const float4 *>(S.nodes) + 2 * (size_t)cur));
+    const uint32_t flags = __float_as_uint(lo.y);
+    const float split = lo.x;
+    st.w0 = __float_as_uint(lo.x);
+    st.tPlane = 0.f; st.belowFirst = false;
+    if (KIND == B200RT_BSP) { st.leaf = (flags & 1u) == 1u; st.payload = flags >> 1; }
+    else { st.leaf = (flags & 7u) == 3u; st.payload = flags >> 3; }
+    if (st.leaf) return st;
+    if (KIND == B200RT_BSPKD && (flags & 7u) < 3u) {  // isKdNode with a valid axis (BSPKd.h:52-60)
+        const uint32_t axis = flags & 7u;
+        const float o = axis == 0 ? r.ox : (axis == 1 ? r.oy : r.oz);
+        const float d = axis == 0 ? r.dx : (axis == 1 ? r.dy : r.dz);
+        const float inv = axis == 0 ? r.ix : (axis == 1 ? r.iy : r.iz);
+        st.belowFirst = (o < split) || (o == split && d <= 0);
+        st.tPlane = (split - o) * inv;
+        return st;
+    }
+    // planeDistance(axis, split, ray, projectedO, inverseProjectedD) (geometry.h:1837-1843)
+    const float projectedO = lo.z * r.ox + lo.w * r.oy + hi.x * r.oz;
+    const float inverseProjectedD = 1 / (lo.z * r.dx + lo.w * r.dy + hi.x * r.dz);
+    st.belowFirst = (projectedO < split) || (projectedO == split && inverseProjectedD <= 0);
+    st.tPlane = (split - projectedO) * inverseProjectedD;
+    return st;
+}
+
 template <int KIND, bool ANY, bool COUNT>
 __device__ __forceinline__ bool bsp_trace(const BspView &S, RayCtx &r, HitRec &h, LocalCount &cnt) {
     float tMin, tMax;
@@ -203,14 +266,12 @@ __device__ __forceinline__ bool bsp_trace(const BspView &S, RayCtx &r, HitRec &h
     for (;;) {
         if (!ANY && r.tMax < tMin) break;  // kdtreeaccel.cpp:400 (closest-hit only)
         if (COUNT) cnt.fetched++;
-        const uint2 n = __ldg(S.nodes + cur);
-        const uint32_t axis = n.y & mask;
-        if (axis != leafTag) {
+        const BspStep n = bsp_fetch<KIND>(S, r, cur, off, mask, leafTag);
+        if (!n.leaf) {
             if (COUNT) cnt.passed++;
-            bool belowFirst;
-            const float tPlane = bsp_interior<KIND>(S, r, axis, __uint_as_float(n.x), belowFirst);
-            const uint32_t above = n.y >> off;
-            const uint32_t first = belowFirst ? cur + 1 : above, second = belowFirst ? above : cur + 1;
+            const float tPlane = n.tPlane;
+            const uint32_t above = n.payload;
+            const uint32_t first = n.belowFirst ? cur + 1 : above, second = n.belowFirst ? above : cur + 1;
             if (tPlane > tMax || tPlane <= 0) cur = first;
             else if (tPlane < tMin) cur = second;
             else {
@@ -220,14 +281,14 @@ __device__ __forceinline__ bool bsp_trace(const BspView &S, RayCtx &r, HitRec &h
             }
         } else {
             if (COUNT) cnt.leaves++;
-            const uint32_t np = n.y >> off;
+            const uint32_t np = n.payload;
             if (np == 1) {
                 if (COUNT) cnt.tests++;
-                if (prim_closest<ANY>(r, S.tris + 3 * (size_t)n.x, h, S.spheres)) { hit = true; if (ANY) return true; }
+                if (prim_closest<ANY>(r, S.tris + 3 * (size_t)n.w0, h, S.spheres)) { hit = true; if (ANY) return true; }
             } else {
                 for (uint32_t i = 0; i < np; ++i) {
                     if (COUNT) { cnt.tests++; cnt.idx++; }
-                    const uint32_t p = __ldg(S.indices + n.x + i);
+                    const uint32_t p = __ldg(S.indices + n.w0 + i);
                     if (prim_closest<ANY>(r, S.tris + 3 * (size_t)p, h, S.spheres)) { hit = true; if (ANY) return true; }
                 }
             }

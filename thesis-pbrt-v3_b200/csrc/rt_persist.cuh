@@ -303,13 +303,11 @@ bsp_persistent_kernel(const __grid_constant__ BspView S, const float4 *__restric
 #pragma unroll 1
                 for (int k = 0; k < B200RT_BSP_STEPS && state == B200RT_ST_NODE; ++k) {
                     if (!ANY && r.tMax < tMin) { finished = true; break; }  // kdtreeaccel.cpp:400 (closest-hit only)
-                    const uint2 nd = __ldg(S.nodes + cur);
-                    const uint32_t axis = nd.y & mask;
-                    if (axis != leafTag) {
-                        bool belowFirst;
-                        const float tPlane = bsp_interior<KIND>(S, r, axis, __uint_as_float(nd.x), belowFirst);
-                        const uint32_t above = nd.y >> off;
-                        const uint32_t first = belowFirst ? cur + 1 : above, second = belowFirst ? above : cur + 1;
+                    const BspStep nd = bsp_fetch<KIND>(S, r, cur, off, mask, leafTag);
+                    if (!nd.leaf) {
+                        const float tPlane = nd.tPlane;
+                        const uint32_t above = nd.payload;
+                        const uint32_t first = nd.belowFirst ? cur + 1 : above, second = nd.belowFirst ? above : cur + 1;
                         if (tPlane > tMax || tPlane <= 0) cur = first;
                         else if (tPlane < tMin) cur = second;
                         else {
@@ -318,7 +316,7 @@ bsp_persistent_kernel(const __grid_constant__ BspView S, const float4 *__restric
                             tMax = tPlane;
                         }
                     } else {
-                        const uint32_t np = nd.y >> off;
+                        const uint32_t np = nd.payload;
                         if (np == 0) {
                             if (todoPos > 0) {
                                 const uint4 e = todo[--todoPos];
@@ -327,7 +325,7 @@ bsp_persistent_kernel(const __grid_constant__ BspView S, const float4 *__restric
                         } else {
                             state = B200RT_ST_LEAF;
                             lsingle = np == 1;
-                            li = nd.x; lend = nd.x + np;  // np == 1: li IS the primitive (kdtreeaccel.cpp:112-118)
+                            li = nd.w0; lend = nd.w0 + np;  // np == 1: li IS the primitive (kdtreeaccel.cpp:112-118)
                         }
                     }
                     if (finished) break;

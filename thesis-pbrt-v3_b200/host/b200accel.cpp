@@ -40,6 +40,10 @@
 #include "accelerators/kdtreeaccel.h"
 #include "accelerators/rbsp.h"
 #include "accelerators/rbspKd.h"
+#include "accelerators/bspPaper.h"
+#include "accelerators/bspPaperKd.h"
+#include "accelerators/bspCluster.h"
+#include "accelerators/bspClusterFastKd.h"
 #undef private
 #undef protected
 #include "core/interaction.h"
@@ -117,7 +121,7 @@ bool capture(const std::vector<std::shared_ptr<Primitive>> &prims, Captured *c) 
 template <class Tree>
 void describeBSP(const Tree *t, b200rt_scene_desc *d, std::vector<float> *dirs) {
     static_assert(sizeof(Float) == 4, "b200rt computes in binary32");
-    d->nodes = (const void *)t->nodes;          // 8-byte nodes (kdtreeaccel.cpp:43-160, rbsp.cpp:15-135)
+    d->nodes = (const void *)t->nodes;          // 8-byte nodes (kdtreeaccel.cpp:43-160, rbsp.cpp:15-135) or 20-byte BSP nodes
     d->node_count = t->nextFreeNode;
     d->prim_indices = t->primitiveIndices.data();
     d->n_indices = (uint32_t)t->primitiveIndices.size();
@@ -198,8 +202,22 @@ B200Accel::B200Accel(std::vector<std::shared_ptr<Primitive>> p, const ParamSet &
     } else if (tree == "rbspkd") {
         std::shared_ptr<RBSPKd> t = CreateRBSPKdTreeAccelerator(prims, ps);
         host = t; d.kind = B200RT_RBSPKD; describeBSP(t.get(), &d, &dirs);
+    } else if (tree == "bsppaper" || tree == "bspcluster") {
+        // general BSP families over 20-byte BSPNode (BSP.h:122-184); the traversal never reads `directions`
+        std::shared_ptr<BSP> t;
+        if (tree == "bsppaper") t = CreateBSPPaperTreeAccelerator(prims, ps);
+        else t = CreateBSPClusterTreeAccelerator(prims, ps);
+        host = t; d.kind = B200RT_BSP; describeBSP(t.get(), &d, &dirs);
+        d.directions = nullptr; d.n_directions = 0;
+    } else if (tree == "bsppaperkd" || tree == "bspclusterfastkd") {
+        std::shared_ptr<BSPKd> t;   // 20-byte BSPKdNode (BSPKd.h:11-174)
+        if (tree == "bsppaperkd") t = CreateBSPPaperKdTreeAccelerator(prims, ps);
+        else t = CreateBSPClusterFastKdTreeAccelerator(prims, ps);
+        host = t; d.kind = B200RT_BSPKD; describeBSP(t.get(), &d, &dirs);
+        d.directions = nullptr; d.n_directions = 0;
     } else {
-        Error("b200: unknown \"tree\" \"%s\" (bvh | kdtree | rbsp | rbspkd)", tree.c_str());
+        Error("b200: unknown \"tree\" \"%s\" (bvh | kdtree | rbsp | rbspkd | bsppaper | bsppaperkd | bspcluster | "
+              "bspclusterfastkd)", tree.c_str());
         return;
     }
     d.tri_verts = cap.verts.data();
