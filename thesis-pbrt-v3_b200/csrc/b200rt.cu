@@ -51,6 +51,8 @@ static uint32_t g_thresh = 14;
 static int g_pblocks[6][2];  // resident persistent blocks per SM, [kind][any]
 static int g_persist_bsp = 1;
 static uint32_t g_bvh_steps = 4;
+static uint32_t g_sstack = 10;     // BVH stack entries kept in shared memory (B200RT_SSTACK; 0 = all in local memory)
+static uint32_t g_sstack_bsp = 0;  // kd/RBSP/BSP todo entries kept in shared memory (B200RT_SSTACK_BSP)
 #define B200RT_PIPE_CHUNK_MAX (1024u * 1024u)
 static uint32_t g_pipe_chunk = 256u * 1024u;  // rays per pipeline stage (B200RT_PIPE_CHUNK overrides, <= 1 Mi)
 
@@ -75,13 +77,29 @@ extern "C" int b200rt_init(int device) {
     if (const char *e = getenv("B200RT_PIPE_CHUNK")) g_pipe_chunk = std::min<uint32_t>(B200RT_PIPE_CHUNK_MAX, std::max(1024, atoi(e)));
     if (const char *e = getenv("B200RT_BVH_STEPS")) g_bvh_steps = std::max(1, atoi(e));
     if (const char *e = getenv("B200RT_PERSIST_BSP")) g_persist_bsp = atoi(e);
+    if (const char *e = getenv("B200RT_SSTACK_BSP")) g_sstack_bsp = (uint32_t)std::min(64, std::max(0, atoi(e)));
+    if (const char *e = getenv("B200RT_SSTACK")) g_sstack = (uint32_t)std::min(64, std::max(0, atoi(e)));
     // the persistent kernels use no shared memory: give the whole 256 KB array to L1 (node working set)
     int carve = 0;
     if (const char *e = getenv("B200RT_CARVEOUT")) carve = atoi(e);
+    const size_t smB = (size_t)g_sstack_bsp * 12 * B200RT_PBLOCK;
+    const int carveB = g_sstack_bsp ? (int)std::min<size_t>(100, (8 * smB * 100) / (228 * 1024) + 1) : carve;
 #define OCC(k, a, fn)                                                                                        \
-    if (carve >= 0) CU(cudaFuncSetAttribute(fn, cudaFuncAttributePreferredSharedMemoryCarveout, carve)); \
-    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_pblocks[k][a], fn, B200RT_PBLOCK, 0))
-    OCC(B200RT_BVH, 0, bvh_persistent_kernel<false>); OCC(B200RT_BVH, 1, bvh_persistent_kernel<true>);
+    CU(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smB));                      \
+    if (carveB >= 0) CU(cudaFuncSetAttribute(fn, cudaFuncAttributePreferredSharedMemoryCarveout, carveB)); \
+    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_pblocks[k][a], fn, B200RT_PBLOCK, smB))
+    {   // BVH kernels: dynamic shared memory = the shared part of the stack
+        const size_t sm = (size_t)g_sstack * sizeof(uint2) * B200RT_PBLOCK;
+        const int bc = g_sstack ? (int)std::min<size_t>(100, (8 * sm * 100) / (228 * 1024) + 1) : carve;
+        CU(cudaFuncSetAttribute(bvh_persistent_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+        CU(cudaFuncSetAttribute(bvh_persistent_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+        if (bc >= 0) {
+            CU(cudaFuncSetAttribute(bvh_persistent_kernel<false>, cudaFuncAttributePreferredSharedMemoryCarveout, bc));
+            CU(cudaFuncSetAttribute(bvh_persistent_kernel<true>, cudaFuncAttributePreferredSharedMemoryCarveout, bc));
+        }
+        CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_pblocks[B200RT_BVH][0], bvh_persistent_kernel<false>, B200RT_PBLOCK, sm));
+        CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_pblocks[B200RT_BVH][1], bvh_persistent_kernel<true>, B200RT_PBLOCK, sm));
+    }
     OCC(B200RT_KDTREE, 0, (bsp_persistent_kernel<B200RT_KDTREE, false>)); OCC(B200RT_KDTREE, 1, (bsp_persistent_kernel<B200RT_KDTREE, true>));
     OCC(B200RT_RBSP, 0, (bsp_persistent_kernel<B200RT_RBSP, false>)); OCC(B200RT_RBSP, 1, (bsp_persistent_kernel<B200RT_RBSP, true>));
     OCC(B200RT_RBSPKD, 0, (bsp_persistent_kernel<B200RT_RBSPKD, false>)); OCC(B200RT_RBSPKD, 1, (bsp_persistent_kernel<B200RT_RBSPKD, true>));
@@ -455,8 +473,8 @@ int b200rt::launch_trace(const b200rt_scene *s, const float4 *rays, uint64_t n, 
             b200rt_hit *ho = any ? nullptr : hits + off;
             uint8_t *oo = any ? occ + off : nullptr;
             const float4 *ri = rays + 2 * off;
-#define PL(fn, view) fn<<<blocks, B200RT_PBLOCK, 0, st>>>(view, ri, m, n_dev, ho, oo, pc, g_thresh, chunk)
-#define PLB(fn, view) fn<<<blocks, B200RT_PBLOCK, 0, st>>>(view, ri, m, n_dev, ho, oo, pc, g_thresh, chunk, g_bvh_steps)
+#define PL(fn, view) fn<<<blocks, B200RT_PBLOCK, (size_t)g_sstack_bsp * 12 * B200RT_PBLOCK, st>>>(view, ri, m, n_dev, ho, oo, pc, g_thresh, chunk, g_sstack_bsp)
+#define PLB(fn, view) fn<<<blocks, B200RT_PBLOCK, (size_t)g_sstack * sizeof(uint2) * B200RT_PBLOCK, st>>>(view, ri, m, n_dev, ho, oo, pc, g_thresh, chunk, g_bvh_steps, g_sstack)
             switch (s->kind * 2 + (any ? 1 : 0)) {
                 case B200RT_BVH * 2: PLB(bvh_persistent_kernel<false>, s->bvh); break;
                 case B200RT_BVH * 2 + 1: PLB(bvh_persistent_kernel<true>, s->bvh); break;

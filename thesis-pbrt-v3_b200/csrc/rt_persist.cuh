@@ -96,7 +96,12 @@ bvh_persistent_kernel(const __grid_constant__ BvhView S, const float4 *__restric
                       const uint32_t *__restrict__ n_dev, b200rt_hit *__restrict__ hits,
                       uint8_t *__restrict__ occluded, PersistCounters *pc, uint32_t thresh,
                       uint32_t chunk /* rays a warp claims per global atomic */,
-                      uint32_t steps /* interior steps a lane may take per vote */) {
+                      uint32_t steps /* interior steps a lane may take per vote */,
+                      uint32_t sdepth /* stack entries [0, sdepth) live in shared memory, the rest in local */) {
+    // Shared-memory bottom of the traversal stack: entry d of thread t sits at sst[d * blockDim + t], i.e. in bank
+    // t % 32 whatever d is, so a push/pop by 32 lanes at 32 DIFFERENT depths is still one conflict-free access
+    // (the per-thread local array would touch up to 32 different 128-byte lines for the same push).
+    extern __shared__ uint2 sst[];
     uint32_t n = (uint32_t)n64;
     if (n_dev) { const uint32_t m = *n_dev; n = m < n ? m : n; }
     const unsigned FULL = 0xFFFFFFFFu;
@@ -187,7 +192,10 @@ bvh_persistent_kernel(const __grid_constant__ BvhView S, const float4 *__restric
                     const bool hitNear = negAxis ? p1 : p0, hitFar = negAxis ? p0 : p1;
                     if (hitNear) {
                         if (hitFar) {
-                            stack[sp++] = make_uint2(farRef, __float_as_uint(negAxis ? t0 : t1));
+                            const uint2 e = make_uint2(farRef, __float_as_uint(negAxis ? t0 : t1));
+                            if ((uint32_t)sp < sdepth) sst[sp * B200RT_PBLOCK + threadIdx.x] = e;
+                            else stack[sp - sdepth] = e;
+                            ++sp;
                         }
                         cur = nearRef;
                     } else if (hitFar) cur = farRef;
@@ -195,7 +203,8 @@ bvh_persistent_kernel(const __grid_constant__ BvhView S, const float4 *__restric
                         // pop: the reference re-tests the far box against the CURRENT ray.tMax (bvh.cpp:367)
                         cur = B200RT_DONE;
                         while (sp > 0) {
-                            const uint2 e = stack[--sp];
+                            --sp;
+                            const uint2 e = (uint32_t)sp < sdepth ? sst[sp * B200RT_PBLOCK + threadIdx.x] : stack[sp - sdepth];
                             if (ANY || __uint_as_float(e.y) < r.tMax) { cur = e.x; break; }
                         }
                     }
@@ -214,7 +223,8 @@ bvh_persistent_kernel(const __grid_constant__ BvhView S, const float4 *__restric
                     else if (__float_as_uint(v1.w) & B200RT_TRI_LAST) {
                         cur = B200RT_DONE;
                         while (sp > 0) {
-                            const uint2 e = stack[--sp];
+                            --sp;
+                            const uint2 e = (uint32_t)sp < sdepth ? sst[sp * B200RT_PBLOCK + threadIdx.x] : stack[sp - sdepth];
                             if (ANY || __uint_as_float(e.y) < r.tMax) { cur = e.x; break; }
                         }
                     } else cur += 1;
@@ -247,7 +257,9 @@ template <int KIND, bool ANY>
 __global__ void __launch_bounds__(B200RT_PBLOCK, 8)
 bsp_persistent_kernel(const __grid_constant__ BspView S, const float4 *__restrict__ rays, uint64_t n64,
                       const uint32_t *__restrict__ n_dev, b200rt_hit *__restrict__ hits,
-                      uint8_t *__restrict__ occluded, PersistCounters *pc, uint32_t thresh, uint32_t chunk) {
+                      uint8_t *__restrict__ occluded, PersistCounters *pc, uint32_t thresh, uint32_t chunk,
+                      uint32_t sdepth /* todo entries [0, sdepth) live in shared memory (see bvh_persistent_kernel) */) {
+    extern __shared__ uint32_t sst32[];  // 3 planes (node, tMin, tMax) of sdepth x blockDim words: bank = lane
     uint32_t n = (uint32_t)n64;
     if (n_dev) { const uint32_t m = *n_dev; n = m < n ? m : n; }
     const unsigned FULL = 0xFFFFFFFFu;
@@ -311,7 +323,12 @@ bsp_persistent_kernel(const __grid_constant__ BspView S, const float4 *__restric
                         if (tPlane > tMax || tPlane <= 0) cur = first;
                         else if (tPlane < tMin) cur = second;
                         else {
-                            todo[todoPos++] = make_uint4(second, __float_as_uint(tPlane), __float_as_uint(tMax), 0u);
+                            if ((uint32_t)todoPos < sdepth) {
+                                uint32_t *q = sst32 + todoPos * B200RT_PBLOCK + threadIdx.x;
+                                q[0] = second; q[sdepth * B200RT_PBLOCK] = __float_as_uint(tPlane);
+                                q[2 * sdepth * B200RT_PBLOCK] = __float_as_uint(tMax);
+                            } else todo[todoPos - sdepth] = make_uint4(second, __float_as_uint(tPlane), __float_as_uint(tMax), 0u);
+                            ++todoPos;
                             cur = first;
                             tMax = tPlane;
                         }
@@ -319,7 +336,12 @@ bsp_persistent_kernel(const __grid_constant__ BspView S, const float4 *__restric
                         const uint32_t np = nd.payload;
                         if (np == 0) {
                             if (todoPos > 0) {
-                                const uint4 e = todo[--todoPos];
+                                --todoPos;
+                            uint4 e;
+                            if ((uint32_t)todoPos < sdepth) {
+                                const uint32_t *q = sst32 + todoPos * B200RT_PBLOCK + threadIdx.x;
+                                e = make_uint4(q[0], q[sdepth * B200RT_PBLOCK], q[2 * sdepth * B200RT_PBLOCK], 0u);
+                            } else e = todo[todoPos - sdepth];
                                 cur = e.x; tMin = __uint_as_float(e.y); tMax = __uint_as_float(e.z);
                             } else finished = true;
                         } else {
@@ -338,7 +360,12 @@ bsp_persistent_kernel(const __grid_constant__ BspView S, const float4 *__restric
                 }
                 if (!finished && ++li == lend) {
                     if (todoPos > 0) {
-                        const uint4 e = todo[--todoPos];
+                        --todoPos;
+                            uint4 e;
+                            if ((uint32_t)todoPos < sdepth) {
+                                const uint32_t *q = sst32 + todoPos * B200RT_PBLOCK + threadIdx.x;
+                                e = make_uint4(q[0], q[sdepth * B200RT_PBLOCK], q[2 * sdepth * B200RT_PBLOCK], 0u);
+                            } else e = todo[todoPos - sdepth];
                         cur = e.x; tMin = __uint_as_float(e.y); tMax = __uint_as_float(e.z);
                         state = B200RT_ST_NODE;
                     } else finished = true;
