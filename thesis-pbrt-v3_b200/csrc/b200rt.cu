@@ -52,7 +52,16 @@ static int g_pblocks[6][2];  // resident persistent blocks per SM, [kind][any]
 static int g_persist_bsp = 1;
 static uint32_t g_bvh_steps = 4;
 static uint32_t g_sstack = 10;     // BVH stack entries kept in shared memory (B200RT_SSTACK; 0 = all in local memory)
-static uint32_t g_sstack_bsp = 0;  // kd/RBSP/BSP todo entries kept in shared memory (B200RT_SSTACK_BSP)
+static uint32_t g_sstack_bsp = 0;
+static int g_minb = 9;             // __launch_bounds__ min blocks/SM variant of the BVH kernels (B200RT_MINB: 8 | 9; 9 = 56 registers, 36 warps/SM: +2 % over 8, 10 spills — profiles/r01_ab_bvh_minblocks.log)
+typedef void (*bvh_kernel_t)(const BvhView, const float4 *, uint64_t, const uint32_t *, b200rt_hit *, uint8_t *, PersistCounters *,
+                             uint32_t, uint32_t, uint32_t, uint32_t);
+static const void *bvh_fn(bool any) {
+    bvh_kernel_t f;
+    if (g_minb == 8) f = any ? bvh_persistent_kernel<true, 8> : bvh_persistent_kernel<false, 8>;
+    else f = any ? bvh_persistent_kernel<true, 9> : bvh_persistent_kernel<false, 9>;
+    return (const void *)f;
+}  // kd/RBSP/BSP todo entries kept in shared memory (B200RT_SSTACK_BSP)
 #define B200RT_PIPE_CHUNK_MAX (1024u * 1024u)
 static uint32_t g_pipe_chunk = 256u * 1024u;  // rays per pipeline stage (B200RT_PIPE_CHUNK overrides, <= 1 Mi)
 
@@ -90,15 +99,15 @@ extern "C" int b200rt_init(int device) {
     CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_pblocks[k][a], fn, B200RT_PBLOCK, smB))
     {   // BVH kernels: dynamic shared memory = the shared part of the stack
         const size_t sm = (size_t)g_sstack * sizeof(uint2) * B200RT_PBLOCK;
-        const int bc = g_sstack ? (int)std::min<size_t>(100, (8 * sm * 100) / (228 * 1024) + 1) : carve;
-        CU(cudaFuncSetAttribute(bvh_persistent_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
-        CU(cudaFuncSetAttribute(bvh_persistent_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
-        if (bc >= 0) {
-            CU(cudaFuncSetAttribute(bvh_persistent_kernel<false>, cudaFuncAttributePreferredSharedMemoryCarveout, bc));
-            CU(cudaFuncSetAttribute(bvh_persistent_kernel<true>, cudaFuncAttributePreferredSharedMemoryCarveout, bc));
+        if (const char *e = getenv("B200RT_MINB")) g_minb = atoi(e);
+        if (g_minb != 8) g_minb = 9;
+        const int bc = g_sstack ? (int)std::min<size_t>(100, ((size_t)g_minb * sm * 100) / (228 * 1024) + 1) : carve;
+        const void *fns[2] = {bvh_fn(false), bvh_fn(true)};
+        for (int a = 0; a < 2; ++a) {
+            CU(cudaFuncSetAttribute(fns[a], cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+            if (bc >= 0) CU(cudaFuncSetAttribute(fns[a], cudaFuncAttributePreferredSharedMemoryCarveout, bc));
+            CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_pblocks[B200RT_BVH][a], fns[a], B200RT_PBLOCK, sm));
         }
-        CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_pblocks[B200RT_BVH][0], bvh_persistent_kernel<false>, B200RT_PBLOCK, sm));
-        CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_pblocks[B200RT_BVH][1], bvh_persistent_kernel<true>, B200RT_PBLOCK, sm));
     }
     OCC(B200RT_KDTREE, 0, (bsp_persistent_kernel<B200RT_KDTREE, false>)); OCC(B200RT_KDTREE, 1, (bsp_persistent_kernel<B200RT_KDTREE, true>));
     OCC(B200RT_RBSP, 0, (bsp_persistent_kernel<B200RT_RBSP, false>)); OCC(B200RT_RBSP, 1, (bsp_persistent_kernel<B200RT_RBSP, true>));
@@ -476,8 +485,13 @@ int b200rt::launch_trace(const b200rt_scene *s, const float4 *rays, uint64_t n, 
 #define PL(fn, view) fn<<<blocks, B200RT_PBLOCK, (size_t)g_sstack_bsp * 12 * B200RT_PBLOCK, st>>>(view, ri, m, n_dev, ho, oo, pc, g_thresh, chunk, g_sstack_bsp)
 #define PLB(fn, view) fn<<<blocks, B200RT_PBLOCK, (size_t)g_sstack * sizeof(uint2) * B200RT_PBLOCK, st>>>(view, ri, m, n_dev, ho, oo, pc, g_thresh, chunk, g_bvh_steps, g_sstack)
             switch (s->kind * 2 + (any ? 1 : 0)) {
-                case B200RT_BVH * 2: PLB(bvh_persistent_kernel<false>, s->bvh); break;
-                case B200RT_BVH * 2 + 1: PLB(bvh_persistent_kernel<true>, s->bvh); break;
+                case B200RT_BVH * 2: case B200RT_BVH * 2 + 1: {
+                    const size_t smem = (size_t)g_sstack * sizeof(uint2) * B200RT_PBLOCK;
+                    void *args[] = {(void *)&s->bvh, (void *)&ri, (void *)&m, (void *)&n_dev, (void *)&ho, (void *)&oo, (void *)&pc,
+                                    (void *)&g_thresh, (void *)&chunk, (void *)&g_bvh_steps, (void *)&g_sstack};
+                    CU(cudaLaunchKernel(bvh_fn(any), dim3(blocks), dim3(B200RT_PBLOCK), args, smem, st));
+                    break;
+                }
                 case B200RT_KDTREE * 2: PL((bsp_persistent_kernel<B200RT_KDTREE, false>), s->bsp); break;
                 case B200RT_KDTREE * 2 + 1: PL((bsp_persistent_kernel<B200RT_KDTREE, true>), s->bsp); break;
                 case B200RT_RBSP * 2: PL((bsp_persistent_kernel<B200RT_RBSP, false>), s->bsp); break;

@@ -69,12 +69,17 @@ struct HitRec {
 // GeometricPrimitive::Intersect (primitive.cpp:123-139): on a hit ray.tMax = tHit.
 // ANY = GeometricPrimitive::IntersectP (:118-121): Triangle::IntersectP has NO degenerate-triangle
 // rejection outside its alpha-mask branch (triangle.cpp:533-556), unlike Intersect (:309-315).
+// dptr (optional): where the ray's (d.xyz, time) float4 lives in global memory.  The BVH persistent kernel passes
+// it so that the direction — needed by nothing but the rare sphere test there — is not held in three registers
+// for the whole traversal.
 template <bool ANY>
 __device__ __forceinline__ bool prim_closest(RayCtx &r, const float4 v0, const float4 v1, const float4 v2, HitRec &h,
-                                             const float4 *spheres) {
+                                             const float4 *spheres, const float4 *dptr = nullptr) {
     float t, b0, b1, b2;
     if (__float_as_uint(v1.w) & B200RT_PRIM_SPHERE) {  // Sphere::Intersect / IntersectP (sphere.cpp:49, 158)
-        if (!sphere_test(spheres + 4 * (size_t)__float_as_uint(v2.w), r.ox, r.oy, r.oz, r.dx, r.dy, r.dz, r.tMax, t))
+        float dx = r.dx, dy = r.dy, dz = r.dz;
+        if (dptr) { const float4 dd = __ldg(dptr); dx = dd.x; dy = dd.y; dz = dd.z; }
+        if (!sphere_test(spheres + 4 * (size_t)__float_as_uint(v2.w), r.ox, r.oy, r.oz, dx, dy, dz, r.tMax, t))
             return false;
         r.tMax = t;
         h.prim = __float_as_uint(v0.w); h.t = t; h.b0 = h.b1 = h.b2 = 0.f;  // no barycentrics on a sphere

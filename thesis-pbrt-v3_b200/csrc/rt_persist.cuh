@@ -90,8 +90,8 @@ __device__ __forceinline__ void warp_exit(PersistCounters *pc, int lane) {
     }
 }
 
-template <bool ANY>
-__global__ void __launch_bounds__(B200RT_PBLOCK, 8)
+template <bool ANY, int MINB>
+__global__ void __launch_bounds__(B200RT_PBLOCK, MINB)
 bvh_persistent_kernel(const __grid_constant__ BvhView S, const float4 *__restrict__ rays, uint64_t n64,
                       const uint32_t *__restrict__ n_dev, b200rt_hit *__restrict__ hits,
                       uint8_t *__restrict__ occluded, PersistCounters *pc, uint32_t thresh,
@@ -215,7 +215,7 @@ bvh_persistent_kernel(const __grid_constant__ BvhView S, const float4 *__restric
                     const float4 *rec = S.tris + 3 * (size_t)(cur & ~B200RT_LEAF_BIT);
                     const float4 v0 = __ldg(rec), v1 = __ldg(rec + 1), v2 = __ldg(rec + 2);
                     bool stop = false;
-                    if (prim_closest<ANY>(r, v0, v1, v2, h, S.spheres)) {
+                    if (prim_closest<ANY>(r, v0, v1, v2, h, S.spheres, rays + 2 * (size_t)rayIdx + 1)) {
                         hit = true;
                         if (ANY) stop = true;
                     }
