@@ -44,6 +44,14 @@ std::unique_ptr<RGBSpectrum[]> ReadImage(const std::string &, Point2i *) { retur
 }  // namespace pbrt
 using namespace pbrt;
 
+// The pixels of the last Film::WriteImage in this process (used by tests/hostplugin for the C++ integrator).
+extern "C" int ref_last_image(float *out_rgb, int *xres, int *yres) {
+    std::lock_guard<std::mutex> l(g_imgMutex);
+    *xres = g_lastRes.x; *yres = g_lastRes.y;
+    if (out_rgb) std::memcpy(out_rgb, g_lastImage.data(), sizeof(float) * g_lastImage.size());
+    return 0;
+}
+
 namespace {
 // Counts the calls that reach the aggregate (what Scene::Intersect/IntersectP count, scene.cpp:41-52).
 struct CountingAggregate : public Aggregate {

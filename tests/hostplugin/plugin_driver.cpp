@@ -88,3 +88,69 @@ extern "C" int plugin_intersect_p_batch(const ref_accel *a, const float *rays, u
     }
     return acc->IntersectPBatch(rs.data(), n, occ) ? 0 : 1;
 }
+
+// ---- Integrator "b200wavefront" (thesis-pbrt-v3_b200/host/b200integrator.cpp) ------------------------------------
+// Same programmatic scene as oracle/ref/ref_render.cpp (matte material, one point light, perspective camera, box
+// filter), but the aggregate is Accelerator "b200" and the integrator is the C++ wavefront plugin.  The image comes
+// back through Film::WriteImage like the reference's.
+#include "core/camera.h"
+#include "core/film.h"
+#include "core/scene.h"
+#include "core/spectrum.h"
+#include "cameras/perspective.h"
+#include "filters/box.h"
+#include "lights/point.h"
+#include "materials/matte.h"
+#include "samplers/random.h"
+#include "textures/constant.h"
+#include "b200integrator.h"
+extern "C" int ref_last_image(float *out_rgb, int *xres, int *yres);
+std::shared_ptr<pbrt::Shape> shape_of(const pbrt::Primitive *p);   // plugin_shape_of.cpp (GeometricPrimitive::shape is private)
+
+extern "C" int plugin_render(ref_scene *s, const char *tree, const float *cam, int xres, int yres, int spp, int maxdepth,
+                             const float *light_pos, const float *light_I, const float *kd, int seed, int rank, int world,
+                             const char *tmp_prefix, float *out_rgb, uint64_t *n_closest, uint64_t *n_shadow) {
+    PbrtOptions.quiet = true;
+    Float rgb[3] = {kd[0], kd[1], kd[2]};
+    auto Kd = std::make_shared<ConstantTexture<Spectrum>>(Spectrum::FromRGB(rgb));
+    auto sigma = std::make_shared<ConstantTexture<Float>>(0.f);
+    auto matte = std::make_shared<MatteMaterial>(Kd, sigma, nullptr);
+    MediumInterface mi;
+    std::vector<std::shared_ptr<Primitive>> prims;
+    for (auto &p : s->prims) prims.push_back(std::make_shared<GeometricPrimitive>(shape_of(p.get()), matte, nullptr, mi));
+    ParamSet aps;
+    std::unique_ptr<std::string[]> t(new std::string[1]);
+    t[0] = tree;
+    aps.AddString("tree", std::move(t), 1);
+    std::shared_ptr<Primitive> accel = CreateB200Accelerator(prims, aps);
+    if (!accel) return 1;
+    Float li[3] = {light_I[0], light_I[1], light_I[2]};
+    Transform l2w = Translate(Vector3f(light_pos[0], light_pos[1], light_pos[2]));
+    std::vector<std::shared_ptr<Light>> lights;
+    lights.push_back(std::make_shared<PointLight>(l2w, mi, Spectrum::FromRGB(li)));
+    Scene scene(accel, lights);
+    std::unique_ptr<Filter> filter(new BoxFilter(Vector2f(0.5f, 0.5f)));
+    Film *film = new Film(Point2i(xres, yres), Bounds2f(Point2f(0, 0), Point2f(1, 1)), std::move(filter), 35.f,
+                          std::string(tmp_prefix) + ".exr", 1.f);
+    Transform c2w = Inverse(LookAt(Point3f(cam[0], cam[1], cam[2]), Point3f(cam[3], cam[4], cam[5]), Vector3f(cam[6], cam[7], cam[8])));
+    AnimatedTransform ac2w(&c2w, 0.f, &c2w, 1.f);
+    Float frame = Float(xres) / Float(yres);
+    Bounds2f screen;
+    if (frame > 1.f) { screen.pMin = Point2f(-frame, -1.f); screen.pMax = Point2f(frame, 1.f); }
+    else { screen.pMin = Point2f(-1.f, -1.f / frame); screen.pMax = Point2f(1.f, 1.f / frame); }
+    std::shared_ptr<const Camera> camera(new PerspectiveCamera(ac2w, screen, 0.f, 1.f, 0.f, 1e6f, cam[9], film, nullptr));
+    std::shared_ptr<Sampler> sampler(new RandomSampler(spp));
+    // what MakeIntegrator's new branch does (api.cpp:1895-1945)
+    ParamSet ips;
+    auto addInt = [&](const char *name, int v) { std::unique_ptr<int[]> a(new int[1]); a[0] = v; ips.AddInt(name, std::move(a), 1); };
+    addInt("maxdepth", maxdepth); addInt("seed", seed); addInt("rank", rank); addInt("world", world);
+    std::unique_ptr<B200WavefrontIntegrator> integ(CreateB200WavefrontIntegrator(ips, sampler, camera));
+    integ->Render(scene);
+    int w = 0, h = 0;
+    ref_last_image(nullptr, &w, &h);
+    if (w != xres || h != yres) return 2;
+    ref_last_image(out_rgb, &w, &h);
+    if (n_closest) *n_closest = integ->stats().closest_rays;
+    if (n_shadow) *n_shadow = integ->stats().shadow_rays;
+    return 0;
+}

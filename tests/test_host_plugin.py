@@ -142,3 +142,52 @@ def test_plugin_with_this_repos_builders(host, gpu, tree):
     rays = _rays(4000, seed=5)
     _same(acc.intersect_batch(rays), ref.intersect(rays))
     assert np.array_equal(acc.intersect_p_batch(rays), ref.intersect_p(rays))
+
+
+@pytest.mark.gpu
+def test_cpp_wavefront_integrator_matches_the_references_render(host, gpu):
+    """`Integrator "b200wavefront"` (host/b200integrator.cpp) over `Accelerator "b200"`, set up exactly like the
+    reference's own render of tests/golden/ref_render.npz (PerspectiveCamera from LookAt/fov, Film + BoxFilter,
+    PointLight, MatteMaterial): Integrator::Render -> b200rt_render -> Film::SetImage/WriteImage.  Same statistical
+    bar as tests/test_gpu_wavefront.py (the samplers differ), plus agreement with the Python mirror of the same
+    driver (same seed; the only difference is the camera frame recovered through Camera::GenerateRay in float32)."""
+    from conftest import load_golden
+    from b200rt import scenes
+    from b200rt.wavefront import film_to_rgb
+    rb, L = host
+    L.plugin_render.argtypes = [C.c_void_p, C.c_char_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
+                                C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_char_p, C.c_void_p, C.POINTER(C.c_uint64),
+                                C.POINTER(C.c_uint64)]
+    g = load_golden("ref_render.npz")
+    res, spp, maxdepth = (int(x) for x in g["killeroo_params"])
+    sc = scenes.killeroo_simple(xres=res, yres=res)
+    tv = sc["tri_verts"]
+    S = rb.RefScene(tv.reshape(-1, 3), np.arange(3 * len(tv), dtype=np.int32).reshape(-1, 3), L=L)
+    r = scenes._rot_z(5.0)   # scenes/killeroo-simple:1-3 (LookAt + Rotate -5 about z)
+    eye = scenes._xform(r, np.array([[400.0, 20, 30]]))[0]
+    look = scenes._xform(r, np.array([[0.0, 63, -110]]))[0]
+    cam = np.array(list(eye) + list(look) + [0, 0, 1, 39.0], np.float32)
+    light = np.asarray(sc["light"], np.float32)
+    I, kd = g["killeroo_I"].astype(np.float32), g["killeroo_kd"].astype(np.float32)
+    out = np.zeros((res, res, 3), np.float32)
+    nc, ns = C.c_uint64(), C.c_uint64()
+    import tempfile
+    with tempfile.TemporaryDirectory() as td:
+        rc = L.plugin_render(S.h, b"bvh", cam.ctypes.data, res, res, spp, maxdepth, light.ctypes.data, I.ctypes.data,
+                             kd.ctypes.data, 9, 0, 1, os.path.join(td, "img").encode(), out.ctypes.data, C.byref(nc), C.byref(ns))
+    assert rc == 0
+    ref = g["killeroo_rgb"].astype(np.float64)
+
+    def blocks(img, k=8):
+        return img.reshape(res // k, k, res // k, k, 3).mean((1, 3))
+    assert abs(out.mean() / ref.mean() - 1) < 0.01
+    assert np.sqrt(((blocks(out.astype(np.float64)) - blocks(ref)) ** 2).mean()) / ref.mean() < 0.03
+    rnc, rns = (int(x) for x in g["killeroo_rays"])
+    assert abs(nc.value / rnc - 1) < 0.01 and abs(ns.value / rns - 1) < 0.01
+    # the Python mirror with the same seed
+    acc = gpu.MakeAccelerator("bvh", tv)
+    film, st = gpu.WavefrontPathIntegrator(sc["camera"], spp=spp, maxdepth=maxdepth, light_pos=light, light_I=I, kd=kd,
+                                           seed=9).Render(acc)
+    py = film_to_rgb(film).astype(np.float64)
+    assert np.sqrt(((blocks(out.astype(np.float64)) - blocks(py)) ** 2).mean()) / py.mean() < 0.005
+    assert abs(st["closest_rays"] / nc.value - 1) < 1e-3

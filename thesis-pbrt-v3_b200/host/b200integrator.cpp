@@ -1,0 +1,167 @@
+// b200integrator.cpp — see b200integrator.h.  Host-side glue only: the frame is rendered by b200rt_render on the B200.
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+
+#include "b200integrator.h"
+#include "b200accel.h"
+#include "camera.h"
+#include "film.h"
+#include "filter.h"
+#include "interaction.h"
+#include "light.h"
+#include "material.h"
+#include "memory.h"
+#include "paramset.h"
+#include "reflection.h"
+#include "sampler.h"
+#include "scene.h"
+
+namespace pbrt {
+
+namespace {
+
+// The pinhole frame of a perspective camera, recovered through Camera::GenerateRay (cameras/perspective.cpp:97-143):
+// d(fx, fy) = dir + (2 fx - 1) right + (1 - 2 fy) up for film coordinates fx, fy in [0,1].
+bool describeCamera(const Camera &cam, b200rt_camera *out) {
+    const Point2i res = cam.film->fullResolution;
+    auto dirAt = [&](Float x, Float y, Point3f *o) {
+        CameraSample cs;
+        cs.pFilm = Point2f(x, y);
+        cs.pLens = Point2f(0.5f, 0.5f);
+        cs.time = 0;
+        Ray r;
+        cam.GenerateRay(cs, &r);
+        if (o) *o = r.o;
+        return Normalize(r.d);
+    };
+    Point3f eye, eye2;
+    const Vector3f dc = dirAt(res.x * 0.5f, res.y * 0.5f, &eye);
+    const Vector3f d00 = dirAt(0, 0, &eye2), d10 = dirAt((Float)res.x, 0, nullptr), d01 = dirAt(0, (Float)res.y, nullptr);
+    if ((eye - eye2).Length() > 1e-6f * (1 + (eye - Point3f(0, 0, 0)).Length())) {
+        Error("b200wavefront: only pinhole perspective cameras (lensradius 0) are supported");
+        return false;
+    }
+    // put the corner directions on the plane at distance 1 along the view direction
+    const Vector3f v00 = d00 / Dot(d00, dc), v10 = d10 / Dot(d10, dc), v01 = d01 / Dot(d01, dc);
+    const Vector3f right = (v10 - v00) * 0.5f, up = (v00 - v01) * 0.5f;
+    const Float e[3] = {eye.x, eye.y, eye.z}, d[3] = {dc.x, dc.y, dc.z}, r[3] = {right.x, right.y, right.z}, u[3] = {up.x, up.y, up.z};
+    std::memcpy(out->eye, e, 12); std::memcpy(out->dir, d, 12); std::memcpy(out->right, r, 12); std::memcpy(out->up, u, 12);
+    out->xres = (uint32_t)res.x; out->yres = (uint32_t)res.y;
+    return true;
+}
+
+// Kd of a Lambertian material, measured through the public BSDF: f(n, n) * Pi (reflection.h LambertianReflection).
+bool lambertianKd(const Material *m, Float kd[3]) {
+    MemoryArena arena;
+    const Normal3f n(0, 0, 1);
+    SurfaceInteraction si(Point3f(0, 0, 0), Vector3f(0, 0, 0), Point2f(0.5f, 0.5f), Vector3f(0, 0, 1), Vector3f(1, 0, 0),
+                          Vector3f(0, 1, 0), Normal3f(0, 0, 0), Normal3f(0, 0, 0), 0, nullptr);
+    m->ComputeScatteringFunctions(&si, arena, TransportMode::Radiance, true);
+    if (!si.bsdf) return false;
+    const int all = si.bsdf->NumComponents(BSDF_ALL);
+    if (all != 1 || si.bsdf->NumComponents(BxDFType(BSDF_REFLECTION | BSDF_DIFFUSE)) != 1) return false;
+    const Vector3f w(0, 0, 1);
+    Float rgb[3];
+    Spectrum(si.bsdf->f(w, w) * Pi).ToRGB(rgb);
+    // a Lambertian lobe is direction-independent; an Oren-Nayar one (sigma > 0) is not
+    Float rgb2[3];
+    Spectrum(si.bsdf->f(w, Normalize(Vector3f(0.6f, 0.3f, 0.5f))) * Pi).ToRGB(rgb2);
+    for (int i = 0; i < 3; ++i) {
+        if (std::abs(rgb[i] - rgb2[i]) > 1e-6f) return false;
+        kd[i] = rgb[i];
+    }
+    return true;
+}
+
+}  // namespace
+
+void B200WavefrontIntegrator::Render(const Scene &scene) {
+    const B200Accel *accel = B200Accel::current();
+    if (!accel || !accel->ok()) {
+        Error("b200wavefront: the scene's aggregate is not Accelerator \"b200\"; nothing rendered");
+        return;
+    }
+    Film *film = camera->film;
+    b200rt_render_desc d;
+    std::memset(&d, 0, sizeof(d));
+    if (!describeCamera(*camera, &d.camera)) return;
+    if (film->croppedPixelBounds.pMin != Point2i(0, 0) || film->croppedPixelBounds.pMax != film->fullResolution) {
+        Error("b200wavefront: crop windows are not supported yet");
+        return;
+    }
+    if (film->filter->radius.x > 0.5f || film->filter->radius.y > 0.5f) {
+        Error("b200wavefront: pixel filters wider than one pixel are not supported (use PixelFilter \"box\")");
+        return;
+    }
+    // one point light (LightSource "point"): position and intensity through Light::Sample_Li (lights/point.cpp:44-53)
+    if (scene.lights.size() != 1 || !(scene.lights[0]->flags & (int)LightFlags::DeltaPosition)) {
+        Error("b200wavefront: exactly one point light is supported");
+        return;
+    }
+    {
+        Interaction ref(Point3f(0, 0, 0), Normal3f(0, 0, 1), Vector3f(0, 0, 0), Vector3f(0, 0, 1), 0, MediumInterface());
+        Vector3f wi;
+        Float pdf;
+        VisibilityTester vis;
+        const Spectrum Li = scene.lights[0]->Sample_Li(ref, Point2f(0.5f, 0.5f), &wi, &pdf, &vis);
+        const Point3f pl = vis.P1().p;
+        const Float d2 = (pl - Point3f(0, 0, 0)).LengthSquared();
+        Float rgb[3];
+        Spectrum(Li * d2).ToRGB(rgb);
+        d.light_pos[0] = pl.x; d.light_pos[1] = pl.y; d.light_pos[2] = pl.z;
+        for (int i = 0; i < 3; ++i) d.light_I[i] = rgb[i];
+    }
+    // one Lambertian Kd shared by every primitive (Material "matte" with a constant Kd, sigma 0)
+    {
+        const Material *seen = nullptr;
+        bool have = false;
+        for (size_t i = 0; i < accel->primitiveCount(); ++i) {
+            const Material *m = accel->primitive((uint32_t)i)->GetMaterial();
+            if (!m || m == seen) continue;
+            Float kd[3];
+            if (!lambertianKd(m, kd)) { Error("b200wavefront: only Lambertian \"matte\" materials are supported"); return; }
+            if (have && (kd[0] != d.kd[0] || kd[1] != d.kd[1] || kd[2] != d.kd[2])) {
+                Error("b200wavefront: one Kd for the whole scene is supported so far");
+                return;
+            }
+            std::memcpy(d.kd, kd, sizeof(kd));
+            have = true;
+            seen = m;
+        }
+        if (!have) { Error("b200wavefront: no material"); return; }
+    }
+    d.spp = (uint32_t)sampler->samplesPerPixel;
+    d.max_depth = (uint32_t)maxDepth;
+    d.tile_size = 16;   // integrator.cpp:237
+    d.rank = (uint32_t)rank; d.world = (uint32_t)world; d.seed = (uint32_t)seed;
+
+    const size_t nPix = (size_t)d.camera.xres * d.camera.yres;
+    std::vector<float> rgbw(4 * nPix, 0.f);
+    if (b200rt_render(accel->deviceScene(), &d, rgbw.data(), &lastStats, nullptr)) {
+        Error("b200wavefront: %s", b200rt_last_error());
+        return;
+    }
+    // Film: pixel = sum / weight (film.cpp:266-305); SetImage stores it with filterWeightSum = 1
+    std::unique_ptr<Spectrum[]> img(new Spectrum[nPix]);
+    for (size_t i = 0; i < nPix; ++i) {
+        const float w = rgbw[4 * i + 3];
+        Float rgb[3] = {0, 0, 0};
+        if (w > 0) for (int c = 0; c < 3; ++c) rgb[c] = rgbw[4 * i + c] / w;
+        img[i] = Spectrum::FromRGB(rgb);
+    }
+    film->SetImage(img.get());
+    film->WriteImage();
+}
+
+B200WavefrontIntegrator *CreateB200WavefrontIntegrator(const ParamSet &params, std::shared_ptr<Sampler> sampler,
+                                                       std::shared_ptr<const Camera> camera) {
+    auto envInt = [](const char *name, int dflt) { const char *e = std::getenv(name); return e ? std::atoi(e) : dflt; };
+    const int maxDepth = params.FindOneInt("maxdepth", 5);
+    const int rank = params.FindOneInt("rank", envInt("RANK", 0));
+    const int world = params.FindOneInt("world", envInt("WORLD_SIZE", 1));
+    const int seed = params.FindOneInt("seed", 0);
+    return new B200WavefrontIntegrator(maxDepth, std::move(camera), std::move(sampler), rank, world, seed);
+}
+
+}  // namespace pbrt

@@ -1,0 +1,49 @@
+// b200integrator.h — `Integrator "b200wavefront"` for Thesis-pbrt-v3: the pbrt-side entry of the wavefront driver.
+//
+// Mirrors the reference's integrator interface for the hot path:
+//   class Integrator { virtual void Render(const Scene &scene) = 0; }            src/core/integrator.h:52-58
+//   SamplerIntegrator::Render (tile / pixel / sample loops)                       src/core/integrator.cpp:230-360
+//   PathIntegrator(maxDepth, camera, sampler, pixelBounds, ...) + CreatePathIntegrator   src/integrators/path.cpp:206-240
+// and hands the frame to b200rt_render (include/b200rt_wavefront.h).  Everything it needs from the scene is read
+// through pbrt's PUBLIC interfaces (Camera::GenerateRay, Light::Sample_Li, Material::ComputeScatteringFunctions +
+// BSDF::f, Film::SetImage / WriteImage): no private member of the reference is touched here.
+//
+// The branch a maintainer adds to RenderOptions::MakeIntegrator (api.cpp:1895-1945, before the final `else`):
+//     else if (IntegratorName == "b200wavefront")
+//         integrator = CreateB200WavefrontIntegrator(IntegratorParams, sampler, camera);
+#ifndef B200RT_HOST_B200INTEGRATOR_H
+#define B200RT_HOST_B200INTEGRATOR_H
+
+#include <memory>
+
+#include "pbrt.h"
+#include "integrator.h"
+#include "b200rt_wavefront.h"
+
+namespace pbrt {
+
+class B200WavefrontIntegrator : public Integrator {
+  public:
+    // rank/world: this process renders the 16x16 tiles t with t % world == rank (integrator.cpp:237-239 tile grid);
+    // the other tiles' pixels stay black in this process's film (the host application gathers them).
+    B200WavefrontIntegrator(int maxDepth, std::shared_ptr<const Camera> camera, std::shared_ptr<Sampler> sampler,
+                            int rank = 0, int world = 1, int seed = 0)
+        : maxDepth(maxDepth), camera(std::move(camera)), sampler(std::move(sampler)), rank(rank), world(world), seed(seed) {}
+    void Render(const Scene &scene);
+    const b200rt_render_stats &stats() const { return lastStats; }
+
+  private:
+    const int maxDepth;
+    std::shared_ptr<const Camera> camera;
+    std::shared_ptr<Sampler> sampler;
+    const int rank, world, seed;
+    b200rt_render_stats lastStats{};
+};
+
+// Parameters: "integer maxdepth" (path.cpp:209, default 5), "integer rank" / "integer world" (default: the RANK /
+// WORLD_SIZE environment of a torchrun-style launch, else 0 / 1), "integer seed".
+B200WavefrontIntegrator *CreateB200WavefrontIntegrator(const ParamSet &params, std::shared_ptr<Sampler> sampler,
+                                                       std::shared_ptr<const Camera> camera);
+
+}  // namespace pbrt
+#endif
