@@ -134,6 +134,20 @@ int b200rt_intersect_closest_counted(b200rt_scene *scene, const b200rt_ray *rays
                                      b200rt_hit *hits, b200rt_counters *counters, void *stream);
 int b200rt_intersect_any_counted(b200rt_scene *scene, const b200rt_ray *rays, uint64_t n,
                                  uint8_t *occluded, b200rt_counters *counters, void *stream);
+/* Per-RAY traversal statistics = the reference's Ray::stats after the call (GeneralStats, src/core/geometry.h:1078-1173;
+ * incremented at bvh.cpp:370,379 / kdtreeaccel.cpp:404,414 / rbsp.cpp / BSP.cpp:49,79 / primitive.cpp:118-126).  The
+ * thesis sums them per pixel into its traversal heat maps (integrator.cpp:328, film.cpp:170-264). */
+typedef struct {
+    uint32_t prim_tests;      /* primitiveIntersections (closest) / primitiveIntersectionsP (any) */
+    uint32_t interior_visits; /* bvh-/kd-/bspTreeNodeTraversals(P): interior nodes processed */
+    uint32_t leaf_visits;     /* leafNodeTraversals(P) */
+    uint32_t nodes_fetched;   /* node records read (not counted by the reference; feeds the roofline's N_fetch) */
+} b200rt_ray_stats;
+/* Instrumented Intersect / IntersectP that also return per_ray[i] (HOST or DEVICE buffer of n records). */
+int b200rt_intersect_closest_stats(b200rt_scene *scene, const b200rt_ray *rays, uint64_t n, b200rt_hit *hits,
+                                   b200rt_ray_stats *per_ray, void *stream);
+int b200rt_intersect_any_stats(b200rt_scene *scene, const b200rt_ray *rays, uint64_t n, uint8_t *occluded,
+                               b200rt_ray_stats *per_ray, void *stream);
 /* Number of kernel launches issued by this library since b200rt_init (bench.py's gpu_launches). */
 uint64_t b200rt_launch_count(void);
 

@@ -68,6 +68,24 @@ int b200rt_render_tiles(const b200rt_render_desc *desc, uint32_t *n_tiles, uint6
 int b200rt_render(b200rt_scene *scene, const b200rt_render_desc *desc, float *film, b200rt_render_stats *stats,
                   void *stream);
 
+/* b200rt_render + the thesis's per-pixel traversal statistics: every ray of a path (camera, bounce and shadow rays)
+ * adds its Ray::stats to the path's pixel, as PathIntegrator::Li does with `r.stats += ray.stats`
+ * (src/integrators/path.cpp:92-200, light.cpp:62) before SamplerIntegrator::Render adds the sample's total to the
+ * film pixel (integrator.cpp:327-328); Film::WriteGeneralStats (film.cpp:170-264) dumps one matrix per counter.
+ * heat: HOST or DEVICE buffer of B200RT_HEAT_PLANES planes of xres*yres uint32, accumulated into (+=).
+ * Runs the instrumented (one-ray-per-thread) traversal kernels, so it is an analysis mode, not the fast path. */
+#define B200RT_HEAT_PLANES 6
+enum {
+    B200RT_HEAT_PRIM = 0,   /* primitiveIntersections                                       */
+    B200RT_HEAT_PRIM_P = 1, /* primitiveIntersectionsP                                      */
+    B200RT_HEAT_NODE = 2,   /* bvh- / kd- / bspTreeNodeTraversals (interior nodes, closest) */
+    B200RT_HEAT_NODE_P = 3, /* ... of shadow rays                                           */
+    B200RT_HEAT_LEAF = 4,   /* leafNodeTraversals                                           */
+    B200RT_HEAT_LEAF_P = 5  /* leafNodeTraversalsP                                          */
+};
+int b200rt_render_heatmaps(b200rt_scene *scene, const b200rt_render_desc *desc, float *film, uint32_t *heat,
+                           b200rt_render_stats *stats, void *stream);
+
 /* Dumps the ray queues of the LAST b200rt_render batch of this scene (the real closest/shadow mix)
  * for kernel benchmarking: queue q = 2*depth (closest) or 2*depth+1 (shadow).  Pass rays = NULL to
  * query the count.  rays: HOST or DEVICE buffer of *n b200rt_ray. */

@@ -8,11 +8,11 @@
 #define private public
 #define protected public
 #include "core/primitive.h"
+#include "core/film.h"
 #undef private
 #undef protected
 #include "core/api.h"
 #include "core/camera.h"
-#include "core/film.h"
 #include "core/imageio.h"
 #include "core/light.h"
 #include "core/parallel.h"
@@ -75,7 +75,7 @@ struct CountingAggregate : public Aggregate {
 extern "C" int ref_render(ref_scene *s, const char *accel_kind, const float *cam, int xres, int yres, int spp,
                           int maxdepth, const float *light_pos, const float *light_I, const float *kd,
                           const char *sampler_name, int n_threads, const char *tmp_prefix, float *out_rgb,
-                          uint64_t *n_closest, uint64_t *n_shadow) {
+                          uint64_t *n_closest, uint64_t *n_shadow, uint32_t *out_heat /* nullable: 6 planes of yres*xres */) {
     PbrtOptions.quiet = true;
     PbrtOptions.nThreads = n_threads;
     // material: Material "matte" "rgb Kd" (materials/matte.cpp:44-60), sigma 0
@@ -133,6 +133,21 @@ extern "C" int ref_render(ref_scene *s, const char *accel_kind, const float *cam
         std::lock_guard<std::mutex> l(g_imgMutex);
         if (g_lastRes.x != xres || g_lastRes.y != yres) return 2;
         std::memcpy(out_rgb, g_lastImage.data(), sizeof(float) * g_lastImage.size());
+    }
+    if (out_heat) {
+        // the thesis's per-pixel GeneralStats (integrator.cpp:327-328), the matrices Film::WriteGeneralStats dumps
+        // (film.cpp:170-264): planes = primitiveIntersections, ...P, {bvh+kd+bsp}TreeNodeTraversals, ...P,
+        // leafNodeTraversals, ...P
+        const size_t npx = (size_t)xres * yres;
+        for (size_t i = 0; i < npx; ++i) {
+            const GeneralStats &g = film->pixels[i].stats;
+            out_heat[0 * npx + i] = (uint32_t)g.primitiveIntersections;
+            out_heat[1 * npx + i] = (uint32_t)g.primitiveIntersectionsP;
+            out_heat[2 * npx + i] = (uint32_t)(g.bvhTreeNodeTraversals + g.kdTreeNodeTraversals + g.bspTreeNodeTraversals);
+            out_heat[3 * npx + i] = (uint32_t)(g.bvhTreeNodeTraversalsP + g.kdTreeNodeTraversalsP + g.bspTreeNodeTraversalsP);
+            out_heat[4 * npx + i] = (uint32_t)g.leafNodeTraversals;
+            out_heat[5 * npx + i] = (uint32_t)g.leafNodeTraversalsP;
+        }
     }
     if (n_closest) *n_closest = counting->nClosest.load();
     if (n_shadow) *n_shadow = counting->nAny.load();

@@ -43,8 +43,10 @@ def main():
         tv = sc["tri_verts"]
         S = rb.RefScene(tv.reshape(-1, 3), np.arange(3 * len(tv), dtype=np.int32).reshape(-1, 3))
         eye, look, up, fov = lookat_of(c["scene"])
-        img, nc, ns = rb.render(S, "bvh", eye, look, up, fov, c["res"], c["res"], c["spp"], c["maxdepth"], sc["light"],
-                                c["I"], c["kd"], sampler="random", n_threads=0)
+        img, nc, ns, heat = rb.render(S, "bvh", eye, look, up, fov, c["res"], c["res"], c["spp"], c["maxdepth"], sc["light"],
+                                      c["I"], c["kd"], sampler="random", n_threads=0, heat=True)
+        if key == "killeroo":   # the thesis's per-pixel traversal statistics for the same frame (BVH)
+            out[key + "_heat"] = heat
         print(key, "mean", img.mean(), "closest", nc, "shadow", ns)
         out[key + "_rgb"] = img
         out[key + "_rays"] = np.array([nc, ns], np.uint64)

@@ -39,6 +39,18 @@ def test_golden_small(gpu, name):
     assert np.array_equal(occ2, g["occluded"])
     assert cp["prim_tests"] == int(g["cntp_tests"].sum())
     assert cp["leaf_visits"] == int(g["cntp_leaf"].sum())
+    # PER-RAY statistics = the reference's Ray::stats after each call, ray by ray (what the thesis's heat maps sum)
+    h3, rs = acc.IntersectStats(g["rays"])
+    _same_hits(h3, hits)
+    assert np.array_equal(rs["prim_tests"], g["cnt_tests"])
+    assert np.array_equal(rs["interior_visits"], g["cnt_interior"])
+    assert np.array_equal(rs["leaf_visits"], g["cnt_leaf"])
+    assert int(rs["nodes_fetched"].sum()) == c["nodes_fetched"]
+    o3, rsp = acc.IntersectStats(g["rays"], any_hit=True)
+    assert np.array_equal(o3, g["occluded"])
+    assert np.array_equal(rsp["prim_tests"], g["cntp_tests"])
+    assert np.array_equal(rsp["interior_visits"], g["cntp_interior"])
+    assert np.array_equal(rsp["leaf_visits"], g["cntp_leaf"])
 
 
 @pytest.mark.parametrize("name", FEET)

@@ -201,3 +201,28 @@ def test_image_matches_the_references_own_render(gpu, case, scene_fn):
     nc, ns = (int(x) for x in g[case + "_rays"])
     assert abs(st["closest_rays"] / nc - 1) < 0.01, (st["closest_rays"], nc)
     assert abs(st["shadow_rays"] / ns - 1) < 0.01, (st["shadow_rays"], ns)
+
+
+def test_heatmaps_match_the_references_per_pixel_statistics(gpu):
+    """The thesis's per-pixel traversal statistics (integrator.cpp:327-328 `pixel.stats += ray.stats`, dumped by
+    Film::WriteGeneralStats, film.cpp:170-264) for the killeroo-simple frame of tests/golden/ref_render.npz, from the
+    reference's own render with its own BVHAccel.  Per-RAY statistics are bit-exact (tests/test_gpu_parity.py); here
+    the rays themselves differ (sample sequences), so the maps agree statistically: each plane's total within 1.5 %,
+    8x8-block maps within 4 % relative RMSE."""
+    from conftest import load_golden
+    from b200rt import scenes, wavefront as wf
+    g = load_golden("ref_render.npz")
+    res, spp, maxdepth = (int(x) for x in g["killeroo_params"])
+    sc = scenes.killeroo_simple(xres=res, yres=res)
+    acc = gpu.MakeAccelerator("bvh", sc["tri_verts"])
+    integ = gpu.WavefrontPathIntegrator(sc["camera"], spp=spp, maxdepth=maxdepth, light_pos=sc["light"],
+                                        light_I=g["killeroo_I"], kd=g["killeroo_kd"], seed=9)
+    film, heat, st = wf.render_heatmaps(integ, acc)
+    film2, st2 = integ.Render(acc)
+    assert np.array_equal(film, film2)          # the instrumented kernels give the same image bit for bit
+    ref = g["killeroo_heat"].astype(np.float64)
+    for k, name in enumerate(wf.HEAT_PLANES):
+        a, b = heat[k].astype(np.float64), ref[k]
+        assert abs(a.sum() / b.sum() - 1) < 0.015, (name, a.sum(), b.sum())
+        ab, bb = _blocks(a[..., None], 8), _blocks(b[..., None], 8)
+        assert np.sqrt(((ab - bb) ** 2).mean()) / bb.mean() < 0.04, name

@@ -7,6 +7,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 MISS = 0xFFFFFFFF
 RAY_DTYPE = np.dtype([("o", "<f4", 3), ("tMax", "<f4"), ("d", "<f4", 3), ("time", "<f4")])
 HIT_DTYPE = np.dtype([("prim", "<u4"), ("t", "<f4"), ("b0", "<f4"), ("b1", "<f4"), ("b2", "<f4")])
+RAY_STATS_DTYPE = np.dtype([("prim_tests", "<u4"), ("interior_visits", "<u4"), ("leaf_visits", "<u4"), ("nodes_fetched", "<u4")])
 COUNTERS_FIELDS = ["rays", "nodes_fetched", "nodes_passed", "leaf_visits", "prim_tests", "index_reads"]
 KINDS = {"bvh": 0, "kdtree": 1, "rbsp": 2, "rbspkd": 3, "bsp": 4, "bspkd": 5}
 ERRORS = {1: "EINVAL", 2: "ENODEVICE", 3: "ECUDA", 4: "EUNSUPPORTED", 5: "ENOMEM"}
@@ -60,6 +61,8 @@ def lib():
         L.b200rt_intersect_any.argtypes = [vp, vp, u64, vp, vp]
         L.b200rt_intersect_closest_counted.argtypes = [vp, vp, u64, vp, C.POINTER(CountersStruct), vp]
         L.b200rt_intersect_any_counted.argtypes = [vp, vp, u64, vp, C.POINTER(CountersStruct), vp]
+        L.b200rt_intersect_closest_stats.argtypes = [vp, vp, u64, vp, vp, vp]
+        L.b200rt_intersect_any_stats.argtypes = [vp, vp, u64, vp, vp, vp]
         L.b200rt_build_bvh.argtypes = [vp, u32, i32, i32, i32, C.POINTER(vp), C.POINTER(u32), C.POINTER(vp)]
         L.b200rt_build_kdtree.argtypes = [vp, u32, i32, i32, C.c_float, i32, i32, C.POINTER(vp), C.POINTER(u32),
                                           C.POINTER(vp), C.POINTER(u32), C.POINTER(C.c_float * 6)]
@@ -184,6 +187,19 @@ class B200Accel:
             return hits, {f: int(getattr(c, f)) for f in COUNTERS_FIELDS}
         _check(lib().b200rt_intersect_closest(self._h, _p(rays), len(rays), _p(hits), stream))
         return hits
+
+    def IntersectStats(self, rays, any_hit=False, stream=None):
+        """Instrumented Intersect / IntersectP: (hits or occluded, per-ray RAY_STATS_DTYPE) — the reference's
+        Ray::stats after each call (src/core/geometry.h:1078-1173)."""
+        rays = np.ascontiguousarray(rays, np.float32).reshape(-1, 8)
+        st = np.zeros(len(rays), RAY_STATS_DTYPE)
+        if any_hit:
+            out = np.zeros(len(rays), np.uint8)
+            _check(lib().b200rt_intersect_any_stats(self._h, _p(rays), len(rays), _p(out), _p(st), stream))
+        else:
+            out = np.zeros(len(rays), HIT_DTYPE)
+            _check(lib().b200rt_intersect_closest_stats(self._h, _p(rays), len(rays), _p(out), _p(st), stream))
+        return out, st
 
     def IntersectP(self, rays, counters=False, stream=None):
         rays = np.ascontiguousarray(rays, np.float32).reshape(-1, 8)

@@ -31,6 +31,7 @@ def _lib():
     L = api.lib()
     if not _bound:
         L.b200rt_render.argtypes = [C.c_void_p, C.POINTER(RenderDesc), C.c_void_p, C.POINTER(RenderStats), C.c_void_p]
+        L.b200rt_render_heatmaps.argtypes = [C.c_void_p, C.POINTER(RenderDesc), C.c_void_p, C.c_void_p, C.POINTER(RenderStats), C.c_void_p]
         L.b200rt_render_tiles.argtypes = [C.POINTER(RenderDesc), C.POINTER(C.c_uint32), C.POINTER(C.c_uint64)]
         L.b200rt_render_keep_queues.argtypes = [C.c_void_p, C.c_int]
         L.b200rt_render_queue.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.POINTER(C.c_uint64)]
@@ -76,6 +77,21 @@ class WavefrontPathIntegrator:
         film = np.zeros(self.shape, np.float32)
         stats = self.render_ptr(accel, film.ctypes.data_as(C.c_void_p), stream)
         return film, stats
+
+
+HEAT_PLANES = ("primitiveIntersections", "primitiveIntersectionsP", "treeNodeTraversals", "treeNodeTraversalsP",
+               "leafNodeTraversals", "leafNodeTraversalsP")
+
+
+def render_heatmaps(integ, accel, stream=None):
+    """Render + the thesis's per-pixel traversal statistics (Film::WriteGeneralStats, reference
+    src/core/film.cpp:170-264): returns (film, heat (6, yres, xres) uint32 in HEAT_PLANES order, stats)."""
+    film = np.zeros(integ.shape, np.float32)
+    heat = np.zeros((len(HEAT_PLANES), integ.shape[0], integ.shape[1]), np.uint32)
+    st = RenderStats()
+    api._check(_lib().b200rt_render_heatmaps(accel._h, C.byref(integ.desc), film.ctypes.data_as(C.c_void_p),
+                                             heat.ctypes.data_as(C.c_void_p), C.byref(st), stream))
+    return film, heat, {f: getattr(st, f) for f, _ in RenderStats._fields_}
 
 
 def keep_queues(accel, keep=True):

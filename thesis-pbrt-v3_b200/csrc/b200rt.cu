@@ -434,16 +434,16 @@ static bool is_device_ptr(const void *p) {
 
 template <bool ANY, bool COUNT>
 static void launch_kind(const b200rt_scene *s, const float4 *rays, uint64_t n, const uint32_t *n_dev, b200rt_hit *hits,
-                        uint8_t *occ, Counters *cnt, cudaStream_t st) {
+                        uint8_t *occ, Counters *cnt, cudaStream_t st, uint4 *per_ray = nullptr) {
     const uint64_t blocks64 = (n + B200RT_BLOCK - 1) / B200RT_BLOCK;
     const unsigned blocks = (unsigned)std::min<uint64_t>(blocks64, (uint64_t)g_sm_count * 64);
     switch (s->kind) {
-        case B200RT_BVH: trace_kernel<B200RT_BVH, ANY, COUNT><<<blocks, B200RT_BLOCK, 0, st>>>(s->bvh, s->bsp, rays, n, n_dev, hits, occ, cnt); break;
-        case B200RT_KDTREE: trace_kernel<B200RT_KDTREE, ANY, COUNT><<<blocks, B200RT_BLOCK, 0, st>>>(s->bvh, s->bsp, rays, n, n_dev, hits, occ, cnt); break;
-        case B200RT_RBSP: trace_kernel<B200RT_RBSP, ANY, COUNT><<<blocks, B200RT_BLOCK, 0, st>>>(s->bvh, s->bsp, rays, n, n_dev, hits, occ, cnt); break;
-        case B200RT_RBSPKD: trace_kernel<B200RT_RBSPKD, ANY, COUNT><<<blocks, B200RT_BLOCK, 0, st>>>(s->bvh, s->bsp, rays, n, n_dev, hits, occ, cnt); break;
-        case B200RT_BSP: trace_kernel<B200RT_BSP, ANY, COUNT><<<blocks, B200RT_BLOCK, 0, st>>>(s->bvh, s->bsp, rays, n, n_dev, hits, occ, cnt); break;
-        default: trace_kernel<B200RT_BSPKD, ANY, COUNT><<<blocks, B200RT_BLOCK, 0, st>>>(s->bvh, s->bsp, rays, n, n_dev, hits, occ, cnt); break;
+        case B200RT_BVH: trace_kernel<B200RT_BVH, ANY, COUNT><<<blocks, B200RT_BLOCK, 0, st>>>(s->bvh, s->bsp, rays, n, n_dev, hits, occ, cnt, per_ray); break;
+        case B200RT_KDTREE: trace_kernel<B200RT_KDTREE, ANY, COUNT><<<blocks, B200RT_BLOCK, 0, st>>>(s->bvh, s->bsp, rays, n, n_dev, hits, occ, cnt, per_ray); break;
+        case B200RT_RBSP: trace_kernel<B200RT_RBSP, ANY, COUNT><<<blocks, B200RT_BLOCK, 0, st>>>(s->bvh, s->bsp, rays, n, n_dev, hits, occ, cnt, per_ray); break;
+        case B200RT_RBSPKD: trace_kernel<B200RT_RBSPKD, ANY, COUNT><<<blocks, B200RT_BLOCK, 0, st>>>(s->bvh, s->bsp, rays, n, n_dev, hits, occ, cnt, per_ray); break;
+        case B200RT_BSP: trace_kernel<B200RT_BSP, ANY, COUNT><<<blocks, B200RT_BLOCK, 0, st>>>(s->bvh, s->bsp, rays, n, n_dev, hits, occ, cnt, per_ray); break;
+        default: trace_kernel<B200RT_BSPKD, ANY, COUNT><<<blocks, B200RT_BLOCK, 0, st>>>(s->bvh, s->bsp, rays, n, n_dev, hits, occ, cnt, per_ray); break;
     }
     g_launches.fetch_add(1);
 }
@@ -461,7 +461,7 @@ __global__ void miss_kernel(const float4 *__restrict__ rays, uint64_t n, b200rt_
 }
 
 int b200rt::launch_trace(const b200rt_scene *s, const float4 *rays, uint64_t n, const uint32_t *n_dev, b200rt_hit *hits,
-                         uint8_t *occ, bool any, Counters *counters, cudaStream_t st) {
+                         uint8_t *occ, bool any, Counters *counters, cudaStream_t st, uint4 *per_ray) {
     if (n == 0) return B200RT_OK;
     if (s->empty) {
         miss_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(rays, n, any ? nullptr : hits, any ? occ : nullptr);
@@ -508,10 +508,10 @@ int b200rt::launch_trace(const b200rt_scene *s, const float4 *rays, uint64_t n, 
             g_launches.fetch_add(1);
         }
     } else if (any) {
-        if (counters) launch_kind<true, true>(s, rays, n, n_dev, nullptr, occ, counters, st);
+        if (counters) launch_kind<true, true>(s, rays, n, n_dev, nullptr, occ, counters, st, per_ray);
         else launch_kind<true, false>(s, rays, n, n_dev, nullptr, occ, nullptr, st);
     } else {
-        if (counters) launch_kind<false, true>(s, rays, n, n_dev, hits, nullptr, counters, st);
+        if (counters) launch_kind<false, true>(s, rays, n, n_dev, hits, nullptr, counters, st, per_ray);
         else launch_kind<false, false>(s, rays, n, n_dev, hits, nullptr, nullptr, st);
     }
     CU(cudaGetLastError());
@@ -562,8 +562,18 @@ static int run_pipelined(b200rt_scene *s, const b200rt_ray *rays, uint64_t n, vo
 }
 
 static int run(b200rt_scene *s, const b200rt_ray *rays, uint64_t n, b200rt_hit *hits, uint8_t *occ, bool any,
-               b200rt_counters *counters, void *stream) {
+               b200rt_counters *counters, void *stream, b200rt_ray_stats *per_ray = nullptr) {
     if (!s) return fail(B200RT_EINVAL, "null scene");
+    b200rt_counters dummy;
+    if (per_ray && !counters) counters = &dummy;  // per-ray stats come from the instrumented kernels
+    uint4 *d_per_ray = nullptr;
+    bool per_ray_tmp = false;
+    if (per_ray && n) {
+        if (is_device_ptr(per_ray)) d_per_ray = (uint4 *)per_ray;
+        else { CU(cudaMalloc(&d_per_ray, n * sizeof(uint4))); per_ray_tmp = true; }
+        CU(cudaMemsetAsync(d_per_ray, 0, n * sizeof(uint4), (cudaStream_t)stream));
+    }
+    struct Guard { uint4 *p; bool own; ~Guard() { if (own) cudaFree(p); } } guard{d_per_ray, per_ray_tmp};
     if (n == 0) { if (counters) std::memset(counters, 0, sizeof(*counters)); return B200RT_OK; }
     if (!rays || (any ? !occ : !hits)) return fail(B200RT_EINVAL, "null ray/result buffer");
     cudaStream_t st = (cudaStream_t)stream;
@@ -591,10 +601,11 @@ static int run(b200rt_scene *s, const b200rt_ray *rays, uint64_t n, b200rt_hit *
     if (counters) CU(cudaMemsetAsync(s->d_counters, 0, sizeof(Counters), st));
     {
         int rc = launch_trace(s, d_rays, n, nullptr, any ? nullptr : (b200rt_hit *)d_out, any ? (uint8_t *)d_out : nullptr, any,
-                              counters ? s->d_counters : nullptr, st);
+                              counters ? s->d_counters : nullptr, st, s->empty ? nullptr : d_per_ray);
         if (rc) return rc;
     }
     CU(cudaGetLastError());
+    if (per_ray_tmp) CU(cudaMemcpyAsync(per_ray, d_per_ray, n * sizeof(uint4), cudaMemcpyDeviceToHost, st));
     if (!out_dev) CU(cudaMemcpyAsync((void *)outp, d_out, n * out_elem, cudaMemcpyDeviceToHost, st));
     if (counters) {
         Counters c;
@@ -623,4 +634,15 @@ extern "C" int b200rt_intersect_any_counted(b200rt_scene *s, const b200rt_ray *r
                                             b200rt_counters *c, void *stream) {
     if (!c) return fail(B200RT_EINVAL, "null counters");
     return run(s, rays, n, nullptr, occ, true, c, stream);
+}
+static_assert(sizeof(b200rt_ray_stats) == sizeof(uint4), "b200rt_ray_stats is four 32-bit words");
+extern "C" int b200rt_intersect_closest_stats(b200rt_scene *s, const b200rt_ray *rays, uint64_t n, b200rt_hit *hits,
+                                              b200rt_ray_stats *per_ray, void *stream) {
+    if (!per_ray) return fail(B200RT_EINVAL, "null per-ray stats buffer");
+    return run(s, rays, n, hits, nullptr, false, nullptr, stream, per_ray);
+}
+extern "C" int b200rt_intersect_any_stats(b200rt_scene *s, const b200rt_ray *rays, uint64_t n, uint8_t *occ,
+                                          b200rt_ray_stats *per_ray, void *stream) {
+    if (!per_ray) return fail(B200RT_EINVAL, "null per-ray stats buffer");
+    return run(s, rays, n, nullptr, occ, true, nullptr, stream, per_ray);
 }

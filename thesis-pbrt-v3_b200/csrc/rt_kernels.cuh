@@ -313,7 +313,7 @@ template <int KIND, bool ANY, bool COUNT>
 __global__ void __launch_bounds__(B200RT_BLOCK)
 trace_kernel(const __grid_constant__ BvhView bvh, const __grid_constant__ BspView bsp, const float4 *__restrict__ rays,
              uint64_t n, const uint32_t *__restrict__ n_dev, b200rt_hit *__restrict__ hits,
-             uint8_t *__restrict__ occluded, Counters *counters) {
+             uint8_t *__restrict__ occluded, Counters *counters, uint4 *__restrict__ per_ray = nullptr) {
     LocalCount cnt;
     if (n_dev) { const uint64_t m = *n_dev; n = m < n ? m : n; }
     const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
@@ -325,8 +325,16 @@ trace_kernel(const __grid_constant__ BvhView bvh, const __grid_constant__ BspVie
             HitRec h;
             h.prim = B200RT_MISS; h.t = r.tMax; h.b0 = h.b1 = h.b2 = 0.f;
             bool hit;
+            const LocalCount before = cnt;
             if (KIND == B200RT_BVH) hit = bvh_trace<ANY, COUNT>(bvh, r, h, cnt);
             else hit = bsp_trace<KIND, ANY, COUNT>(bsp, r, h, cnt);
+            if (COUNT && per_ray) {
+                // the reference's per-ray GeneralStats (geometry.h:1078-1173): primitiveIntersections(P),
+                // {bvh,kd,bsp}TreeNodeTraversals(P) (interior nodes only: bvh.cpp:379, kdtreeaccel.cpp:404), leafNodeTraversals(P)
+                const uint32_t leaves = cnt.leaves - before.leaves, passed = cnt.passed - before.passed;
+                per_ray[i] = make_uint4(cnt.tests - before.tests, KIND == B200RT_BVH ? passed - leaves : passed, leaves,
+                                        cnt.fetched - before.fetched);
+            }
             if (ANY) occluded[i] = hit ? 1 : 0;
             else {
                 b200rt_hit o;

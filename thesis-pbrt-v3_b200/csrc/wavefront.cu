@@ -262,8 +262,26 @@ __global__ void k_film(const __grid_constant__ WfParams P, uint64_t batchStart, 
     film[(size_t)y * P.cam.xres + x] = f;
 }
 
+// Per-pixel traversal statistics (b200rt_render_heatmaps): the rays of queue entries [0, *nQ) add their per-ray
+// stats to the pixel of their path.  plane = 0 for closest-hit queues, 1 for shadow queues.
+__global__ void k_heat(const __grid_constant__ WfParams P, uint64_t batchStart, const uint32_t *__restrict__ nQ,
+                       const uint32_t *__restrict__ qPath, const uint4 *__restrict__ perRay, uint32_t *heat, uint32_t plane) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= *nQ) return;
+    uint32_t x, y, s;
+    path_pixel(P.tl, batchStart + qPath[i], x, y, s);
+    const size_t npx = (size_t)P.cam.xres * P.cam.yres, pix = (size_t)y * P.cam.xres + x;
+    const uint4 v = perRay[i];
+    if (v.x) atomicAdd(heat + (B200RT_HEAT_PRIM + plane) * npx + pix, v.x);
+    if (v.y) atomicAdd(heat + (B200RT_HEAT_NODE + plane) * npx + pix, v.y);
+    if (v.z) atomicAdd(heat + (B200RT_HEAT_LEAF + plane) * npx + pix, v.z);
+}
+
 struct Workspace {
     size_t cap = 0;
+    uint4 *perRay = nullptr;   // heat-map mode only
+    uint32_t *heat = nullptr;
+    size_t heat_px = 0;
     float4 *rays[2] = {nullptr, nullptr}, *shRays = nullptr, *shContrib = nullptr, *beta = nullptr, *L = nullptr;
     uint32_t *qPath[2] = {nullptr, nullptr}, *shPath = nullptr, *counts = nullptr;
     b200rt_hit *hits = nullptr;
@@ -280,7 +298,7 @@ struct Workspace {
 void free_ws(Workspace *w) {
     for (int k = 0; k < 2; ++k) { cudaFree(w->rays[k]); cudaFree(w->qPath[k]); }
     cudaFree(w->shRays); cudaFree(w->shContrib); cudaFree(w->beta); cudaFree(w->L); cudaFree(w->shPath);
-    cudaFree(w->counts); cudaFree(w->hits); cudaFree(w->occ); cudaFree(w->film);
+    cudaFree(w->counts); cudaFree(w->hits); cudaFree(w->occ); cudaFree(w->film); cudaFree(w->perRay); cudaFree(w->heat);
     for (float4 *p : w->kept) cudaFree(p);
     *w = Workspace();
 }
@@ -351,8 +369,19 @@ extern "C" int b200rt_render_queue(b200rt_scene *s, uint32_t q, b200rt_ray *rays
     return B200RT_OK;
 }
 
+static int render_impl(b200rt_scene *s, const b200rt_render_desc *d, float *film, uint32_t *heat, b200rt_render_stats *stats,
+                       void *stream);
 extern "C" int b200rt_render(b200rt_scene *s, const b200rt_render_desc *d, float *film, b200rt_render_stats *stats,
                              void *stream) {
+    return render_impl(s, d, film, nullptr, stats, stream);
+}
+extern "C" int b200rt_render_heatmaps(b200rt_scene *s, const b200rt_render_desc *d, float *film, uint32_t *heat,
+                                      b200rt_render_stats *stats, void *stream) {
+    if (!heat) return set_error(B200RT_EINVAL, "null heat-map buffer");
+    return render_impl(s, d, film, heat, stats, stream);
+}
+static int render_impl(b200rt_scene *s, const b200rt_render_desc *d, float *film, uint32_t *heat, b200rt_render_stats *stats,
+                       void *stream) {
     if (!s || !d || !film) return set_error(B200RT_EINVAL, "null argument");
     WfParams P;
     std::memset(&P, 0, sizeof(P));
@@ -393,6 +422,19 @@ extern "C" int b200rt_render(b200rt_scene *s, const b200rt_render_desc *d, float
         WCU(cudaMemcpyAsync(w->film, film, npx * 16, cudaMemcpyHostToDevice, st));
         d_film = w->film;
     }
+    uint32_t *d_heat = heat;
+    bool heat_dev = true;
+    if (heat) {
+        if (!w->perRay) WCU(cudaMalloc(&w->perRay, w->cap * sizeof(uint4)));
+        heat_dev = cudaPointerGetAttributes(&pa, heat) == cudaSuccess &&
+                   (pa.type == cudaMemoryTypeDevice || pa.type == cudaMemoryTypeManaged);
+        cudaGetLastError();
+        if (!heat_dev) {
+            if (w->heat_px < npx) { cudaFree(w->heat); w->heat = nullptr; WCU(cudaMalloc(&w->heat, npx * 4 * B200RT_HEAT_PLANES)); w->heat_px = npx; }
+            WCU(cudaMemcpyAsync(w->heat, heat, npx * 4 * B200RT_HEAT_PLANES, cudaMemcpyHostToDevice, st));
+            d_heat = w->heat;
+        }
+    }
     if (w->keep) {
         const size_t nq = 2 * (size_t)(d->max_depth + 1);
         if (w->kept.size() != nq || w->keptCap < cap) {
@@ -423,9 +465,14 @@ extern "C" int b200rt_render(b200rt_scene *s, const b200rt_render_desc *d, float
         for (uint32_t depth = 0; depth <= d->max_depth; ++depth) {
             if (w->keep) WCU(cudaMemcpyAsync(w->kept[2 * depth], w->rays[cur], (size_t)nSlots * 32, cudaMemcpyDeviceToDevice, st));
             cudaEvent_t a = ev();
-            rc = launch_trace(s, w->rays[cur], nSlots, w->counts + 2 * depth, w->hits, nullptr, false, nullptr, st);
+            rc = launch_trace(s, w->rays[cur], nSlots, w->counts + 2 * depth, w->hits, nullptr, false,
+                              heat ? s->d_counters : nullptr, st, heat ? w->perRay : nullptr);
             if (rc) return rc;
             spans.push_back({a, ev(), false});
+            if (heat) {
+                k_heat<<<gridSlots, TB, 0, st>>>(P, start, w->counts + 2 * depth, w->qPath[cur], w->perRay, d_heat, 0u);
+                g_launches.fetch_add(1);
+            }
             if (depth == d->max_depth) break;  // path.cpp:110: the last intersection is found, then the path ends
             k_shade<<<gridSlots, TB, 0, st>>>(P, depth, start, w->counts + 2 * depth, w->rays[cur], w->qPath[cur], w->hits,
                                               s->d_prim_tris, w->beta, w->rays[cur ^ 1], w->qPath[cur ^ 1],
@@ -434,9 +481,14 @@ extern "C" int b200rt_render(b200rt_scene *s, const b200rt_render_desc *d, float
             g_launches.fetch_add(1);
             if (w->keep) WCU(cudaMemcpyAsync(w->kept[2 * depth + 1], w->shRays, (size_t)nSlots * 32, cudaMemcpyDeviceToDevice, st));
             a = ev();
-            rc = launch_trace(s, w->shRays, nSlots, w->counts + 2 * depth + 1, nullptr, w->occ, true, nullptr, st);
+            rc = launch_trace(s, w->shRays, nSlots, w->counts + 2 * depth + 1, nullptr, w->occ, true,
+                              heat ? s->d_counters : nullptr, st, heat ? w->perRay : nullptr);
             if (rc) return rc;
             spans.push_back({a, ev(), true});
+            if (heat) {
+                k_heat<<<gridSlots, TB, 0, st>>>(P, start, w->counts + 2 * depth + 1, w->shPath, w->perRay, d_heat, 1u);
+                g_launches.fetch_add(1);
+            }
             k_shadow_resolve<<<gridSlots, TB, 0, st>>>(w->counts + 2 * depth + 1, w->occ, w->shPath, w->shContrib, w->L);
             g_launches.fetch_add(1);
             cur ^= 1;
@@ -457,6 +509,7 @@ extern "C" int b200rt_render(b200rt_scene *s, const b200rt_render_desc *d, float
         }
     }
     if (!film_dev) WCU(cudaMemcpyAsync(film, d_film, npx * 16, cudaMemcpyDeviceToHost, st));
+    if (heat && !heat_dev) WCU(cudaMemcpyAsync(heat, d_heat, npx * 4 * B200RT_HEAT_PLANES, cudaMemcpyDeviceToHost, st));
     cudaEvent_t t1 = ev();
     WCU(cudaStreamSynchronize(st));
     WCU(cudaGetLastError());
