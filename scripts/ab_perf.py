@@ -77,7 +77,12 @@ def main():
             if name == "baseline":
                 ref_out[q] = out.clone()
             else:
-                assert torch.equal(out, ref_out[q]), "MISMATCH vs baseline kernel on queue %d (thresh %s)" % (q, t)
+                if os.environ.get("B200RT_AB_ALLOW_MISMATCH"):
+                    bad = int((out != ref_out[q]).view(-1, 5 if not anyq else 1).any(1).sum())
+                    if bad:
+                        print("   queue %d: %d of %d results differ from the baseline kernel (%s)" % (q, bad, n, t))
+                else:
+                    assert torch.equal(out, ref_out[q]), "MISMATCH vs baseline kernel on queue %d (thresh %s)" % (q, t)
             if q < 100:
                 if anyq: tot_a += ms
                 else: tot_c += ms

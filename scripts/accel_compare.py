@@ -1,0 +1,119 @@
+"""BASELINE config 4 (scenes/killeroo-feet + scripts/run_rbsps.sh of the reference): the thesis's accelerator
+comparison — BVH vs kd-tree vs RBSP with 3/7/9/13 directions (+ RBSPKd, BSPPaper) ON THE SAME RAYS — on the B200.
+
+    python scripts/accel_compare.py --build     # HERE (needs /root/reference): reference builders -> oracle/_ref/feet_trees.npz
+    python scripts/accel_compare.py             # on the GPU box: Mrays/s + the thesis's per-ray statistics per accelerator
+
+The tree file is git-ignored (oracle/_ref/) but travels to the GPU box with the snapshot.  The full killeroo of the
+scene (33 264 triangles) is used; rays = the crop window's camera rays (1000 x 2000 px of the 5000^2 film) and the
+diffuse bounce + shadow rays leaving the first hits.  Tuning / reporting aid (test infrastructure: it drives the
+reference's builders through oracle/refbind.py); not the bench contract.
+"""
+import os
+import sys
+import time
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "thesis-pbrt-v3_b200"))
+TREES = os.path.join(ROOT, "oracle", "_ref", "feet_trees.npz")
+CASES = [("bvh", "bvh", {}), ("kdtree", "kdtree", {}), ("rbsp3", "rbsp", {"nbDirections": 3}),
+         ("rbsp7", "rbsp", {"nbDirections": 7}), ("rbsp9", "rbsp", {"nbDirections": 9}),
+         ("rbsp13", "rbsp", {"nbDirections": 13}), ("rbspkd13", "rbspkd", {"nbDirections": 13}),
+         ("bsppaper", "bsppaper", {}), ("bsppaperkd", "bsppaperkd", {})]
+
+
+def build():
+    from oracle import refbind as rb
+    from b200rt import scenes
+    sc = scenes.killeroo_feet()
+    tv = sc["tri_verts"]
+    S = rb.RefScene(tv.reshape(-1, 3), np.arange(3 * len(tv), dtype=np.int32).reshape(-1, 3))
+    out = dict(tri_verts=tv)
+    only = [a for a in sys.argv[1:] if not a.startswith("--")]
+    if os.path.exists(TREES):
+        out.update(dict(np.load(TREES)))
+    for name, kind, ip in CASES:
+        if (only and name not in only) or (not only and name + "_nodes" in out):
+            continue
+        t0 = time.time()
+        acc = rb.RefAccel(S, kind, ip)
+        tb = time.time() - t0
+        ex = acc.export()
+        for k in ("nodes", "indices", "directions", "bounds"):
+            out["%s_%s" % (name, k)] = ex[k]
+        out[name + "_kind"] = np.array(ex["kind"])
+        out[name + "_build_s"] = np.array(tb)
+        print("%-10s reference build %.1f s, %d nodes, %d indices" % (name, tb, len(ex["nodes"]), len(ex["indices"])), flush=True)
+        np.savez(TREES, **out)
+
+
+def timeit(fn, sync, reps=5):
+    fn(); sync()
+    import torch
+    best = 1e9
+    for _ in range(reps):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(); fn(); b.record(); sync()
+        best = min(best, a.elapsed_time(b))
+    return best
+
+
+def run():
+    import torch
+    import b200rt
+    from b200rt import scenes
+    z = np.load(TREES)
+    tv = z["tri_verts"]
+    b200rt.init(0)
+    torch.zeros(1, device="cuda")
+    st = torch.cuda.current_stream().cuda_stream
+    sc = scenes.killeroo_feet()
+    x0, x1, y0, y1 = sc["crop"]
+    cam = scenes.camera_rays(sc["camera"], x0=x0, x1=x1, y0=y0, y1=y1)   # the crop window at the scene's resolution
+    names = [n for n, _, _ in CASES if n + "_nodes" in z.files]
+    ref = None
+    print("killeroo-feet: %d triangles, %d camera rays (crop %s of 5000^2)" % (len(tv), len(cam), (x0, x1, y0, y1)))
+    print("%-10s %9s | %-28s | %-28s | %-28s" % ("accel", "nodes", "camera closest", "bounce closest", "shadow any-hit"))
+    print("%-10s %9s | %8s %8s %9s | %8s %8s %9s | %8s %8s %9s" % (("", "") + ("Mrays/s", "nodes/r", "tests/r") * 3))
+    for name in names:
+        tree = dict(kind=str(z[name + "_kind"]), nodes=z[name + "_nodes"], indices=z[name + "_indices"],
+                    directions=z[name + "_directions"], bounds=z[name + "_bounds"], n_prims=len(tv))
+        acc = b200rt.B200Accel(tree, tv)
+        hits = acc.Intersect(cam)
+        if ref is None:
+            ref = hits
+            m = hits["prim"] != b200rt.MISS
+            rng = np.random.default_rng(3)
+            p = cam[m, 0:3] + hits["t"][m, None] * cam[m, 4:7]
+            v = tv.reshape(-1, 3, 3)[hits["prim"][m]]
+            n = np.cross(v[:, 0] - v[:, 2], v[:, 1] - v[:, 2])
+            n /= np.maximum(np.linalg.norm(n, axis=1, keepdims=True), 1e-30)
+            n = np.where((np.sum(n * -cam[m, 4:7], 1) < 0)[:, None], -n, n)
+            d = rng.normal(size=p.shape)
+            d /= np.linalg.norm(d, axis=1, keepdims=True)
+            d = np.where((np.sum(d * n, 1) < 0)[:, None], -d, d)
+            bounce = np.zeros((len(p), 8), np.float32)
+            bounce[:, 0:3], bounce[:, 4:7], bounce[:, 3] = p + 1e-2 * n, d, np.inf
+            shadow = bounce.copy()   # distant light along the view direction (scene's LightSource "distant")
+            L = sc["light_dir"] / np.linalg.norm(sc["light_dir"])
+            shadow[:, 4:7], shadow[:, 3] = L * 1000.0, 1 - 1e-4
+        else:   # every accelerator answers the same rays identically (hit prim up to exact-t ties, t bit for bit)
+            assert np.array_equal(hits["t"].view(np.uint32), ref["t"].view(np.uint32)), name
+            assert (hits["prim"] != ref["prim"]).mean() < 1e-5, name
+        row = "%-10s %9d |" % (name, len(tree["nodes"]))
+        for rays, anyhit in ((cam, False), (bounce, False), (shadow, True)):
+            dr = torch.from_numpy(rays).cuda()
+            n = len(rays)
+            out = torch.zeros(n * 5, dtype=torch.int32, device="cuda") if not anyhit else torch.zeros(n, dtype=torch.uint8, device="cuda")
+            fn = (lambda: acc.intersect_p_ptr(dr.data_ptr(), n, out.data_ptr(), st)) if anyhit else \
+                 (lambda: acc.intersect_ptr(dr.data_ptr(), n, out.data_ptr(), st))
+            ms = timeit(fn, torch.cuda.synchronize)
+            _, rs = acc.IntersectStats(rays[:: max(1, n // 200000)], any_hit=anyhit)
+            row += " %8.0f %8.2f %9.2f |" % (n / ms / 1e3, (rs["interior_visits"] + rs["leaf_visits"]).mean(), rs["prim_tests"].mean())
+        print(row, flush=True)
+
+
+if __name__ == "__main__":
+    build() if "--build" in sys.argv else run()
