@@ -10,8 +10,9 @@
  * queue, bounce closest-hit queue) -> ... up to maxdepth, with warp-ballot queue compaction.
  *
  * Shading subset (what the config scenes' templates need around the traversal): perspective camera
- * (src/cameras/perspective.cpp), one point light (src/lights/point.cpp), Lambertian "matte" material
- * (src/materials/matte.cpp), box pixel filter, Russian roulette of path.cpp:190-199.  Samples come
+ * (src/cameras/perspective.cpp), one point light (src/lights/point.cpp) OR one sphere area light with multiple
+ * importance sampling (src/lights/diffuse.cpp, Sphere::Sample/Pdf, EstimateDirect's two strategies), Lambertian "matte"
+ * materials with one Kd per primitive (src/materials/matte.cpp), box pixel filter, Russian roulette of path.cpp:190-199.  Samples come
  * from a counter-based hash of (pixel, sample, dimension), so the image does not depend on the
  * execution order, the batch size or the number of GPUs.
  *
@@ -45,7 +46,23 @@ typedef struct {
     uint32_t rank, world; /* this process renders tiles t with t % world == rank */
     uint32_t seed;
     uint32_t max_batch;  /* paths in flight per wavefront (0 = default 1<<22) */
+    /* ---- appended in ABI v4; all-zero = the v3 behaviour (one point light, one Kd for every primitive) ---- */
+    uint32_t light_kind;   /* B200RT_LIGHT_POINT, or B200RT_LIGHT_SPHERE = AreaLightSource "area" on a full `Shape "sphere"`
+                              (lights/diffuse.cpp:68-87 + Sphere::Sample / Pdf, shapes/sphere.cpp:232-305; one-sided),
+                              sampled with multiple importance sampling as EstimateDirect does (integrator.cpp:109-217):
+                              a light sample (shadow any-hit ray) AND a BSDF sample (an extra closest-hit "MIS" ray) per bounce,
+                              plus the emitted radiance seen directly by camera rays (path.cpp:97-107). */
+    float light_radius;    /* sphere radius; light_pos = its centre, light_I = its emitted radiance "L" */
+    uint32_t light_prim;   /* primitive number of that sphere inside the aggregate (scene-desc prim_kind == 1) */
+    /* Materials: NULL = Material "matte" "Kd" = kd for all.  Else n_materials records of 8 floats
+     * (kind, Kd.r, Kd.g, Kd.b, Ks.r, Ks.g, Ks.b, roughness), kind B200RT_MAT_MATTE (materials/matte.cpp, sigma 0),
+     * and one material index per primitive.  HOST pointers, read during the call. */
+    const float *materials;
+    uint32_t n_materials;
+    const uint8_t *prim_material; /* n_prims bytes */
 } b200rt_render_desc;
+enum { B200RT_LIGHT_POINT = 0, B200RT_LIGHT_SPHERE = 1 };
+enum { B200RT_MAT_MATTE = 0 };
 
 typedef struct {
     uint64_t camera_rays;   /* = paths started */
@@ -57,6 +74,7 @@ typedef struct {
     float ms_total;         /* whole call on the stream */
     uint32_t n_tiles;       /* tiles rendered by this rank */
     uint32_t launches_closest, launches_any; /* traversal-kernel launches behind ms_closest / ms_any */
+    uint64_t mis_rays;      /* of closest_rays: the BSDF-sampled MIS rays of EstimateDirect (integrator.cpp:203) */
 } b200rt_render_stats;
 
 /* Number of tiles / pixels rank `rank` of `world` owns for this camera and tile size. */

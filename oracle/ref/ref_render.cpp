@@ -24,6 +24,7 @@
 #include "filters/box.h"
 #include "integrators/path.h"
 #include "lights/point.h"
+#include "lights/diffuse.h"
 #include "materials/matte.h"
 #include "samplers/halton.h"
 #include "samplers/random.h"
@@ -75,7 +76,10 @@ struct CountingAggregate : public Aggregate {
 extern "C" int ref_render(ref_scene *s, const char *accel_kind, const float *cam, int xres, int yres, int spp,
                           int maxdepth, const float *light_pos, const float *light_I, const float *kd,
                           const char *sampler_name, int n_threads, const char *tmp_prefix, float *out_rgb,
-                          uint64_t *n_closest, uint64_t *n_shadow, uint32_t *out_heat /* nullable: 6 planes of yres*xres */) {
+                          uint64_t *n_closest, uint64_t *n_shadow, uint32_t *out_heat /* nullable: 6 planes of yres*xres */,
+                          const float *prim_kd /* nullable: one matte Kd (rgb) per primitive instead of `kd` */,
+                          const float *emitter_L /* nullable: rgb; the scene's LAST primitive (a sphere) becomes
+                                                    AreaLightSource "area" "color L" and replaces the point light */) {
     PbrtOptions.quiet = true;
     PbrtOptions.nThreads = n_threads;
     // material: Material "matte" "rgb Kd" (materials/matte.cpp:44-60), sigma 0
@@ -85,9 +89,31 @@ extern "C" int ref_render(ref_scene *s, const char *accel_kind, const float *cam
     auto matte = std::make_shared<MatteMaterial>(Kd, sigma, nullptr);
     MediumInterface mi;
     std::vector<std::shared_ptr<Primitive>> prims;
-    for (auto &p : s->prims) {
-        auto *gp = static_cast<GeometricPrimitive *>(p.get());
-        prims.push_back(std::make_shared<GeometricPrimitive>(gp->shape, matte, nullptr, mi));
+    std::shared_ptr<AreaLight> area;
+    std::map<std::array<float, 3>, std::shared_ptr<Material>> byKd;   // one MatteMaterial per distinct Kd
+    for (size_t i = 0; i < s->prims.size(); ++i) {
+        auto *gp = static_cast<GeometricPrimitive *>(s->prims[i].get());
+        std::shared_ptr<Material> m = matte;
+        if (prim_kd) {
+            std::array<float, 3> k = {prim_kd[3 * i], prim_kd[3 * i + 1], prim_kd[3 * i + 2]};
+            auto it = byKd.find(k);
+            if (it == byKd.end()) {
+                Float c[3] = {k[0], k[1], k[2]};
+                auto tex = std::make_shared<ConstantTexture<Spectrum>>(Spectrum::FromRGB(c));
+                it = byKd.emplace(k, std::make_shared<MatteMaterial>(tex, sigma, nullptr)).first;
+            }
+            m = it->second;
+        }
+        std::shared_ptr<AreaLight> al;
+        if (emitter_L && i + 1 == s->prims.size()) {
+            // AttributeBegin Material "matte" Kd 0 ; AreaLightSource "area" L ; Shape "sphere" (scenes/killeroo-simple:18-24)
+            Float c[3] = {0, 0, 0}, le[3] = {emitter_L[0], emitter_L[1], emitter_L[2]};
+            auto tex = std::make_shared<ConstantTexture<Spectrum>>(Spectrum::FromRGB(c));
+            m = std::make_shared<MatteMaterial>(tex, sigma, nullptr);
+            area = std::make_shared<DiffuseAreaLight>(*gp->shape->ObjectToWorld, mi, Spectrum::FromRGB(le), 1, gp->shape, false);
+            al = area;
+        }
+        prims.push_back(std::make_shared<GeometricPrimitive>(gp->shape, m, al, mi));
     }
     ParamSet ps;
     std::shared_ptr<Primitive> accel;
@@ -105,7 +131,8 @@ extern "C" int ref_render(ref_scene *s, const char *accel_kind, const float *cam
     Float li[3] = {light_I[0], light_I[1], light_I[2]};
     Transform l2w = Translate(Vector3f(light_pos[0], light_pos[1], light_pos[2]));
     std::vector<std::shared_ptr<Light>> lights;
-    lights.push_back(std::make_shared<PointLight>(l2w, mi, Spectrum::FromRGB(li)));
+    if (area) lights.push_back(area);
+    else lights.push_back(std::make_shared<PointLight>(l2w, mi, Spectrum::FromRGB(li)));
     Scene scene(counting, lights);
 
     // Film "image" + PixelFilter "box" (film.cpp:307-351, filters/box.cpp) — defaults of every thesis template

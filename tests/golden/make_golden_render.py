@@ -19,6 +19,9 @@ CASES = {
     # BASELINE config 1: scenes/killeroo-simple geometry + camera (point light at the sphere light's centre)
     "killeroo": dict(scene="killeroo_simple", res=128, spp=256, maxdepth=5, I=(50000.0,) * 3, kd=(.5, .5, .5)),
     # BASELINE config 2: the sponza stand-in the bench renders
+    # BASELINE config 1 with the scene's own light and Kd's: sphere AreaLightSource L = 2000 (MIS in EstimateDirect),
+    # ground matte (.5 .5 .8), killeroos with the diffuse part of their "plastic" (Kd .4 .2 .2 / .4 .5 .4)
+    "killeroo_area": dict(scene="killeroo_simple", res=128, spp=256, maxdepth=5, I=(2000.0,) * 3, kd=(.5, .5, .5), area=True),
     "sponza": dict(scene="sponza_standin", res=96, spp=256, maxdepth=5, I=(1.0,) * 3, kd=(.5, .5, .5)),
 }
 
@@ -41,10 +44,17 @@ def main():
             continue
         sc = getattr(scenes, c["scene"])(xres=c["res"], yres=c["res"])
         tv = sc["tri_verts"]
-        S = rb.RefScene(tv.reshape(-1, 3), np.arange(3 * len(tv), dtype=np.int32).reshape(-1, 3))
+        extra = {}
+        spheres = None
+        if c.get("area"):
+            sl = sc["sphere_light"]
+            spheres = np.array([list(sl["center"]) + [sl["radius"]]], np.float32)
+            extra = dict(prim_kd=np.concatenate([sc["material_kd"][sc["prim_material"]], np.zeros((1, 3), np.float32)]),
+                         emitter_L=sl["L"])
+        S = rb.RefScene(tv.reshape(-1, 3), np.arange(3 * len(tv), dtype=np.int32).reshape(-1, 3), spheres=spheres)
         eye, look, up, fov = lookat_of(c["scene"])
         img, nc, ns, heat = rb.render(S, "bvh", eye, look, up, fov, c["res"], c["res"], c["spp"], c["maxdepth"], sc["light"],
-                                      c["I"], c["kd"], sampler="random", n_threads=0, heat=True)
+                                      c["I"], c["kd"], sampler="random", n_threads=0, heat=True, **extra)
         if key == "killeroo":   # the thesis's per-pixel traversal statistics for the same frame (BVH)
             out[key + "_heat"] = heat
         print(key, "mean", img.mean(), "closest", nc, "shadow", ns)

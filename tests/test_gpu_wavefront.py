@@ -226,3 +226,41 @@ def test_heatmaps_match_the_references_per_pixel_statistics(gpu):
         assert abs(a.sum() / b.sum() - 1) < 0.015, (name, a.sum(), b.sum())
         ab, bb = _blocks(a[..., None], 8), _blocks(b[..., None], 8)
         assert np.sqrt(((ab - bb) ** 2).mean()) / bb.mean() < 0.04, name
+
+
+def test_area_light_mis_matches_the_references_render(gpu):
+    """BASELINE config 1 with the scene's OWN light: scenes/killeroo-simple's sphere `AreaLightSource "area" L 2000`
+    sampled with multiple importance sampling as EstimateDirect does (light sample -> shadow any-hit ray, BSDF sample
+    -> an extra closest-hit MIS ray, emitted radiance for camera rays) and one matte Kd per primitive, against the
+    reference's own render of the same setup (tests/golden/ref_render.npz `killeroo_area`).  Statistical bar as above;
+    the closest-ray count now includes the MIS rays."""
+    from conftest import load_golden
+    from b200rt import scenes
+    from b200rt.wavefront import film_to_rgb
+    g = load_golden("ref_render.npz")
+    res, spp, maxdepth = (int(x) for x in g["killeroo_area_params"])
+    sc = scenes.killeroo_simple(xres=res, yres=res)
+    verts, prim_kind, rows, pm, mats = scenes.with_sphere_light(sc)
+    acc = gpu.B200Accel(gpu.build_bvh(verts), verts, prim_kind=prim_kind, spheres=rows)
+    sl = sc["sphere_light"]
+    integ = gpu.WavefrontPathIntegrator(sc["camera"], spp=spp, maxdepth=maxdepth, light_pos=sl["center"], light_I=sl["L"],
+                                        seed=4, sphere_light=(sl["radius"], len(verts) - 1), materials=mats, prim_material=pm)
+    film, st = integ.Render(acc)
+    rgb, ref = film_to_rgb(film).astype(np.float64), g["killeroo_area_rgb"].astype(np.float64)
+    nc, ns = (int(x) for x in g["killeroo_area_rays"])
+    assert abs(st["closest_rays"] / nc - 1) < 0.01, (st["closest_rays"], nc)
+    assert abs(st["shadow_rays"] / ns - 1) < 0.01, (st["shadow_rays"], ns)
+    assert 0 < st["mis_rays"] < st["closest_rays"]
+    # the emitter itself covers a few pixels at radiance 2000: compare them apart from the reflected light
+    # (pixels it covers only partly hold a noisy fraction of 2000, far above the reflected light: mask those too)
+    lit = ref.max(-1) > 1000
+    assert lit.sum() > 0 and abs((rgb.max(-1) > 1000).sum() / lit.sum() - 1) < 0.2
+    near = (ref.max(-1) > 50) | (rgb.max(-1) > 50)
+    for _ in range(2):   # dilate by two pixels
+        near = near | np.roll(near, 1, 0) | np.roll(near, -1, 0) | np.roll(near, 1, 1) | np.roll(near, -1, 1)
+    assert near.sum() < 200
+    a, b = np.where(near[..., None], 0, rgb), np.where(near[..., None], 0, ref)
+    assert abs(a.mean() / b.mean() - 1) < 0.01, (a.mean(), b.mean())
+    for ch in range(3):   # per colour channel: the per-primitive Kd's tint the bounce light
+        assert abs(a[..., ch].mean() / b[..., ch].mean() - 1) < 0.015
+    assert np.sqrt(((_blocks(a, 8) - _blocks(b, 8)) ** 2).mean()) / b.mean() < 0.04

@@ -174,8 +174,37 @@ def killeroo_simple(xres=700, yres=700):
     tris.append(_xform(ctm, P)[idx].reshape(-1, 9))
     tv = np.concatenate(tris).astype(np.float32) + np.float32(0)
     cam = _killeroo_camera(xres, yres)
+    nk = len(idx)
+    # Material per primitive (scenes/killeroo-simple:27,40,44): ground matte Kd (.5 .5 .8); the two killeroos are
+    # "plastic" Kd (.4 .2 .2) / (.4 .5 .4) — their diffuse part; index 3 = the emitter's matte Kd 0 (:19)
+    prim_material = np.concatenate([np.zeros(4, np.uint8), np.full(nk, 1, np.uint8), np.full(nk, 2, np.uint8)])
+    kds = np.array([[.5, .5, .8], [.4, .2, .2], [.4, .5, .4], [0, 0, 0]], np.float32)
     return dict(name="killeroo-simple", tri_verts=tv, camera=cam, light=np.array([150, 120, 20], np.float32),
-                note="reference geometry (fixture); sphere area light replaced by a point light at its centre")
+                sphere_light=dict(center=np.array([150, 120, 20], np.float32), radius=3.0, L=np.array([2000.0] * 3, np.float32)),
+                prim_material=prim_material, material_kd=kds,
+                note="reference geometry (fixture); light = the scene's sphere area light (scenes/killeroo-simple:18-24) "
+                     "or, for the point-light integrator, a point light at its centre")
+
+
+def with_sphere_light(sc):
+    """Aggregate of `sc` with its sphere area light appended as the LAST primitive, as pbrtShape adds it to the
+    primitive list (scenes/killeroo-simple:18-24): returns (bounds_verts, prim_kind, sphere_rows, prim_material,
+    materials).  bounds_verts gives the sphere primitive a stand-in triangle with the sphere's world bound, which is
+    all the BVH / kd builders read; the device gets prim_kind/sphere_rows for the real test."""
+    c, r = sc["sphere_light"]["center"].astype(np.float32), np.float32(sc["sphere_light"]["radius"])
+    lo, hi = c - r, c + r
+    fake = np.concatenate([lo, hi, lo]).astype(np.float32)[None]
+    verts = np.concatenate([sc["tri_verts"], fake])
+    n = len(verts)
+    prim_kind = np.zeros(n, np.uint8)
+    prim_kind[-1] = 1
+    rows = np.zeros((1, 16), np.float32)   # WorldToObject = Translate(-c), radius
+    rows[0, 0] = rows[0, 5] = rows[0, 10] = 1
+    rows[0, 3], rows[0, 7], rows[0, 11], rows[0, 12] = -c[0], -c[1], -c[2], r
+    pm = np.concatenate([sc["prim_material"], np.array([len(sc["material_kd"]) - 1], np.uint8)])
+    mats = np.zeros((len(sc["material_kd"]), 8), np.float32)
+    mats[:, 1:4] = sc["material_kd"]
+    return verts, prim_kind, rows, pm, mats
 
 
 # ---- procedural stand-ins --------------------------------------------------------------------

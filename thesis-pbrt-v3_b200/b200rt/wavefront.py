@@ -14,13 +14,16 @@ class Camera(C.Structure):
 class RenderDesc(C.Structure):
     _fields_ = [("camera", Camera), ("spp", C.c_uint32), ("max_depth", C.c_uint32), ("light_pos", C.c_float * 3),
                 ("light_I", C.c_float * 3), ("kd", C.c_float * 3), ("tile_size", C.c_uint32), ("rank", C.c_uint32),
-                ("world", C.c_uint32), ("seed", C.c_uint32), ("max_batch", C.c_uint32)]
+                ("world", C.c_uint32), ("seed", C.c_uint32), ("max_batch", C.c_uint32),
+                ("light_kind", C.c_uint32), ("light_radius", C.c_float), ("light_prim", C.c_uint32),
+                ("materials", C.c_void_p), ("n_materials", C.c_uint32), ("prim_material", C.c_void_p)]
 
 
 class RenderStats(C.Structure):
     _fields_ = [("camera_rays", C.c_uint64), ("closest_rays", C.c_uint64), ("shadow_rays", C.c_uint64),
                 ("launches", C.c_uint64), ("ms_closest", C.c_float), ("ms_any", C.c_float), ("ms_total", C.c_float),
-                ("n_tiles", C.c_uint32), ("launches_closest", C.c_uint32), ("launches_any", C.c_uint32)]
+                ("n_tiles", C.c_uint32), ("launches_closest", C.c_uint32), ("launches_any", C.c_uint32),
+                ("mis_rays", C.c_uint64)]
 
 
 _bound = False
@@ -46,7 +49,11 @@ class WavefrontPathIntegrator:
     this rank's tiles (tile t belongs to rank t % world); stats as a dict."""
 
     def __init__(self, camera, spp=8, maxdepth=5, light_pos=(0, 0, 0), light_I=(1, 1, 1), kd=(.5, .5, .5),
-                 rank=0, world=1, seed=0, tile_size=16, max_batch=0):
+                 rank=0, world=1, seed=0, tile_size=16, max_batch=0, sphere_light=None, materials=None,
+                 prim_material=None):
+        """sphere_light=(radius, prim): `AreaLightSource "area" "color L" light_I` on the full sphere primitive number
+        `prim` of the aggregate, centred at light_pos (sampled with MIS like EstimateDirect).  materials: (n, 8) rows
+        (kind, Kd.rgb, Ks.rgb, roughness) + prim_material: (n_prims,) uint8 index per primitive."""
         d = RenderDesc()
         for k in ("eye", "dir", "right", "up"):
             setattr(d.camera, k, (C.c_float * 3)(*[float(x) for x in camera[k]]))
@@ -56,6 +63,13 @@ class WavefrontPathIntegrator:
         d.light_I = (C.c_float * 3)(*[float(x) for x in light_I])
         d.kd = (C.c_float * 3)(*[float(x) for x in kd])
         d.tile_size, d.rank, d.world, d.seed, d.max_batch = tile_size, rank, world, seed, max_batch
+        if sphere_light is not None:
+            d.light_kind, d.light_radius, d.light_prim = 1, float(sphere_light[0]), int(sphere_light[1])
+        if materials is not None:
+            self._mats = np.ascontiguousarray(materials, np.float32).reshape(-1, 8)
+            self._pm = np.ascontiguousarray(prim_material, np.uint8)
+            d.materials, d.n_materials = self._mats.ctypes.data, len(self._mats)
+            d.prim_material = self._pm.ctypes.data
         self.desc = d
 
     @property

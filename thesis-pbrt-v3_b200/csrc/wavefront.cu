@@ -44,7 +44,12 @@ struct WfParams {
     Tiling tl;
     float light_pos[3], light_I[3], kd[3];
     uint32_t max_depth, seed;
+    uint32_t light_kind, light_prim;
+    float light_radius;
+    const float4 *mats;       // 2 x float4 per material: (kind, Kd.rgb) (Ks.rgb, roughness); nullptr = one matte kd
+    const uint8_t *primMat;   // material index per primitive
 };
+constexpr float kGamma5 = rt_gamma(5);
 
 // ---- counter-based sampler: value = hash(seed, pixel, sample, dimension) ------------------------
 __device__ __forceinline__ uint32_t mix32(uint32_t x) {
@@ -129,11 +134,13 @@ __global__ void k_shade(const __grid_constant__ WfParams P, uint32_t depth, uint
                         const uint32_t *__restrict__ nCur, const float4 *__restrict__ rays,
                         const uint32_t *__restrict__ qPath, const b200rt_hit *__restrict__ hits,
                         const float4 *__restrict__ primTris, float4 *beta, float4 *nextRays, uint32_t *nextPath,
-                        uint32_t *nNext, float4 *shRays, uint32_t *shPath, float4 *shContrib, uint32_t *nShadow) {
+                        uint32_t *nNext, float4 *shRays, uint32_t *shPath, float4 *shContrib, uint32_t *nShadow,
+                        float4 *L, float4 *misRays, uint32_t *misPath, float4 *misContrib, uint32_t *nMis) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     const uint32_t n = *nCur;
-    bool wantShadow = false, wantNext = false;
-    float3 so = make_float3(0, 0, 0), sd = so, no = so, nd = so, contrib = so;
+    const bool area = P.light_kind == B200RT_LIGHT_SPHERE;
+    bool wantShadow = false, wantNext = false, wantMis = false;
+    float3 so = make_float3(0, 0, 0), sd = so, no = so, nd = so, contrib = so, mo = so, md = so, mcontrib = so;
     uint32_t path = 0;
     if (i < n) {
         const b200rt_hit h = hits[i];
@@ -152,9 +159,26 @@ __global__ void k_shade(const __grid_constant__ WfParams P, uint32_t depth, uint
             const float3 e0 = make_float3(a.x - c.x, a.y - c.y, a.z - c.z), e1 = make_float3(b.x - c.x, b.y - c.y, b.z - c.z);
             float3 ng = make_float3(e0.y * e1.z - e0.z * e1.y, e0.z * e1.x - e0.x * e1.z, e0.x * e1.y - e0.y * e1.x);
             const float nl = sqrtf(ng.x * ng.x + ng.y * ng.y + ng.z * ng.z);
-            // a sphere primitive (killeroo-simple's emitter: matte Kd = 0) ends the path: nothing to reflect
+            // a sphere primitive (killeroo-simple's emitter: matte Kd = 0) ends the path: nothing to reflect.  Seen by a
+            // camera ray it adds its emitted radiance (path.cpp:97-107: bounces == 0; later hits are covered by MIS).
+            if (area && depth == 0 && h.prim == P.light_prim) {
+                const float4 ro = rays[2 * (size_t)i];
+                const float3 ph = make_float3(ro.x + h.t * rd.x, ro.y + h.t * rd.y, ro.z + h.t * rd.z);
+                const float cosl = (ph.x - P.light_pos[0]) * -rd.x + (ph.y - P.light_pos[1]) * -rd.y + (ph.z - P.light_pos[2]) * -rd.z;
+                if (cosl > 0.f) {  // DiffuseAreaLight::L, one-sided (diffuse.h:56-58)
+                    const float4 bt = beta[path];
+                    float4 l = L[path];
+                    l.x += bt.x * P.light_I[0]; l.y += bt.y * P.light_I[1]; l.z += bt.z * P.light_I[2];
+                    L[path] = l;
+                }
+            }
             if (nl > 0.f && !(__float_as_uint(b.w) & B200RT_PRIM_SPHERE)) {
                 ng.x /= nl; ng.y /= nl; ng.z /= nl;
+                float kdr = P.kd[0], kdg = P.kd[1], kdb = P.kd[2];
+                if (P.mats) {
+                    const float4 m0 = __ldg(P.mats + 2 * (size_t)__ldg(P.primMat + h.prim));
+                    kdr = m0.y; kdg = m0.z; kdb = m0.w;
+                }
                 const float3 wo = make_float3(-rd.x, -rd.y, -rd.z);
                 const float side = (ng.x * wo.x + ng.y * wo.y + ng.z * wo.z) < 0.f ? -1.f : 1.f;
                 const float3 nf = make_float3(side * ng.x, side * ng.y, side * ng.z);  // wo's hemisphere
@@ -162,13 +186,97 @@ __global__ void k_shade(const __grid_constant__ WfParams P, uint32_t depth, uint
                 // -- direct lighting: PointLight::Sample_Li (point.cpp:44-53) + matte f * |cos|
                 const float3 wl = make_float3(P.light_pos[0] - p.x, P.light_pos[1] - p.y, P.light_pos[2] - p.z);
                 const float d2 = wl.x * wl.x + wl.y * wl.y + wl.z * wl.z;
-                if (d2 > 0.f) {
+                uint32_t x, y, s;
+                path_pixel(P.tl, batchStart + path, x, y, s);
+                const uint32_t pix = y * P.cam.xres + x, dim = 2 + 3 * depth;
+                if (area) {
+                    // ---- EstimateDirect with MIS (integrator.cpp:109-217) against the sphere light ----
+                    const float r2 = P.light_radius * P.light_radius;
+                    const float3 pO = offset_ray_origin(p, pe, ng, wl);  // Sphere::Sample's inside test (sphere.cpp:237-239)
+                    const float dO2 = (pO.x - P.light_pos[0]) * (pO.x - P.light_pos[0]) + (pO.y - P.light_pos[1]) * (pO.y - P.light_pos[1]) +
+                                      (pO.z - P.light_pos[2]) * (pO.z - P.light_pos[2]);
+                    if (dO2 > r2 && d2 > 0.f) {  // reference points outside the sphere (the only case the config scenes have)
+                        const float dc = sqrtf(d2);
+                        const float3 wc = make_float3(wl.x / dc, wl.y / dc, wl.z / dc);
+                        float3 wcX;
+                        if (fabsf(wc.x) > fabsf(wc.y)) { const float il = 1.f / sqrtf(wc.x * wc.x + wc.z * wc.z); wcX = make_float3(-wc.z * il, 0.f, wc.x * il); }
+                        else { const float il = 1.f / sqrtf(wc.y * wc.y + wc.z * wc.z); wcX = make_float3(0.f, wc.z * il, -wc.y * il); }
+                        const float3 wcY = make_float3(wc.y * wcX.z - wc.z * wcX.y, wc.z * wcX.x - wc.x * wcX.z, wc.x * wcX.y - wc.y * wcX.x);
+                        const float sinThetaMax2 = r2 / d2;
+                        const float cosThetaMax = sqrtf(fmaxf(0.f, 1.f - sinThetaMax2));
+                        const float lightPdf = 1.f / (2.f * kPi * (1.f - cosThetaMax));  // UniformConePdf
+                        // (a) light sample: Sphere::Sample(ref, u) cone sampling (sphere.cpp:254-291)
+                        {
+                            const float u0 = rnd(P.seed, pix, s, 1000 + 4 * depth), u1 = rnd(P.seed, pix, s, 1001 + 4 * depth);
+                            const float cosTheta = (1.f - u0) + u0 * cosThetaMax;
+                            const float sinTheta = sqrtf(fmaxf(0.f, 1.f - cosTheta * cosTheta));
+                            const float phi = u1 * 2.f * kPi;
+                            const float ds = dc * cosTheta - sqrtf(fmaxf(0.f, r2 - dc * dc * sinTheta * sinTheta));
+                            const float cosAlpha = (dc * dc + r2 - ds * ds) / (2.f * dc * P.light_radius);
+                            const float sinAlpha = sqrtf(fmaxf(0.f, 1.f - cosAlpha * cosAlpha));
+                            const float cx = -sinAlpha * cosf(phi), cy = -sinAlpha * sinf(phi), cz = -cosAlpha;
+                            const float3 nW = make_float3(cx * wcX.x + cy * wcY.x + cz * wc.x, cx * wcX.y + cy * wcY.y + cz * wc.y,
+                                                          cx * wcX.z + cy * wcY.z + cz * wc.z);
+                            const float3 pW = make_float3(P.light_pos[0] + P.light_radius * nW.x, P.light_pos[1] + P.light_radius * nW.y,
+                                                          P.light_pos[2] + P.light_radius * nW.z);
+                            float3 wi = make_float3(pW.x - p.x, pW.y - p.y, pW.z - p.z);
+                            const float wl2 = wi.x * wi.x + wi.y * wi.y + wi.z * wi.z;
+                            if (wl2 > 0.f) {
+                                const float il = 1.f / sqrtf(wl2);
+                                wi.x *= il; wi.y *= il; wi.z *= il;
+                                const bool emits = (nW.x * -wi.x + nW.y * -wi.y + nW.z * -wi.z) > 0.f;
+                                const float cosi = nf.x * wi.x + nf.y * wi.y + nf.z * wi.z;
+                                if (emits && cosi > 0.f) {  // reflective Lambertian lobe: wi in wo's hemisphere
+                                    const float scatPdf = cosi * kInvPi;
+                                    const float wgt = (lightPdf * lightPdf) / (lightPdf * lightPdf + scatPdf * scatPdf);  // PowerHeuristic
+                                    const float g = cosi * kInvPi * wgt / lightPdf;
+                                    contrib = make_float3(bt.x * kdr * P.light_I[0] * g, bt.y * kdg * P.light_I[1] * g, bt.z * kdb * P.light_I[2] * g);
+                                    if (contrib.x > 0.f || contrib.y > 0.f || contrib.z > 0.f) {
+                                        // Interaction::SpawnRayTo(const Interaction &) (interaction.h:73-78)
+                                        const float3 peL = make_float3(kGamma5 * fabsf(pW.x), kGamma5 * fabsf(pW.y), kGamma5 * fabsf(pW.z));
+                                        so = offset_ray_origin(p, pe, ng, make_float3(pW.x - p.x, pW.y - p.y, pW.z - p.z));
+                                        const float3 tg = offset_ray_origin(pW, peL, nW, make_float3(so.x - pW.x, so.y - pW.y, so.z - pW.z));
+                                        sd = make_float3(tg.x - so.x, tg.y - so.y, tg.z - so.z);
+                                        wantShadow = true;
+                                    }
+                                }
+                            }
+                        }
+                        // (b) BSDF sample: CosineSampleHemisphere; the ray is traced to see whether it reaches the light
+                        {
+                            const float u0 = 2.f * rnd(P.seed, pix, s, 1002 + 4 * depth) - 1.f, u1 = 2.f * rnd(P.seed, pix, s, 1003 + 4 * depth) - 1.f;
+                            float dxl = 0.f, dyl = 0.f;
+                            if (u0 != 0.f || u1 != 0.f) {
+                                float r, th;
+                                if (fabsf(u0) > fabsf(u1)) { r = u0; th = (kPi / 4.f) * (u1 / u0); }
+                                else { r = u1; th = (kPi / 2.f) - (kPi / 4.f) * (u0 / u1); }
+                                dxl = r * cosf(th); dyl = r * sinf(th);
+                            }
+                            const float dzl = sqrtf(fmaxf(0.f, 1.f - dxl * dxl - dyl * dyl));
+                            float3 ss;
+                            if (fabsf(nf.x) > fabsf(nf.y)) { const float il = 1.f / sqrtf(nf.x * nf.x + nf.z * nf.z); ss = make_float3(-nf.z * il, 0.f, nf.x * il); }
+                            else { const float il = 1.f / sqrtf(nf.y * nf.y + nf.z * nf.z); ss = make_float3(0.f, nf.z * il, -nf.y * il); }
+                            const float3 ts = make_float3(nf.y * ss.z - nf.z * ss.y, nf.z * ss.x - nf.x * ss.z, nf.x * ss.y - nf.y * ss.x);
+                            const float3 wi = make_float3(ss.x * dxl + ts.x * dyl + nf.x * dzl, ss.y * dxl + ts.y * dyl + nf.y * dzl,
+                                                          ss.z * dxl + ts.z * dyl + nf.z * dzl);
+                            const float scatPdf = dzl * kInvPi;
+                            if (scatPdf > 0.f && (kdr > 0.f || kdg > 0.f || kdb > 0.f)) {  // !f.IsBlack() && scatteringPdf > 0
+                                const float wgt = (scatPdf * scatPdf) / (scatPdf * scatPdf + lightPdf * lightPdf);
+                                // f * |cos| / pdf = Kd; Li = L when the ray's closest hit is the emitter
+                                mcontrib = make_float3(bt.x * kdr * P.light_I[0] * wgt, bt.y * kdg * P.light_I[1] * wgt, bt.z * kdb * P.light_I[2] * wgt);
+                                mo = offset_ray_origin(p, pe, ng, wi);
+                                md = wi;
+                                wantMis = true;
+                            }
+                        }
+                    }
+                } else if (d2 > 0.f) {
                     const float invd = 1.f / sqrtf(d2);
                     const float cosl = (nf.x * wl.x + nf.y * wl.y + nf.z * wl.z) * invd;
                     if (cosl > 0.f) {  // SameHemisphere(wo, wi) for a reflective Lambertian lobe
                         const float g = cosl * kInvPi / d2;
-                        contrib = make_float3(bt.x * P.kd[0] * P.light_I[0] * g, bt.y * P.kd[1] * P.light_I[1] * g,
-                                              bt.z * P.kd[2] * P.light_I[2] * g);
+                        contrib = make_float3(bt.x * kdr * P.light_I[0] * g, bt.y * kdg * P.light_I[1] * g,
+                                              bt.z * kdb * P.light_I[2] * g);
                         if (contrib.x > 0.f || contrib.y > 0.f || contrib.z > 0.f) {
                             // Interaction::SpawnRayTo (interaction.h:68-72)
                             so = offset_ray_origin(p, pe, ng, wl);
@@ -178,9 +286,6 @@ __global__ void k_shade(const __grid_constant__ WfParams P, uint32_t depth, uint
                     }
                 }
                 // -- BSDF sample: CosineSampleHemisphere via ConcentricSampleDisk (sampling.cpp)
-                uint32_t x, y, s;
-                path_pixel(P.tl, batchStart + path, x, y, s);
-                const uint32_t pix = y * P.cam.xres + x, dim = 2 + 3 * depth;
                 const float u0 = 2.f * rnd(P.seed, pix, s, dim) - 1.f, u1 = 2.f * rnd(P.seed, pix, s, dim + 1) - 1.f;
                 float dxl = 0.f, dyl = 0.f;
                 if (u0 != 0.f || u1 != 0.f) {
@@ -199,7 +304,7 @@ __global__ void k_shade(const __grid_constant__ WfParams P, uint32_t depth, uint
                                               ss.z * dxl + ts.z * dyl + nf.z * dzl);
                 if (dzl > 0.f) {
                     // beta *= f * |cos| / pdf = Kd (path.cpp:151)
-                    float3 nb = make_float3(bt.x * P.kd[0], bt.y * P.kd[1], bt.z * P.kd[2]);
+                    float3 nb = make_float3(bt.x * kdr, bt.y * kdg, bt.z * kdb);
                     bool alive = nb.x > 0.f || nb.y > 0.f || nb.z > 0.f;
                     // Russian roulette (path.cpp:190-199): bounces > 3 and max(beta) < rrThreshold = 1
                     const float mx = fmaxf(nb.x, fmaxf(nb.y, nb.z));
@@ -231,6 +336,27 @@ __global__ void k_shade(const __grid_constant__ WfParams P, uint32_t depth, uint
         nextRays[2 * (size_t)nj + 1] = make_float4(nd.x, nd.y, nd.z, 0.f);
         nextPath[nj] = path;
     }
+    if (area) {  // warp-uniform
+        const uint32_t mj = warp_append(wantMis, nMis);
+        if (wantMis) {
+            misRays[2 * (size_t)mj] = make_float4(mo.x, mo.y, mo.z, __int_as_float(0x7f800000));
+            misRays[2 * (size_t)mj + 1] = make_float4(md.x, md.y, md.z, 0.f);
+            misPath[mj] = path;
+            misContrib[mj] = make_float4(mcontrib.x, mcontrib.y, mcontrib.z, 0.f);
+        }
+    }
+}
+
+// The BSDF-sampled ray of EstimateDirect (integrator.cpp:196-212): it contributes when its closest hit is the emitter
+// (`lightIsect.primitive->GetAreaLight() == &light`, Li = lightIsect.Le(-wi); seen from outside the sphere is front-facing).
+__global__ void k_mis_resolve(const uint32_t *__restrict__ nMis, const b200rt_hit *__restrict__ hits, uint32_t lightPrim,
+                              const uint32_t *__restrict__ misPath, const float4 *__restrict__ misContrib, float4 *L) {
+    const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= *nMis || hits[j].prim != lightPrim) return;
+    const float4 c = misContrib[j];
+    float4 l = L[misPath[j]];   // one MIS ray per path and depth: no two threads share a path
+    l.x += c.x; l.y += c.y; l.z += c.z;
+    L[misPath[j]] = l;
 }
 
 // VisibilityTester::Unoccluded (light.cpp:59-64): add the light sample when the shadow ray is free.
@@ -279,6 +405,11 @@ __global__ void k_heat(const __grid_constant__ WfParams P, uint64_t batchStart, 
 
 struct Workspace {
     size_t cap = 0;
+    float4 *misRays = nullptr, *misContrib = nullptr;   // area-light mode only (EstimateDirect's BSDF-sampled rays)
+    uint32_t *misPath = nullptr;
+    float4 *mats = nullptr;
+    uint8_t *primMat = nullptr;
+    size_t mats_n = 0, primMat_n = 0;
     uint4 *perRay = nullptr;   // heat-map mode only
     uint32_t *heat = nullptr;
     size_t heat_px = 0;
@@ -299,6 +430,7 @@ void free_ws(Workspace *w) {
     for (int k = 0; k < 2; ++k) { cudaFree(w->rays[k]); cudaFree(w->qPath[k]); }
     cudaFree(w->shRays); cudaFree(w->shContrib); cudaFree(w->beta); cudaFree(w->L); cudaFree(w->shPath);
     cudaFree(w->counts); cudaFree(w->hits); cudaFree(w->occ); cudaFree(w->film); cudaFree(w->perRay); cudaFree(w->heat);
+    cudaFree(w->misRays); cudaFree(w->misContrib); cudaFree(w->misPath); cudaFree(w->mats); cudaFree(w->primMat);
     for (float4 *p : w->kept) cudaFree(p);
     *w = Workspace();
 }
@@ -391,6 +523,13 @@ static int render_impl(b200rt_scene *s, const b200rt_render_desc *d, float *film
     std::memcpy(P.light_pos, d->light_pos, 12); std::memcpy(P.light_I, d->light_I, 12); std::memcpy(P.kd, d->kd, 12);
     P.max_depth = d->max_depth; P.seed = d->seed;
     if (d->max_depth > 64) return set_error(B200RT_EINVAL, "max_depth %u too large", d->max_depth);
+    P.light_kind = d->light_kind; P.light_prim = d->light_prim; P.light_radius = d->light_radius;
+    const bool area = d->light_kind == B200RT_LIGHT_SPHERE;
+    if (d->light_kind > B200RT_LIGHT_SPHERE) return set_error(B200RT_EINVAL, "unknown light_kind %u", d->light_kind);
+    if (area && (!(d->light_radius > 0.f) || d->light_prim >= s->n_prims))
+        return set_error(B200RT_EINVAL, "sphere light: radius must be > 0 and light_prim a primitive of the scene");
+    if (d->materials && (!d->prim_material || d->n_materials == 0 || d->n_materials > 256))
+        return set_error(B200RT_EINVAL, "materials need prim_material and 1..256 records");
     cudaStream_t st = (cudaStream_t)stream;
     Workspace *w = ws_of(s);
     const uint32_t tp = P.tl.tile * P.tl.tile;
@@ -399,7 +538,8 @@ static int render_impl(b200rt_scene *s, const b200rt_render_desc *d, float *film
     uint64_t cap = std::max<uint64_t>(unit, want / unit * unit);
     cap = std::min<uint64_t>(cap, std::max<uint64_t>(unit, P.tl.n_paths_rank));
     if (cap > 0x7fffffffull) return set_error(B200RT_EINVAL, "batch too large");
-    const uint32_t nCounts = 2 * (d->max_depth + 2);
+    const uint32_t misBase = 2 * (d->max_depth + 2);          // counts[misBase + depth] = MIS queue size at depth
+    const uint32_t nCounts = misBase + d->max_depth + 1;
     if (w->cap < cap) {
         const bool keep = w->keep;
         free_ws(w);
@@ -408,8 +548,22 @@ static int render_impl(b200rt_scene *s, const b200rt_render_desc *d, float *film
         WCU(cudaMalloc(&w->shRays, cap * 32)); WCU(cudaMalloc(&w->shContrib, cap * 16)); WCU(cudaMalloc(&w->shPath, cap * 4));
         WCU(cudaMalloc(&w->beta, cap * 16)); WCU(cudaMalloc(&w->L, cap * 16));
         WCU(cudaMalloc(&w->hits, cap * sizeof(b200rt_hit))); WCU(cudaMalloc(&w->occ, cap));
-        WCU(cudaMalloc(&w->counts, 4 * 2 * 66));
+        WCU(cudaMalloc(&w->counts, 4 * 3 * 66));
         w->cap = cap;
+    }
+    if (area && !w->misRays) {
+        WCU(cudaMalloc(&w->misRays, w->cap * 32)); WCU(cudaMalloc(&w->misContrib, w->cap * 16)); WCU(cudaMalloc(&w->misPath, w->cap * 4));
+    }
+    if (d->materials) {
+        for (uint32_t k = 0; k < d->n_materials; ++k)
+            if (d->materials[8 * k] != (float)B200RT_MAT_MATTE) return set_error(B200RT_EUNSUPPORTED, "material %u: only matte is supported", k);
+        if (w->mats_n < d->n_materials) { cudaFree(w->mats); w->mats = nullptr; WCU(cudaMalloc(&w->mats, (size_t)d->n_materials * 32)); w->mats_n = d->n_materials; }
+        if (w->primMat_n < s->n_prims) { cudaFree(w->primMat); w->primMat = nullptr; WCU(cudaMalloc(&w->primMat, s->n_prims)); w->primMat_n = s->n_prims; }
+        for (uint32_t k = 0; k < s->n_prims; ++k)
+            if (d->prim_material[k] >= d->n_materials) return set_error(B200RT_EINVAL, "prim_material[%u] out of range", k);
+        WCU(cudaMemcpyAsync(w->mats, d->materials, (size_t)d->n_materials * 32, cudaMemcpyHostToDevice, st));
+        WCU(cudaMemcpyAsync(w->primMat, d->prim_material, s->n_prims, cudaMemcpyHostToDevice, st));
+        P.mats = w->mats; P.primMat = w->primMat;
     }
     const size_t npx = (size_t)P.tl.xres * P.tl.yres;
     cudaPointerAttributes pa;
@@ -450,7 +604,7 @@ static int render_impl(b200rt_scene *s, const b200rt_render_desc *d, float *film
     struct Span { cudaEvent_t a, b; bool any; };
     std::vector<Span> spans;
     const uint64_t launches0 = g_launches.load();
-    uint64_t nClosest = 0, nShadow = 0, nCamera = 0;
+    uint64_t nClosest = 0, nShadow = 0, nCamera = 0, nMis = 0;
     std::vector<uint32_t> hostCounts(nCounts);
     cudaEvent_t t0 = ev();
     const unsigned TB = 256;
@@ -477,7 +631,8 @@ static int render_impl(b200rt_scene *s, const b200rt_render_desc *d, float *film
             k_shade<<<gridSlots, TB, 0, st>>>(P, depth, start, w->counts + 2 * depth, w->rays[cur], w->qPath[cur], w->hits,
                                               s->d_prim_tris, w->beta, w->rays[cur ^ 1], w->qPath[cur ^ 1],
                                               w->counts + 2 * (depth + 1), w->shRays, w->shPath, w->shContrib,
-                                              w->counts + 2 * depth + 1);
+                                              w->counts + 2 * depth + 1, w->L, w->misRays, w->misPath, w->misContrib,
+                                              w->counts + misBase + depth);
             g_launches.fetch_add(1);
             if (w->keep) WCU(cudaMemcpyAsync(w->kept[2 * depth + 1], w->shRays, (size_t)nSlots * 32, cudaMemcpyDeviceToDevice, st));
             a = ev();
@@ -491,6 +646,19 @@ static int render_impl(b200rt_scene *s, const b200rt_render_desc *d, float *film
             }
             k_shadow_resolve<<<gridSlots, TB, 0, st>>>(w->counts + 2 * depth + 1, w->occ, w->shPath, w->shContrib, w->L);
             g_launches.fetch_add(1);
+            if (area) {  // EstimateDirect's BSDF-sampled ray: one more closest-hit queue per bounce (w->hits is free again)
+                a = ev();
+                rc = launch_trace(s, w->misRays, nSlots, w->counts + misBase + depth, w->hits, nullptr, false,
+                                  heat ? s->d_counters : nullptr, st, heat ? w->perRay : nullptr);
+                if (rc) return rc;
+                spans.push_back({a, ev(), false});
+                if (heat) {
+                    k_heat<<<gridSlots, TB, 0, st>>>(P, start, w->counts + misBase + depth, w->misPath, w->perRay, d_heat, 0u);
+                    g_launches.fetch_add(1);
+                }
+                k_mis_resolve<<<gridSlots, TB, 0, st>>>(w->counts + misBase + depth, w->hits, d->light_prim, w->misPath, w->misContrib, w->L);
+                g_launches.fetch_add(1);
+            }
             cur ^= 1;
         }
         const uint32_t nPix = nSlots / P.tl.spp;
@@ -502,6 +670,7 @@ static int render_impl(b200rt_scene *s, const b200rt_render_desc *d, float *film
         for (uint32_t depth = 0; depth <= d->max_depth; ++depth) {
             nClosest += hostCounts[2 * depth];
             if (depth < d->max_depth) nShadow += hostCounts[2 * depth + 1];
+            if (area && depth < d->max_depth) { nClosest += hostCounts[misBase + depth]; nMis += hostCounts[misBase + depth]; }
             if (w->keep) {
                 w->keptCount[2 * depth] = hostCounts[2 * depth];
                 if (depth < d->max_depth) w->keptCount[2 * depth + 1] = hostCounts[2 * depth + 1];
@@ -515,7 +684,7 @@ static int render_impl(b200rt_scene *s, const b200rt_render_desc *d, float *film
     WCU(cudaGetLastError());
     if (stats) {
         std::memset(stats, 0, sizeof(*stats));
-        stats->camera_rays = nCamera; stats->closest_rays = nClosest; stats->shadow_rays = nShadow;
+        stats->camera_rays = nCamera; stats->closest_rays = nClosest; stats->shadow_rays = nShadow; stats->mis_rays = nMis;
         stats->launches = g_launches.load() - launches0;
         stats->n_tiles = P.tl.n_tiles_rank;
         for (const Span &sp : spans) (sp.any ? stats->launches_any : stats->launches_closest) += 1;
