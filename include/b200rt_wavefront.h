@@ -55,14 +55,14 @@ typedef struct {
     float light_radius;    /* sphere radius; light_pos = its centre, light_I = its emitted radiance "L" */
     uint32_t light_prim;   /* primitive number of that sphere inside the aggregate (scene-desc prim_kind == 1) */
     /* Materials: NULL = Material "matte" "Kd" = kd for all.  Else n_materials records of 8 floats
-     * (kind, Kd.r, Kd.g, Kd.b, Ks.r, Ks.g, Ks.b, roughness), kind B200RT_MAT_MATTE (materials/matte.cpp, sigma 0),
+     * (kind, Kd.r, Kd.g, Kd.b, Ks.r, Ks.g, Ks.b, roughness), kind B200RT_MAT_MATTE (materials/matte.cpp, sigma 0) or B200RT_MAT_PLASTIC (materials/plastic.cpp),
      * and one material index per primitive.  HOST pointers, read during the call. */
     const float *materials;
     uint32_t n_materials;
     const uint8_t *prim_material; /* n_prims bytes */
 } b200rt_render_desc;
 enum { B200RT_LIGHT_POINT = 0, B200RT_LIGHT_SPHERE = 1 };
-enum { B200RT_MAT_MATTE = 0 };
+enum { B200RT_MAT_MATTE = 0, B200RT_MAT_PLASTIC = 1 /* materials/plastic.cpp: Kd + Ks microfacet lobe, roughness remapped */ };
 
 typedef struct {
     uint64_t camera_rays;   /* = paths started */

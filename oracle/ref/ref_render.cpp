@@ -26,6 +26,7 @@
 #include "lights/point.h"
 #include "lights/diffuse.h"
 #include "materials/matte.h"
+#include "materials/plastic.h"
 #include "samplers/halton.h"
 #include "samplers/random.h"
 #include "textures/constant.h"
@@ -77,7 +78,8 @@ extern "C" int ref_render(ref_scene *s, const char *accel_kind, const float *cam
                           int maxdepth, const float *light_pos, const float *light_I, const float *kd,
                           const char *sampler_name, int n_threads, const char *tmp_prefix, float *out_rgb,
                           uint64_t *n_closest, uint64_t *n_shadow, uint32_t *out_heat /* nullable: 6 planes of yres*xres */,
-                          const float *prim_kd /* nullable: one matte Kd (rgb) per primitive instead of `kd` */,
+                          const float *prim_mat /* nullable: 8 floats per primitive (kind 0 matte / 1 plastic, Kd rgb, Ks rgb,
+                                                   roughness) instead of the single matte `kd` */,
                           const float *emitter_L /* nullable: rgb; the scene's LAST primitive (a sphere) becomes
                                                     AreaLightSource "area" "color L" and replaces the point light */) {
     PbrtOptions.quiet = true;
@@ -90,17 +92,24 @@ extern "C" int ref_render(ref_scene *s, const char *accel_kind, const float *cam
     MediumInterface mi;
     std::vector<std::shared_ptr<Primitive>> prims;
     std::shared_ptr<AreaLight> area;
-    std::map<std::array<float, 3>, std::shared_ptr<Material>> byKd;   // one MatteMaterial per distinct Kd
+    std::map<std::array<float, 8>, std::shared_ptr<Material>> byKd;   // one Material per distinct record
     for (size_t i = 0; i < s->prims.size(); ++i) {
         auto *gp = static_cast<GeometricPrimitive *>(s->prims[i].get());
         std::shared_ptr<Material> m = matte;
-        if (prim_kd) {
-            std::array<float, 3> k = {prim_kd[3 * i], prim_kd[3 * i + 1], prim_kd[3 * i + 2]};
+        if (prim_mat) {
+            std::array<float, 8> k;
+            std::memcpy(k.data(), prim_mat + 8 * i, sizeof(float) * 8);
             auto it = byKd.find(k);
             if (it == byKd.end()) {
-                Float c[3] = {k[0], k[1], k[2]};
+                Float c[3] = {k[1], k[2], k[3]}, cs[3] = {k[4], k[5], k[6]};
                 auto tex = std::make_shared<ConstantTexture<Spectrum>>(Spectrum::FromRGB(c));
-                it = byKd.emplace(k, std::make_shared<MatteMaterial>(tex, sigma, nullptr)).first;
+                std::shared_ptr<Material> mm;
+                if (k[0] == 1.f) {   // Material "plastic" "color Kd" "color Ks" "float roughness" (materials/plastic.cpp:72-84)
+                    auto texS = std::make_shared<ConstantTexture<Spectrum>>(Spectrum::FromRGB(cs));
+                    auto rough = std::make_shared<ConstantTexture<Float>>(k[7]);
+                    mm = std::make_shared<PlasticMaterial>(tex, texS, rough, nullptr, true);
+                } else mm = std::make_shared<MatteMaterial>(tex, sigma, nullptr);
+                it = byKd.emplace(k, mm).first;
             }
             m = it->second;
         }

@@ -162,7 +162,7 @@ class RefAccel:
 
 
 def render(scene, accel_kind, eye, look, up, fov, xres, yres, spp, maxdepth, light_pos, light_I, kd,
-           sampler="random", n_threads=0, tmp_prefix=None, heat=False, prim_kd=None, emitter_L=None):
+           sampler="random", n_threads=0, tmp_prefix=None, heat=False, prim_mat=None, emitter_L=None):
     """The reference's OWN render (SamplerIntegrator::Render + PathIntegrator::Li + Film, oracle/ref/ref_render.cpp)
     of `scene` with a matte material and one point light.  Returns (rgb (yres,xres,3), n_closest, n_shadow)."""
     import tempfile
@@ -171,7 +171,7 @@ def render(scene, accel_kind, eye, look, up, fov, xres, yres, spp, maxdepth, lig
     out = np.zeros((yres, xres, 3), np.float32)
     nc, ns = C.c_uint64(), C.c_uint64()
     hm = np.zeros((6, yres, xres), np.uint32) if heat else None
-    pk = None if prim_kd is None else np.ascontiguousarray(prim_kd, np.float32).reshape(-1, 3)
+    pk = None if prim_mat is None else np.ascontiguousarray(prim_mat, np.float32).reshape(-1, 8)
     el = None if emitter_L is None else np.ascontiguousarray(emitter_L, np.float32)
     with tempfile.TemporaryDirectory() as td:   # the thesis's per-pixel stat dumps (film.cpp:170-264) land here
         pre = (tmp_prefix or os.path.join(td, "ref")).encode()

@@ -22,6 +22,8 @@ CASES = {
     # BASELINE config 1 with the scene's own light and Kd's: sphere AreaLightSource L = 2000 (MIS in EstimateDirect),
     # ground matte (.5 .5 .8), killeroos with the diffuse part of their "plastic" (Kd .4 .2 .2 / .4 .5 .4)
     "killeroo_area": dict(scene="killeroo_simple", res=128, spp=256, maxdepth=5, I=(2000.0,) * 3, kd=(.5, .5, .5), area=True),
+    # BASELINE config 1 as the scene file has it: area light + matte ground + the two "plastic" killeroos
+    "killeroo_full": dict(scene="killeroo_simple", res=128, spp=256, maxdepth=5, I=(2000.0,) * 3, kd=(.5, .5, .5), area=True, plastic=True),
     "sponza": dict(scene="sponza_standin", res=96, spp=256, maxdepth=5, I=(1.0,) * 3, kd=(.5, .5, .5)),
 }
 
@@ -49,8 +51,8 @@ def main():
         if c.get("area"):
             sl = sc["sphere_light"]
             spheres = np.array([list(sl["center"]) + [sl["radius"]]], np.float32)
-            extra = dict(prim_kd=np.concatenate([sc["material_kd"][sc["prim_material"]], np.zeros((1, 3), np.float32)]),
-                         emitter_L=sl["L"])
+            mats = sc["materials"] if c.get("plastic") else np.pad(sc["material_kd"], ((0, 0), (1, 4)))
+            extra = dict(prim_mat=np.concatenate([mats[sc["prim_material"]], np.zeros((1, 8), np.float32)]), emitter_L=sl["L"])
         S = rb.RefScene(tv.reshape(-1, 3), np.arange(3 * len(tv), dtype=np.int32).reshape(-1, 3), spheres=spheres)
         eye, look, up, fov = lookat_of(c["scene"])
         img, nc, ns, heat = rb.render(S, "bvh", eye, look, up, fov, c["res"], c["res"], c["spp"], c["maxdepth"], sc["light"],

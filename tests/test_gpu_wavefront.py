@@ -228,8 +228,12 @@ def test_heatmaps_match_the_references_per_pixel_statistics(gpu):
         assert np.sqrt(((ab - bb) ** 2).mean()) / bb.mean() < 0.04, name
 
 
-def test_area_light_mis_matches_the_references_render(gpu):
-    """BASELINE config 1 with the scene's OWN light: scenes/killeroo-simple's sphere `AreaLightSource "area" L 2000`
+@pytest.mark.parametrize("case,plastic", [("killeroo_area", False), ("killeroo_full", True)])
+def test_area_light_mis_matches_the_references_render(gpu, case, plastic):
+    """killeroo_full = BASELINE config 1 exactly as scenes/killeroo-simple describes it (sphere area light, matte
+    ground, two "plastic" killeroos: Lambertian + Trowbridge-Reitz microfacet lobe with FresnelDielectric(1.5, 1),
+    two-lobe BSDF sampling); killeroo_area = the same with the plastics' diffuse part only.
+    BASELINE config 1 with the scene's OWN light: scenes/killeroo-simple's sphere `AreaLightSource "area" L 2000`
     sampled with multiple importance sampling as EstimateDirect does (light sample -> shadow any-hit ray, BSDF sample
     -> an extra closest-hit MIS ray, emitted radiance for camera rays) and one matte Kd per primitive, against the
     reference's own render of the same setup (tests/golden/ref_render.npz `killeroo_area`).  Statistical bar as above;
@@ -238,16 +242,16 @@ def test_area_light_mis_matches_the_references_render(gpu):
     from b200rt import scenes
     from b200rt.wavefront import film_to_rgb
     g = load_golden("ref_render.npz")
-    res, spp, maxdepth = (int(x) for x in g["killeroo_area_params"])
+    res, spp, maxdepth = (int(x) for x in g[case + "_params"])
     sc = scenes.killeroo_simple(xres=res, yres=res)
-    verts, prim_kind, rows, pm, mats = scenes.with_sphere_light(sc)
+    verts, prim_kind, rows, pm, mats = scenes.with_sphere_light(sc, plastic=plastic)
     acc = gpu.B200Accel(gpu.build_bvh(verts), verts, prim_kind=prim_kind, spheres=rows)
     sl = sc["sphere_light"]
     integ = gpu.WavefrontPathIntegrator(sc["camera"], spp=spp, maxdepth=maxdepth, light_pos=sl["center"], light_I=sl["L"],
                                         seed=4, sphere_light=(sl["radius"], len(verts) - 1), materials=mats, prim_material=pm)
     film, st = integ.Render(acc)
-    rgb, ref = film_to_rgb(film).astype(np.float64), g["killeroo_area_rgb"].astype(np.float64)
-    nc, ns = (int(x) for x in g["killeroo_area_rays"])
+    rgb, ref = film_to_rgb(film).astype(np.float64), g[case + "_rgb"].astype(np.float64)
+    nc, ns = (int(x) for x in g[case + "_rays"])
     assert abs(st["closest_rays"] / nc - 1) < 0.01, (st["closest_rays"], nc)
     assert abs(st["shadow_rays"] / ns - 1) < 0.01, (st["shadow_rays"], ns)
     assert 0 < st["mis_rays"] < st["closest_rays"]

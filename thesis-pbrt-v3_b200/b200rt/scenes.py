@@ -179,14 +179,17 @@ def killeroo_simple(xres=700, yres=700):
     # "plastic" Kd (.4 .2 .2) / (.4 .5 .4) — their diffuse part; index 3 = the emitter's matte Kd 0 (:19)
     prim_material = np.concatenate([np.zeros(4, np.uint8), np.full(nk, 1, np.uint8), np.full(nk, 2, np.uint8)])
     kds = np.array([[.5, .5, .8], [.4, .2, .2], [.4, .5, .4], [0, 0, 0]], np.float32)
+    # the scene's full materials (kind 0 matte / 1 plastic, Kd, Ks, roughness), scenes/killeroo-simple:19,27,40-41,44-45
+    materials = np.array([[0, .5, .5, .8, 0, 0, 0, 0], [1, .4, .2, .2, .5, .5, .5, .025], [1, .4, .5, .4, .3, .3, .3, .15],
+                          [0, 0, 0, 0, 0, 0, 0, 0]], np.float32)
     return dict(name="killeroo-simple", tri_verts=tv, camera=cam, light=np.array([150, 120, 20], np.float32),
                 sphere_light=dict(center=np.array([150, 120, 20], np.float32), radius=3.0, L=np.array([2000.0] * 3, np.float32)),
-                prim_material=prim_material, material_kd=kds,
+                prim_material=prim_material, material_kd=kds, materials=materials,
                 note="reference geometry (fixture); light = the scene's sphere area light (scenes/killeroo-simple:18-24) "
                      "or, for the point-light integrator, a point light at its centre")
 
 
-def with_sphere_light(sc):
+def with_sphere_light(sc, plastic=False):
     """Aggregate of `sc` with its sphere area light appended as the LAST primitive, as pbrtShape adds it to the
     primitive list (scenes/killeroo-simple:18-24): returns (bounds_verts, prim_kind, sphere_rows, prim_material,
     materials).  bounds_verts gives the sphere primitive a stand-in triangle with the sphere's world bound, which is
@@ -203,7 +206,9 @@ def with_sphere_light(sc):
     rows[0, 3], rows[0, 7], rows[0, 11], rows[0, 12] = -c[0], -c[1], -c[2], r
     pm = np.concatenate([sc["prim_material"], np.array([len(sc["material_kd"]) - 1], np.uint8)])
     mats = np.zeros((len(sc["material_kd"]), 8), np.float32)
-    mats[:, 1:4] = sc["material_kd"]
+    mats[:, 1:4] = sc["material_kd"]   # the diffuse part only, or (plastic=True) the scene's own materials
+    if plastic:
+        mats = sc["materials"].copy()
     return verts, prim_kind, rows, pm, mats
 
 

@@ -13,6 +13,7 @@
 #include <vector>
 #include "../../include/b200rt_wavefront.h"
 #include "scene_internal.h"
+#include "wf_bsdf.cuh"
 
 using namespace b200rt;
 
@@ -127,6 +128,130 @@ __global__ void k_camera(const __grid_constant__ WfParams P, uint64_t batchStart
     qPath[slot] = i;
 }
 
+
+// ---- shading of one hit for materials with a glossy lobe (Material "plastic") --------------------------------
+// The same steps as the matte code in k_shade — direct lighting by UniformSampleOneLight / EstimateDirect
+// (integrator.cpp:86-217) and the path's next direction (path.cpp:144-164) — written against the general BSDF
+// of wf_bsdf.cuh (f, Pdf, Sample_f over two lobes).
+struct ShadeOut {
+    bool wantShadow, wantNext, wantMis;
+    float3 so, sd, contrib, no, nd, mo, md, mcontrib, beta;
+};
+struct Frame { float3 s, t, n; };
+__device__ __forceinline__ float3 to_local(const Frame &f, float3 v) {
+    return make_float3(v.x * f.s.x + v.y * f.s.y + v.z * f.s.z, v.x * f.t.x + v.y * f.t.y + v.z * f.t.z, v.x * f.n.x + v.y * f.n.y + v.z * f.n.z);
+}
+__device__ __forceinline__ float3 to_world(const Frame &f, float3 v) {
+    return make_float3(f.s.x * v.x + f.t.x * v.y + f.n.x * v.z, f.s.y * v.x + f.t.y * v.y + f.n.y * v.z, f.s.z * v.x + f.t.z * v.y + f.n.z * v.z);
+}
+// Sphere::Sample(ref, u, &pdf) for a reference point outside the sphere (sphere.cpp:254-291): point + normal on the
+// sphere inside the subtended cone; returns the uniform cone pdf.
+__device__ __forceinline__ float sphere_cone_sample(const WfParams &P, float3 wl /* centre - p */, float d2, float u0, float u1,
+                                                    float3 &pW, float3 &nW) {
+    const float r2 = P.light_radius * P.light_radius;
+    const float dc = sqrtf(d2);
+    const float3 wc = make_float3(wl.x / dc, wl.y / dc, wl.z / dc);
+    float3 wcX;
+    if (fabsf(wc.x) > fabsf(wc.y)) { const float il = 1.f / sqrtf(wc.x * wc.x + wc.z * wc.z); wcX = make_float3(-wc.z * il, 0.f, wc.x * il); }
+    else { const float il = 1.f / sqrtf(wc.y * wc.y + wc.z * wc.z); wcX = make_float3(0.f, wc.z * il, -wc.y * il); }
+    const float3 wcY = make_float3(wc.y * wcX.z - wc.z * wcX.y, wc.z * wcX.x - wc.x * wcX.z, wc.x * wcX.y - wc.y * wcX.x);
+    const float cosThetaMax = sqrtf(fmaxf(0.f, 1.f - r2 / d2));
+    const float cosTheta = (1.f - u0) + u0 * cosThetaMax;
+    const float sinTheta = sqrtf(fmaxf(0.f, 1.f - cosTheta * cosTheta));
+    const float phi = u1 * 2.f * kPi;
+    const float ds = dc * cosTheta - sqrtf(fmaxf(0.f, r2 - dc * dc * sinTheta * sinTheta));
+    const float cosAlpha = (dc * dc + r2 - ds * ds) / (2.f * dc * P.light_radius);
+    const float sinAlpha = sqrtf(fmaxf(0.f, 1.f - cosAlpha * cosAlpha));
+    const float cx = -sinAlpha * cosf(phi), cy = -sinAlpha * sinf(phi), cz = -cosAlpha;
+    nW = make_float3(cx * wcX.x + cy * wcY.x + cz * wc.x, cx * wcX.y + cy * wcY.y + cz * wc.y, cx * wcX.z + cy * wcY.z + cz * wc.z);
+    pW = make_float3(P.light_pos[0] + P.light_radius * nW.x, P.light_pos[1] + P.light_radius * nW.y, P.light_pos[2] + P.light_radius * nW.z);
+    return 1.f / (2.f * kPi * (1.f - cosThetaMax));
+}
+
+__device__ void shade_general(const WfParams &P, const WfMat &m, uint32_t depth, uint32_t pix, uint32_t s, float3 p, float3 pe,
+                              float3 ng, float3 nf, float3 wo, float4 bt, ShadeOut &o) {
+    Frame fr;
+    fr.n = nf;
+    if (fabsf(nf.x) > fabsf(nf.y)) { const float il = 1.f / sqrtf(nf.x * nf.x + nf.z * nf.z); fr.s = make_float3(-nf.z * il, 0.f, nf.x * il); }
+    else { const float il = 1.f / sqrtf(nf.y * nf.y + nf.z * nf.z); fr.s = make_float3(0.f, nf.z * il, -nf.y * il); }
+    fr.t = make_float3(nf.y * fr.s.z - nf.z * fr.s.y, nf.z * fr.s.x - nf.x * fr.s.z, nf.x * fr.s.y - nf.y * fr.s.x);
+    const float3 woL = to_local(fr, wo);
+    const float3 wl = make_float3(P.light_pos[0] - p.x, P.light_pos[1] - p.y, P.light_pos[2] - p.z);
+    const float d2 = wl.x * wl.x + wl.y * wl.y + wl.z * wl.z;
+    const uint32_t dim = 2 + 3 * depth;
+    if (P.light_kind == B200RT_LIGHT_SPHERE) {
+        const float r2 = P.light_radius * P.light_radius;
+        const float3 pO = offset_ray_origin(p, pe, ng, wl);
+        const float dO2 = (pO.x - P.light_pos[0]) * (pO.x - P.light_pos[0]) + (pO.y - P.light_pos[1]) * (pO.y - P.light_pos[1]) +
+                          (pO.z - P.light_pos[2]) * (pO.z - P.light_pos[2]);
+        if (dO2 > r2 && d2 > 0.f) {
+            float3 pW, nW;
+            const float lightPdf = sphere_cone_sample(P, wl, d2, rnd(P.seed, pix, s, 1000 + 4 * depth), rnd(P.seed, pix, s, 1001 + 4 * depth), pW, nW);
+            float3 wi = make_float3(pW.x - p.x, pW.y - p.y, pW.z - p.z);
+            const float wl2 = wi.x * wi.x + wi.y * wi.y + wi.z * wi.z;
+            if (wl2 > 0.f) {
+                const float il = 1.f / sqrtf(wl2);
+                wi.x *= il; wi.y *= il; wi.z *= il;
+                if ((nW.x * -wi.x + nW.y * -wi.y + nW.z * -wi.z) > 0.f) {
+                    const float3 wiL = to_local(fr, wi);
+                    float3 f; float scatPdf;
+                    bsdf_eval(m, woL, wiL, f, scatPdf);
+                    const float c = fabsf(wiL.z);
+                    if (f.x * c > 0.f || f.y * c > 0.f || f.z * c > 0.f) {
+                        const float g = c * ((lightPdf * lightPdf) / (lightPdf * lightPdf + scatPdf * scatPdf)) / lightPdf;
+                        o.contrib = make_float3(bt.x * f.x * P.light_I[0] * g, bt.y * f.y * P.light_I[1] * g, bt.z * f.z * P.light_I[2] * g);
+                        const float3 peL = make_float3(kGamma5 * fabsf(pW.x), kGamma5 * fabsf(pW.y), kGamma5 * fabsf(pW.z));
+                        o.so = offset_ray_origin(p, pe, ng, make_float3(pW.x - p.x, pW.y - p.y, pW.z - p.z));
+                        const float3 tg = offset_ray_origin(pW, peL, nW, make_float3(o.so.x - pW.x, o.so.y - pW.y, o.so.z - pW.z));
+                        o.sd = make_float3(tg.x - o.so.x, tg.y - o.so.y, tg.z - o.so.z);
+                        o.wantShadow = true;
+                    }
+                }
+            }
+            float3 wiL, f; float scatPdf;
+            if (bsdf_sample(m, woL, rnd(P.seed, pix, s, 1002 + 4 * depth), rnd(P.seed, pix, s, 1003 + 4 * depth), wiL, f, scatPdf)) {
+                const float c = fabsf(wiL.z);
+                const float g = c * ((scatPdf * scatPdf) / (scatPdf * scatPdf + lightPdf * lightPdf)) / scatPdf;
+                o.mcontrib = make_float3(bt.x * f.x * P.light_I[0] * g, bt.y * f.y * P.light_I[1] * g, bt.z * f.z * P.light_I[2] * g);
+                o.md = to_world(fr, wiL);
+                o.mo = offset_ray_origin(p, pe, ng, o.md);
+                o.wantMis = true;
+            }
+        }
+    } else if (d2 > 0.f) {   // PointLight::Sample_Li (point.cpp:44-53): Li = I / d^2, pdf = 1
+        const float invd = 1.f / sqrtf(d2);
+        const float3 wiL = to_local(fr, make_float3(wl.x * invd, wl.y * invd, wl.z * invd));
+        float3 f; float scatPdf;
+        bsdf_eval(m, woL, wiL, f, scatPdf);
+        const float g = fabsf(wiL.z) / d2;
+        o.contrib = make_float3(bt.x * f.x * P.light_I[0] * g, bt.y * f.y * P.light_I[1] * g, bt.z * f.z * P.light_I[2] * g);
+        if (o.contrib.x > 0.f || o.contrib.y > 0.f || o.contrib.z > 0.f) {
+            o.so = offset_ray_origin(p, pe, ng, wl);
+            o.sd = make_float3(P.light_pos[0] - o.so.x, P.light_pos[1] - o.so.y, P.light_pos[2] - o.so.z);
+            o.wantShadow = true;
+        }
+    }
+    // the path's next direction: bsdf->Sample_f, beta *= f |cos| / pdf (path.cpp:144-151), Russian roulette (:190-199)
+    float3 wiL, f; float pdf;
+    if (bsdf_sample(m, woL, rnd(P.seed, pix, s, dim), rnd(P.seed, pix, s, dim + 1), wiL, f, pdf)) {
+        const float c = fabsf(wiL.z) / pdf;
+        float3 nb = make_float3(bt.x * f.x * c, bt.y * f.y * c, bt.z * f.z * c);
+        bool alive = nb.x > 0.f || nb.y > 0.f || nb.z > 0.f;
+        const float mx = fmaxf(nb.x, fmaxf(nb.y, nb.z));
+        if (alive && mx < 1.f && depth > 3) {
+            const float q = fmaxf(.05f, 1.f - mx);
+            if (rnd(P.seed, pix, s, dim + 2) < q) alive = false;
+            else { const float k = 1.f / (1.f - q); nb.x *= k; nb.y *= k; nb.z *= k; }
+        }
+        if (alive) {
+            o.beta = nb;
+            o.nd = to_world(fr, wiL);
+            o.no = offset_ray_origin(p, pe, ng, o.nd);
+            o.wantNext = true;
+        }
+    }
+}
+
 // Shade one wavefront (PathIntegrator::Li body for one bounce, path.cpp:89-199; direct lighting =
 // UniformSampleOneLight with one point light, integrator.cpp:86-217; matte BSDF, reflection.h
 // LambertianReflection; CosineSampleHemisphere, sampling.h).
@@ -175,14 +300,32 @@ __global__ void k_shade(const __grid_constant__ WfParams P, uint32_t depth, uint
             if (nl > 0.f && !(__float_as_uint(b.w) & B200RT_PRIM_SPHERE)) {
                 ng.x /= nl; ng.y /= nl; ng.z /= nl;
                 float kdr = P.kd[0], kdg = P.kd[1], kdb = P.kd[2];
+                WfMat gm;
+                gm.glossy = false;
                 if (P.mats) {
-                    const float4 m0 = __ldg(P.mats + 2 * (size_t)__ldg(P.primMat + h.prim));
+                    const uint32_t mi = __ldg(P.primMat + h.prim);
+                    const float4 m0 = __ldg(P.mats + 2 * (size_t)mi), m1 = __ldg(P.mats + 2 * (size_t)mi + 1);
                     kdr = m0.y; kdg = m0.z; kdb = m0.w;
+                    gm.glossy = m0.x == (float)B200RT_MAT_PLASTIC && (m1.x > 0.f || m1.y > 0.f || m1.z > 0.f);
+                    gm.ks[0] = m1.x; gm.ks[1] = m1.y; gm.ks[2] = m1.z; gm.alpha = m1.w;
                 }
                 const float3 wo = make_float3(-rd.x, -rd.y, -rd.z);
                 const float side = (ng.x * wo.x + ng.y * wo.y + ng.z * wo.z) < 0.f ? -1.f : 1.f;
                 const float3 nf = make_float3(side * ng.x, side * ng.y, side * ng.z);  // wo's hemisphere
                 const float4 bt = beta[path];
+                if (gm.glossy) {   // Material "plastic": the general two-lobe BSDF
+                    gm.kd[0] = kdr; gm.kd[1] = kdg; gm.kd[2] = kdb;
+                    gm.diffuse = kdr > 0.f || kdg > 0.f || kdb > 0.f;
+                    uint32_t gx, gy, gs;
+                    path_pixel(P.tl, batchStart + path, gx, gy, gs);
+                    ShadeOut o;
+                    o.wantShadow = o.wantNext = o.wantMis = false;
+                    shade_general(P, gm, depth, gy * P.cam.xres + gx, gs, p, pe, ng, nf, wo, bt, o);
+                    wantShadow = o.wantShadow; so = o.so; sd = o.sd; contrib = o.contrib;
+                    wantMis = o.wantMis; mo = o.mo; md = o.md; mcontrib = o.mcontrib;
+                    wantNext = o.wantNext; no = o.no; nd = o.nd;
+                    if (o.wantNext) beta[path] = make_float4(o.beta.x, o.beta.y, o.beta.z, 0.f);
+                } else {
                 // -- direct lighting: PointLight::Sample_Li (point.cpp:44-53) + matte f * |cos|
                 const float3 wl = make_float3(P.light_pos[0] - p.x, P.light_pos[1] - p.y, P.light_pos[2] - p.z);
                 const float d2 = wl.x * wl.x + wl.y * wl.y + wl.z * wl.z;
@@ -320,6 +463,7 @@ __global__ void k_shade(const __grid_constant__ WfParams P, uint32_t depth, uint
                         wantNext = true;
                     }
                 }
+                }  // matte
             }
         }
     }
@@ -556,12 +700,19 @@ static int render_impl(b200rt_scene *s, const b200rt_render_desc *d, float *film
     }
     if (d->materials) {
         for (uint32_t k = 0; k < d->n_materials; ++k)
-            if (d->materials[8 * k] != (float)B200RT_MAT_MATTE) return set_error(B200RT_EUNSUPPORTED, "material %u: only matte is supported", k);
+            if (d->materials[8 * k] != (float)B200RT_MAT_MATTE && d->materials[8 * k] != (float)B200RT_MAT_PLASTIC)
+                return set_error(B200RT_EUNSUPPORTED, "material %u: only matte and plastic are supported", k);
         if (w->mats_n < d->n_materials) { cudaFree(w->mats); w->mats = nullptr; WCU(cudaMalloc(&w->mats, (size_t)d->n_materials * 32)); w->mats_n = d->n_materials; }
         if (w->primMat_n < s->n_prims) { cudaFree(w->primMat); w->primMat = nullptr; WCU(cudaMalloc(&w->primMat, s->n_prims)); w->primMat_n = s->n_prims; }
         for (uint32_t k = 0; k < s->n_prims; ++k)
             if (d->prim_material[k] >= d->n_materials) return set_error(B200RT_EINVAL, "prim_material[%u] out of range", k);
-        WCU(cudaMemcpyAsync(w->mats, d->materials, (size_t)d->n_materials * 32, cudaMemcpyHostToDevice, st));
+        std::vector<float> mt(d->materials, d->materials + 8 * (size_t)d->n_materials);
+        for (uint32_t k = 0; k < d->n_materials; ++k)
+            if (mt[8 * k] == (float)B200RT_MAT_PLASTIC) {  // TrowbridgeReitzDistribution::RoughnessToAlpha (microfacet.h:123-128), remaproughness true
+                const float x = std::log(std::max(mt[8 * k + 7], 1e-3f));
+                mt[8 * k + 7] = 1.62142f + 0.819955f * x + 0.1734f * x * x + 0.0171201f * x * x * x + 0.000640711f * x * x * x * x;
+            }
+        WCU(cudaMemcpy(w->mats, mt.data(), mt.size() * 4, cudaMemcpyHostToDevice));
         WCU(cudaMemcpyAsync(w->primMat, d->prim_material, s->n_prims, cudaMemcpyHostToDevice, st));
         P.mats = w->mats; P.primMat = w->primMat;
     }

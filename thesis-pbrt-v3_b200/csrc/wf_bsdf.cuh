@@ -1,0 +1,169 @@
+// BSDFs of the wavefront shade stage, in the local shading frame (z = the normal on wo's side, so wo.z >= 0).
+//
+//   Material "matte"   (materials/matte.cpp:44-60, sigma 0)   : LambertianReflection(Kd)
+//   Material "plastic" (materials/plastic.cpp:44-70)           : LambertianReflection(Kd) + MicrofacetReflection(Ks,
+//        TrowbridgeReitzDistribution(alpha, alpha) with alpha = RoughnessToAlpha(roughness), FresnelDielectric(1.5, 1))
+// and the BSDF container's rules for several lobes (reflection.cpp BSDF::f / Pdf / Sample_f: lobe picked uniformly by
+// u[0], pdf = mean of the lobes' pdfs, f = sum of the lobes).  Isotropic lobes only, so any orthonormal frame around
+// the normal is equivalent to the reference's dpdu frame.
+#pragma once
+#include <cuda_runtime.h>
+
+namespace b200rt {
+
+struct WfMat {
+    float kd[3], ks[3];
+    float alpha;     // TrowbridgeReitz alpha (already remapped from "roughness" on the host)
+    bool diffuse;    // !Kd.IsBlack()
+    bool glossy;     // !Ks.IsBlack()
+};
+
+constexpr float kBsdfPi = 3.14159265358979323846f;
+constexpr float kBsdfInvPi = 0.31830988618379067154f;
+constexpr float kOneMinusEpsilon = 0.99999994f;
+
+// FrDielectric (reflection.cpp:47-68)
+__device__ __forceinline__ float fr_dielectric(float cosThetaI, float etaI, float etaT) {
+    cosThetaI = fminf(fmaxf(cosThetaI, -1.f), 1.f);
+    if (!(cosThetaI > 0.f)) { const float t = etaI; etaI = etaT; etaT = t; cosThetaI = fabsf(cosThetaI); }
+    const float sinThetaI = sqrtf(fmaxf(0.f, 1.f - cosThetaI * cosThetaI));
+    const float sinThetaT = etaI / etaT * sinThetaI;
+    if (sinThetaT >= 1.f) return 1.f;
+    const float cosThetaT = sqrtf(fmaxf(0.f, 1.f - sinThetaT * sinThetaT));
+    const float Rparl = ((etaT * cosThetaI) - (etaI * cosThetaT)) / ((etaT * cosThetaI) + (etaI * cosThetaT));
+    const float Rperp = ((etaI * cosThetaI) - (etaT * cosThetaT)) / ((etaI * cosThetaI) + (etaT * cosThetaT));
+    return (Rparl * Rparl + Rperp * Rperp) / 2.f;
+}
+
+// TrowbridgeReitzDistribution, alphax == alphay == a (microfacet.cpp:155-163, 176-184; microfacet.h:54-60)
+__device__ __forceinline__ float tr_D(const float3 wh, float a) {
+    const float cos2 = wh.z * wh.z, sin2 = fmaxf(0.f, 1.f - cos2);
+    const float tan2 = sin2 / cos2;
+    if (isinf(tan2)) return 0.f;
+    const float e = tan2 / (a * a);   // (Cos2Phi + Sin2Phi) / a^2 * tan2Theta
+    return 1.f / (kBsdfPi * a * a * cos2 * cos2 * (1.f + e) * (1.f + e));
+}
+__device__ __forceinline__ float tr_lambda(const float3 w, float a) {
+    const float sin2 = fmaxf(0.f, 1.f - w.z * w.z);
+    const float absTan = fabsf(sqrtf(sin2) / w.z);
+    if (isinf(absTan)) return 0.f;
+    const float at = (a * absTan) * (a * absTan);
+    return (-1.f + sqrtf(1.f + at)) / 2.f;
+}
+// MicrofacetDistribution::Pdf with sampleVisibleArea (microfacet.cpp:338-344)
+__device__ __forceinline__ float tr_pdf(const float3 wo, const float3 wh, float a) {
+    const float g1 = 1.f / (1.f + tr_lambda(wo, a));
+    return tr_D(wh, a) * g1 * fabsf(wo.x * wh.x + wo.y * wh.y + wo.z * wh.z) / fabsf(wo.z);
+}
+// TrowbridgeReitzSample11 + TrowbridgeReitzSample (microfacet.cpp:238-305), visible-normal sampling
+__device__ __forceinline__ float3 tr_sample_wh(const float3 wo, float U1, float U2, float a) {
+    float3 ws = make_float3(a * wo.x, a * wo.y, wo.z);
+    const float il = 1.f / sqrtf(ws.x * ws.x + ws.y * ws.y + ws.z * ws.z);
+    ws.x *= il; ws.y *= il; ws.z *= il;
+    float slope_x, slope_y;
+    const float cosTheta = ws.z;
+    if (cosTheta > .9999f) {
+        const float r = sqrtf(U1 / (1.f - U1)), phi = 6.28318530718f * U2;
+        slope_x = r * cosf(phi); slope_y = r * sinf(phi);
+    } else {
+        const float sinTheta = sqrtf(fmaxf(0.f, 1.f - cosTheta * cosTheta));
+        const float tanTheta = sinTheta / cosTheta;
+        const float aa = 1.f / tanTheta;
+        const float G1 = 2.f / (1.f + sqrtf(1.f + 1.f / (aa * aa)));
+        const float A = 2.f * U1 / G1 - 1.f;
+        float tmp = 1.f / (A * A - 1.f);
+        if (tmp > 1e10f) tmp = 1e10f;
+        const float B = tanTheta;
+        const float D = sqrtf(fmaxf(B * B * tmp * tmp - (A * A - B * B) * tmp, 0.f));
+        const float s1 = B * tmp - D, s2 = B * tmp + D;
+        slope_x = (A < 0.f || s2 > 1.f / tanTheta) ? s1 : s2;
+        float S;
+        if (U2 > 0.5f) { S = 1.f; U2 = 2.f * (U2 - .5f); }
+        else { S = -1.f; U2 = 2.f * (.5f - U2); }
+        const float z = (U2 * (U2 * (U2 * 0.27385f - 0.73369f) + 0.46341f)) /
+                        (U2 * (U2 * (U2 * 0.093073f + 0.309420f) - 1.000000f) + 0.597999f);
+        slope_y = S * z * sqrtf(1.f + slope_x * slope_x);
+    }
+    const float sinT = sqrtf(fmaxf(0.f, 1.f - ws.z * ws.z));
+    const float cosPhi = sinT == 0.f ? 1.f : fminf(fmaxf(ws.x / sinT, -1.f), 1.f);
+    const float sinPhi = sinT == 0.f ? 0.f : fminf(fmaxf(ws.y / sinT, -1.f), 1.f);
+    const float t = cosPhi * slope_x - sinPhi * slope_y;
+    slope_y = sinPhi * slope_x + cosPhi * slope_y;
+    slope_x = t;
+    slope_x *= a; slope_y *= a;
+    float3 wh = make_float3(-slope_x, -slope_y, 1.f);
+    const float ih = 1.f / sqrtf(wh.x * wh.x + wh.y * wh.y + 1.f);
+    wh.x *= ih; wh.y *= ih; wh.z *= ih;
+    return wh;
+}
+
+// MicrofacetReflection::f (reflection.cpp:226-236), scalar part (times Ks)
+__device__ __forceinline__ float glossy_f(const float3 wo, const float3 wi, float a) {
+    const float cosO = fabsf(wo.z), cosI = fabsf(wi.z);
+    float3 wh = make_float3(wi.x + wo.x, wi.y + wo.y, wi.z + wo.z);
+    if (cosI == 0.f || cosO == 0.f) return 0.f;
+    if (wh.x == 0.f && wh.y == 0.f && wh.z == 0.f) return 0.f;
+    const float il = 1.f / sqrtf(wh.x * wh.x + wh.y * wh.y + wh.z * wh.z);
+    wh.x *= il; wh.y *= il; wh.z *= il;
+    const float F = fr_dielectric(wi.x * wh.x + wi.y * wh.y + wi.z * wh.z, 1.5f, 1.f);   // FresnelDielectric(1.5f, 1.f), plastic.cpp:59
+    const float G = 1.f / (1.f + tr_lambda(wo, a) + tr_lambda(wi, a));
+    return tr_D(wh, a) * G * F / (4.f * cosI * cosO);
+}
+__device__ __forceinline__ float glossy_pdf(const float3 wo, const float3 wi, float a) {
+    if (!(wo.z * wi.z > 0.f)) return 0.f;
+    float3 wh = make_float3(wo.x + wi.x, wo.y + wi.y, wo.z + wi.z);
+    const float il = 1.f / sqrtf(wh.x * wh.x + wh.y * wh.y + wh.z * wh.z);
+    wh.x *= il; wh.y *= il; wh.z *= il;
+    return tr_pdf(wo, wh, a) / (4.f * (wo.x * wh.x + wo.y * wh.y + wo.z * wh.z));
+}
+
+// BSDF::f and BSDF::Pdf (reflection.cpp): both lobes are reflective, so f = 0 across the surface.
+__device__ __forceinline__ void bsdf_eval(const WfMat &m, const float3 wo, const float3 wi, float3 &f, float &pdf) {
+    f = make_float3(0.f, 0.f, 0.f);
+    pdf = 0.f;
+    const int n = (m.diffuse ? 1 : 0) + (m.glossy ? 1 : 0);
+    if (n == 0) return;
+    const bool same = wo.z * wi.z > 0.f;
+    if (m.diffuse) {
+        if (same) { f.x += m.kd[0] * kBsdfInvPi; f.y += m.kd[1] * kBsdfInvPi; f.z += m.kd[2] * kBsdfInvPi; pdf += fabsf(wi.z) * kBsdfInvPi; }
+    }
+    if (m.glossy) {
+        if (same) { const float g = glossy_f(wo, wi, m.alpha); f.x += m.ks[0] * g; f.y += m.ks[1] * g; f.z += m.ks[2] * g; }
+        pdf += glossy_pdf(wo, wi, m.alpha);
+    }
+    pdf /= (float)n;
+}
+
+// BSDF::Sample_f (reflection.cpp): false = the sample carries nothing (pdf == 0 or f black).
+__device__ __forceinline__ bool bsdf_sample(const WfMat &m, const float3 wo, float u0, float u1, float3 &wi, float3 &f, float &pdf) {
+    const int n = (m.diffuse ? 1 : 0) + (m.glossy ? 1 : 0);
+    if (n == 0) return false;
+    int comp = (int)floorf(u0 * n);
+    if (comp > n - 1) comp = n - 1;
+    u0 = fminf(u0 * n - comp, kOneMinusEpsilon);
+    const bool pickGlossy = m.glossy && (!m.diffuse || comp == 1);
+    if (!pickGlossy) {
+        // BxDF::Sample_f: CosineSampleHemisphere via ConcentricSampleDisk (sampling.cpp)
+        const float a0 = 2.f * u0 - 1.f, a1 = 2.f * u1 - 1.f;
+        float dx = 0.f, dy = 0.f;
+        if (a0 != 0.f || a1 != 0.f) {
+            float r, th;
+            if (fabsf(a0) > fabsf(a1)) { r = a0; th = (kBsdfPi / 4.f) * (a1 / a0); }
+            else { r = a1; th = (kBsdfPi / 2.f) - (kBsdfPi / 4.f) * (a0 / a1); }
+            dx = r * cosf(th); dy = r * sinf(th);
+        }
+        wi = make_float3(dx, dy, sqrtf(fmaxf(0.f, 1.f - dx * dx - dy * dy)));
+        if (wi.z * kBsdfInvPi == 0.f) return false;
+    } else {
+        if (wo.z == 0.f) return false;
+        const float3 wh = tr_sample_wh(wo, u0, u1, m.alpha);
+        const float d = wo.x * wh.x + wo.y * wh.y + wo.z * wh.z;
+        wi = make_float3(-wo.x + 2.f * d * wh.x, -wo.y + 2.f * d * wh.y, -wo.z + 2.f * d * wh.z);   // Reflect(wo, wh)
+        if (!(wo.z * wi.z > 0.f)) return false;
+        if (tr_pdf(wo, wh, m.alpha) / (4.f * d) == 0.f) return false;
+    }
+    bsdf_eval(m, wo, wi, f, pdf);
+    return pdf > 0.f && (f.x > 0.f || f.y > 0.f || f.z > 0.f);
+}
+
+}  // namespace b200rt
