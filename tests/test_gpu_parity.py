@@ -234,3 +234,66 @@ def test_full_size_properties(gpu):
     orc = ob.OracleAccel(acc.tree, v)
     idx = np.random.default_rng(0).choice(len(rays), 200000, replace=False)
     _same_hits(h[idx], orc.intersect(rays[idx], n_threads=8))
+
+
+@pytest.mark.parametrize("kind", ["bvh", "kdtree"])
+def test_degenerate_rays(gpu, kind):
+    """Rays the reference never rejects up front: zero direction, NaN / infinite components, tMax of 0, negative or
+    NaN.  Whatever the reference's float arithmetic makes of them (NaN compares false, 0 * inf = NaN ...), the
+    kernels make the same: compared with the oracle restatement bit for bit."""
+    from b200rt import scenes
+    v = scenes.soup(1500, seed=8)
+    acc = gpu.MakeAccelerator(kind, v)
+    orc = ob.OracleAccel(acc.tree, v)
+    rays = _rays(4096, 77)
+    n = len(rays)
+    nan, inf = np.float32(np.nan), np.float32(np.inf)
+    rays[0:n:16, 4:7] = 0                         # zero direction
+    rays[1:n:16, 4] = nan                         # NaN direction component
+    rays[2:n:16, 0] = nan                         # NaN origin component
+    rays[3:n:16, 3] = 0                           # tMax = 0
+    rays[4:n:16, 3] = -1                          # negative tMax
+    rays[5:n:16, 3] = nan                         # NaN tMax
+    rays[6:n:16, 5] = inf                         # infinite direction component
+    rays[7:n:16, 1] = -inf                        # infinite origin component
+    rays[8:n:16, 4:7] *= np.float32(1e-30)        # denormal-scale direction
+    rays[9:n:16, 4:6] = 0                         # axis-aligned along z
+    h, o = acc.Intersect(rays), orc.intersect(rays)
+    assert np.array_equal(h["prim"], o["prim"])
+    for f in ("t", "b0", "b1", "b2"):
+        # a NaN stays a NaN on both sides (x86 and the GPU differ only in the NaN's sign/payload bits: 0xffc00000 vs
+        # 0x7fffffff); every other value is bit-identical
+        nn = np.isnan(o[f])
+        assert np.array_equal(np.isnan(h[f]), nn), f
+        assert np.array_equal(h[f].view(np.uint32)[~nn], o[f].view(np.uint32)[~nn]), f
+    assert np.isnan(o["t"]).sum() > 100   # the reference does report "hits" at t = NaN for such rays; so do we
+    assert np.array_equal(acc.IntersectP(rays), orc.intersect_p(rays))
+
+
+def test_more_than_2pow30_rays(gpu):
+    """Maximum sizes: one call with more than 2^30 rays (the persistent kernels index rays with 32 bits, so the
+    library splits the launch; b200rt.cu launch_trace).  2^30 + 777 device-resident rays = a 2^20-ray block tiled
+    1024 times + a tail, so the expected answer is the block's answer tiled."""
+    import torch
+    from b200rt import scenes
+    v = scenes.soup(20000, seed=2)
+    acc = gpu.MakeAccelerator("bvh", v)
+    block = scenes.random_rays(acc.WorldBound(), 1 << 20, seed=4)
+    want = acc.IntersectP(block)
+    assert 0.05 < want.mean() < 0.95
+    n = (1 << 30) + 777
+    free, _ = torch.cuda.mem_get_info()
+    if free < 40 * (1 << 30):
+        pytest.skip("needs 40 GB of free HBM")
+    d_block = torch.from_numpy(block).cuda()
+    rays = torch.empty((n, 8), dtype=torch.float32, device="cuda")
+    rays[: 1 << 30].view(1024, 1 << 20, 8).copy_(d_block.unsqueeze(0).expand(1024, -1, -1))
+    rays[1 << 30:] = d_block[:777]
+    occ = torch.full((n,), 7, dtype=torch.uint8, device="cuda")
+    acc.intersect_p_ptr(rays.data_ptr(), n, occ.data_ptr(), torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    d_want = torch.from_numpy(want).cuda()
+    assert torch.equal(occ[: 1 << 30].view(1024, 1 << 20), d_want.unsqueeze(0).expand(1024, -1))
+    assert torch.equal(occ[1 << 30:], d_want[:777])
+    del rays, occ
+    torch.cuda.empty_cache()
