@@ -22,13 +22,15 @@ acc = b200rt.MakeAccelerator("bvh", sc["tri_verts"])
 rays = torch.from_numpy(scenes.random_rays(acc.WorldBound(), 1 << 22)).pin_memory()
 hits = torch.empty((1 << 22, 5), dtype=torch.int32).pin_memory()
 occ = torch.empty(1 << 22, dtype=torch.uint8).pin_memory()
-for chunk in (65536, 131072, 262144, 524288, 1048576):
+N = int(os.environ.get("E2E_N", 1 << 22))
+for chunk, ramp in ((131072, 0), (131072, 1), (262144, 0), (262144, 1), (524288, 0), (524288, 1)):
     os.environ["B200RT_PIPE_CHUNK"] = str(chunk)
+    os.environ["B200RT_PIPE_RAMP"] = str(ramp)
     b200rt.init(0)
-    for nm, fn in (("closest", lambda: acc.intersect_ptr(rays.data_ptr(), 1 << 22, hits.data_ptr(), st)),
-                   ("any", lambda: acc.intersect_p_ptr(rays.data_ptr(), 1 << 22, occ.data_ptr(), st))):
+    for nm, fn in (("closest", lambda: acc.intersect_ptr(rays.data_ptr(), N, hits.data_ptr(), st)),
+                   ("any", lambda: acc.intersect_p_ptr(rays.data_ptr(), N, occ.data_ptr(), st))):
         fn(); fn(); torch.cuda.synchronize()
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         a.record(); [fn() for _ in range(5)]; b.record(); torch.cuda.synchronize()
         ms = a.elapsed_time(b) / 5
-        print("chunk %8d %-7s %.3f ms = %.0f Mrays/s (H2D %.1f GB/s)" % (chunk, nm, ms, (1 << 22) / ms / 1e3, (1 << 27) / ms / 1e6), flush=True)
+        print("n %8d chunk %8d ramp %d %-7s %.3f ms = %.0f Mrays/s (H2D %.1f GB/s)" % (N, chunk, ramp, nm, ms, N / ms / 1e3, 32 * N / ms / 1e6), flush=True)

@@ -63,6 +63,7 @@ static const void *bvh_fn(bool any) {
     return (const void *)f;
 }  // kd/RBSP/BSP todo entries kept in shared memory (B200RT_SSTACK_BSP)
 #define B200RT_PIPE_CHUNK_MAX (1024u * 1024u)
+static int g_pipe_ramp = 1;                   // B200RT_PIPE_RAMP=0: uniform chunks (A/B)
 static uint32_t g_pipe_chunk = 256u * 1024u;  // rays per pipeline stage (B200RT_PIPE_CHUNK overrides, <= 1 Mi)
 
 extern "C" const char *b200rt_last_error(void) { return g_err; }
@@ -84,6 +85,7 @@ extern "C" int b200rt_init(int device) {
     if (const char *e = getenv("B200RT_KERNEL")) g_use_baseline = std::strcmp(e, "baseline") == 0;
     if (const char *e = getenv("B200RT_THRESH")) g_thresh = (uint32_t)atoi(e);
     if (const char *e = getenv("B200RT_PIPE_CHUNK")) g_pipe_chunk = std::min<uint32_t>(B200RT_PIPE_CHUNK_MAX, std::max(1024, atoi(e)));
+    if (const char *e = getenv("B200RT_PIPE_RAMP")) g_pipe_ramp = atoi(e);
     if (const char *e = getenv("B200RT_BVH_STEPS")) g_bvh_steps = std::max(1, atoi(e));
     if (const char *e = getenv("B200RT_PERSIST_BSP")) g_persist_bsp = atoi(e);
     if (const char *e = getenv("B200RT_SSTACK_BSP")) g_sstack_bsp = (uint32_t)std::min(64, std::max(0, atoi(e)));
@@ -543,10 +545,19 @@ static int run_pipelined(b200rt_scene *s, const b200rt_ray *rays, uint64_t n, vo
     }
     CU(cudaEventRecord(s->ev_start, user));
     for (auto &l : s->lanes) CU(cudaStreamWaitEvent(l.st, s->ev_start, 0));
-    int k = 0;
-    for (uint64_t off = 0; off < n; off += g_pipe_chunk, k = (k + 1) % 3) {
+    // Chunk schedule: a short head (c/4, c/2) so the first kernel starts after 1/4 of a chunk's copy time, full chunks
+    // in the middle, and the last chunk split in two so the un-overlapped tail (last kernel + last D2H) is short too.
+    int k = 0, idx = 0;
+    uint64_t m = 0;
+    for (uint64_t off = 0; off < n; off += m, k = (k + 1) % 3, ++idx) {
         b200rt_scene::Lane &l = s->lanes[k];
-        const uint64_t m = std::min<uint64_t>(g_pipe_chunk, n - off);
+        const uint64_t rem = n - off, c = g_pipe_chunk;
+        m = std::min<uint64_t>(c, rem);
+        if (g_pipe_ramp) {
+            if (idx == 0) m = std::min<uint64_t>(rem, std::max<uint64_t>(c / 4, 1024));
+            else if (idx == 1) m = std::min<uint64_t>(rem, std::max<uint64_t>(c / 2, 1024));
+            else if (rem <= c && rem > c / 2) m = rem / 2;
+        }
         CU(cudaMemcpyAsync(l.d_in, rays + off, m * sizeof(b200rt_ray), cudaMemcpyHostToDevice, l.st));
         int rc = launch_trace(s, (const float4 *)l.d_in, m, nullptr, any ? nullptr : (b200rt_hit *)l.d_out,
                               any ? (uint8_t *)l.d_out : nullptr, any, nullptr, l.st);

@@ -255,6 +255,9 @@ __device__ void shade_general(const WfParams &P, const WfMat &m, uint32_t depth,
 // Shade one wavefront (PathIntegrator::Li body for one bounce, path.cpp:89-199; direct lighting =
 // UniformSampleOneLight with one point light, integrator.cpp:86-217; matte BSDF, reflection.h
 // LambertianReflection; CosineSampleHemisphere, sampling.h).
+// FULL = false: the lean instantiation for one point light + one matte Kd (the bench workload); FULL = true adds the
+// sphere area light with MIS, the per-primitive material table and the plastic BSDF.
+template <bool FULL>
 __global__ void k_shade(const __grid_constant__ WfParams P, uint32_t depth, uint64_t batchStart,
                         const uint32_t *__restrict__ nCur, const float4 *__restrict__ rays,
                         const uint32_t *__restrict__ qPath, const b200rt_hit *__restrict__ hits,
@@ -263,7 +266,7 @@ __global__ void k_shade(const __grid_constant__ WfParams P, uint32_t depth, uint
                         float4 *L, float4 *misRays, uint32_t *misPath, float4 *misContrib, uint32_t *nMis) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     const uint32_t n = *nCur;
-    const bool area = P.light_kind == B200RT_LIGHT_SPHERE;
+    const bool area = FULL && P.light_kind == B200RT_LIGHT_SPHERE;
     bool wantShadow = false, wantNext = false, wantMis = false;
     float3 so = make_float3(0, 0, 0), sd = so, no = so, nd = so, contrib = so, mo = so, md = so, mcontrib = so;
     uint32_t path = 0;
@@ -302,7 +305,7 @@ __global__ void k_shade(const __grid_constant__ WfParams P, uint32_t depth, uint
                 float kdr = P.kd[0], kdg = P.kd[1], kdb = P.kd[2];
                 WfMat gm;
                 gm.glossy = false;
-                if (P.mats) {
+                if (FULL && P.mats) {
                     const uint32_t mi = __ldg(P.primMat + h.prim);
                     const float4 m0 = __ldg(P.mats + 2 * (size_t)mi), m1 = __ldg(P.mats + 2 * (size_t)mi + 1);
                     kdr = m0.y; kdg = m0.z; kdb = m0.w;
@@ -313,7 +316,7 @@ __global__ void k_shade(const __grid_constant__ WfParams P, uint32_t depth, uint
                 const float side = (ng.x * wo.x + ng.y * wo.y + ng.z * wo.z) < 0.f ? -1.f : 1.f;
                 const float3 nf = make_float3(side * ng.x, side * ng.y, side * ng.z);  // wo's hemisphere
                 const float4 bt = beta[path];
-                if (gm.glossy) {   // Material "plastic": the general two-lobe BSDF
+                if (FULL && gm.glossy) {   // Material "plastic": the general two-lobe BSDF
                     gm.kd[0] = kdr; gm.kd[1] = kdg; gm.kd[2] = kdb;
                     gm.diffuse = kdr > 0.f || kdg > 0.f || kdb > 0.f;
                     uint32_t gx, gy, gs;
@@ -779,7 +782,7 @@ static int render_impl(b200rt_scene *s, const b200rt_render_desc *d, float *film
                 g_launches.fetch_add(1);
             }
             if (depth == d->max_depth) break;  // path.cpp:110: the last intersection is found, then the path ends
-            k_shade<<<gridSlots, TB, 0, st>>>(P, depth, start, w->counts + 2 * depth, w->rays[cur], w->qPath[cur], w->hits,
+            (area || P.mats ? k_shade<true> : k_shade<false>)<<<gridSlots, TB, 0, st>>>(P, depth, start, w->counts + 2 * depth, w->rays[cur], w->qPath[cur], w->hits,
                                               s->d_prim_tris, w->beta, w->rays[cur ^ 1], w->qPath[cur ^ 1],
                                               w->counts + 2 * (depth + 1), w->shRays, w->shPath, w->shContrib,
                                               w->counts + 2 * depth + 1, w->L, w->misRays, w->misPath, w->misContrib,
