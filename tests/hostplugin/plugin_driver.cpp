@@ -101,6 +101,8 @@ extern "C" int plugin_intersect_p_batch(const ref_accel *a, const float *rays, u
 #include "filters/box.h"
 #include "lights/point.h"
 #include "materials/matte.h"
+#include "materials/plastic.h"
+#include "lights/diffuse.h"
 #include "samplers/random.h"
 #include "textures/constant.h"
 #include "b200integrator.h"
@@ -109,7 +111,9 @@ std::shared_ptr<pbrt::Shape> shape_of(const pbrt::Primitive *p);   // plugin_sha
 
 extern "C" int plugin_render(ref_scene *s, const char *tree, const float *cam, int xres, int yres, int spp, int maxdepth,
                              const float *light_pos, const float *light_I, const float *kd, int seed, int rank, int world,
-                             const char *tmp_prefix, float *out_rgb, uint64_t *n_closest, uint64_t *n_shadow) {
+                             const char *tmp_prefix, float *out_rgb, uint64_t *n_closest, uint64_t *n_shadow,
+                             const float *prim_mat /* nullable: 8 floats per primitive, as in ref_render */,
+                             const float *emitter_L /* nullable: the LAST primitive (a sphere) is an area light */) {
     PbrtOptions.quiet = true;
     Float rgb[3] = {kd[0], kd[1], kd[2]};
     auto Kd = std::make_shared<ConstantTexture<Spectrum>>(Spectrum::FromRGB(rgb));
@@ -117,7 +121,36 @@ extern "C" int plugin_render(ref_scene *s, const char *tree, const float *cam, i
     auto matte = std::make_shared<MatteMaterial>(Kd, sigma, nullptr);
     MediumInterface mi;
     std::vector<std::shared_ptr<Primitive>> prims;
-    for (auto &p : s->prims) prims.push_back(std::make_shared<GeometricPrimitive>(shape_of(p.get()), matte, nullptr, mi));
+    std::shared_ptr<AreaLight> area;
+    std::map<std::array<float, 8>, std::shared_ptr<Material>> byRec;
+    for (size_t i = 0; i < s->prims.size(); ++i) {
+        std::shared_ptr<Shape> shape = shape_of(s->prims[i].get());
+        std::shared_ptr<Material> m = matte;
+        if (prim_mat) {
+            std::array<float, 8> k;
+            std::memcpy(k.data(), prim_mat + 8 * i, sizeof(float) * 8);
+            auto it = byRec.find(k);
+            if (it == byRec.end()) {
+                Float c[3] = {k[1], k[2], k[3]}, cs[3] = {k[4], k[5], k[6]};
+                auto tex = std::make_shared<ConstantTexture<Spectrum>>(Spectrum::FromRGB(c));
+                std::shared_ptr<Material> mm;
+                if (k[0] == 1.f)
+                    mm = std::make_shared<PlasticMaterial>(tex, std::make_shared<ConstantTexture<Spectrum>>(Spectrum::FromRGB(cs)),
+                                                           std::make_shared<ConstantTexture<Float>>(k[7]), nullptr, true);
+                else mm = std::make_shared<MatteMaterial>(tex, sigma, nullptr);
+                it = byRec.emplace(k, mm).first;
+            }
+            m = it->second;
+        }
+        std::shared_ptr<AreaLight> al;
+        if (emitter_L && i + 1 == s->prims.size()) {
+            Float z[3] = {0, 0, 0}, le[3] = {emitter_L[0], emitter_L[1], emitter_L[2]};
+            m = std::make_shared<MatteMaterial>(std::make_shared<ConstantTexture<Spectrum>>(Spectrum::FromRGB(z)), sigma, nullptr);
+            area = std::make_shared<DiffuseAreaLight>(*shape->ObjectToWorld, mi, Spectrum::FromRGB(le), 1, shape, false);
+            al = area;
+        }
+        prims.push_back(std::make_shared<GeometricPrimitive>(shape, m, al, mi));
+    }
     ParamSet aps;
     std::unique_ptr<std::string[]> t(new std::string[1]);
     t[0] = tree;
@@ -127,7 +160,8 @@ extern "C" int plugin_render(ref_scene *s, const char *tree, const float *cam, i
     Float li[3] = {light_I[0], light_I[1], light_I[2]};
     Transform l2w = Translate(Vector3f(light_pos[0], light_pos[1], light_pos[2]));
     std::vector<std::shared_ptr<Light>> lights;
-    lights.push_back(std::make_shared<PointLight>(l2w, mi, Spectrum::FromRGB(li)));
+    if (area) lights.push_back(area);
+    else lights.push_back(std::make_shared<PointLight>(l2w, mi, Spectrum::FromRGB(li)));
     Scene scene(accel, lights);
     std::unique_ptr<Filter> filter(new BoxFilter(Vector2f(0.5f, 0.5f)));
     Film *film = new Film(Point2i(xres, yres), Bounds2f(Point2f(0, 0), Point2f(1, 1)), std::move(filter), 35.f,

@@ -1,7 +1,38 @@
 // b200integrator.cpp — see b200integrator.h.  Host-side glue only: the frame is rendered by b200rt_render on the B200.
+#include <algorithm>
+#include <array>
+#include <atomic>
+#include <cmath>
+#include <cstdint>
 #include <cstdlib>
 #include <cstring>
+#include <fstream>
+#include <functional>
+#include <iostream>
+#include <limits>
+#include <list>
+#include <map>
+#include <memory>
+#include <mutex>
+#include <set>
+#include <sstream>
+#include <string>
+#include <thread>
+#include <unordered_map>
+#include <utility>
 #include <vector>
+#include <glog/logging.h>
+
+// The point-light / matte case reads the scene through pbrt's public interfaces only.  The sphere area light and
+// "plastic" need three things that have no accessor (inside the reference tree: `friend class B200WavefrontIntegrator;`):
+// GeometricPrimitive::shape + Sphere::radius (the emitter's geometry) and PlasticMaterial::Kd/Ks/roughness.
+#define private public
+#define protected public
+#include "core/primitive.h"
+#include "shapes/sphere.h"
+#include "materials/plastic.h"
+#undef private
+#undef protected
 
 #include "b200integrator.h"
 #include "b200accel.h"
@@ -60,6 +91,7 @@ bool lambertianKd(const Material *m, Float kd[3]) {
     m->ComputeScatteringFunctions(&si, arena, TransportMode::Radiance, true);
     if (!si.bsdf) return false;
     const int all = si.bsdf->NumComponents(BSDF_ALL);
+    if (all == 0) { kd[0] = kd[1] = kd[2] = 0; return true; }   // Material "matte" Kd 0 adds no lobe (matte.cpp:52-58)
     if (all != 1 || si.bsdf->NumComponents(BxDFType(BSDF_REFLECTION | BSDF_DIFFUSE)) != 1) return false;
     const Vector3f w(0, 0, 1);
     Float rgb[3];
@@ -94,42 +126,86 @@ void B200WavefrontIntegrator::Render(const Scene &scene) {
         Error("b200wavefront: pixel filters wider than one pixel are not supported (use PixelFilter \"box\")");
         return;
     }
-    // one point light (LightSource "point"): position and intensity through Light::Sample_Li (lights/point.cpp:44-53)
-    if (scene.lights.size() != 1 || !(scene.lights[0]->flags & (int)LightFlags::DeltaPosition)) {
-        Error("b200wavefront: exactly one point light is supported");
-        return;
-    }
-    {
+    // the light: LightSource "point" (through Light::Sample_Li, lights/point.cpp:44-53) or AreaLightSource "area" on
+    // a full Shape "sphere" that is a primitive of the aggregate (lights/diffuse.cpp, scenes/killeroo-simple:18-24)
+    if (scene.lights.size() != 1) { Error("b200wavefront: exactly one light is supported"); return; }
+    const Light *light = scene.lights[0].get();
+    if (light->flags & (int)LightFlags::DeltaPosition) {
         Interaction ref(Point3f(0, 0, 0), Normal3f(0, 0, 1), Vector3f(0, 0, 0), Vector3f(0, 0, 1), 0, MediumInterface());
         Vector3f wi;
         Float pdf;
         VisibilityTester vis;
-        const Spectrum Li = scene.lights[0]->Sample_Li(ref, Point2f(0.5f, 0.5f), &wi, &pdf, &vis);
+        const Spectrum Li = light->Sample_Li(ref, Point2f(0.5f, 0.5f), &wi, &pdf, &vis);
         const Point3f pl = vis.P1().p;
         const Float d2 = (pl - Point3f(0, 0, 0)).LengthSquared();
         Float rgb[3];
         Spectrum(Li * d2).ToRGB(rgb);
         d.light_pos[0] = pl.x; d.light_pos[1] = pl.y; d.light_pos[2] = pl.z;
         for (int i = 0; i < 3; ++i) d.light_I[i] = rgb[i];
+    } else if (light->flags & (int)LightFlags::Area) {
+        int lp = -1;
+        for (size_t i = 0; i < accel->primitiveCount(); ++i)
+            if (accel->primitive((uint32_t)i)->GetAreaLight() == light) {
+                if (lp >= 0) { Error("b200wavefront: the area light must sit on ONE sphere primitive"); return; }
+                lp = (int)i;
+            }
+        const GeometricPrimitive *gp = lp < 0 ? nullptr : dynamic_cast<const GeometricPrimitive *>(accel->primitive((uint32_t)lp).get());
+        const Sphere *sp = gp ? dynamic_cast<const Sphere *>(gp->shape.get()) : nullptr;
+        if (!sp) { Error("b200wavefront: the area light's shape must be a sphere inside the b200 aggregate"); return; }
+        const AreaLight *al = static_cast<const AreaLight *>(light);
+        Interaction it;
+        it.n = Normal3f(0, 0, 1);
+        Float le[3];
+        al->L(it, Vector3f(0, 0, 1)).ToRGB(le);
+        if (!al->L(it, Vector3f(0, 0, -1)).IsBlack()) { Error("b200wavefront: two-sided area lights are not supported"); return; }
+        const Point3f c = (*sp->ObjectToWorld)(Point3f(0, 0, 0));
+        d.light_kind = B200RT_LIGHT_SPHERE;
+        d.light_radius = sp->radius;
+        d.light_prim = (uint32_t)lp;
+        d.light_pos[0] = c.x; d.light_pos[1] = c.y; d.light_pos[2] = c.z;
+        for (int i = 0; i < 3; ++i) d.light_I[i] = le[i];
+    } else {
+        Error("b200wavefront: only a point light or a sphere area light is supported");
+        return;
     }
-    // one Lambertian Kd shared by every primitive (Material "matte" with a constant Kd, sigma 0)
+    // materials: Material "matte" (constant Kd, sigma 0; measured through the public BSDF) and Material "plastic"
+    // (constant Kd / Ks / roughness, remaproughness true), one record per distinct Material object
+    std::vector<float> mats;
+    std::vector<uint8_t> primMat(accel->primitiveCount(), 0);
     {
-        const Material *seen = nullptr;
-        bool have = false;
+        std::map<const Material *, int> seen;
+        SurfaceInteraction si(Point3f(0, 0, 0), Vector3f(0, 0, 0), Point2f(0.5f, 0.5f), Vector3f(0, 0, 1), Vector3f(1, 0, 0),
+                              Vector3f(0, 1, 0), Normal3f(0, 0, 0), Normal3f(0, 0, 0), 0, nullptr);
         for (size_t i = 0; i < accel->primitiveCount(); ++i) {
             const Material *m = accel->primitive((uint32_t)i)->GetMaterial();
-            if (!m || m == seen) continue;
-            Float kd[3];
-            if (!lambertianKd(m, kd)) { Error("b200wavefront: only Lambertian \"matte\" materials are supported"); return; }
-            if (have && (kd[0] != d.kd[0] || kd[1] != d.kd[1] || kd[2] != d.kd[2])) {
-                Error("b200wavefront: one Kd for the whole scene is supported so far");
-                return;
+            if (!m) { Error("b200wavefront: primitive %d has no material", (int)i); return; }
+            auto it = seen.find(m);
+            if (it == seen.end()) {
+                if (seen.size() >= 256) { Error("b200wavefront: more than 256 materials"); return; }
+                float rec[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+                if (const PlasticMaterial *pm = dynamic_cast<const PlasticMaterial *>(m)) {
+                    if (pm->bumpMap || !pm->remapRoughness) { Error("b200wavefront: plastic with bump map / unremapped roughness is not supported"); return; }
+                    Float kd[3], ks[3];
+                    Spectrum(pm->Kd->Evaluate(si).Clamp()).ToRGB(kd);
+                    Spectrum(pm->Ks->Evaluate(si).Clamp()).ToRGB(ks);
+                    rec[0] = (float)B200RT_MAT_PLASTIC;
+                    for (int c = 0; c < 3; ++c) { rec[1 + c] = kd[c]; rec[4 + c] = ks[c]; }
+                    rec[7] = pm->roughness->Evaluate(si);
+                } else {
+                    Float kd[3];
+                    if (!lambertianKd(m, kd)) { Error("b200wavefront: only \"matte\" and \"plastic\" materials are supported"); return; }
+                    for (int c = 0; c < 3; ++c) rec[1 + c] = kd[c];
+                }
+                it = seen.emplace(m, (int)seen.size()).first;
+                mats.insert(mats.end(), rec, rec + 8);
             }
-            std::memcpy(d.kd, kd, sizeof(kd));
-            have = true;
-            seen = m;
+            primMat[i] = (uint8_t)it->second;
         }
-        if (!have) { Error("b200wavefront: no material"); return; }
+        if (mats.size() == 8 && mats[0] == 0.f && d.light_kind == B200RT_LIGHT_POINT) {
+            for (int c = 0; c < 3; ++c) d.kd[c] = mats[1 + c];   // one matte Kd: the lean kernel path
+        } else {
+            d.materials = mats.data(); d.n_materials = (uint32_t)(mats.size() / 8); d.prim_material = primMat.data();
+        }
     }
     d.spp = (uint32_t)sampler->samplesPerPixel;
     d.max_depth = (uint32_t)maxDepth;

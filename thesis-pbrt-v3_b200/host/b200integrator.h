@@ -4,9 +4,10 @@
 //   class Integrator { virtual void Render(const Scene &scene) = 0; }            src/core/integrator.h:52-58
 //   SamplerIntegrator::Render (tile / pixel / sample loops)                       src/core/integrator.cpp:230-360
 //   PathIntegrator(maxDepth, camera, sampler, pixelBounds, ...) + CreatePathIntegrator   src/integrators/path.cpp:206-240
-// and hands the frame to b200rt_render (include/b200rt_wavefront.h).  Everything it needs from the scene is read
-// through pbrt's PUBLIC interfaces (Camera::GenerateRay, Light::Sample_Li, Material::ComputeScatteringFunctions +
-// BSDF::f, Film::SetImage / WriteImage): no private member of the reference is touched here.
+// and hands the frame to b200rt_render (include/b200rt_wavefront.h).  The camera, a point light, matte materials and
+// the film are read / written through pbrt's PUBLIC interfaces (Camera::GenerateRay, Light::Sample_Li,
+// Material::ComputeScatteringFunctions + BSDF::f, Film::SetImage / WriteImage); the sphere area light's geometry and
+// PlasticMaterial's parameters have no accessors and are read as b200integrator.cpp explains.
 //
 // The branch a maintainer adds to RenderOptions::MakeIntegrator (api.cpp:1895-1945, before the final `else`):
 //     else if (IntegratorName == "b200wavefront")
