@@ -55,19 +55,39 @@ extern "C" int ref_last_image(float *out_rgb, int *xres, int *yres) {
 }
 
 namespace {
-// Counts the calls that reach the aggregate (what Scene::Intersect/IntersectP count, scene.cpp:41-52).
+// Counts the calls that reach the aggregate (what Scene::Intersect/IntersectP count, scene.cpp:41-52) in per-thread,
+// cache-line-sized slots, so that counting does not slow the multithreaded render down.
+struct alignas(64) CountSlot { uint64_t closest = 0, any = 0; };
+static std::mutex g_slotMutex;
+static std::vector<CountSlot *> g_slots;
+static CountSlot *my_slot() {
+    static thread_local CountSlot *tl = nullptr;
+    if (!tl) {
+        tl = new CountSlot;   // lives until process exit: pool threads may outlive the render
+        std::lock_guard<std::mutex> l(g_slotMutex);
+        g_slots.push_back(tl);
+    }
+    return tl;
+}
 struct CountingAggregate : public Aggregate {
     std::shared_ptr<Primitive> inner;
-    mutable std::atomic<uint64_t> nClosest{0}, nAny{0};
-    explicit CountingAggregate(std::shared_ptr<Primitive> p) : inner(std::move(p)) {}
+    explicit CountingAggregate(std::shared_ptr<Primitive> p) : inner(std::move(p)) {
+        std::lock_guard<std::mutex> l(g_slotMutex);
+        for (CountSlot *c : g_slots) c->closest = c->any = 0;
+    }
     Bounds3f WorldBound() const override { return inner->WorldBound(); }
     bool Intersect(const Ray &r, SurfaceInteraction *si) const override {
-        nClosest.fetch_add(1, std::memory_order_relaxed);
+        my_slot()->closest++;
         return inner->Intersect(r, si);
     }
     bool IntersectP(const Ray &r) const override {
-        nAny.fetch_add(1, std::memory_order_relaxed);
+        my_slot()->any++;
         return inner->IntersectP(r);
+    }
+    void totals(uint64_t *c, uint64_t *a) const {
+        std::lock_guard<std::mutex> l(g_slotMutex);
+        *c = *a = 0;
+        for (CountSlot *s : g_slots) { *c += s->closest; *a += s->any; }
     }
 };
 }  // namespace
@@ -81,7 +101,8 @@ extern "C" int ref_render(ref_scene *s, const char *accel_kind, const float *cam
                           const float *prim_mat /* nullable: 8 floats per primitive (kind 0 matte / 1 plastic, Kd rgb, Ks rgb,
                                                    roughness) instead of the single matte `kd` */,
                           const float *emitter_L /* nullable: rgb; the scene's LAST primitive (a sphere) becomes
-                                                    AreaLightSource "area" "color L" and replaces the point light */) {
+                                                    AreaLightSource "area" "color L" and replaces the point light */,
+                          double *render_seconds /* nullable: wall time of integrator.Render() alone (no tree build) */) {
     PbrtOptions.quiet = true;
     PbrtOptions.nThreads = n_threads;
     // material: Material "matte" "rgb Kd" (materials/matte.cpp:44-60), sigma 0
@@ -163,7 +184,9 @@ extern "C" int ref_render(ref_scene *s, const char *accel_kind, const float *cam
     PathIntegrator integ(maxdepth, camera, sampler, film->GetSampleBounds(), 1.f, "spatial");
 
     if (n_threads != 1) ParallelInit();
+    const auto t0 = std::chrono::steady_clock::now();
     integ.Render(scene);     // -> film->WriteImage() -> the WriteImage above
+    if (render_seconds) *render_seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
     if (n_threads != 1) ParallelCleanup();
     {
         std::lock_guard<std::mutex> l(g_imgMutex);
@@ -185,8 +208,10 @@ extern "C" int ref_render(ref_scene *s, const char *accel_kind, const float *cam
             out_heat[5 * npx + i] = (uint32_t)g.leafNodeTraversalsP;
         }
     }
-    if (n_closest) *n_closest = counting->nClosest.load();
-    if (n_shadow) *n_shadow = counting->nAny.load();
+    uint64_t tc, ta;
+    counting->totals(&tc, &ta);
+    if (n_closest) *n_closest = tc;
+    if (n_shadow) *n_shadow = ta;
     // film is owned (and deleted) by the Camera (core/camera.cpp)
     return 0;
 }

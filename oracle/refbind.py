@@ -49,7 +49,7 @@ def bind(path):
         if hasattr(L, "ref_render"):
             L.ref_render.argtypes = [C.c_void_p, C.c_char_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p,
                                      C.c_void_p, C.c_void_p, C.c_char_p, C.c_int, C.c_char_p, C.c_void_p,
-                                     C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), C.c_void_p, C.c_void_p, C.c_void_p]
+                                     C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_double)]
     return L
 
 
@@ -162,21 +162,23 @@ class RefAccel:
 
 
 def render(scene, accel_kind, eye, look, up, fov, xres, yres, spp, maxdepth, light_pos, light_I, kd,
-           sampler="random", n_threads=0, tmp_prefix=None, heat=False, prim_mat=None, emitter_L=None):
+           sampler="random", n_threads=0, tmp_prefix=None, heat=False, prim_mat=None, emitter_L=None, timing=False):
     """The reference's OWN render (SamplerIntegrator::Render + PathIntegrator::Li + Film, oracle/ref/ref_render.cpp)
     of `scene` with a matte material and one point light.  Returns (rgb (yres,xres,3), n_closest, n_shadow)."""
     import tempfile
     cam = np.array(list(eye) + list(look) + list(up) + [fov], np.float32)
     lp, li, k = (np.array(a, np.float32) for a in (light_pos, light_I, kd))
     out = np.zeros((yres, xres, 3), np.float32)
-    nc, ns = C.c_uint64(), C.c_uint64()
+    nc, ns, secs = C.c_uint64(), C.c_uint64(), C.c_double()
     hm = np.zeros((6, yres, xres), np.uint32) if heat else None
     pk = None if prim_mat is None else np.ascontiguousarray(prim_mat, np.float32).reshape(-1, 8)
     el = None if emitter_L is None else np.ascontiguousarray(emitter_L, np.float32)
     with tempfile.TemporaryDirectory() as td:   # the thesis's per-pixel stat dumps (film.cpp:170-264) land here
         pre = (tmp_prefix or os.path.join(td, "ref")).encode()
         rc = scene.L.ref_render(scene.h, accel_kind.encode(), _p(cam), xres, yres, spp, maxdepth, _p(lp), _p(li), _p(k),
-                                sampler.encode(), n_threads, pre, _p(out), C.byref(nc), C.byref(ns), _p(hm), _p(pk), _p(el))
+                                sampler.encode(), n_threads, pre, _p(out), C.byref(nc), C.byref(ns), _p(hm), _p(pk), _p(el), C.byref(secs))
     if rc != 0:
         raise RuntimeError("ref_render failed (%d)" % rc)
+    if timing:   # (rgb, n_closest, n_shadow, seconds spent inside Integrator::Render)
+        return out, nc.value, ns.value, secs.value
     return (out, nc.value, ns.value, hm) if heat else (out, nc.value, ns.value)

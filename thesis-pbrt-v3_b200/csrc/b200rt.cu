@@ -52,6 +52,7 @@ static int g_pblocks[6][2];  // resident persistent blocks per SM, [kind][any]
 static int g_persist_bsp = 1;
 static uint32_t g_bvh_steps = 4;
 static uint32_t g_sstack = 10;     // BVH stack entries kept in shared memory (B200RT_SSTACK; 0 = all in local memory)
+static uint32_t g_bsp_steps = B200RT_BSP_STEPS;  // B200RT_BSP_STEPS_N
 static uint32_t g_sstack_bsp = 0;
 static int g_minb = 9;             // __launch_bounds__ min blocks/SM variant of the BVH kernels (B200RT_MINB: 8 | 9; 9 = 56 registers, 36 warps/SM: +2 % over 8, 10 spills — profiles/r01_ab_bvh_minblocks.log)
 typedef void (*bvh_kernel_t)(const BvhView, const float4 *, uint64_t, const uint32_t *, b200rt_hit *, uint8_t *, PersistCounters *,
@@ -88,6 +89,7 @@ extern "C" int b200rt_init(int device) {
     if (const char *e = getenv("B200RT_PIPE_RAMP")) g_pipe_ramp = atoi(e);
     if (const char *e = getenv("B200RT_BVH_STEPS")) g_bvh_steps = std::max(1, atoi(e));
     if (const char *e = getenv("B200RT_PERSIST_BSP")) g_persist_bsp = atoi(e);
+    if (const char *e = getenv("B200RT_BSP_STEPS_N")) g_bsp_steps = (uint32_t)std::max(1, atoi(e));
     if (const char *e = getenv("B200RT_SSTACK_BSP")) g_sstack_bsp = (uint32_t)std::min(64, std::max(0, atoi(e)));
     if (const char *e = getenv("B200RT_SSTACK")) g_sstack = (uint32_t)std::min(64, std::max(0, atoi(e)));
     // the persistent kernels use no shared memory: give the whole 256 KB array to L1 (node working set)
@@ -484,7 +486,7 @@ int b200rt::launch_trace(const b200rt_scene *s, const float4 *rays, uint64_t n, 
             b200rt_hit *ho = any ? nullptr : hits + off;
             uint8_t *oo = any ? occ + off : nullptr;
             const float4 *ri = rays + 2 * off;
-#define PL(fn, view) fn<<<blocks, B200RT_PBLOCK, (size_t)g_sstack_bsp * 12 * B200RT_PBLOCK, st>>>(view, ri, m, n_dev, ho, oo, pc, g_thresh, chunk, g_sstack_bsp)
+#define PL(fn, view) fn<<<blocks, B200RT_PBLOCK, (size_t)g_sstack_bsp * 12 * B200RT_PBLOCK, st>>>(view, ri, m, n_dev, ho, oo, pc, g_thresh, chunk, g_sstack_bsp, g_bsp_steps)
 #define PLB(fn, view) fn<<<blocks, B200RT_PBLOCK, (size_t)g_sstack * sizeof(uint2) * B200RT_PBLOCK, st>>>(view, ri, m, n_dev, ho, oo, pc, g_thresh, chunk, g_bvh_steps, g_sstack)
             switch (s->kind * 2 + (any ? 1 : 0)) {
                 case B200RT_BVH * 2: case B200RT_BVH * 2 + 1: {

@@ -260,7 +260,8 @@ __global__ void __launch_bounds__(B200RT_PBLOCK, 8)
 bsp_persistent_kernel(const __grid_constant__ BspView S, const float4 *__restrict__ rays, uint64_t n64,
                       const uint32_t *__restrict__ n_dev, b200rt_hit *__restrict__ hits,
                       uint8_t *__restrict__ occluded, PersistCounters *pc, uint32_t thresh, uint32_t chunk,
-                      uint32_t sdepth /* todo entries [0, sdepth) live in shared memory (see bvh_persistent_kernel) */) {
+                      uint32_t sdepth /* todo entries [0, sdepth) live in shared memory (see bvh_persistent_kernel) */,
+                      uint32_t steps /* interior steps a lane may take per vote */) {
     extern __shared__ uint32_t sst32[];  // 3 planes (node, tMin, tMax) of sdepth x blockDim words: bank = lane
     uint32_t n = (uint32_t)n64;
     if (n_dev) { const uint32_t m = *n_dev; n = m < n ? m : n; }
@@ -315,7 +316,7 @@ bsp_persistent_kernel(const __grid_constant__ BspView S, const float4 *__restric
             bool finished = false;
             if (nN >= nL) {
 #pragma unroll 1
-                for (int k = 0; k < B200RT_BSP_STEPS && state == B200RT_ST_NODE; ++k) {
+                for (uint32_t k = 0; k < steps && state == B200RT_ST_NODE; ++k) {
                     if (!ANY && r.tMax < tMin) { finished = true; break; }  // kdtreeaccel.cpp:400 (closest-hit only)
                     const BspStep nd = bsp_fetch<KIND>(S, r, cur, off, mask, leafTag);
                     if (!nd.leaf) {
