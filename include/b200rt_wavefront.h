@@ -52,7 +52,11 @@ typedef struct {
                               sampled with multiple importance sampling as EstimateDirect does (integrator.cpp:109-217):
                               a light sample (shadow any-hit ray) AND a BSDF sample (an extra closest-hit "MIS" ray) per bounce,
                               plus the emitted radiance seen directly by camera rays (path.cpp:97-107). */
-    float light_radius;    /* sphere radius; light_pos = its centre, light_I = its emitted radiance "L" */
+    float light_radius;    /* sphere radius; light_pos = its centre, light_I = its emitted radiance "L".
+                              B200RT_LIGHT_DISTANT (LightSource "distant", lights/distant.cpp:44-69): light_pos = the unit
+                              direction TOWARDS the light (wLight = Normalize(from - to)), light_I = its radiance "L", and
+                              light_radius = the scene's bounding-sphere radius (DistantLight::Preprocess); shadow rays end
+                              at p + wLight * 2 * radius.  A delta light: no MIS rays. */
     uint32_t light_prim;   /* primitive number of that sphere inside the aggregate (scene-desc prim_kind == 1) */
     /* Materials: NULL = Material "matte" "Kd" = kd for all.  Else n_materials records of 8 floats
      * (kind, Kd.r, Kd.g, Kd.b, Ks.r, Ks.g, Ks.b, roughness), kind B200RT_MAT_MATTE (materials/matte.cpp, sigma 0) or B200RT_MAT_PLASTIC (materials/plastic.cpp),
@@ -61,7 +65,7 @@ typedef struct {
     uint32_t n_materials;
     const uint8_t *prim_material; /* n_prims bytes */
 } b200rt_render_desc;
-enum { B200RT_LIGHT_POINT = 0, B200RT_LIGHT_SPHERE = 1 };
+enum { B200RT_LIGHT_POINT = 0, B200RT_LIGHT_SPHERE = 1, B200RT_LIGHT_DISTANT = 2 };
 enum { B200RT_MAT_MATTE = 0, B200RT_MAT_PLASTIC = 1 /* materials/plastic.cpp: Kd + Ks microfacet lobe, roughness remapped */ };
 
 typedef struct {

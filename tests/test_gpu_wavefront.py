@@ -156,6 +156,27 @@ def test_tile_sharding_is_bit_identical(gpu, small_scene):
     assert np.array_equal(small, full)
 
 
+def test_tile_sharding_area_light_and_materials(gpu):
+    """Same invariants for the full shade stage (sphere area light with MIS rays, matte + plastic materials): the
+    union of the ranks' films and a small-batch render both equal the single-rank film bit for bit."""
+    from b200rt import scenes
+    sc = scenes.killeroo_simple(xres=72, yres=56)
+    verts, prim_kind, rows, pm, mats = scenes.with_sphere_light(sc, plastic=True)
+    acc = gpu.B200Accel(gpu.build_bvh(verts), verts, prim_kind=prim_kind, spheres=rows)
+    sl = sc["sphere_light"]
+    kw = dict(spp=3, maxdepth=4, light_pos=sl["center"], light_I=sl["L"], seed=2,
+              sphere_light=(sl["radius"], len(verts) - 1), materials=mats, prim_material=pm)
+    full, st1 = gpu.WavefrontPathIntegrator(sc["camera"], **kw).Render(acc)
+    assert st1["mis_rays"] > 0 and full[..., :3].max() > 0
+    for world in (2, 5):
+        parts = [gpu.WavefrontPathIntegrator(sc["camera"], rank=r, world=world, **kw).Render(acc) for r in range(world)]
+        assert np.array_equal(sum(p[0] for p in parts), full)
+        for k in ("closest_rays", "shadow_rays", "mis_rays"):
+            assert sum(p[1][k] for p in parts) == st1[k], k
+    small, st2 = gpu.WavefrontPathIntegrator(sc["camera"], max_batch=1536, **kw).Render(acc)
+    assert np.array_equal(small, full) and st2["mis_rays"] == st1["mis_rays"]
+
+
 def test_film_matches_float64_restatement(gpu, small_scene):
     sc, acc = small_scene
     orc = ob.OracleAccel(acc.tree, sc["tri_verts"])

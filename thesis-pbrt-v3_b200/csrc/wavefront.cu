@@ -9,6 +9,7 @@
 #include <cuda_runtime.h>
 #include <algorithm>
 #include <atomic>
+#include <cmath>
 #include <cstring>
 #include <vector>
 #include "../../include/b200rt_wavefront.h"
@@ -218,6 +219,19 @@ __device__ void shade_general(const WfParams &P, const WfMat &m, uint32_t depth,
                 o.wantMis = true;
             }
         }
+    } else if (P.light_kind == B200RT_LIGHT_DISTANT) {   // DistantLight::Sample_Li (lights/distant.cpp:49-59)
+        const float3 wiL = to_local(fr, make_float3(P.light_pos[0], P.light_pos[1], P.light_pos[2]));
+        float3 f; float scatPdf;
+        bsdf_eval(m, woL, wiL, f, scatPdf);
+        const float g = fabsf(wiL.z);
+        o.contrib = make_float3(bt.x * f.x * P.light_I[0] * g, bt.y * f.y * P.light_I[1] * g, bt.z * f.z * P.light_I[2] * g);
+        if (o.contrib.x > 0.f || o.contrib.y > 0.f || o.contrib.z > 0.f) {
+            const float r2x = 2.f * P.light_radius;
+            const float3 pOut = make_float3(p.x + P.light_pos[0] * r2x, p.y + P.light_pos[1] * r2x, p.z + P.light_pos[2] * r2x);
+            o.so = offset_ray_origin(p, pe, ng, make_float3(pOut.x - p.x, pOut.y - p.y, pOut.z - p.z));
+            o.sd = make_float3(pOut.x - o.so.x, pOut.y - o.so.y, pOut.z - o.so.z);
+            o.wantShadow = true;
+        }
     } else if (d2 > 0.f) {   // PointLight::Sample_Li (point.cpp:44-53): Li = I / d^2, pdf = 1
         const float invd = 1.f / sqrtf(d2);
         const float3 wiL = to_local(fr, make_float3(wl.x * invd, wl.y * invd, wl.z * invd));
@@ -414,6 +428,21 @@ __global__ void k_shade(const __grid_constant__ WfParams P, uint32_t depth, uint
                                 md = wi;
                                 wantMis = true;
                             }
+                        }
+                    }
+                } else if (FULL && P.light_kind == B200RT_LIGHT_DISTANT) {
+                    // DistantLight::Sample_Li (lights/distant.cpp:49-59): wi = wLight, Li = L, pdf = 1
+                    const float cosl = nf.x * P.light_pos[0] + nf.y * P.light_pos[1] + nf.z * P.light_pos[2];
+                    if (cosl > 0.f) {
+                        const float g = cosl * kInvPi;
+                        contrib = make_float3(bt.x * kdr * P.light_I[0] * g, bt.y * kdg * P.light_I[1] * g,
+                                              bt.z * kdb * P.light_I[2] * g);
+                        if (contrib.x > 0.f || contrib.y > 0.f || contrib.z > 0.f) {
+                            const float r2x = 2.f * P.light_radius;   // pOutside = ref.p + wLight * (2 * worldRadius)
+                            const float3 pOut = make_float3(p.x + P.light_pos[0] * r2x, p.y + P.light_pos[1] * r2x, p.z + P.light_pos[2] * r2x);
+                            so = offset_ray_origin(p, pe, ng, make_float3(pOut.x - p.x, pOut.y - p.y, pOut.z - p.z));
+                            sd = make_float3(pOut.x - so.x, pOut.y - so.y, pOut.z - so.z);
+                            wantShadow = true;
                         }
                     }
                 } else if (d2 > 0.f) {
@@ -672,7 +701,13 @@ static int render_impl(b200rt_scene *s, const b200rt_render_desc *d, float *film
     if (d->max_depth > 64) return set_error(B200RT_EINVAL, "max_depth %u too large", d->max_depth);
     P.light_kind = d->light_kind; P.light_prim = d->light_prim; P.light_radius = d->light_radius;
     const bool area = d->light_kind == B200RT_LIGHT_SPHERE;
-    if (d->light_kind > B200RT_LIGHT_SPHERE) return set_error(B200RT_EINVAL, "unknown light_kind %u", d->light_kind);
+    if (d->light_kind > B200RT_LIGHT_DISTANT) return set_error(B200RT_EINVAL, "unknown light_kind %u", d->light_kind);
+    const bool distant = d->light_kind == B200RT_LIGHT_DISTANT;
+    if (distant) {
+        const float l2 = d->light_pos[0] * d->light_pos[0] + d->light_pos[1] * d->light_pos[1] + d->light_pos[2] * d->light_pos[2];
+        if (!(d->light_radius > 0.f) || !(std::fabs(l2 - 1.f) < 1e-3f))
+            return set_error(B200RT_EINVAL, "distant light: light_pos must be the unit direction to the light and light_radius the scene's bounding-sphere radius");
+    }
     if (area && (!(d->light_radius > 0.f) || d->light_prim >= s->n_prims))
         return set_error(B200RT_EINVAL, "sphere light: radius must be > 0 and light_prim a primitive of the scene");
     if (d->materials && (!d->prim_material || d->n_materials == 0 || d->n_materials > 256))
@@ -782,7 +817,7 @@ static int render_impl(b200rt_scene *s, const b200rt_render_desc *d, float *film
                 g_launches.fetch_add(1);
             }
             if (depth == d->max_depth) break;  // path.cpp:110: the last intersection is found, then the path ends
-            (area || P.mats ? k_shade<true> : k_shade<false>)<<<gridSlots, TB, 0, st>>>(P, depth, start, w->counts + 2 * depth, w->rays[cur], w->qPath[cur], w->hits,
+            (area || distant || P.mats ? k_shade<true> : k_shade<false>)<<<gridSlots, TB, 0, st>>>(P, depth, start, w->counts + 2 * depth, w->rays[cur], w->qPath[cur], w->hits,
                                               s->d_prim_tris, w->beta, w->rays[cur ^ 1], w->qPath[cur ^ 1],
                                               w->counts + 2 * (depth + 1), w->shRays, w->shPath, w->shContrib,
                                               w->counts + 2 * depth + 1, w->L, w->misRays, w->misPath, w->misContrib,
