@@ -25,6 +25,7 @@
 #include "integrators/path.h"
 #include "lights/point.h"
 #include "lights/diffuse.h"
+#include "lights/distant.h"
 #include "materials/matte.h"
 #include "materials/plastic.h"
 #include "samplers/halton.h"
@@ -91,6 +92,20 @@ struct CountingAggregate : public Aggregate {
     }
 };
 }  // namespace
+
+// LightSource "distant" "point from" "point to" for the NEXT ref_render calls (NULL = back to the point light):
+// from_to = from[3], to[3]; its radiance "L" is ref_render's light_I (lights/distant.cpp:117-125, CreateDistantLight).
+static bool g_distant = false;
+static float g_from_to[6];
+extern "C" void ref_render_set_distant(const float *from_to) {
+    g_distant = from_to != nullptr;
+    if (from_to) std::memcpy(g_from_to, from_to, sizeof(g_from_to));
+}
+
+extern "C" int ref_render_get_distant(float *from_to) {   // for tests/hostplugin's driver, which builds the same scene
+    if (g_distant) std::memcpy(from_to, g_from_to, sizeof(g_from_to));
+    return g_distant ? 1 : 0;
+}
 
 // cam: eye[3], look[3], up[3], fov — exactly a scene file's `LookAt` + `Camera "perspective" "float fov"`.
 // sampler: "random" | "halton".  out_rgb: yres*xres*3 floats (Film::WriteImage's buffer).  Returns 0 on success.
@@ -162,6 +177,10 @@ extern "C" int ref_render(ref_scene *s, const char *accel_kind, const float *cam
     Transform l2w = Translate(Vector3f(light_pos[0], light_pos[1], light_pos[2]));
     std::vector<std::shared_ptr<Light>> lights;
     if (area) lights.push_back(area);
+    else if (g_distant)
+        lights.push_back(std::make_shared<DistantLight>(Transform(), Spectrum::FromRGB(li),
+                                                        Point3f(g_from_to[0], g_from_to[1], g_from_to[2]) -
+                                                            Point3f(g_from_to[3], g_from_to[4], g_from_to[5])));
     else lights.push_back(std::make_shared<PointLight>(l2w, mi, Spectrum::FromRGB(li)));
     Scene scene(counting, lights);
 

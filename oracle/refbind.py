@@ -162,7 +162,8 @@ class RefAccel:
 
 
 def render(scene, accel_kind, eye, look, up, fov, xres, yres, spp, maxdepth, light_pos, light_I, kd,
-           sampler="random", n_threads=0, tmp_prefix=None, heat=False, prim_mat=None, emitter_L=None, timing=False):
+           sampler="random", n_threads=0, tmp_prefix=None, heat=False, prim_mat=None, emitter_L=None, timing=False,
+           distant=None):
     """The reference's OWN render (SamplerIntegrator::Render + PathIntegrator::Li + Film, oracle/ref/ref_render.cpp)
     of `scene` with a matte material and one point light.  Returns (rgb (yres,xres,3), n_closest, n_shadow)."""
     import tempfile
@@ -173,6 +174,12 @@ def render(scene, accel_kind, eye, look, up, fov, xres, yres, spp, maxdepth, lig
     hm = np.zeros((6, yres, xres), np.uint32) if heat else None
     pk = None if prim_mat is None else np.ascontiguousarray(prim_mat, np.float32).reshape(-1, 8)
     el = None if emitter_L is None else np.ascontiguousarray(emitter_L, np.float32)
+    if hasattr(scene.L, "ref_render_set_distant"):   # distant=(from, to): LightSource "distant" with L = light_I
+        scene.L.ref_render_set_distant.argtypes = [C.c_void_p]
+        ft = None if distant is None else np.array(list(distant[0]) + list(distant[1]), np.float32)
+        scene.L.ref_render_set_distant(_p(ft))
+    elif distant is not None:
+        raise RuntimeError("libpbrtref.so predates ref_render_set_distant: rebuild oracle/ref")
     with tempfile.TemporaryDirectory() as td:   # the thesis's per-pixel stat dumps (film.cpp:170-264) land here
         pre = (tmp_prefix or os.path.join(td, "ref")).encode()
         rc = scene.L.ref_render(scene.h, accel_kind.encode(), _p(cam), xres, yres, spp, maxdepth, _p(lp), _p(li), _p(k),

@@ -24,13 +24,16 @@ CASES = {
     "killeroo_area": dict(scene="killeroo_simple", res=128, spp=256, maxdepth=5, I=(2000.0,) * 3, kd=(.5, .5, .5), area=True),
     # BASELINE config 1 as the scene file has it: area light + matte ground + the two "plastic" killeroos
     "killeroo_full": dict(scene="killeroo_simple", res=128, spp=256, maxdepth=5, I=(2000.0,) * 3, kd=(.5, .5, .5), area=True, plastic=True),
+    # BASELINE config 4's scene as written (scenes/killeroo-feet: LightSource "distant" from the eye towards the look-at
+    # point, Material "plastic" Kd (.4 .5 .4) Ks .3 roughness .15, path maxdepth 5), whole frame instead of the crop window
+    "feet": dict(scene="killeroo_feet", res=192, spp=256, maxdepth=5, I=(1.0,) * 3, kd=(.5, .5, .5), distant=True),
     "sponza": dict(scene="sponza_standin", res=96, spp=256, maxdepth=5, I=(1.0,) * 3, kd=(.5, .5, .5)),
 }
 
 
 def lookat_of(name):
     """eye, look, up, fov of the scene templates (scenes/killeroo-simple:1-3, scenes/sponza:1-3)."""
-    if name == "killeroo_simple":
+    if name in ("killeroo_simple", "killeroo_feet"):
         r = scenes._rot_z(5.0)
         eye = scenes._xform(r, np.array([[400.0, 20, 30]]))[0]
         look = scenes._xform(r, np.array([[0.0, 63, -110]]))[0]
@@ -53,6 +56,9 @@ def main():
             spheres = np.array([list(sl["center"]) + [sl["radius"]]], np.float32)
             mats = sc["materials"] if c.get("plastic") else np.pad(sc["material_kd"], ((0, 0), (1, 4)))
             extra = dict(prim_mat=np.concatenate([mats[sc["prim_material"]], np.zeros((1, 8), np.float32)]), emitter_L=sl["L"])
+        if c.get("distant"):
+            extra = dict(prim_mat=np.repeat(sc["materials"], len(tv), 0), distant=(sc["light_from"], sc["light_to"]))
+            sc["light"] = np.zeros(3, np.float32)
         S = rb.RefScene(tv.reshape(-1, 3), np.arange(3 * len(tv), dtype=np.int32).reshape(-1, 3), spheres=spheres)
         eye, look, up, fov = lookat_of(c["scene"])
         img, nc, ns, heat = rb.render(S, "bvh", eye, look, up, fov, c["res"], c["res"], c["spp"], c["maxdepth"], sc["light"],

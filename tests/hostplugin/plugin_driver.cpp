@@ -103,10 +103,12 @@ extern "C" int plugin_intersect_p_batch(const ref_accel *a, const float *rays, u
 #include "materials/matte.h"
 #include "materials/plastic.h"
 #include "lights/diffuse.h"
+#include "lights/distant.h"
 #include "samplers/random.h"
 #include "textures/constant.h"
 #include "b200integrator.h"
 extern "C" int ref_last_image(float *out_rgb, int *xres, int *yres);
+extern "C" int ref_render_get_distant(float *from_to);   // set through ref_render_set_distant (oracle/ref/ref_render.cpp)
 std::shared_ptr<pbrt::Shape> shape_of(const pbrt::Primitive *p);   // plugin_shape_of.cpp (GeometricPrimitive::shape is private)
 
 extern "C" int plugin_render(ref_scene *s, const char *tree, const float *cam, int xres, int yres, int spp, int maxdepth,
@@ -160,7 +162,11 @@ extern "C" int plugin_render(ref_scene *s, const char *tree, const float *cam, i
     Float li[3] = {light_I[0], light_I[1], light_I[2]};
     Transform l2w = Translate(Vector3f(light_pos[0], light_pos[1], light_pos[2]));
     std::vector<std::shared_ptr<Light>> lights;
+    float ft[6];
     if (area) lights.push_back(area);
+    else if (ref_render_get_distant(ft))
+        lights.push_back(std::make_shared<DistantLight>(Transform(), Spectrum::FromRGB(li),
+                                                        Point3f(ft[0], ft[1], ft[2]) - Point3f(ft[3], ft[4], ft[5])));
     else lights.push_back(std::make_shared<PointLight>(l2w, mi, Spectrum::FromRGB(li)));
     Scene scene(accel, lights);
     std::unique_ptr<Filter> filter(new BoxFilter(Vector2f(0.5f, 0.5f)));

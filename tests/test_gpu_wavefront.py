@@ -289,3 +289,33 @@ def test_area_light_mis_matches_the_references_render(gpu, case, plastic):
     for ch in range(3):   # per colour channel: the per-primitive Kd's tint the bounce light
         assert abs(a[..., ch].mean() / b[..., ch].mean() - 1) < 0.015
     assert np.sqrt(((_blocks(a, 8) - _blocks(b, 8)) ** 2).mean()) / b.mean() < 0.04
+
+
+def test_distant_light_scene_matches_the_references_render(gpu):
+    """BASELINE config 4's scene as written (scenes/killeroo-feet): `LightSource "distant"` (lights/distant.cpp) and the
+    "plastic" killeroo, whole frame at 192^2, against the reference's own render (tests/golden/ref_render.npz `feet`).
+    A delta light: EstimateDirect takes no BSDF sample, so there are no MIS rays.  Statistical bar as above (only ~10 %
+    of the frame is covered, so the block RMSE is taken over covered blocks' mean)."""
+    from conftest import load_golden
+    from b200rt import scenes, wavefront as wf
+    from b200rt.wavefront import film_to_rgb
+    g = load_golden("ref_render.npz")
+    res, spp, maxdepth = (int(x) for x in g["feet_params"])
+    sc = scenes.killeroo_feet(xres=res, yres=res)
+    tv = sc["tri_verts"]
+    acc = gpu.MakeAccelerator("bvh", tv)
+    integ = gpu.WavefrontPathIntegrator(sc["camera"], spp=spp, maxdepth=maxdepth, light_I=g["feet_I"], seed=6,
+                                        distant_light=(sc["light_from"] - sc["light_to"], wf.world_radius(tv)),
+                                        materials=sc["materials"], prim_material=np.zeros(len(tv), np.uint8))
+    film, st = integ.Render(acc)
+    rgb, ref = film_to_rgb(film).astype(np.float64), g["feet_rgb"].astype(np.float64)
+    nc, ns = (int(x) for x in g["feet_rays"])
+    assert abs(st["closest_rays"] / nc - 1) < 0.01, (st["closest_rays"], nc)
+    assert abs(st["shadow_rays"] / ns - 1) < 0.01, (st["shadow_rays"], ns)
+    assert st["mis_rays"] == 0
+    assert abs(rgb.mean() / ref.mean() - 1) < 0.01, (rgb.mean(), ref.mean())
+    for ch in range(3):
+        assert abs(rgb[..., ch].mean() / ref[..., ch].mean() - 1) < 0.015
+    a, b = _blocks(rgb, 8), _blocks(ref, 8)
+    covered = b.max(-1) > 0
+    assert np.sqrt(((a - b) ** 2)[covered].mean()) / b[covered].mean() < 0.04

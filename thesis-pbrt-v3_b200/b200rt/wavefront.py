@@ -50,10 +50,12 @@ class WavefrontPathIntegrator:
 
     def __init__(self, camera, spp=8, maxdepth=5, light_pos=(0, 0, 0), light_I=(1, 1, 1), kd=(.5, .5, .5),
                  rank=0, world=1, seed=0, tile_size=16, max_batch=0, sphere_light=None, materials=None,
-                 prim_material=None):
+                 prim_material=None, distant_light=None):
         """sphere_light=(radius, prim): `AreaLightSource "area" "color L" light_I` on the full sphere primitive number
         `prim` of the aggregate, centred at light_pos (sampled with MIS like EstimateDirect).  materials: (n, 8) rows
-        (kind, Kd.rgb, Ks.rgb, roughness) + prim_material: (n_prims,) uint8 index per primitive."""
+        (kind, Kd.rgb, Ks.rgb, roughness) + prim_material: (n_prims,) uint8 index per primitive.
+        distant_light=(from - to, world_radius): `LightSource "distant"` with radiance light_I (lights/distant.cpp);
+        world_radius = the aggregate's bounding-sphere radius (see world_radius())."""
         d = RenderDesc()
         for k in ("eye", "dir", "right", "up"):
             setattr(d.camera, k, (C.c_float * 3)(*[float(x) for x in camera[k]]))
@@ -65,6 +67,11 @@ class WavefrontPathIntegrator:
         d.tile_size, d.rank, d.world, d.seed, d.max_batch = tile_size, rank, world, seed, max_batch
         if sphere_light is not None:
             d.light_kind, d.light_radius, d.light_prim = 1, float(sphere_light[0]), int(sphere_light[1])
+        if distant_light is not None:
+            w = np.asarray(distant_light[0], np.float32)
+            w = w / np.sqrt((w * w).sum(dtype=np.float32))
+            d.light_kind, d.light_radius = 2, float(distant_light[1])
+            d.light_pos = (C.c_float * 3)(*[float(x) for x in w])
         if materials is not None:
             self._mats = np.ascontiguousarray(materials, np.float32).reshape(-1, 8)
             self._pm = np.ascontiguousarray(prim_material, np.uint8)
@@ -91,6 +98,14 @@ class WavefrontPathIntegrator:
         film = np.zeros(self.shape, np.float32)
         stats = self.render_ptr(accel, film.ctypes.data_as(C.c_void_p), stream)
         return film, stats
+
+
+def world_radius(tri_verts):
+    """Bounds3::BoundingSphere of the aggregate's world bound (geometry.h), as DistantLight::Preprocess uses it."""
+    v = np.asarray(tri_verts, np.float32).reshape(-1, 3)
+    lo, hi = v.min(0), v.max(0)
+    c = (lo + hi) / np.float32(2)
+    return float(np.sqrt(((hi - c) ** 2).sum(dtype=np.float32)))
 
 
 HEAT_PLANES = ("primitiveIntersections", "primitiveIntersectionsP", "treeNodeTraversals", "treeNodeTraversalsP",

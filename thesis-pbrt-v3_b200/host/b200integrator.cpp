@@ -126,7 +126,7 @@ void B200WavefrontIntegrator::Render(const Scene &scene) {
         Error("b200wavefront: pixel filters wider than one pixel are not supported (use PixelFilter \"box\")");
         return;
     }
-    // the light: LightSource "point" (through Light::Sample_Li, lights/point.cpp:44-53) or AreaLightSource "area" on
+    // the light: LightSource "point" (through Light::Sample_Li, lights/point.cpp:44-53), LightSource "distant", or AreaLightSource "area" on
     // a full Shape "sphere" that is a primitive of the aggregate (lights/diffuse.cpp, scenes/killeroo-simple:18-24)
     if (scene.lights.size() != 1) { Error("b200wavefront: exactly one light is supported"); return; }
     const Light *light = scene.lights[0].get();
@@ -141,6 +141,23 @@ void B200WavefrontIntegrator::Render(const Scene &scene) {
         Float rgb[3];
         Spectrum(Li * d2).ToRGB(rgb);
         d.light_pos[0] = pl.x; d.light_pos[1] = pl.y; d.light_pos[2] = pl.z;
+        for (int i = 0; i < 3; ++i) d.light_I[i] = rgb[i];
+    } else if (light->flags & (int)LightFlags::DeltaDirection) {
+        // LightSource "distant" (lights/distant.cpp:49-59): wi = wLight, Li = L for every reference point; shadow rays
+        // end 2 * worldRadius away, worldRadius as DistantLight::Preprocess takes it from the scene's bound (distant.h)
+        Interaction ref(Point3f(0, 0, 0), Normal3f(0, 0, 1), Vector3f(0, 0, 0), Vector3f(0, 0, 1), 0, MediumInterface());
+        Vector3f wi;
+        Float pdf;
+        VisibilityTester vis;
+        const Spectrum Li = light->Sample_Li(ref, Point2f(0.5f, 0.5f), &wi, &pdf, &vis);
+        Point3f wc;
+        Float wr;
+        scene.WorldBound().BoundingSphere(&wc, &wr);
+        Float rgb[3];
+        Li.ToRGB(rgb);
+        d.light_kind = B200RT_LIGHT_DISTANT;
+        d.light_radius = wr;
+        d.light_pos[0] = wi.x; d.light_pos[1] = wi.y; d.light_pos[2] = wi.z;
         for (int i = 0; i < 3; ++i) d.light_I[i] = rgb[i];
     } else if (light->flags & (int)LightFlags::Area) {
         int lp = -1;
@@ -165,7 +182,7 @@ void B200WavefrontIntegrator::Render(const Scene &scene) {
         d.light_pos[0] = c.x; d.light_pos[1] = c.y; d.light_pos[2] = c.z;
         for (int i = 0; i < 3; ++i) d.light_I[i] = le[i];
     } else {
-        Error("b200wavefront: only a point light or a sphere area light is supported");
+        Error("b200wavefront: only a point light, a distant light or a sphere area light is supported");
         return;
     }
     // materials: Material "matte" (constant Kd, sigma 0; measured through the public BSDF) and Material "plastic"
