@@ -64,6 +64,11 @@ typedef struct {
     const float *materials;
     uint32_t n_materials;
     const uint8_t *prim_material; /* n_prims bytes */
+    /* ---- appended in ABI v5 ---- */
+    uint32_t crop[4];      /* Film "cropwindow" in PIXELS of the camera's frame: x0, x1, y0, y1 (= Film::croppedPixelBounds,
+                              film.cpp:49-57: ceil(res * window)); all zero = the whole frame.  Tiles are laid from the
+                              window's first pixel (integrator.cpp:237-246 over GetSampleBounds), and `film` / `heat` hold
+                              (y1-y0) x (x1-x0) pixels, like the reference's Film. */
 } b200rt_render_desc;
 enum { B200RT_LIGHT_POINT = 0, B200RT_LIGHT_SPHERE = 1, B200RT_LIGHT_DISTANT = 2 };
 enum { B200RT_MAT_MATTE = 0, B200RT_MAT_PLASTIC = 1 /* materials/plastic.cpp: Kd + Ks microfacet lobe, roughness remapped */ };

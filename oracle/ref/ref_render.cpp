@@ -102,6 +102,14 @@ extern "C" void ref_render_set_distant(const float *from_to) {
     if (from_to) std::memcpy(g_from_to, from_to, sizeof(g_from_to));
 }
 
+// Film "float cropwindow" [x0 x1 y0 y1] for the NEXT renders (NULL = whole frame); out_rgb / out_heat then hold the
+// window's pixels only (Film::croppedPixelBounds, film.cpp:49-57).
+static float g_crop[4] = {0.f, 1.f, 0.f, 1.f};
+extern "C" void ref_render_set_crop(const float *cw) {
+    const float full[4] = {0.f, 1.f, 0.f, 1.f};
+    std::memcpy(g_crop, cw ? cw : full, sizeof(g_crop));
+}
+extern "C" void ref_render_get_crop(float *cw) { std::memcpy(cw, g_crop, sizeof(g_crop)); }
 extern "C" int ref_render_get_distant(float *from_to) {   // for tests/hostplugin's driver, which builds the same scene
     if (g_distant) std::memcpy(from_to, g_from_to, sizeof(g_from_to));
     return g_distant ? 1 : 0;
@@ -187,7 +195,9 @@ extern "C" int ref_render(ref_scene *s, const char *accel_kind, const float *cam
     // Film "image" + PixelFilter "box" (film.cpp:307-351, filters/box.cpp) — defaults of every thesis template
     std::unique_ptr<Filter> filter(new BoxFilter(Vector2f(0.5f, 0.5f)));
     std::string fname = std::string(tmp_prefix) + ".exr";
-    Film *film = new Film(Point2i(xres, yres), Bounds2f(Point2f(0, 0), Point2f(1, 1)), std::move(filter), 35.f, fname, 1.f);
+    Film *film = new Film(Point2i(xres, yres), Bounds2f(Point2f(g_crop[0], g_crop[2]), Point2f(g_crop[1], g_crop[3])),
+                          std::move(filter), 35.f, fname, 1.f);
+    const Vector2i cres = film->croppedPixelBounds.Diagonal();
     // LookAt + Camera "perspective" (api.cpp:1338-1370 pbrtCamera; cameras/perspective.cpp:231-279)
     Transform w2c = LookAt(Point3f(cam[0], cam[1], cam[2]), Point3f(cam[3], cam[4], cam[5]), Vector3f(cam[6], cam[7], cam[8]));
     Transform c2w = Inverse(w2c);
@@ -209,14 +219,14 @@ extern "C" int ref_render(ref_scene *s, const char *accel_kind, const float *cam
     if (n_threads != 1) ParallelCleanup();
     {
         std::lock_guard<std::mutex> l(g_imgMutex);
-        if (g_lastRes.x != xres || g_lastRes.y != yres) return 2;
+        if (g_lastRes.x != cres.x || g_lastRes.y != cres.y) return 2;
         std::memcpy(out_rgb, g_lastImage.data(), sizeof(float) * g_lastImage.size());
     }
     if (out_heat) {
         // the thesis's per-pixel GeneralStats (integrator.cpp:327-328), the matrices Film::WriteGeneralStats dumps
         // (film.cpp:170-264): planes = primitiveIntersections, ...P, {bvh+kd+bsp}TreeNodeTraversals, ...P,
         // leafNodeTraversals, ...P
-        const size_t npx = (size_t)xres * yres;
+        const size_t npx = (size_t)cres.x * cres.y;
         for (size_t i = 0; i < npx; ++i) {
             const GeneralStats &g = film->pixels[i].stats;
             out_heat[0 * npx + i] = (uint32_t)g.primitiveIntersections;

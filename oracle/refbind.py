@@ -163,15 +163,21 @@ class RefAccel:
 
 def render(scene, accel_kind, eye, look, up, fov, xres, yres, spp, maxdepth, light_pos, light_I, kd,
            sampler="random", n_threads=0, tmp_prefix=None, heat=False, prim_mat=None, emitter_L=None, timing=False,
-           distant=None):
+           distant=None, cropwindow=None):
     """The reference's OWN render (SamplerIntegrator::Render + PathIntegrator::Li + Film, oracle/ref/ref_render.cpp)
     of `scene` with a matte material and one point light.  Returns (rgb (yres,xres,3), n_closest, n_shadow)."""
     import tempfile
     cam = np.array(list(eye) + list(look) + list(up) + [fov], np.float32)
     lp, li, k = (np.array(a, np.float32) for a in (light_pos, light_I, kd))
-    out = np.zeros((yres, xres, 3), np.float32)
+    cw_, ch_ = xres, yres
+    if cropwindow is not None:   # Film "float cropwindow" [x0 x1 y0 y1]: the outputs hold Film::croppedPixelBounds only
+        x0, x1, y0, y1 = (float(np.float32(c)) for c in cropwindow)
+        f32 = np.float32
+        cw_ = int(np.ceil(f32(xres) * f32(x1))) - int(np.ceil(f32(xres) * f32(x0)))
+        ch_ = int(np.ceil(f32(yres) * f32(y1))) - int(np.ceil(f32(yres) * f32(y0)))
+    out = np.zeros((ch_, cw_, 3), np.float32)
     nc, ns, secs = C.c_uint64(), C.c_uint64(), C.c_double()
-    hm = np.zeros((6, yres, xres), np.uint32) if heat else None
+    hm = np.zeros((6, ch_, cw_), np.uint32) if heat else None
     pk = None if prim_mat is None else np.ascontiguousarray(prim_mat, np.float32).reshape(-1, 8)
     el = None if emitter_L is None else np.ascontiguousarray(emitter_L, np.float32)
     if hasattr(scene.L, "ref_render_set_distant"):   # distant=(from, to): LightSource "distant" with L = light_I
@@ -180,6 +186,11 @@ def render(scene, accel_kind, eye, look, up, fov, xres, yres, spp, maxdepth, lig
         scene.L.ref_render_set_distant(_p(ft))
     elif distant is not None:
         raise RuntimeError("libpbrtref.so predates ref_render_set_distant: rebuild oracle/ref")
+    if hasattr(scene.L, "ref_render_set_crop"):
+        scene.L.ref_render_set_crop.argtypes = [C.c_void_p]
+        scene.L.ref_render_set_crop(_p(None if cropwindow is None else np.array(cropwindow, np.float32)))
+    elif cropwindow is not None:
+        raise RuntimeError("libpbrtref.so predates ref_render_set_crop: rebuild oracle/ref")
     with tempfile.TemporaryDirectory() as td:   # the thesis's per-pixel stat dumps (film.cpp:170-264) land here
         pre = (tmp_prefix or os.path.join(td, "ref")).encode()
         rc = scene.L.ref_render(scene.h, accel_kind.encode(), _p(cam), xres, yres, spp, maxdepth, _p(lp), _p(li), _p(k),

@@ -74,6 +74,7 @@ def run():
     cam = scenes.camera_rays(sc["camera"], x0=x0, x1=x1, y0=y0, y1=y1)   # the crop window at the scene's resolution
     names = [n for n, _, _ in CASES if n + "_nodes" in z.files]
     ref = None
+    accs = {}
     print("killeroo-feet: %d triangles, %d camera rays (crop %s of 5000^2)" % (len(tv), len(cam), (x0, x1, y0, y1)))
     print("%-10s %9s | %-28s | %-28s | %-28s" % ("accel", "nodes", "camera closest", "bounce closest", "shadow any-hit"))
     print("%-10s %9s | %8s %8s %9s | %8s %8s %9s | %8s %8s %9s" % (("", "") + ("Mrays/s", "nodes/r", "tests/r") * 3))
@@ -113,6 +114,27 @@ def run():
             _, rs = acc.IntersectStats(rays[:: max(1, n // 200000)], any_hit=anyhit)
             row += " %8.0f %8.2f %9.2f |" % (n / ms / 1e3, (rs["interior_visits"] + rs["leaf_visits"]).mean(), rs["prim_tests"].mean())
         print(row, flush=True)
+        accs[name] = acc
+    # ---- the thesis's experiment itself: the scene file rendered per accelerator (scripts/run_rbsps.sh of the reference:
+    # 5000^2 film, cropwindow [.3 .5 .4 .8], 8 spp, path maxdepth 5, distant light, plastic killeroo) ----
+    from b200rt import wavefront as wf
+    print("\nscenes/killeroo-feet as written (crop %d x %d px @ 8 spp, maxdepth 5), whole frame per accelerator:" % (x1 - x0, y1 - y0))
+    print("%-10s %10s %12s %12s %10s %12s" % ("accel", "frame ms", "closest rays", "shadow rays", "Mrays/s", "film mean"))
+    film = torch.zeros((y1 - y0, x1 - x0, 4), dtype=torch.float32, device="cuda")
+    for name in names:
+        integ = b200rt.WavefrontPathIntegrator(sc["camera"], spp=8, maxdepth=5, light_I=(1, 1, 1), seed=1, crop=sc["crop"],
+                                               distant_light=(sc["light_from"] - sc["light_to"], wf.world_radius(tv)),
+                                               materials=sc["materials"], prim_material=np.zeros(len(tv), np.uint8))
+        stats = {}
+
+        def go():
+            film.zero_()
+            stats.update(integ.render_ptr(accs[name], film.data_ptr(), st))
+        ms = timeit(go, torch.cuda.synchronize, reps=3)
+        f = film.cpu().numpy()
+        rays = stats["closest_rays"] + stats["shadow_rays"]
+        print("%-10s %10.2f %12d %12d %10.0f %12.6f" % (name, ms, stats["closest_rays"], stats["shadow_rays"], rays / ms / 1e3,
+                                                         (f[..., :3] / np.maximum(f[..., 3:4], 1)).mean()), flush=True)
 
 
 if __name__ == "__main__":

@@ -27,6 +27,8 @@ CASES = {
     # BASELINE config 4's scene as written (scenes/killeroo-feet: LightSource "distant" from the eye towards the look-at
     # point, Material "plastic" Kd (.4 .5 .4) Ks .3 roughness .15, path maxdepth 5), whole frame instead of the crop window
     "feet": dict(scene="killeroo_feet", res=192, spp=256, maxdepth=5, I=(1.0,) * 3, kd=(.5, .5, .5), distant=True),
+    # ... and through its Film "cropwindow" [.3 .5 .4 .8] (the feet): 640^2 frame -> 128 x 256 pixel window
+    "feet_crop": dict(scene="killeroo_feet", res=640, spp=64, maxdepth=5, I=(1.0,) * 3, kd=(.5, .5, .5), distant=True, crop=True),
     "sponza": dict(scene="sponza_standin", res=96, spp=256, maxdepth=5, I=(1.0,) * 3, kd=(.5, .5, .5)),
 }
 
@@ -59,6 +61,8 @@ def main():
         if c.get("distant"):
             extra = dict(prim_mat=np.repeat(sc["materials"], len(tv), 0), distant=(sc["light_from"], sc["light_to"]))
             sc["light"] = np.zeros(3, np.float32)
+        if c.get("crop"):
+            extra["cropwindow"] = sc["cropwindow"]
         S = rb.RefScene(tv.reshape(-1, 3), np.arange(3 * len(tv), dtype=np.int32).reshape(-1, 3), spheres=spheres)
         eye, look, up, fov = lookat_of(c["scene"])
         img, nc, ns, heat = rb.render(S, "bvh", eye, look, up, fov, c["res"], c["res"], c["spp"], c["maxdepth"], sc["light"],

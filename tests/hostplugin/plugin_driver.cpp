@@ -108,7 +108,8 @@ extern "C" int plugin_intersect_p_batch(const ref_accel *a, const float *rays, u
 #include "textures/constant.h"
 #include "b200integrator.h"
 extern "C" int ref_last_image(float *out_rgb, int *xres, int *yres);
-extern "C" int ref_render_get_distant(float *from_to);   // set through ref_render_set_distant (oracle/ref/ref_render.cpp)
+extern "C" int ref_render_get_distant(float *from_to);
+extern "C" void ref_render_get_crop(float *cw);           // set through ref_render_set_crop   // set through ref_render_set_distant (oracle/ref/ref_render.cpp)
 std::shared_ptr<pbrt::Shape> shape_of(const pbrt::Primitive *p);   // plugin_shape_of.cpp (GeometricPrimitive::shape is private)
 
 extern "C" int plugin_render(ref_scene *s, const char *tree, const float *cam, int xres, int yres, int spp, int maxdepth,
@@ -170,8 +171,11 @@ extern "C" int plugin_render(ref_scene *s, const char *tree, const float *cam, i
     else lights.push_back(std::make_shared<PointLight>(l2w, mi, Spectrum::FromRGB(li)));
     Scene scene(accel, lights);
     std::unique_ptr<Filter> filter(new BoxFilter(Vector2f(0.5f, 0.5f)));
-    Film *film = new Film(Point2i(xres, yres), Bounds2f(Point2f(0, 0), Point2f(1, 1)), std::move(filter), 35.f,
+    float cw[4];
+    ref_render_get_crop(cw);
+    Film *film = new Film(Point2i(xres, yres), Bounds2f(Point2f(cw[0], cw[2]), Point2f(cw[1], cw[3])), std::move(filter), 35.f,
                           std::string(tmp_prefix) + ".exr", 1.f);
+    const Vector2i cres = film->croppedPixelBounds.Diagonal();
     Transform c2w = Inverse(LookAt(Point3f(cam[0], cam[1], cam[2]), Point3f(cam[3], cam[4], cam[5]), Vector3f(cam[6], cam[7], cam[8])));
     AnimatedTransform ac2w(&c2w, 0.f, &c2w, 1.f);
     Float frame = Float(xres) / Float(yres);
@@ -188,7 +192,7 @@ extern "C" int plugin_render(ref_scene *s, const char *tree, const float *cam, i
     integ->Render(scene);
     int w = 0, h = 0;
     ref_last_image(nullptr, &w, &h);
-    if (w != xres || h != yres) return 2;
+    if (w != cres.x || h != cres.y) return 2;
     ref_last_image(out_rgb, &w, &h);
     if (n_closest) *n_closest = integ->stats().closest_rays;
     if (n_shadow) *n_shadow = integ->stats().shadow_rays;

@@ -291,25 +291,49 @@ def test_area_light_mis_matches_the_references_render(gpu, case, plastic):
     assert np.sqrt(((_blocks(a, 8) - _blocks(b, 8)) ** 2).mean()) / b.mean() < 0.04
 
 
-def test_distant_light_scene_matches_the_references_render(gpu):
+def test_crop_window_is_the_window_of_the_full_frame(gpu, small_scene):
+    """Film "cropwindow": tiles are laid from the window's first pixel (integrator.cpp:237-246 over GetSampleBounds) but
+    a pixel's samples depend on its position in the FULL frame only, so the cropped film equals that window of the
+    full-frame film bit for bit — also when the window is sharded over ranks."""
+    sc, acc = small_scene
+    kw = dict(spp=3, maxdepth=4, light_pos=sc["light"], seed=11)
+    full, _ = gpu.WavefrontPathIntegrator(sc["camera"], **kw).Render(acc)
+    for crop in ((5, 77, 9, 50), (16, 32, 0, 64), (95, 96, 63, 64)):
+        x0, x1, y0, y1 = crop
+        part, st = gpu.WavefrontPathIntegrator(sc["camera"], crop=crop, **kw).Render(acc)
+        assert part.shape == (y1 - y0, x1 - x0, 4) and st["camera_rays"] == (y1 - y0) * (x1 - x0) * 3
+        assert np.array_equal(part, full[y0:y1, x0:x1])
+        both = [gpu.WavefrontPathIntegrator(sc["camera"], crop=crop, rank=r, world=2, **kw).Render(acc)[0] for r in range(2)]
+        assert np.array_equal(both[0] + both[1], part)
+    with pytest.raises(Exception):
+        gpu.WavefrontPathIntegrator(sc["camera"], crop=(10, 10, 0, 64), **kw).Render(acc)
+    with pytest.raises(Exception):
+        gpu.WavefrontPathIntegrator(sc["camera"], crop=(0, 97, 0, 64), **kw).Render(acc)
+
+
+@pytest.mark.parametrize("case", ["feet", "feet_crop"])
+def test_distant_light_scene_matches_the_references_render(gpu, case):
     """BASELINE config 4's scene as written (scenes/killeroo-feet): `LightSource "distant"` (lights/distant.cpp) and the
     "plastic" killeroo, whole frame at 192^2, against the reference's own render (tests/golden/ref_render.npz `feet`).
     A delta light: EstimateDirect takes no BSDF sample, so there are no MIS rays.  Statistical bar as above (only ~10 %
-    of the frame is covered, so the block RMSE is taken over covered blocks' mean)."""
+    of the frame is covered, so the block RMSE is taken over covered blocks' mean).  `feet_crop` = the same through
+    the scene's Film "cropwindow" [.3 .5 .4 .8] (the feet) of a 640^2 frame."""
     from conftest import load_golden
     from b200rt import scenes, wavefront as wf
     from b200rt.wavefront import film_to_rgb
     g = load_golden("ref_render.npz")
-    res, spp, maxdepth = (int(x) for x in g["feet_params"])
+    res, spp, maxdepth = (int(x) for x in g[case + "_params"])
     sc = scenes.killeroo_feet(xres=res, yres=res)
     tv = sc["tri_verts"]
     acc = gpu.MakeAccelerator("bvh", tv)
-    integ = gpu.WavefrontPathIntegrator(sc["camera"], spp=spp, maxdepth=maxdepth, light_I=g["feet_I"], seed=6,
+    integ = gpu.WavefrontPathIntegrator(sc["camera"], spp=spp, maxdepth=maxdepth, light_I=g[case + "_I"], seed=6,
                                         distant_light=(sc["light_from"] - sc["light_to"], wf.world_radius(tv)),
-                                        materials=sc["materials"], prim_material=np.zeros(len(tv), np.uint8))
+                                        materials=sc["materials"], prim_material=np.zeros(len(tv), np.uint8),
+                                        crop=sc["crop"] if case == "feet_crop" else None)
     film, st = integ.Render(acc)
-    rgb, ref = film_to_rgb(film).astype(np.float64), g["feet_rgb"].astype(np.float64)
-    nc, ns = (int(x) for x in g["feet_rays"])
+    rgb, ref = film_to_rgb(film).astype(np.float64), g[case + "_rgb"].astype(np.float64)
+    assert rgb.shape == ref.shape
+    nc, ns = (int(x) for x in g[case + "_rays"])
     assert abs(st["closest_rays"] / nc - 1) < 0.01, (st["closest_rays"], nc)
     assert abs(st["shadow_rays"] / ns - 1) < 0.01, (st["shadow_rays"], ns)
     assert st["mis_rays"] == 0

@@ -145,7 +145,7 @@ def test_plugin_with_this_repos_builders(host, gpu, tree):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("case", ["killeroo", "killeroo_full", "feet"])
+@pytest.mark.parametrize("case", ["killeroo", "killeroo_full", "feet", "feet_crop"])
 def test_cpp_wavefront_integrator_matches_the_references_render(host, gpu, case):
     """`Integrator "b200wavefront"` (host/b200integrator.cpp) over `Accelerator "b200"`, set up exactly like the
     reference's own render of tests/golden/ref_render.npz (PerspectiveCamera from LookAt/fov, Film + BoxFilter,
@@ -166,7 +166,8 @@ def test_cpp_wavefront_integrator_matches_the_references_render(host, gpu, case)
     g = load_golden("ref_render.npz")
     full = case == "killeroo_full"
     res, spp, maxdepth = (int(x) for x in g[case + "_params"])
-    feet = case == "feet"
+    feet = case.startswith("feet")
+    crop = case == "feet_crop"   # the scene's Film "cropwindow" [.3 .5 .4 .8] as well
     sc = scenes.killeroo_feet(xres=res, yres=res) if feet else scenes.killeroo_simple(xres=res, yres=res)
     tv = sc["tri_verts"]
     sl = sc.get("sphere_light")
@@ -189,7 +190,10 @@ def test_cpp_wavefront_integrator_matches_the_references_render(host, gpu, case)
         L.ref_render_set_distant(ft.ctypes.data)
     else:
         L.ref_render_set_distant(None)
-    out = np.zeros((res, res, 3), np.float32)
+    L.ref_render_set_crop.argtypes = [C.c_void_p]
+    L.ref_render_set_crop(np.array(sc["cropwindow"], np.float32).ctypes.data if crop else None)
+    oh, ow = (sc["crop"][3] - sc["crop"][2], sc["crop"][1] - sc["crop"][0]) if crop else (res, res)
+    out = np.zeros((oh, ow, 3), np.float32)
     nc, ns = C.c_uint64(), C.c_uint64()
     import tempfile
     with tempfile.TemporaryDirectory() as td:
@@ -197,12 +201,13 @@ def test_cpp_wavefront_integrator_matches_the_references_render(host, gpu, case)
                              kd.ctypes.data, 9, 0, 1, os.path.join(td, "img").encode(), out.ctypes.data, C.byref(nc), C.byref(ns),
                              None if prim_mat is None else prim_mat.ctypes.data, None if emitter is None else emitter.ctypes.data)
     L.ref_render_set_distant(None)
+    L.ref_render_set_crop(None)
     assert rc == 0
     ref = g[case + "_rgb"].astype(np.float64)
     img = out.astype(np.float64)
 
     def blocks(a, k=8):
-        return a.reshape(res // k, k, res // k, k, 3).mean((1, 3))
+        return a.reshape(oh // k, k, ow // k, k, 3).mean((1, 3))
     rnc, rns = (int(x) for x in g[case + "_rays"])
     assert abs(nc.value / rnc - 1) < 0.01 and abs(ns.value / rns - 1) < 0.01
     # python mirror with the same seed
@@ -216,7 +221,8 @@ def test_cpp_wavefront_integrator_matches_the_references_render(host, gpu, case)
         acc = gpu.MakeAccelerator("bvh", tv)
         integ = gpu.WavefrontPathIntegrator(sc["camera"], spp=spp, maxdepth=maxdepth, light_I=I, seed=9,
                                             distant_light=(sc["light_from"] - sc["light_to"], world_radius(tv)),
-                                            materials=sc["materials"], prim_material=np.zeros(len(tv), np.uint8))
+                                            materials=sc["materials"], prim_material=np.zeros(len(tv), np.uint8),
+                                            crop=sc["crop"] if crop else None)
     else:
         acc = gpu.MakeAccelerator("bvh", tv)
         integ = gpu.WavefrontPathIntegrator(sc["camera"], spp=spp, maxdepth=maxdepth, light_pos=light, light_I=I, kd=kd, seed=9)

@@ -151,10 +151,13 @@ def killeroo_feet(xres=5000, yres=5000):
     P, idx = killeroo_mesh()
     tv = _xform(_translate(-200, 100, -100), P)[idx].reshape(-1, 9).astype(np.float32) + np.float32(0)
     cam = _killeroo_camera(xres, yres)
-    crop = (int(np.ceil(.3 * xres)), int(np.ceil(.5 * xres)), int(np.ceil(.4 * yres)), int(np.ceil(.8 * yres)))
+    f32 = np.float32   # Film::croppedPixelBounds (film.cpp:56-60): ceil(int resolution * float window), in float
+    cropwindow = (.3, .5, .4, .8)
+    crop = (int(np.ceil(f32(xres) * f32(.3))), int(np.ceil(f32(xres) * f32(.5))),
+            int(np.ceil(f32(yres) * f32(.4))), int(np.ceil(f32(yres) * f32(.8))))
     # LightSource "distant" "point from" [400 20 30] "point to" [0 63 -110] (L = 1); Material "plastic" Kd (.4 .5 .4)
     # Ks .3 roughness .15 on every triangle (scenes/killeroo-feet:17-25)
-    return dict(name="killeroo-feet", tri_verts=tv, camera=cam, crop=crop,
+    return dict(name="killeroo-feet", tri_verts=tv, camera=cam, crop=crop, cropwindow=cropwindow,
                 light_dir=np.array([400 - 0, 20 - 63, 30 + 110], np.float32),
                 light_from=np.array([400, 20, 30], np.float32), light_to=np.array([0, 63, -110], np.float32),
                 materials=np.array([[1, .4, .5, .4, .3, .3, .3, .15]], np.float32))

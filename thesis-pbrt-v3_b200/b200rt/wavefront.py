@@ -16,7 +16,8 @@ class RenderDesc(C.Structure):
                 ("light_I", C.c_float * 3), ("kd", C.c_float * 3), ("tile_size", C.c_uint32), ("rank", C.c_uint32),
                 ("world", C.c_uint32), ("seed", C.c_uint32), ("max_batch", C.c_uint32),
                 ("light_kind", C.c_uint32), ("light_radius", C.c_float), ("light_prim", C.c_uint32),
-                ("materials", C.c_void_p), ("n_materials", C.c_uint32), ("prim_material", C.c_void_p)]
+                ("materials", C.c_void_p), ("n_materials", C.c_uint32), ("prim_material", C.c_void_p),
+                ("crop", C.c_uint32 * 4)]
 
 
 class RenderStats(C.Structure):
@@ -50,12 +51,14 @@ class WavefrontPathIntegrator:
 
     def __init__(self, camera, spp=8, maxdepth=5, light_pos=(0, 0, 0), light_I=(1, 1, 1), kd=(.5, .5, .5),
                  rank=0, world=1, seed=0, tile_size=16, max_batch=0, sphere_light=None, materials=None,
-                 prim_material=None, distant_light=None):
+                 prim_material=None, distant_light=None, crop=None):
         """sphere_light=(radius, prim): `AreaLightSource "area" "color L" light_I` on the full sphere primitive number
         `prim` of the aggregate, centred at light_pos (sampled with MIS like EstimateDirect).  materials: (n, 8) rows
         (kind, Kd.rgb, Ks.rgb, roughness) + prim_material: (n_prims,) uint8 index per primitive.
         distant_light=(from - to, world_radius): `LightSource "distant"` with radiance light_I (lights/distant.cpp);
-        world_radius = the aggregate's bounding-sphere radius (see world_radius())."""
+        world_radius = the aggregate's bounding-sphere radius (see world_radius()).
+        crop=(x0, x1, y0, y1): Film "cropwindow" in pixels (scenes.killeroo_feet()["crop"]); the film then holds
+        (y1-y0, x1-x0) pixels, as the reference's Film does."""
         d = RenderDesc()
         for k in ("eye", "dir", "right", "up"):
             setattr(d.camera, k, (C.c_float * 3)(*[float(x) for x in camera[k]]))
@@ -67,6 +70,8 @@ class WavefrontPathIntegrator:
         d.tile_size, d.rank, d.world, d.seed, d.max_batch = tile_size, rank, world, seed, max_batch
         if sphere_light is not None:
             d.light_kind, d.light_radius, d.light_prim = 1, float(sphere_light[0]), int(sphere_light[1])
+        if crop is not None:
+            d.crop = (C.c_uint32 * 4)(*[int(c) for c in crop])
         if distant_light is not None:
             w = np.asarray(distant_light[0], np.float32)
             w = w / np.sqrt((w * w).sum(dtype=np.float32))
@@ -81,6 +86,9 @@ class WavefrontPathIntegrator:
 
     @property
     def shape(self):
+        c = self.desc.crop
+        if c[0] or c[1] or c[2] or c[3]:
+            return (c[3] - c[2], c[1] - c[0], 4)
         return (self.desc.camera.yres, self.desc.camera.xres, 4)
 
     def tiles(self):

@@ -36,7 +36,8 @@ constexpr float kShadowEpsilon = 0.0001f;  // pbrt.h:204
 constexpr float kGamma7 = rt_gamma(7);
 
 struct Tiling {
-    uint32_t xres, yres, tile, ntx, nty, rank, world, spp;
+    uint32_t xres, yres, tile, ntx, nty, rank, world, spp;   // xres, yres = extent of the film's crop window
+    uint32_t x0, y0;            // its first pixel inside the camera's full frame (Film::croppedPixelBounds.pMin)
     uint32_t n_tiles_rank;      // tiles owned by this rank
     uint64_t n_paths_rank;      // n_tiles_rank * tile^2 * spp (incl. slots outside the image on edge tiles)
 };
@@ -117,8 +118,9 @@ __global__ void k_camera(const __grid_constant__ WfParams P, uint64_t batchStart
     }
     const uint32_t slot = warp_append(active, count);
     if (!active) return;
-    const uint32_t pix = y * P.cam.xres + x;
-    const float fx = (x + rnd(P.seed, pix, s, 0)) / P.cam.xres, fy = (y + rnd(P.seed, pix, s, 1)) / P.cam.yres;
+    const uint32_t gx = x + P.tl.x0, gy = y + P.tl.y0;   // pixel in the full frame
+    const uint32_t pix = gy * P.cam.xres + gx;
+    const float fx = (gx + rnd(P.seed, pix, s, 0)) / P.cam.xres, fy = (gy + rnd(P.seed, pix, s, 1)) / P.cam.yres;
     const float sx = 2.f * fx - 1.f, sy = 1.f - 2.f * fy;  // raster x grows along camera +x, raster y downwards (camera.h ScreenToRaster)
     float dx = P.cam.dir[0] + sx * P.cam.right[0] + sy * P.cam.up[0];
     float dy = P.cam.dir[1] + sx * P.cam.right[1] + sy * P.cam.up[1];
@@ -337,7 +339,7 @@ __global__ void k_shade(const __grid_constant__ WfParams P, uint32_t depth, uint
                     path_pixel(P.tl, batchStart + path, gx, gy, gs);
                     ShadeOut o;
                     o.wantShadow = o.wantNext = o.wantMis = false;
-                    shade_general(P, gm, depth, gy * P.cam.xres + gx, gs, p, pe, ng, nf, wo, bt, o);
+                    shade_general(P, gm, depth, (gy + P.tl.y0) * P.cam.xres + gx + P.tl.x0, gs, p, pe, ng, nf, wo, bt, o);
                     wantShadow = o.wantShadow; so = o.so; sd = o.sd; contrib = o.contrib;
                     wantMis = o.wantMis; mo = o.mo; md = o.md; mcontrib = o.mcontrib;
                     wantNext = o.wantNext; no = o.no; nd = o.nd;
@@ -348,7 +350,7 @@ __global__ void k_shade(const __grid_constant__ WfParams P, uint32_t depth, uint
                 const float d2 = wl.x * wl.x + wl.y * wl.y + wl.z * wl.z;
                 uint32_t x, y, s;
                 path_pixel(P.tl, batchStart + path, x, y, s);
-                const uint32_t pix = y * P.cam.xres + x, dim = 2 + 3 * depth;
+                const uint32_t pix = (y + P.tl.y0) * P.cam.xres + x + P.tl.x0, dim = 2 + 3 * depth;
                 if (area) {
                     // ---- EstimateDirect with MIS (integrator.cpp:109-217) against the sphere light ----
                     const float r2 = P.light_radius * P.light_radius;
@@ -559,9 +561,9 @@ __global__ void k_film(const __grid_constant__ WfParams P, uint64_t batchStart, 
         const float4 l = L[(size_t)i * P.tl.spp + k];
         acc.x += l.x; acc.y += l.y; acc.z += l.z; acc.w += l.w;
     }
-    float4 f = film[(size_t)y * P.cam.xres + x];
+    float4 f = film[(size_t)y * P.tl.xres + x];
     f.x += acc.x; f.y += acc.y; f.z += acc.z; f.w += acc.w;
-    film[(size_t)y * P.cam.xres + x] = f;
+    film[(size_t)y * P.tl.xres + x] = f;
 }
 
 // Per-pixel traversal statistics (b200rt_render_heatmaps): the rays of queue entries [0, *nQ) add their per-ray
@@ -572,7 +574,7 @@ __global__ void k_heat(const __grid_constant__ WfParams P, uint64_t batchStart, 
     if (i >= *nQ) return;
     uint32_t x, y, s;
     path_pixel(P.tl, batchStart + qPath[i], x, y, s);
-    const size_t npx = (size_t)P.cam.xres * P.cam.yres, pix = (size_t)y * P.cam.xres + x;
+    const size_t npx = (size_t)P.tl.xres * P.tl.yres, pix = (size_t)y * P.tl.xres + x;
     const uint4 v = perRay[i];
     if (v.x) atomicAdd(heat + (B200RT_HEAT_PRIM + plane) * npx + pix, v.x);
     if (v.y) atomicAdd(heat + (B200RT_HEAT_NODE + plane) * npx + pix, v.y);
@@ -615,6 +617,13 @@ int tiling_of(const b200rt_render_desc *d, Tiling *t) {
     if (!d || d->camera.xres == 0 || d->camera.yres == 0 || d->spp == 0 || d->world == 0 || d->rank >= d->world)
         return set_error(B200RT_EINVAL, "bad render description (resolution/spp/rank/world)");
     t->xres = d->camera.xres; t->yres = d->camera.yres;
+    t->x0 = t->y0 = 0;
+    if (d->crop[0] | d->crop[1] | d->crop[2] | d->crop[3]) {   // Film "cropwindow" in pixels: [x0, x1) x [y0, y1)
+        if (d->crop[0] >= d->crop[1] || d->crop[2] >= d->crop[3] || d->crop[1] > d->camera.xres || d->crop[3] > d->camera.yres)
+            return set_error(B200RT_EINVAL, "bad crop window [%u, %u) x [%u, %u)", d->crop[0], d->crop[1], d->crop[2], d->crop[3]);
+        t->x0 = d->crop[0]; t->y0 = d->crop[2];
+        t->xres = d->crop[1] - d->crop[0]; t->yres = d->crop[3] - d->crop[2];
+    }
     t->tile = d->tile_size ? d->tile_size : 16;
     t->ntx = (t->xres + t->tile - 1) / t->tile;
     t->nty = (t->yres + t->tile - 1) / t->tile;

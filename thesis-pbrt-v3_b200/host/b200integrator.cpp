@@ -118,9 +118,10 @@ void B200WavefrontIntegrator::Render(const Scene &scene) {
     b200rt_render_desc d;
     std::memset(&d, 0, sizeof(d));
     if (!describeCamera(*camera, &d.camera)) return;
-    if (film->croppedPixelBounds.pMin != Point2i(0, 0) || film->croppedPixelBounds.pMax != film->fullResolution) {
-        Error("b200wavefront: crop windows are not supported yet");
-        return;
+    const Bounds2i cb = film->croppedPixelBounds;   // Film "cropwindow" (film.cpp:49-57); the film's pixels are the window's
+    if (cb.pMin != Point2i(0, 0) || cb.pMax != film->fullResolution) {
+        d.crop[0] = (uint32_t)cb.pMin.x; d.crop[1] = (uint32_t)cb.pMax.x;
+        d.crop[2] = (uint32_t)cb.pMin.y; d.crop[3] = (uint32_t)cb.pMax.y;
     }
     if (film->filter->radius.x > 0.5f || film->filter->radius.y > 0.5f) {
         Error("b200wavefront: pixel filters wider than one pixel are not supported (use PixelFilter \"box\")");
@@ -229,7 +230,7 @@ void B200WavefrontIntegrator::Render(const Scene &scene) {
     d.tile_size = 16;   // integrator.cpp:237
     d.rank = (uint32_t)rank; d.world = (uint32_t)world; d.seed = (uint32_t)seed;
 
-    const size_t nPix = (size_t)d.camera.xres * d.camera.yres;
+    const size_t nPix = (size_t)cb.Area();
     std::vector<float> rgbw(4 * nPix, 0.f);
     if (b200rt_render(accel->deviceScene(), &d, rgbw.data(), &lastStats, nullptr)) {
         Error("b200wavefront: %s", b200rt_last_error());
