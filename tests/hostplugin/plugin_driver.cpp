@@ -112,6 +112,10 @@ extern "C" int ref_render_get_distant(float *from_to);
 extern "C" void ref_render_get_crop(float *cw);           // set through ref_render_set_crop   // set through ref_render_set_distant (oracle/ref/ref_render.cpp)
 std::shared_ptr<pbrt::Shape> shape_of(const pbrt::Primitive *p);   // plugin_shape_of.cpp (GeometricPrimitive::shape is private)
 
+// "bool generalstats" of the NEXT plugin_render calls (the thesis's per-pixel statistic matrices, Film::WriteGeneralStats)
+static bool g_generalStats = false;
+extern "C" void plugin_set_generalstats(int on) { g_generalStats = on != 0; }
+
 extern "C" int plugin_render(ref_scene *s, const char *tree, const float *cam, int xres, int yres, int spp, int maxdepth,
                              const float *light_pos, const float *light_I, const float *kd, int seed, int rank, int world,
                              const char *tmp_prefix, float *out_rgb, uint64_t *n_closest, uint64_t *n_shadow,
@@ -188,6 +192,7 @@ extern "C" int plugin_render(ref_scene *s, const char *tree, const float *cam, i
     ParamSet ips;
     auto addInt = [&](const char *name, int v) { std::unique_ptr<int[]> a(new int[1]); a[0] = v; ips.AddInt(name, std::move(a), 1); };
     addInt("maxdepth", maxdepth); addInt("seed", seed); addInt("rank", rank); addInt("world", world);
+    if (g_generalStats) { std::unique_ptr<bool[]> b(new bool[1]); b[0] = true; ips.AddBool("generalstats", std::move(b), 1); }
     std::unique_ptr<B200WavefrontIntegrator> integ(CreateB200WavefrontIntegrator(ips, sampler, camera));
     integ->Render(scene);
     int w = 0, h = 0;

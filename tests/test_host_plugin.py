@@ -239,3 +239,70 @@ def test_cpp_wavefront_integrator_matches_the_references_render(host, gpu, case)
     assert np.sqrt(((blocks(img) - blocks(ref)) ** 2)[cov].mean()) / rm < (0.03 if case == "killeroo" else 0.04)
     assert np.sqrt(((blocks(img) - blocks(py)) ** 2)[cov].mean()) / rm < (0.005 if case == "killeroo" else 0.01)
     assert abs(st["closest_rays"] / nc.value - 1) < 1e-3
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("tree", ["bvh", "kdtree"])
+def test_cpp_integrator_writes_the_thesis_statistic_matrices(host, gpu, tree):
+    """`Integrator "b200wavefront" "bool generalstats" "true"`: the per-pixel GeneralStats the thesis accumulates
+    (integrator.cpp:327-328) come from the instrumented kernels, are stored in the reference's Film pixels and written by
+    the reference's own Film::WriteGeneralStats (film.cpp:170-209) as `<image>-<counter>.txt` matrices.  Compared with
+    the Python mirror of the same driver (same seed: totals within 0.2 %) and, for the BVH, with the matrices of the
+    reference's own render of the frame (golden killeroo_heat; different sampler: totals 1.5 %, 8x8 blocks 4 %).
+    The node counter lands in the field the tree's family owns: kdTreeNodeTraversals for the kd-tree (the BVH's own
+    counter is not among the matrices the reference dumps)."""
+    from conftest import load_golden
+    from b200rt import scenes, wavefront as wf
+    rb, L = host
+    L.plugin_render.argtypes = [C.c_void_p, C.c_char_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
+                                C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_char_p, C.c_void_p, C.POINTER(C.c_uint64),
+                                C.POINTER(C.c_uint64), C.c_void_p, C.c_void_p]
+    g = load_golden("ref_render.npz")
+    res, spp, maxdepth = (int(x) for x in g["killeroo_params"])
+    if tree != "bvh":
+        spp = 16
+    sc = scenes.killeroo_simple(xres=res, yres=res)
+    tv = sc["tri_verts"]
+    S = rb.RefScene(tv.reshape(-1, 3), np.arange(3 * len(tv), dtype=np.int32).reshape(-1, 3), L=L)
+    r = scenes._rot_z(5.0)
+    eye = scenes._xform(r, np.array([[400.0, 20, 30]]))[0]
+    look = scenes._xform(r, np.array([[0.0, 63, -110]]))[0]
+    cam = np.array(list(eye) + list(look) + [0, 0, 1, 39.0], np.float32)
+    light = np.asarray(sc["light"], np.float32)
+    I, kd = g["killeroo_I"].astype(np.float32), g["killeroo_kd"].astype(np.float32)
+    out = np.zeros((res, res, 3), np.float32)
+    nc, ns = C.c_uint64(), C.c_uint64()
+    import tempfile
+    names = ["primitiveIntersections", "primitiveIntersectionsP", "kdTreeNodeTraversals", "kdTreeNodeTraversalsP",
+             "leafNodeTraversals", "leafNodeTraversalsP", "bspTreeNodeTraversals"]
+    mats = {}
+    L.plugin_set_generalstats(1)
+    try:
+        with tempfile.TemporaryDirectory() as td:
+            rc = L.plugin_render(S.h, tree.encode(), cam.ctypes.data, res, res, spp, maxdepth, light.ctypes.data, I.ctypes.data,
+                                 kd.ctypes.data, 9, 0, 1, os.path.join(td, "img").encode(), out.ctypes.data, C.byref(nc), C.byref(ns),
+                                 None, None)
+            assert rc == 0
+            for n in names:
+                mats[n] = np.loadtxt(os.path.join(td, "img-%s.txt" % n), dtype=np.uint64).reshape(res, res)
+    finally:
+        L.plugin_set_generalstats(0)
+    acc = gpu.MakeAccelerator(tree, tv)
+    integ = gpu.WavefrontPathIntegrator(sc["camera"], spp=spp, maxdepth=maxdepth, light_pos=light, light_I=I, kd=kd, seed=9)
+    _, heat, _ = wf.render_heatmaps(integ, acc)
+    planes = {"primitiveIntersections": 0, "primitiveIntersectionsP": 1, "leafNodeTraversals": 4, "leafNodeTraversalsP": 5}
+    if tree == "kdtree":
+        planes.update(kdTreeNodeTraversals=2, kdTreeNodeTraversalsP=3)
+        assert mats["kdTreeNodeTraversals"].sum() > 0
+    else:
+        assert mats["kdTreeNodeTraversals"].sum() == 0
+    assert mats["bspTreeNodeTraversals"].sum() == 0
+    ref = g["killeroo_heat"].astype(np.float64)
+    for n, k in planes.items():
+        a, b = mats[n].astype(np.float64), heat[k].astype(np.float64)
+        assert abs(a.sum() / b.sum() - 1) < 2e-3, (n, a.sum(), b.sum())
+        if tree == "bvh":
+            assert abs(a.sum() / ref[k].sum() - 1) < 0.015, (n, a.sum(), ref[k].sum())
+            ab = a.reshape(res // 8, 8, res // 8, 8).mean((1, 3))
+            bb = ref[k].reshape(res // 8, 8, res // 8, 8).mean((1, 3))
+            assert np.sqrt(((ab - bb) ** 2).mean()) / bb.mean() < 0.04, n

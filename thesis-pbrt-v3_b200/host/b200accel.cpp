@@ -230,6 +230,7 @@ B200Accel::B200Accel(std::vector<std::shared_ptr<Primitive>> p, const ParamSet &
     if (ownNodes) b200rt_free(ownNodes);
     if (ownIdx) b200rt_free(ownIdx);
     if (rc) { Error("b200: %s", b200rt_last_error()); scene = nullptr; return; }
+    kind = (int)d.kind;
     for (const auto &q : prims) bounds = Union(bounds, q->WorldBound());
     g_current.store(this);
 }

@@ -59,12 +59,14 @@ class B200Accel : public Aggregate {
     const std::shared_ptr<Primitive> &primitive(uint32_t i) const { return prims[i]; }
     size_t primitiveCount() const { return prims.size(); }
     b200rt_scene *deviceScene() const { return scene; }
+    int treeKind() const { return kind; }   // B200RT_BVH ... B200RT_BSPKD of the uploaded tree
     // The process-global the `b200wavefront` integrator looks up (Scene::aggregate is private, scene.h:78).
     static const B200Accel *current();
 
   private:
     std::vector<std::shared_ptr<Primitive>> prims;
     b200rt_scene *scene = nullptr;
+    int kind = B200RT_BVH;
     Bounds3f bounds;
 };
 

@@ -31,6 +31,7 @@
 #include "core/primitive.h"
 #include "shapes/sphere.h"
 #include "materials/plastic.h"
+#include "core/film.h"   // Film::pixels / Pixel::stats for "bool generalstats" (no accessor either)
 #undef private
 #undef protected
 
@@ -232,7 +233,10 @@ void B200WavefrontIntegrator::Render(const Scene &scene) {
 
     const size_t nPix = (size_t)cb.Area();
     std::vector<float> rgbw(4 * nPix, 0.f);
-    if (b200rt_render(accel->deviceScene(), &d, rgbw.data(), &lastStats, nullptr)) {
+    std::vector<uint32_t> heat;
+    if (generalStats) heat.assign((size_t)B200RT_HEAT_PLANES * nPix, 0u);
+    if (generalStats ? b200rt_render_heatmaps(accel->deviceScene(), &d, rgbw.data(), heat.data(), &lastStats, nullptr)
+                     : b200rt_render(accel->deviceScene(), &d, rgbw.data(), &lastStats, nullptr)) {
         Error("b200wavefront: %s", b200rt_last_error());
         return;
     }
@@ -246,6 +250,25 @@ void B200WavefrontIntegrator::Render(const Scene &scene) {
     }
     film->SetImage(img.get());
     film->WriteImage();
+    if (generalStats) {
+        // pixel.stats += ray.stats over the pixel's samples (integrator.cpp:327-328); the node counter is the one the
+        // uploaded tree's family increments (bvh.cpp / kdtreeaccel.cpp / rbsp.cpp, BSP.cpp); rays = samples taken
+        const int k = accel->treeKind();
+        for (size_t i = 0; i < nPix; ++i) {
+            GeneralStats &g = film->pixels[i].stats;
+            g = GeneralStats();
+            g.rays = (uint64_t)rgbw[4 * i + 3];
+            g.primitiveIntersections = heat[B200RT_HEAT_PRIM * nPix + i];
+            g.primitiveIntersectionsP = heat[B200RT_HEAT_PRIM_P * nPix + i];
+            uint64_t &n = k == B200RT_BVH ? g.bvhTreeNodeTraversals : k == B200RT_KDTREE ? g.kdTreeNodeTraversals : g.bspTreeNodeTraversals;
+            uint64_t &np = k == B200RT_BVH ? g.bvhTreeNodeTraversalsP : k == B200RT_KDTREE ? g.kdTreeNodeTraversalsP : g.bspTreeNodeTraversalsP;
+            n = heat[B200RT_HEAT_NODE * nPix + i];
+            np = heat[B200RT_HEAT_NODE_P * nPix + i];
+            g.leafNodeTraversals = heat[B200RT_HEAT_LEAF * nPix + i];
+            g.leafNodeTraversalsP = heat[B200RT_HEAT_LEAF_P * nPix + i];
+        }
+        film->WriteGeneralStats();   // film.cpp:170-188: <image name>-primitiveIntersections.txt, ...
+    }
 }
 
 B200WavefrontIntegrator *CreateB200WavefrontIntegrator(const ParamSet &params, std::shared_ptr<Sampler> sampler,
@@ -255,7 +278,8 @@ B200WavefrontIntegrator *CreateB200WavefrontIntegrator(const ParamSet &params, s
     const int rank = params.FindOneInt("rank", envInt("RANK", 0));
     const int world = params.FindOneInt("world", envInt("WORLD_SIZE", 1));
     const int seed = params.FindOneInt("seed", 0);
-    return new B200WavefrontIntegrator(maxDepth, std::move(camera), std::move(sampler), rank, world, seed);
+    const bool generalStats = params.FindOneBool("generalstats", false);
+    return new B200WavefrontIntegrator(maxDepth, std::move(camera), std::move(sampler), rank, world, seed, generalStats);
 }
 
 }  // namespace pbrt

@@ -28,8 +28,9 @@ class B200WavefrontIntegrator : public Integrator {
     // rank/world: this process renders the 16x16 tiles t with t % world == rank (integrator.cpp:237-239 tile grid);
     // the other tiles' pixels stay black in this process's film (the host application gathers them).
     B200WavefrontIntegrator(int maxDepth, std::shared_ptr<const Camera> camera, std::shared_ptr<Sampler> sampler,
-                            int rank = 0, int world = 1, int seed = 0)
-        : maxDepth(maxDepth), camera(std::move(camera)), sampler(std::move(sampler)), rank(rank), world(world), seed(seed) {}
+                            int rank = 0, int world = 1, int seed = 0, bool generalStats = false)
+        : maxDepth(maxDepth), camera(std::move(camera)), sampler(std::move(sampler)), rank(rank), world(world), seed(seed),
+          generalStats(generalStats) {}
     void Render(const Scene &scene);
     const b200rt_render_stats &stats() const { return lastStats; }
 
@@ -38,11 +39,15 @@ class B200WavefrontIntegrator : public Integrator {
     std::shared_ptr<const Camera> camera;
     std::shared_ptr<Sampler> sampler;
     const int rank, world, seed;
+    const bool generalStats;
     b200rt_render_stats lastStats{};
 };
 
 // Parameters: "integer maxdepth" (path.cpp:209, default 5), "integer rank" / "integer world" (default: the RANK /
-// WORLD_SIZE environment of a torchrun-style launch, else 0 / 1), "integer seed".
+// WORLD_SIZE environment of a torchrun-style launch, else 0 / 1), "integer seed", "bool generalstats" (default false:
+// true renders through the instrumented kernels, b200rt_render_heatmaps, fills the Film's per-pixel GeneralStats and
+// writes the thesis's statistic matrices with Film::WriteGeneralStats like SamplerIntegrator::Render does,
+// integrator.cpp:327-328,359).
 B200WavefrontIntegrator *CreateB200WavefrontIntegrator(const ParamSet &params, std::shared_ptr<Sampler> sampler,
                                                        std::shared_ptr<const Camera> camera);
 
