@@ -69,8 +69,18 @@ typedef struct {
                               film.cpp:49-57: ceil(res * window)); all zero = the whole frame.  Tiles are laid from the
                               window's first pixel (integrator.cpp:237-246 over GetSampleBounds), and `film` / `heat` hold
                               (y1-y0) x (x1-x0) pixels, like the reference's Film. */
+    /* ---- appended in ABI v6 ---- */
+    float light_to_world[9]; /* B200RT_LIGHT_INFINITE (LightSource "infinite", lights/infinite.cpp:44-150) with a CONSTANT
+                              radiance — what the reference builds when "mapname" is absent or unreadable (a 1x1 map,
+                              infinite.cpp:52-60; scenes/living-room's "textures/Sky 19.pfm" is not in the tree):
+                              row-major 3x3 rotation part of LightToWorld, light_I = its radiance "L" (x "scale"),
+                              light_radius = the scene's bounding-sphere radius (Preprocess).  Sampled with multiple
+                              importance sampling as EstimateDirect does: Sample_Li over (theta, phi) = (u1 pi, u0 2pi)
+                              with pdf 1 / (2 pi^2 sin theta) -> shadow ray to p + wi * 2 * radius; a BSDF-sampled
+                              closest-hit "MIS" ray that contributes Le when it ESCAPES (integrator.cpp:196-212); camera
+                              rays that escape add Le (path.cpp:97-107).  All zero = identity. */
 } b200rt_render_desc;
-enum { B200RT_LIGHT_POINT = 0, B200RT_LIGHT_SPHERE = 1, B200RT_LIGHT_DISTANT = 2 };
+enum { B200RT_LIGHT_POINT = 0, B200RT_LIGHT_SPHERE = 1, B200RT_LIGHT_DISTANT = 2, B200RT_LIGHT_INFINITE = 3 };
 enum { B200RT_MAT_MATTE = 0, B200RT_MAT_PLASTIC = 1 /* materials/plastic.cpp: Kd + Ks microfacet lobe, roughness remapped */ };
 
 typedef struct {

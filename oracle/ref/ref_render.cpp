@@ -26,6 +26,7 @@
 #include "lights/point.h"
 #include "lights/diffuse.h"
 #include "lights/distant.h"
+#include "lights/infinite.h"
 #include "materials/matte.h"
 #include "materials/plastic.h"
 #include "samplers/halton.h"
@@ -100,6 +101,24 @@ static float g_from_to[6];
 extern "C" void ref_render_set_distant(const float *from_to) {
     g_distant = from_to != nullptr;
     if (from_to) std::memcpy(g_from_to, from_to, sizeof(g_from_to));
+}
+
+// LightSource "infinite" "rgb L" (no readable "mapname": the constant 1x1 map of lights/infinite.cpp:52-60) for the NEXT
+// renders, under the LightToWorld whose row-major 4x4 is l2w16 (NULL arguments = off).  ReadImage above returns null,
+// exactly what the reference gets for scenes/living-room's missing "textures/Sky 19.pfm".
+static bool g_infinite = false;
+static float g_infL[3], g_infM[16];
+extern "C" void ref_render_set_infinite(const float *L_rgb, const float *l2w16) {
+    g_infinite = L_rgb != nullptr && l2w16 != nullptr;
+    if (g_infinite) { std::memcpy(g_infL, L_rgb, sizeof(g_infL)); std::memcpy(g_infM, l2w16, sizeof(g_infM)); }
+}
+// `Transform [16 floats]` before `Camera` (scenes/living-room/scene.pbrt:2): the world-to-camera CTM as a row-major
+// 4x4 for the NEXT renders instead of the LookAt in `cam` (NULL = LookAt again); cam[9] stays the fov.
+static bool g_camMatrix = false;
+static float g_w2c[16];
+extern "C" void ref_render_set_camera_matrix(const float *w2c16) {
+    g_camMatrix = w2c16 != nullptr;
+    if (w2c16) std::memcpy(g_w2c, w2c16, sizeof(g_w2c));
 }
 
 // Film "float cropwindow" [x0 x1 y0 y1] for the NEXT renders (NULL = whole frame); out_rgb / out_heat then hold the
@@ -184,8 +203,14 @@ extern "C" int ref_render(ref_scene *s, const char *accel_kind, const float *cam
     Float li[3] = {light_I[0], light_I[1], light_I[2]};
     Transform l2w = Translate(Vector3f(light_pos[0], light_pos[1], light_pos[2]));
     std::vector<std::shared_ptr<Light>> lights;
+    if (n_threads != 1) ParallelInit();   // as pbrtInit does before any object is made (InfiniteAreaLight's constructor runs a ParallelFor)
     if (area) lights.push_back(area);
-    else if (g_distant)
+    else if (g_infinite) {
+        Matrix4x4 m(g_infM[0], g_infM[1], g_infM[2], g_infM[3], g_infM[4], g_infM[5], g_infM[6], g_infM[7], g_infM[8], g_infM[9],
+                    g_infM[10], g_infM[11], g_infM[12], g_infM[13], g_infM[14], g_infM[15]);
+        Float lrgb[3] = {g_infL[0], g_infL[1], g_infL[2]};
+        lights.push_back(std::make_shared<InfiniteAreaLight>(Transform(m), Spectrum::FromRGB(lrgb), 1, std::string("")));
+    } else if (g_distant)
         lights.push_back(std::make_shared<DistantLight>(Transform(), Spectrum::FromRGB(li),
                                                         Point3f(g_from_to[0], g_from_to[1], g_from_to[2]) -
                                                             Point3f(g_from_to[3], g_from_to[4], g_from_to[5])));
@@ -200,6 +225,9 @@ extern "C" int ref_render(ref_scene *s, const char *accel_kind, const float *cam
     const Vector2i cres = film->croppedPixelBounds.Diagonal();
     // LookAt + Camera "perspective" (api.cpp:1338-1370 pbrtCamera; cameras/perspective.cpp:231-279)
     Transform w2c = LookAt(Point3f(cam[0], cam[1], cam[2]), Point3f(cam[3], cam[4], cam[5]), Vector3f(cam[6], cam[7], cam[8]));
+    if (g_camMatrix)
+        w2c = Transform(Matrix4x4(g_w2c[0], g_w2c[1], g_w2c[2], g_w2c[3], g_w2c[4], g_w2c[5], g_w2c[6], g_w2c[7], g_w2c[8], g_w2c[9],
+                                  g_w2c[10], g_w2c[11], g_w2c[12], g_w2c[13], g_w2c[14], g_w2c[15]));
     Transform c2w = Inverse(w2c);
     AnimatedTransform ac2w(&c2w, 0.f, &c2w, 1.f);
     Float frame = Float(xres) / Float(yres);
@@ -212,7 +240,6 @@ extern "C" int ref_render(ref_scene *s, const char *accel_kind, const float *cam
     else sampler.reset(new RandomSampler(spp));
     PathIntegrator integ(maxdepth, camera, sampler, film->GetSampleBounds(), 1.f, "spatial");
 
-    if (n_threads != 1) ParallelInit();
     const auto t0 = std::chrono::steady_clock::now();
     integ.Render(scene);     // -> film->WriteImage() -> the WriteImage above
     if (render_seconds) *render_seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();

@@ -163,7 +163,7 @@ class RefAccel:
 
 def render(scene, accel_kind, eye, look, up, fov, xres, yres, spp, maxdepth, light_pos, light_I, kd,
            sampler="random", n_threads=0, tmp_prefix=None, heat=False, prim_mat=None, emitter_L=None, timing=False,
-           distant=None, cropwindow=None):
+           distant=None, cropwindow=None, infinite=None, camera_matrix=None):
     """The reference's OWN render (SamplerIntegrator::Render + PathIntegrator::Li + Film, oracle/ref/ref_render.cpp)
     of `scene` with a matte material and one point light.  Returns (rgb (yres,xres,3), n_closest, n_shadow)."""
     import tempfile
@@ -186,6 +186,17 @@ def render(scene, accel_kind, eye, look, up, fov, xres, yres, spp, maxdepth, lig
         scene.L.ref_render_set_distant(_p(ft))
     elif distant is not None:
         raise RuntimeError("libpbrtref.so predates ref_render_set_distant: rebuild oracle/ref")
+    # infinite=(L rgb, LightToWorld 4x4 row-major): LightSource "infinite" with a constant map; camera_matrix = the
+    # world-to-camera CTM of a `Transform [...]` before `Camera` (eye/look/up are then ignored, fov still applies)
+    if hasattr(scene.L, "ref_render_set_infinite"):
+        scene.L.ref_render_set_infinite.argtypes = [C.c_void_p, C.c_void_p]
+        scene.L.ref_render_set_camera_matrix.argtypes = [C.c_void_p]
+        il = None if infinite is None else np.ascontiguousarray(infinite[0], np.float32)
+        im = None if infinite is None else np.ascontiguousarray(infinite[1], np.float32).reshape(16)
+        scene.L.ref_render_set_infinite(_p(il), _p(im))
+        scene.L.ref_render_set_camera_matrix(_p(None if camera_matrix is None else np.ascontiguousarray(camera_matrix, np.float32).reshape(16)))
+    elif infinite is not None or camera_matrix is not None:
+        raise RuntimeError("libpbrtref.so predates ref_render_set_infinite: rebuild oracle/ref")
     if hasattr(scene.L, "ref_render_set_crop"):
         scene.L.ref_render_set_crop.argtypes = [C.c_void_p]
         scene.L.ref_render_set_crop(_p(None if cropwindow is None else np.array(cropwindow, np.float32)))

@@ -219,6 +219,60 @@ def with_sphere_light(sc, plastic=False):
     return verts, prim_kind, rows, pm, mats
 
 
+def matrix_camera(world_to_camera, fov_deg, xres, yres):
+    """Camera of a scene file that sets the CTM with `Transform [...]` before `Camera "perspective"` (e.g.
+    scenes/living-room/scene.pbrt:2,6): camera-to-world = inverse CTM, whose columns are the camera's x (raster right),
+    y (up), z (view direction) axes and position (cameras/perspective.cpp:61-66).  Works for CTMs that swap
+    handedness (living-room's has determinant -1)."""
+    c2w = np.linalg.inv(np.asarray(world_to_camera, np.float64))
+    right, up, d, eye = c2w[:3, 0], c2w[:3, 1], c2w[:3, 2], c2w[:3, 3]
+    right, up, d = right / np.linalg.norm(right), up / np.linalg.norm(up), d / np.linalg.norm(d)
+    aspect = xres / yres
+    t = np.tan(np.radians(fov_deg) / 2)
+    sx, sy = (aspect, 1.0) if aspect > 1 else (1.0, 1 / aspect)
+    return dict(eye=eye.astype(np.float32), dir=d.astype(np.float32), right=(right * t * sx).astype(np.float32),
+                up=(up * t * sy).astype(np.float32), xres=int(xres), yres=int(yres), world_to_camera=np.asarray(world_to_camera, np.float64))
+
+
+def living_room(xres=1280, yres=720):
+    """scenes/living-room/scene.pbrt (BASELINE config 5): the reference's OWN geometry — 65 `plymesh` shapes,
+    143 163 triangles in file order, world space — from the committed fixture tests/golden/living_room_mesh.npz
+    (made from the reference's scene by tests/golden/make_living_room.py); camera = the file's `Transform` + fov
+    58.715508; film 1280x720 in the file (BASELINE quotes 1920x1080 @ 1024 spp).
+
+    Light: `LightSource "infinite" "string mapname" "textures/Sky 19.pfm"` under the file's rotation; the map is NOT in
+    the reference tree, so the reference itself falls back to a constant radiance L = 1 (infinite.cpp:52-60) — that is
+    what `infinite_light` describes.
+    Materials: the file uses matte (88 114 triangles), substrate, glass, metal, uber and mirror with image textures
+    (two of the four texture files are absent too).  The wavefront shade stage has matte and plastic only, so
+    `materials` is a documented SUBSTITUTION, identical on the reference side of the parity test: matte keeps its Kd;
+    substrate becomes plastic (its Kd, or .5 where Kd is a texture, Ks .04, its roughness); everything else is matte
+    Kd .5.  Vertex normals and uvs of the PLY files are not used for shading (geometric normals on both sides).  The
+    TRAVERSAL workload (tree, rays, hit parity) is the reference scene's as shipped."""
+    z = np.load(os.path.join(_GOLDEN, "living_room_mesh.npz"))
+    P, UV, idx = z["P"], z["UV"], z["idx"]
+    tv = P[idx].reshape(-1, 9).astype(np.float32) + np.float32(0)
+    uv = UV[idx].reshape(-1, 6).astype(np.float32)
+    kinds, kd = [str(k) for k in z["material_kinds"]], z["material_kd"]
+    rough = {"Floor": .15, "TableWood": .05, "Paneling": .2}   # scene.pbrt:13,14,18 ("remaproughness" false in the file)
+    mats = np.zeros((len(kinds), 8), np.float32)
+    for i, (k, name) in enumerate(zip(kinds, [str(n) for n in z["material_names"]])):
+        c = kd[i] if kd[i][0] >= 0 else np.array([.5, .5, .5], np.float32)
+        if k == "substrate":
+            mats[i] = [1, c[0], c[1], c[2], .04, .04, .04, rough[name]]
+        elif k == "matte":
+            mats[i] = [0, c[0], c[1], c[2], 0, 0, 0, 0]
+        else:
+            mats[i] = [0, .5, .5, .5, 0, 0, 0, 0]
+    # TransformBegin Transform [-1 0 8.74228e-008 0  -8.74228e-008 0 -1 0  0 1 0 0  0 0 0 1] LightSource "infinite"
+    # (scene.pbrt:163-166; column-major in the file) -> row-major LightToWorld rotation
+    l2w = np.array([-1, 0, 8.74228e-008, 0, -8.74228e-008, 0, -1, 0, 0, 1, 0, 0, 0, 0, 0, 1], np.float64).reshape(4, 4).T[:3, :3]
+    return dict(name="living-room", tri_verts=tv, tri_uvs=uv, camera=matrix_camera(z["world_to_camera"], 58.715508, xres, yres),
+                materials=mats, prim_material=z["tri_material"].astype(np.uint8), material_names=[str(n) for n in z["material_names"]],
+                material_kinds=kinds, infinite_light=dict(L=np.array([1, 1, 1], np.float32), light_to_world=l2w),
+                maxdepth=65, spp=64)
+
+
 # ---- procedural stand-ins --------------------------------------------------------------------
 def sponza_standin(seed=7, detail=0.885, xres=700, yres=700):
     """Procedural atrium standing in for Crytek Sponza (geometry absent from the reference tree).

@@ -17,7 +17,7 @@ class RenderDesc(C.Structure):
                 ("world", C.c_uint32), ("seed", C.c_uint32), ("max_batch", C.c_uint32),
                 ("light_kind", C.c_uint32), ("light_radius", C.c_float), ("light_prim", C.c_uint32),
                 ("materials", C.c_void_p), ("n_materials", C.c_uint32), ("prim_material", C.c_void_p),
-                ("crop", C.c_uint32 * 4)]
+                ("crop", C.c_uint32 * 4), ("light_to_world", C.c_float * 9)]
 
 
 class RenderStats(C.Structure):
@@ -51,14 +51,16 @@ class WavefrontPathIntegrator:
 
     def __init__(self, camera, spp=8, maxdepth=5, light_pos=(0, 0, 0), light_I=(1, 1, 1), kd=(.5, .5, .5),
                  rank=0, world=1, seed=0, tile_size=16, max_batch=0, sphere_light=None, materials=None,
-                 prim_material=None, distant_light=None, crop=None):
+                 prim_material=None, distant_light=None, crop=None, infinite_light=None):
         """sphere_light=(radius, prim): `AreaLightSource "area" "color L" light_I` on the full sphere primitive number
         `prim` of the aggregate, centred at light_pos (sampled with MIS like EstimateDirect).  materials: (n, 8) rows
         (kind, Kd.rgb, Ks.rgb, roughness) + prim_material: (n_prims,) uint8 index per primitive.
         distant_light=(from - to, world_radius): `LightSource "distant"` with radiance light_I (lights/distant.cpp);
         world_radius = the aggregate's bounding-sphere radius (see world_radius()).
         crop=(x0, x1, y0, y1): Film "cropwindow" in pixels (scenes.killeroo_feet()["crop"]); the film then holds
-        (y1-y0, x1-x0) pixels, as the reference's Film does."""
+        (y1-y0, x1-x0) pixels, as the reference's Film does.
+        infinite_light=(light_to_world 3x3 or None, world_radius): `LightSource "infinite"` with the constant radiance
+        light_I (lights/infinite.cpp without a readable "mapname"), sampled with MIS."""
         d = RenderDesc()
         for k in ("eye", "dir", "right", "up"):
             setattr(d.camera, k, (C.c_float * 3)(*[float(x) for x in camera[k]]))
@@ -77,6 +79,10 @@ class WavefrontPathIntegrator:
             w = w / np.sqrt((w * w).sum(dtype=np.float32))
             d.light_kind, d.light_radius = 2, float(distant_light[1])
             d.light_pos = (C.c_float * 3)(*[float(x) for x in w])
+        if infinite_light is not None:
+            m = np.eye(3) if infinite_light[0] is None else np.asarray(infinite_light[0], np.float64)[:3, :3]
+            d.light_kind, d.light_radius = 3, float(infinite_light[1])
+            d.light_to_world = (C.c_float * 9)(*[float(x) for x in m.ravel()])
         if materials is not None:
             self._mats = np.ascontiguousarray(materials, np.float32).reshape(-1, 8)
             self._pm = np.ascontiguousarray(prim_material, np.uint8)

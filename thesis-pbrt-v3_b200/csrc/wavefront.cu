@@ -49,6 +49,7 @@ struct WfParams {
     uint32_t max_depth, seed;
     uint32_t light_kind, light_prim;
     float light_radius;
+    float l2w[9];             // B200RT_LIGHT_INFINITE: rotation of LightToWorld, row-major
     const float4 *mats;       // 2 x float4 per material: (kind, Kd.rgb) (Ks.rgb, roughness); nullptr = one matte kd
     const uint8_t *primMat;   // material index per primitive
 };
@@ -221,6 +222,51 @@ __device__ void shade_general(const WfParams &P, const WfMat &m, uint32_t depth,
                 o.wantMis = true;
             }
         }
+    } else if (P.light_kind == B200RT_LIGHT_INFINITE) {
+        // InfiniteAreaLight with a 1x1 (constant) map: Distribution2D::SampleContinuous(u) = u with mapPdf 1
+        // (sampling.h:95-137), so Sample_Li (infinite.cpp:104-131) is theta = u[1] pi, phi = u[0] 2 pi,
+        // wi = LightToWorld(sin t cos p, sin t sin p, cos t), pdf = 1 / (2 pi^2 sin t); Li = L.
+        {
+            const float theta = rnd(P.seed, pix, s, 1001 + 4 * depth) * kPi, phi = rnd(P.seed, pix, s, 1000 + 4 * depth) * 2.f * kPi;
+            const float cosT = cosf(theta), sinT = sinf(theta);
+            if (sinT != 0.f) {
+                const float lightPdf = 1.f / (2.f * kPi * kPi * sinT);
+                const float lx = sinT * cosf(phi), ly = sinT * sinf(phi), lz = cosT;
+                const float3 wi = make_float3(P.l2w[0] * lx + P.l2w[1] * ly + P.l2w[2] * lz, P.l2w[3] * lx + P.l2w[4] * ly + P.l2w[5] * lz,
+                                              P.l2w[6] * lx + P.l2w[7] * ly + P.l2w[8] * lz);
+                const float3 wiL = to_local(fr, wi);
+                float3 f; float scatPdf;
+                bsdf_eval(m, woL, wiL, f, scatPdf);
+                const float c = fabsf(wiL.z);
+                if (lightPdf > 0.f && (f.x * c > 0.f || f.y * c > 0.f || f.z * c > 0.f)) {
+                    const float g = c * ((lightPdf * lightPdf) / (lightPdf * lightPdf + scatPdf * scatPdf)) / lightPdf;
+                    o.contrib = make_float3(bt.x * f.x * P.light_I[0] * g, bt.y * f.y * P.light_I[1] * g, bt.z * f.z * P.light_I[2] * g);
+                    if (o.contrib.x > 0.f || o.contrib.y > 0.f || o.contrib.z > 0.f) {
+                        const float r2x = 2.f * P.light_radius;   // vis = (ref, ref.p + wi * (2 * worldRadius)) (infinite.cpp:127-128)
+                        const float3 pOut = make_float3(p.x + wi.x * r2x, p.y + wi.y * r2x, p.z + wi.z * r2x);
+                        o.so = offset_ray_origin(p, pe, ng, make_float3(pOut.x - p.x, pOut.y - p.y, pOut.z - p.z));
+                        o.sd = make_float3(pOut.x - o.so.x, pOut.y - o.so.y, pOut.z - o.so.z);
+                        o.wantShadow = true;
+                    }
+                }
+            }
+        }
+        // the BSDF-sampled ray (integrator.cpp:176-212): lightPdf = Pdf_Li(wi) (infinite.cpp:133-142); it carries Le when it escapes
+        float3 wiL, f; float scatPdf;
+        if (bsdf_sample(m, woL, rnd(P.seed, pix, s, 1002 + 4 * depth), rnd(P.seed, pix, s, 1003 + 4 * depth), wiL, f, scatPdf)) {
+            const float3 wiW = to_world(fr, wiL);
+            const float lz = P.l2w[2] * wiW.x + P.l2w[5] * wiW.y + P.l2w[8] * wiW.z;   // WorldToLight = transpose
+            const float sinT = sinf(acosf(fminf(fmaxf(lz, -1.f), 1.f)));              // SphericalTheta (geometry.h)
+            if (sinT != 0.f) {
+                const float lightPdf = 1.f / (2.f * kPi * kPi * sinT);
+                const float c = fabsf(wiL.z);
+                const float g = c * ((scatPdf * scatPdf) / (scatPdf * scatPdf + lightPdf * lightPdf)) / scatPdf;
+                o.mcontrib = make_float3(bt.x * f.x * P.light_I[0] * g, bt.y * f.y * P.light_I[1] * g, bt.z * f.z * P.light_I[2] * g);
+                o.md = wiW;
+                o.mo = offset_ray_origin(p, pe, ng, o.md);
+                o.wantMis = true;
+            }
+        }
     } else if (P.light_kind == B200RT_LIGHT_DISTANT) {   // DistantLight::Sample_Li (lights/distant.cpp:49-59)
         const float3 wiL = to_local(fr, make_float3(P.light_pos[0], P.light_pos[1], P.light_pos[2]));
         float3 f; float scatPdf;
@@ -283,11 +329,21 @@ __global__ void k_shade(const __grid_constant__ WfParams P, uint32_t depth, uint
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     const uint32_t n = *nCur;
     const bool area = FULL && P.light_kind == B200RT_LIGHT_SPHERE;
+    const bool infinite = FULL && P.light_kind == B200RT_LIGHT_INFINITE;
     bool wantShadow = false, wantNext = false, wantMis = false;
     float3 so = make_float3(0, 0, 0), sd = so, no = so, nd = so, contrib = so, mo = so, md = so, mcontrib = so;
     uint32_t path = 0;
     if (i < n) {
         const b200rt_hit h = hits[i];
+        if (infinite && depth == 0 && h.prim == B200RT_MISS) {
+            // a camera ray that escapes sees the environment: L += beta * light->Le(ray) (path.cpp:97-107, bounces == 0;
+            // infinite.cpp:95-101 with the constant map).  Later escapes are accounted for by the MIS ray.
+            const uint32_t pth = qPath[i];
+            const float4 bt = beta[pth];
+            float4 l = L[pth];
+            l.x += bt.x * P.light_I[0]; l.y += bt.y * P.light_I[1]; l.z += bt.z * P.light_I[2];
+            L[pth] = l;
+        }
         if (h.prim != B200RT_MISS && depth < P.max_depth) {  // path.cpp:110
             path = qPath[i];
             const float4 rd = rays[2 * (size_t)i + 1];
@@ -332,7 +388,7 @@ __global__ void k_shade(const __grid_constant__ WfParams P, uint32_t depth, uint
                 const float side = (ng.x * wo.x + ng.y * wo.y + ng.z * wo.z) < 0.f ? -1.f : 1.f;
                 const float3 nf = make_float3(side * ng.x, side * ng.y, side * ng.z);  // wo's hemisphere
                 const float4 bt = beta[path];
-                if (FULL && gm.glossy) {   // Material "plastic": the general two-lobe BSDF
+                if (FULL && (gm.glossy || infinite)) {   // Material "plastic" / the infinite light: the general BSDF + light code
                     gm.kd[0] = kdr; gm.kd[1] = kdg; gm.kd[2] = kdb;
                     gm.diffuse = kdr > 0.f || kdg > 0.f || kdb > 0.f;
                     uint32_t gx, gy, gs;
@@ -514,7 +570,7 @@ __global__ void k_shade(const __grid_constant__ WfParams P, uint32_t depth, uint
         nextRays[2 * (size_t)nj + 1] = make_float4(nd.x, nd.y, nd.z, 0.f);
         nextPath[nj] = path;
     }
-    if (area) {  // warp-uniform
+    if (area || infinite) {  // warp-uniform
         const uint32_t mj = warp_append(wantMis, nMis);
         if (wantMis) {
             misRays[2 * (size_t)mj] = make_float4(mo.x, mo.y, mo.z, __int_as_float(0x7f800000));
@@ -707,10 +763,18 @@ static int render_impl(b200rt_scene *s, const b200rt_render_desc *d, float *film
     P.cam = d->camera;
     std::memcpy(P.light_pos, d->light_pos, 12); std::memcpy(P.light_I, d->light_I, 12); std::memcpy(P.kd, d->kd, 12);
     P.max_depth = d->max_depth; P.seed = d->seed;
-    if (d->max_depth > 64) return set_error(B200RT_EINVAL, "max_depth %u too large", d->max_depth);
+    if (d->max_depth > 68) return set_error(B200RT_EINVAL, "max_depth %u too large", d->max_depth);
     P.light_kind = d->light_kind; P.light_prim = d->light_prim; P.light_radius = d->light_radius;
     const bool area = d->light_kind == B200RT_LIGHT_SPHERE;
-    if (d->light_kind > B200RT_LIGHT_DISTANT) return set_error(B200RT_EINVAL, "unknown light_kind %u", d->light_kind);
+    const bool infinite = d->light_kind == B200RT_LIGHT_INFINITE;
+    const bool mis = area || infinite;   // lights with area: EstimateDirect traces a BSDF-sampled ray too
+    if (infinite) {
+        bool zero = true;
+        for (int k = 0; k < 9; ++k) zero = zero && d->light_to_world[k] == 0.f;
+        for (int k = 0; k < 9; ++k) P.l2w[k] = zero ? (k % 4 == 0 ? 1.f : 0.f) : d->light_to_world[k];
+        if (!(d->light_radius > 0.f)) return set_error(B200RT_EINVAL, "infinite light: light_radius must be the scene's bounding-sphere radius");
+    }
+    if (d->light_kind > B200RT_LIGHT_INFINITE) return set_error(B200RT_EINVAL, "unknown light_kind %u", d->light_kind);
     const bool distant = d->light_kind == B200RT_LIGHT_DISTANT;
     if (distant) {
         const float l2 = d->light_pos[0] * d->light_pos[0] + d->light_pos[1] * d->light_pos[1] + d->light_pos[2] * d->light_pos[2];
@@ -739,10 +803,10 @@ static int render_impl(b200rt_scene *s, const b200rt_render_desc *d, float *film
         WCU(cudaMalloc(&w->shRays, cap * 32)); WCU(cudaMalloc(&w->shContrib, cap * 16)); WCU(cudaMalloc(&w->shPath, cap * 4));
         WCU(cudaMalloc(&w->beta, cap * 16)); WCU(cudaMalloc(&w->L, cap * 16));
         WCU(cudaMalloc(&w->hits, cap * sizeof(b200rt_hit))); WCU(cudaMalloc(&w->occ, cap));
-        WCU(cudaMalloc(&w->counts, 4 * 3 * 66));
+        WCU(cudaMalloc(&w->counts, 4 * 3 * 72));
         w->cap = cap;
     }
-    if (area && !w->misRays) {
+    if (mis && !w->misRays) {
         WCU(cudaMalloc(&w->misRays, w->cap * 32)); WCU(cudaMalloc(&w->misContrib, w->cap * 16)); WCU(cudaMalloc(&w->misPath, w->cap * 4));
     }
     if (d->materials) {
@@ -826,7 +890,7 @@ static int render_impl(b200rt_scene *s, const b200rt_render_desc *d, float *film
                 g_launches.fetch_add(1);
             }
             if (depth == d->max_depth) break;  // path.cpp:110: the last intersection is found, then the path ends
-            (area || distant || P.mats ? k_shade<true> : k_shade<false>)<<<gridSlots, TB, 0, st>>>(P, depth, start, w->counts + 2 * depth, w->rays[cur], w->qPath[cur], w->hits,
+            (mis || distant || P.mats ? k_shade<true> : k_shade<false>)<<<gridSlots, TB, 0, st>>>(P, depth, start, w->counts + 2 * depth, w->rays[cur], w->qPath[cur], w->hits,
                                               s->d_prim_tris, w->beta, w->rays[cur ^ 1], w->qPath[cur ^ 1],
                                               w->counts + 2 * (depth + 1), w->shRays, w->shPath, w->shContrib,
                                               w->counts + 2 * depth + 1, w->L, w->misRays, w->misPath, w->misContrib,
@@ -844,7 +908,7 @@ static int render_impl(b200rt_scene *s, const b200rt_render_desc *d, float *film
             }
             k_shadow_resolve<<<gridSlots, TB, 0, st>>>(w->counts + 2 * depth + 1, w->occ, w->shPath, w->shContrib, w->L);
             g_launches.fetch_add(1);
-            if (area) {  // EstimateDirect's BSDF-sampled ray: one more closest-hit queue per bounce (w->hits is free again)
+            if (mis) {  // EstimateDirect's BSDF-sampled ray: one more closest-hit queue per bounce (w->hits is free again)
                 a = ev();
                 rc = launch_trace(s, w->misRays, nSlots, w->counts + misBase + depth, w->hits, nullptr, false,
                                   heat ? s->d_counters : nullptr, st, heat ? w->perRay : nullptr);
@@ -854,7 +918,7 @@ static int render_impl(b200rt_scene *s, const b200rt_render_desc *d, float *film
                     k_heat<<<gridSlots, TB, 0, st>>>(P, start, w->counts + misBase + depth, w->misPath, w->perRay, d_heat, 0u);
                     g_launches.fetch_add(1);
                 }
-                k_mis_resolve<<<gridSlots, TB, 0, st>>>(w->counts + misBase + depth, w->hits, d->light_prim, w->misPath, w->misContrib, w->L);
+                k_mis_resolve<<<gridSlots, TB, 0, st>>>(w->counts + misBase + depth, w->hits, infinite ? (uint32_t)B200RT_MISS : d->light_prim, w->misPath, w->misContrib, w->L);
                 g_launches.fetch_add(1);
             }
             cur ^= 1;
@@ -868,7 +932,7 @@ static int render_impl(b200rt_scene *s, const b200rt_render_desc *d, float *film
         for (uint32_t depth = 0; depth <= d->max_depth; ++depth) {
             nClosest += hostCounts[2 * depth];
             if (depth < d->max_depth) nShadow += hostCounts[2 * depth + 1];
-            if (area && depth < d->max_depth) { nClosest += hostCounts[misBase + depth]; nMis += hostCounts[misBase + depth]; }
+            if (mis && depth < d->max_depth) { nClosest += hostCounts[misBase + depth]; nMis += hostCounts[misBase + depth]; }
             if (w->keep) {
                 w->keptCount[2 * depth] = hostCounts[2 * depth];
                 if (depth < d->max_depth) w->keptCount[2 * depth + 1] = hostCounts[2 * depth + 1];
