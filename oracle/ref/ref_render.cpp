@@ -121,6 +121,15 @@ extern "C" void ref_render_set_camera_matrix(const float *w2c16) {
     if (w2c16) std::memcpy(g_w2c, w2c16, sizeof(g_w2c));
 }
 
+extern "C" int ref_render_get_infinite(float *L_rgb, float *l2w16) {   // for tests/hostplugin's driver (same scene)
+    if (g_infinite) { std::memcpy(L_rgb, g_infL, sizeof(g_infL)); std::memcpy(l2w16, g_infM, sizeof(g_infM)); }
+    return g_infinite ? 1 : 0;
+}
+extern "C" int ref_render_get_camera_matrix(float *w2c16) {
+    if (g_camMatrix) std::memcpy(w2c16, g_w2c, sizeof(g_w2c));
+    return g_camMatrix ? 1 : 0;
+}
+
 // Film "float cropwindow" [x0 x1 y0 y1] for the NEXT renders (NULL = whole frame); out_rgb / out_heat then hold the
 // window's pixels only (Film::croppedPixelBounds, film.cpp:49-57).
 static float g_crop[4] = {0.f, 1.f, 0.f, 1.f};

@@ -104,11 +104,16 @@ extern "C" int plugin_intersect_p_batch(const ref_accel *a, const float *rays, u
 #include "materials/plastic.h"
 #include "lights/diffuse.h"
 #include "lights/distant.h"
+#include "core/sampling.h"
+#include "core/parallel.h"
+#include "lights/infinite.h"
 #include "samplers/random.h"
 #include "textures/constant.h"
 #include "b200integrator.h"
 extern "C" int ref_last_image(float *out_rgb, int *xres, int *yres);
 extern "C" int ref_render_get_distant(float *from_to);
+extern "C" int ref_render_get_infinite(float *L_rgb, float *l2w16);      // set through ref_render_set_infinite
+extern "C" int ref_render_get_camera_matrix(float *w2c16);             // set through ref_render_set_camera_matrix
 extern "C" void ref_render_get_crop(float *cw);           // set through ref_render_set_crop   // set through ref_render_set_distant (oracle/ref/ref_render.cpp)
 std::shared_ptr<pbrt::Shape> shape_of(const pbrt::Primitive *p);   // plugin_shape_of.cpp (GeometricPrimitive::shape is private)
 
@@ -168,8 +173,16 @@ extern "C" int plugin_render(ref_scene *s, const char *tree, const float *cam, i
     Transform l2w = Translate(Vector3f(light_pos[0], light_pos[1], light_pos[2]));
     std::vector<std::shared_ptr<Light>> lights;
     float ft[6];
+    float infL[3], m16[16];
     if (area) lights.push_back(area);
-    else if (ref_render_get_distant(ft))
+    else if (ref_render_get_infinite(infL, m16)) {   // LightSource "infinite" with the constant map (no readable "mapname")
+        Float lrgb[3] = {infL[0], infL[1], infL[2]};
+        ParallelInit();   // InfiniteAreaLight's constructor runs a ParallelFor (pbrtInit starts the pool before any object is made)
+        lights.push_back(std::make_shared<InfiniteAreaLight>(
+            Transform(Matrix4x4(m16[0], m16[1], m16[2], m16[3], m16[4], m16[5], m16[6], m16[7], m16[8], m16[9], m16[10], m16[11],
+                                m16[12], m16[13], m16[14], m16[15])), Spectrum::FromRGB(lrgb), 1, std::string("")));
+        ParallelCleanup();
+    } else if (ref_render_get_distant(ft))
         lights.push_back(std::make_shared<DistantLight>(Transform(), Spectrum::FromRGB(li),
                                                         Point3f(ft[0], ft[1], ft[2]) - Point3f(ft[3], ft[4], ft[5])));
     else lights.push_back(std::make_shared<PointLight>(l2w, mi, Spectrum::FromRGB(li)));
@@ -180,7 +193,11 @@ extern "C" int plugin_render(ref_scene *s, const char *tree, const float *cam, i
     Film *film = new Film(Point2i(xres, yres), Bounds2f(Point2f(cw[0], cw[2]), Point2f(cw[1], cw[3])), std::move(filter), 35.f,
                           std::string(tmp_prefix) + ".exr", 1.f);
     const Vector2i cres = film->croppedPixelBounds.Diagonal();
-    Transform c2w = Inverse(LookAt(Point3f(cam[0], cam[1], cam[2]), Point3f(cam[3], cam[4], cam[5]), Vector3f(cam[6], cam[7], cam[8])));
+    Transform w2c = LookAt(Point3f(cam[0], cam[1], cam[2]), Point3f(cam[3], cam[4], cam[5]), Vector3f(cam[6], cam[7], cam[8]));
+    if (ref_render_get_camera_matrix(m16))   // `Transform [...]` before `Camera` (scenes/living-room/scene.pbrt:2)
+        w2c = Transform(Matrix4x4(m16[0], m16[1], m16[2], m16[3], m16[4], m16[5], m16[6], m16[7], m16[8], m16[9], m16[10], m16[11],
+                                  m16[12], m16[13], m16[14], m16[15]));
+    Transform c2w = Inverse(w2c);
     AnimatedTransform ac2w(&c2w, 0.f, &c2w, 1.f);
     Float frame = Float(xres) / Float(yres);
     Bounds2f screen;

@@ -242,6 +242,63 @@ def test_cpp_wavefront_integrator_matches_the_references_render(host, gpu, case)
 
 
 @pytest.mark.gpu
+def test_cpp_integrator_renders_living_room(host, gpu):
+    """BASELINE config 5 through the C++ drop-in: scenes/living-room's geometry and camera (`Transform [...]` CTM), path
+    maxdepth 65, `LightSource "infinite"` with the constant map the reference falls back to (read by the integrator
+    through Light::Sample_Li / Le only), substituted materials — against the reference's own render of the same setup
+    (tests/golden/ref_living_room.npz) and against the Python mirror with the same seed."""
+    from conftest import load_golden
+    from b200rt import scenes, wavefront as wf
+    from b200rt.wavefront import film_to_rgb
+    rb, L = host
+    L.plugin_render.argtypes = [C.c_void_p, C.c_char_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
+                                C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_char_p, C.c_void_p, C.POINTER(C.c_uint64),
+                                C.POINTER(C.c_uint64), C.c_void_p, C.c_void_p]
+    g = load_golden("ref_living_room.npz")
+    xres, yres, spp, maxdepth = (int(x) for x in g["render_params"])
+    sc = scenes.living_room(xres, yres)
+    tv, il = sc["tri_verts"], sc["infinite_light"]
+    S = rb.RefScene(tv.reshape(-1, 3), np.arange(3 * len(tv), dtype=np.int32).reshape(-1, 3), L=L)
+    l2w = np.eye(4, dtype=np.float32)
+    l2w[:3, :3] = il["light_to_world"]
+    w2c = np.ascontiguousarray(sc["camera"]["world_to_camera"], np.float32)
+    Lrgb = np.ascontiguousarray(il["L"], np.float32)
+    L.ref_render_set_infinite.argtypes = [C.c_void_p, C.c_void_p]
+    L.ref_render_set_camera_matrix.argtypes = [C.c_void_p]
+    L.ref_render_set_infinite(Lrgb.ctypes.data, l2w.ctypes.data)
+    L.ref_render_set_camera_matrix(w2c.ctypes.data)
+    cam = np.array([0, 0, 0, 0, 0, 1, 0, 1, 0, 58.715508], np.float32)
+    prim_mat = np.ascontiguousarray(sc["materials"][sc["prim_material"]])
+    zero, kd = np.zeros(3, np.float32), np.full(3, .5, np.float32)
+    out = np.zeros((yres, xres, 3), np.float32)
+    nc, ns = C.c_uint64(), C.c_uint64()
+    import tempfile
+    with tempfile.TemporaryDirectory() as td:
+        rc = L.plugin_render(S.h, b"bvh", cam.ctypes.data, xres, yres, spp, maxdepth, zero.ctypes.data, Lrgb.ctypes.data,
+                             kd.ctypes.data, 9, 0, 1, os.path.join(td, "img").encode(), out.ctypes.data, C.byref(nc), C.byref(ns),
+                             prim_mat.ctypes.data, None)
+    L.ref_render_set_infinite(None, None)
+    L.ref_render_set_camera_matrix(None)
+    assert rc == 0
+    img, ref = out.astype(np.float64), g["render_rgb"].astype(np.float64)
+    rnc, rns = (int(x) for x in g["render_rays"])
+    assert abs(nc.value / rnc - 1) < 0.015 and abs(ns.value / rns - 1) < 0.015
+    assert abs(img.mean() / ref.mean() - 1) < 0.015
+
+    def blocks(a, k=4):
+        return a[:yres // k * k, :xres // k * k].reshape(yres // k, k, xres // k, k, 3).mean((1, 3))
+    assert np.sqrt(((blocks(img) - blocks(ref)) ** 2).mean()) / ref.mean() < 0.07
+    acc = gpu.MakeAccelerator("bvh", tv)
+    integ = gpu.WavefrontPathIntegrator(sc["camera"], spp=spp, maxdepth=maxdepth, light_I=il["L"], seed=9,
+                                        infinite_light=(il["light_to_world"], wf.world_radius(tv)),
+                                        materials=sc["materials"], prim_material=sc["prim_material"])
+    film, st = integ.Render(acc)
+    py = film_to_rgb(film).astype(np.float64)
+    assert np.sqrt(((blocks(img) - blocks(py)) ** 2).mean()) / ref.mean() < 0.02
+    assert abs(st["closest_rays"] / nc.value - 1) < 2e-3
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("tree", ["bvh", "kdtree"])
 def test_cpp_integrator_writes_the_thesis_statistic_matrices(host, gpu, tree):
     """`Integrator "b200wavefront" "bool generalstats" "true"`: the per-pixel GeneralStats the thesis accumulates

@@ -183,8 +183,35 @@ void B200WavefrontIntegrator::Render(const Scene &scene) {
         d.light_prim = (uint32_t)lp;
         d.light_pos[0] = c.x; d.light_pos[1] = c.y; d.light_pos[2] = c.z;
         for (int i = 0; i < 3; ++i) d.light_I[i] = le[i];
+    } else if (light->flags & (int)LightFlags::Infinite) {
+        // LightSource "infinite" (lights/infinite.cpp) with a CONSTANT map — what the reference builds when "mapname" is
+        // absent or unreadable (scenes/living-room's sky map is not in the tree).  Read through the public interface:
+        // with the 1x1 map Sample_Li(u) is (theta, phi) = (u[1] pi, u[0] 2 pi) -> LightToWorld's columns, pdf 1/(2 pi^2 sin theta).
+        Point3f c; Float wr;
+        scene.WorldBound().BoundingSphere(&c, &wr);
+        Interaction ref(c, Normal3f(), Vector3f(), Vector3f(0, 0, 1), 0.f, MediumInterface());
+        Vector3f col[3]; Float pdf; VisibilityTester vis;
+        const Point2f us[3] = {Point2f(0.f, 0.5f), Point2f(0.25f, 0.5f), Point2f(0.f, 0.f)};
+        Float le[3];
+        for (int k = 0; k < 3; ++k) {
+            const Spectrum Li = light->Sample_Li(ref, us[k], &col[k], &pdf, &vis);
+            if (k == 0) Li.ToRGB(le);
+            if (k < 2 && std::abs(pdf * 2 * Pi * Pi - 1) > 1e-4f) { Error("b200wavefront: only a constant infinite light (no usable \"mapname\") is supported"); return; }
+        }
+        for (int k = 0; k < 26; ++k) {   // Le must not depend on the direction
+            const Vector3f w = Normalize(Vector3f(Float(k % 3) - 1, Float(k / 3 % 3) - 1, Float(k / 9) - 1 + 0.01f));
+            Float q[3];
+            light->Le(RayDifferential(Ray(c, w))).ToRGB(q);
+            for (int i = 0; i < 3; ++i)
+                if (std::abs(q[i] - le[i]) > 1e-5f * (1 + std::abs(le[i]))) { Error("b200wavefront: only a constant infinite light is supported"); return; }
+        }
+        d.light_kind = B200RT_LIGHT_INFINITE;
+        d.light_radius = wr;
+        for (int r = 0; r < 3; ++r)
+            for (int k = 0; k < 3; ++k) d.light_to_world[3 * r + k] = col[k][r];
+        for (int i = 0; i < 3; ++i) d.light_I[i] = le[i];
     } else {
-        Error("b200wavefront: only a point light, a distant light or a sphere area light is supported");
+        Error("b200wavefront: only a point light, a distant light, a sphere area light or a constant infinite light is supported");
         return;
     }
     // materials: Material "matte" (constant Kd, sigma 0; measured through the public BSDF) and Material "plastic"
