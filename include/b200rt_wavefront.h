@@ -10,9 +10,11 @@
  * queue, bounce closest-hit queue) -> ... up to maxdepth, with warp-ballot queue compaction.
  *
  * Shading subset (what the config scenes' templates need around the traversal): perspective camera
- * (src/cameras/perspective.cpp), one point light (src/lights/point.cpp) OR one sphere area light with multiple
- * importance sampling (src/lights/diffuse.cpp, Sphere::Sample/Pdf, EstimateDirect's two strategies), Lambertian "matte"
- * materials with one Kd per primitive (src/materials/matte.cpp), box pixel filter, Russian roulette of path.cpp:190-199.  Samples come
+ * (src/cameras/perspective.cpp), one point light (src/lights/point.cpp), one distant light (src/lights/distant.cpp), one
+ * sphere area light (src/lights/diffuse.cpp, Sphere::Sample/Pdf) OR one constant infinite light (src/lights/infinite.cpp
+ * with the 1x1 map) — the last two with multiple importance sampling (EstimateDirect's two strategies) —, "matte" and
+ * "plastic" materials per primitive (src/materials/matte.cpp, plastic.cpp), box pixel filter, Russian roulette of
+ * path.cpp:190-199, path depths up to 68 (scenes/living-room uses 65).  Samples come
  * from a counter-based hash of (pixel, sample, dimension), so the image does not depend on the
  * execution order, the batch size or the number of GPUs.
  *

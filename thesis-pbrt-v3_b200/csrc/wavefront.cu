@@ -922,6 +922,14 @@ static int render_impl(b200rt_scene *s, const b200rt_render_desc *d, float *film
                 g_launches.fetch_add(1);
             }
             cur ^= 1;
+            // deep paths (scenes/living-room: maxdepth 65): Russian roulette empties the queues long before maxdepth, so
+            // look at the next queue's size every 4th depth and stop launching once no path is left
+            if (depth >= 7 && (depth & 3) == 3 && depth + 1 < d->max_depth) {
+                uint32_t left = 0;
+                WCU(cudaMemcpyAsync(&left, w->counts + 2 * (depth + 1), 4, cudaMemcpyDeviceToHost, st));
+                WCU(cudaStreamSynchronize(st));
+                if (left == 0) break;
+            }
         }
         const uint32_t nPix = nSlots / P.tl.spp;
         k_film<<<(nPix + TB - 1) / TB, TB, 0, st>>>(P, start, nPix, w->L, d_film);
