@@ -21,7 +21,7 @@
 extern "C" {
 #endif
 
-#define B200RT_VERSION 6
+#define B200RT_VERSION 7
 
 enum {
     B200RT_OK = 0,

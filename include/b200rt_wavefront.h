@@ -13,7 +13,7 @@
  * (src/cameras/perspective.cpp), one point light (src/lights/point.cpp), one distant light (src/lights/distant.cpp), one
  * sphere area light (src/lights/diffuse.cpp, Sphere::Sample/Pdf) OR one constant infinite light (src/lights/infinite.cpp
  * with the 1x1 map) — the last two with multiple importance sampling (EstimateDirect's two strategies) —, "matte" and
- * "plastic" materials per primitive (src/materials/matte.cpp, plastic.cpp), box pixel filter, Russian roulette of
+ * "plastic", "mirror" and smooth "glass" materials per primitive (src/materials/matte.cpp, plastic.cpp, mirror.cpp, glass.cpp), box pixel filter, Russian roulette of
  * path.cpp:190-199, path depths up to 68 (scenes/living-room uses 65).  Samples come
  * from a counter-based hash of (pixel, sample, dimension), so the image does not depend on the
  * execution order, the batch size or the number of GPUs.
@@ -61,7 +61,7 @@ typedef struct {
                               at p + wLight * 2 * radius.  A delta light: no MIS rays. */
     uint32_t light_prim;   /* primitive number of that sphere inside the aggregate (scene-desc prim_kind == 1) */
     /* Materials: NULL = Material "matte" "Kd" = kd for all.  Else n_materials records of 8 floats
-     * (kind, Kd.r, Kd.g, Kd.b, Ks.r, Ks.g, Ks.b, roughness), kind B200RT_MAT_MATTE (materials/matte.cpp, sigma 0) or B200RT_MAT_PLASTIC (materials/plastic.cpp),
+     * (kind, Kd.r, Kd.g, Kd.b, Ks.r, Ks.g, Ks.b, roughness), kind B200RT_MAT_MATTE (materials/matte.cpp, sigma 0), B200RT_MAT_PLASTIC (materials/plastic.cpp), B200RT_MAT_MIRROR or B200RT_MAT_GLASS (records below),
      * and one material index per primitive.  HOST pointers, read during the call. */
     const float *materials;
     uint32_t n_materials;
@@ -83,7 +83,16 @@ typedef struct {
                               rays that escape add Le (path.cpp:97-107).  All zero = identity. */
 } b200rt_render_desc;
 enum { B200RT_LIGHT_POINT = 0, B200RT_LIGHT_SPHERE = 1, B200RT_LIGHT_DISTANT = 2, B200RT_LIGHT_INFINITE = 3 };
-enum { B200RT_MAT_MATTE = 0, B200RT_MAT_PLASTIC = 1 /* materials/plastic.cpp: Kd + Ks microfacet lobe, roughness remapped */ };
+enum {
+    B200RT_MAT_MATTE = 0,
+    B200RT_MAT_PLASTIC = 1, /* materials/plastic.cpp: Kd + Ks microfacet lobe, roughness remapped */
+    /* ---- ABI v7: the perfectly specular materials (path.cpp's specularBounce / etaScale bookkeeping comes with them) ---- */
+    B200RT_MAT_MIRROR = 2,  /* materials/mirror.cpp:44-56: SpecularReflection(Kr, FresnelNoOp); record = (kind, Kr.rgb, -, -, -, -) */
+    B200RT_MAT_GLASS = 3,   /* materials/glass.cpp:44-63 with roughness 0 under the path integrator (allowMultipleLobes):
+                               FresnelSpecular(Kr, Kt, 1, index); record = (kind, Kr.rgb, Kt.rgb, index) */
+    B200RT_MAT_REVERSE_ORIENTATION = 16 /* added to `kind`: the shape's reverseOrientation ^ transformSwapsHandedness
+                               (triangle.cpp:421-424) — flips the side of a triangle its normal (= the glass's outside) is on */
+};
 
 typedef struct {
     uint64_t camera_rays;   /* = paths started */

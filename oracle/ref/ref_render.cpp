@@ -29,6 +29,8 @@
 #include "lights/infinite.h"
 #include "materials/matte.h"
 #include "materials/plastic.h"
+#include "materials/mirror.h"
+#include "materials/glass.h"
 #include "samplers/halton.h"
 #include "samplers/random.h"
 #include "textures/constant.h"
@@ -150,7 +152,8 @@ extern "C" int ref_render(ref_scene *s, const char *accel_kind, const float *cam
                           const char *sampler_name, int n_threads, const char *tmp_prefix, float *out_rgb,
                           uint64_t *n_closest, uint64_t *n_shadow, uint32_t *out_heat /* nullable: 6 planes of yres*xres */,
                           const float *prim_mat /* nullable: 8 floats per primitive (kind 0 matte / 1 plastic, Kd rgb, Ks rgb,
-                                                   roughness) instead of the single matte `kd` */,
+                                                   roughness; kind 2 mirror: Kr; kind 3 glass: Kr, Kt, index) instead of the
+                                                   single matte `kd` */,
                           const float *emitter_L /* nullable: rgb; the scene's LAST primitive (a sphere) becomes
                                                     AreaLightSource "area" "color L" and replaces the point light */,
                           double *render_seconds /* nullable: wall time of integrator.Render() alone (no tree build) */) {
@@ -180,6 +183,13 @@ extern "C" int ref_render(ref_scene *s, const char *accel_kind, const float *cam
                     auto texS = std::make_shared<ConstantTexture<Spectrum>>(Spectrum::FromRGB(cs));
                     auto rough = std::make_shared<ConstantTexture<Float>>(k[7]);
                     mm = std::make_shared<PlasticMaterial>(tex, texS, rough, nullptr, true);
+                } else if (k[0] == 2.f) {   // Material "mirror" "color Kr" (materials/mirror.cpp:58-63)
+                    mm = std::make_shared<MirrorMaterial>(tex, nullptr);
+                } else if (k[0] == 3.f) {   // Material "glass" "color Kr" "color Kt" "float index" (materials/glass.cpp:97-110), roughness 0
+                    auto texT = std::make_shared<ConstantTexture<Spectrum>>(Spectrum::FromRGB(cs));
+                    auto zero = std::make_shared<ConstantTexture<Float>>(0.f);
+                    auto index = std::make_shared<ConstantTexture<Float>>(k[7]);
+                    mm = std::make_shared<GlassMaterial>(tex, texT, zero, zero, index, nullptr, true);
                 } else mm = std::make_shared<MatteMaterial>(tex, sigma, nullptr);
                 it = byKd.emplace(k, mm).first;
             }

@@ -102,6 +102,8 @@ extern "C" int plugin_intersect_p_batch(const ref_accel *a, const float *rays, u
 #include "lights/point.h"
 #include "materials/matte.h"
 #include "materials/plastic.h"
+#include "materials/mirror.h"
+#include "materials/glass.h"
 #include "lights/diffuse.h"
 #include "lights/distant.h"
 #include "core/sampling.h"
@@ -149,6 +151,11 @@ extern "C" int plugin_render(ref_scene *s, const char *tree, const float *cam, i
                 if (k[0] == 1.f)
                     mm = std::make_shared<PlasticMaterial>(tex, std::make_shared<ConstantTexture<Spectrum>>(Spectrum::FromRGB(cs)),
                                                            std::make_shared<ConstantTexture<Float>>(k[7]), nullptr, true);
+                else if (k[0] == 2.f) mm = std::make_shared<MirrorMaterial>(tex, nullptr);
+                else if (k[0] == 3.f)
+                    mm = std::make_shared<GlassMaterial>(tex, std::make_shared<ConstantTexture<Spectrum>>(Spectrum::FromRGB(cs)),
+                                                         std::make_shared<ConstantTexture<Float>>(0.f), std::make_shared<ConstantTexture<Float>>(0.f),
+                                                         std::make_shared<ConstantTexture<Float>>(k[7]), nullptr, true);
                 else mm = std::make_shared<MatteMaterial>(tex, sigma, nullptr);
                 it = byRec.emplace(k, mm).first;
             }

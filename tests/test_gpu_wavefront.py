@@ -156,12 +156,15 @@ def test_tile_sharding_is_bit_identical(gpu, small_scene):
     assert np.array_equal(small, full)
 
 
-def test_tile_sharding_area_light_and_materials(gpu):
-    """Same invariants for the full shade stage (sphere area light with MIS rays, matte + plastic materials): the
-    union of the ranks' films and a small-batch render both equal the single-rank film bit for bit."""
+@pytest.mark.parametrize("specular", [False, True])
+def test_tile_sharding_area_light_and_materials(gpu, specular):
+    """Same invariants for the full shade stage (sphere area light with MIS rays, matte + plastic materials — or the glass
+    + mirror killeroos): the union of the ranks' films and a small-batch render both equal the single-rank film bit for bit."""
     from b200rt import scenes
     sc = scenes.killeroo_simple(xres=72, yres=56)
     verts, prim_kind, rows, pm, mats = scenes.with_sphere_light(sc, plastic=True)
+    if specular:
+        mats = scenes.specular_materials(sc)
     acc = gpu.B200Accel(gpu.build_bvh(verts), verts, prim_kind=prim_kind, spheres=rows)
     sl = sc["sphere_light"]
     kw = dict(spp=3, maxdepth=4, light_pos=sl["center"], light_I=sl["L"], seed=2,
@@ -249,7 +252,7 @@ def test_heatmaps_match_the_references_per_pixel_statistics(gpu):
         assert np.sqrt(((ab - bb) ** 2).mean()) / bb.mean() < 0.04, name
 
 
-@pytest.mark.parametrize("case,plastic", [("killeroo_area", False), ("killeroo_full", True)])
+@pytest.mark.parametrize("case,plastic", [("killeroo_area", False), ("killeroo_full", True), ("killeroo_glass", "specular")])
 def test_area_light_mis_matches_the_references_render(gpu, case, plastic):
     """killeroo_full = BASELINE config 1 exactly as scenes/killeroo-simple describes it (sphere area light, matte
     ground, two "plastic" killeroos: Lambertian + Trowbridge-Reitz microfacet lobe with FresnelDielectric(1.5, 1),
@@ -258,14 +261,20 @@ def test_area_light_mis_matches_the_references_render(gpu, case, plastic):
     sampled with multiple importance sampling as EstimateDirect does (light sample -> shadow any-hit ray, BSDF sample
     -> an extra closest-hit MIS ray, emitted radiance for camera rays) and one matte Kd per primitive, against the
     reference's own render of the same setup (tests/golden/ref_render.npz `killeroo_area`).  Statistical bar as above;
-    the closest-ray count now includes the MIS rays."""
+    the closest-ray count now includes the MIS rays.
+    killeroo_glass = the same scene with the first killeroo `Material "glass"` (index 1.5) and the second `Material "mirror"`
+    (scenes.specular_materials), maxdepth 8: the specular path of path.cpp (no direct lighting at a specular vertex,
+    emitted radiance seen after a specular bounce, etaScale in the Russian roulette) with FresnelSpecular /
+    SpecularReflection sampling, against the reference's own render with its GlassMaterial / MirrorMaterial."""
     from conftest import load_golden
     from b200rt import scenes
     from b200rt.wavefront import film_to_rgb
     g = load_golden("ref_render.npz")
     res, spp, maxdepth = (int(x) for x in g[case + "_params"])
     sc = scenes.killeroo_simple(xres=res, yres=res)
-    verts, prim_kind, rows, pm, mats = scenes.with_sphere_light(sc, plastic=plastic)
+    verts, prim_kind, rows, pm, mats = scenes.with_sphere_light(sc, plastic=bool(plastic))
+    if plastic == "specular":
+        mats = scenes.specular_materials(sc)
     acc = gpu.B200Accel(gpu.build_bvh(verts), verts, prim_kind=prim_kind, spheres=rows)
     sl = sc["sphere_light"]
     integ = gpu.WavefrontPathIntegrator(sc["camera"], spp=spp, maxdepth=maxdepth, light_pos=sl["center"], light_I=sl["L"],
@@ -285,10 +294,20 @@ def test_area_light_mis_matches_the_references_render(gpu, case, plastic):
         near = near | np.roll(near, 1, 0) | np.roll(near, -1, 0) | np.roll(near, 1, 1) | np.roll(near, -1, 1)
     assert near.sum() < 200
     a, b = np.where(near[..., None], 0, rgb), np.where(near[..., None], 0, ref)
+    if plastic == "specular":
+        # caustic paths (diffuse -> glass / mirror -> emitter) each carry ~2000 / 256 into one pixel: over six seeds the
+        # raw mean scatters by 1 % (sd) around the reference's 0.1300 (scripts/specular_check.py, profiles/
+        # r01_specular_check.log), the mean of the image clamped at 1 by 0.1 %.  Raw mean within 3 sd; the tight bars
+        # below are taken on the clamped images.
+        assert abs(a.mean() / b.mean() - 1) < 0.03, (a.mean(), b.mean())
+        a, b = np.minimum(a, 1.0), np.minimum(b, 1.0)
     assert abs(a.mean() / b.mean() - 1) < 0.01, (a.mean(), b.mean())
     for ch in range(3):   # per colour channel: the per-primitive Kd's tint the bounce light
         assert abs(a[..., ch].mean() / b[..., ch].mean() - 1) < 0.015
-    assert np.sqrt(((_blocks(a, 8) - _blocks(b, 8)) ** 2).mean()) / b.mean() < 0.04
+    # block noise of the specular case: two seeds of THIS driver differ by 6.5 % +- 0.6 % (the caustics), a seed and the
+    # reference by the same 6.6 %, the 6-seed average by 5.0 % = what two independent 4.6 % noises predict: no bias
+    # visible (profiles/r01_specular_check.log)
+    assert np.sqrt(((_blocks(a, 8) - _blocks(b, 8)) ** 2).mean()) / b.mean() < (0.085 if plastic == "specular" else 0.04)
 
 
 def test_crop_window_is_the_window_of_the_full_frame(gpu, small_scene):
@@ -343,3 +362,19 @@ def test_distant_light_scene_matches_the_references_render(gpu, case):
     a, b = _blocks(rgb, 8), _blocks(ref, 8)
     covered = b.max(-1) > 0
     assert np.sqrt(((a - b) ** 2)[covered].mean()) / b[covered].mean() < 0.04
+
+
+def test_specular_material_records_are_validated(gpu, small_scene):
+    """Unknown material kinds and a glass without its index of refraction are refused at the C ABI (no silent matte)."""
+    sc, acc = small_scene
+    pm = np.zeros(len(sc["tri_verts"]), np.uint8)
+    kw = dict(spp=1, maxdepth=2, light_pos=sc["light"], seed=1, prim_material=pm)
+    for bad in ([5, .5, .5, .5, 0, 0, 0, 0], [3, 1, 1, 1, 1, 1, 1, 0], [2.5, .9, .9, .9, 0, 0, 0, 0], [-1, 0, 0, 0, 0, 0, 0, 0]):
+        with pytest.raises(Exception):
+            gpu.WavefrontPathIntegrator(sc["camera"], materials=np.array([bad], np.float32), **kw).Render(acc)
+    # a mirror everywhere under a point light: no diffuse vertex, so nothing is ever lit and no shadow ray is cast
+    film, st = gpu.WavefrontPathIntegrator(sc["camera"], materials=np.array([[2, .9, .9, .9, 0, 0, 0, 0]], np.float32), **kw).Render(acc)
+    assert st["shadow_rays"] == 0 and film[..., :3].max() == 0 and st["closest_rays"] > st["camera_rays"]
+    # the orientation flag only matters for glass: a mirror reflects the same way from either side
+    flip, st2 = gpu.WavefrontPathIntegrator(sc["camera"], materials=np.array([[2 + 16, .9, .9, .9, 0, 0, 0, 0]], np.float32), **kw).Render(acc)
+    assert st2["closest_rays"] == st["closest_rays"]

@@ -145,7 +145,7 @@ def test_plugin_with_this_repos_builders(host, gpu, tree):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("case", ["killeroo", "killeroo_full", "feet", "feet_crop"])
+@pytest.mark.parametrize("case", ["killeroo", "killeroo_full", "killeroo_glass", "feet", "feet_crop"])
 def test_cpp_wavefront_integrator_matches_the_references_render(host, gpu, case):
     """`Integrator "b200wavefront"` (host/b200integrator.cpp) over `Accelerator "b200"`, set up exactly like the
     reference's own render of tests/golden/ref_render.npz (PerspectiveCamera from LookAt/fov, Film + BoxFilter,
@@ -164,7 +164,8 @@ def test_cpp_wavefront_integrator_matches_the_references_render(host, gpu, case)
                                 C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_char_p, C.c_void_p, C.POINTER(C.c_uint64),
                                 C.POINTER(C.c_uint64), C.c_void_p, C.c_void_p]
     g = load_golden("ref_render.npz")
-    full = case == "killeroo_full"
+    glass = case == "killeroo_glass"   # MirrorMaterial / GlassMaterial objects read by the C++ integrator
+    full = case == "killeroo_full" or glass
     res, spp, maxdepth = (int(x) for x in g[case + "_params"])
     feet = case.startswith("feet")
     crop = case == "feet_crop"   # the scene's Film "cropwindow" [.3 .5 .4 .8] as well
@@ -181,7 +182,8 @@ def test_cpp_wavefront_integrator_matches_the_references_render(host, gpu, case)
     I, kd = g[case + "_I"].astype(np.float32), g[case + "_kd"].astype(np.float32)
     prim_mat = emitter = None
     if full:
-        prim_mat = np.ascontiguousarray(np.concatenate([sc["materials"][sc["prim_material"]], np.zeros((1, 8), np.float32)]))
+        mt = scenes.specular_materials(sc) if glass else sc["materials"]
+        prim_mat = np.ascontiguousarray(np.concatenate([mt[sc["prim_material"]], np.zeros((1, 8), np.float32)]))
         emitter = np.ascontiguousarray(sl["L"], np.float32)
     L.ref_render_set_distant.argtypes = [C.c_void_p]
     if feet:
@@ -213,6 +215,8 @@ def test_cpp_wavefront_integrator_matches_the_references_render(host, gpu, case)
     # python mirror with the same seed
     if full:
         verts, prim_kind, rows, pm, mats = scenes.with_sphere_light(sc, plastic=True)
+        if glass:
+            mats = scenes.specular_materials(sc)
         acc = gpu.B200Accel(gpu.build_bvh(verts), verts, prim_kind=prim_kind, spheres=rows)
         integ = gpu.WavefrontPathIntegrator(sc["camera"], spp=spp, maxdepth=maxdepth, light_pos=sl["center"], light_I=sl["L"], seed=9,
                                             sphere_light=(sl["radius"], len(verts) - 1), materials=mats, prim_material=pm)
@@ -233,10 +237,13 @@ def test_cpp_wavefront_integrator_matches_the_references_render(host, gpu, case)
     for _ in range(2):
         near = near | np.roll(near, 1, 0) | np.roll(near, -1, 0) | np.roll(near, 1, 1) | np.roll(near, -1, 1)
     img, ref, py = (np.where(near[..., None], 0, a) for a in (img, ref, py))
+    if glass:   # caustic fireflies: raw mean within 3 %, the tight bars on the images clamped at 1 (see tests/test_gpu_wavefront.py)
+        assert abs(img.mean() / ref.mean() - 1) < 0.03
+        img, ref, py = (np.minimum(a, 1.0) for a in (img, ref, py))
     assert abs(img.mean() / ref.mean() - 1) < 0.01
     cov = blocks(ref).max(-1) > 0   # `feet` covers ~10 % of the frame: RMSE over the covered blocks and their mean
     rm = blocks(ref)[cov].mean()
-    assert np.sqrt(((blocks(img) - blocks(ref)) ** 2)[cov].mean()) / rm < (0.03 if case == "killeroo" else 0.04)
+    assert np.sqrt(((blocks(img) - blocks(ref)) ** 2)[cov].mean()) / rm < (0.03 if case == "killeroo" else 0.085 if glass else 0.04)
     assert np.sqrt(((blocks(img) - blocks(py)) ** 2)[cov].mean()) / rm < (0.005 if case == "killeroo" else 0.01)
     assert abs(st["closest_rays"] / nc.value - 1) < 1e-3
 

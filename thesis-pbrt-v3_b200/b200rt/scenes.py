@@ -196,6 +196,17 @@ def killeroo_simple(xres=700, yres=700):
                      "or, for the point-light integrator, a point light at its centre")
 
 
+def specular_materials(sc):
+    """scenes/killeroo-simple with its two killeroos made perfectly specular — the first `Material "glass"` (Kr 1, Kt 1,
+    index 1.5: materials/glass.cpp's defaults), the second `Material "mirror" "color Kr" [.9 .9 .9]` (mirror.cpp's
+    default) — over the scene's own matte ground and sphere area light: the test scene of the specular path
+    (specularBounce / etaScale in path.cpp, FresnelSpecular and SpecularReflection in reflection.cpp)."""
+    m = sc["materials"].copy()
+    m[1] = [3, 1, 1, 1, 1, 1, 1, 1.5]
+    m[2] = [2, .9, .9, .9, 0, 0, 0, 0]
+    return m
+
+
 def with_sphere_light(sc, plastic=False):
     """Aggregate of `sc` with its sphere area light appended as the LAST primitive, as pbrtShape adds it to the
     primitive list (scenes/killeroo-simple:18-24): returns (bounds_verts, prim_kind, sphere_rows, prim_material,

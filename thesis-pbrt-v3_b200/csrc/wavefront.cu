@@ -52,6 +52,8 @@ struct WfParams {
     float l2w[9];             // B200RT_LIGHT_INFINITE: rotation of LightToWorld, row-major
     const float4 *mats;       // 2 x float4 per material: (kind, Kd.rgb) (Ks.rgb, roughness); nullptr = one matte kd
     const uint8_t *primMat;   // material index per primitive
+    uint32_t has_specular;    // some material is "mirror" / "glass": beta.w then carries the path's specularBounce flag and
+                              // etaScale (path.cpp:76-83,153-160): 0 = (false, 1); else |w| = etaScale, w < 0 = specular bounce
 };
 constexpr float kGamma5 = rt_gamma(5);
 
@@ -140,6 +142,7 @@ __global__ void k_camera(const __grid_constant__ WfParams P, uint64_t batchStart
 struct ShadeOut {
     bool wantShadow, wantNext, wantMis;
     float3 so, sd, contrib, no, nd, mo, md, mcontrib, beta;
+    float betaW;   // the new beta.w (see WfParams::has_specular)
 };
 struct Frame { float3 s, t, n; };
 __device__ __forceinline__ float3 to_local(const Frame &f, float3 v) {
@@ -174,6 +177,42 @@ __device__ __forceinline__ float sphere_cone_sample(const WfParams &P, float3 wl
 
 __device__ void shade_general(const WfParams &P, const WfMat &m, uint32_t depth, uint32_t pix, uint32_t s, float3 p, float3 pe,
                               float3 ng, float3 nf, float3 wo, float4 bt, ShadeOut &o) {
+    const float etaScale = bt.w == 0.f ? 1.f : fabsf(bt.w);
+    o.betaW = etaScale;
+    const uint32_t dim = 2 + 3 * depth;
+    if (m.kind == B200RT_MAT_MIRROR || m.kind == B200RT_MAT_GLASS) {
+        // A perfectly specular BSDF: no direct lighting (path.cpp:130-141 skips UniformSampleOneLight when there is no
+        // non-specular component), only the next direction.  The frame's z is the shape's TRUE normal (isect.n =
+        // isect.shading.n for meshes without "N", triangle.cpp:346,421-424), not the one on wo's side.
+        const float3 ns = m.flip ? make_float3(-ng.x, -ng.y, -ng.z) : ng;
+        Frame fs;
+        fs.n = ns;
+        if (fabsf(ns.x) > fabsf(ns.y)) { const float il = 1.f / sqrtf(ns.x * ns.x + ns.z * ns.z); fs.s = make_float3(-ns.z * il, 0.f, ns.x * il); }
+        else { const float il = 1.f / sqrtf(ns.y * ns.y + ns.z * ns.z); fs.s = make_float3(0.f, ns.z * il, -ns.y * il); }
+        fs.t = make_float3(ns.y * fs.s.z - ns.z * fs.s.y, ns.z * fs.s.x - ns.x * fs.s.z, ns.x * fs.s.y - ns.y * fs.s.x);
+        const float3 woS = to_local(fs, wo);
+        float3 wiS, wgt;
+        bool transmitted;
+        if (!specular_sample(m, woS, rnd(P.seed, pix, s, dim), wiS, wgt, transmitted)) return;
+        float3 nb = make_float3(bt.x * wgt.x, bt.y * wgt.y, bt.z * wgt.z);
+        float es = etaScale;
+        if (transmitted) es *= woS.z > 0.f ? m.alpha * m.alpha : 1.f / (m.alpha * m.alpha);   // path.cpp:154-160
+        bool alive = nb.x > 0.f || nb.y > 0.f || nb.z > 0.f;
+        const float mx = fmaxf(nb.x * es, fmaxf(nb.y * es, nb.z * es));   // rrBeta = beta * etaScale (path.cpp:192)
+        if (alive && mx < 1.f && depth > 3) {
+            const float q = fmaxf(.05f, 1.f - mx);
+            if (rnd(P.seed, pix, s, dim + 2) < q) alive = false;
+            else { const float k = 1.f / (1.f - q); nb.x *= k; nb.y *= k; nb.z *= k; }
+        }
+        if (alive) {
+            o.beta = nb;
+            o.betaW = -es;
+            o.nd = to_world(fs, wiS);
+            o.no = offset_ray_origin(p, pe, ng, o.nd);
+            o.wantNext = true;
+        }
+        return;
+    }
     Frame fr;
     fr.n = nf;
     if (fabsf(nf.x) > fabsf(nf.y)) { const float il = 1.f / sqrtf(nf.x * nf.x + nf.z * nf.z); fr.s = make_float3(-nf.z * il, 0.f, nf.x * il); }
@@ -182,7 +221,6 @@ __device__ void shade_general(const WfParams &P, const WfMat &m, uint32_t depth,
     const float3 woL = to_local(fr, wo);
     const float3 wl = make_float3(P.light_pos[0] - p.x, P.light_pos[1] - p.y, P.light_pos[2] - p.z);
     const float d2 = wl.x * wl.x + wl.y * wl.y + wl.z * wl.z;
-    const uint32_t dim = 2 + 3 * depth;
     if (P.light_kind == B200RT_LIGHT_SPHERE) {
         const float r2 = P.light_radius * P.light_radius;
         const float3 pO = offset_ray_origin(p, pe, ng, wl);
@@ -299,7 +337,7 @@ __device__ void shade_general(const WfParams &P, const WfMat &m, uint32_t depth,
         const float c = fabsf(wiL.z) / pdf;
         float3 nb = make_float3(bt.x * f.x * c, bt.y * f.y * c, bt.z * f.z * c);
         bool alive = nb.x > 0.f || nb.y > 0.f || nb.z > 0.f;
-        const float mx = fmaxf(nb.x, fmaxf(nb.y, nb.z));
+        const float mx = fmaxf(nb.x * etaScale, fmaxf(nb.y * etaScale, nb.z * etaScale));   // etaScale == 1 without glass: exact
         if (alive && mx < 1.f && depth > 3) {
             const float q = fmaxf(.05f, 1.f - mx);
             if (rnd(P.seed, pix, s, dim + 2) < q) alive = false;
@@ -335,7 +373,11 @@ __global__ void k_shade(const __grid_constant__ WfParams P, uint32_t depth, uint
     uint32_t path = 0;
     if (i < n) {
         const b200rt_hit h = hits[i];
-        if (infinite && depth == 0 && h.prim == B200RT_MISS) {
+        // path.cpp:97-107: emitted radiance is added for camera rays and after a specular bounce (every other vertex gets
+        // it through EstimateDirect's MIS pair)
+        bool seesLe = depth == 0;
+        if (FULL && P.has_specular && depth > 0 && (area || infinite)) seesLe = beta[qPath[i]].w < 0.f;
+        if (infinite && seesLe && h.prim == B200RT_MISS) {
             // a camera ray that escapes sees the environment: L += beta * light->Le(ray) (path.cpp:97-107, bounces == 0;
             // infinite.cpp:95-101 with the constant map).  Later escapes are accounted for by the MIS ray.
             const uint32_t pth = qPath[i];
@@ -344,7 +386,9 @@ __global__ void k_shade(const __grid_constant__ WfParams P, uint32_t depth, uint
             l.x += bt.x * P.light_I[0]; l.y += bt.y * P.light_I[1]; l.z += bt.z * P.light_I[2];
             L[pth] = l;
         }
-        if (h.prim != B200RT_MISS && depth < P.max_depth) {  // path.cpp:110
+        // path.cpp:110: the path ends at maxdepth AFTER the emitted radiance was added; the launch at depth == max_depth
+        // exists only for that (scenes with specular materials)
+        if (h.prim != B200RT_MISS && (depth < P.max_depth || (area && seesLe))) {
             path = qPath[i];
             const float4 rd = rays[2 * (size_t)i + 1];
             const float4 a = __ldg(primTris + 3 * (size_t)h.prim), b = __ldg(primTris + 3 * (size_t)h.prim + 1),
@@ -361,7 +405,7 @@ __global__ void k_shade(const __grid_constant__ WfParams P, uint32_t depth, uint
             const float nl = sqrtf(ng.x * ng.x + ng.y * ng.y + ng.z * ng.z);
             // a sphere primitive (killeroo-simple's emitter: matte Kd = 0) ends the path: nothing to reflect.  Seen by a
             // camera ray it adds its emitted radiance (path.cpp:97-107: bounces == 0; later hits are covered by MIS).
-            if (area && depth == 0 && h.prim == P.light_prim) {
+            if (area && seesLe && h.prim == P.light_prim) {
                 const float4 ro = rays[2 * (size_t)i];
                 const float3 ph = make_float3(ro.x + h.t * rd.x, ro.y + h.t * rd.y, ro.z + h.t * rd.z);
                 const float cosl = (ph.x - P.light_pos[0]) * -rd.x + (ph.y - P.light_pos[1]) * -rd.y + (ph.z - P.light_pos[2]) * -rd.z;
@@ -372,23 +416,26 @@ __global__ void k_shade(const __grid_constant__ WfParams P, uint32_t depth, uint
                     L[path] = l;
                 }
             }
-            if (nl > 0.f && !(__float_as_uint(b.w) & B200RT_PRIM_SPHERE)) {
+            if (depth < P.max_depth && nl > 0.f && !(__float_as_uint(b.w) & B200RT_PRIM_SPHERE)) {
                 ng.x /= nl; ng.y /= nl; ng.z /= nl;
                 float kdr = P.kd[0], kdg = P.kd[1], kdb = P.kd[2];
                 WfMat gm;
                 gm.glossy = false;
+                gm.kind = B200RT_MAT_MATTE; gm.flip = false;
                 if (FULL && P.mats) {
                     const uint32_t mi = __ldg(P.primMat + h.prim);
                     const float4 m0 = __ldg(P.mats + 2 * (size_t)mi), m1 = __ldg(P.mats + 2 * (size_t)mi + 1);
                     kdr = m0.y; kdg = m0.z; kdb = m0.w;
-                    gm.glossy = m0.x == (float)B200RT_MAT_PLASTIC && (m1.x > 0.f || m1.y > 0.f || m1.z > 0.f);
+                    const uint32_t kf = (uint32_t)m0.x;
+                    gm.kind = kf & 15u; gm.flip = (kf & B200RT_MAT_REVERSE_ORIENTATION) != 0;
+                    gm.glossy = gm.kind == B200RT_MAT_PLASTIC && (m1.x > 0.f || m1.y > 0.f || m1.z > 0.f);
                     gm.ks[0] = m1.x; gm.ks[1] = m1.y; gm.ks[2] = m1.z; gm.alpha = m1.w;
                 }
                 const float3 wo = make_float3(-rd.x, -rd.y, -rd.z);
                 const float side = (ng.x * wo.x + ng.y * wo.y + ng.z * wo.z) < 0.f ? -1.f : 1.f;
                 const float3 nf = make_float3(side * ng.x, side * ng.y, side * ng.z);  // wo's hemisphere
                 const float4 bt = beta[path];
-                if (FULL && (gm.glossy || infinite)) {   // Material "plastic" / the infinite light: the general BSDF + light code
+                if (FULL && (gm.glossy || infinite || P.has_specular)) {   // Material "plastic" / the infinite light / scenes with specular materials: the general BSDF + light code
                     gm.kd[0] = kdr; gm.kd[1] = kdg; gm.kd[2] = kdb;
                     gm.diffuse = kdr > 0.f || kdg > 0.f || kdb > 0.f;
                     uint32_t gx, gy, gs;
@@ -399,7 +446,7 @@ __global__ void k_shade(const __grid_constant__ WfParams P, uint32_t depth, uint
                     wantShadow = o.wantShadow; so = o.so; sd = o.sd; contrib = o.contrib;
                     wantMis = o.wantMis; mo = o.mo; md = o.md; mcontrib = o.mcontrib;
                     wantNext = o.wantNext; no = o.no; nd = o.nd;
-                    if (o.wantNext) beta[path] = make_float4(o.beta.x, o.beta.y, o.beta.z, 0.f);
+                    if (o.wantNext) beta[path] = make_float4(o.beta.x, o.beta.y, o.beta.z, P.has_specular ? o.betaW : 0.f);
                 } else {
                 // -- direct lighting: PointLight::Sample_Li (point.cpp:44-53) + matte f * |cos|
                 const float3 wl = make_float3(P.light_pos[0] - p.x, P.light_pos[1] - p.y, P.light_pos[2] - p.z);
@@ -811,15 +858,22 @@ static int render_impl(b200rt_scene *s, const b200rt_render_desc *d, float *film
     }
     if (d->materials) {
         for (uint32_t k = 0; k < d->n_materials; ++k)
-            if (d->materials[8 * k] != (float)B200RT_MAT_MATTE && d->materials[8 * k] != (float)B200RT_MAT_PLASTIC)
-                return set_error(B200RT_EUNSUPPORTED, "material %u: only matte and plastic are supported", k);
+        {
+            const float kf = d->materials[8 * k];
+            const uint32_t kind = (uint32_t)kf & 15u;
+            if (!(kf >= 0.f && kf < 32.f) || kf != (float)(uint32_t)kf || kind > B200RT_MAT_GLASS)
+                return set_error(B200RT_EUNSUPPORTED, "material %u: only matte, plastic, mirror and glass are supported", k);
+            if (kind == B200RT_MAT_GLASS && !(d->materials[8 * k + 7] > 0.f))
+                return set_error(B200RT_EINVAL, "material %u: glass needs its \"index\" of refraction in the roughness slot", k);
+            if (kind == B200RT_MAT_MIRROR || kind == B200RT_MAT_GLASS) P.has_specular = 1;
+        }
         if (w->mats_n < d->n_materials) { cudaFree(w->mats); w->mats = nullptr; WCU(cudaMalloc(&w->mats, (size_t)d->n_materials * 32)); w->mats_n = d->n_materials; }
         if (w->primMat_n < s->n_prims) { cudaFree(w->primMat); w->primMat = nullptr; WCU(cudaMalloc(&w->primMat, s->n_prims)); w->primMat_n = s->n_prims; }
         for (uint32_t k = 0; k < s->n_prims; ++k)
             if (d->prim_material[k] >= d->n_materials) return set_error(B200RT_EINVAL, "prim_material[%u] out of range", k);
         std::vector<float> mt(d->materials, d->materials + 8 * (size_t)d->n_materials);
         for (uint32_t k = 0; k < d->n_materials; ++k)
-            if (mt[8 * k] == (float)B200RT_MAT_PLASTIC) {  // TrowbridgeReitzDistribution::RoughnessToAlpha (microfacet.h:123-128), remaproughness true
+            if (((uint32_t)mt[8 * k] & 15u) == B200RT_MAT_PLASTIC) {  // TrowbridgeReitzDistribution::RoughnessToAlpha (microfacet.h:123-128), remaproughness true
                 const float x = std::log(std::max(mt[8 * k + 7], 1e-3f));
                 mt[8 * k + 7] = 1.62142f + 0.819955f * x + 0.1734f * x * x + 0.0171201f * x * x * x + 0.000640711f * x * x * x * x;
             }
@@ -889,13 +943,16 @@ static int render_impl(b200rt_scene *s, const b200rt_render_desc *d, float *film
                 k_heat<<<gridSlots, TB, 0, st>>>(P, start, w->counts + 2 * depth, w->qPath[cur], w->perRay, d_heat, 0u);
                 g_launches.fetch_add(1);
             }
-            if (depth == d->max_depth) break;  // path.cpp:110: the last intersection is found, then the path ends
+            // path.cpp:110: the last intersection is found, then the path ends — after the emitted radiance a specular
+            // bounce may still see there (path.cpp:97-107): one more shade launch, which only adds Le
+            if (depth == d->max_depth && !(P.has_specular && mis)) break;
             (mis || distant || P.mats ? k_shade<true> : k_shade<false>)<<<gridSlots, TB, 0, st>>>(P, depth, start, w->counts + 2 * depth, w->rays[cur], w->qPath[cur], w->hits,
                                               s->d_prim_tris, w->beta, w->rays[cur ^ 1], w->qPath[cur ^ 1],
                                               w->counts + 2 * (depth + 1), w->shRays, w->shPath, w->shContrib,
                                               w->counts + 2 * depth + 1, w->L, w->misRays, w->misPath, w->misContrib,
                                               w->counts + misBase + depth);
             g_launches.fetch_add(1);
+            if (depth == d->max_depth) break;
             if (w->keep) WCU(cudaMemcpyAsync(w->kept[2 * depth + 1], w->shRays, (size_t)nSlots * 32, cudaMemcpyDeviceToDevice, st));
             a = ev();
             rc = launch_trace(s, w->shRays, nSlots, w->counts + 2 * depth + 1, nullptr, w->occ, true,

@@ -3,6 +3,9 @@
 //   Material "matte"   (materials/matte.cpp:44-60, sigma 0)   : LambertianReflection(Kd)
 //   Material "plastic" (materials/plastic.cpp:44-70)           : LambertianReflection(Kd) + MicrofacetReflection(Ks,
 //        TrowbridgeReitzDistribution(alpha, alpha) with alpha = RoughnessToAlpha(roughness), FresnelDielectric(1.5, 1))
+//   Material "mirror"  (materials/mirror.cpp:44-56)            : SpecularReflection(Kr, FresnelNoOp)
+//   Material "glass"   (materials/glass.cpp:44-63, roughness 0; PathIntegrator asks for allowMultipleLobes)
+//                                                              : FresnelSpecular(Kr, Kt, 1, index, Radiance)
 // and the BSDF container's rules for several lobes (reflection.cpp BSDF::f / Pdf / Sample_f: lobe picked uniformly by
 // u[0], pdf = mean of the lobes' pdfs, f = sum of the lobes).  Isotropic lobes only, so any orthonormal frame around
 // the normal is equivalent to the reference's dpdu frame.
@@ -16,6 +19,10 @@ struct WfMat {
     float alpha;     // TrowbridgeReitz alpha (already remapped from "roughness" on the host)
     bool diffuse;    // !Kd.IsBlack()
     bool glossy;     // !Ks.IsBlack()
+    // perfectly specular materials: kd = Kr, ks = Kt, alpha = "index"; `flip` = reverseOrientation ^ transformSwapsHandedness
+    // of the shape (triangle.cpp:421-424), which decides on which side of a triangle the glass is
+    uint32_t kind;   // B200RT_MAT_*
+    bool flip;
 };
 
 constexpr float kBsdfPi = 3.14159265358979323846f;
@@ -164,6 +171,47 @@ __device__ __forceinline__ bool bsdf_sample(const WfMat &m, const float3 wo, flo
     }
     bsdf_eval(m, wo, wi, f, pdf);
     return pdf > 0.f && (f.x > 0.f || f.y > 0.f || f.z > 0.f);
+}
+
+// The single specular lobe of "mirror" / "glass" through BSDF::Sample_f (reflection.cpp:703-770; one matching
+// component, so u0 reaches the BxDF unchanged): SpecularReflection::Sample_f (reflection.cpp:136-143) with FresnelNoOp,
+// or FresnelSpecular::Sample_f (reflection.cpp:477-511, TransportMode::Radiance).  wo in the frame of the TRUE shading
+// normal (wo.z < 0 = seen from the back: for glass, from inside).  Returns false when the path ends (f black / pdf 0);
+// else wi, w = f |cos wi| / pdf per channel (what path.cpp:151 multiplies beta by) and whether the lobe transmitted.
+__device__ __forceinline__ bool specular_sample(const WfMat &m, const float3 wo, float u0, float3 &wi, float3 &w, bool &transmitted) {
+    transmitted = false;
+    if (wo.z == 0.f) return false;   // BSDF::Sample_f (reflection.cpp:735)
+    if (m.kind == 2u /* B200RT_MAT_MIRROR */) {
+        if (!(m.kd[0] > 0.f || m.kd[1] > 0.f || m.kd[2] > 0.f)) return false;   // R.IsBlack(): no BxDF at all
+        wi = make_float3(-wo.x, -wo.y, wo.z);
+        const float a = fabsf(wi.z);
+        w = make_float3(m.kd[0] / a * a, m.kd[1] / a * a, m.kd[2] / a * a);
+        return w.x > 0.f || w.y > 0.f || w.z > 0.f;
+    }
+    const bool rBlack = !(m.kd[0] > 0.f || m.kd[1] > 0.f || m.kd[2] > 0.f), tBlack = !(m.ks[0] > 0.f || m.ks[1] > 0.f || m.ks[2] > 0.f);
+    if (rBlack && tBlack) return false;   // glass.cpp:58
+    const float eta = m.alpha;
+    const float F = fr_dielectric(wo.z, 1.f, eta);
+    if (u0 < F) {
+        wi = make_float3(-wo.x, -wo.y, wo.z);
+        const float a = fabsf(wi.z);
+        w = make_float3(F * m.kd[0] / a * a / F, F * m.kd[1] / a * a / F, F * m.kd[2] / a * a / F);
+        return w.x > 0.f || w.y > 0.f || w.z > 0.f;
+    }
+    const bool entering = wo.z > 0.f;
+    const float etaI = entering ? 1.f : eta, etaT = entering ? eta : 1.f;
+    // Refract(wo, Faceforward(Normal3f(0, 0, 1), wo), etaI / etaT, wi) (reflection.h:96-108)
+    const float nz = wo.z < 0.f ? -1.f : 1.f, e = etaI / etaT;
+    const float cosThetaI = nz * wo.z;
+    const float sin2ThetaI = fmaxf(0.f, 1.f - cosThetaI * cosThetaI);
+    const float sin2ThetaT = e * e * sin2ThetaI;
+    if (sin2ThetaT >= 1.f) return false;   // total internal reflection on the transmission branch: f = 0, the path ends
+    const float cosThetaT = sqrtf(1.f - sin2ThetaT);
+    wi = make_float3(e * -wo.x, e * -wo.y, e * -wo.z + (e * cosThetaI - cosThetaT) * nz);
+    const float k = (1.f - F) * ((etaI * etaI) / (etaT * etaT)), a = fabsf(wi.z), pdf = 1.f - F;
+    w = make_float3(m.ks[0] * k / a * a / pdf, m.ks[1] * k / a * a / pdf, m.ks[2] * k / a * a / pdf);
+    transmitted = true;
+    return pdf > 0.f && (w.x > 0.f || w.y > 0.f || w.z > 0.f);
 }
 
 }  // namespace b200rt

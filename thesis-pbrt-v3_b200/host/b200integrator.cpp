@@ -25,12 +25,15 @@
 
 // The point-light / matte case reads the scene through pbrt's public interfaces only.  The sphere area light and
 // "plastic" need three things that have no accessor (inside the reference tree: `friend class B200WavefrontIntegrator;`):
-// GeometricPrimitive::shape + Sphere::radius (the emitter's geometry) and PlasticMaterial::Kd/Ks/roughness.
+// GeometricPrimitive::shape + Sphere::radius (the emitter's geometry) and PlasticMaterial::Kd/Ks/roughness (likewise
+// MirrorMaterial::Kr and GlassMaterial::Kr/Kt/index/uRoughness/vRoughness).
 #define private public
 #define protected public
 #include "core/primitive.h"
 #include "shapes/sphere.h"
 #include "materials/plastic.h"
+#include "materials/mirror.h"
+#include "materials/glass.h"
 #include "core/film.h"   // Film::pixels / Pixel::stats for "bool generalstats" (no accessor either)
 #undef private
 #undef protected
@@ -219,13 +222,19 @@ void B200WavefrontIntegrator::Render(const Scene &scene) {
     std::vector<float> mats;
     std::vector<uint8_t> primMat(accel->primitiveCount(), 0);
     {
-        std::map<const Material *, int> seen;
+        // one record per distinct (Material object, orientation flag): glass needs to know on which side of a triangle the
+        // shape's normal is (Shape::reverseOrientation ^ transformSwapsHandedness, triangle.cpp:421-424)
+        std::map<std::pair<const Material *, bool>, int> seen;
         SurfaceInteraction si(Point3f(0, 0, 0), Vector3f(0, 0, 0), Point2f(0.5f, 0.5f), Vector3f(0, 0, 1), Vector3f(1, 0, 0),
                               Vector3f(0, 1, 0), Normal3f(0, 0, 0), Normal3f(0, 0, 0), 0, nullptr);
         for (size_t i = 0; i < accel->primitiveCount(); ++i) {
             const Material *m = accel->primitive((uint32_t)i)->GetMaterial();
             if (!m) { Error("b200wavefront: primitive %d has no material", (int)i); return; }
-            auto it = seen.find(m);
+            bool flip = false;
+            if (dynamic_cast<const GlassMaterial *>(m))
+                if (const GeometricPrimitive *gpm = dynamic_cast<const GeometricPrimitive *>(accel->primitive((uint32_t)i).get()))
+                    flip = gpm->shape->reverseOrientation ^ gpm->shape->transformSwapsHandedness;
+            auto it = seen.find(std::make_pair(m, flip));
             if (it == seen.end()) {
                 if (seen.size() >= 256) { Error("b200wavefront: more than 256 materials"); return; }
                 float rec[8] = {0, 0, 0, 0, 0, 0, 0, 0};
@@ -237,12 +246,29 @@ void B200WavefrontIntegrator::Render(const Scene &scene) {
                     rec[0] = (float)B200RT_MAT_PLASTIC;
                     for (int c = 0; c < 3; ++c) { rec[1 + c] = kd[c]; rec[4 + c] = ks[c]; }
                     rec[7] = pm->roughness->Evaluate(si);
+                } else if (const MirrorMaterial *mm = dynamic_cast<const MirrorMaterial *>(m)) {
+                    if (mm->bumpMap) { Error("b200wavefront: mirror with a bump map is not supported"); return; }
+                    Float kr[3];
+                    Spectrum(mm->Kr->Evaluate(si).Clamp()).ToRGB(kr);
+                    rec[0] = (float)B200RT_MAT_MIRROR;
+                    for (int c = 0; c < 3; ++c) rec[1 + c] = kr[c];
+                } else if (const GlassMaterial *gm = dynamic_cast<const GlassMaterial *>(m)) {
+                    if (gm->bumpMap || gm->uRoughness->Evaluate(si) != 0 || gm->vRoughness->Evaluate(si) != 0) {
+                        Error("b200wavefront: only smooth glass (roughness 0, no bump map) is supported");
+                        return;
+                    }
+                    Float kr[3], kt[3];
+                    Spectrum(gm->Kr->Evaluate(si).Clamp()).ToRGB(kr);
+                    Spectrum(gm->Kt->Evaluate(si).Clamp()).ToRGB(kt);
+                    rec[0] = (float)(B200RT_MAT_GLASS + (flip ? B200RT_MAT_REVERSE_ORIENTATION : 0));
+                    for (int c = 0; c < 3; ++c) { rec[1 + c] = kr[c]; rec[4 + c] = kt[c]; }
+                    rec[7] = gm->index->Evaluate(si);
                 } else {
                     Float kd[3];
-                    if (!lambertianKd(m, kd)) { Error("b200wavefront: only \"matte\" and \"plastic\" materials are supported"); return; }
+                    if (!lambertianKd(m, kd)) { Error("b200wavefront: only \"matte\", \"plastic\", \"mirror\" and smooth \"glass\" materials are supported"); return; }
                     for (int c = 0; c < 3; ++c) rec[1 + c] = kd[c];
                 }
-                it = seen.emplace(m, (int)seen.size()).first;
+                it = seen.emplace(std::make_pair(m, flip), (int)seen.size()).first;
                 mats.insert(mats.end(), rec, rec + 8);
             }
             primMat[i] = (uint8_t)it->second;
