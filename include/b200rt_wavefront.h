@@ -13,7 +13,7 @@
  * (src/cameras/perspective.cpp), one point light (src/lights/point.cpp), one distant light (src/lights/distant.cpp), one
  * sphere area light (src/lights/diffuse.cpp, Sphere::Sample/Pdf) OR one constant infinite light (src/lights/infinite.cpp
  * with the 1x1 map) — the last two with multiple importance sampling (EstimateDirect's two strategies) —, "matte" and
- * "plastic", "mirror" and smooth "glass" materials per primitive (src/materials/matte.cpp, plastic.cpp, mirror.cpp, glass.cpp), box pixel filter, Russian roulette of
+ * "plastic", "mirror", smooth "glass", "metal" and "substrate" materials per primitive (src/materials/matte.cpp, plastic.cpp, mirror.cpp, glass.cpp, metal.cpp, substrate.cpp), box pixel filter, Russian roulette of
  * path.cpp:190-199, path depths up to 68 (scenes/living-room uses 65).  Samples come
  * from a counter-based hash of (pixel, sample, dimension), so the image does not depend on the
  * execution order, the batch size or the number of GPUs.
@@ -61,7 +61,7 @@ typedef struct {
                               at p + wLight * 2 * radius.  A delta light: no MIS rays. */
     uint32_t light_prim;   /* primitive number of that sphere inside the aggregate (scene-desc prim_kind == 1) */
     /* Materials: NULL = Material "matte" "Kd" = kd for all.  Else n_materials records of 8 floats
-     * (kind, Kd.r, Kd.g, Kd.b, Ks.r, Ks.g, Ks.b, roughness), kind B200RT_MAT_MATTE (materials/matte.cpp, sigma 0), B200RT_MAT_PLASTIC (materials/plastic.cpp), B200RT_MAT_MIRROR or B200RT_MAT_GLASS (records below),
+     * (kind, Kd.r, Kd.g, Kd.b, Ks.r, Ks.g, Ks.b, roughness), kind B200RT_MAT_MATTE (materials/matte.cpp, sigma 0), B200RT_MAT_PLASTIC (materials/plastic.cpp), B200RT_MAT_MIRROR, B200RT_MAT_GLASS, B200RT_MAT_METAL or B200RT_MAT_SUBSTRATE (records below),
      * and one material index per primitive.  HOST pointers, read during the call. */
     const float *materials;
     uint32_t n_materials;
@@ -90,6 +90,12 @@ enum {
     B200RT_MAT_MIRROR = 2,  /* materials/mirror.cpp:44-56: SpecularReflection(Kr, FresnelNoOp); record = (kind, Kr.rgb, -, -, -, -) */
     B200RT_MAT_GLASS = 3,   /* materials/glass.cpp:44-63 with roughness 0 under the path integrator (allowMultipleLobes):
                                FresnelSpecular(Kr, Kt, 1, index); record = (kind, Kr.rgb, Kt.rgb, index) */
+    B200RT_MAT_METAL = 4,   /* materials/metal.cpp:60-82: MicrofacetReflection(1, TrowbridgeReitz, FresnelConductor(1, eta, k)),
+                               isotropic; record = (kind, eta.rgb, k.rgb, roughness) */
+    B200RT_MAT_SUBSTRATE = 5, /* materials/substrate.cpp:45-66: FresnelBlend(Kd, Ks, TrowbridgeReitz), isotropic;
+                               record = (kind, Kd.rgb, Ks.rgb, roughness) */
+    B200RT_MAT_NO_REMAP = 32, /* added to `kind`: "bool remaproughness" false — roughness IS the Trowbridge-Reitz alpha
+                               (plastic, metal, substrate; scenes/living-room's materials are written that way) */
     B200RT_MAT_REVERSE_ORIENTATION = 16 /* added to `kind`: the shape's reverseOrientation ^ transformSwapsHandedness
                                (triangle.cpp:421-424) — flips the side of a triangle its normal (= the glass's outside) is on */
 };

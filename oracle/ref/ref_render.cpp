@@ -31,6 +31,8 @@
 #include "materials/plastic.h"
 #include "materials/mirror.h"
 #include "materials/glass.h"
+#include "materials/metal.h"
+#include "materials/substrate.h"
 #include "samplers/halton.h"
 #include "samplers/random.h"
 #include "textures/constant.h"
@@ -152,7 +154,8 @@ extern "C" int ref_render(ref_scene *s, const char *accel_kind, const float *cam
                           const char *sampler_name, int n_threads, const char *tmp_prefix, float *out_rgb,
                           uint64_t *n_closest, uint64_t *n_shadow, uint32_t *out_heat /* nullable: 6 planes of yres*xres */,
                           const float *prim_mat /* nullable: 8 floats per primitive (kind 0 matte / 1 plastic, Kd rgb, Ks rgb,
-                                                   roughness; kind 2 mirror: Kr; kind 3 glass: Kr, Kt, index) instead of the
+                                                   roughness; kind 2 mirror: Kr; kind 3 glass: Kr, Kt, index; kind 4 metal: eta, k,
+                                                   roughness; kind 5 substrate: Kd, Ks, roughness; +32 = remaproughness false) instead of the
                                                    single matte `kd` */,
                           const float *emitter_L /* nullable: rgb; the scene's LAST primitive (a sphere) becomes
                                                     AreaLightSource "area" "color L" and replaces the point light */,
@@ -179,13 +182,23 @@ extern "C" int ref_render(ref_scene *s, const char *accel_kind, const float *cam
                 Float c[3] = {k[1], k[2], k[3]}, cs[3] = {k[4], k[5], k[6]};
                 auto tex = std::make_shared<ConstantTexture<Spectrum>>(Spectrum::FromRGB(c));
                 std::shared_ptr<Material> mm;
-                if (k[0] == 1.f) {   // Material "plastic" "color Kd" "color Ks" "float roughness" (materials/plastic.cpp:72-84)
+                const int kind = (int)k[0] & 15;
+                const bool remap = !((int)k[0] & 32);   // "bool remaproughness"
+                if (kind == 1) {   // Material "plastic" "color Kd" "color Ks" "float roughness" (materials/plastic.cpp:72-84)
                     auto texS = std::make_shared<ConstantTexture<Spectrum>>(Spectrum::FromRGB(cs));
                     auto rough = std::make_shared<ConstantTexture<Float>>(k[7]);
-                    mm = std::make_shared<PlasticMaterial>(tex, texS, rough, nullptr, true);
-                } else if (k[0] == 2.f) {   // Material "mirror" "color Kr" (materials/mirror.cpp:58-63)
+                    mm = std::make_shared<PlasticMaterial>(tex, texS, rough, nullptr, remap);
+                } else if (kind == 4) {   // Material "metal" "rgb eta" "rgb k" "float roughness" (materials/metal.cpp:111-128)
+                    auto texK = std::make_shared<ConstantTexture<Spectrum>>(Spectrum::FromRGB(cs));
+                    auto rough = std::make_shared<ConstantTexture<Float>>(k[7]);
+                    mm = std::make_shared<MetalMaterial>(tex, texK, rough, nullptr, nullptr, nullptr, remap);
+                } else if (kind == 5) {   // Material "substrate" "rgb Kd" "rgb Ks" "float uroughness" = "vroughness" (materials/substrate.cpp:68-83)
+                    auto texS = std::make_shared<ConstantTexture<Spectrum>>(Spectrum::FromRGB(cs));
+                    auto rough = std::make_shared<ConstantTexture<Float>>(k[7]);
+                    mm = std::make_shared<SubstrateMaterial>(tex, texS, rough, rough, nullptr, remap);
+                } else if (kind == 2) {   // Material "mirror" "color Kr" (materials/mirror.cpp:58-63)
                     mm = std::make_shared<MirrorMaterial>(tex, nullptr);
-                } else if (k[0] == 3.f) {   // Material "glass" "color Kr" "color Kt" "float index" (materials/glass.cpp:97-110), roughness 0
+                } else if (kind == 3) {   // Material "glass" "color Kr" "color Kt" "float index" (materials/glass.cpp:97-110), roughness 0
                     auto texT = std::make_shared<ConstantTexture<Spectrum>>(Spectrum::FromRGB(cs));
                     auto zero = std::make_shared<ConstantTexture<Float>>(0.f);
                     auto index = std::make_shared<ConstantTexture<Float>>(k[7]);

@@ -27,6 +27,8 @@ CASES = {
     # the same scene with the killeroos made perfectly specular (glass index 1.5 / mirror Kr .9): specularBounce, etaScale,
     # FresnelSpecular and SpecularReflection of the reference; maxdepth 8 so that Russian roulette sees etaScale
     "killeroo_glass": dict(scene="killeroo_simple", res=128, spp=256, maxdepth=8, I=(2000.0,) * 3, kd=(.5, .5, .5), area=True, specular=True),
+    # ... and with scenes/living-room's microfacet materials: substrate ground, metal (conductor Fresnel) and substrate killeroos
+    "killeroo_metal": dict(scene="killeroo_simple", res=128, spp=256, maxdepth=5, I=(2000.0,) * 3, kd=(.5, .5, .5), area=True, metal=True),
     # BASELINE config 4's scene as written (scenes/killeroo-feet: LightSource "distant" from the eye towards the look-at
     # point, Material "plastic" Kd (.4 .5 .4) Ks .3 roughness .15, path maxdepth 5), whole frame instead of the crop window
     "feet": dict(scene="killeroo_feet", res=192, spp=256, maxdepth=5, I=(1.0,) * 3, kd=(.5, .5, .5), distant=True),
@@ -62,6 +64,8 @@ def main():
             mats = sc["materials"] if c.get("plastic") else np.pad(sc["material_kd"], ((0, 0), (1, 4)))
             if c.get("specular"):
                 mats = scenes.specular_materials(sc)
+            if c.get("metal"):
+                mats = scenes.metal_materials(sc)
             extra = dict(prim_mat=np.concatenate([mats[sc["prim_material"]], np.zeros((1, 8), np.float32)]), emitter_L=sl["L"])
         if c.get("distant"):
             extra = dict(prim_mat=np.repeat(sc["materials"], len(tv), 0), distant=(sc["light_from"], sc["light_to"]))

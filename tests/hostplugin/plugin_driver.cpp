@@ -104,6 +104,8 @@ extern "C" int plugin_intersect_p_batch(const ref_accel *a, const float *rays, u
 #include "materials/plastic.h"
 #include "materials/mirror.h"
 #include "materials/glass.h"
+#include "materials/metal.h"
+#include "materials/substrate.h"
 #include "lights/diffuse.h"
 #include "lights/distant.h"
 #include "core/sampling.h"
@@ -148,11 +150,15 @@ extern "C" int plugin_render(ref_scene *s, const char *tree, const float *cam, i
                 Float c[3] = {k[1], k[2], k[3]}, cs[3] = {k[4], k[5], k[6]};
                 auto tex = std::make_shared<ConstantTexture<Spectrum>>(Spectrum::FromRGB(c));
                 std::shared_ptr<Material> mm;
-                if (k[0] == 1.f)
-                    mm = std::make_shared<PlasticMaterial>(tex, std::make_shared<ConstantTexture<Spectrum>>(Spectrum::FromRGB(cs)),
-                                                           std::make_shared<ConstantTexture<Float>>(k[7]), nullptr, true);
-                else if (k[0] == 2.f) mm = std::make_shared<MirrorMaterial>(tex, nullptr);
-                else if (k[0] == 3.f)
+                const int kind = (int)k[0] & 15;
+                const bool remap = !((int)k[0] & 32);
+                auto texS = std::make_shared<ConstantTexture<Spectrum>>(Spectrum::FromRGB(cs));
+                auto rough = std::make_shared<ConstantTexture<Float>>(k[7]);
+                if (kind == 1) mm = std::make_shared<PlasticMaterial>(tex, texS, rough, nullptr, remap);
+                else if (kind == 4) mm = std::make_shared<MetalMaterial>(tex, texS, rough, nullptr, nullptr, nullptr, remap);
+                else if (kind == 5) mm = std::make_shared<SubstrateMaterial>(tex, texS, rough, rough, nullptr, remap);
+                else if (kind == 2) mm = std::make_shared<MirrorMaterial>(tex, nullptr);
+                else if (kind == 3)
                     mm = std::make_shared<GlassMaterial>(tex, std::make_shared<ConstantTexture<Spectrum>>(Spectrum::FromRGB(cs)),
                                                          std::make_shared<ConstantTexture<Float>>(0.f), std::make_shared<ConstantTexture<Float>>(0.f),
                                                          std::make_shared<ConstantTexture<Float>>(k[7]), nullptr, true);

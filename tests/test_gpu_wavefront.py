@@ -252,7 +252,7 @@ def test_heatmaps_match_the_references_per_pixel_statistics(gpu):
         assert np.sqrt(((ab - bb) ** 2).mean()) / bb.mean() < 0.04, name
 
 
-@pytest.mark.parametrize("case,plastic", [("killeroo_area", False), ("killeroo_full", True), ("killeroo_glass", "specular")])
+@pytest.mark.parametrize("case,plastic", [("killeroo_area", False), ("killeroo_full", True), ("killeroo_glass", "specular"), ("killeroo_metal", "metal")])
 def test_area_light_mis_matches_the_references_render(gpu, case, plastic):
     """killeroo_full = BASELINE config 1 exactly as scenes/killeroo-simple describes it (sphere area light, matte
     ground, two "plastic" killeroos: Lambertian + Trowbridge-Reitz microfacet lobe with FresnelDielectric(1.5, 1),
@@ -275,6 +275,8 @@ def test_area_light_mis_matches_the_references_render(gpu, case, plastic):
     verts, prim_kind, rows, pm, mats = scenes.with_sphere_light(sc, plastic=bool(plastic))
     if plastic == "specular":
         mats = scenes.specular_materials(sc)
+    if plastic == "metal":   # substrate ground, metal + substrate killeroos (scenes.metal_materials): FresnelBlend and
+        mats = scenes.metal_materials(sc)   # MicrofacetReflection with FresnelConductor, remapped and unremapped roughness
     acc = gpu.B200Accel(gpu.build_bvh(verts), verts, prim_kind=prim_kind, spheres=rows)
     sl = sc["sphere_light"]
     integ = gpu.WavefrontPathIntegrator(sc["camera"], spp=spp, maxdepth=maxdepth, light_pos=sl["center"], light_I=sl["L"],

@@ -207,6 +207,18 @@ def specular_materials(sc):
     return m
 
 
+def metal_materials(sc):
+    """scenes/killeroo-simple with the microfacet materials scenes/living-room uses (scene.pbrt:14-21): ground =
+    `Material "substrate"` Kd (.5 .5 .8) Ks .04 roughness .1 (remapped); first killeroo = `Material "metal"` with the
+    file's BrushedStainlessSteel eta / k, roughness .1, "remaproughness" false (kind + 32); second = the file's
+    "Paneling" substrate (Kd .8, Ks .04, roughness .2, "remaproughness" false)."""
+    m = sc["materials"].copy()
+    m[0] = [5, .5, .5, .8, .04, .04, .04, .1]
+    m[1] = [4 + 32, 1.657460, 0.880369, 0.521229, 9.223869, 6.269523, 4.837001, .1]
+    m[2] = [5 + 32, .8, .8, .8, .04, .04, .04, .2]
+    return m
+
+
 def with_sphere_light(sc, plastic=False):
     """Aggregate of `sc` with its sphere area light appended as the LAST primitive, as pbrtShape adds it to the
     primitive list (scenes/killeroo-simple:18-24): returns (bounds_verts, prim_kind, sphere_rows, prim_material,

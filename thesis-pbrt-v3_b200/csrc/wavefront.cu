@@ -428,14 +428,14 @@ __global__ void k_shade(const __grid_constant__ WfParams P, uint32_t depth, uint
                     kdr = m0.y; kdg = m0.z; kdb = m0.w;
                     const uint32_t kf = (uint32_t)m0.x;
                     gm.kind = kf & 15u; gm.flip = (kf & B200RT_MAT_REVERSE_ORIENTATION) != 0;
-                    gm.glossy = gm.kind == B200RT_MAT_PLASTIC && (m1.x > 0.f || m1.y > 0.f || m1.z > 0.f);
+                    gm.glossy = (gm.kind == B200RT_MAT_PLASTIC || gm.kind == B200RT_MAT_SUBSTRATE) && (m1.x > 0.f || m1.y > 0.f || m1.z > 0.f);
                     gm.ks[0] = m1.x; gm.ks[1] = m1.y; gm.ks[2] = m1.z; gm.alpha = m1.w;
                 }
                 const float3 wo = make_float3(-rd.x, -rd.y, -rd.z);
                 const float side = (ng.x * wo.x + ng.y * wo.y + ng.z * wo.z) < 0.f ? -1.f : 1.f;
                 const float3 nf = make_float3(side * ng.x, side * ng.y, side * ng.z);  // wo's hemisphere
                 const float4 bt = beta[path];
-                if (FULL && (gm.glossy || infinite || P.has_specular)) {   // Material "plastic" / the infinite light / scenes with specular materials: the general BSDF + light code
+                if (FULL && (gm.glossy || infinite || P.has_specular || gm.kind >= B200RT_MAT_MIRROR)) {   // Material "plastic" / the infinite light / scenes with specular materials: the general BSDF + light code
                     gm.kd[0] = kdr; gm.kd[1] = kdg; gm.kd[2] = kdb;
                     gm.diffuse = kdr > 0.f || kdg > 0.f || kdb > 0.f;
                     uint32_t gx, gy, gs;
@@ -861,8 +861,10 @@ static int render_impl(b200rt_scene *s, const b200rt_render_desc *d, float *film
         {
             const float kf = d->materials[8 * k];
             const uint32_t kind = (uint32_t)kf & 15u;
-            if (!(kf >= 0.f && kf < 32.f) || kf != (float)(uint32_t)kf || kind > B200RT_MAT_GLASS)
-                return set_error(B200RT_EUNSUPPORTED, "material %u: only matte, plastic, mirror and glass are supported", k);
+            if (!(kf >= 0.f && kf < 64.f) || kf != (float)(uint32_t)kf || kind > B200RT_MAT_SUBSTRATE)
+                return set_error(B200RT_EUNSUPPORTED, "material %u: only matte, plastic, mirror, glass, metal and substrate are supported", k);
+            if ((kind == B200RT_MAT_METAL || kind == B200RT_MAT_SUBSTRATE) && !(d->materials[8 * k + 7] > 0.f))
+                return set_error(B200RT_EINVAL, "material %u: roughness must be > 0 (perfectly smooth microfacet lobes are not supported)", k);
             if (kind == B200RT_MAT_GLASS && !(d->materials[8 * k + 7] > 0.f))
                 return set_error(B200RT_EINVAL, "material %u: glass needs its \"index\" of refraction in the roughness slot", k);
             if (kind == B200RT_MAT_MIRROR || kind == B200RT_MAT_GLASS) P.has_specular = 1;
@@ -873,7 +875,8 @@ static int render_impl(b200rt_scene *s, const b200rt_render_desc *d, float *film
             if (d->prim_material[k] >= d->n_materials) return set_error(B200RT_EINVAL, "prim_material[%u] out of range", k);
         std::vector<float> mt(d->materials, d->materials + 8 * (size_t)d->n_materials);
         for (uint32_t k = 0; k < d->n_materials; ++k)
-            if (((uint32_t)mt[8 * k] & 15u) == B200RT_MAT_PLASTIC) {  // TrowbridgeReitzDistribution::RoughnessToAlpha (microfacet.h:123-128), remaproughness true
+            if (const uint32_t kf = (uint32_t)mt[8 * k]; !(kf & B200RT_MAT_NO_REMAP) && ((kf & 15u) == B200RT_MAT_PLASTIC ||
+                                                                                            (kf & 15u) == B200RT_MAT_METAL || (kf & 15u) == B200RT_MAT_SUBSTRATE)) {  // TrowbridgeReitzDistribution::RoughnessToAlpha (microfacet.h:123-128), remaproughness true
                 const float x = std::log(std::max(mt[8 * k + 7], 1e-3f));
                 mt[8 * k + 7] = 1.62142f + 0.819955f * x + 0.1734f * x * x + 0.0171201f * x * x * x + 0.000640711f * x * x * x * x;
             }

@@ -3,6 +3,9 @@
 //   Material "matte"   (materials/matte.cpp:44-60, sigma 0)   : LambertianReflection(Kd)
 //   Material "plastic" (materials/plastic.cpp:44-70)           : LambertianReflection(Kd) + MicrofacetReflection(Ks,
 //        TrowbridgeReitzDistribution(alpha, alpha) with alpha = RoughnessToAlpha(roughness), FresnelDielectric(1.5, 1))
+//   Material "metal"   (materials/metal.cpp:60-82)              : MicrofacetReflection(1, TrowbridgeReitz(alpha, alpha),
+//                                                                FresnelConductor(1, eta, k))
+//   Material "substrate" (materials/substrate.cpp:45-66)        : FresnelBlend(Kd, Ks, TrowbridgeReitz(alpha, alpha))
 //   Material "mirror"  (materials/mirror.cpp:44-56)            : SpecularReflection(Kr, FresnelNoOp)
 //   Material "glass"   (materials/glass.cpp:44-63, roughness 0; PathIntegrator asks for allowMultipleLobes)
 //                                                              : FresnelSpecular(Kr, Kt, 1, index, Radiance)
@@ -124,10 +127,73 @@ __device__ __forceinline__ float glossy_pdf(const float3 wo, const float3 wi, fl
     return tr_pdf(wo, wh, a) / (4.f * (wo.x * wh.x + wo.y * wh.y + wo.z * wh.z));
 }
 
-// BSDF::f and BSDF::Pdf (reflection.cpp): both lobes are reflective, so f = 0 across the surface.
+// FrConductor (reflection.cpp:71-94) for one channel, etaI = 1 (FresnelConductor::Evaluate passes |cos|)
+__device__ __forceinline__ float fr_conductor(float cosThetaI, float eta, float k) {
+    cosThetaI = fminf(fmaxf(cosThetaI, -1.f), 1.f);
+    const float c2 = cosThetaI * cosThetaI, s2 = 1.f - c2;
+    const float eta2 = eta * eta, etak2 = k * k;
+    const float t0 = eta2 - etak2 - s2;
+    const float a2plusb2 = sqrtf(t0 * t0 + 4.f * eta2 * etak2);
+    const float t1 = a2plusb2 + c2;
+    const float a = sqrtf(0.5f * (a2plusb2 + t0));
+    const float t2 = 2.f * cosThetaI * a;
+    const float Rs = (t1 - t2) / (t1 + t2);
+    const float t3 = c2 * a2plusb2 + s2 * s2;
+    const float t4 = t2 * s2;
+    const float Rp = Rs * (t3 - t4) / (t3 + t4);
+    return 0.5f * (Rp + Rs);
+}
+// MicrofacetReflection::f (reflection.cpp:226-236) with R = 1 and FresnelConductor(1, eta = m.kd, k = m.ks)
+__device__ __forceinline__ float3 metal_f(const WfMat &m, const float3 wo, const float3 wi) {
+    const float cosO = fabsf(wo.z), cosI = fabsf(wi.z);
+    float3 wh = make_float3(wi.x + wo.x, wi.y + wo.y, wi.z + wo.z);
+    if (cosI == 0.f || cosO == 0.f) return make_float3(0.f, 0.f, 0.f);
+    if (wh.x == 0.f && wh.y == 0.f && wh.z == 0.f) return make_float3(0.f, 0.f, 0.f);
+    const float il = 1.f / sqrtf(wh.x * wh.x + wh.y * wh.y + wh.z * wh.z);
+    wh.x *= il; wh.y *= il; wh.z *= il;
+    const float c = fabsf(wi.x * wh.x + wi.y * wh.y + wi.z * wh.z);
+    const float G = 1.f / (1.f + tr_lambda(wo, m.alpha) + tr_lambda(wi, m.alpha));
+    const float s = tr_D(wh, m.alpha) * G / (4.f * cosI * cosO);
+    return make_float3(s * fr_conductor(c, m.kd[0], m.ks[0]), s * fr_conductor(c, m.kd[1], m.ks[1]), s * fr_conductor(c, m.kd[2], m.ks[2]));
+}
+// FresnelBlend::f (reflection.cpp:285-298) and ::Pdf (:470-475), Rd = m.kd, Rs = m.ks
+__device__ __forceinline__ float pow5f(float v) { return (v * v) * (v * v) * v; }
+__device__ __forceinline__ float3 blend_f(const WfMat &m, const float3 wo, const float3 wi) {
+    const float dterm = (28.f / (23.f * kBsdfPi)) * (1.f - pow5f(1.f - .5f * fabsf(wi.z))) * (1.f - pow5f(1.f - .5f * fabsf(wo.z)));
+    float3 f = make_float3(m.kd[0] * (1.f - m.ks[0]) * dterm, m.kd[1] * (1.f - m.ks[1]) * dterm, m.kd[2] * (1.f - m.ks[2]) * dterm);
+    float3 wh = make_float3(wi.x + wo.x, wi.y + wo.y, wi.z + wo.z);
+    if (wh.x == 0.f && wh.y == 0.f && wh.z == 0.f) return make_float3(0.f, 0.f, 0.f);
+    const float il = 1.f / sqrtf(wh.x * wh.x + wh.y * wh.y + wh.z * wh.z);
+    wh.x *= il; wh.y *= il; wh.z *= il;
+    const float d = wi.x * wh.x + wi.y * wh.y + wi.z * wh.z;
+    const float s = tr_D(wh, m.alpha) / (4.f * fabsf(d) * fmaxf(fabsf(wi.z), fabsf(wo.z)));
+    const float p = pow5f(1.f - d);
+    f.x += s * (m.ks[0] + p * (1.f - m.ks[0])); f.y += s * (m.ks[1] + p * (1.f - m.ks[1])); f.z += s * (m.ks[2] + p * (1.f - m.ks[2]));
+    return f;
+}
+__device__ __forceinline__ float blend_pdf(const WfMat &m, const float3 wo, const float3 wi) {
+    if (!(wo.z * wi.z > 0.f)) return 0.f;
+    float3 wh = make_float3(wo.x + wi.x, wo.y + wi.y, wo.z + wi.z);
+    const float il = 1.f / sqrtf(wh.x * wh.x + wh.y * wh.y + wh.z * wh.z);
+    wh.x *= il; wh.y *= il; wh.z *= il;
+    return .5f * (fabsf(wi.z) * kBsdfInvPi + tr_pdf(wo, wh, m.alpha) / (4.f * (wo.x * wh.x + wo.y * wh.y + wo.z * wh.z)));
+}
+
+// BSDF::f and BSDF::Pdf (reflection.cpp): every lobe here is reflective, so f = 0 across the surface.
 __device__ __forceinline__ void bsdf_eval(const WfMat &m, const float3 wo, const float3 wi, float3 &f, float &pdf) {
     f = make_float3(0.f, 0.f, 0.f);
     pdf = 0.f;
+    if (m.kind == 4u /* B200RT_MAT_METAL */) {
+        if (wo.z * wi.z > 0.f) f = metal_f(m, wo, wi);
+        pdf = glossy_pdf(wo, wi, m.alpha);
+        return;
+    }
+    if (m.kind == 5u /* B200RT_MAT_SUBSTRATE */) {
+        if (!m.diffuse && !m.glossy) return;   // substrate.cpp:56: no BxDF when Kd and Ks are black
+        if (wo.z * wi.z > 0.f) f = blend_f(m, wo, wi);
+        pdf = blend_pdf(m, wo, wi);
+        return;
+    }
     const int n = (m.diffuse ? 1 : 0) + (m.glossy ? 1 : 0);
     if (n == 0) return;
     const bool same = wo.z * wi.z > 0.f;
@@ -143,12 +209,22 @@ __device__ __forceinline__ void bsdf_eval(const WfMat &m, const float3 wo, const
 
 // BSDF::Sample_f (reflection.cpp): false = the sample carries nothing (pdf == 0 or f black).
 __device__ __forceinline__ bool bsdf_sample(const WfMat &m, const float3 wo, float u0, float u1, float3 &wi, float3 &f, float &pdf) {
-    const int n = (m.diffuse ? 1 : 0) + (m.glossy ? 1 : 0);
-    if (n == 0) return false;
-    int comp = (int)floorf(u0 * n);
-    if (comp > n - 1) comp = n - 1;
-    u0 = fminf(u0 * n - comp, kOneMinusEpsilon);
-    const bool pickGlossy = m.glossy && (!m.diffuse || comp == 1);
+    int n = (m.diffuse ? 1 : 0) + (m.glossy ? 1 : 0);
+    bool pickGlossy;
+    if (m.kind == 4u) { n = 1; pickGlossy = true; }   // metal: the one microfacet lobe
+    else if (m.kind == 5u) {
+        // FresnelBlend::Sample_f (reflection.cpp:450-468): u0 < .5 the cosine lobe, else the microfacet half vector
+        if (n == 0 || wo.z == 0.f) return false;
+        n = 1;
+        pickGlossy = !(u0 < .5f);
+        u0 = pickGlossy ? fminf(2.f * (u0 - .5f), kOneMinusEpsilon) : fminf(2.f * u0, kOneMinusEpsilon);
+    } else {
+        if (n == 0) return false;
+        int comp = (int)floorf(u0 * n);
+        if (comp > n - 1) comp = n - 1;
+        u0 = fminf(u0 * n - comp, kOneMinusEpsilon);
+        pickGlossy = m.glossy && (!m.diffuse || comp == 1);
+    }
     if (!pickGlossy) {
         // BxDF::Sample_f: CosineSampleHemisphere via ConcentricSampleDisk (sampling.cpp)
         const float a0 = 2.f * u0 - 1.f, a1 = 2.f * u1 - 1.f;
@@ -160,14 +236,14 @@ __device__ __forceinline__ bool bsdf_sample(const WfMat &m, const float3 wo, flo
             dx = r * cosf(th); dy = r * sinf(th);
         }
         wi = make_float3(dx, dy, sqrtf(fmaxf(0.f, 1.f - dx * dx - dy * dy)));
-        if (wi.z * kBsdfInvPi == 0.f) return false;
+        if (m.kind != 5u && wi.z * kBsdfInvPi == 0.f) return false;
     } else {
         if (wo.z == 0.f) return false;
         const float3 wh = tr_sample_wh(wo, u0, u1, m.alpha);
         const float d = wo.x * wh.x + wo.y * wh.y + wo.z * wh.z;
         wi = make_float3(-wo.x + 2.f * d * wh.x, -wo.y + 2.f * d * wh.y, -wo.z + 2.f * d * wh.z);   // Reflect(wo, wh)
         if (!(wo.z * wi.z > 0.f)) return false;
-        if (tr_pdf(wo, wh, m.alpha) / (4.f * d) == 0.f) return false;
+        if (m.kind != 5u && tr_pdf(wo, wh, m.alpha) / (4.f * d) == 0.f) return false;
     }
     bsdf_eval(m, wo, wi, f, pdf);
     return pdf > 0.f && (f.x > 0.f || f.y > 0.f || f.z > 0.f);

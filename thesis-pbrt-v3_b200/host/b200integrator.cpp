@@ -26,7 +26,8 @@
 // The point-light / matte case reads the scene through pbrt's public interfaces only.  The sphere area light and
 // "plastic" need three things that have no accessor (inside the reference tree: `friend class B200WavefrontIntegrator;`):
 // GeometricPrimitive::shape + Sphere::radius (the emitter's geometry) and PlasticMaterial::Kd/Ks/roughness (likewise
-// MirrorMaterial::Kr and GlassMaterial::Kr/Kt/index/uRoughness/vRoughness).
+// MirrorMaterial::Kr, GlassMaterial::Kr/Kt/index/uRoughness/vRoughness, MetalMaterial::eta/k/roughness and
+// SubstrateMaterial::Kd/Ks/nu/nv).
 #define private public
 #define protected public
 #include "core/primitive.h"
@@ -34,6 +35,8 @@
 #include "materials/plastic.h"
 #include "materials/mirror.h"
 #include "materials/glass.h"
+#include "materials/metal.h"
+#include "materials/substrate.h"
 #include "core/film.h"   // Film::pixels / Pixel::stats for "bool generalstats" (no accessor either)
 #undef private
 #undef protected
@@ -239,13 +242,31 @@ void B200WavefrontIntegrator::Render(const Scene &scene) {
                 if (seen.size() >= 256) { Error("b200wavefront: more than 256 materials"); return; }
                 float rec[8] = {0, 0, 0, 0, 0, 0, 0, 0};
                 if (const PlasticMaterial *pm = dynamic_cast<const PlasticMaterial *>(m)) {
-                    if (pm->bumpMap || !pm->remapRoughness) { Error("b200wavefront: plastic with bump map / unremapped roughness is not supported"); return; }
+                    if (pm->bumpMap) { Error("b200wavefront: plastic with a bump map is not supported"); return; }
                     Float kd[3], ks[3];
                     Spectrum(pm->Kd->Evaluate(si).Clamp()).ToRGB(kd);
                     Spectrum(pm->Ks->Evaluate(si).Clamp()).ToRGB(ks);
-                    rec[0] = (float)B200RT_MAT_PLASTIC;
+                    rec[0] = (float)(B200RT_MAT_PLASTIC + (pm->remapRoughness ? 0 : B200RT_MAT_NO_REMAP));
                     for (int c = 0; c < 3; ++c) { rec[1 + c] = kd[c]; rec[4 + c] = ks[c]; }
                     rec[7] = pm->roughness->Evaluate(si);
+                } else if (const MetalMaterial *me = dynamic_cast<const MetalMaterial *>(m)) {
+                    const Float ur = me->uRoughness ? me->uRoughness->Evaluate(si) : me->roughness->Evaluate(si);
+                    const Float vr = me->vRoughness ? me->vRoughness->Evaluate(si) : me->roughness->Evaluate(si);
+                    if (me->bumpMap || ur != vr) { Error("b200wavefront: only isotropic metal without a bump map is supported"); return; }
+                    Float e[3], kk[3];
+                    me->eta->Evaluate(si).ToRGB(e);
+                    me->k->Evaluate(si).ToRGB(kk);
+                    rec[0] = (float)(B200RT_MAT_METAL + (me->remapRoughness ? 0 : B200RT_MAT_NO_REMAP));
+                    for (int c = 0; c < 3; ++c) { rec[1 + c] = e[c]; rec[4 + c] = kk[c]; }
+                    rec[7] = ur;
+                } else if (const SubstrateMaterial *sm = dynamic_cast<const SubstrateMaterial *>(m)) {
+                    if (sm->bumpMap || sm->nu->Evaluate(si) != sm->nv->Evaluate(si)) { Error("b200wavefront: only isotropic substrate without a bump map is supported"); return; }
+                    Float kd[3], ks[3];
+                    Spectrum(sm->Kd->Evaluate(si).Clamp()).ToRGB(kd);
+                    Spectrum(sm->Ks->Evaluate(si).Clamp()).ToRGB(ks);
+                    rec[0] = (float)(B200RT_MAT_SUBSTRATE + (sm->remapRoughness ? 0 : B200RT_MAT_NO_REMAP));
+                    for (int c = 0; c < 3; ++c) { rec[1 + c] = kd[c]; rec[4 + c] = ks[c]; }
+                    rec[7] = sm->nu->Evaluate(si);
                 } else if (const MirrorMaterial *mm = dynamic_cast<const MirrorMaterial *>(m)) {
                     if (mm->bumpMap) { Error("b200wavefront: mirror with a bump map is not supported"); return; }
                     Float kr[3];
@@ -265,7 +286,7 @@ void B200WavefrontIntegrator::Render(const Scene &scene) {
                     rec[7] = gm->index->Evaluate(si);
                 } else {
                     Float kd[3];
-                    if (!lambertianKd(m, kd)) { Error("b200wavefront: only \"matte\", \"plastic\", \"mirror\" and smooth \"glass\" materials are supported"); return; }
+                    if (!lambertianKd(m, kd)) { Error("b200wavefront: only \"matte\", \"plastic\", \"mirror\", smooth \"glass\", \"metal\" and \"substrate\" materials are supported"); return; }
                     for (int c = 0; c < 3; ++c) rec[1 + c] = kd[c];
                 }
                 it = seen.emplace(std::make_pair(m, flip), (int)seen.size()).first;
