@@ -97,7 +97,7 @@ def main():
             np.save(args.out, rgb)
         print(json.dumps({
             "workload": "scenes/living-room (reference geometry, 143163 triangles, %s), %dx%d @ %d spp, path maxdepth %d, "
-                        "constant infinite light + MIS, substituted materials" % (args.accel, args.xres, args.yres, args.spp, args.maxdepth),
+                        "constant infinite light + MIS, the file's material kinds (matte, substrate, metal, glass, mirror) with constant textures" % (args.accel, args.xres, args.yres, args.spp, args.maxdepth),
             "n_gpus": world, "ms_per_frame": ms, "rays_per_frame": rays, "mrays_per_s": rays / ms / 1e3,
             "camera_rays": float(tsum[6]) / args.frames, "closest_rays": float(tsum[1]) / args.frames,
             "shadow_rays": float(tsum[2]) / args.frames, "mis_rays": float(tsum[5]) / args.frames,
