@@ -84,7 +84,7 @@ typedef struct {
 } b200rt_render_desc;
 enum { B200RT_LIGHT_POINT = 0, B200RT_LIGHT_SPHERE = 1, B200RT_LIGHT_DISTANT = 2, B200RT_LIGHT_INFINITE = 3 };
 enum {
-    B200RT_MAT_MATTE = 0,
+    B200RT_MAT_MATTE = 0,   /* materials/matte.cpp:44-62; record = (kind, Kd.rgb, sigma, -, -, -): sigma (degrees) > 0 = OrenNayar */
     B200RT_MAT_PLASTIC = 1, /* materials/plastic.cpp: Kd + Ks microfacet lobe, roughness remapped */
     /* ---- ABI v7: the perfectly specular materials (path.cpp's specularBounce / etaScale bookkeeping comes with them) ---- */
     B200RT_MAT_MIRROR = 2,  /* materials/mirror.cpp:44-56: SpecularReflection(Kr, FresnelNoOp); record = (kind, Kr.rgb, -, -, -, -) */

@@ -203,7 +203,8 @@ extern "C" int ref_render(ref_scene *s, const char *accel_kind, const float *cam
                     auto zero = std::make_shared<ConstantTexture<Float>>(0.f);
                     auto index = std::make_shared<ConstantTexture<Float>>(k[7]);
                     mm = std::make_shared<GlassMaterial>(tex, texT, zero, zero, index, nullptr, true);
-                } else mm = std::make_shared<MatteMaterial>(tex, sigma, nullptr);
+                } else   // Material "matte" "rgb Kd" "float sigma" (sigma > 0: Oren-Nayar, materials/matte.cpp:55-61)
+                    mm = std::make_shared<MatteMaterial>(tex, std::make_shared<ConstantTexture<Float>>(k[4]), nullptr);
                 it = byKd.emplace(k, mm).first;
             }
             m = it->second;

@@ -17,8 +17,8 @@ sc = scenes.killeroo_simple(xres=res, yres=res)
 verts, prim_kind, rows, pm, mats = scenes.with_sphere_light(sc, plastic=True)
 if case == "killeroo_glass":
     mats = scenes.specular_materials(sc)
-if case == "killeroo_metal":
-    mats = scenes.metal_materials(sc)
+if case in ("killeroo_metal", "killeroo_oren"):
+    mats = scenes.metal_materials(sc, oren_nayar=case == "killeroo_oren")
 acc = gpu.B200Accel(gpu.build_bvh(verts), verts, prim_kind=prim_kind, spheres=rows)
 sl = sc["sphere_light"]
 ref = g[case + "_rgb"].astype(np.float64)

@@ -29,12 +29,16 @@ CASES = {
     "killeroo_glass": dict(scene="killeroo_simple", res=128, spp=256, maxdepth=8, I=(2000.0,) * 3, kd=(.5, .5, .5), area=True, specular=True),
     # ... and with scenes/living-room's microfacet materials: substrate ground, metal (conductor Fresnel) and substrate killeroos
     "killeroo_metal": dict(scene="killeroo_simple", res=128, spp=256, maxdepth=5, I=(2000.0,) * 3, kd=(.5, .5, .5), area=True, metal=True),
+    # ... the same with an Oren-Nayar ground (Material "matte" "float sigma" [40])
+    "killeroo_oren": dict(scene="killeroo_simple", res=128, spp=256, maxdepth=5, I=(2000.0,) * 3, kd=(.5, .5, .5), area=True, metal="oren"),
     # BASELINE config 4's scene as written (scenes/killeroo-feet: LightSource "distant" from the eye towards the look-at
     # point, Material "plastic" Kd (.4 .5 .4) Ks .3 roughness .15, path maxdepth 5), whole frame instead of the crop window
     "feet": dict(scene="killeroo_feet", res=192, spp=256, maxdepth=5, I=(1.0,) * 3, kd=(.5, .5, .5), distant=True),
     # ... and through its Film "cropwindow" [.3 .5 .4 .8] (the feet): 640^2 frame -> 128 x 256 pixel window
     "feet_crop": dict(scene="killeroo_feet", res=640, spp=64, maxdepth=5, I=(1.0,) * 3, kd=(.5, .5, .5), distant=True, crop=True),
     "sponza": dict(scene="sponza_standin", res=96, spp=256, maxdepth=5, I=(1.0,) * 3, kd=(.5, .5, .5)),
+    # BASELINE config 3: the museum stand-in as scenes/test_museum_local_k renders it — Accelerator "kdtree", path maxdepth 1
+    "museum": dict(scene="museum_standin", res=96, spp=256, maxdepth=1, I=(1.0,) * 3, kd=(.5, .5, .5), accel="kdtree"),
 }
 
 
@@ -45,6 +49,8 @@ def lookat_of(name):
         eye = scenes._xform(r, np.array([[400.0, 20, 30]]))[0]
         look = scenes._xform(r, np.array([[0.0, 63, -110]]))[0]
         return eye, look, (0, 0, 1), 39.0
+    if name == "museum_standin":   # scenes/museum:1-3: LookAt -0.4 0.06 0.05  0.2 0.1 -0.05  0 1 0 ; Rotate 180 0 1 0 ; fov 60
+        return (0.4, 0.06, -0.05), (-0.2, 0.1, 0.05), (0, 1, 0), 60.0
     return (-0.7, .45, .05), (0, .25, 0), (0, 1, 0), 42.0
 
 
@@ -65,7 +71,7 @@ def main():
             if c.get("specular"):
                 mats = scenes.specular_materials(sc)
             if c.get("metal"):
-                mats = scenes.metal_materials(sc)
+                mats = scenes.metal_materials(sc, oren_nayar=c["metal"] == "oren")
             extra = dict(prim_mat=np.concatenate([mats[sc["prim_material"]], np.zeros((1, 8), np.float32)]), emitter_L=sl["L"])
         if c.get("distant"):
             extra = dict(prim_mat=np.repeat(sc["materials"], len(tv), 0), distant=(sc["light_from"], sc["light_to"]))
@@ -74,7 +80,7 @@ def main():
             extra["cropwindow"] = sc["cropwindow"]
         S = rb.RefScene(tv.reshape(-1, 3), np.arange(3 * len(tv), dtype=np.int32).reshape(-1, 3), spheres=spheres)
         eye, look, up, fov = lookat_of(c["scene"])
-        img, nc, ns, heat = rb.render(S, "bvh", eye, look, up, fov, c["res"], c["res"], c["spp"], c["maxdepth"], sc["light"],
+        img, nc, ns, heat = rb.render(S, c.get("accel", "bvh"), eye, look, up, fov, c["res"], c["res"], c["spp"], c["maxdepth"], sc["light"],
                                       c["I"], c["kd"], sampler="random", n_threads=0, heat=True, **extra)
         if key == "killeroo":   # the thesis's per-pixel traversal statistics for the same frame (BVH)
             out[key + "_heat"] = heat

@@ -162,7 +162,7 @@ extern "C" int plugin_render(ref_scene *s, const char *tree, const float *cam, i
                     mm = std::make_shared<GlassMaterial>(tex, std::make_shared<ConstantTexture<Spectrum>>(Spectrum::FromRGB(cs)),
                                                          std::make_shared<ConstantTexture<Float>>(0.f), std::make_shared<ConstantTexture<Float>>(0.f),
                                                          std::make_shared<ConstantTexture<Float>>(k[7]), nullptr, true);
-                else mm = std::make_shared<MatteMaterial>(tex, sigma, nullptr);
+                else mm = std::make_shared<MatteMaterial>(tex, std::make_shared<ConstantTexture<Float>>(k[4]), nullptr);
                 it = byRec.emplace(k, mm).first;
             }
             m = it->second;

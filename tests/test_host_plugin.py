@@ -145,7 +145,7 @@ def test_plugin_with_this_repos_builders(host, gpu, tree):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("case", ["killeroo", "killeroo_full", "killeroo_glass", "killeroo_metal", "feet", "feet_crop"])
+@pytest.mark.parametrize("case", ["killeroo", "killeroo_full", "killeroo_glass", "killeroo_metal", "killeroo_oren", "feet", "feet_crop"])
 def test_cpp_wavefront_integrator_matches_the_references_render(host, gpu, case):
     """`Integrator "b200wavefront"` (host/b200integrator.cpp) over `Accelerator "b200"`, set up exactly like the
     reference's own render of tests/golden/ref_render.npz (PerspectiveCamera from LookAt/fov, Film + BoxFilter,
@@ -165,7 +165,8 @@ def test_cpp_wavefront_integrator_matches_the_references_render(host, gpu, case)
                                 C.POINTER(C.c_uint64), C.c_void_p, C.c_void_p]
     g = load_golden("ref_render.npz")
     glass = case == "killeroo_glass"   # MirrorMaterial / GlassMaterial objects read by the C++ integrator
-    metal = case == "killeroo_metal"   # MetalMaterial / SubstrateMaterial objects
+    oren = case == "killeroo_oren"     # ... with MatteMaterial sigma 40 (Oren-Nayar) on the ground
+    metal = case == "killeroo_metal" or oren   # MetalMaterial / SubstrateMaterial objects
     full = case == "killeroo_full" or glass or metal
     res, spp, maxdepth = (int(x) for x in g[case + "_params"])
     feet = case.startswith("feet")
@@ -183,7 +184,7 @@ def test_cpp_wavefront_integrator_matches_the_references_render(host, gpu, case)
     I, kd = g[case + "_I"].astype(np.float32), g[case + "_kd"].astype(np.float32)
     prim_mat = emitter = None
     if full:
-        mt = scenes.specular_materials(sc) if glass else scenes.metal_materials(sc) if metal else sc["materials"]
+        mt = scenes.specular_materials(sc) if glass else scenes.metal_materials(sc, oren_nayar=oren) if metal else sc["materials"]
         prim_mat = np.ascontiguousarray(np.concatenate([mt[sc["prim_material"]], np.zeros((1, 8), np.float32)]))
         emitter = np.ascontiguousarray(sl["L"], np.float32)
     L.ref_render_set_distant.argtypes = [C.c_void_p]
@@ -219,7 +220,7 @@ def test_cpp_wavefront_integrator_matches_the_references_render(host, gpu, case)
         if glass:
             mats = scenes.specular_materials(sc)
         if metal:
-            mats = scenes.metal_materials(sc)
+            mats = scenes.metal_materials(sc, oren_nayar=oren)
         acc = gpu.B200Accel(gpu.build_bvh(verts), verts, prim_kind=prim_kind, spheres=rows)
         integ = gpu.WavefrontPathIntegrator(sc["camera"], spp=spp, maxdepth=maxdepth, light_pos=sl["center"], light_I=sl["L"], seed=9,
                                             sphere_light=(sl["radius"], len(verts) - 1), materials=mats, prim_material=pm)
@@ -240,7 +241,7 @@ def test_cpp_wavefront_integrator_matches_the_references_render(host, gpu, case)
     for _ in range(2):
         near = near | np.roll(near, 1, 0) | np.roll(near, -1, 0) | np.roll(near, 1, 1) | np.roll(near, -1, 1)
     img, ref, py = (np.where(near[..., None], 0, a) for a in (img, ref, py))
-    if glass:   # caustic fireflies: raw mean within 3 %, the tight bars on the images clamped at 1 (see tests/test_gpu_wavefront.py)
+    if glass or metal:   # caustic fireflies: raw mean within 3 %, the tight bars on the images clamped at 1 (see tests/test_gpu_wavefront.py)
         assert abs(img.mean() / ref.mean() - 1) < 0.03
         img, ref, py = (np.minimum(a, 1.0) for a in (img, ref, py))
     assert abs(img.mean() / ref.mean() - 1) < 0.01

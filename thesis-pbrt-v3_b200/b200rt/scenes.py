@@ -207,13 +207,15 @@ def specular_materials(sc):
     return m
 
 
-def metal_materials(sc):
+def metal_materials(sc, oren_nayar=False):
     """scenes/killeroo-simple with the microfacet materials scenes/living-room uses (scene.pbrt:14-21): ground =
     `Material "substrate"` Kd (.5 .5 .8) Ks .04 roughness .1 (remapped); first killeroo = `Material "metal"` with the
     file's BrushedStainlessSteel eta / k, roughness .1, "remaproughness" false (kind + 32); second = the file's
     "Paneling" substrate (Kd .8, Ks .04, roughness .2, "remaproughness" false)."""
     m = sc["materials"].copy()
     m[0] = [5, .5, .5, .8, .04, .04, .04, .1]
+    if oren_nayar:   # ground = `Material "matte" "float sigma" [40]`: the Oren-Nayar lobe (living-room's PlantPot has sigma 1)
+        m[0] = [0, .5, .5, .8, 40, 0, 0, 0]
     m[1] = [4 + 32, 1.657460, 0.880369, 0.521229, 9.223869, 6.269523, 4.837001, .1]
     m[2] = [5 + 32, .8, .8, .8, .04, .04, .04, .2]
     return m
@@ -272,8 +274,7 @@ def living_room(xres=1280, yres=720):
     u = v roughness, "remaproughness" false); "metal" with the file's eta / k and roughness .02 unremapped; "glass"
     index 1.5 (Kr = Kt = 1, glass.cpp's defaults); "mirror" Kr .9 (mirror.cpp's default).  What stays SUBSTITUTED,
     identically on the reference side of the parity test: texture-mapped Kd -> constant .5 (image textures are out of
-    scope and half the files are absent), "uber" Leaves (Ks 0, opacity texture) -> matte .5, PlantPot's Oren-Nayar sigma 1
-    -> sigma 0, and the PLY files' vertex normals are not used (geometric normals on both sides; for glass the outside
+    scope and half the files are absent), "uber" Leaves (Ks 0, opacity texture) -> matte .5, and the PLY files' vertex normals are not used (geometric normals on both sides; for glass the outside
     is the side the triangle's winding normal points to).  `legacy_materials` keeps the earlier matte + plastic table
     (the numbers of profiles/r01_living_room_*.json).  The TRAVERSAL workload (tree, rays, hit parity) is the reference
     scene's as shipped."""
@@ -293,6 +294,8 @@ def living_room(xres=1280, yres=720):
             legacy[i] = [1, c[0], c[1], c[2], .04, .04, .04, rough[name]]
         elif k == "matte":
             mats[i] = legacy[i] = [0, c[0], c[1], c[2], 0, 0, 0, 0]
+            if name == "PlantPot":   # scene.pbrt:26 "float sigma" [1]: Oren-Nayar
+                mats[i] = [0, c[0], c[1], c[2], 1, 0, 0, 0]
         elif k == "metal":     # scene.pbrt:21 BrushedStainlessSteel
             mats[i] = [4 + 32, 1.657460, 0.880369, 0.521229, 9.223869, 6.269523, 4.837001, .02]
         elif k == "glass":     # scene.pbrt:25
@@ -405,6 +408,105 @@ def sponza_standin(seed=7, detail=0.885, xres=700, yres=700):
     cam = look_at_camera((-0.7, 0.45, 0.05), (0, 0.25, 0), (0, 1, 0), 42, xres, yres)
     return dict(name="sponza-standin", tri_verts=tv, camera=cam, light=np.array([0, .5, 0], np.float32),
                 note="PROCEDURAL STAND-IN for scenes/sponza (geometry absent from the reference tree), seed=%d detail=%g, %d triangles"
+                     % (seed, detail, len(tv)))
+
+
+def museum_standin(seed=11, detail=1.45, xres=700, yres=700):
+    """Procedural exhibition hall standing in for the thesis's museum scene (scenes/museum + its `_k` kd-tree variant
+    scenes/test_museum_local_k: the geometry/museum/*.pbrt parts — bone, brushedmetals, floor, glass, painted, stone,
+    wood... — are absent from the reference tree).  A hall with a relief floor, panelled walls, roof beams, pedestals
+    carrying lathe-turned and blobby exhibits, display cases, paintings, benches and a rib-cage skeleton down the
+    middle; ~250 k triangles at the default detail.  Camera, light and integrator settings are the template's
+    (scenes/museum:1-3,12,15): `LookAt -0.4 0.06 0.05  0.2 0.1 -0.05  0 1 0` followed by `Rotate 180 0 1 0` (so the
+    world-space eye is (0.4, 0.06, -0.05) looking at (-0.2, 0.1, 0.05)), fov 60, point light at (0, .5, 0),
+    path maxdepth 1, 64 spp, 700x700."""
+    rng = np.random.default_rng(seed)
+    k = float(np.sqrt(detail))
+    n = lambda x: max(2, int(round(x * k)))
+    parts = []
+    X0, X1, Z0, Z1, H = -0.7, 0.7, -0.4, 0.4, 0.62
+    def floor(u, v):
+        x, z = X0 + u * (X1 - X0), Z0 + v * (Z1 - Z0)
+        y = 0.0015 * (np.abs(np.sin(24 * np.pi * x)) < 0.06) + 0.0015 * (np.abs(np.sin(24 * np.pi * z)) < 0.06)
+        return np.stack([x, y, z], 1)
+    parts.append(_surface(floor, n(200), n(120)))
+    def wall_x(zpos, sgn):   # long walls with vertical panels
+        def f(u, v):
+            x, y = X0 + u * (X1 - X0), v * H
+            z = zpos + sgn * 0.004 * (np.sin(30 * np.pi * u) > 0.8) + sgn * 0.006 * (v < 0.12)
+            return np.stack([x, y, z], 1)
+        return f
+    parts.append(_surface(wall_x(Z0, 1), n(160), n(60)))
+    parts.append(_surface(wall_x(Z1, -1), n(160), n(60)))
+    for xpos in (X0, X1):
+        def f(u, v, xpos=xpos):
+            z, y = Z0 + u * (Z1 - Z0), v * H
+            return np.stack([np.full_like(z, xpos), y, z], 1)
+        parts.append(_surface(f, n(70), n(50)))
+    parts.append(_box((X0, H, Z0), (X1, H + 0.02, Z1), n(20)))
+    for x in np.linspace(X0 + 0.08, X1 - 0.08, 10):   # roof beams
+        parts.append(_box((x - 0.01, H - 0.04, Z0), (x + 0.01, H, Z1), n(4)))
+    # pedestals with exhibits along both sides
+    def vase(v):
+        return 0.012 + 0.022 * np.sin(np.pi * v) ** 1.5 + 0.006 * (v > 0.92), 0.09 * v
+    def urn(v):
+        return 0.02 * (1 + 0.6 * np.sin(2.5 * np.pi * v) * (1 - v)), 0.07 * v
+    def blob(cx, cy, cz, r, a, b):
+        def f(u, v):
+            th, ph = np.pi * v, 2 * np.pi * u
+            rr = r * (1 + 0.2 * np.sin(a * ph) * np.sin(b * th))
+            return np.stack([cx + rr * np.sin(th) * np.cos(ph), cy + rr * np.cos(th), cz + rr * np.sin(th) * np.sin(ph)], 1)
+        return _surface(f, n(44), n(32))
+    px = np.linspace(X0 + 0.15, X1 - 0.15, 7)
+    for i, x in enumerate(px):
+        for z in (-0.27, 0.27):
+            parts.append(_box((x - 0.035, 0, z - 0.035), (x + 0.035, 0.11, z + 0.035), n(6)))
+            kind = int(rng.integers(0, 3))
+            if kind == 0:
+                parts.append(_lathe(vase, x, z, 0.11, n(36), n(28)))
+            elif kind == 1:
+                parts.append(_lathe(urn, x, z, 0.11, n(36), n(28)))
+            else:
+                parts.append(blob(x, 0.15, z, 0.035, int(rng.integers(3, 7)), int(rng.integers(2, 6))))
+            if i % 2 == 0:   # display case around it (thin posts + top)
+                for dx in (-0.045, 0.045):
+                    for dz in (-0.045, 0.045):
+                        parts.append(_box((x + dx - 0.003, 0.11, z + dz - 0.003), (x + dx + 0.003, 0.24, z + dz + 0.003), n(2)))
+                parts.append(_box((x - 0.048, 0.24, z - 0.048), (x + 0.048, 0.245, z + 0.048), n(6)))
+    # paintings on the long walls
+    for x in np.linspace(X0 + 0.2, X1 - 0.2, 6):
+        for z, sgn in ((Z0, 1), (Z1, -1)):
+            w, h = 0.05 + 0.03 * rng.random(), 0.04 + 0.03 * rng.random()
+            z0, z1 = sorted((z + sgn * 0.006, z + sgn * 0.014))
+            parts.append(_box((x - w, 0.30 - h, z0), (x + w, 0.30 + h, z1), n(8)))
+    # benches down the middle
+    for x in (-0.35, 0.35):
+        parts.append(_box((x - 0.08, 0.035, -0.03), (x + 0.08, 0.045, 0.03), n(8)))
+        for dx in (-0.07, 0.07):
+            parts.append(_box((x + dx - 0.005, 0, -0.025), (x + dx + 0.005, 0.035, 0.025), n(2)))
+    # the skeleton: a spine with rib hoops, skull blob and tail
+    def spine(u, v):
+        t = -0.22 + 0.44 * u
+        y = 0.17 + 0.03 * np.sin(np.pi * u)
+        a = 2 * np.pi * v
+        return np.stack([t, y + 0.006 * np.sin(a), 0.006 * np.cos(a)], 1)
+    parts.append(_surface(spine, n(120), n(10)))
+    for t in np.linspace(-0.12, 0.1, 14):
+        R = 0.045 * (1 - 2.5 * (t + 0.01) ** 2 / 0.05)
+        yc = 0.17 + 0.03 * np.sin(np.pi * (t + 0.22) / 0.44) - R * 0.85
+        def rib(u, v, t=t, R=R, yc=yc):
+            a, b = (0.15 + 1.7 * u) * np.pi + np.pi / 2 + 0.15 * np.pi, 2 * np.pi * v
+            rr = R + 0.003 * np.cos(b)
+            return np.stack([t + 0.003 * np.sin(b), yc + rr * np.sin(a) * 1.1, rr * np.cos(a)], 1)
+        parts.append(_surface(rib, n(40), n(8)))
+    parts.append(blob(-0.26, 0.2, 0.0, 0.03, 2, 3))
+    for lx in (-0.1, 0.08):   # leg posts carrying it
+        for lz in (-0.03, 0.03):
+            parts.append(_lathe(lambda v: (0.005 + 0.002 * np.sin(6 * np.pi * v), 0.15 * v), lx, lz, 0.0, n(12), n(24)))
+    tv = np.concatenate(parts).astype(np.float32) + np.float32(0)
+    cam = look_at_camera((0.4, 0.06, -0.05), (-0.2, 0.1, 0.05), (0, 1, 0), 60, xres, yres)
+    return dict(name="museum-standin", tri_verts=tv, camera=cam, light=np.array([0, .5, 0], np.float32), maxdepth=1, spp=64,
+                note="PROCEDURAL STAND-IN for scenes/museum (geometry absent from the reference tree), seed=%d detail=%g, %d triangles"
                      % (seed, detail, len(tv)))
 
 

@@ -421,7 +421,7 @@ __global__ void k_shade(const __grid_constant__ WfParams P, uint32_t depth, uint
                 float kdr = P.kd[0], kdg = P.kd[1], kdb = P.kd[2];
                 WfMat gm;
                 gm.glossy = false;
-                gm.kind = B200RT_MAT_MATTE; gm.flip = false;
+                gm.kind = B200RT_MAT_MATTE; gm.flip = false; gm.alpha = 0.f;
                 if (FULL && P.mats) {
                     const uint32_t mi = __ldg(P.primMat + h.prim);
                     const float4 m0 = __ldg(P.mats + 2 * (size_t)mi), m1 = __ldg(P.mats + 2 * (size_t)mi + 1);
@@ -430,12 +430,13 @@ __global__ void k_shade(const __grid_constant__ WfParams P, uint32_t depth, uint
                     gm.kind = kf & 15u; gm.flip = (kf & B200RT_MAT_REVERSE_ORIENTATION) != 0;
                     gm.glossy = (gm.kind == B200RT_MAT_PLASTIC || gm.kind == B200RT_MAT_SUBSTRATE) && (m1.x > 0.f || m1.y > 0.f || m1.z > 0.f);
                     gm.ks[0] = m1.x; gm.ks[1] = m1.y; gm.ks[2] = m1.z; gm.alpha = m1.w;
+                    if (gm.kind == B200RT_MAT_MATTE) gm.alpha = fminf(fmaxf(m1.x, 0.f), 90.f);   // "sigma" (matte.cpp:55), > 0 = Oren-Nayar
                 }
                 const float3 wo = make_float3(-rd.x, -rd.y, -rd.z);
                 const float side = (ng.x * wo.x + ng.y * wo.y + ng.z * wo.z) < 0.f ? -1.f : 1.f;
                 const float3 nf = make_float3(side * ng.x, side * ng.y, side * ng.z);  // wo's hemisphere
                 const float4 bt = beta[path];
-                if (FULL && (gm.glossy || infinite || P.has_specular || gm.kind >= B200RT_MAT_MIRROR)) {   // Material "plastic" / the infinite light / scenes with specular materials: the general BSDF + light code
+                if (FULL && (gm.glossy || infinite || P.has_specular || gm.kind >= B200RT_MAT_MIRROR || gm.alpha > 0.f)) {   // Material "plastic" / the infinite light / scenes with specular materials: the general BSDF + light code
                     gm.kd[0] = kdr; gm.kd[1] = kdg; gm.kd[2] = kdb;
                     gm.diffuse = kdr > 0.f || kdg > 0.f || kdb > 0.f;
                     uint32_t gx, gy, gs;

@@ -1,6 +1,6 @@
 // BSDFs of the wavefront shade stage, in the local shading frame (z = the normal on wo's side, so wo.z >= 0).
 //
-//   Material "matte"   (materials/matte.cpp:44-60, sigma 0)   : LambertianReflection(Kd)
+//   Material "matte"   (materials/matte.cpp:44-62)            : LambertianReflection(Kd), or OrenNayar(Kd, sigma) for sigma > 0
 //   Material "plastic" (materials/plastic.cpp:44-70)           : LambertianReflection(Kd) + MicrofacetReflection(Ks,
 //        TrowbridgeReitzDistribution(alpha, alpha) with alpha = RoughnessToAlpha(roughness), FresnelDielectric(1.5, 1))
 //   Material "metal"   (materials/metal.cpp:60-82)              : MicrofacetReflection(1, TrowbridgeReitz(alpha, alpha),
@@ -19,7 +19,7 @@ namespace b200rt {
 
 struct WfMat {
     float kd[3], ks[3];
-    float alpha;     // TrowbridgeReitz alpha (already remapped from "roughness" on the host)
+    float alpha;     // TrowbridgeReitz alpha (already remapped from "roughness" on the host); matte: "sigma" in degrees
     bool diffuse;    // !Kd.IsBlack()
     bool glossy;     // !Ks.IsBlack()
     // perfectly specular materials: kd = Kr, ks = Kt, alpha = "index"; `flip` = reverseOrientation ^ transformSwapsHandedness
@@ -198,7 +198,26 @@ __device__ __forceinline__ void bsdf_eval(const WfMat &m, const float3 wo, const
     if (n == 0) return;
     const bool same = wo.z * wi.z > 0.f;
     if (m.diffuse) {
-        if (same) { f.x += m.kd[0] * kBsdfInvPi; f.y += m.kd[1] * kBsdfInvPi; f.z += m.kd[2] * kBsdfInvPi; pdf += fabsf(wi.z) * kBsdfInvPi; }
+        if (same) {
+            float on = 1.f;
+            if (m.kind == 0u && m.alpha > 0.f) {   // OrenNayar (reflection.h:414-420, reflection.cpp:197-219); sampled like any BxDF (cosine)
+                const float sigma = (kBsdfPi / 180.f) * m.alpha, sigma2 = sigma * sigma;
+                const float A = 1.f - (sigma2 / (2.f * (sigma2 + 0.33f))), B = 0.45f * sigma2 / (sigma2 + 0.09f);
+                const float sinI = sqrtf(fmaxf(0.f, 1.f - wi.z * wi.z)), sinO = sqrtf(fmaxf(0.f, 1.f - wo.z * wo.z));
+                float maxCos = 0.f;
+                if (sinI > 1e-4f && sinO > 1e-4f) {
+                    const float cpi = fminf(fmaxf(wi.x / sinI, -1.f), 1.f), spi = fminf(fmaxf(wi.y / sinI, -1.f), 1.f);
+                    const float cpo = fminf(fmaxf(wo.x / sinO, -1.f), 1.f), spo = fminf(fmaxf(wo.y / sinO, -1.f), 1.f);
+                    maxCos = fmaxf(0.f, cpi * cpo + spi * spo);
+                }
+                float sinAlpha, tanBeta;
+                if (fabsf(wi.z) > fabsf(wo.z)) { sinAlpha = sinO; tanBeta = sinI / fabsf(wi.z); }
+                else { sinAlpha = sinI; tanBeta = sinO / fabsf(wo.z); }
+                on = A + B * maxCos * sinAlpha * tanBeta;
+            }
+            f.x += m.kd[0] * kBsdfInvPi * on; f.y += m.kd[1] * kBsdfInvPi * on; f.z += m.kd[2] * kBsdfInvPi * on;
+            pdf += fabsf(wi.z) * kBsdfInvPi;
+        }
     }
     if (m.glossy) {
         if (same) { const float g = glossy_f(wo, wi, m.alpha); f.x += m.ks[0] * g; f.y += m.ks[1] * g; f.z += m.ks[2] * g; }

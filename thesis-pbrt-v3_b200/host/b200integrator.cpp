@@ -33,6 +33,7 @@
 #include "core/primitive.h"
 #include "shapes/sphere.h"
 #include "materials/plastic.h"
+#include "materials/matte.h"
 #include "materials/mirror.h"
 #include "materials/glass.h"
 #include "materials/metal.h"
@@ -284,6 +285,13 @@ void B200WavefrontIntegrator::Render(const Scene &scene) {
                     rec[0] = (float)(B200RT_MAT_GLASS + (flip ? B200RT_MAT_REVERSE_ORIENTATION : 0));
                     for (int c = 0; c < 3; ++c) { rec[1 + c] = kr[c]; rec[4 + c] = kt[c]; }
                     rec[7] = gm->index->Evaluate(si);
+                } else if (const MatteMaterial *mt = dynamic_cast<const MatteMaterial *>(m);
+                           mt && !mt->bumpMap && mt->sigma->Evaluate(si) != 0) {
+                    // Material "matte" with "float sigma" > 0: an Oren-Nayar lobe (matte.cpp:55-61); sigma has no accessor
+                    Float kd[3];
+                    Spectrum(mt->Kd->Evaluate(si).Clamp()).ToRGB(kd);
+                    for (int c = 0; c < 3; ++c) rec[1 + c] = kd[c];
+                    rec[4] = Clamp(mt->sigma->Evaluate(si), 0, 90);
                 } else {
                     Float kd[3];
                     if (!lambertianKd(m, kd)) { Error("b200wavefront: only \"matte\", \"plastic\", \"mirror\", smooth \"glass\", \"metal\" and \"substrate\" materials are supported"); return; }
