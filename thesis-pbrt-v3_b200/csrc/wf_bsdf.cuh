@@ -180,7 +180,10 @@ __device__ __forceinline__ float blend_pdf(const WfMat &m, const float3 wo, cons
 }
 
 // BSDF::f and BSDF::Pdf (reflection.cpp): every lobe here is reflective, so f = 0 across the surface.
-__device__ __forceinline__ void bsdf_eval(const WfMat &m, const float3 wo, const float3 wi, float3 &f, float &pdf) {
+// (not inlined: shade_general evaluates the BSDF at up to four places and samples it at three; inlining every material
+// kind at each of them made k_shade<true> 21.7 k SASS lines and instruction-fetch bound — ncu `no_instruction` 8-9 warps
+// per issue, profiles/r01_ncu_full_k_shade_living_room_summary.txt)
+__device__ __noinline__ void bsdf_eval(const WfMat &m, const float3 wo, const float3 wi, float3 &f, float &pdf) {
     f = make_float3(0.f, 0.f, 0.f);
     pdf = 0.f;
     if (m.kind == 4u /* B200RT_MAT_METAL */) {
@@ -227,7 +230,7 @@ __device__ __forceinline__ void bsdf_eval(const WfMat &m, const float3 wo, const
 }
 
 // BSDF::Sample_f (reflection.cpp): false = the sample carries nothing (pdf == 0 or f black).
-__device__ __forceinline__ bool bsdf_sample(const WfMat &m, const float3 wo, float u0, float u1, float3 &wi, float3 &f, float &pdf) {
+__device__ __noinline__ bool bsdf_sample(const WfMat &m, const float3 wo, float u0, float u1, float3 &wi, float3 &f, float &pdf) {
     int n = (m.diffuse ? 1 : 0) + (m.glossy ? 1 : 0);
     bool pickGlossy;
     if (m.kind == 4u) { n = 1; pickGlossy = true; }   // metal: the one microfacet lobe
