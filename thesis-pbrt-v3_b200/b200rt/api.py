@@ -32,7 +32,8 @@ class CountersStruct(C.Structure):
 
 
 def lib_path():
-    return os.path.join(_HERE, "libb200rt.so")
+    # B200RT_LIB: another build of the same library, for same-box A/B measurements only (scripts/ab_shade_inline.sh)
+    return os.environ.get("B200RT_LIB") or os.path.join(_HERE, "libb200rt.so")
 
 
 _lib = None

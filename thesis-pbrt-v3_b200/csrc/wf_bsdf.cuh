@@ -180,10 +180,16 @@ __device__ __forceinline__ float blend_pdf(const WfMat &m, const float3 wo, cons
 }
 
 // BSDF::f and BSDF::Pdf (reflection.cpp): every lobe here is reflective, so f = 0 across the surface.
-// (not inlined: shade_general evaluates the BSDF at up to four places and samples it at three; inlining every material
-// kind at each of them made k_shade<true> 21.7 k SASS lines and instruction-fetch bound — ncu `no_instruction` 8-9 warps
-// per issue, profiles/r01_ncu_full_k_shade_living_room_summary.txt)
-__device__ __noinline__ void bsdf_eval(const WfMat &m, const float3 wo, const float3 wi, float3 &f, float &pdf) {
+// (inlined on purpose: shade_general evaluates the BSDF at up to four places and samples it at three, which makes
+// k_shade<true> 21.7 k SASS lines, and a SMALL launch shows instruction-fetch stalls in ncu (`no_instruction` 8-9 warps per
+// issue, profiles/r01_ncu_full_k_shade_living_room_summary.txt).  Measured out of line (__noinline__: 10.1 k lines, 200-byte
+// stack frame): the non-traversal part of a 1280x720 @ 64 spp living-room frame went from 167 ms to 188 ms — not adopted.)
+#ifdef B200RT_BSDF_NOINLINE   // A/B build only (scripts/ab_shade_inline.sh)
+#define B200RT_BSDF_FN __device__ __noinline__
+#else
+#define B200RT_BSDF_FN __device__ __forceinline__
+#endif
+B200RT_BSDF_FN void bsdf_eval(const WfMat &m, const float3 wo, const float3 wi, float3 &f, float &pdf) {
     f = make_float3(0.f, 0.f, 0.f);
     pdf = 0.f;
     if (m.kind == 4u /* B200RT_MAT_METAL */) {
@@ -230,7 +236,7 @@ __device__ __noinline__ void bsdf_eval(const WfMat &m, const float3 wo, const fl
 }
 
 // BSDF::Sample_f (reflection.cpp): false = the sample carries nothing (pdf == 0 or f black).
-__device__ __noinline__ bool bsdf_sample(const WfMat &m, const float3 wo, float u0, float u1, float3 &wi, float3 &f, float &pdf) {
+B200RT_BSDF_FN bool bsdf_sample(const WfMat &m, const float3 wo, float u0, float u1, float3 &wi, float3 &f, float &pdf) {
     int n = (m.diffuse ? 1 : 0) + (m.glossy ? 1 : 0);
     bool pickGlossy;
     if (m.kind == 4u) { n = 1; pickGlossy = true; }   // metal: the one microfacet lobe
