@@ -183,7 +183,8 @@ __device__ __forceinline__ float blend_pdf(const WfMat &m, const float3 wo, cons
 // (inlined on purpose: shade_general evaluates the BSDF at up to four places and samples it at three, which makes
 // k_shade<true> 21.7 k SASS lines, and a SMALL launch shows instruction-fetch stalls in ncu (`no_instruction` 8-9 warps per
 // issue, profiles/r01_ncu_full_k_shade_living_room_summary.txt).  Measured out of line (__noinline__: 10.1 k lines, 200-byte
-// stack frame): the non-traversal part of a 1280x720 @ 64 spp living-room frame went from 167 ms to 188 ms — not adopted.)
+// stack frame), same box, alternating runs: 1280x720 @ 64 spp living-room frames of 970 / 977 ms inline vs 980 / 981 ms out
+// of line (profiles/r01_ab_shade_inline.log) — not adopted.)
 #ifdef B200RT_BSDF_NOINLINE   // A/B build only (scripts/ab_shade_inline.sh)
 #define B200RT_BSDF_FN __device__ __noinline__
 #else
