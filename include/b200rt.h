@@ -21,7 +21,7 @@
 extern "C" {
 #endif
 
-#define B200RT_VERSION 7
+#define B200RT_VERSION 8
 
 enum {
     B200RT_OK = 0,
@@ -80,8 +80,8 @@ typedef struct {
     uint32_t n_directions;   /* M (3 for kd) */
     float bounds[6];         /* kd/RBSP root bounds pMin.xyz pMax.xyz (genericBSP.h:190); BVH: ignored */
     const float *tri_verts;  /* n_prims x 9 floats: world-space p0,p1,p2 (TriangleMesh::p, triangle.h:50-69) */
-    const float *tri_uvs;    /* n_prims x 6 floats or NULL (default (0,0),(1,0),(1,1), triangle.h:109-121);
-                                only used for the degenerate-triangle rejection of triangle.cpp:302-315 */
+    const float *tri_uvs;    /* n_prims x 6 floats or NULL (default (0,0),(1,0),(1,1), triangle.h:109-121): the
+                                degenerate-triangle rejection of triangle.cpp:302-315 and the shade stage's dpdu frame */
     uint32_t n_prims;
     /* Non-triangle primitives in the aggregate (Sphere::Intersect / IntersectP, src/shapes/sphere.cpp:49-156,
      * 158-215; killeroo-simple's area light and scenes/simple put spheres next to the triangles).
@@ -93,6 +93,12 @@ typedef struct {
     const uint8_t *prim_kind;
     const float *sphere_params;
     uint32_t n_spheres;
+    /* ---- appended in ABI v8: what Triangle::Intersect's tail (triangle.cpp:294-425) reads besides the vertices; used by the
+     * wavefront shade stage only (the traversal never looks at them) ---- */
+    const float *tri_normals;   /* n_prims x 9 floats: TriangleMesh::n at the triangle's three vertices (world space, as the mesh
+                                   stores them), or NULL.  Rows of primitives without normals are ignored (prim_flags bit 1). */
+    const uint8_t *prim_flags;  /* n_prims bytes or NULL (= all 0): bit 0 = Shape::reverseOrientation ^ transformSwapsHandedness
+                                   (triangle.cpp:421-424, interaction.cpp:62-66), bit 1 = the primitive's mesh has vertex normals */
 } b200rt_scene_desc;
 
 typedef struct b200rt_scene b200rt_scene;

@@ -81,7 +81,27 @@ typedef struct {
                               with pdf 1 / (2 pi^2 sin theta) -> shadow ray to p + wi * 2 * radius; a BSDF-sampled
                               closest-hit "MIS" ray that contributes Le when it ESCAPES (integrator.cpp:196-212); camera
                               rays that escape add Le (path.cpp:97-107).  All zero = identity. */
+    /* ---- appended in ABI v8: the reference's sample streams and its camera arithmetic ---- */
+    uint32_t sampler;      /* B200RT_SAMPLER_HASH (the v7 counter hash), B200RT_SAMPLER_HALTON = Sampler "halton"
+                              (samplers/halton.cpp: GetIndexForSample / SampleDimension over the sample bounds of the film's
+                              crop window, digit permutations from the reference's default RNG) or B200RT_SAMPLER_SOBOL =
+                              Sampler "sobol" (samplers/sobol.cpp) over the generator matrices below.  Both are GlobalSamplers:
+                              a value depends on (pixel, sample number, dimension) only, so the image is still independent
+                              of batch size and rank count.  Dimensions are consumed in PathIntegrator::Li's order (camera
+                              0-4; per bounce: light choice, uLight, uScattering, BSDF sample, Russian roulette if drawn). */
+    uint32_t camera_exact; /* != 0: camera rays are generated from the two matrices below with the reference's float
+                              operations (PerspectiveCamera::GenerateRayDifferential, cameras/perspective.cpp:97-143, lensradius 0;
+                              Transform::operator()(Ray), transform.h:251-264) instead of camera.eye/dir/right/up */
+    float raster_to_camera[16]; /* ProjectiveCamera::RasterToCamera.m, row-major (camera.h:101-107) */
+    float camera_to_world[16];  /* Camera::CameraToWorld at the shutter-open time, row-major */
+    const uint32_t *sobol_matrices32; /* B200RT_SAMPLER_SOBOL: SobolMatrices32 (1024 x 52, sobolmatrices.cpp), HOST pointer */
+    const uint64_t *sobol_vdc;        /* VdCSobolMatrices, sobol_vdc_rows x 52 */
+    const uint64_t *sobol_vdc_inv;    /* VdCSobolMatricesInv, sobol_vdc_rows x 52 */
+    uint32_t sobol_vdc_rows;
+    uint32_t material_stride; /* floats per material record: 0 or 8 = the v7 records; 20 = v8 records
+                              (kind, c0.rgb, c1.rgb, roughness, Kr.rgb, Kt.rgb, opacity.rgb, eta, -, -) which B200RT_MAT_UBER needs */
 } b200rt_render_desc;
+enum { B200RT_SAMPLER_HASH = 0, B200RT_SAMPLER_HALTON = 1, B200RT_SAMPLER_SOBOL = 2 };
 enum { B200RT_LIGHT_POINT = 0, B200RT_LIGHT_SPHERE = 1, B200RT_LIGHT_DISTANT = 2, B200RT_LIGHT_INFINITE = 3 };
 enum {
     B200RT_MAT_MATTE = 0,   /* materials/matte.cpp:44-62; record = (kind, Kd.rgb, sigma, -, -, -): sigma (degrees) > 0 = OrenNayar */
@@ -94,6 +114,10 @@ enum {
                                isotropic; record = (kind, eta.rgb, k.rgb, roughness) */
     B200RT_MAT_SUBSTRATE = 5, /* materials/substrate.cpp:45-66: FresnelBlend(Kd, Ks, TrowbridgeReitz), isotropic;
                                record = (kind, Kd.rgb, Ks.rgb, roughness) */
+    /* ---- ABI v8 ---- */
+    B200RT_MAT_UBER = 6,    /* materials/uber.cpp:45-100 (20-float records): SpecularTransmission(1 - opacity) + Lambertian(op Kd) +
+                               MicrofacetReflection(op Ks, TrowbridgeReitz, FresnelDielectric(1, eta)) + SpecularReflection(op Kr) +
+                               SpecularTransmission(op Kt, 1, eta); c0 = Kd, c1 = Ks */
     B200RT_MAT_NO_REMAP = 32, /* added to `kind`: "bool remaproughness" false — roughness IS the Trowbridge-Reitz alpha
                                (plastic, metal, substrate; scenes/living-room's materials are written that way) */
     B200RT_MAT_REVERSE_ORIENTATION = 16 /* added to `kind`: the shape's reverseOrientation ^ transformSwapsHandedness
@@ -145,6 +169,18 @@ int b200rt_render_heatmaps(b200rt_scene *scene, const b200rt_render_desc *desc, 
  * query the count.  rays: HOST or DEVICE buffer of *n b200rt_ray. */
 int b200rt_render_queue(b200rt_scene *scene, uint32_t queue, b200rt_ray *rays, uint64_t *n);
 int b200rt_render_keep_queues(b200rt_scene *scene, int keep); /* enable recording (off by default) */
+/* Path slot (index into the batch; see b200rt_render_slot_pixel) of every entry of queue q, and — for shadow (odd q) and
+ * MIS queues — the radiance the ray carries if it is unoccluded / reaches the light.  MIS queues are q = 2*(max_depth+1)+depth.
+ * path / contrib: HOST buffers of *n entries (contrib: 4 floats each; NULL to skip). */
+int b200rt_render_queue_paths(b200rt_scene *scene, uint32_t queue, uint32_t *path, float *contrib, uint64_t *n);
+
+/* The camera matrices of `LookAt eye look up` (or of an explicit world-to-camera matrix, `Transform [...]`, when w2c16 != NULL)
+ * + `Camera "perspective" "float fov"` on an xres x yres film (frame aspect default screen window), computed with the
+ * reference's own float operations: LookAt / Perspective / Scale / Translate / Inverse / operator* (src/core/transform.cpp:82-136,
+ * 203-236,303-311; camera.h:87-108; api.cpp pbrtCamera).  Fills desc->camera (xres, yres and the legacy frame),
+ * raster_to_camera, camera_to_world and sets camera_exact = 1.  lookat9 = eye, look, up. */
+int b200rt_camera_perspective(const float *lookat9, const float *w2c16, float fov, uint32_t xres, uint32_t yres,
+                              b200rt_render_desc *desc);
 
 #ifdef __cplusplus
 }

@@ -7,6 +7,8 @@
 #include "ref_internal.h"
 #define private public
 #define protected public
+#include "core/sampler.h"
+#include "core/camera.h"
 #include "core/primitive.h"
 #include "core/film.h"
 #undef private
@@ -34,6 +36,7 @@
 #include "materials/metal.h"
 #include "materials/substrate.h"
 #include "samplers/halton.h"
+#include "samplers/sobol.h"
 #include "samplers/random.h"
 #include "textures/constant.h"
 
@@ -97,6 +100,99 @@ struct CountingAggregate : public Aggregate {
     }
 };
 }  // namespace
+
+// ---- event trace of a single-threaded render (tests/: the shade stage's sample dimensions and spawned rays are pinned
+// against it).  One 16-word record per event, in execution order:
+//   1 StartPixel        [1] x [2] y
+//   2 StartNextSample   [1] returned bool
+//   3 Get1D             [1] dimension the value came from [2] value
+//   4 Get2D             [1] dimension [2] [3] values
+//   5 Intersect         [1..3] o [4..6] d [7] tMax before [8] primitive (-1 miss) [9] tMax after [10..12] isect.n [13..15] isect.shading.n
+//   6 IntersectP        [1..3] o [4..6] d [7] tMax [8] occluded
+static bool g_trace = false;
+static std::vector<uint32_t> g_traceLog;
+static inline uint32_t fbits(float f) { uint32_t u; std::memcpy(&u, &f, 4); return u; }
+static void trace_push(const uint32_t (&r)[16]) { g_traceLog.insert(g_traceLog.end(), r, r + 16); }
+extern "C" void ref_trace_enable(int on) { g_trace = on != 0; g_traceLog.clear(); }
+extern "C" uint64_t ref_trace_records(void) { return g_traceLog.size() / 16; }
+extern "C" void ref_trace_copy(uint32_t *out) { std::memcpy(out, g_traceLog.data(), g_traceLog.size() * 4); }
+
+namespace {
+template <class Base>
+struct TracingSampler : public Base {
+    template <class... A> explicit TracingSampler(A &&... a) : Base(std::forward<A>(a)...) {}
+    void StartPixel(const Point2i &p) override {
+        uint32_t r[16] = {1, (uint32_t)p.x, (uint32_t)p.y};
+        trace_push(r);
+        Base::StartPixel(p);
+    }
+    bool StartNextSample() override {
+        const bool b = Base::StartNextSample();
+        uint32_t r[16] = {2, b ? 1u : 0u};
+        trace_push(r);
+        return b;
+    }
+    Float Get1D() override {
+        const Float v = Base::Get1D();
+        uint32_t r[16] = {3, (uint32_t)(this->dimension - 1), fbits(v)};
+        trace_push(r);
+        return v;
+    }
+    Point2f Get2D() override {
+        const Point2f v = Base::Get2D();
+        uint32_t r[16] = {4, (uint32_t)(this->dimension - 2), fbits(v.x), fbits(v.y)};
+        trace_push(r);
+        return v;
+    }
+    std::unique_ptr<Sampler> Clone(int) override { return std::unique_ptr<Sampler>(new TracingSampler<Base>(*this)); }
+};
+struct TracingAggregate : public Aggregate {
+    std::shared_ptr<Primitive> inner;
+    std::unordered_map<const Primitive *, int> index;
+    explicit TracingAggregate(std::shared_ptr<Primitive> p) : inner(std::move(p)) {}
+    Bounds3f WorldBound() const override { return inner->WorldBound(); }
+    bool Intersect(const Ray &ray, SurfaceInteraction *si) const override {
+        uint32_t r[16] = {5, fbits(ray.o.x), fbits(ray.o.y), fbits(ray.o.z), fbits(ray.d.x), fbits(ray.d.y), fbits(ray.d.z), fbits(ray.tMax)};
+        const bool hit = inner->Intersect(ray, si);
+        int prim = -1;
+        if (hit) { auto it = index.find(si->primitive); prim = it == index.end() ? -2 : it->second; }
+        r[8] = (uint32_t)prim; r[9] = fbits(ray.tMax);
+        if (hit) {
+            r[10] = fbits(si->n.x); r[11] = fbits(si->n.y); r[12] = fbits(si->n.z);
+            r[13] = fbits(si->shading.n.x); r[14] = fbits(si->shading.n.y); r[15] = fbits(si->shading.n.z);
+        }
+        trace_push(r);
+        return hit;
+    }
+    bool IntersectP(const Ray &ray) const override {
+        uint32_t r[16] = {6, fbits(ray.o.x), fbits(ray.o.y), fbits(ray.o.z), fbits(ray.d.x), fbits(ray.d.y), fbits(ray.d.z), fbits(ray.tMax)};
+        const bool occ = inner->IntersectP(ray);
+        r[8] = occ ? 1u : 0u;
+        trace_push(r);
+        return occ;
+    }
+};
+}  // namespace
+
+// The matrices of the camera ref_render builds for (cam, xres, yres): ProjectiveCamera::RasterToCamera and CameraToWorld
+// (row-major 4x4 each) — what tests compare b200rt_camera_perspective with.
+extern "C" void ref_camera_matrices(const float *cam, int xres, int yres, const float *w2c16, float *r2c_out, float *c2w_out) {
+    std::unique_ptr<Filter> filter(new BoxFilter(Vector2f(0.5f, 0.5f)));
+    Film *film = new Film(Point2i(xres, yres), Bounds2f(Point2f(0, 0), Point2f(1, 1)), std::move(filter), 35.f, "x.exr", 1.f);
+    Transform w2c = LookAt(Point3f(cam[0], cam[1], cam[2]), Point3f(cam[3], cam[4], cam[5]), Vector3f(cam[6], cam[7], cam[8]));
+    if (w2c16)
+        w2c = Transform(Matrix4x4(w2c16[0], w2c16[1], w2c16[2], w2c16[3], w2c16[4], w2c16[5], w2c16[6], w2c16[7], w2c16[8], w2c16[9],
+                                  w2c16[10], w2c16[11], w2c16[12], w2c16[13], w2c16[14], w2c16[15]));
+    Transform c2w = Inverse(w2c);
+    AnimatedTransform ac2w(&c2w, 0.f, &c2w, 1.f);
+    Float frame = Float(xres) / Float(yres);
+    Bounds2f screen;
+    if (frame > 1.f) { screen.pMin = Point2f(-frame, -1.f); screen.pMax = Point2f(frame, 1.f); }
+    else { screen.pMin = Point2f(-1.f, -1.f / frame); screen.pMax = Point2f(1.f, 1.f / frame); }
+    PerspectiveCamera pc(ac2w, screen, 0.f, 1.f, 0.f, 1e6f, cam[9], film, nullptr);
+    std::memcpy(r2c_out, pc.RasterToCamera.GetMatrix().m, 64);
+    std::memcpy(c2w_out, c2w.GetMatrix().m, 64);
+}
 
 // LightSource "distant" "point from" "point to" for the NEXT ref_render calls (NULL = back to the point light):
 // from_to = from[3], to[3]; its radiance "L" is ref_render's light_I (lights/distant.cpp:117-125, CreateDistantLight).
@@ -231,7 +327,14 @@ extern "C" int ref_render(ref_scene *s, const char *accel_kind, const float *cam
         accel = a->agg;
         delete a;
     }
-    auto counting = std::make_shared<CountingAggregate>(accel);
+    std::shared_ptr<Primitive> traced = accel;
+    if (g_trace) {
+        if (n_threads != 1) return 3;   // the trace is an ordered log: single-threaded renders only
+        auto ta = std::make_shared<TracingAggregate>(accel);
+        for (size_t i = 0; i < prims.size(); ++i) ta->index[prims[i].get()] = (int)i;
+        traced = ta;
+    }
+    auto counting = std::make_shared<CountingAggregate>(traced);
     // LightSource "point" "point from" "rgb I" (lights/point.cpp:81-89)
     Float li[3] = {light_I[0], light_I[1], light_I[2]};
     Transform l2w = Translate(Vector3f(light_pos[0], light_pos[1], light_pos[2]));
@@ -269,8 +372,13 @@ extern "C" int ref_render(ref_scene *s, const char *accel_kind, const float *cam
     else { screen.pMin = Point2f(-1.f, -1.f / frame); screen.pMax = Point2f(1.f, 1.f / frame); }
     std::shared_ptr<const Camera> camera(new PerspectiveCamera(ac2w, screen, 0.f, 1.f, 0.f, 1e6f, cam[9], film, nullptr));
     std::shared_ptr<Sampler> sampler;
-    if (std::string(sampler_name) == "halton") sampler.reset(new HaltonSampler(spp, film->GetSampleBounds()));
-    else sampler.reset(new RandomSampler(spp));
+    if (std::string(sampler_name) == "halton") {
+        if (g_trace) sampler.reset(new TracingSampler<HaltonSampler>(spp, film->GetSampleBounds()));
+        else sampler.reset(new HaltonSampler(spp, film->GetSampleBounds()));
+    } else if (std::string(sampler_name) == "sobol") {
+        if (g_trace) sampler.reset(new TracingSampler<SobolSampler>(spp, film->GetSampleBounds()));
+        else sampler.reset(new SobolSampler(spp, film->GetSampleBounds()));
+    } else sampler.reset(new RandomSampler(spp));
     PathIntegrator integ(maxdepth, camera, sampler, film->GetSampleBounds(), 1.f, "spatial");
 
     const auto t0 = std::chrono::steady_clock::now();

@@ -24,7 +24,8 @@ class SceneDesc(C.Structure):
                 ("prim_indices", C.c_void_p), ("n_indices", C.c_uint32), ("directions", C.c_void_p),
                 ("n_directions", C.c_uint32), ("bounds", C.c_float * 6), ("tri_verts", C.c_void_p),
                 ("tri_uvs", C.c_void_p), ("n_prims", C.c_uint32), ("prim_kind", C.c_void_p),
-                ("sphere_params", C.c_void_p), ("n_spheres", C.c_uint32)]
+                ("sphere_params", C.c_void_p), ("n_spheres", C.c_uint32),
+                ("tri_normals", C.c_void_p), ("prim_flags", C.c_void_p)]
 
 
 class CountersStruct(C.Structure):
@@ -146,14 +147,21 @@ class B200Accel:
     """Aggregate over a device-resident tree.  Mirrors pbrt's Aggregate (src/core/primitive.h:49-56,
     188-198) for ray BATCHES: WorldBound(), Intersect(rays) -> hits, IntersectP(rays) -> occluded."""
 
-    def __init__(self, tree, tri_verts, tri_uvs=None, prim_kind=None, spheres=None):
+    def __init__(self, tree, tri_verts, tri_uvs=None, prim_kind=None, spheres=None, tri_normals=None, prim_flags=None):
         """prim_kind: optional (n_prims,) uint8 with 1 = full sphere; spheres: (n_spheres,16) float32 rows
-        (WorldToObject 3x4, radius, pad) — see b200rt_scene_desc in include/b200rt.h."""
+        (WorldToObject 3x4, radius, pad) — see b200rt_scene_desc in include/b200rt.h.
+        tri_normals: optional (n_prims, 9) world-space vertex normals (TriangleMesh::n); prim_flags: optional (n_prims,)
+        uint8, bit 0 = reverseOrientation ^ transformSwapsHandedness, bit 1 = the primitive has vertex normals (set for
+        every primitive when tri_normals is given and prim_flags is not)."""
         self.tree = tree
         v = np.ascontiguousarray(tri_verts, np.float32).reshape(-1, 9)
         pk = None if prim_kind is None else np.ascontiguousarray(prim_kind, np.uint8)
         sp = None if spheres is None else np.ascontiguousarray(spheres, np.float32).reshape(-1, 16)
         uv = None if tri_uvs is None else np.ascontiguousarray(tri_uvs, np.float32).reshape(-1, 6)
+        tn = None if tri_normals is None else np.ascontiguousarray(tri_normals, np.float32).reshape(-1, 9)
+        if tn is not None and prim_flags is None:
+            prim_flags = np.full(len(v), 2, np.uint8)
+        pf = None if prim_flags is None else np.ascontiguousarray(prim_flags, np.uint8)
         nodes = np.ascontiguousarray(tree["nodes"], np.uint32)
         idx = np.ascontiguousarray(tree["indices"], np.uint32)
         dirs = tree.get("directions")
@@ -166,6 +174,7 @@ class B200Accel:
         d.bounds = (C.c_float * 6)(*[float(x) for x in np.asarray(tree["bounds"], np.float32)])
         d.tri_verts, d.tri_uvs, d.n_prims = _p(v), _p(uv), len(v)
         d.prim_kind, d.sphere_params, d.n_spheres = _p(pk), _p(sp), 0 if sp is None else len(sp)
+        d.tri_normals, d.prim_flags = _p(tn), _p(pf)
         h = C.c_void_p()
         _check(lib().b200rt_scene_create(C.byref(d), C.byref(h)))
         self._h = h
@@ -236,7 +245,7 @@ _KD_DEFAULTS = dict(intersectcost=80, traversalcost=1, emptybonus=0.0, maxprims=
 _IGNORED = {"splitalpha", "alphatype", "axisselectiontype", "axisselectionamount", "nbDirections"}
 
 
-def MakeAccelerator(name, tri_verts, paramSet=None, tri_uvs=None, tree=None):
+def MakeAccelerator(name, tri_verts, paramSet=None, tri_uvs=None, tree=None, tri_normals=None, prim_flags=None):
     """Mirror of MakeAccelerator(name, prims, paramSet) (reference src/core/api.cpp:790-1015) for
     the accelerators on the hot path.  `paramSet` uses the .pbrt parameter names.  "bvh" and
     "kdtree" are built by this repo's host builders; "rbsp"/"rbspkd" take a host-built tree
@@ -244,7 +253,7 @@ def MakeAccelerator(name, tri_verts, paramSet=None, tri_uvs=None, tree=None):
     Unknown names return None after a warning, like the reference (api.cpp:1011-1012)."""
     ps = dict(paramSet or {})
     if tree is not None:
-        return B200Accel(tree, tri_verts, tri_uvs)
+        return B200Accel(tree, tri_verts, tri_uvs, tri_normals=tri_normals, prim_flags=prim_flags)
     if name == "bvh":
         args = {k: ps.pop(k, v) for k, v in _BVH_DEFAULTS.items()}
         tree = build_bvh(tri_verts, **args)
@@ -262,4 +271,4 @@ def MakeAccelerator(name, tri_verts, paramSet=None, tri_uvs=None, tree=None):
         if k not in _IGNORED:
             import warnings
             warnings.warn('Parameter "%s" not used' % k)  # api.cpp:1013 paramSet.ReportUnused()
-    return B200Accel(tree, tri_verts, tri_uvs)
+    return B200Accel(tree, tri_verts, tri_uvs, tri_normals=tri_normals, prim_flags=prim_flags)

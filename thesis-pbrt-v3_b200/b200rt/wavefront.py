@@ -17,7 +17,13 @@ class RenderDesc(C.Structure):
                 ("world", C.c_uint32), ("seed", C.c_uint32), ("max_batch", C.c_uint32),
                 ("light_kind", C.c_uint32), ("light_radius", C.c_float), ("light_prim", C.c_uint32),
                 ("materials", C.c_void_p), ("n_materials", C.c_uint32), ("prim_material", C.c_void_p),
-                ("crop", C.c_uint32 * 4), ("light_to_world", C.c_float * 9)]
+                ("crop", C.c_uint32 * 4), ("light_to_world", C.c_float * 9),
+                ("sampler", C.c_uint32), ("camera_exact", C.c_uint32), ("raster_to_camera", C.c_float * 16),
+                ("camera_to_world", C.c_float * 16), ("sobol_matrices32", C.c_void_p), ("sobol_vdc", C.c_void_p),
+                ("sobol_vdc_inv", C.c_void_p), ("sobol_vdc_rows", C.c_uint32), ("material_stride", C.c_uint32)]
+
+
+SAMPLERS = {"hash": 0, "halton": 1, "sobol": 2}
 
 
 class RenderStats(C.Structure):
@@ -39,6 +45,8 @@ def _lib():
         L.b200rt_render_tiles.argtypes = [C.POINTER(RenderDesc), C.POINTER(C.c_uint32), C.POINTER(C.c_uint64)]
         L.b200rt_render_keep_queues.argtypes = [C.c_void_p, C.c_int]
         L.b200rt_render_queue.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.POINTER(C.c_uint64)]
+        L.b200rt_render_queue_paths.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.POINTER(C.c_uint64)]
+        L.b200rt_camera_perspective.argtypes = [C.c_void_p, C.c_void_p, C.c_float, C.c_uint32, C.c_uint32, C.POINTER(RenderDesc)]
         _bound = True
     return L
 
@@ -51,7 +59,7 @@ class WavefrontPathIntegrator:
 
     def __init__(self, camera, spp=8, maxdepth=5, light_pos=(0, 0, 0), light_I=(1, 1, 1), kd=(.5, .5, .5),
                  rank=0, world=1, seed=0, tile_size=16, max_batch=0, sphere_light=None, materials=None,
-                 prim_material=None, distant_light=None, crop=None, infinite_light=None):
+                 prim_material=None, distant_light=None, crop=None, infinite_light=None, sampler="hash", sobol_tables=None):
         """sphere_light=(radius, prim): `AreaLightSource "area" "color L" light_I` on the full sphere primitive number
         `prim` of the aggregate, centred at light_pos (sampled with MIS like EstimateDirect).  materials: (n, 8) rows
         (kind, Kd.rgb, Ks.rgb, roughness) + prim_material: (n_prims,) uint8 index per primitive.
@@ -60,11 +68,33 @@ class WavefrontPathIntegrator:
         crop=(x0, x1, y0, y1): Film "cropwindow" in pixels (scenes.killeroo_feet()["crop"]); the film then holds
         (y1-y0, x1-x0) pixels, as the reference's Film does.
         infinite_light=(light_to_world 3x3 or None, world_radius): `LightSource "infinite"` with the constant radiance
-        light_I (lights/infinite.cpp without a readable "mapname"), sampled with MIS."""
+        light_I (lights/infinite.cpp without a readable "mapname"), sampled with MIS.
+        camera: either the pinhole frame dict (eye / dir / right / up / xres / yres) or a dict with "lookat" (9 floats:
+        eye, look, up) or "w2c" (4x4 world-to-camera matrix) + "fov", "xres", "yres": the latter is turned into the
+        reference camera's own matrices (b200rt_camera_perspective) and camera rays are bit-identical to the reference's.
+        sampler: "hash" | "halton" | "sobol" (Sampler "halton" / "sobol" of the reference, same sample values and
+        dimension order); sobol needs sobol_tables = (SobolMatrices32, VdCSobolMatrices, VdCSobolMatricesInv) arrays.
+        materials: (n, 8) rows, or (n, 20) rows (needed for "uber", kind 6)."""
         d = RenderDesc()
-        for k in ("eye", "dir", "right", "up"):
-            setattr(d.camera, k, (C.c_float * 3)(*[float(x) for x in camera[k]]))
-        d.camera.xres, d.camera.yres = int(camera["xres"]), int(camera["yres"])
+        if "lookat" in camera or "w2c" in camera:
+            la = None if camera.get("lookat") is None else np.ascontiguousarray(camera["lookat"], np.float32).reshape(9)
+            m = None if camera.get("w2c") is None else np.ascontiguousarray(camera["w2c"], np.float32).reshape(16)
+            api._check(_lib().b200rt_camera_perspective(None if la is None else la.ctypes.data, None if m is None else m.ctypes.data,
+                                                        float(camera["fov"]), int(camera["xres"]), int(camera["yres"]), C.byref(d)))
+        else:
+            for k in ("eye", "dir", "right", "up"):
+                setattr(d.camera, k, (C.c_float * 3)(*[float(x) for x in camera[k]]))
+            d.camera.xres, d.camera.yres = int(camera["xres"]), int(camera["yres"])
+        d.sampler = SAMPLERS[sampler]
+        if sampler == "sobol":
+            if sobol_tables is None:
+                raise ValueError('sampler "sobol" needs sobol_tables')
+            self._sobol = [np.ascontiguousarray(sobol_tables[0], np.uint32).reshape(-1),
+                           np.ascontiguousarray(sobol_tables[1], np.uint64).reshape(-1, 52),
+                           np.ascontiguousarray(sobol_tables[2], np.uint64).reshape(-1, 52)]
+            d.sobol_matrices32 = self._sobol[0].ctypes.data
+            d.sobol_vdc, d.sobol_vdc_inv = self._sobol[1].ctypes.data, self._sobol[2].ctypes.data
+            d.sobol_vdc_rows = len(self._sobol[1])
         d.spp, d.max_depth = int(spp), int(maxdepth)
         d.light_pos = (C.c_float * 3)(*[float(x) for x in light_pos])
         d.light_I = (C.c_float * 3)(*[float(x) for x in light_I])
@@ -84,9 +114,11 @@ class WavefrontPathIntegrator:
             d.light_kind, d.light_radius = 3, float(infinite_light[1])
             d.light_to_world = (C.c_float * 9)(*[float(x) for x in m.ravel()])
         if materials is not None:
-            self._mats = np.ascontiguousarray(materials, np.float32).reshape(-1, 8)
+            m = np.asarray(materials, np.float32)
+            stride = 20 if m.ndim == 2 and m.shape[1] == 20 else 8
+            self._mats = np.ascontiguousarray(m, np.float32).reshape(-1, stride)
             self._pm = np.ascontiguousarray(prim_material, np.uint8)
-            d.materials, d.n_materials = self._mats.ctypes.data, len(self._mats)
+            d.materials, d.n_materials, d.material_stride = self._mats.ctypes.data, len(self._mats), stride
             d.prim_material = self._pm.ctypes.data
         self.desc = d
 
@@ -158,6 +190,34 @@ def queue_rays(accel, q, ptr=None):
     if n.value:
         api._check(_lib().b200rt_render_queue(accel._h, q, out.ctypes.data_as(C.c_void_p), C.byref(n)))
     return out
+
+
+def queue_paths(accel, q, contrib=False):
+    """Path slot of every entry of kept queue q (2*depth closest, 2*depth+1 shadow, 2*(maxdepth+1)+depth MIS); with
+    contrib=True also the (n,4) radiance each shadow / MIS ray carries."""
+    n = C.c_uint64(queue_count(accel, q))
+    path = np.zeros(n.value, np.uint32)
+    c = np.zeros((n.value, 4), np.float32) if contrib else None
+    if n.value:
+        api._check(_lib().b200rt_render_queue_paths(accel._h, q, path.ctypes.data_as(C.c_void_p),
+                                                    None if c is None else c.ctypes.data_as(C.c_void_p), C.byref(n)))
+    return (path, c) if contrib else path
+
+
+def slot_pixels(desc, n_slots, start=0):
+    """(x, y, s, valid) of path slots start .. start+n_slots-1 of a render: tiles of the crop window in row-major order
+    (those with index % world == rank), pixels row-major inside a tile, samples innermost (wf_shade.cuh path_pixel)."""
+    c = desc.crop
+    xres, yres = (c[1] - c[0], c[3] - c[2]) if (c[0] or c[1] or c[2] or c[3]) else (desc.camera.xres, desc.camera.yres)
+    tile = desc.tile_size or 16
+    ntx, nty = (xres + tile - 1) // tile, (yres + tile - 1) // tile
+    g = np.arange(start, start + n_slots, dtype=np.int64)
+    pix, s = g // desc.spp, g % desc.spp
+    tile_ord, in_tile = pix // (tile * tile), pix % (tile * tile)
+    idx = desc.rank + tile_ord * desc.world
+    tx, ty = idx % ntx, idx // ntx
+    x, y = tx * tile + in_tile % tile, ty * tile + in_tile // tile
+    return x, y, s, (ty < nty) & (x < xres) & (y < yres)
 
 
 def film_to_rgb(film):

@@ -403,6 +403,27 @@ extern "C" int b200rt_scene_create(const b200rt_scene_desc *d, b200rt_scene **ou
         if (e == cudaSuccess) e = cudaMemset(s->d_pc, 0, B200RT_PC_SLOTS * sizeof(PersistCounters));
         if (e != cudaSuccess) rc = fail(B200RT_ECUDA, "cudaMalloc(counters): %s", cudaGetErrorString(e));
     }
+    // shading attributes of the wavefront stage (ABI v8): per-primitive UVs, vertex normals and orientation flags
+    if (rc == B200RT_OK && !s->empty) {
+        cudaError_t e = cudaSuccess;
+        if (d->tri_uvs) {
+            e = cudaMalloc(&s->d_prim_uv, (size_t)d->n_prims * 6 * sizeof(float));
+            if (e == cudaSuccess) e = cudaMemcpy(s->d_prim_uv, d->tri_uvs, (size_t)d->n_prims * 6 * sizeof(float), cudaMemcpyHostToDevice);
+        }
+        if (e == cudaSuccess && d->tri_normals) {
+            e = cudaMalloc(&s->d_prim_n, (size_t)d->n_prims * 9 * sizeof(float));
+            if (e == cudaSuccess) e = cudaMemcpy(s->d_prim_n, d->tri_normals, (size_t)d->n_prims * 9 * sizeof(float), cudaMemcpyHostToDevice);
+        }
+        if (e == cudaSuccess && d->prim_flags) {
+            for (uint32_t i = 0; i < d->n_prims && rc == B200RT_OK; ++i)
+                if ((d->prim_flags[i] & 2u) && !d->tri_normals) rc = fail(B200RT_EINVAL, "prim_flags[%u] says vertex normals but tri_normals is null", i);
+            if (rc == B200RT_OK) {
+                e = cudaMalloc(&s->d_prim_flags, d->n_prims);
+                if (e == cudaSuccess) e = cudaMemcpy(s->d_prim_flags, d->prim_flags, d->n_prims, cudaMemcpyHostToDevice);
+            }
+        }
+        if (e != cudaSuccess) rc = fail(B200RT_ECUDA, "cudaMalloc(shading attributes): %s", cudaGetErrorString(e));
+    }
     if (rc != B200RT_OK) { b200rt_scene_destroy(s); return rc; }
     *out = s;
     return B200RT_OK;
@@ -413,6 +434,7 @@ extern "C" void b200rt_scene_destroy(b200rt_scene *s) {
     b200rt_wavefront_release(s);
     if (s->d_prim_tris != s->d_tris) cudaFree(s->d_prim_tris);
     cudaFree(s->d_nodes); cudaFree(s->d_indices); cudaFree(s->d_tris); cudaFree(s->d_spheres);
+    cudaFree(s->d_prim_uv); cudaFree(s->d_prim_n); cudaFree(s->d_prim_flags);
     cudaFree(s->d_stage_in); cudaFree(s->d_stage_out); cudaFree(s->d_counters); cudaFree(s->d_pc);
     for (auto &l : s->lanes) {
         cudaFree(l.d_in); cudaFree(l.d_out);

@@ -14,6 +14,9 @@ struct b200rt_scene {
     float4 *d_tris = nullptr;       // traversal order (BVH: leaf slots; kd/RBSP: original primitive order)
     float4 *d_spheres = nullptr;    // 4 x float4 per sphere primitive (rt_math.cuh sphere_test)
     float4 *d_prim_tris = nullptr;  // original primitive order, for the shading stage (== d_tris for kd/RBSP)
+    float *d_prim_uv = nullptr;     // 6 floats per primitive (ABI v8; nullptr = the default UVs)
+    float *d_prim_n = nullptr;      // 9 floats per primitive: vertex normals (nullptr = none)
+    uint8_t *d_prim_flags = nullptr;  // bit 0 orientation flip, bit 1 has vertex normals
     float bounds[6] = {0, 0, 0, 0, 0, 0};
     uint32_t n_prims = 0;
     bool empty = false;  // zero primitives: every ray misses (bvh.cpp:355 `if (!nodes) return false`)

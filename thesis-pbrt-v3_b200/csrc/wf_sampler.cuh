@@ -1,0 +1,170 @@
+// The reference's sample streams, as pure functions of (pixel, sample number, dimension) — which is what a GlobalSampler
+// is (src/core/sampler.h:108-128, sampler.cpp:137-195): value = SampleDimension(GetIndexForSample(sampleNum), dimension).
+// A wavefront path therefore draws exactly the reference's numbers in any execution order, on any rank.
+//
+//   Sampler "halton"  src/samplers/halton.cpp:64-127; RadicalInverse / ScrambledRadicalInverse src/core/lowdiscrepancy.cpp:389-424,
+//                     the digit permutations of ComputeRadicalInversePermutations (:2490-2504) built on the host by
+//                     wf_sampler_host.cpp from the reference's default RNG (PCG32, rng.h)
+//   Sampler "sobol"   src/samplers/sobol.cpp:43-60; SobolIntervalToIndex / SobolSampleFloat src/core/lowdiscrepancy.h:229-272 over
+//                     the generator matrices the HOST hands in (SobolMatrices32, VdCSobolMatrices[Inv], sobolmatrices.cpp)
+//   kind 0            the round-1 counter hash (order independent too, but no reference stream)
+#pragma once
+#include "wf_core.cuh"
+
+namespace b200rt {
+
+enum { WF_SAMPLER_HASH = 0, WF_SAMPLER_HALTON = 1, WF_SAMPLER_SOBOL = 2 };
+constexpr int kSobolMatrixSize = 52;     // sobolmatrices.h:48
+constexpr int kSobolDims = 1024;         // sobolmatrices.h:47
+constexpr int kHaltonDims = 1000;        // PrimeTableSize (lowdiscrepancy.h)
+
+struct HaltonDim { uint32_t prime, offset; };
+
+struct WfSampler {
+    uint32_t kind, seed;
+    // halton
+    const uint16_t *perms;       // radicalInversePermutations
+    const HaltonDim *dimInfo;    // per dimension: (prime, offset of its permutation = PrimeSums[dim])
+    uint32_t baseScale0, baseScale1, baseExp0, baseExp1, stride, multInv0, multInv1, nDims;
+    // sobol
+    const uint32_t *sobol32;     // kSobolDims x 52
+    const uint64_t *vdc, *vdcInv;   // row log2Res - 1 of VdCSobolMatrices / VdCSobolMatricesInv (52 entries each)
+    uint32_t log2Res, res;
+    int32_t sbMinX, sbMinY;      // sampleBounds.pMin
+};
+
+WF_HD uint32_t hash_mix32(uint32_t x) {
+    x ^= x >> 16; x *= 0x7feb352dU; x ^= x >> 15; x *= 0x846ca68bU; x ^= x >> 16;
+    return x;
+}
+WF_HD float hash_sample(uint32_t seed, uint32_t pixel, uint32_t sample, uint32_t dim) {
+    uint32_t h = hash_mix32(seed ^ 0x9e3779b9U);
+    h = hash_mix32(h ^ pixel);
+    h = hash_mix32(h + sample * 0x85ebca6bU);
+    h = hash_mix32(h ^ (dim * 0xc2b2ae35U + 0x27d4eb2fU));
+    return (h >> 8) * 5.9604644775390625e-08f;  // [0,1)
+}
+
+WF_HD uint64_t reverse_bits64(uint64_t n) {
+#ifdef __CUDA_ARCH__
+    return __brevll(n);
+#else
+    uint64_t r = 0;
+    for (int i = 0; i < 64; ++i) { r = (r << 1) | (n & 1); n >>= 1; }
+    return r;
+#endif
+}
+
+// InverseRadicalInverse<base>(inverse, nDigits) (lowdiscrepancy.h:82-91)
+WF_HD uint64_t inverse_radical_inverse(uint32_t base, uint64_t inverse, uint32_t nDigits) {
+    uint64_t index = 0;
+    for (uint32_t i = 0; i < nDigits; ++i) {
+        const uint64_t digit = inverse % base;
+        inverse /= base;
+        index = index * base + digit;
+    }
+    return index;
+}
+
+// GlobalSampler::GetIndexForSample: the index of sample `s` of full-frame pixel (px, py) in the global sequence.
+WF_HD uint64_t sampler_index(const WfSampler &S, int32_t px, int32_t py, uint32_t s) {
+    if (S.kind == WF_SAMPLER_HALTON) {
+        // HaltonSampler::GetIndexForSample (halton.cpp:96-116); kMaxResolution = 128
+        uint64_t offset = 0;
+        if (S.stride > 1) {
+            const uint32_t pmx = (uint32_t)(((px % 128) + 128) % 128), pmy = (uint32_t)(((py % 128) + 128) % 128);
+            const uint64_t d0 = inverse_radical_inverse(2, pmx, S.baseExp0);
+            const uint64_t d1 = inverse_radical_inverse(3, pmy, S.baseExp1);
+            offset += d0 * (S.stride / S.baseScale0) * S.multInv0;
+            offset += d1 * (S.stride / S.baseScale1) * S.multInv1;
+            offset %= S.stride;
+        }
+        return offset + (uint64_t)s * S.stride;
+    }
+    if (S.kind == WF_SAMPLER_SOBOL) {
+        // SobolIntervalToIndex(log2Resolution, sampleNum, currentPixel - sampleBounds.pMin) (lowdiscrepancy.h:229-250)
+        const uint32_t m = S.log2Res;
+        if (m == 0) return 0;
+        uint64_t frame = s;
+        uint64_t index = frame << (m << 1);
+        uint64_t delta = 0;
+        for (int c = 0; frame; frame >>= 1, ++c)
+            if (frame & 1) delta ^= S.vdc[c];
+        uint64_t b = (((uint64_t)((uint32_t)(px - S.sbMinX)) << m) | ((uint32_t)(py - S.sbMinY))) ^ delta;
+        for (int c = 0; b; b >>= 1, ++c)
+            if (b & 1) index ^= S.vdcInv[c];
+        return index;
+    }
+    return s;
+}
+
+// RadicalInverseSpecialized<base> (lowdiscrepancy.cpp:389-403); the digits of `a` come off with 32-bit divisions whenever
+// a < 2^32 (every frame this library is asked for: stride <= 128 * 243), the reversed number is kept in 64 bits.
+WF_HD float radical_inverse(uint32_t base, uint64_t a) {
+    const float invBase = 1.f / (float)base;
+    uint64_t rev = 0;
+    float invBaseN = 1.f;
+    while (a >> 32) {
+        const uint64_t next = a / base, digit = a - next * base;
+        rev = rev * base + digit;
+        invBaseN *= invBase;
+        a = next;
+    }
+    uint32_t a32 = (uint32_t)a;
+    while (a32) {
+        const uint32_t next = a32 / base, digit = a32 - next * base;
+        rev = rev * base + digit;
+        invBaseN *= invBase;
+        a32 = next;
+    }
+    return smin((float)rev * invBaseN, kOneMinusEps);
+}
+// ScrambledRadicalInverseSpecialized<base> (lowdiscrepancy.cpp:405-424)
+WF_HD float scrambled_radical_inverse(uint32_t base, const uint16_t *perm, uint64_t a) {
+    const float invBase = 1.f / (float)base;
+    uint64_t rev = 0;
+    float invBaseN = 1.f;
+    while (a >> 32) {
+        const uint64_t next = a / base, digit = a - next * base;
+        rev = rev * base + perm[digit];
+        invBaseN *= invBase;
+        a = next;
+    }
+    uint32_t a32 = (uint32_t)a;
+    while (a32) {
+        const uint32_t next = a32 / base, digit = a32 - next * base;
+        rev = rev * base + perm[digit];
+        invBaseN *= invBase;
+        a32 = next;
+    }
+    return smin(invBaseN * ((float)rev + invBase * (float)perm[0] / (1.f - invBase)), kOneMinusEps);
+}
+
+// GlobalSampler::SampleDimension of the sample with global index `index` at full-frame pixel (px, py).
+WF_HD float sampler_dim(const WfSampler &S, uint64_t index, uint32_t dim, int32_t px, int32_t py, uint32_t pixOrd, uint32_t s) {
+    if (S.kind == WF_SAMPLER_HALTON) {
+        // HaltonSampler::SampleDimension (halton.cpp:118-127)
+        if (dim == 0) return (float)((double)reverse_bits64(index >> S.baseExp0) * 0x1p-64);   // RadicalInverse base 2 (:427-435)
+        if (dim == 1) return radical_inverse(3, index / S.baseScale1);
+        if (dim >= S.nDims) dim = S.nDims - 1;   // host rejects frames that can get here (max_depth vs. table size)
+        const HaltonDim di = S.dimInfo[dim];
+        return scrambled_radical_inverse(di.prime, S.perms + di.offset, index);
+    }
+    if (S.kind == WF_SAMPLER_SOBOL) {
+        // SobolSampler::SampleDimension (sobol.cpp:48-60) over SobolSampleFloat (lowdiscrepancy.h:252-266), scramble 0
+        if (dim >= (uint32_t)kSobolDims) dim = kSobolDims - 1;
+        uint32_t v = 0;
+        uint64_t a = index;
+        for (uint32_t i = dim * kSobolMatrixSize; a != 0; a >>= 1, i++)
+            if (a & 1) v ^= S.sobol32[i];
+        float sv = smin((float)v * 0x1p-32f, kOneMinusEps);
+        if (dim < 2) {
+            sv = sv * (float)(int32_t)S.res + (float)(dim == 0 ? S.sbMinX : S.sbMinY);
+            sv = clampf(sv - (float)(dim == 0 ? px : py), 0.f, kOneMinusEps);
+        }
+        return sv;
+    }
+    return hash_sample(S.seed, pixOrd, s, dim);
+}
+
+}  // namespace b200rt

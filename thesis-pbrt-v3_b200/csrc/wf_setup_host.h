@@ -1,0 +1,14 @@
+// Host-side set-up shared by the wavefront driver (wavefront.cu) and the host-compiled check of the shade stage
+// (tests/hostshade): tile layout of a render description and the material record -> lobe list conversion.
+#pragma once
+#include "wf_shade.cuh"
+
+namespace b200rt {
+int set_error(int code, const char *fmt, ...);
+int tiling_of(const b200rt_render_desc *d, WfTiling *t);
+// One material record -> its lobes, in the order the material's ComputeScatteringFunctions adds BxDFs.
+// rec: `stride` floats (b200rt_wavefront.h).  out: kMatFloats floats.  Returns false (with the error set) on a bad record.
+bool material_lobes(const float *rec, uint32_t stride, uint32_t index, float *out, bool *hasSpecular);
+// Light block of WfParams from the description; returns an error code for unsupported / inconsistent lights.
+int light_of(const b200rt_render_desc *d, uint32_t n_prims, WfLight *Lt);
+}  // namespace b200rt
