@@ -20,6 +20,8 @@ typedef struct ref_accel ref_accel;   // shared_ptr<Primitive> aggregate built b
 // (pure Translate object-to-world, as in scenes/killeroo-simple:20-24).
 ref_scene *ref_scene_create(const float *P, int n_verts, const int *indices, int n_tris,
                             const float *uv, const float *spheres, int n_spheres);
+ref_scene *ref_scene_create2(const float *P, int n_verts, const int *indices, int n_tris, const float *uv,
+                             const float *N, int reverse_orientation, const float *spheres, int n_spheres);
 void ref_scene_destroy(ref_scene *);
 int ref_scene_num_prims(const ref_scene *);
 

@@ -55,6 +55,31 @@ extern "C" ref_scene *ref_scene_create(const float *P, int n_verts, const int *i
     for (size_t i = 0; i < s->prims.size(); ++i) s->index[s->prims[i].get()] = (int)i;
     return s;
 }
+// ref_scene_create + per-vertex normals N (n_verts x 3, nullable; kept by the mesh as TriangleMesh::n) and the shape's
+// reverseOrientation flag (`ReverseOrientation` in a scene file): what Triangle::Intersect's shading-geometry tail reads.
+extern "C" ref_scene *ref_scene_create2(const float *P, int n_verts, const int *indices, int n_tris, const float *uv,
+                                        const float *N, int reverse_orientation, const float *spheres, int n_spheres) {
+    ref_scene *s = ref_scene_create(nullptr, 0, nullptr, 0, nullptr, spheres, n_spheres);
+    std::vector<std::shared_ptr<Primitive>> sph;
+    sph.swap(s->prims);
+    MediumInterface mi;
+    if (n_tris > 0) {
+        std::vector<Point3f> p(n_verts);
+        for (int i = 0; i < n_verts; ++i) p[i] = Point3f(P[3 * i], P[3 * i + 1], P[3 * i + 2]);
+        std::vector<Point2f> uvs;
+        if (uv) { uvs.resize(n_verts); for (int i = 0; i < n_verts; ++i) uvs[i] = Point2f(uv[2 * i], uv[2 * i + 1]); }
+        std::vector<Normal3f> ns;
+        if (N) { ns.resize(n_verts); for (int i = 0; i < n_verts; ++i) ns[i] = Normal3f(N[3 * i], N[3 * i + 1], N[3 * i + 2]); }
+        std::vector<std::shared_ptr<Shape>> shapes =
+            CreateTriangleMesh(&g_identity, &g_identity, reverse_orientation != 0, n_tris, indices, n_verts, p.data(), nullptr,
+                               N ? ns.data() : nullptr, uv ? uvs.data() : nullptr, nullptr, nullptr);
+        for (auto &sh : shapes) s->prims.push_back(std::make_shared<GeometricPrimitive>(sh, nullptr, nullptr, mi));
+    }
+    for (auto &q : sph) s->prims.push_back(q);
+    s->index.clear();
+    for (size_t i = 0; i < s->prims.size(); ++i) s->index[s->prims[i].get()] = (int)i;
+    return s;
+}
 extern "C" void ref_scene_destroy(ref_scene *s) { delete s; }
 extern "C" int ref_scene_num_prims(const ref_scene *s) { return (int)s->prims.size(); }
 extern "C" void ref_free(void *p) { std::free(p); }

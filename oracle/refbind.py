@@ -32,6 +32,14 @@ def bind(path):
         L = C.CDLL(path)
         L.ref_scene_create.restype = C.c_void_p
         L.ref_scene_create.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int]
+        if hasattr(L, "ref_scene_create2"):
+            L.ref_scene_create2.restype = C.c_void_p
+            L.ref_scene_create2.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int]
+        if hasattr(L, "ref_trace_enable"):
+            L.ref_trace_enable.argtypes = [C.c_int]
+            L.ref_trace_records.restype = C.c_uint64
+            L.ref_trace_copy.argtypes = [C.c_void_p]
+            L.ref_camera_matrices.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
         L.ref_scene_destroy.argtypes = [C.c_void_p]
         L.ref_scene_num_prims.argtypes = [C.c_void_p]
         L.ref_loopsubdiv.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_void_p),
@@ -67,15 +75,22 @@ def _p(a):
 class RefScene:
     """vector<shared_ptr<Primitive>>: one GeometricPrimitive per triangle, then the spheres."""
 
-    def __init__(self, P, indices, uv=None, spheres=None, L=None):
+    def __init__(self, P, indices, uv=None, spheres=None, L=None, normals=None, reverse_orientation=False):
+        """normals: optional (n_verts, 3) per-vertex normals (TriangleMesh::n); reverse_orientation: the shape's
+        `ReverseOrientation` flag."""
         self.L = L or lib()
         self.P = np.ascontiguousarray(P, np.float32).reshape(-1, 3)
         self.idx = np.ascontiguousarray(indices, np.int32).reshape(-1, 3)
         self.uv = None if uv is None else np.ascontiguousarray(uv, np.float32).reshape(-1, 2)
         self.spheres = None if spheres is None else np.ascontiguousarray(spheres, np.float32).reshape(-1, 4)
         ns = 0 if self.spheres is None else len(self.spheres)
-        self.h = self.L.ref_scene_create(_p(self.P), len(self.P), _p(self.idx), len(self.idx), _p(self.uv),
-                                        _p(self.spheres), ns)
+        self.N = None if normals is None else np.ascontiguousarray(normals, np.float32).reshape(-1, 3)
+        if self.N is not None or reverse_orientation:
+            self.h = self.L.ref_scene_create2(_p(self.P), len(self.P), _p(self.idx), len(self.idx), _p(self.uv), _p(self.N),
+                                              int(bool(reverse_orientation)), _p(self.spheres), ns)
+        else:
+            self.h = self.L.ref_scene_create(_p(self.P), len(self.P), _p(self.idx), len(self.idx), _p(self.uv),
+                                            _p(self.spheres), ns)
         self.n_prims = self.L.ref_scene_num_prims(self.h)
 
     def prim_intersect(self, prim, rays):
@@ -159,6 +174,30 @@ class RefAccel:
         if getattr(self, "h", None):
             self.L.ref_accel_destroy(self.h)
             self.h = None
+
+
+def trace_render(scene, *args, **kw):
+    """render(..., n_threads=1) with the event trace on: returns (render's result, records (n, 16) uint32) — every
+    sampler call and every ray of the render in execution order (oracle/ref/ref_render.cpp, tests/hostwf.parse_trace)."""
+    kw["n_threads"] = 1
+    scene.L.ref_trace_enable(1)
+    try:
+        out = render(scene, *args, **kw)
+        n = scene.L.ref_trace_records()
+        rec = np.zeros((n, 16), np.uint32)
+        scene.L.ref_trace_copy(rec.ctypes.data)
+    finally:
+        scene.L.ref_trace_enable(0)
+    return out, rec
+
+
+def camera_matrices(eye, look, up, fov, xres, yres, camera_matrix=None):
+    """(RasterToCamera, CameraToWorld) 4x4 of the PerspectiveCamera ref_render builds."""
+    cam = np.array(list(eye) + list(look) + list(up) + [fov], np.float32)
+    r2c, c2w = np.zeros(16, np.float32), np.zeros(16, np.float32)
+    m = None if camera_matrix is None else np.ascontiguousarray(camera_matrix, np.float32).reshape(16)
+    lib().ref_camera_matrices(_p(cam), xres, yres, _p(m), _p(r2c), _p(c2w))
+    return r2c.reshape(4, 4), c2w.reshape(4, 4)
 
 
 def render(scene, accel_kind, eye, look, up, fov, xres, yres, spp, maxdepth, light_pos, light_I, kd,

@@ -159,3 +159,17 @@ extern "C" void hs_shade(const hs_ctx *c, uint32_t depth, uint64_t start, uint32
     }
     nOut[0] = nNext; nOut[1] = nSh; nOut[2] = nMis;
 }
+
+// sin_ref / cos_ref (wf_core.cuh) against this machine's libm sinf / cosf over the float bit patterns [lo, hi) with the given
+// stride, both signs; returns the number of mismatches.
+#include <cmath>
+extern "C" uint64_t hs_sincos_check(uint32_t lo, uint32_t hi, uint32_t stride) {
+    uint64_t bad = 0;
+    for (uint32_t u = lo; u < hi; u += stride)
+        for (int sg = 0; sg < 2; ++sg) {
+            const float x = u2f(u | (sg ? 0x80000000u : 0u));
+            const float a = sinf(x), b = sin_ref(x), c = cosf(x), d = cos_ref(x);
+            bad += (f2u(a) != f2u(b)) + (f2u(c) != f2u(d));
+        }
+    return bad;
+}

@@ -246,3 +246,74 @@ def _after_uscattering(ev, k):
             return False
         j -= 1
     return j >= 0 and n2d == 2
+
+
+def reference_trace(case, spp, res, sampler="halton"):
+    """Runs the reference's own renderer on shade_cases.build(case) single-threaded with the event trace on.
+    Returns (built case, rgb image, (n_closest, n_shadow), parsed samples)."""
+    import shade_cases
+    from oracle import refbind as rb
+    c = shade_cases.build(case, res)
+    S = rb.RefScene(**c["ref"])
+    r = dict(c["render"])
+    rres = c.get("res", res)
+    (img, nc, ns), rec = rb.trace_render(S, "bvh", r.pop("eye"), r.pop("look"), r.pop("up"), r.pop("fov"), rres, rres, spp,
+                                         c["maxdepth"], r.pop("light_pos"), r.pop("light_I"), r.pop("kd"), sampler=sampler, **r)
+    return c, img, (nc, ns), parse_trace(rec)
+
+
+def ulp_diff(a, b):
+    """Largest distance in units in the last place between two float32 arrays (same shape)."""
+    a, b = np.ascontiguousarray(a, np.float32), np.ascontiguousarray(b, np.float32)
+    ia, ib = a.view(np.int32).astype(np.int64), b.view(np.int32).astype(np.int64)
+    ia = np.where(ia < 0, -(ia & 0x7fffffff), ia)
+    ib = np.where(ib < 0, -(ib & 0x7fffffff), ib)
+    return np.abs(ia - ib)
+
+
+def compare_queues(queues, ref_queues, desc, n_slots):
+    """queues: {q: dict(rays, path)} of a wavefront render (host or device); ref_queues: trace_queues(...) of the reference.
+    Returns {q: dict(n, n_ref, missing, origin_diff, dir_diff, max_ulp_dir)}: entries are matched by (pixel, sample)."""
+    from b200rt import wavefront as wf
+    x, y, s, _ = wf.slot_pixels(desc, n_slots)
+    c = desc.crop
+    x0, y0 = (c[0], c[2]) if (c[0] or c[1] or c[2] or c[3]) else (0, 0)
+    out = {}
+    for q in sorted(set(queues) | set(ref_queues)):
+        Q = queues.get(q, dict(rays=np.zeros((0, 8), np.float32), path=np.zeros(0, np.uint32)))
+        ref = ref_queues.get(q, {})
+        n = len(Q["rays"])
+        st = dict(n=n, n_ref=len(ref), missing=0, origin_diff=0, dir_diff=0, tmax_diff=0, max_ulp_dir=0, max_ulp_origin=0)
+        if n:
+            keys = list(zip((x[Q["path"]] + x0).tolist(), (y[Q["path"]] + y0).tolist(), s[Q["path"]].tolist()))
+            want = np.zeros((n, 7), np.float32)
+            have = np.ones(n, bool)
+            for i, k in enumerate(keys):
+                e = ref.get(k)
+                if e is None:
+                    have[i] = False
+                else:
+                    want[i] = e[1]
+            st["missing"] = int((~have).sum())
+            r = Q["rays"][have]
+            w = want[have]
+            uo, ud = ulp_diff(r[:, 0:3], w[:, 0:3]), ulp_diff(r[:, 4:7], w[:, 3:6])
+            st["origin_diff"] = int((uo.max(1) > 0).sum()) if len(r) else 0
+            st["dir_diff"] = int((ud.max(1) > 0).sum()) if len(r) else 0
+            st["tmax_diff"] = int((r[:, 3].view(np.uint32) != w[:, 6].view(np.uint32)).sum())
+            st["max_ulp_dir"] = int(ud.max()) if len(r) else 0
+            st["max_ulp_origin"] = int(uo.max()) if len(r) else 0
+        out[q] = st
+    return out
+
+
+def image_stats(rgb, ref):
+    """Per-pixel comparison of two (h, w, 3) images: relative RMSE over the frame, and the pixels that differ by more than
+    1e-3 of their own value (visibility / Russian-roulette flips show up here)."""
+    rgb, ref = rgb.astype(np.float64), ref.astype(np.float64)
+    d = rgb - ref
+    rel_rmse = float(np.sqrt((d ** 2).mean()) / max(np.sqrt((ref ** 2).mean()), 1e-30))
+    differ = np.abs(d).max(-1) > 1e-3 * np.maximum(np.abs(ref).max(-1), 1e-6)
+    ok = ~differ
+    rel_rmse_ok = float(np.sqrt((d[ok] ** 2).mean()) / max(np.sqrt((ref[ok] ** 2).mean()), 1e-30)) if ok.any() else 0.0
+    return dict(rel_rmse=rel_rmse, differing=int(differ.sum()), frac_differing=float(differ.mean()), rel_rmse_excl=rel_rmse_ok)

@@ -1,0 +1,121 @@
+"""TEST INFRASTRUCTURE ONLY.  Scenes of the matched-sample parity tests, described once for both sides: the reference's
+own renderer (oracle/refbind.render: SamplerIntegrator::Render + PathIntegrator::Li over reference Materials / Lights)
+and the wavefront driver (b200rt.WavefrontPathIntegrator over the same geometry, light and material records)."""
+import numpy as np
+
+
+def _lookat(sc):
+    la = sc["camera"]["lookat"]
+    return la[0:3], la[3:6], la[6:9], sc["camera"]["fov"]
+
+
+def _bumpy_sphere(n=24, seed=3):
+    """A lumpy sphere mesh with smooth per-vertex normals and a (u, v) parameterisation, Triangle.Watertight-style
+    (src/tests/shapes.cpp:28-60 builds the same kind of mesh)."""
+    rng = np.random.default_rng(seed)
+    u, v = np.meshgrid(np.linspace(0, 1, n + 1), np.linspace(0.02, 0.98, n + 1), indexing="ij")
+    th, ph = v * np.pi, u * 2 * np.pi
+    r = 1 + 0.15 * np.sin(3 * ph) * np.sin(4 * th) + 0.02 * rng.standard_normal(th.shape)
+    r[-1] = r[0]
+    P = np.stack([r * np.sin(th) * np.cos(ph), r * np.sin(th) * np.sin(ph), r * np.cos(th)], -1).reshape(-1, 3)
+    N = np.stack([np.sin(th) * np.cos(ph), np.sin(th) * np.sin(ph), np.cos(th)], -1).reshape(-1, 3)
+    N += 0.1 * rng.standard_normal(N.shape)
+    UV = np.stack([u, v], -1).reshape(-1, 2)
+    i, j = np.meshgrid(np.arange(n), np.arange(n), indexing="ij")
+    a = (i * (n + 1) + j).ravel()
+    idx = np.concatenate([np.stack([a, a + n + 1, a + n + 2], 1), np.stack([a, a + n + 2, a + 1], 1)])
+    return P.astype(np.float32), N.astype(np.float32), UV.astype(np.float32), idx.astype(np.int32)
+
+
+def build(name, res=48):
+    """Returns a dict:
+       ref      : kwargs of refbind.RefScene (P, indices, uv, spheres, normals, reverse_orientation)
+       render   : kwargs of refbind.render after (scene, accel) — eye .. kd, plus extras
+       integ    : kwargs of WavefrontPathIntegrator (without sampler / spp)
+       accel    : (verts, kwargs) for B200Accel / OracleAccel (prim_kind, spheres, tri_uvs, tri_normals, prim_flags)
+       maxdepth, mis (bool: the light has area)"""
+    from b200rt import scenes
+    out = dict(mis=False, maxdepth=5)
+    if name == "sponza_point":
+        sc = scenes.sponza_standin(detail=0.05, xres=res, yres=res)
+        tv = sc["tri_verts"]
+        eye, look, up, fov = _lookat(sc)
+        I, kd = (1.0, .9, .8), (.6, .5, .4)
+        out.update(ref=dict(P=tv.reshape(-1, 3), indices=np.arange(3 * len(tv), dtype=np.int32).reshape(-1, 3)),
+                   render=dict(eye=eye, look=look, up=up, fov=fov, light_pos=sc["light"], light_I=I, kd=kd),
+                   integ=dict(camera=sc["camera"], light_pos=sc["light"], light_I=I, kd=kd), accel=(tv, {}))
+        return out
+    if name.startswith("killeroo_"):
+        sc = scenes.killeroo_simple(xres=res, yres=res)
+        eye, look, up, fov = _lookat(sc)
+        verts, prim_kind, rows, pm, mats = scenes.with_sphere_light(sc, plastic=True)
+        kind = name[len("killeroo_"):]
+        if kind == "glass":
+            mats = scenes.specular_materials(sc)
+            out["maxdepth"] = 8
+        elif kind == "metal":
+            mats = scenes.metal_materials(sc)
+        elif kind == "oren":
+            mats = scenes.metal_materials(sc, oren_nayar=True)
+        tv = sc["tri_verts"]
+        sl = sc["sphere_light"]
+        prim_mat = np.concatenate([mats[sc["prim_material"]], np.zeros((1, 8), np.float32)])
+        spheres = np.array([list(sl["center"]) + [sl["radius"]]], np.float32)
+        render = dict(eye=eye, look=look, up=up, fov=fov, light_pos=sl["center"], light_I=sl["L"], kd=(.5, .5, .5), prim_mat=prim_mat)
+        integ = dict(camera=sc["camera"], light_pos=sl["center"], light_I=sl["L"], materials=mats, prim_material=pm)
+        if kind == "infinite":
+            # LightSource "infinite" with a constant map under a rotated LightToWorld, camera through a `Transform [...]` CTM
+            # (what scenes/living-room does); the emitter sphere stays in the aggregate as a black matte primitive
+            c, s_ = np.cos(0.7), np.sin(0.7)
+            l2w = np.array([[c, 0, s_, 0], [0, 1, 0, 0], [-s_, 0, c, 0], [0, 0, 0, 1]], np.float32) @ \
+                np.array([[1, 0, 0, 0], [0, 0, -1, 0], [0, 1, 0, 0], [0, 0, 0, 1]], np.float32)
+            from b200rt import wavefront as wf
+            render.update(infinite=((1.0, 0.9, 0.8), l2w), light_I=(1.0, 0.9, 0.8))
+            del integ["light_pos"]
+            integ.update(light_I=(1.0, 0.9, 0.8), infinite_light=(l2w[:3, :3], wf.world_radius(verts)))
+            out["mis"] = True
+            out["infinite_scene"] = True
+        else:
+            render["emitter_L"] = sl["L"]
+            integ["sphere_light"] = (sl["radius"], len(verts) - 1)
+            out["mis"] = True
+        out.update(ref=dict(P=tv.reshape(-1, 3), indices=np.arange(3 * len(tv), dtype=np.int32).reshape(-1, 3), spheres=spheres),
+                   render=render, integ=integ, accel=(verts, dict(prim_kind=prim_kind, spheres=rows)))
+        return out
+    if name == "feet_distant":
+        sc = scenes.killeroo_feet(xres=res * 4, yres=res * 4)
+        eye, look, up, fov = _lookat(sc)
+        tv = sc["tri_verts"]
+        from b200rt import wavefront as wf
+        out.update(ref=dict(P=tv.reshape(-1, 3), indices=np.arange(3 * len(tv), dtype=np.int32).reshape(-1, 3)),
+                   render=dict(eye=eye, look=look, up=up, fov=fov, light_pos=(0, 0, 0), light_I=(1, 1, 1), kd=(.5, .5, .5),
+                               prim_mat=np.repeat(sc["materials"], len(tv), 0), distant=(sc["light_from"], sc["light_to"]),
+                               cropwindow=sc["cropwindow"]),
+                   integ=dict(camera=sc["camera"], light_I=(1, 1, 1), materials=sc["materials"], prim_material=np.zeros(len(tv), np.uint8),
+                              distant_light=(sc["light_dir"], wf.world_radius(tv)), crop=sc["crop"]),
+                   accel=(tv, {}), res=res * 4)
+        return out
+    if name in ("normals", "normals_flipped"):
+        # vertex normals (interpolated shading normal, triangle.cpp:348-400), a real (u, v) parameterisation (dpdu frame) and,
+        # for normals_flipped, `ReverseOrientation`; two-lobe plastic so that the frame matters for both lobes
+        P, N, UV, idx = _bumpy_sphere()
+        flip = name == "normals_flipped"
+        tv = P[idx].reshape(-1, 9)
+        tn = N[idx].reshape(-1, 9)
+        tuv = UV[idx].reshape(-1, 6)
+        cam = scenes.look_at_camera((3.2, 1.1, 0.9), (0, 0, 0), (0, 0, 1), 40.0, res, res)
+        eye, look, up, fov = cam["lookat"][0:3], cam["lookat"][3:6], cam["lookat"][6:9], cam["fov"]
+        mats = np.array([[1, .5, .4, .3, .4, .4, .4, .12]], np.float32)
+        light, I = np.array([4.0, -2.0, 3.0], np.float32), (40.0, 40.0, 40.0)
+        flags = np.full(len(tv), 2 | (1 if flip else 0), np.uint8)
+        out.update(ref=dict(P=P, indices=idx, uv=UV, normals=N, reverse_orientation=flip),
+                   render=dict(eye=eye, look=look, up=up, fov=fov, light_pos=light, light_I=I, kd=(.5, .5, .5),
+                               prim_mat=np.repeat(mats, len(tv), 0)),
+                   integ=dict(camera=cam, light_pos=light, light_I=I, materials=mats, prim_material=np.zeros(len(tv), np.uint8)),
+                   accel=(tv, dict(tri_uvs=tuv, tri_normals=tn, prim_flags=flags)))
+        return out
+    raise KeyError(name)
+
+
+CASES = ["sponza_point", "killeroo_plastic", "killeroo_glass", "killeroo_metal", "killeroo_oren", "killeroo_infinite",
+         "feet_distant", "normals", "normals_flipped"]

@@ -2,109 +2,14 @@
  * queue 0 of the recorded queues = the camera rays; every queue re-traced through the C ABI gives the
    oracle's hits (so the rays the integrator feeds the kernels are answered exactly);
  * tile sharding: rendering ranks 0..N-1 separately and summing equals the N=1 film BIT FOR BIT;
- * the film equals a float64 numpy restatement of the same estimator (same counter-based samples, oracle
-   for visibility) within 2e-4 relative RMSE (float32 shading arithmetic vs float64);
+ * (the shade stage itself is pinned against the reference: tests/test_shade_host.py on the CPU, tests/test_gpu_halton.py
+   on the device);
  * stats are self-consistent."""
 import numpy as np
 import pytest
 from oracle import orcbind as ob
 
 pytestmark = pytest.mark.gpu
-
-
-def _mix32(x):
-    x = np.asarray(x, np.uint32).copy()
-    x ^= x >> np.uint32(16); x *= np.uint32(0x7feb352d); x ^= x >> np.uint32(15); x *= np.uint32(0x846ca68b); x ^= x >> np.uint32(16)
-    return x
-
-
-def _rnd(seed, pix, s, dim):
-    with np.errstate(over="ignore"):
-        h = _mix32(np.uint32(seed) ^ np.uint32(0x9e3779b9))
-        h = _mix32(h ^ pix.astype(np.uint32))
-        h = _mix32(h + s.astype(np.uint32) * np.uint32(0x85ebca6b))
-        h = _mix32(h ^ (np.uint32(dim) * np.uint32(0xc2b2ae35) + np.uint32(0x27d4eb2f)))
-    return (h >> np.uint32(8)).astype(np.float64) * 2.0 ** -24
-
-
-def _reference_film(cam, tv, orc, spp, maxdepth, light, I, kd, seed):
-    """float64 restatement of csrc/wavefront.cu (path.cpp:64-204 with a point light and a matte BSDF)."""
-    xres, yres = cam["xres"], cam["yres"]
-    px, py = np.meshgrid(np.arange(xres), np.arange(yres), indexing="xy")
-    pix = np.repeat((py * xres + px).ravel(), spp)
-    s = np.tile(np.arange(spp), xres * yres)
-    x, y = pix % xres, pix // xres
-    fx = ((x + _rnd(seed, pix, s, 0).astype(np.float32)).astype(np.float32) / np.float32(xres)).astype(np.float64)
-    fy = ((y + _rnd(seed, pix, s, 1).astype(np.float32)).astype(np.float32) / np.float32(yres)).astype(np.float64)
-    sx, sy = 2 * fx - 1, 1 - 2 * fy
-    d = cam["dir"][None].astype(np.float64) + sx[:, None] * cam["right"][None] + sy[:, None] * cam["up"][None]
-    d /= np.linalg.norm(d, axis=1, keepdims=True)
-    o = np.repeat(cam["eye"][None].astype(np.float64), len(d), 0)
-    L = np.zeros((len(d), 3))
-    beta = np.ones((len(d), 3))
-    alive = np.arange(len(d))
-    tvv = tv.reshape(-1, 3, 3).astype(np.float64)
-    kd, I, light = np.asarray(kd, np.float64), np.asarray(I, np.float64), np.asarray(light, np.float64)
-    for depth in range(maxdepth + 1):
-        rays = np.zeros((len(alive), 8), np.float32)
-        rays[:, 0:3], rays[:, 4:7], rays[:, 3] = o, d, np.inf
-        h = orc.intersect(rays, n_threads=8)
-        if depth == maxdepth:
-            break
-        m = h["prim"] != ob.MISS
-        alive, o, d, h = alive[m], rays[m, 0:3].astype(np.float64), rays[m, 4:7].astype(np.float64), h[m]
-        v = tvv[h["prim"]]
-        b = np.stack([h["b0"], h["b1"], h["b2"]], 1).astype(np.float64)
-        p = (b[:, :, None] * v).sum(1)
-        ng = np.cross(v[:, 0] - v[:, 2], v[:, 1] - v[:, 2])
-        ng /= np.linalg.norm(ng, axis=1, keepdims=True)
-        nf = np.where((np.sum(ng * -d, 1) < 0)[:, None], -ng, ng)
-        wl = light[None] - p
-        d2 = np.sum(wl * wl, 1)
-        cosl = np.sum(nf * wl, 1) / np.sqrt(d2)
-        lit = cosl > 0
-        contrib = beta[alive] * kd[None] * I[None] * (np.maximum(cosl, 0) / np.pi / d2)[:, None]
-        # shadow rays: a small normal offset instead of the float32 OffsetRayOrigin (visibility-equivalent here)
-        sgn = np.where(np.sum(wl * ng, 1) < 0, -1.0, 1.0)
-        so = p + ng * sgn[:, None] * 1e-5
-        sh = np.zeros((len(p), 8), np.float32)
-        sh[:, 0:3], sh[:, 4:7], sh[:, 3] = so, light[None] - so, 1 - 1e-4
-        occ = orc.intersect_p(sh, n_threads=8).astype(bool)
-        L[alive] += np.where((lit & ~occ)[:, None], contrib, 0)
-        dim = 2 + 3 * depth
-        pa, sa = pix[alive], s[alive]
-        u0 = 2 * _rnd(seed, pa, sa, dim).astype(np.float32).astype(np.float64) - 1
-        u1 = 2 * _rnd(seed, pa, sa, dim + 1).astype(np.float32).astype(np.float64) - 1
-        big = np.abs(u0) > np.abs(u1)
-        with np.errstate(divide="ignore", invalid="ignore"):
-            r = np.where(big, u0, u1)
-            th = np.where(big, (np.pi / 4) * (u1 / u0), np.pi / 2 - (np.pi / 4) * (u0 / u1))
-        zero = (u0 == 0) & (u1 == 0)
-        dx, dy = np.where(zero, 0, r * np.cos(th)), np.where(zero, 0, r * np.sin(th))
-        dz = np.sqrt(np.maximum(0, 1 - dx * dx - dy * dy))
-        useX = np.abs(nf[:, 0]) > np.abs(nf[:, 1])
-        ilx = 1 / np.sqrt(nf[:, 0] ** 2 + nf[:, 2] ** 2 + 1e-300)
-        ily = 1 / np.sqrt(nf[:, 1] ** 2 + nf[:, 2] ** 2 + 1e-300)
-        ss = np.where(useX[:, None], np.stack([-nf[:, 2] * ilx, 0 * ilx, nf[:, 0] * ilx], 1),
-                      np.stack([0 * ily, nf[:, 2] * ily, -nf[:, 1] * ily], 1))
-        ts = np.cross(nf, ss)
-        wi = ss * dx[:, None] + ts * dy[:, None] + nf * dz[:, None]
-        nb = beta[alive] * kd[None]
-        keep = dz > 0
-        mx = nb.max(1)
-        if depth > 3:
-            q = np.maximum(.05, 1 - mx)
-            rr = _rnd(seed, pa, sa, dim + 2).astype(np.float32).astype(np.float64)
-            kill = (mx < 1) & (rr < q)
-            nb = np.where(((mx < 1) & ~kill)[:, None], nb / (1 - q)[:, None], nb)
-            keep &= ~kill
-        beta[alive] = nb
-        sgn = np.where(np.sum(wi * ng, 1) < 0, -1.0, 1.0)
-        o, d, alive = (p + ng * sgn[:, None] * 1e-5)[keep], wi[keep], alive[keep]
-    film = np.zeros((yres * xres, 4))
-    np.add.at(film[:, :3], pix, L)
-    film[:, 3] = spp
-    return film.reshape(yres, xres, 4)
 
 
 @pytest.fixture(scope="module")
@@ -178,18 +83,6 @@ def test_tile_sharding_area_light_and_materials(gpu, specular):
             assert sum(p[1][k] for p in parts) == st1[k], k
     small, st2 = gpu.WavefrontPathIntegrator(sc["camera"], max_batch=1536, **kw).Render(acc)
     assert np.array_equal(small, full) and st2["mis_rays"] == st1["mis_rays"]
-
-
-def test_film_matches_float64_restatement(gpu, small_scene):
-    sc, acc = small_scene
-    orc = ob.OracleAccel(acc.tree, sc["tri_verts"])
-    kw = dict(spp=4, maxdepth=5, light_pos=sc["light"], light_I=(1, .9, .8), kd=(.6, .5, .4), seed=3)
-    film, _ = gpu.WavefrontPathIntegrator(sc["camera"], **kw).Render(acc)
-    want = _reference_film(sc["camera"], sc["tri_verts"], orc, 4, 5, sc["light"], (1, .9, .8), (.6, .5, .4), 3)
-    rel_rmse = np.sqrt(np.mean((film[..., :3] - want[..., :3]) ** 2)) / np.sqrt(np.mean(want[..., :3] ** 2))
-    # paths whose float32/float64 sample differs in the last ulp can flip a visibility test: allow 1e-2
-    assert rel_rmse < 1e-2, rel_rmse
-    assert abs(film[..., :3].mean() / want[..., :3].mean() - 1) < 2e-3
 
 
 def _blocks(img, k):

@@ -68,8 +68,11 @@ def look_at_camera(eye, look, up, fov_deg, xres, yres):
     aspect = xres / yres
     t = np.tan(np.radians(fov_deg) / 2)
     sx, sy = (aspect, 1.0) if aspect > 1 else (1.0, 1 / aspect)
+    # "lookat" / "fov": what WavefrontPathIntegrator turns into the reference camera's own matrices (camera rays bit-identical
+    # to PerspectiveCamera::GenerateRayDifferential); eye / dir / right / up: the pinhole frame for host-side ray generators
     return dict(eye=eye.astype(np.float32), dir=d.astype(np.float32), right=(right * t * sx).astype(np.float32),
-                up=(newup * t * sy).astype(np.float32), xres=int(xres), yres=int(yres))
+                up=(newup * t * sy).astype(np.float32), xres=int(xres), yres=int(yres),
+                lookat=np.concatenate([eye, look, up]).astype(np.float32), fov=float(fov_deg))
 
 
 def camera_rays(cam, spp=1, seed=0, x0=0, x1=None, y0=0, y1=None):
@@ -256,7 +259,8 @@ def matrix_camera(world_to_camera, fov_deg, xres, yres):
     t = np.tan(np.radians(fov_deg) / 2)
     sx, sy = (aspect, 1.0) if aspect > 1 else (1.0, 1 / aspect)
     return dict(eye=eye.astype(np.float32), dir=d.astype(np.float32), right=(right * t * sx).astype(np.float32),
-                up=(up * t * sy).astype(np.float32), xres=int(xres), yres=int(yres), world_to_camera=np.asarray(world_to_camera, np.float64))
+                up=(up * t * sy).astype(np.float32), xres=int(xres), yres=int(yres), world_to_camera=np.asarray(world_to_camera, np.float64),
+                w2c=np.asarray(world_to_camera, np.float32).reshape(16), fov=float(fov_deg))
 
 
 def living_room(xres=1280, yres=720):

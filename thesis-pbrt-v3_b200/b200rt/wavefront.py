@@ -59,7 +59,7 @@ class WavefrontPathIntegrator:
 
     def __init__(self, camera, spp=8, maxdepth=5, light_pos=(0, 0, 0), light_I=(1, 1, 1), kd=(.5, .5, .5),
                  rank=0, world=1, seed=0, tile_size=16, max_batch=0, sphere_light=None, materials=None,
-                 prim_material=None, distant_light=None, crop=None, infinite_light=None, sampler="hash", sobol_tables=None):
+                 prim_material=None, distant_light=None, crop=None, infinite_light=None, sampler="halton", sobol_tables=None):
         """sphere_light=(radius, prim): `AreaLightSource "area" "color L" light_I` on the full sphere primitive number
         `prim` of the aggregate, centred at light_pos (sampled with MIS like EstimateDirect).  materials: (n, 8) rows
         (kind, Kd.rgb, Ks.rgb, roughness) + prim_material: (n_prims,) uint8 index per primitive.
@@ -88,7 +88,7 @@ class WavefrontPathIntegrator:
         d.sampler = SAMPLERS[sampler]
         if sampler == "sobol":
             if sobol_tables is None:
-                raise ValueError('sampler "sobol" needs sobol_tables')
+                sobol_tables = load_sobol_tables()
             self._sobol = [np.ascontiguousarray(sobol_tables[0], np.uint32).reshape(-1),
                            np.ascontiguousarray(sobol_tables[1], np.uint64).reshape(-1, 52),
                            np.ascontiguousarray(sobol_tables[2], np.uint64).reshape(-1, 52)]
@@ -105,8 +105,10 @@ class WavefrontPathIntegrator:
         if crop is not None:
             d.crop = (C.c_uint32 * 4)(*[int(c) for c in crop])
         if distant_light is not None:
+            # wLight = Normalize(LightToWorld(from - to)) (lights/distant.cpp:44-47): v * (1 / Length), in float
             w = np.asarray(distant_light[0], np.float32)
-            w = w / np.sqrt((w * w).sum(dtype=np.float32))
+            inv = np.float32(1) / np.sqrt(w[0] * w[0] + w[1] * w[1] + w[2] * w[2], dtype=np.float32)
+            w = (w * inv).astype(np.float32)
             d.light_kind, d.light_radius = 2, float(distant_light[1])
             d.light_pos = (C.c_float * 3)(*[float(x) for x in w])
         if infinite_light is not None:
@@ -150,8 +152,9 @@ def world_radius(tri_verts):
     """Bounds3::BoundingSphere of the aggregate's world bound (geometry.h), as DistantLight::Preprocess uses it."""
     v = np.asarray(tri_verts, np.float32).reshape(-1, 3)
     lo, hi = v.min(0), v.max(0)
-    c = (lo + hi) / np.float32(2)
-    return float(np.sqrt(((hi - c) ** 2).sum(dtype=np.float32)))
+    c = (lo + hi) * (np.float32(1) / np.float32(2))   # Point3::operator/(2): multiplication by the reciprocal
+    d = (hi - c).astype(np.float32)
+    return float(np.sqrt(d[0] * d[0] + d[1] * d[1] + d[2] * d[2], dtype=np.float32))
 
 
 HEAT_PLANES = ("primitiveIntersections", "primitiveIntersectionsP", "treeNodeTraversals", "treeNodeTraversalsP",
@@ -190,6 +193,14 @@ def queue_rays(accel, q, ptr=None):
     if n.value:
         api._check(_lib().b200rt_render_queue(accel._h, q, out.ctypes.data_as(C.c_void_p), C.byref(n)))
     return out
+
+
+def load_sobol_tables():
+    """(SobolMatrices32, VdCSobolMatrices, VdCSobolMatricesInv) of the reference's Sampler "sobol" (data/sobol_tables.npz,
+    exported from the compiled reference by tests/golden/make_sobol_tables.py)."""
+    import os
+    z = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "data", "sobol_tables.npz"))
+    return z["matrices32"], z["vdc"], z["vdc_inv"]
 
 
 def queue_paths(accel, q, contrib=False):

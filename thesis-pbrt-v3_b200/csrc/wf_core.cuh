@@ -71,31 +71,65 @@ WF_HD float next_float_down(float v) {
     return u2f(ui);
 }
 
-// sin / cos / acos as the reference's libm gives them: glibc's float functions are correctly rounded except in roughly one
-// case per 10^4; the device evaluates in double and rounds once, which is correctly rounded except in ~1 case per 10^9, so
-// device and reference agree bit for bit on all but a ~1e-4 fraction of the calls (CUDA's own sinf/cosf, 1-2 ulp, would
-// differ on ~20 %).  B200 runs FP64 at half the FP32 rate; these calls are a few per path vertex.
-WF_HD float sin_ref(float x) {
-#ifdef __CUDA_ARCH__
-    return (float)sin((double)x);
-#else
-    return sinf(x);
-#endif
+// sinf / cosf as the reference's libm gives them.  The reference calls std::sin / std::cos on floats (sampling.cpp:129,
+// geometry.h:1805-1813, infinite.cpp:104-105), i.e. glibc's sinf / cosf — since glibc 2.28 the double-precision polynomial
+// scheme of the ARM optimized routines (sysdeps/ieee754/flt-32/s_sinf.c, s_cosf.c, sincosf.h; pinned version on this image:
+// glibc 2.39): reduce x by multiples of pi/2 in double, evaluate a degree-7 (sine) or degree-8 (cosine) polynomial in double,
+// round once to float.  Its result is NOT the correctly rounded sine (the polynomial's error is ~2^-30: it differs from the
+// correctly rounded value on ~1.5 % of the arguments), so matching the reference's sampled directions bit for bit means
+// restating that algorithm — published constants below (tests/test_shade_host.py checks this text against the libm it runs
+// with on 4e7 arguments).  Arguments of 120 and above (never produced by the samplers here) fall back to a double evaluation.
+struct SinCosTab { double c0, c1, c2, c3, c4, s1, s2, s3; };
+WF_HD float sincosf_poly(double x, double x2, bool negCos, int n) {
+    // __sincosf_table[0] / [1] (sincosf_data.c): the second entry negates the cosine coefficients
+    const double sg = negCos ? -1.0 : 1.0;
+    const double c0 = sg * 0x1p0, c1 = sg * -0x1.ffffffd0c621cp-2, c2 = sg * 0x1.55553e1068f19p-5, c3 = sg * -0x1.6c087e89a359dp-10,
+                 c4 = sg * 0x1.99343027bf8c3p-16;
+    const double s1 = -0x1.555545995a603p-3, s2 = 0x1.1107605230bc4p-7, s3 = -0x1.994eb3774cf24p-13;
+    if ((n & 1) == 0) {   // sinf_poly, sine branch
+        const double x3 = x * x2, t1 = s2 + x2 * s3, x7 = x3 * x2, sv = x + x3 * s1;
+        return (float)(sv + x7 * t1);
+    }
+    const double x4 = x2 * x2, t2 = c3 + x2 * c4, t1 = c0 + x2 * c1, x6 = x4 * x2, cv = t1 + x4 * c2;
+    return (float)(cv + x6 * t2);
 }
-WF_HD float cos_ref(float x) {
-#ifdef __CUDA_ARCH__
-    return (float)cos((double)x);
-#else
-    return cosf(x);
-#endif
+WF_HD uint32_t abstop12(float x) { return (f2u(x) >> 20) & 0x7ffu; }
+WF_HD double sincosf_reduce(double x, int &n) {   // reduce_fast without TOINT_INTRINSICS (x86-64): hpi_inv is prescaled by 2^24
+    const double r = x * 0x1.45F306DC9C883p+23;
+    n = ((int32_t)r + 0x800000) >> 24;
+    return x - n * 0x1.921FB54442D18p0;
 }
-WF_HD float acos_ref(float x) {
-#ifdef __CUDA_ARCH__
-    return (float)acos((double)x);
-#else
-    return acosf(x);
-#endif
+WF_HD float sin_ref(float y) {
+    double x = y;
+    if (abstop12(y) < abstop12(0x1.921FB6p-1f)) {   // |y| < pi/4
+        if (abstop12(y) < abstop12(0x1p-12f)) return y;
+        return sincosf_poly(x, x * x, false, 0);
+    }
+    if (abstop12(y) < abstop12(120.0f)) {
+        int n;
+        x = sincosf_reduce(x, n);
+        const double sgn = ((n & 3) == 1 || (n & 3) == 2) ? -1.0 : 1.0;   // sign[n & 3] = {1, -1, -1, 1}
+        return sincosf_poly(x * sgn, x * x, (n & 2) != 0, n);
+    }
+    return (float)sin(x);
 }
+WF_HD float cos_ref(float y) {
+    double x = y;
+    if (abstop12(y) < abstop12(0x1.921FB6p-1f)) {
+        if (abstop12(y) < abstop12(0x1p-12f)) return 1.0f;
+        return sincosf_poly(x, x * x, false, 1);
+    }
+    if (abstop12(y) < abstop12(120.0f)) {
+        int n;
+        x = sincosf_reduce(x, n);
+        const double sgn = ((n & 3) == 1 || (n & 3) == 2) ? -1.0 : 1.0;
+        return sincosf_poly(x * sgn, x * x, (n & 2) != 0, n ^ 1);
+    }
+    return (float)cos(x);
+}
+// acosf (SphericalTheta in InfiniteAreaLight::Pdf_Li only: it enters a MIS weight, never a ray): evaluated in double and
+// rounded once; glibc's float routine can differ from that in the last place.
+WF_HD float acos_ref(float x) { return (float)acos((double)x); }
 
 WF_HD V3 v3(float x, float y, float z) { V3 r; r.x = x; r.y = y; r.z = z; return r; }
 WF_HD V3 vadd(V3 a, V3 b) { return v3(a.x + b.x, a.y + b.y, a.z + b.z); }

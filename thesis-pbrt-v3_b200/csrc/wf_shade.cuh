@@ -349,14 +349,15 @@ WF_HD void shade_vertex(const WfParams &P, uint32_t depth, uint32_t x, uint32_t 
     V3 wi;
     float pdf;
     uint32_t flags;
-    const V3 f = bsdf_sample(bs, it.wo, ub0, ub1, BSDF_ALL, wi, pdf, flags);
+    const V3 woPath = vneg(rayD);   // path.cpp:143 `Vector3f wo = -ray.d`: NOT isect.wo, i.e. not renormalised
+    const V3 f = bsdf_sample(bs, woPath, ub0, ub1, BSDF_ALL, wi, pdf, flags);
     if (spec_black(f) || pdf == 0.f) return;
     V3 nb = spec_mul(beta, spec_div(vmul(f, fabsf(vdot(wi, it.ns))), pdf));
     float es = etaScale;
     const bool spec = (flags & BSDF_SPECULAR) != 0;
     if (FULL && spec && (flags & BSDF_TRANSMISSION)) {
         const float eta = bs.eta;
-        es *= (vdot(it.wo, it.n) > 0) ? (eta * eta) : 1.f / (eta * eta);
+        es *= (vdot(woPath, it.n) > 0) ? (eta * eta) : 1.f / (eta * eta);
     }
     // Russian roulette (path.cpp:190-199)
     const V3 rr = vmul(nb, es);

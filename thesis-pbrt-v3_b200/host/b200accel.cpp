@@ -60,9 +60,9 @@ const B200Accel *B200Accel::current() { return g_current.load(); }
 namespace {
 
 struct Captured {
-    std::vector<float> verts, uvs, spheres;
-    std::vector<uint8_t> kind;
-    bool anyUV = false;
+    std::vector<float> verts, uvs, spheres, normals;
+    std::vector<uint8_t> kind, flags;   // flags: b200rt_scene_desc::prim_flags
+    bool anyUV = false, anyN = false, anyFlag = false;
     uint32_t nSpheres = 0;
 };
 
@@ -72,6 +72,7 @@ bool capture(const std::vector<std::shared_ptr<Primitive>> &prims, Captured *c) 
     c->verts.assign(9 * n, 0.f);
     c->uvs.assign(6 * n, 0.f);
     c->kind.assign(n, 0);
+    c->flags.assign(n, 0);
     for (size_t i = 0; i < n; ++i) {
         auto *gp = dynamic_cast<const GeometricPrimitive *>(prims[i].get());
         if (!gp) {
@@ -97,6 +98,22 @@ bool capture(const std::vector<std::shared_ptr<Primitive>> &prims, Captured *c) 
             } else {
                 uv[0] = 0; uv[1] = 0; uv[2] = 1; uv[3] = 0; uv[4] = 1; uv[5] = 1;
             }
+            // what the shading-geometry tail of Triangle::Intersect reads (triangle.cpp:346-424): per-vertex normals
+            // (interpolated shading normal), the orientation flag; per-vertex tangents (mesh->s) are not on the device
+            if (m->s) {
+                Error("b200: triangle meshes with per-vertex tangents (\"S\") are unsupported");
+                return false;
+            }
+            if (m->n) {
+                if (!c->anyN) { c->normals.assign(9 * n, 0.f); c->anyN = true; }
+                for (int k = 0; k < 3; ++k) {
+                    const Normal3f &q = m->n[tri->v[k]];
+                    c->normals[9 * i + 3 * k] = q.x; c->normals[9 * i + 3 * k + 1] = q.y; c->normals[9 * i + 3 * k + 2] = q.z;
+                }
+                c->flags[i] |= 2;
+            }
+            if (tri->reverseOrientation ^ tri->transformSwapsHandedness) c->flags[i] |= 1;
+            if (c->flags[i]) c->anyFlag = true;
         } else if (auto *sp = dynamic_cast<const Sphere *>(sh)) {
             const Float twoPi = 2 * Pi;
             if (sp->zMin > -sp->radius || sp->zMax < sp->radius || sp->phiMax < twoPi) {
@@ -222,6 +239,8 @@ B200Accel::B200Accel(std::vector<std::shared_ptr<Primitive>> p, const ParamSet &
     }
     d.tri_verts = cap.verts.data();
     d.tri_uvs = cap.anyUV ? cap.uvs.data() : nullptr;
+    d.tri_normals = cap.anyN ? cap.normals.data() : nullptr;
+    d.prim_flags = cap.anyFlag ? cap.flags.data() : nullptr;
     d.n_prims = (uint32_t)prims.size();
     if (cap.nSpheres) { d.prim_kind = cap.kind.data(); d.sphere_params = cap.spheres.data(); d.n_spheres = cap.nSpheres; }
 

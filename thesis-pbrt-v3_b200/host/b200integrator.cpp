@@ -38,9 +38,17 @@
 #include "materials/glass.h"
 #include "materials/metal.h"
 #include "materials/substrate.h"
+#include "materials/uber.h"
 #include "core/film.h"   // Film::pixels / Pixel::stats for "bool generalstats" (no accessor either)
+#include "core/transform.h"       // AnimatedTransform::startTransform
+#include "core/camera.h"          // ProjectiveCamera::RasterToCamera / lensRadius
+#include "cameras/perspective.h"
+#include "core/sampler.h"
+#include "samplers/halton.h"      // HaltonSampler::sampleAtPixelCenter
+#include "samplers/sobol.h"
 #undef private
 #undef protected
+#include "core/sobolmatrices.h"
 
 #include "b200integrator.h"
 #include "b200accel.h"
@@ -126,6 +134,30 @@ void B200WavefrontIntegrator::Render(const Scene &scene) {
     b200rt_render_desc d;
     std::memset(&d, 0, sizeof(d));
     if (!describeCamera(*camera, &d.camera)) return;
+    // The reference camera's own matrices: the device then generates PerspectiveCamera::GenerateRayDifferential's rays bit
+    // for bit (cameras/perspective.cpp:97-143 with lensradius 0; csrc/wf_core.cuh camera_ray_ref)
+    if (const PerspectiveCamera *pc = dynamic_cast<const PerspectiveCamera *>(camera.get())) {
+        if (pc->lensRadius == 0 && !pc->CameraToWorld.actuallyAnimated) {
+            std::memcpy(d.raster_to_camera, pc->RasterToCamera.GetMatrix().m, 64);
+            std::memcpy(d.camera_to_world, pc->CameraToWorld.startTransform->GetMatrix().m, 64);
+            d.camera_exact = 1;
+        }
+    }
+    // The scene's Sampler: "halton" and "sobol" are restated on the device (same values, same dimension order as
+    // PathIntegrator::Li); any other sampler's stream is not reproducible out of order -> the counter hash
+    if (const HaltonSampler *hs = dynamic_cast<const HaltonSampler *>(sampler.get())) {
+        if (hs->sampleAtPixelCenter) { Error("b200wavefront: Sampler \"halton\" \"bool samplepixelcenter\" is not supported"); return; }
+        d.sampler = B200RT_SAMPLER_HALTON;
+    } else if (dynamic_cast<const SobolSampler *>(sampler.get())) {
+        d.sampler = B200RT_SAMPLER_SOBOL;
+        d.sobol_matrices32 = SobolMatrices32;
+        d.sobol_vdc = &VdCSobolMatrices[0][0];
+        d.sobol_vdc_inv = &VdCSobolMatricesInv[0][0];
+        d.sobol_vdc_rows = 25;
+    } else {
+        Warning("b200wavefront: only Sampler \"halton\" and \"sobol\" are reproduced sample for sample; using the counter-hash stream");
+        d.sampler = B200RT_SAMPLER_HASH;
+    }
     const Bounds2i cb = film->croppedPixelBounds;   // Film "cropwindow" (film.cpp:49-57); the film's pixels are the window's
     if (cb.pMin != Point2i(0, 0) || cb.pMax != film->fullResolution) {
         d.crop[0] = (uint32_t)cb.pMin.x; d.crop[1] = (uint32_t)cb.pMax.x;
@@ -241,7 +273,7 @@ void B200WavefrontIntegrator::Render(const Scene &scene) {
             auto it = seen.find(std::make_pair(m, flip));
             if (it == seen.end()) {
                 if (seen.size() >= 256) { Error("b200wavefront: more than 256 materials"); return; }
-                float rec[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+                float rec[20] = {0};
                 if (const PlasticMaterial *pm = dynamic_cast<const PlasticMaterial *>(m)) {
                     if (pm->bumpMap) { Error("b200wavefront: plastic with a bump map is not supported"); return; }
                     Float kd[3], ks[3];
@@ -268,6 +300,19 @@ void B200WavefrontIntegrator::Render(const Scene &scene) {
                     rec[0] = (float)(B200RT_MAT_SUBSTRATE + (sm->remapRoughness ? 0 : B200RT_MAT_NO_REMAP));
                     for (int c = 0; c < 3; ++c) { rec[1 + c] = kd[c]; rec[4 + c] = ks[c]; }
                     rec[7] = sm->nu->Evaluate(si);
+                } else if (const UberMaterial *um = dynamic_cast<const UberMaterial *>(m)) {
+                    // Material "uber" (uber.cpp:45-100): constant textures only, isotropic roughness
+                    if (um->bumpMap || um->roughnessu || um->roughnessv) { Error("b200wavefront: only isotropic uber without a bump map is supported"); return; }
+                    Float kd[3], ks[3], kr[3], kt[3], op[3];
+                    Spectrum(um->Kd->Evaluate(si).Clamp()).ToRGB(kd);
+                    Spectrum(um->Ks->Evaluate(si).Clamp()).ToRGB(ks);
+                    Spectrum(um->Kr->Evaluate(si).Clamp()).ToRGB(kr);
+                    Spectrum(um->Kt->Evaluate(si).Clamp()).ToRGB(kt);
+                    Spectrum(um->opacity->Evaluate(si).Clamp()).ToRGB(op);
+                    rec[0] = (float)(B200RT_MAT_UBER + (um->remapRoughness ? 0 : B200RT_MAT_NO_REMAP));
+                    for (int c = 0; c < 3; ++c) { rec[1 + c] = kd[c]; rec[4 + c] = ks[c]; rec[8 + c] = kr[c]; rec[11 + c] = kt[c]; rec[14 + c] = op[c]; }
+                    rec[7] = um->roughness->Evaluate(si);
+                    rec[17] = um->eta->Evaluate(si);
                 } else if (const MirrorMaterial *mm = dynamic_cast<const MirrorMaterial *>(m)) {
                     if (mm->bumpMap) { Error("b200wavefront: mirror with a bump map is not supported"); return; }
                     Float kr[3];
@@ -294,18 +339,19 @@ void B200WavefrontIntegrator::Render(const Scene &scene) {
                     rec[4] = Clamp(mt->sigma->Evaluate(si), 0, 90);
                 } else {
                     Float kd[3];
-                    if (!lambertianKd(m, kd)) { Error("b200wavefront: only \"matte\", \"plastic\", \"mirror\", smooth \"glass\", \"metal\" and \"substrate\" materials are supported"); return; }
+                    if (!lambertianKd(m, kd)) { Error("b200wavefront: only \"matte\", \"plastic\", \"mirror\", smooth \"glass\", \"metal\", \"substrate\" and \"uber\" materials are supported"); return; }
                     for (int c = 0; c < 3; ++c) rec[1 + c] = kd[c];
                 }
                 it = seen.emplace(std::make_pair(m, flip), (int)seen.size()).first;
-                mats.insert(mats.end(), rec, rec + 8);
+                mats.insert(mats.end(), rec, rec + 20);
             }
             primMat[i] = (uint8_t)it->second;
         }
-        if (mats.size() == 8 && mats[0] == 0.f && d.light_kind == B200RT_LIGHT_POINT) {
-            for (int c = 0; c < 3; ++c) d.kd[c] = mats[1 + c];   // one matte Kd: the lean kernel path
+        if (mats.size() == 20 && mats[0] == 0.f && mats[4] == 0.f && d.light_kind == B200RT_LIGHT_POINT) {
+            for (int c = 0; c < 3; ++c) d.kd[c] = mats[1 + c];   // one Lambertian Kd (sigma 0): the lean kernel path
         } else {
-            d.materials = mats.data(); d.n_materials = (uint32_t)(mats.size() / 8); d.prim_material = primMat.data();
+            d.materials = mats.data(); d.n_materials = (uint32_t)(mats.size() / 20); d.prim_material = primMat.data();
+            d.material_stride = 20;
         }
     }
     d.spp = (uint32_t)sampler->samplesPerPixel;
@@ -355,10 +401,10 @@ void B200WavefrontIntegrator::Render(const Scene &scene) {
 
 B200WavefrontIntegrator *CreateB200WavefrontIntegrator(const ParamSet &params, std::shared_ptr<Sampler> sampler,
                                                        std::shared_ptr<const Camera> camera) {
-    auto envInt = [](const char *name, int dflt) { const char *e = std::getenv(name); return e ? std::atoi(e) : dflt; };
     const int maxDepth = params.FindOneInt("maxdepth", 5);
-    const int rank = params.FindOneInt("rank", envInt("RANK", 0));
-    const int world = params.FindOneInt("world", envInt("WORLD_SIZE", 1));
+    const int rank = params.FindOneInt("rank", 0);
+    // "integer rank" / "integer world" are explicit: a stray WORLD_SIZE in the environment must not make a render partial
+    const int world = params.FindOneInt("world", 1);
     const int seed = params.FindOneInt("seed", 0);
     const bool generalStats = params.FindOneBool("generalstats", false);
     return new B200WavefrontIntegrator(maxDepth, std::move(camera), std::move(sampler), rank, world, seed, generalStats);
