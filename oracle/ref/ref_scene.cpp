@@ -84,6 +84,7 @@ extern "C" void ref_scene_destroy(ref_scene *s) { delete s; }
 extern "C" int ref_scene_num_prims(const ref_scene *s) { return (int)s->prims.size(); }
 extern "C" void ref_free(void *p) { std::free(p); }
 
+static std::vector<float> g_lastSubdivN;
 extern "C" int ref_loopsubdiv(const float *P, int n_verts, const int *indices, int n_indices, int n_levels,
                               float **outP, int *out_n_verts, int **out_indices, int *out_n_tris) {
     ParamSet ps;
@@ -108,7 +109,16 @@ extern "C" int ref_loopsubdiv(const float *P, int n_verts, const int *indices, i
         (*outP)[3 * i] = m->p[i].x; (*outP)[3 * i + 1] = m->p[i].y; (*outP)[3 * i + 2] = m->p[i].z;
     }
     std::memcpy(*out_indices, m->vertexIndices.data(), sizeof(int) * 3 * m->nTriangles);
+    // the limit-surface normals LoopSubdivide hands to CreateTriangleMesh (loopsubdiv.cpp:395-398), as the mesh stores them
+    g_lastSubdivN.clear();
+    if (m->n)
+        for (int i = 0; i < m->nVertices; ++i) { g_lastSubdivN.push_back(m->n[i].x); g_lastSubdivN.push_back(m->n[i].y); g_lastSubdivN.push_back(m->n[i].z); }
     return 0;
+}
+// Per-vertex normals of the LAST ref_loopsubdiv result (n_verts x 3; returns 0 when the mesh has none).
+extern "C" int ref_loopsubdiv_normals(float *out) {
+    if (out) std::memcpy(out, g_lastSubdivN.data(), sizeof(float) * g_lastSubdivN.size());
+    return (int)(g_lastSubdivN.size() / 3);
 }
 
 extern "C" ref_accel *ref_accel_create(ref_scene *s, const char *kind, const char *const *int_names,

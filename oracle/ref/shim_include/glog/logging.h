@@ -55,4 +55,9 @@ struct Voidify { void operator&(const NullStream &) {} void operator&(const Fata
 #define DCHECK_GT(a, b) while (false) CHECK_GT(a, b)
 #define DCHECK_GE(a, b) while (false) CHECK_GE(a, b)
 namespace google { inline void InitGoogleLogging(const char *) {} }
+// glog's command-line flags that src/main/pbrt.cpp sets (no-ops here)
+#include <string>
+static int FLAGS_stderrthreshold = 0, FLAGS_minloglevel = 0, FLAGS_v = 0;
+static bool FLAGS_logtostderr = false;
+static std::string FLAGS_log_dir;
 #endif

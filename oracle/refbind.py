@@ -111,7 +111,7 @@ class RefScene:
             self.h = None
 
 
-def loopsubdiv(P, indices, n_levels):
+def loopsubdiv(P, indices, n_levels, with_normals=False):
     P = np.ascontiguousarray(P, np.float32).reshape(-1, 3)
     idx = np.ascontiguousarray(indices, np.int32).reshape(-1)
     oP, oI = C.c_void_p(), C.c_void_p()
@@ -124,6 +124,12 @@ def loopsubdiv(P, indices, n_levels):
     outI = np.ctypeslib.as_array(C.cast(oI, C.POINTER(C.c_int)), (nt.value, 3)).copy()
     lib().ref_free(oP)
     lib().ref_free(oI)
+    if with_normals:   # the limit-surface normals the reference's mesh carries (TriangleMesh::n)
+        lib().ref_loopsubdiv_normals.argtypes = [C.c_void_p]
+        N = np.zeros((nv.value, 3), np.float32)
+        if lib().ref_loopsubdiv_normals(_p(N)) != nv.value:
+            raise RuntimeError("the subdivided mesh has no normals")
+        return outP, outI, N
     return outP, outI
 
 

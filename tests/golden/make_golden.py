@@ -4,7 +4,7 @@ built from /root/reference by oracle/ref/Makefile).  Run in the build container 
     python tests/golden/make_golden.py
 
 Outputs (tests/golden/):
-  killeroo_mesh.npz      scenes/geometry/killeroo.pbrt after the reference's own LoopSubdivide
+  killeroo_mesh.npz      scenes/geometry/killeroo.pbrt: the control mesh (ctrl_*) and the mesh after the reference's own LoopSubdivide (P, idx, N)
                          (shapes/loopsubdiv.cpp), nlevels 1: P (float32), idx (uint16/uint32)
   ref_small_<kind>.npz   a 600-triangle soup, the reference-built tree (node arrays as exported from
                          the reference's memory), 4096 rays, and the reference's own Intersect /
@@ -41,10 +41,11 @@ def parse_killeroo():
 
 def gen_killeroo():
     P, idx, lv = parse_killeroo()
-    oP, oI = rb.loopsubdiv(P, idx, lv)
+    oP, oI, oN = rb.loopsubdiv(P, idx, lv, with_normals=True)
     print("killeroo: control %d verts / %d tris -> %d verts / %d tris" % (len(P), len(idx) // 3, len(oP), len(oI)))
     it = np.uint16 if len(oP) < 65536 else np.uint32
-    np.savez_compressed(os.path.join(OUT, "killeroo_mesh.npz"), P=oP.astype(np.float32), idx=oI.astype(it))
+    np.savez_compressed(os.path.join(OUT, "killeroo_mesh.npz"), P=oP.astype(np.float32), idx=oI.astype(it), N=oN.astype(np.float32),
+                        ctrl_P=P.astype(np.float32), ctrl_idx=idx.astype(np.uint16 if len(P) < 65536 else np.uint32), ctrl_levels=np.int32(lv))
 
 
 def soup(n, seed):

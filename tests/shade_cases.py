@@ -79,8 +79,19 @@ def build(name, res=48):
             render["emitter_L"] = sl["L"]
             integ["sphere_light"] = (sl["radius"], len(verts) - 1)
             out["mis"] = True
-        out.update(ref=dict(P=tv.reshape(-1, 3), indices=np.arange(3 * len(tv), dtype=np.int32).reshape(-1, 3), spheres=spheres),
-                   render=render, integ=integ, accel=(verts, dict(prim_kind=prim_kind, spheres=rows)))
+        akw = dict(prim_kind=prim_kind, spheres=rows)
+        ref = dict(P=tv.reshape(-1, 3), indices=np.arange(3 * len(tv), dtype=np.int32).reshape(-1, 3), spheres=spheres)
+        if kind == "normals":
+            # scenes/killeroo-simple with the vertex normals its loop-subdivided killeroos carry (the scene as written).  The
+            # reference harness builds ONE mesh, so every triangle gets normals there: the four ground triangles get their
+            # geometric normal at all three vertices (and the flag on this side: both take the mesh-with-normals path for them)
+            tn = sc["tri_normals"].copy()
+            e1, e2 = tv[:4, 0:3] - tv[:4, 6:9], tv[:4, 3:6] - tv[:4, 6:9]
+            tn[:4] = np.tile(np.cross(e1.astype(np.float64), e2.astype(np.float64)), (1, 3)).astype(np.float32)
+            ref["normals"] = tn.reshape(-1, 3)
+            akw.update(tri_normals=np.concatenate([tn, np.zeros((1, 9), np.float32)]),
+                       prim_flags=np.concatenate([np.full(len(tv), 2, np.uint8), np.zeros(1, np.uint8)]))
+        out.update(ref=ref, render=render, integ=integ, accel=(verts, akw))
         return out
     if name == "feet_distant":
         sc = scenes.killeroo_feet(xres=res * 4, yres=res * 4)
@@ -117,5 +128,5 @@ def build(name, res=48):
     raise KeyError(name)
 
 
-CASES = ["sponza_point", "killeroo_plastic", "killeroo_glass", "killeroo_metal", "killeroo_oren", "killeroo_infinite",
+CASES = ["sponza_point", "killeroo_plastic", "killeroo_normals", "killeroo_glass", "killeroo_metal", "killeroo_oren", "killeroo_infinite",
          "feet_distant", "normals", "normals_flipped"]

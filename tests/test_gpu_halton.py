@@ -41,7 +41,7 @@ def _device_queues(gpu, c, spp, sampler):
     return integ, film, st, queues
 
 
-@pytest.mark.parametrize("case,sampler", [("sponza_point", "halton"), ("killeroo_plastic", "halton"), ("killeroo_glass", "halton"),
+@pytest.mark.parametrize("case,sampler", [("sponza_point", "halton"), ("killeroo_plastic", "halton"), ("killeroo_normals", "halton"), ("killeroo_glass", "halton"),
                                           ("killeroo_metal", "halton"), ("killeroo_oren", "halton"), ("killeroo_infinite", "halton"),
                                           ("feet_distant", "halton"), ("normals", "halton"), ("normals_flipped", "halton"),
                                           ("killeroo_metal", "sobol"), ("feet_distant", "sobol")])
@@ -76,6 +76,8 @@ def test_device_rays_are_the_references(gpu, case, sampler):
 IMAGE_CASES = {
     # BASELINE config 1: scenes/killeroo-simple as written — 700 x 700, Sampler "halton" 8 spp, path maxdepth 5, sphere area light, plastic
     "killeroo_plastic": dict(res=700, spp=8),
+    # ... with the vertex normals of its loop-subdivided killeroos (interpolated shading normals, triangle.cpp:348-400)
+    "killeroo_normals": dict(res=700, spp=8),
     # BASELINE config 2 (the bench workload): sponza stand-in, point light, path maxdepth 5, halton
     "sponza_point": dict(res=700, spp=4, full_detail=True),
     # BASELINE config 4: scenes/killeroo-feet through its crop window (res x 4 frame), distant light + plastic

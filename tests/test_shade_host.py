@@ -45,7 +45,7 @@ def test_camera_matrices_equal_the_reference_cameras(built_lib):
     assert np.array_equal(np.array(d.camera_to_world, np.float32).view(np.uint32), c2w.ravel().view(np.uint32))
 
 
-@pytest.mark.parametrize("case", ["sponza_point", "killeroo_plastic", "killeroo_glass", "killeroo_metal", "killeroo_oren",
+@pytest.mark.parametrize("case", ["sponza_point", "killeroo_plastic", "killeroo_normals", "killeroo_glass", "killeroo_metal", "killeroo_oren",
                                   "killeroo_infinite", "feet_distant", "normals", "normals_flipped"])
 def test_every_sample_and_every_ray_is_the_references(built_lib, case):
     _check_case(built_lib, case, "halton")

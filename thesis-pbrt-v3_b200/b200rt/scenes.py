@@ -131,6 +131,18 @@ def _xform(m, P):
     return P @ m[:3, :3].T + m[:3, 3]
 
 
+def killeroo_normals():
+    """Per-vertex limit-surface normals of the subdivided killeroo, as the reference's mesh stores them (object space;
+    LoopSubdivide hands them to CreateTriangleMesh, shapes/loopsubdiv.cpp:395-398)."""
+    z = np.load(os.path.join(_GOLDEN, "killeroo_mesh.npz"))
+    return z["N"].astype(np.float64)
+
+
+def _xform_normals(m, N):
+    """Transform::operator()(Normal3f): multiplication by the inverse transpose of the matrix's 3x3 part."""
+    return N @ np.linalg.inv(m[:3, :3])
+
+
 def killeroo_mesh():
     f = os.path.join(_GOLDEN, "killeroo_mesh.npz")
     z = np.load(f)
@@ -180,8 +192,13 @@ def killeroo_simple(xres=700, yres=700):
     # Scale .5 .5 .5 ; Rotate -60 0 0 1 ; Translate 100 200 -140 ; killeroo ; Translate -200 0 0 ; killeroo (:38-49)
     ctm = _scale(.5, .5, .5) @ _rot_z(-60) @ _translate(100, 200, -140)
     tris.append(_xform(ctm, P)[idx].reshape(-1, 9))
+    # world-space vertex normals (TriangleMesh::n = ObjectToWorld(N)); the ground quads have none (flag bit 1 clear)
+    N = killeroo_normals()
+    normals = [np.zeros((4, 9)), _xform_normals(ctm, N)[idx].reshape(-1, 9)]
     ctm = ctm @ _translate(-200, 0, 0)
     tris.append(_xform(ctm, P)[idx].reshape(-1, 9))
+    normals.append(_xform_normals(ctm, N)[idx].reshape(-1, 9))
+    tn = np.concatenate(normals).astype(np.float32)
     tv = np.concatenate(tris).astype(np.float32) + np.float32(0)
     cam = _killeroo_camera(xres, yres)
     nk = len(idx)
@@ -195,6 +212,7 @@ def killeroo_simple(xres=700, yres=700):
     return dict(name="killeroo-simple", tri_verts=tv, camera=cam, light=np.array([150, 120, 20], np.float32),
                 sphere_light=dict(center=np.array([150, 120, 20], np.float32), radius=3.0, L=np.array([2000.0] * 3, np.float32)),
                 prim_material=prim_material, material_kd=kds, materials=materials,
+                tri_normals=tn, prim_flags=np.concatenate([np.zeros(4, np.uint8), np.full(2 * nk, 2, np.uint8)]),
                 note="reference geometry (fixture); light = the scene's sphere area light (scenes/killeroo-simple:18-24) "
                      "or, for the point-light integrator, a point light at its centre")
 
