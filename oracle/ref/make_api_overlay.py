@@ -1,5 +1,5 @@
 """TEST INFRASTRUCTURE.  The attach mechanism of SURVEY.md §8(b): a scripted two-hunk overlay of the reference's
-src/core/api.cpp, written to the git-ignored build directory (oracle/_ref/obj/api_overlay.cpp — the reference tree is
+src/core/api.cpp, written to the git-ignored build directory (oracle/_ref/objfull/api_overlay.cpp — the reference tree is
 never edited and no reference source is committed), that adds the two name branches a maintainer would add by hand
 (INTEGRATION.md):
 
