@@ -248,8 +248,10 @@ def test_cpp_wavefront_integrator_matches_the_references_render(host, gpu, case)
     cov = blocks(ref).max(-1) > 0   # `feet` covers ~10 % of the frame: RMSE over the covered blocks and their mean
     rm = blocks(ref)[cov].mean()
     assert np.sqrt(((blocks(img) - blocks(ref)) ** 2)[cov].mean()) / rm < (0.03 if case == "killeroo" else 0.085 if glass else 0.04)
-    assert np.sqrt(((blocks(img) - blocks(py)) ** 2)[cov].mean()) / rm < (0.005 if case == "killeroo" else 0.01)
-    assert abs(st["closest_rays"] / nc.value - 1) < 1e-3
+    # the C++ drop-in and the Python mirror hand the device the same description (reference camera matrices, Halton stream,
+    # materials, light): the same film up to the Film's RGB -> XYZ -> RGB round trip, and the same rays
+    assert np.abs(img - py).max() <= 2e-6 * max(1.0, np.abs(py).max()), np.abs(img - py).max()
+    assert (st["closest_rays"], st["shadow_rays"]) == (nc.value, ns.value)
 
 
 @pytest.mark.gpu
@@ -305,8 +307,8 @@ def test_cpp_integrator_renders_living_room(host, gpu):
                                         materials=sc["materials"], prim_material=sc["prim_material"])
     film, st = integ.Render(acc)
     py = film_to_rgb(film).astype(np.float64)
-    assert np.sqrt(((blocks(img) - blocks(py)) ** 2).mean()) / ref.mean() < 0.02
-    assert abs(st["closest_rays"] / nc.value - 1) < 2e-3
+    assert np.abs(img - py).max() <= 2e-6 * max(1.0, np.abs(py).max()), np.abs(img - py).max()
+    assert (st["closest_rays"], st["shadow_rays"]) == (nc.value, ns.value)
 
 
 @pytest.mark.gpu
@@ -368,7 +370,7 @@ def test_cpp_integrator_writes_the_thesis_statistic_matrices(host, gpu, tree):
     ref = g["killeroo_heat"].astype(np.float64)
     for n, k in planes.items():
         a, b = mats[n].astype(np.float64), heat[k].astype(np.float64)
-        assert abs(a.sum() / b.sum() - 1) < 2e-3, (n, a.sum(), b.sum())
+        assert np.array_equal(a, b), (n, a.sum(), b.sum())   # same description, same Halton stream: the same rays
         if tree == "bvh":
             assert abs(a.sum() / ref[k].sum() - 1) < 0.015, (n, a.sum(), ref[k].sum())
             ab = a.reshape(res // 8, 8, res // 8, 8).mean((1, 3))
