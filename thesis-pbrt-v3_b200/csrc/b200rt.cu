@@ -52,11 +52,15 @@ static int g_pblocks[6][2];  // resident persistent blocks per SM, [kind][any]
 static int g_persist_bsp = 1;
 static uint32_t g_bvh_steps = 4;
 static uint32_t g_sstack = 10;     // BVH stack entries kept in shared memory (B200RT_SSTACK; 0 = all in local memory)
+static uint32_t g_toplevels = 5;   // BVH levels staged in shared memory per block (B200RT_TOPLEVELS; 0 = none): 5 levels = 31
+                                   // records = 2 KB per block, +1 % on the path queues; 8 levels cost more L1 than they save
+                                   // (profiles/r02_ab_bvh_toplevels.log)
+static size_t g_bvh_attr[2] = {0, 0};   // MaxDynamicSharedMemorySize currently set on the two BVH kernels
 static uint32_t g_bsp_steps = B200RT_BSP_STEPS;  // B200RT_BSP_STEPS_N
 static uint32_t g_sstack_bsp = 0;
 static int g_minb = 9;             // __launch_bounds__ min blocks/SM variant of the BVH kernels (B200RT_MINB: 8 | 9; 9 = 56 registers, 36 warps/SM: +2 % over 8, 10 spills — profiles/r01_ab_bvh_minblocks.log)
 typedef void (*bvh_kernel_t)(const BvhView, const float4 *, uint64_t, const uint32_t *, b200rt_hit *, uint8_t *, PersistCounters *,
-                             uint32_t, uint32_t, uint32_t, uint32_t);
+                             uint32_t, uint32_t, uint32_t, uint32_t, uint32_t);
 static const void *bvh_fn(bool any) {
     bvh_kernel_t f;
     if (g_minb == 8) f = any ? bvh_persistent_kernel<true, 8> : bvh_persistent_kernel<false, 8>;
@@ -92,7 +96,9 @@ extern "C" int b200rt_init(int device) {
     if (const char *e = getenv("B200RT_BSP_STEPS_N")) g_bsp_steps = (uint32_t)std::max(1, atoi(e));
     if (const char *e = getenv("B200RT_SSTACK_BSP")) g_sstack_bsp = (uint32_t)std::min(64, std::max(0, atoi(e)));
     if (const char *e = getenv("B200RT_SSTACK")) g_sstack = (uint32_t)std::min(64, std::max(0, atoi(e)));
-    // the persistent kernels use no shared memory: give the whole 256 KB array to L1 (node working set)
+    if (const char *e = getenv("B200RT_TOPLEVELS")) g_toplevels = (uint32_t)std::min(B200RT_TOP_MAXLEVELS, std::max(0, atoi(e)));
+    // shared memory of the persistent kernels: the bottom of the traversal stack (+ the staged top levels of the BVH); the
+    // carve-out asks for just that much, the rest of the 256 KB array stays L1 (node working set)
     int carve = 0;
     if (const char *e = getenv("B200RT_CARVEOUT")) carve = atoi(e);
     const size_t smB = (size_t)g_sstack_bsp * 12 * B200RT_PBLOCK;
@@ -109,6 +115,7 @@ extern "C" int b200rt_init(int device) {
         const void *fns[2] = {bvh_fn(false), bvh_fn(true)};
         for (int a = 0; a < 2; ++a) {
             CU(cudaFuncSetAttribute(fns[a], cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+            g_bvh_attr[a] = sm;
             if (bc >= 0) CU(cudaFuncSetAttribute(fns[a], cudaFuncAttributePreferredSharedMemoryCarveout, bc));
             CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_pblocks[B200RT_BVH][a], fns[a], B200RT_PBLOCK, sm));
         }
@@ -228,6 +235,30 @@ static int build_bvh_scene(const b200rt_scene_desc *d, b200rt_scene *s) {
             wide[i] = nInterior++;
         }
     }
+    // Renumber: interior nodes of depth < B200RT_TOP_MAXLEVELS first, level by level (breadth-first), the others after
+    // them in the reference's depth-first order.  Only the device-side record order changes, never the traversal order.
+    uint32_t topCount[12] = {0};
+    {
+        std::vector<uint32_t> depthOf(N, 0);
+        for (uint32_t i = 0; i < N; ++i)
+            if ((ref[i].word & 3u) != 3u) { depthOf[i + 1] = depthOf[i] + 1; depthOf[ref[i].offset] = depthOf[i] + 1; }
+        std::vector<uint32_t> level{0};   // reference node numbers of the current level, in left-to-right order
+        uint32_t next = 0;
+        std::vector<uint8_t> placed(N, 0);
+        for (int lv = 0; lv < B200RT_TOP_MAXLEVELS; ++lv) {
+            std::vector<uint32_t> nxt;
+            for (uint32_t i : level) {
+                if ((ref[i].word & 3u) == 3u) continue;
+                wide[i] = next++; placed[i] = 1;
+                nxt.push_back(i + 1); nxt.push_back((uint32_t)ref[i].offset);
+            }
+            topCount[lv + 1] = next;
+            level.swap(nxt);
+        }
+        for (uint32_t i = 0; i < N; ++i)
+            if ((ref[i].word & 3u) != 3u && !placed[i]) wide[i] = next++;
+        if (next != nInterior) return fail(B200RT_EINVAL, "BVH: inconsistent interior-node numbering");
+    }
     // depth check (the reference's traversal stack holds 64 entries, bvh.cpp:362)
     {
         std::vector<uint32_t> depth(N, 0);
@@ -290,6 +321,7 @@ static int build_bvh_scene(const b200rt_scene_desc *d, b200rt_scene *s) {
     s->bvh.spheres = s->d_spheres;
     for (int k = 0; k < 3; ++k) { s->bvh.root[k] = ref[0].lo[k]; s->bvh.root[3 + k] = ref[0].hi[k]; }
     s->bvh.rootRef = ref_of(0);
+    std::memcpy(s->bvh.topCount, topCount, sizeof(topCount));
     std::memcpy(s->bounds, s->bvh.root, sizeof(s->bounds));
     return B200RT_OK;
 }
@@ -509,13 +541,24 @@ int b200rt::launch_trace(const b200rt_scene *s, const float4 *rays, uint64_t n, 
             uint8_t *oo = any ? occ + off : nullptr;
             const float4 *ri = rays + 2 * off;
 #define PL(fn, view) fn<<<blocks, B200RT_PBLOCK, (size_t)g_sstack_bsp * 12 * B200RT_PBLOCK, st>>>(view, ri, m, n_dev, ho, oo, pc, g_thresh, chunk, g_sstack_bsp, g_bsp_steps)
-#define PLB(fn, view) fn<<<blocks, B200RT_PBLOCK, (size_t)g_sstack * sizeof(uint2) * B200RT_PBLOCK, st>>>(view, ri, m, n_dev, ho, oo, pc, g_thresh, chunk, g_bvh_steps, g_sstack)
             switch (s->kind * 2 + (any ? 1 : 0)) {
                 case B200RT_BVH * 2: case B200RT_BVH * 2 + 1: {
-                    const size_t smem = (size_t)g_sstack * sizeof(uint2) * B200RT_PBLOCK;
+                    uint32_t topN = g_toplevels ? s->bvh.topCount[g_toplevels] : 0u;
+                    const size_t smem = (size_t)g_sstack * sizeof(uint2) * B200RT_PBLOCK + (size_t)topN * sizeof(BvhNode2);
+                    unsigned blk = blocks;
+                    if (topN) {   // experiment path: shared memory per block depends on the scene, so does the residency
+                        // (b200rt_init sets the attribute for the stack alone; the staged records come on top, per scene)
+                        if (g_bvh_attr[any ? 1 : 0] < smem) {
+                            CU(cudaFuncSetAttribute(bvh_fn(any), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+                            g_bvh_attr[any ? 1 : 0] = smem;
+                        }
+                        int per = 0;
+                        CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per, bvh_fn(any), B200RT_PBLOCK, smem));
+                        blk = (unsigned)std::min<uint64_t>((m + chunk * wpb - 1) / (chunk * wpb), (uint64_t)g_sm_count * std::max(1, per));
+                    }
                     void *args[] = {(void *)&s->bvh, (void *)&ri, (void *)&m, (void *)&n_dev, (void *)&ho, (void *)&oo, (void *)&pc,
-                                    (void *)&g_thresh, (void *)&chunk, (void *)&g_bvh_steps, (void *)&g_sstack};
-                    CU(cudaLaunchKernel(bvh_fn(any), dim3(blocks), dim3(B200RT_PBLOCK), args, smem, st));
+                                    (void *)&g_thresh, (void *)&chunk, (void *)&g_bvh_steps, (void *)&g_sstack, (void *)&topN};
+                    CU(cudaLaunchKernel(bvh_fn(any), dim3(blk), dim3(B200RT_PBLOCK), args, smem, st));
                     break;
                 }
                 case B200RT_KDTREE * 2: PL((bsp_persistent_kernel<B200RT_KDTREE, false>), s->bsp); break;

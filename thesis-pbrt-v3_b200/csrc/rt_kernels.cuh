@@ -35,7 +35,12 @@ struct BvhView {
     const float4 *spheres;  // 4 x float4 per sphere: WorldToObject rows 0..2, (radius, -, -, -)
     float root[6];       // nodes[0].bounds of the reference tree
     uint32_t rootRef;
+    // The interior nodes of the top levels come first in the array, level by level: levels [0, k) are the records
+    // [0, topCount[k]), so a block can stage them in shared memory with one contiguous copy (north-star item (3);
+    // B200RT_TOPLEVELS, measured in profiles/r02_ab_bvh_toplevels.log).  Deeper nodes keep the reference's depth-first order.
+    uint32_t topCount[12];
 };
+#define B200RT_TOP_MAXLEVELS 11
 
 // kd / RBSP: the reference's own 8-byte nodes (w0 = split | onePrimitive | indicesOffset,
 // w1 = axis bits + aboveChild/nPrims) + primitiveIndices + triangles in original primitive order.

@@ -97,7 +97,8 @@ bvh_persistent_kernel(const __grid_constant__ BvhView S, const float4 *__restric
                       uint8_t *__restrict__ occluded, PersistCounters *pc, uint32_t thresh,
                       uint32_t chunk /* rays a warp claims per global atomic */,
                       uint32_t steps /* interior steps a lane may take per vote */,
-                      uint32_t sdepth /* stack entries [0, sdepth) live in shared memory, the rest in local */) {
+                      uint32_t sdepth /* stack entries [0, sdepth) live in shared memory, the rest in local */,
+                      uint32_t topN /* the first topN node records (= the top levels, BvhView::topCount) are staged in shared memory */) {
     // Shared-memory bottom of the traversal stack: entry d of thread t sits at sst[d * blockDim + t], i.e. in bank
     // t % 32 whatever d is, so a push/pop by 32 lanes at 32 DIFFERENT depths is still one conflict-free access
     // (the per-thread local array would touch up to 32 different 128-byte lines for the same push).
@@ -106,6 +107,14 @@ bvh_persistent_kernel(const __grid_constant__ BvhView S, const float4 *__restric
     if (n_dev) { const uint32_t m = *n_dev; n = m < n ? m : n; }
     const unsigned FULL = 0xFFFFFFFFu;
     const int lane = threadIdx.x & 31;
+    // Top of the tree in shared memory (north-star item (3)): one cooperative copy per block, behind the stack area.
+    // Off by default (topN = 0): measured slower than leaving those records to L1 (profiles/r02_ab_bvh_toplevels.log).
+    const float4 *stop = reinterpret_cast<const float4 *>(sst + (size_t)sdepth * B200RT_PBLOCK);
+    if (topN) {
+        float4 *w = reinterpret_cast<float4 *>(sst + (size_t)sdepth * B200RT_PBLOCK);
+        for (uint32_t i = threadIdx.x; i < topN * 4u; i += blockDim.x) w[i] = __ldg(reinterpret_cast<const float4 *>(S.nodes) + i);
+        __syncthreads();
+    }
 
     // per-lane traversal state
     RayCtx r;
@@ -169,8 +178,8 @@ bvh_persistent_kernel(const __grid_constant__ BvhView S, const float4 *__restric
                 for (uint32_t k = 0; k < steps && !(cur & B200RT_LEAF_BIT) && cur != B200RT_DONE; ++k) {
                     const BvhNode2 *nd = S.nodes + cur;
                     float4 a, b, c, mf;
-                    ldg256(&nd->a, a, b);
-                    ldg256(&nd->c, c, mf);
+                    if (cur < topN) { const float4 *q = stop + 4 * (size_t)cur; a = q[0]; b = q[1]; c = q[2]; mf = q[3]; }
+                    else { ldg256(&nd->a, a, b); ldg256(&nd->c, c, mf); }
                     const uint4 m = make_uint4(__float_as_uint(mf.x), __float_as_uint(mf.y), __float_as_uint(mf.z), 0u);
                     float t0, t1;
                     bool g0, g1;
