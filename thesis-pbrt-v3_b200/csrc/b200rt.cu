@@ -4,6 +4,7 @@
 // (reference src/core/scene.cpp:45-55 -> src/accelerators/{bvh,kdtreeaccel,rbsp,rbspKd}.cpp).
 // There is no CPU path in this file: every compute entry point needs a CUDA device.
 #include <cuda_runtime.h>
+#include <limits>
 #include <atomic>
 #include <cstdarg>
 #include <cstdio>
@@ -61,8 +62,14 @@ static uint32_t g_sstack_bsp = 0;
 static int g_minb = 9;             // __launch_bounds__ min blocks/SM variant of the BVH kernels (B200RT_MINB: 8 | 9; 9 = 56 registers, 36 warps/SM: +2 % over 8, 10 spills — profiles/r01_ab_bvh_minblocks.log)
 typedef void (*bvh_kernel_t)(const BvhView, const float4 *, uint64_t, const uint32_t *, b200rt_hit *, uint8_t *, PersistCounters *,
                              uint32_t, uint32_t, uint32_t, uint32_t, uint32_t);
+static int g_bvh4 = 0;             // B200RT_BVH4=1: the two-levels-per-record kernel (BvhNode4)
 static const void *bvh_fn(bool any) {
     bvh_kernel_t f;
+    if (g_bvh4) {
+        if (g_minb == 8) f = any ? bvh4_persistent_kernel<true, 8> : bvh4_persistent_kernel<false, 8>;
+        else f = any ? bvh4_persistent_kernel<true, 9> : bvh4_persistent_kernel<false, 9>;
+        return (const void *)f;
+    }
     if (g_minb == 8) f = any ? bvh_persistent_kernel<true, 8> : bvh_persistent_kernel<false, 8>;
     else f = any ? bvh_persistent_kernel<true, 9> : bvh_persistent_kernel<false, 9>;
     return (const void *)f;
@@ -108,10 +115,14 @@ extern "C" int b200rt_init(int device) {
     if (carveB >= 0) CU(cudaFuncSetAttribute(fn, cudaFuncAttributePreferredSharedMemoryCarveout, carveB)); \
     CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_pblocks[k][a], fn, B200RT_PBLOCK, smB))
     {   // BVH kernels: dynamic shared memory = the shared part of the stack
-        const size_t sm = (size_t)g_sstack * sizeof(uint2) * B200RT_PBLOCK;
         if (const char *e = getenv("B200RT_MINB")) g_minb = atoi(e);
+        if (const char *e = getenv("B200RT_BVH4")) g_bvh4 = atoi(e);
         if (g_minb != 8) g_minb = 9;
-        const int bc = g_sstack ? (int)std::min<size_t>(100, ((size_t)g_minb * sm * 100) / (228 * 1024) + 1) : carve;
+        // the shared part of the stack + room for the staged top levels (at most 2^levels - 1 records; the launch passes the
+        // scene's actual count): attribute, carve-out and residency are all taken for this size
+        const size_t sm = (size_t)g_sstack * sizeof(uint2) * B200RT_PBLOCK +
+                          ((g_toplevels && !g_bvh4) ? (((size_t)1 << g_toplevels) - 1) * sizeof(BvhNode2) : 0);
+        const int bc = sm ? (int)std::min<size_t>(100, ((size_t)g_minb * (sm + 1024) * 100) / (228 * 1024) + 1) : carve;
         const void *fns[2] = {bvh_fn(false), bvh_fn(true)};
         for (int a = 0; a < 2; ++a) {
             CU(cudaFuncSetAttribute(fns[a], cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
@@ -304,6 +315,61 @@ static int build_bvh_scene(const b200rt_scene_desc *d, b200rt_scene *s) {
         w.c = make_float4(c1.lo[2], c1.hi[0], c1.hi[1], c1.hi[2]);
         w.m = make_uint4(ref_of(i + 1), ref_of((uint32_t)ref[i].offset), ref[i].word & 3u, ref[i].word >> 2);
     }
+    // ---- BvhNode4: two levels per record (rt_kernels.cuh) ----
+    {
+        std::vector<uint32_t> w4(N, 0xFFFFFFFFu);
+        std::vector<uint32_t> order;          // reference node numbers of the wide records, depth-first
+        if ((ref[0].word & 3u) != 3u) {
+            std::vector<uint32_t> st{0};
+            while (!st.empty()) {
+                const uint32_t i = st.back(); st.pop_back();
+                w4[i] = (uint32_t)order.size(); order.push_back(i);
+                const uint32_t ch[2] = {i + 1, (uint32_t)ref[i].offset};
+                for (int c = 1; c >= 0; --c) {
+                    if ((ref[ch[c]].word & 3u) == 3u) continue;
+                    const uint32_t g[2] = {ch[c] + 1, (uint32_t)ref[ch[c]].offset};
+                    for (int k = 1; k >= 0; --k)
+                        if ((ref[g[k]].word & 3u) != 3u) st.push_back(g[k]);
+                }
+            }
+        }
+        auto ref4_of = [&](uint32_t j) -> uint32_t {
+            return (ref[j].word & 3u) == 3u ? (B200RT_LEAF_BIT | (uint32_t)ref[j].offset) : w4[j];
+        };
+        std::vector<BvhNode4> n4(order.size() ? order.size() : 1);
+        std::memset(n4.data(), 0, n4.size() * sizeof(BvhNode4));
+        const float inf = std::numeric_limits<float>::infinity();
+        for (size_t w = 0; w < order.size(); ++w) {
+            const uint32_t i = order[w];
+            const uint32_t ch[2] = {i + 1, (uint32_t)ref[i].offset};
+            uint32_t meta = ref[i].word & 3u;
+            for (int c = 0; c < 2; ++c) {
+                const RefBvhNode *slot[2] = {nullptr, nullptr};
+                uint32_t sref[2] = {B200RT_EMPTY_SLOT, B200RT_EMPTY_SLOT};
+                if ((ref[ch[c]].word & 3u) == 3u) { slot[0] = &ref[ch[c]]; sref[0] = ref4_of(ch[c]); }
+                else {
+                    const uint32_t g[2] = {ch[c] + 1, (uint32_t)ref[ch[c]].offset};
+                    for (int k = 0; k < 2; ++k) { slot[k] = &ref[g[k]]; sref[k] = ref4_of(g[k]); }
+                    meta |= (ref[ch[c]].word & 3u) << (2 + 2 * c);
+                }
+                float lo[2][3], hi[2][3];
+                for (int k = 0; k < 2; ++k)
+                    for (int a = 0; a < 3; ++a) { lo[k][a] = slot[k] ? slot[k]->lo[a] : inf; hi[k][a] = slot[k] ? slot[k]->hi[a] : -inf; }
+                float4 *q = n4[w].q + 4 * c;
+                q[0] = make_float4(lo[0][0], lo[0][1], lo[0][2], hi[0][0]);
+                q[1] = make_float4(hi[0][1], hi[0][2], lo[1][0], lo[1][1]);
+                q[2] = make_float4(lo[1][2], hi[1][0], hi[1][1], hi[1][2]);
+                float r0, r1;
+                std::memcpy(&r0, &sref[0], 4); std::memcpy(&r1, &sref[1], 4);
+                q[3] = make_float4(r0, r1, 0.f, 0.f);
+            }
+            std::memcpy(&n4[w].q[3].z, &meta, 4);
+        }
+        CU(cudaMalloc(&s->d_nodes4, n4.size() * sizeof(BvhNode4)));
+        CU(cudaMemcpy(s->d_nodes4, n4.data(), n4.size() * sizeof(BvhNode4), cudaMemcpyHostToDevice));
+        s->bvh.nodes4 = (const BvhNode4 *)s->d_nodes4;
+        s->bvh.rootRef4 = ref4_of(0);
+    }
     CU(cudaMalloc(&s->d_nodes, nodes.size() * sizeof(BvhNode2)));
     CU(cudaMemcpy(s->d_nodes, nodes.data(), nodes.size() * sizeof(BvhNode2), cudaMemcpyHostToDevice));
     CU(cudaMalloc(&s->d_tris, recs.size() * sizeof(float4)));
@@ -466,7 +532,7 @@ extern "C" void b200rt_scene_destroy(b200rt_scene *s) {
     b200rt_wavefront_release(s);
     if (s->d_prim_tris != s->d_tris) cudaFree(s->d_prim_tris);
     cudaFree(s->d_nodes); cudaFree(s->d_indices); cudaFree(s->d_tris); cudaFree(s->d_spheres);
-    cudaFree(s->d_prim_uv); cudaFree(s->d_prim_n); cudaFree(s->d_prim_flags);
+    cudaFree(s->d_prim_uv); cudaFree(s->d_prim_n); cudaFree(s->d_prim_flags); cudaFree(s->d_nodes4);
     cudaFree(s->d_stage_in); cudaFree(s->d_stage_out); cudaFree(s->d_counters); cudaFree(s->d_pc);
     for (auto &l : s->lanes) {
         cudaFree(l.d_in); cudaFree(l.d_out);
@@ -543,7 +609,7 @@ int b200rt::launch_trace(const b200rt_scene *s, const float4 *rays, uint64_t n, 
 #define PL(fn, view) fn<<<blocks, B200RT_PBLOCK, (size_t)g_sstack_bsp * 12 * B200RT_PBLOCK, st>>>(view, ri, m, n_dev, ho, oo, pc, g_thresh, chunk, g_sstack_bsp, g_bsp_steps)
             switch (s->kind * 2 + (any ? 1 : 0)) {
                 case B200RT_BVH * 2: case B200RT_BVH * 2 + 1: {
-                    uint32_t topN = g_toplevels ? s->bvh.topCount[g_toplevels] : 0u;
+                    uint32_t topN = (g_toplevels && !g_bvh4) ? s->bvh.topCount[g_toplevels] : 0u;
                     const size_t smem = (size_t)g_sstack * sizeof(uint2) * B200RT_PBLOCK + (size_t)topN * sizeof(BvhNode2);
                     unsigned blk = blocks;
                     if (topN) {   // experiment path: shared memory per block depends on the scene, so does the residency

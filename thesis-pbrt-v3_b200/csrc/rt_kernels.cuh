@@ -29,7 +29,23 @@ struct __align__(16) BvhNode2 {
 };
 #define B200RT_LEAF_BIT 0x80000000u
 
+// Two binary levels collapsed into one 128-byte record (B200RT_BVH4): the four GRANDCHILDREN of a reference interior node,
+// as two BvhNode2-shaped halves (pair 0 = the children of child 0, pair 1 = those of child 1; a child that is a leaf
+// occupies slot 0 of its pair with its own box, slot 1 is then empty).  Visiting order and results stay the reference's:
+// a grandchild's box lies inside its parent's, and every term of the slab test is monotone in the bounds, so a box that
+// fails implies that everything below it fails — skipping the child's own test changes no outcome; pairs are ordered by
+// dirIsNeg[axis of the node], slots inside a pair by dirIsNeg[axis of that child] (bvh.cpp:382-388), deferred slots are
+// re-tested against the current ray.tMax when popped (bvh.cpp:367).  The chain of dependent node fetches halves.
+//   half h: a, b, c as in BvhNode2; m = (slot 0 ref, slot 1 ref, meta, -), meta (half 0 only): bits 0-1 the node's split
+//   axis, 2-3 child 0's, 4-5 child 1's
+struct __align__(16) BvhNode4 {
+    float4 q[8];
+};
+#define B200RT_EMPTY_SLOT 0x7FFFFFFEu
+
 struct BvhView {
+    const BvhNode4 *nodes4;   // nullptr when the tree has no interior node
+    uint32_t rootRef4;
     const BvhNode2 *nodes;
     const float4 *tris;  // 3 x float4 per slot: (p0, primId) (p1, flags) (p2, sphere index)
     const float4 *spheres;  // 4 x float4 per sphere: WorldToObject rows 0..2, (radius, -, -, -)

@@ -254,6 +254,163 @@ bvh_persistent_kernel(const __grid_constant__ BvhView S, const float4 *__restric
     warp_exit(pc, lane);
 }
 
+// ---- BVH, two levels per step (BvhNode4, rt_kernels.cuh) --------------------------------------------------------------
+// Same persistent-warp / vote skeleton as bvh_persistent_kernel; an interior step fetches one 128-byte record (four
+// 256-bit loads issued together), tests the four grandchild boxes and continues with the first one that passes in the
+// reference's visiting order, pushing the others (up to three) in reverse order with their entry distances.
+template <bool ANY, int MINB>
+__global__ void __launch_bounds__(B200RT_PBLOCK, MINB)
+bvh4_persistent_kernel(const __grid_constant__ BvhView S, const float4 *__restrict__ rays, uint64_t n64,
+                       const uint32_t *__restrict__ n_dev, b200rt_hit *__restrict__ hits,
+                       uint8_t *__restrict__ occluded, PersistCounters *pc, uint32_t thresh, uint32_t chunk,
+                       uint32_t steps, uint32_t sdepth, uint32_t /*topN: unused*/) {
+    extern __shared__ uint2 sst[];
+    uint32_t n = (uint32_t)n64;
+    if (n_dev) { const uint32_t m = *n_dev; n = m < n ? m : n; }
+    const unsigned FULL = 0xFFFFFFFFu;
+    const int lane = threadIdx.x & 31;
+    RayCtx r;
+    HitRec h;
+    uint32_t cur = B200RT_DONE, rayIdx = 0;
+    bool nx = false, ny = false, nz = false, slow = false, hit = false;
+    bool live = false;
+    uint32_t negMask = 0;
+    uint2 stack[96];   // up to three deferred slots per two reference levels (upload checks depth <= 64)
+    int sp = 0;
+    WarpQueue wq;
+#define B4_PUSH(refv, tv)                                                                   \
+    do {                                                                                    \
+        const uint2 e_ = make_uint2((refv), __float_as_uint(tv));                           \
+        if ((uint32_t)sp < sdepth) sst[sp * B200RT_PBLOCK + threadIdx.x] = e_;              \
+        else stack[sp - sdepth] = e_;                                                       \
+        ++sp;                                                                               \
+    } while (0)
+#define B4_POP()                                                                            \
+    do {                                                                                    \
+        cur = B200RT_DONE;                                                                  \
+        while (sp > 0) {                                                                    \
+            --sp;                                                                           \
+            const uint2 e_ = (uint32_t)sp < sdepth ? sst[sp * B200RT_PBLOCK + threadIdx.x] : stack[sp - sdepth]; \
+            if (ANY || __uint_as_float(e_.y) < r.tMax) { cur = e_.x; break; }               \
+        }                                                                                   \
+    } while (0)
+    for (;;) {
+        const unsigned idle = __ballot_sync(FULL, cur == B200RT_DONE);
+        if (idle && !wq.drained) {
+            const uint32_t got = warp_claim(wq, pc, n, chunk, idle, cur == B200RT_DONE, lane);
+            if (got != 0xFFFFFFFFu) {
+                rayIdx = got;
+                ray_setup(r, __ldg(rays + 2 * (size_t)rayIdx), __ldg(rays + 2 * (size_t)rayIdx + 1));
+                nx = r.ix < 0; ny = r.iy < 0; nz = r.iz < 0;
+                negMask = (nx ? 1u : 0u) | (ny ? 2u : 0u) | (nz ? 4u : 0u);
+                slow = !(fabsf(r.ix) <= 3.402823466e+38f) || !(fabsf(r.iy) <= 3.402823466e+38f) ||
+                       !(fabsf(r.iz) <= 3.402823466e+38f) || !(fabsf(r.ox) <= 3.402823466e+38f) ||
+                       !(fabsf(r.oy) <= 3.402823466e+38f) || !(fabsf(r.oz) <= 3.402823466e+38f);
+                h.prim = B200RT_MISS; h.t = r.tMax; h.b0 = h.b1 = h.b2 = 0.f;
+                hit = false;
+                sp = 0;
+                float te;
+                const bool ok = slab_geom(r, nx ? S.root[3] : S.root[0], ny ? S.root[4] : S.root[1],
+                                          nz ? S.root[5] : S.root[2], nx ? S.root[0] : S.root[3],
+                                          ny ? S.root[1] : S.root[4], nz ? S.root[2] : S.root[5], te);
+                if (ok && te < r.tMax) { cur = S.rootRef4; live = true; }
+                else {
+                    if (ANY) occluded[rayIdx] = 0;
+                    else {
+                        b200rt_hit o; o.prim = B200RT_MISS; o.t = h.t; o.b0 = o.b1 = o.b2 = 0.f;
+                        hits[rayIdx] = o;
+                    }
+                }
+            }
+        }
+        if (__ballot_sync(FULL, cur != B200RT_DONE) == 0) {
+            if (wq.drained) break;
+            continue;
+        }
+        for (;;) {
+            const unsigned mI = __ballot_sync(FULL, !(cur & B200RT_LEAF_BIT) && cur != B200RT_DONE);
+            const unsigned mL = __ballot_sync(FULL, (cur & B200RT_LEAF_BIT) != 0);
+            const uint32_t nI = __popc(mI), nL = __popc(mL);
+            if (nI + nL == 0 || (!wq.drained && nI + nL < thresh)) break;
+            if (nI >= nL) {
+#pragma unroll 1
+                for (uint32_t k = 0; k < steps && !(cur & B200RT_LEAF_BIT) && cur != B200RT_DONE; ++k) {
+                    const float4 *nd = S.nodes4[cur].q;
+                    float4 a0, b0, c0, m0, a1, b1, c1, m1;
+                    ldg256(nd, a0, b0); ldg256(nd + 2, c0, m0); ldg256(nd + 4, a1, b1); ldg256(nd + 6, c1, m1);
+                    const uint32_t meta = __float_as_uint(m0.z);
+                    float t[4];
+                    bool g[4];
+#define B4_PAIR(a, b, c, i0)                                                                                       \
+                    {                                                                                              \
+                        const float l0x = nx ? a.w : a.x, l0y = ny ? b.x : a.y, l0z = nz ? b.y : a.z;              \
+                        const float h0x = nx ? a.x : a.w, h0y = ny ? a.y : b.x, h0z = nz ? a.z : b.y;              \
+                        const float l1x = nx ? c.y : b.z, l1y = ny ? c.z : b.w, l1z = nz ? c.w : c.x;              \
+                        const float h1x = nx ? b.z : c.y, h1y = ny ? b.w : c.z, h1z = nz ? c.x : c.w;              \
+                        if (!slow) {                                                                               \
+                            g[i0] = slab_fast(r, l0x, l0y, l0z, h0x, h0y, h0z, t[i0]);                             \
+                            g[i0 + 1] = slab_fast(r, l1x, l1y, l1z, h1x, h1y, h1z, t[i0 + 1]);                     \
+                        } else {                                                                                   \
+                            g[i0] = slab_geom(r, l0x, l0y, l0z, h0x, h0y, h0z, t[i0]);                             \
+                            g[i0 + 1] = slab_geom(r, l1x, l1y, l1z, h1x, h1y, h1z, t[i0 + 1]);                     \
+                        }                                                                                          \
+                    }
+                    B4_PAIR(a0, b0, c0, 0)
+                    B4_PAIR(a1, b1, c1, 2)
+#undef B4_PAIR
+                    const uint32_t rf[4] = {__float_as_uint(m0.x), __float_as_uint(m0.y), __float_as_uint(m1.x), __float_as_uint(m1.y)};
+                    bool p[4];
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) p[q] = g[q] && t[q] < r.tMax && rf[q] != B200RT_EMPTY_SLOT;
+                    const bool negTop = (negMask >> (meta & 3u)) & 1u, neg0 = (negMask >> ((meta >> 2) & 3u)) & 1u,
+                               neg1 = (negMask >> ((meta >> 4) & 3u)) & 1u;
+                    // visiting order: near pair first (by the node's axis), inside a pair the near slot first (by that child's axis)
+                    const int i0 = negTop ? (neg1 ? 3 : 2) : (neg0 ? 1 : 0), i1 = negTop ? (neg1 ? 2 : 3) : (neg0 ? 0 : 1);
+                    const int i2 = negTop ? (neg0 ? 1 : 0) : (neg1 ? 3 : 2), i3 = negTop ? (neg0 ? 0 : 1) : (neg1 ? 2 : 3);
+#define B4_SEL(arr, i) ((i) == 0 ? arr[0] : (i) == 1 ? arr[1] : (i) == 2 ? arr[2] : arr[3])
+                    const bool q0 = B4_SEL(p, i0), q1 = B4_SEL(p, i1), q2 = B4_SEL(p, i2), q3 = B4_SEL(p, i3);
+                    const uint32_t r0 = B4_SEL(rf, i0), r1 = B4_SEL(rf, i1), r2 = B4_SEL(rf, i2), r3 = B4_SEL(rf, i3);
+                    const float t0 = B4_SEL(t, i0), t1 = B4_SEL(t, i1), t2 = B4_SEL(t, i2), t3 = B4_SEL(t, i3);
+#undef B4_SEL
+                    (void)t0;
+                    if (q3 && (q0 || q1 || q2)) B4_PUSH(r3, t3);
+                    if (q2 && (q0 || q1)) B4_PUSH(r2, t2);
+                    if (q1 && q0) B4_PUSH(r1, t1);
+                    if (q0) cur = r0;
+                    else if (q1) cur = r1;
+                    else if (q2) cur = r2;
+                    else if (q3) cur = r3;
+                    else B4_POP();
+                }
+            } else {
+                if (cur & B200RT_LEAF_BIT) {
+                    const float4 *rec = S.tris + 3 * (size_t)(cur & ~B200RT_LEAF_BIT);
+                    const float4 v0 = __ldg(rec), v1 = __ldg(rec + 1), v2 = __ldg(rec + 2);
+                    bool stop = false;
+                    if (prim_closest<ANY>(r, v0, v1, v2, h, S.spheres, rays + 2 * (size_t)rayIdx + 1)) {
+                        hit = true;
+                        if (ANY) stop = true;
+                    }
+                    if (stop) cur = B200RT_DONE;
+                    else if (__float_as_uint(v1.w) & B200RT_TRI_LAST) B4_POP();
+                    else cur += 1;
+                }
+            }
+            if (live && cur == B200RT_DONE) {
+                live = false;
+                if (ANY) occluded[rayIdx] = hit ? 1 : 0;
+                else {
+                    b200rt_hit o; o.prim = h.prim; o.t = h.t; o.b0 = h.b0; o.b1 = h.b1; o.b2 = h.b2;
+                    hits[rayIdx] = o;
+                }
+            }
+        }
+    }
+#undef B4_PUSH
+#undef B4_POP
+    warp_exit(pc, lane);
+}
+
 // ---- kd-tree / RBSP / RBSPKd ---------------------------------------------------------------------
 // Same persistent-warp + vote skeleton over the reference's 8-byte nodes (kdtreeaccel.cpp:381-521,
 // rbsp.cpp:405-547, rbspKd.cpp).  Lane states: walking interior nodes (cheap step: one 8-byte fetch, a

@@ -10,6 +10,7 @@ struct b200rt_scene {
     b200rt::BvhView bvh{};
     b200rt::BspView bsp{};
     void *d_nodes = nullptr;
+    void *d_nodes4 = nullptr;       // BVH: two-levels-per-record layout (BvhNode4)
     uint32_t *d_indices = nullptr;
     float4 *d_tris = nullptr;       // traversal order (BVH: leaf slots; kd/RBSP: original primitive order)
     float4 *d_spheres = nullptr;    // 4 x float4 per sphere primitive (rt_math.cuh sphere_test)
