@@ -38,7 +38,7 @@ KD = (0.5, 0.5, 0.5)
 
 
 def workload_name(spp=SPP):
-    return ("sponza-standin(procedural, seed 7) BVHAccel(sweep-SAH) path maxdepth %d, %dx%d @ %d spp, point light, "
+    return ("sponza-standin(procedural, seed 7) BVHAccel(sweep-SAH) path maxdepth %d, %dx%d @ %d spp, Sampler halton, point light, "
             "matte; wavefront closest+shadow queues" % (MAXDEPTH, XRES, YRES, spp))
 
 
@@ -95,44 +95,32 @@ class ClockSampler:
                 "samples": len(sm)}
 
 
-# ---- host-side (numpy) wavefront used ONLY by the reference arm to produce the same kind of ray queues
-def numpy_queues(intersect, cam, light, spp, maxdepth, seed, tri_verts, x0, x1, y0, y1):
-    """Camera / bounce / shadow queues of the path integrator for a pixel window, with `intersect`
-    answering closest-hit queries.  Returns [(kind, rays)], kind in {"closest", "shadow"}."""
-    from b200rt import scenes
-    rng = np.random.default_rng(seed)
-    rays = scenes.camera_rays(cam, spp=spp, seed=seed + 1, x0=x0, x1=x1, y0=y0, y1=y1)
+# ---- the GPU arm's ray queues, regenerated on the host for the reference arm ------------------------------------------
+def host_queues(sc, tri_verts, window, spp, maxdepth):
+    """The wavefront driver's closest / shadow queues for a crop window of the workload, produced WITHOUT a GPU by the host
+    build of the shade stage (tests/hostshade: the same csrc/wf_*.cuh text the device runs — on the B200 every one of these
+    rays is bit-equal to the reference renderer's own, tests/test_gpu_halton.py) with the CPU oracle answering the rays.
+    They are written to and read back from the ray-set file format of b200rt/rayfile.py, the form in which
+    the GPU arm's queues are dumped.  Returns [(kind, rays)]."""
+    import tempfile
+    import b200rt
+    from b200rt import rayfile
+    from oracle import orcbind as ob
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import hostwf
+    integ = b200rt.WavefrontPathIntegrator(sc["camera"], spp=spp, maxdepth=maxdepth, light_pos=sc["light"], light_I=LIGHT_I, kd=KD,
+                                           crop=window, sampler="halton")
+    orc = ob.OracleAccel(b200rt.build_bvh(tri_verts), tri_verts)
+    _, queues, _ = hostwf.HostWavefront(integ.desc, tri_verts, orc).render()
     out = []
-    tv = tri_verts.reshape(-1, 3, 3)
-    for depth in range(maxdepth + 1):
-        out.append(("closest", rays))
-        if depth == maxdepth or len(rays) == 0:
-            break
-        prim, t = intersect(rays)
-        m = prim >= 0
-        o, d, t, prim = rays[m, 0:3], rays[m, 4:7], t[m], prim[m]
-        p = o + t[:, None] * d
-        v = tv[prim]
-        n = np.cross(v[:, 0] - v[:, 2], v[:, 1] - v[:, 2])
-        n /= np.maximum(np.linalg.norm(n, axis=1, keepdims=True), 1e-30)
-        n = np.where((np.sum(n * -d, 1) < 0)[:, None], -n, n)
-        eps = 1e-4 * np.maximum(1.0, np.abs(p).max(1, keepdims=True))
-        wl = light[None, :] - p
-        lit = np.sum(n * wl, 1) > 0
-        so = p[lit] + n[lit] * eps[lit]
-        sh = np.zeros((lit.sum(), 8), np.float32)
-        sh[:, 0:3], sh[:, 4:7], sh[:, 3] = so, light[None, :] - so, 1 - 1e-4
-        out.append(("shadow", sh))
-        u0, u1 = rng.random(len(p)), rng.random(len(p))
-        r, ph = np.sqrt(u0), 2 * np.pi * u1
-        a = np.where(np.abs(n[:, :1]) > 0.9, np.array([[0, 1, 0]]), np.array([[1, 0, 0]]))
-        s = np.cross(a, n)
-        s /= np.linalg.norm(s, axis=1, keepdims=True)
-        tt = np.cross(n, s)
-        wi = s * (r * np.cos(ph))[:, None] + tt * (r * np.sin(ph))[:, None] + n * np.sqrt(np.maximum(0, 1 - u0))[:, None]
-        nr = np.zeros((len(p), 8), np.float32)
-        nr[:, 0:3], nr[:, 4:7], nr[:, 3] = p + n * eps, wi, np.inf
-        rays = nr
+    with tempfile.TemporaryDirectory() as td:
+        for q in sorted(queues):
+            if len(queues[q]["rays"]) == 0:
+                continue
+            f = os.path.join(td, "q%d.rays" % q)
+            rayfile.save(f, queues[q]["rays"], any_hit=q % 2 == 1)
+            rays, flags = rayfile.load(f)
+            out.append(("shadow" if flags & rayfile.FLAG_ANY_HIT else "closest", rays))
     return out
 
 
@@ -184,7 +172,7 @@ def run_reference(args):
 
         def one():
             _, nc, ns, secs = rb.render(S, "bvh", (-0.7, .45, .05), (0, .25, 0), (0, 1, 0), 42.0, XRES, YRES, spp, MAXDEPTH,
-                                        sc["light"], LIGHT_I, KD, sampler="random", n_threads=0, timing=True)
+                                        sc["light"], LIGHT_I, KD, sampler="halton", n_threads=0, timing=True)
             return nc + ns, secs
         for _ in range(min(1, args.warmup)):
             one()
@@ -218,22 +206,17 @@ def run_reference(args):
             extra["reference_render_living_room"] = {"unavailable": str(e)[:200]}
     # traversal alone (the reference's BVHAccel::Intersect / IntersectP, or the oracle port, on path-like ray queues)
     tkind, acc, isect, isect_p = build_reference_accel(tv)
-    cam = sc["camera"]
-
-    def closest(r):
-        h = isect(r, threads)
-        return (h["prim"].astype(np.int64) if tkind == "reference"
-                else np.where(h["prim"] == 0xFFFFFFFF, -1, h["prim"].astype(np.int64))), h["t"]
     w = 128
-    queues = numpy_queues(closest, cam, sc["light"], 2, MAXDEPTH, 1, tv, XRES // 2 - w, XRES // 2 + w, YRES // 2 - w, YRES // 2 + w)
+    queues = host_queues(sc, tv, (XRES // 2 - w, XRES // 2 + w, YRES // 2 - w, YRES // 2 + w), 8, MAXDEPTH)
     time_cpu(queues, isect, isect_p, threads)
     tn, tt = 0, 0.0
     for _ in range(max(1, min(3, args.steps))):
         n, t = time_cpu(queues, isect, isect_p, threads)
         tn += n
         tt += t
-    tsample = "%d rays: traversal only (%s BVHAccel), path queues (closest+shadow, maxdepth %d) of a centred %dx%d window at 2 spp" % (
-        n, "reference's own" if tkind == "reference" else "oracle port of the", MAXDEPTH, 2 * w, 2 * w)
+    tsample = ("%d rays: traversal only (%s BVHAccel) over the wavefront driver's own closest + shadow queues (Halton stream, maxdepth %d) "
+               "of a centred %dx%d crop window at 8 spp, read from ray-set files" % (
+                   n, "reference's own" if tkind == "reference" else "oracle port of the", MAXDEPTH, 2 * w, 2 * w))
     # headline of this arm = the traversal alone: that is what `e2e` of the b200rt arm measures (Intersect / IntersectP
     # over ray batches); the whole reference render (its shading and per-ray statistics included) is reported beside it
     kind, sample, tot_n, tot_t = tkind, tsample, tn, tt
@@ -353,8 +336,37 @@ def main():
         buf = torch.empty((n, 8), dtype=torch.float32, device=dev)
         wf.queue_rays(accel, q, buf.data_ptr())
         kept[q] = buf
-    # ---- e2e: the same queues through the C ABI from pinned host memory -------------------
-    hq = {q: b.cpu().pin_memory() for q, b in kept.items()}
+    # ---- e2e: a FIXED workload at every N — the whole frame at E2E_SPP samples per pixel, its tiles sharded by rank like
+    # the render's — pushed through the C ABI from pinned HOST buffers (copies inside the timed region) ----------------
+    E2E_SPP = 8
+    affinity = None
+    try:   # allocate this rank's pinned buffers from the CPUs (NUMA node) its GPU hangs off
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(local)
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (os.cpu_count() + 63) // 64)
+        cpus = [64 * i + b for i, w in enumerate(words) for b in range(64) if (w >> b) & 1]
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            affinity = "%d-%d (%d cpus)" % (min(cpus), max(cpus), len(cpus))
+    except Exception as e:   # noqa: BLE001
+        affinity = "unavailable: %s" % str(e)[:80]
+    integ8 = b200rt.WavefrontPathIntegrator(sc["camera"], spp=E2E_SPP, maxdepth=MAXDEPTH, light_pos=sc["light"],
+                                            light_I=LIGHT_I, kd=KD, rank=rank, world=world, seed=1)
+    wf.keep_queues(accel, True)
+    film.zero_()
+    integ8.render_ptr(accel, film.data_ptr(), stream)
+    torch.cuda.synchronize()
+    wf.keep_queues(accel, False)
+    hq = {}
+    for q in range(nq):
+        n = wf.queue_count(accel, q)
+        if n == 0:
+            continue
+        buf = torch.empty((n, 8), dtype=torch.float32, device=dev)
+        wf.queue_rays(accel, q, buf.data_ptr())
+        hq[q] = buf.cpu().pin_memory()
+        del buf
     outs = {q: (torch.empty((len(b), 5), dtype=torch.int32).pin_memory() if q % 2 == 0
                 else torch.empty(len(b), dtype=torch.uint8).pin_memory()) for q, b in hq.items()}
 
@@ -364,30 +376,55 @@ def main():
                 accel.intersect_ptr(b.data_ptr(), len(b), outs[q].data_ptr(), stream)
             else:
                 accel.intersect_p_ptr(b.data_ptr(), len(b), outs[q].data_ptr(), stream)
-    for _ in range(3):
-        e2e_pass()
-    barrier()
-    a, b_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    a.record()
-    reps = 3
-    for _ in range(reps):
-        e2e_pass()
-    b_.record()
-    barrier()
-    e2e_ms = a.elapsed_time(b_) / reps
+
+    # the copies alone (same bytes, H2D and D2H on two streams at once): the ceiling the host links put on e2e
+    dbuf = {q: torch.empty_like(b, device=dev) for q, b in hq.items()}
+    dout = {q: torch.empty_like(o, device=dev) for q, o in outs.items()}
+    s_in, s_out = torch.cuda.Stream(), torch.cuda.Stream()
+
+    def copy_pass():
+        with torch.cuda.stream(s_in):
+            for q, b in hq.items():
+                dbuf[q].copy_(b, non_blocking=True)
+        with torch.cuda.stream(s_out):
+            for q, o in outs.items():
+                o.copy_(dout[q], non_blocking=True)
+        s_in.synchronize(); s_out.synchronize()
+
+    def timed(fn, reps=3):
+        for _ in range(2):
+            fn()
+        barrier()
+        t0 = time.perf_counter()
+        a, b_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(reps):
+            fn()
+        b_.record()
+        barrier()
+        return max(a.elapsed_time(b_), 0.0) / reps, (time.perf_counter() - t0) * 1e3 / reps
+    e2e_ms, _ = timed(e2e_pass)
+    _, copy_ms = timed(copy_pass)   # (the copies run on side streams: wall clock between barriers)
+    del dbuf, dout
     n_e2e = sum(len(b) for b in hq.values())
     h2d = sum(len(b) * 32 for b in hq.values())
     d2h = sum(len(b) * (20 if q % 2 == 0 else 1) for q, b in hq.items())
-    if world > 1:  # every rank pushes its own queues through its own PCIe link at the same time
-        tm = torch.tensor([e2e_ms], dtype=torch.float64, device=dev)
+    per_rank = {"h2d_gbs": h2d / (e2e_ms * 1e-3) / 1e9, "d2h_gbs": d2h / (e2e_ms * 1e-3) / 1e9}
+    if world > 1:  # every rank pushes its share through its own PCIe link at the same time
+        tm = torch.tensor([e2e_ms, copy_ms], dtype=torch.float64, device=dev)
         dist.all_reduce(tm, op=dist.ReduceOp.MAX)
         ts = torch.tensor([float(n_e2e), float(h2d), float(d2h)], dtype=torch.float64, device=dev)
         dist.all_reduce(ts, op=dist.ReduceOp.SUM)
-        e2e_ms, n_e2e, h2d, d2h = float(tm[0]), int(ts[0]), int(ts[1]), int(ts[2])
+        e2e_ms, copy_ms, n_e2e, h2d, d2h = float(tm[0]), float(tm[1]), int(ts[0]), int(ts[1]), int(ts[2])
     e2e = {"value": n_e2e / (e2e_ms * 1e-3) / 1e6, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
            "rays_per_step": n_e2e, "ms_per_step": e2e_ms,
-           "what": "b200rt_intersect_closest/any on each rank's last-batch ray queues of the frame, pinned HOST rays in, HOST "
-                   "hits out, all ranks at once (sum of rays / max-over-ranks time)"}
+           "copies_only_ms": copy_ms, "copies_only_mrays_s": n_e2e / (copy_ms * 1e-3) / 1e6,
+           "h2d_gbs_all_ranks": h2d / (e2e_ms * 1e-3) / 1e9, "d2h_gbs_all_ranks": d2h / (e2e_ms * 1e-3) / 1e9,
+           "rank0_link": per_rank, "cpu_affinity_rank0": affinity,
+           "what": "FIXED workload at every N: the closest + shadow queues of the whole %dx%d frame at %d spp (tiles sharded by rank "
+                   "like the render's), b200rt_intersect_closest/any with pinned HOST rays in and HOST hits out on every rank at once "
+                   "(sum of rays / max-over-ranks time); copies_only = the same bytes moved by plain cudaMemcpyAsync (H2D and D2H "
+                   "streams together, no kernel): what the host links allow" % (XRES, YRES, E2E_SPP)}
     if rank == 0:
         from oracle import orcbind as ob
         orc = ob.OracleAccel(accel.tree, tv)
@@ -408,14 +445,16 @@ def main():
         closest_rays_rank0 = agg["closest_rays"]
         avg_ms = agg["ms_closest"] / max(1, n_launch_closest)
         achieved = (b_ray * closest_rays_rank0 / max(1, n_launch_closest)) / (avg_ms * 1e-3) / 1e9 if avg_ms > 0 else 0.0
-        # DRAM traffic per launch: measured once with `ncu --set full` (profiles/, see the json's "source")
+        # DRAM traffic per launch: NOT measured in this run — the per-ray figure of one `ncu --set full` capture
+        # (profiles/ncu_traffic.json, see its "source") times this run's rays per launch
         traffic = None
         tp = os.path.join(ROOT, "profiles", "ncu_traffic.json")
         if os.path.exists(tp):
             tj = json.load(open(tp))
             traffic = tj["closest_dram_bytes_per_ray"] * closest_rays_rank0 / max(1, n_launch_closest)
         roofline = {"bound": "hbm", "kernel": "bvh_persistent_kernel<closest>", "achieved": achieved, "peak": peak,
-                    "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
+                    "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
+                    "traffic_source": "ncu constant x rays (profiles/ncu_traffic.json), not a per-run measurement", "peak_source": peak_src,
                     "bytes_per_ray": b_ray, "n_fetch_per_ray": fetch / max(1, rays_c), "n_tri_per_ray": tests / max(1, rays_c),
                     "avg_launch_ms": avg_ms, "launches": n_launch_closest,
                     "closest_kernel_mrays_s": closest_rays_rank0 / max(1e-9, agg["ms_closest"]) / 1e3,
@@ -437,7 +476,7 @@ def main():
             time_cpu(sample[:1], isect, isect_p, threads)
             n, tsec = time_cpu(sample, isect, isect_p, threads)
             cpu = {"value": n / tsec / 1e6, "unit": UNIT, "cores": threads, "kind": kind,
-                   "sample": "every %d-th ray of the last batch's %d queues (%d rays), %s BVHAccel::Intersect/IntersectP"
+                   "sample": "every %d-th ray of the e2e workload's %d queues (%d rays), %s BVHAccel::Intersect/IntersectP"
                              % (stride, len(hq), n, "reference's own" if kind == "reference" else "oracle port of the")}
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup),
                 "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,

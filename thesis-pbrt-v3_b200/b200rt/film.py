@@ -2,9 +2,8 @@
 
 The reference merges FilmTiles under a mutex inside one process (Film::MergeFilmTile,
 src/core/film.cpp:118-133).  Here each rank owns the tiles t with t % world == rank of the
-reference's 16x16 tile grid (src/core/integrator.cpp:237-239); with the box filter no pixel is
-shared between tiles, so reassembly is a pure gather of each rank's tile pixels to rank 0
-(torch.distributed.gather -> NCCL send/recv over NVLink on GPUs, gloo on CPU)."""
+reference's 16x16 tile grid (src/core/integrator.cpp:237-239) and the frame is reassembled on rank 0
+(see FilmGather)."""
 import numpy as np
 import torch
 import torch.distributed as dist
@@ -23,29 +22,23 @@ def tile_pixel_indices(xres, yres, tile, rank, world):
 
 
 class FilmGather:
-    """Precomputes the per-rank pixel lists once; gather() moves only this rank's pixels."""
+    """Reassembles the frame on rank 0.
+
+    Each rank's film holds its own tiles and — for samples that sit exactly on a pixel boundary (FilmTile::AddSample's
+    footprint then covers the neighbouring pixel too, film.h:136-141; Halton's first samples do) — contributions to the
+    one-pixel halo around them, which may belong to another rank's tile.  Every other pixel is zero, so the frame is the
+    SUM of the ranks' films: one reduce to rank 0 (NCCL over NVLink / NVSwitch on GPUs, gloo in the CPU tests).  A pixel
+    that received no halo contribution is `own + 0 + ... + 0`, i.e. bit-identical to the single-rank film."""
 
     def __init__(self, xres, yres, tile, rank, world, device):
         self.rank, self.world, self.device = rank, world, device
         self.xres, self.yres = xres, yres
-        self.idx = [torch.from_numpy(tile_pixel_indices(xres, yres, tile, r, world)).to(device) for r in range(world)]
-        self.maxlen = max(len(i) for i in self.idx)
-        self.send = torch.zeros((self.maxlen, 4), dtype=torch.float32, device=device)
-        self.recv = [torch.zeros((self.maxlen, 4), dtype=torch.float32, device=device) for _ in range(world)] \
-            if rank == 0 else None
-        self.bytes_per_gather = self.maxlen * 16 * (world - 1)
+        self.bytes_per_gather = xres * yres * 16 * (world - 1)
 
     def gather(self, film):
-        """film: (yres, xres, 4) tensor holding this rank's tiles.  Returns the full frame on rank 0
-        (the same tensor, completed in place), None elsewhere."""
-        flat = film.view(-1, 4)
+        """film: (yres, xres, 4) tensor holding this rank's tiles (+ halo contributions).  Returns the full frame on
+        rank 0 (the same tensor, completed in place), None elsewhere."""
         if self.world == 1:
             return film
-        mine = self.idx[self.rank]
-        self.send[: len(mine)] = flat[mine]
-        dist.gather(self.send, self.recv, dst=0)
-        if self.rank != 0:
-            return None
-        for r in range(1, self.world):
-            flat[self.idx[r]] = self.recv[r][: len(self.idx[r])]
-        return film
+        dist.reduce(film, dst=0, op=dist.ReduceOp.SUM)
+        return film if self.rank == 0 else None
