@@ -53,9 +53,9 @@ static int g_pblocks[6][2];  // resident persistent blocks per SM, [kind][any]
 static int g_persist_bsp = 1;
 static uint32_t g_bvh_steps = 4;
 static uint32_t g_sstack = 10;     // BVH stack entries kept in shared memory (B200RT_SSTACK; 0 = all in local memory)
-static uint32_t g_toplevels = 5;   // BVH levels staged in shared memory per block (B200RT_TOPLEVELS; 0 = none): 5 levels = 31
-                                   // records = 2 KB per block, +1 % on the path queues; 8 levels cost more L1 than they save
-                                   // (profiles/r02_ab_bvh_toplevels.log)
+static uint32_t g_toplevels = 0;   // BVH levels staged in shared memory per block (B200RT_TOPLEVELS; 0 = none, the default):
+                                   // north-star item (3), built and measured — neutral at 3-6 levels, -1 % at 8
+                                   // (profiles/r02_ab_bvh_toplevels*.log): those records are L1-resident anyway
 static size_t g_bvh_attr[2] = {0, 0};   // MaxDynamicSharedMemorySize currently set on the two BVH kernels
 static uint32_t g_bsp_steps = B200RT_BSP_STEPS;  // B200RT_BSP_STEPS_N
 static uint32_t g_sstack_bsp = 0;
@@ -68,6 +68,11 @@ static const void *bvh_fn(bool any) {
     if (g_bvh4) {
         if (g_minb == 8) f = any ? bvh4_persistent_kernel<true, 8> : bvh4_persistent_kernel<false, 8>;
         else f = any ? bvh4_persistent_kernel<true, 9> : bvh4_persistent_kernel<false, 9>;
+        return (const void *)f;
+    }
+    if (g_toplevels) {   // the instantiation that stages the top levels in shared memory
+        if (g_minb == 8) f = any ? bvh_persistent_kernel<true, 8, true> : bvh_persistent_kernel<false, 8, true>;
+        else f = any ? bvh_persistent_kernel<true, 9, true> : bvh_persistent_kernel<false, 9, true>;
         return (const void *)f;
     }
     if (g_minb == 8) f = any ? bvh_persistent_kernel<true, 8> : bvh_persistent_kernel<false, 8>;
@@ -122,7 +127,7 @@ extern "C" int b200rt_init(int device) {
         // scene's actual count): attribute, carve-out and residency are all taken for this size
         const size_t sm = (size_t)g_sstack * sizeof(uint2) * B200RT_PBLOCK +
                           ((g_toplevels && !g_bvh4) ? (((size_t)1 << g_toplevels) - 1) * sizeof(BvhNode2) : 0);
-        const int bc = sm ? (int)std::min<size_t>(100, ((size_t)g_minb * (sm + 1024) * 100) / (228 * 1024) + 1) : carve;
+        const int bc = sm ? (int)std::min<size_t>(100, ((size_t)g_minb * (sm + (g_toplevels ? 1024 : 0)) * 100) / (228 * 1024) + 1) : carve;
         const void *fns[2] = {bvh_fn(false), bvh_fn(true)};
         for (int a = 0; a < 2; ++a) {
             CU(cudaFuncSetAttribute(fns[a], cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
@@ -256,7 +261,8 @@ static int build_bvh_scene(const b200rt_scene_desc *d, b200rt_scene *s) {
         std::vector<uint32_t> level{0};   // reference node numbers of the current level, in left-to-right order
         uint32_t next = 0;
         std::vector<uint8_t> placed(N, 0);
-        for (int lv = 0; lv < B200RT_TOP_MAXLEVELS; ++lv) {
+        // (only the levels that are staged are renumbered: the depth-first order keeps a first child next to its parent)
+        for (int lv = 0; lv < (int)g_toplevels; ++lv) {
             std::vector<uint32_t> nxt;
             for (uint32_t i : level) {
                 if ((ref[i].word & 3u) == 3u) continue;

@@ -90,7 +90,7 @@ __device__ __forceinline__ void warp_exit(PersistCounters *pc, int lane) {
     }
 }
 
-template <bool ANY, int MINB>
+template <bool ANY, int MINB, bool TOP = false>
 __global__ void __launch_bounds__(B200RT_PBLOCK, MINB)
 bvh_persistent_kernel(const __grid_constant__ BvhView S, const float4 *__restrict__ rays, uint64_t n64,
                       const uint32_t *__restrict__ n_dev, b200rt_hit *__restrict__ hits,
@@ -108,9 +108,11 @@ bvh_persistent_kernel(const __grid_constant__ BvhView S, const float4 *__restric
     const unsigned FULL = 0xFFFFFFFFu;
     const int lane = threadIdx.x & 31;
     // Top of the tree in shared memory (north-star item (3)): one cooperative copy per block, behind the stack area.
-    // Off by default (topN = 0): measured slower than leaving those records to L1 (profiles/r02_ab_bvh_toplevels.log).
+    // A separate instantiation (TOP), off by default: the staged records were L1-resident anyway, so the frame time does not
+    // move (profiles/r02_ab_bvh_toplevels_v2.log), while the extra branch in the node fetch costs the default path 5 % when it
+    // is compiled in (profiles/r02_ab_bench_old_vs_new.log).
     const float4 *stop = reinterpret_cast<const float4 *>(sst + (size_t)sdepth * B200RT_PBLOCK);
-    if (topN) {
+    if (TOP && topN) {
         float4 *w = reinterpret_cast<float4 *>(sst + (size_t)sdepth * B200RT_PBLOCK);
         for (uint32_t i = threadIdx.x; i < topN * 4u; i += blockDim.x) w[i] = __ldg(reinterpret_cast<const float4 *>(S.nodes) + i);
         __syncthreads();
@@ -178,7 +180,7 @@ bvh_persistent_kernel(const __grid_constant__ BvhView S, const float4 *__restric
                 for (uint32_t k = 0; k < steps && !(cur & B200RT_LEAF_BIT) && cur != B200RT_DONE; ++k) {
                     const BvhNode2 *nd = S.nodes + cur;
                     float4 a, b, c, mf;
-                    if (cur < topN) { const float4 *q = stop + 4 * (size_t)cur; a = q[0]; b = q[1]; c = q[2]; mf = q[3]; }
+                    if (TOP && cur < topN) { const float4 *q = stop + 4 * (size_t)cur; a = q[0]; b = q[1]; c = q[2]; mf = q[3]; }
                     else { ldg256(&nd->a, a, b); ldg256(&nd->c, c, mf); }
                     const uint4 m = make_uint4(__float_as_uint(mf.x), __float_as_uint(mf.y), __float_as_uint(mf.z), 0u);
                     float t0, t1;
