@@ -146,6 +146,12 @@ int b200rt_render_tiles(const b200rt_render_desc *desc, uint32_t *n_tiles, uint6
 int b200rt_render(b200rt_scene *scene, const b200rt_render_desc *desc, float *film, b200rt_render_stats *stats,
                   void *stream);
 
+/* Wavefront batches in flight per render call (default 2, or B200RT_WF_STREAMS): consecutive batches are independent, so the
+ * next batch's camera / shade / film kernels and the head of its traversal fill the gaps the current batch's traversal tails
+ * leave (one B200: 114.5 -> 105.3 ms per headline frame, profiles/r02_ab_wf_streams.log).  The image does not depend on it.
+ * With n > 1 the per-kernel times in b200rt_render_stats overlap each other; measure kernels with n = 1. */
+int b200rt_render_set_streams(int n);
+
 /* b200rt_render + the thesis's per-pixel traversal statistics: every ray of a path (camera, bounce and shadow rays)
  * adds its Ray::stats to the path's pixel, as PathIntegrator::Li does with `r.stats += ray.stats`
  * (src/integrators/path.cpp:92-200, light.cpp:62) before SamplerIntegrator::Render adds the sample's total to the

@@ -172,6 +172,11 @@ def render_heatmaps(integ, accel, stream=None):
     return film, heat, {f: getattr(st, f) for f, _ in RenderStats._fields_}
 
 
+def set_streams(n):
+    """Wavefront batches in flight per render call (b200rt_render_set_streams; default 2).  Use 1 to time kernels alone."""
+    api._check(_lib().b200rt_render_set_streams(int(n)))
+
+
 def keep_queues(accel, keep=True):
     api._check(_lib().b200rt_render_keep_queues(accel._h, int(keep)))
 

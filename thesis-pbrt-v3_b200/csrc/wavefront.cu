@@ -244,8 +244,24 @@ __global__ void k_heat(const __grid_constant__ WfParams P, uint64_t batchStart, 
     if (v.z) atomicAdd(heat + (B200RT_HEAT_LEAF + plane) * npx + pix, v.z);
 }
 
+// The per-batch buffers of one wavefront in flight.
+struct QSet {
+    float4 *rays[2], *shRays, *shContrib, *beta, *L, *misRays, *misContrib;
+    uint32_t *qPath[2], *shPath, *counts, *pdim, *misPath;
+    b200rt_hit *hits;
+    uint8_t *occ;
+};
+
 struct Workspace {
     std::mutex mu;   // one render at a time per scene: the queues below are shared state
+    // A second set of batch buffers + two side streams: consecutive batches are independent, so batch k+1's camera / shade /
+    // film kernels and the head of its traversal run in the gaps batch k's traversal tails leave (B200RT_WF_STREAMS=1: off)
+    static constexpr int kMaxSets = 4;
+    QSet alt[kMaxSets - 1] = {};
+    size_t altCap[kMaxSets - 1] = {0, 0, 0};
+    bool altMis[kMaxSets - 1] = {false, false, false};
+    cudaStream_t side[kMaxSets] = {nullptr, nullptr, nullptr, nullptr};
+    cudaEvent_t evFork = nullptr, evJoin[kMaxSets] = {nullptr, nullptr, nullptr, nullptr};
     size_t cap = 0;
     float4 *misRays = nullptr, *misContrib = nullptr;   // lights with area only (EstimateDirect's BSDF-sampled rays)
     uint32_t *misPath = nullptr;
@@ -304,8 +320,19 @@ void free_queues(Workspace *w) {
     w->cap = 0;
     free_kept(w);
 }
+void free_alt(Workspace *w, int i) {
+    QSet &a = w->alt[i];
+    for (int k = 0; k < 2; ++k) { cudaFree(a.rays[k]); cudaFree(a.qPath[k]); }
+    cudaFree(a.shRays); cudaFree(a.shContrib); cudaFree(a.beta); cudaFree(a.L); cudaFree(a.misRays); cudaFree(a.misContrib);
+    cudaFree(a.shPath); cudaFree(a.counts); cudaFree(a.pdim); cudaFree(a.misPath); cudaFree(a.hits); cudaFree(a.occ);
+    a = QSet{};
+    w->altCap[i] = 0; w->altMis[i] = false;
+}
 void free_ws(Workspace *w) {
     free_queues(w);
+    for (int i = 0; i < Workspace::kMaxSets - 1; ++i) free_alt(w, i);
+    for (int k = 0; k < Workspace::kMaxSets; ++k) { if (w->side[k]) cudaStreamDestroy(w->side[k]); if (w->evJoin[k]) cudaEventDestroy(w->evJoin[k]); }
+    if (w->evFork) cudaEventDestroy(w->evFork);
     cudaFree(w->film); cudaFree(w->heat); cudaFree(w->mats); cudaFree(w->primMat);
     cudaFree(w->splatCount); cudaFree(w->splatPix); cudaFree(w->splatVal);
     cudaFree(w->haltonPerms); cudaFree(w->haltonDims); cudaFree(w->sobol32); cudaFree(w->sobolVdc);
@@ -382,6 +409,13 @@ extern "C" int b200rt_render_queue_paths(b200rt_scene *s, uint32_t q, uint32_t *
     return B200RT_OK;
 }
 
+// wavefronts in flight (B200RT_WF_STREAMS in the environment, or b200rt_render_set_streams): 1 .. 4, default 2
+static std::atomic<int> g_wf_sets{[] { const char *e = getenv("B200RT_WF_STREAMS"); const int v = e ? atoi(e) : 2; return v < 1 ? 1 : (v > 4 ? 4 : v); }()};
+extern "C" int b200rt_render_set_streams(int n) {
+    if (n < 1 || n > 4) return set_error(B200RT_EINVAL, "b200rt_render_set_streams: 1 .. 4");
+    g_wf_sets.store(n);
+    return B200RT_OK;
+}
 static int render_impl(b200rt_scene *s, const b200rt_render_desc *d, float *film, uint32_t *heat, b200rt_render_stats *stats,
                        void *stream);
 extern "C" int b200rt_render(b200rt_scene *s, const b200rt_render_desc *d, float *film, b200rt_render_stats *stats,
@@ -469,7 +503,8 @@ static int render_impl(b200rt_scene *s, const b200rt_render_desc *d, float *film
     std::lock_guard<std::mutex> wsLock(w->mu);
     const uint32_t tp = P.tl.tile * P.tl.tile;
     const uint64_t unit = (uint64_t)tp * P.tl.spp;  // batches hold whole tiles so a pixel's samples never split
-    uint64_t want = d->max_batch ? d->max_batch : (1u << 22);
+    static const uint64_t envBatch = [] { const char *e = getenv("B200RT_WF_BATCH"); return e ? (uint64_t)atoll(e) : 0ull; }();
+    uint64_t want = d->max_batch ? d->max_batch : (envBatch ? envBatch : (1u << 22));
     uint64_t cap = std::max<uint64_t>(unit, want / unit * unit);
     cap = std::min<uint64_t>(cap, std::max<uint64_t>(unit, P.tl.n_paths_rank));
     if (cap > 0x7fffffffull) return set_error(B200RT_EINVAL, "batch too large");
@@ -566,14 +601,14 @@ static int render_impl(b200rt_scene *s, const b200rt_render_desc *d, float *film
     // timing events come from the workspace's pool and are only recorded when statistics are asked for
     size_t evUsed = 0;
     bool evFail = false;
-    auto ev = [&]() -> cudaEvent_t {
+    auto ev = [&](cudaStream_t on) -> cudaEvent_t {
         if (evUsed == w->events.size()) {
             cudaEvent_t e = nullptr;
             if (cudaEventCreate(&e) != cudaSuccess) { evFail = true; return nullptr; }
             w->events.push_back(e);
         }
         cudaEvent_t e = w->events[evUsed++];
-        cudaEventRecord(e, st);
+        cudaEventRecord(e, on);
         return e;
     };
     struct Span { cudaEvent_t a, b; bool any; };
@@ -581,74 +616,108 @@ static int render_impl(b200rt_scene *s, const b200rt_render_desc *d, float *film
     const bool timed = stats != nullptr;
     const uint64_t launches0 = g_launches.load();
     uint64_t nClosest = 0, nShadow = 0, nCamera = 0, nMis = 0;
-    cudaEvent_t t0 = timed ? ev() : nullptr;
+    // ---- one or two wavefronts in flight ----
+    const int envSets = g_wf_sets.load();
+    const int nSets = (heat || w->keep) ? 1 : (int)std::min<uint64_t>((uint64_t)envSets, nBatches);
+    const bool two = nSets >= 2;
+    if (two) {
+        if (!w->evFork) WCU(cudaEventCreateWithFlags(&w->evFork, cudaEventDisableTiming));
+        for (int k = 0; k < nSets; ++k)
+            if (!w->side[k]) { WCU(cudaStreamCreateWithFlags(&w->side[k], cudaStreamNonBlocking)); WCU(cudaEventCreateWithFlags(&w->evJoin[k], cudaEventDisableTiming)); }
+        for (int i = 0; i < nSets - 1; ++i) {
+            if (w->altCap[i] >= w->cap && (!mis || w->altMis[i])) continue;
+            free_alt(w, i);
+            QSet &q = w->alt[i];
+            const size_t c = w->cap;
+            for (int k = 0; k < 2; ++k) { WCU(cudaMalloc(&q.rays[k], c * 32)); WCU(cudaMalloc(&q.qPath[k], c * 4)); }
+            WCU(cudaMalloc(&q.shRays, c * 32)); WCU(cudaMalloc(&q.shContrib, c * 16)); WCU(cudaMalloc(&q.shPath, c * 4));
+            WCU(cudaMalloc(&q.beta, c * 16)); WCU(cudaMalloc(&q.L, c * 16)); WCU(cudaMalloc(&q.pdim, c * 4));
+            WCU(cudaMalloc(&q.hits, c * sizeof(b200rt_hit))); WCU(cudaMalloc(&q.occ, c));
+            WCU(cudaMalloc(&q.counts, 4 * 3 * 72));
+            if (mis) { WCU(cudaMalloc(&q.misRays, c * 32)); WCU(cudaMalloc(&q.misContrib, c * 16)); WCU(cudaMalloc(&q.misPath, c * 4)); w->altMis[i] = true; }
+            w->altCap[i] = c;
+        }
+    }
+    QSet prim;
+    prim.rays[0] = w->rays[0]; prim.rays[1] = w->rays[1]; prim.qPath[0] = w->qPath[0]; prim.qPath[1] = w->qPath[1];
+    prim.shRays = w->shRays; prim.shContrib = w->shContrib; prim.shPath = w->shPath; prim.beta = w->beta; prim.L = w->L; prim.pdim = w->pdim;
+    prim.hits = w->hits; prim.occ = w->occ; prim.counts = w->counts;
+    prim.misRays = w->misRays; prim.misContrib = w->misContrib; prim.misPath = w->misPath;
+    cudaEvent_t t0 = timed ? ev(st) : nullptr;
+    if (two) {   // the side streams start after everything queued on the caller's stream so far (uploads, film copy, memsets)
+        WCU(cudaEventRecord(w->evFork, st));
+        for (int k = 0; k < nSets; ++k) WCU(cudaStreamWaitEvent(w->side[k], w->evFork, 0));
+    }
     const unsigned TB = 256;
     uint64_t batch = 0;
     for (uint64_t start = 0; start < P.tl.n_paths_rank; start += cap, ++batch) {
         const uint32_t nSlots = (uint32_t)std::min<uint64_t>(cap, P.tl.n_paths_rank - start);
+        const int set = two ? (int)(batch % (uint64_t)nSets) : 0;
+        const QSet &Q = set ? w->alt[set - 1] : prim;
+        cudaStream_t bs = two ? w->side[set] : st;
         const unsigned gridSlots = (nSlots + TB - 1) / TB;
-        WCU(cudaMemsetAsync(w->counts, 0, 4 * nCounts, st));
+        WCU(cudaMemsetAsync(Q.counts, 0, 4 * nCounts, bs));
         // counts[2*depth] = closest queue size at depth, counts[2*depth+1] = shadow queue size at depth
-        k_camera<<<gridSlots, TB, 0, st>>>(P, start, nSlots, w->rays[0], w->qPath[0], w->counts, w->beta, w->L, w->pdim);
+        k_camera<<<gridSlots, TB, 0, bs>>>(P, start, nSlots, Q.rays[0], Q.qPath[0], Q.counts, Q.beta, Q.L, Q.pdim);
         g_launches.fetch_add(1);
         int cur = 0;
         for (uint32_t depth = 0; depth <= d->max_depth; ++depth) {
             if (w->keep) {
-                WCU(cudaMemcpyAsync(w->kept[2 * depth], w->rays[cur], (size_t)nSlots * 32, cudaMemcpyDeviceToDevice, st));
-                WCU(cudaMemcpyAsync(w->keptPath[2 * depth], w->qPath[cur], (size_t)nSlots * 4, cudaMemcpyDeviceToDevice, st));
+                WCU(cudaMemcpyAsync(w->kept[2 * depth], Q.rays[cur], (size_t)nSlots * 32, cudaMemcpyDeviceToDevice, bs));
+                WCU(cudaMemcpyAsync(w->keptPath[2 * depth], Q.qPath[cur], (size_t)nSlots * 4, cudaMemcpyDeviceToDevice, bs));
             }
-            cudaEvent_t a = timed ? ev() : nullptr;
-            rc = launch_trace(s, w->rays[cur], nSlots, w->counts + 2 * depth, w->hits, nullptr, false,
-                              heat ? s->d_counters : nullptr, st, heat ? w->perRay : nullptr);
+            cudaEvent_t a = timed ? ev(bs) : nullptr;
+            rc = launch_trace(s, Q.rays[cur], nSlots, Q.counts + 2 * depth, Q.hits, nullptr, false,
+                              heat ? s->d_counters : nullptr, bs, heat ? w->perRay : nullptr);
             if (rc) return rc;
-            if (timed) spans.push_back({a, ev(), false});
+            if (timed) spans.push_back({a, ev(bs), false});
             if (heat) {
-                k_heat<<<gridSlots, TB, 0, st>>>(P, start, w->counts + 2 * depth, w->qPath[cur], w->perRay, d_heat, 0u);
+                k_heat<<<gridSlots, TB, 0, bs>>>(P, start, Q.counts + 2 * depth, Q.qPath[cur], w->perRay, d_heat, 0u);
                 g_launches.fetch_add(1);
             }
             // path.cpp:110: the last intersection is found, then the path ends — after the emitted radiance a specular
             // bounce may still see there (path.cpp:97-107): one more shade launch, which only adds Le
             if (depth == d->max_depth && !(P.has_specular && mis)) break;
-            (full ? k_shade<true> : k_shade<false>)<<<gridSlots, TB, 0, st>>>(P, depth, start, w->counts + 2 * depth, w->rays[cur], w->qPath[cur], w->hits,
-                                              s->d_prim_tris, w->beta, w->pdim, w->rays[cur ^ 1], w->qPath[cur ^ 1],
-                                              w->counts + 2 * (depth + 1), w->shRays, w->shPath, w->shContrib,
-                                              w->counts + 2 * depth + 1, w->L, w->misRays, w->misPath, w->misContrib,
-                                              w->counts + misBase + depth);
+            (full ? k_shade<true> : k_shade<false>)<<<gridSlots, TB, 0, bs>>>(P, depth, start, Q.counts + 2 * depth, Q.rays[cur], Q.qPath[cur], Q.hits,
+                                              s->d_prim_tris, Q.beta, Q.pdim, Q.rays[cur ^ 1], Q.qPath[cur ^ 1],
+                                              Q.counts + 2 * (depth + 1), Q.shRays, Q.shPath, Q.shContrib,
+                                              Q.counts + 2 * depth + 1, Q.L, Q.misRays, Q.misPath, Q.misContrib,
+                                              Q.counts + misBase + depth);
             g_launches.fetch_add(1);
             if (depth == d->max_depth) break;
             if (w->keep) {
-                WCU(cudaMemcpyAsync(w->kept[2 * depth + 1], w->shRays, (size_t)nSlots * 32, cudaMemcpyDeviceToDevice, st));
-                WCU(cudaMemcpyAsync(w->keptPath[2 * depth + 1], w->shPath, (size_t)nSlots * 4, cudaMemcpyDeviceToDevice, st));
-                WCU(cudaMemcpyAsync(w->keptContrib[2 * depth + 1], w->shContrib, (size_t)nSlots * 16, cudaMemcpyDeviceToDevice, st));
+                WCU(cudaMemcpyAsync(w->kept[2 * depth + 1], Q.shRays, (size_t)nSlots * 32, cudaMemcpyDeviceToDevice, bs));
+                WCU(cudaMemcpyAsync(w->keptPath[2 * depth + 1], Q.shPath, (size_t)nSlots * 4, cudaMemcpyDeviceToDevice, bs));
+                WCU(cudaMemcpyAsync(w->keptContrib[2 * depth + 1], Q.shContrib, (size_t)nSlots * 16, cudaMemcpyDeviceToDevice, bs));
                 if (mis) {
                     const size_t q = 2 * (size_t)(d->max_depth + 1) + depth;
-                    WCU(cudaMemcpyAsync(w->kept[q], w->misRays, (size_t)nSlots * 32, cudaMemcpyDeviceToDevice, st));
-                    WCU(cudaMemcpyAsync(w->keptPath[q], w->misPath, (size_t)nSlots * 4, cudaMemcpyDeviceToDevice, st));
-                    WCU(cudaMemcpyAsync(w->keptContrib[q], w->misContrib, (size_t)nSlots * 16, cudaMemcpyDeviceToDevice, st));
+                    WCU(cudaMemcpyAsync(w->kept[q], Q.misRays, (size_t)nSlots * 32, cudaMemcpyDeviceToDevice, bs));
+                    WCU(cudaMemcpyAsync(w->keptPath[q], Q.misPath, (size_t)nSlots * 4, cudaMemcpyDeviceToDevice, bs));
+                    WCU(cudaMemcpyAsync(w->keptContrib[q], Q.misContrib, (size_t)nSlots * 16, cudaMemcpyDeviceToDevice, bs));
                 }
             }
-            a = timed ? ev() : nullptr;
-            rc = launch_trace(s, w->shRays, nSlots, w->counts + 2 * depth + 1, nullptr, w->occ, true,
-                              heat ? s->d_counters : nullptr, st, heat ? w->perRay : nullptr);
+            a = timed ? ev(bs) : nullptr;
+            rc = launch_trace(s, Q.shRays, nSlots, Q.counts + 2 * depth + 1, nullptr, Q.occ, true,
+                              heat ? s->d_counters : nullptr, bs, heat ? w->perRay : nullptr);
             if (rc) return rc;
-            if (timed) spans.push_back({a, ev(), true});
+            if (timed) spans.push_back({a, ev(bs), true});
             if (heat) {
-                k_heat<<<gridSlots, TB, 0, st>>>(P, start, w->counts + 2 * depth + 1, w->shPath, w->perRay, d_heat, 1u);
+                k_heat<<<gridSlots, TB, 0, bs>>>(P, start, Q.counts + 2 * depth + 1, Q.shPath, w->perRay, d_heat, 1u);
                 g_launches.fetch_add(1);
             }
-            k_shadow_resolve<<<gridSlots, TB, 0, st>>>(w->counts + 2 * depth + 1, w->occ, w->shPath, w->shContrib, w->L);
+            k_shadow_resolve<<<gridSlots, TB, 0, bs>>>(Q.counts + 2 * depth + 1, Q.occ, Q.shPath, Q.shContrib, Q.L);
             g_launches.fetch_add(1);
-            if (mis) {  // EstimateDirect's BSDF-sampled ray: one more closest-hit queue per bounce (w->hits is free again)
-                a = timed ? ev() : nullptr;
-                rc = launch_trace(s, w->misRays, nSlots, w->counts + misBase + depth, w->hits, nullptr, false,
-                                  heat ? s->d_counters : nullptr, st, heat ? w->perRay : nullptr);
+            if (mis) {  // EstimateDirect's BSDF-sampled ray: one more closest-hit queue per bounce (Q.hits is free again)
+                a = timed ? ev(bs) : nullptr;
+                rc = launch_trace(s, Q.misRays, nSlots, Q.counts + misBase + depth, Q.hits, nullptr, false,
+                                  heat ? s->d_counters : nullptr, bs, heat ? w->perRay : nullptr);
                 if (rc) return rc;
-                if (timed) spans.push_back({a, ev(), false});
+                if (timed) spans.push_back({a, ev(bs), false});
                 if (heat) {
-                    k_heat<<<gridSlots, TB, 0, st>>>(P, start, w->counts + misBase + depth, w->misPath, w->perRay, d_heat, 0u);
+                    k_heat<<<gridSlots, TB, 0, bs>>>(P, start, Q.counts + misBase + depth, Q.misPath, w->perRay, d_heat, 0u);
                     g_launches.fetch_add(1);
                 }
-                k_mis_resolve<<<gridSlots, TB, 0, st>>>(w->counts + misBase + depth, w->hits, infinite ? (uint32_t)B200RT_MISS : d->light_prim, w->misPath, w->misContrib, w->L);
+                k_mis_resolve<<<gridSlots, TB, 0, bs>>>(Q.counts + misBase + depth, Q.hits, infinite ? (uint32_t)B200RT_MISS : d->light_prim, Q.misPath, Q.misContrib, Q.L);
                 g_launches.fetch_add(1);
             }
             cur ^= 1;
@@ -656,17 +725,19 @@ static int render_impl(b200rt_scene *s, const b200rt_render_desc *d, float *film
             // look at the next queue's size every 4th depth and stop launching once no path is left
             if (depth >= 7 && (depth & 3) == 3 && depth + 1 < d->max_depth) {
                 uint32_t *left = w->hCounts + batch * nCounts + 2 * (depth + 1);
-                WCU(cudaMemcpyAsync(left, w->counts + 2 * (depth + 1), 4, cudaMemcpyDeviceToHost, st));
-                WCU(cudaStreamSynchronize(st));
+                WCU(cudaMemcpyAsync(left, Q.counts + 2 * (depth + 1), 4, cudaMemcpyDeviceToHost, bs));
+                WCU(cudaStreamSynchronize(bs));
                 if (*left == 0) break;
             }
         }
         const uint32_t nPix = nSlots / P.tl.spp;
-        k_film<<<(nPix + TB - 1) / TB, TB, 0, st>>>(P, start, nPix, w->L, d_film, w->splatCount, w->splatPix, w->splatVal, w->splatCap);
+        k_film<<<(nPix + TB - 1) / TB, TB, 0, bs>>>(P, start, nPix, Q.L, d_film, w->splatCount, w->splatPix, w->splatVal, w->splatCap);
         g_launches.fetch_add(1);
         // the batch's queue sizes go to pinned host memory without stopping the stream; they are read after the last batch
-        WCU(cudaMemcpyAsync(w->hCounts + batch * nCounts, w->counts, 4 * nCounts, cudaMemcpyDeviceToHost, st));
+        WCU(cudaMemcpyAsync(w->hCounts + batch * nCounts, Q.counts, 4 * nCounts, cudaMemcpyDeviceToHost, bs));
     }
+    if (two)
+        for (int k = 0; k < nSets; ++k) { WCU(cudaEventRecord(w->evJoin[k], w->side[k])); WCU(cudaStreamWaitEvent(st, w->evJoin[k], 0)); }
     // boundary samples' contributions to neighbouring pixels, one direction after the other (grid-stride over the
     // device-side list sizes: no host round trip; an overflow of the lists is reported after the frame)
     uint32_t *hSplat = w->hCounts + nBatches * nCounts;
@@ -677,7 +748,7 @@ static int render_impl(b200rt_scene *s, const b200rt_render_desc *d, float *film
     WCU(cudaMemcpyAsync(hSplat, w->splatCount, 8 * 4, cudaMemcpyDeviceToHost, st));
     if (!film_dev) WCU(cudaMemcpyAsync(film, d_film, npx * 16, cudaMemcpyDeviceToHost, st));
     if (heat && !heat_dev) WCU(cudaMemcpyAsync(heat, d_heat, npx * 4 * B200RT_HEAT_PLANES, cudaMemcpyDeviceToHost, st));
-    cudaEvent_t t1 = timed ? ev() : nullptr;
+    cudaEvent_t t1 = timed ? ev(st) : nullptr;
     WCU(cudaStreamSynchronize(st));
     WCU(cudaGetLastError());
     if (evFail) return set_error(B200RT_ECUDA, "cudaEventCreate failed");
