@@ -96,7 +96,7 @@ def test_golden_triangles(gpu):
     """Single-triangle scenes: watertight vertex/edge rays, 1e+-8 coordinates, BadCases, degenerates."""
     g = load_golden("ref_triangle.npz")
     n = len(g["tris"])
-    for i in list(range(0, n, 7)) + list(range(3195, n)):
+    for i in range(n):   # every case of the fixture
         v = g["tris"][i:i + 1]
         acc = gpu.B200Accel(gpu.build_bvh(v), v)
         h = acc.Intersect(g["rays"][i:i + 1])

@@ -71,3 +71,12 @@ def test_living_room_materials_are_the_files_kinds():
                        [1.657460, 0.880369, 0.521229, 9.223869, 6.269523, 4.837001, .02])   # scene.pbrt:21
     assert set(np.unique(lr["legacy_materials"][:, 0])) <= {0.0, 1.0}
     assert lr["prim_material"].max() < len(lr["materials"]) and len(lr["prim_material"]) == 143163
+
+
+def test_conference_standin_is_deterministic_and_sized():
+    """BASELINE config 3 names conference next to museum; neither geometry is in the reference tree."""
+    from b200rt import scenes
+    a, b = scenes.conference_standin(xres=64, yres=64), scenes.conference_standin(xres=64, yres=64)
+    assert np.array_equal(a["tri_verts"], b["tri_verts"])
+    assert 250_000 < len(a["tri_verts"]) < 320_000 and np.isfinite(a["tri_verts"]).all()
+    assert a["maxdepth"] == 1 and "STAND-IN" in a["note"]

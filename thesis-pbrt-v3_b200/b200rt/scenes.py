@@ -532,6 +532,74 @@ def museum_standin(seed=11, detail=1.45, xres=700, yres=700):
                      % (seed, detail, len(tv)))
 
 
+def conference_standin(seed=5, detail=1.65, xres=700, yres=700):
+    """Procedural meeting room standing in for the thesis's conference scene (BASELINE config 3 names it next to the
+    museum; `scenes/conference` and `scenes/test_conference_local(_k)` are listed in .MISSING_LARGE_BLOBS, so the reference
+    tree holds neither the geometry nor the template).  A room with a coffered ceiling and panelled walls, a long oval
+    table with a raised rim, two rows of chairs (seat, back of vertical slats, four turned legs, arm rests), ceiling lamps
+    and a lectern; ~280 k triangles at the default detail (the classic conference model has 282 k).  No template exists, so
+    camera and light follow the museum template's conventions: an eye at head height in a corner looking along the table,
+    fov 60, a point light under the ceiling, path maxdepth 1, 64 spp, 700x700."""
+    rng = np.random.default_rng(seed)
+    k = float(np.sqrt(detail))
+    n = lambda x: max(2, int(round(x * k)))
+    parts = []
+    X0, X1, Z0, Z1, H = -0.8, 0.8, -0.45, 0.45, 0.55
+    def floor(u, v):
+        x, z = X0 + u * (X1 - X0), Z0 + v * (Z1 - Z0)
+        return np.stack([x, 0.001 * np.sin(40 * np.pi * u) * np.sin(40 * np.pi * v), z], 1)
+    parts.append(_surface(floor, n(150), n(90)))
+    def ceiling(u, v):   # coffers
+        x, z = X0 + u * (X1 - X0), Z0 + v * (Z1 - Z0)
+        y = H - 0.02 * ((np.abs(np.sin(8 * np.pi * u)) < 0.15) | (np.abs(np.sin(5 * np.pi * v)) < 0.15))
+        return np.stack([x, y, z], 1)
+    parts.append(_surface(ceiling, n(170), n(100)))
+    for zpos, sgn in ((Z0, 1), (Z1, -1)):
+        def wall(u, v, zpos=zpos, sgn=sgn):
+            x, y = X0 + u * (X1 - X0), v * H
+            return np.stack([x, y, zpos + sgn * 0.005 * (np.sin(22 * np.pi * u) > 0.85) + sgn * 0.008 * (v < 0.1)], 1)
+        parts.append(_surface(wall, n(140), n(50)))
+    for xpos in (X0, X1):
+        def wall(u, v, xpos=xpos):
+            z, y = Z0 + u * (Z1 - Z0), v * H
+            return np.stack([np.full_like(z, xpos), y, z], 1)
+        parts.append(_surface(wall, n(60), n(40)))
+    # the table: an oval top with a raised rim on a central plinth
+    def top(u, v):
+        ang, r = 2 * np.pi * u, v
+        y = 0.2 + 0.004 * (v > 0.93)
+        return np.stack([0.5 * r * np.cos(ang), y, 0.16 * r * np.sin(ang)], 1)
+    parts.append(_surface(top, n(220), n(40)))
+    def rim(u, v):
+        ang = 2 * np.pi * u
+        return np.stack([0.5 * np.cos(ang), 0.185 + 0.02 * v, 0.16 * np.sin(ang)], 1)
+    parts.append(_surface(rim, n(220), n(4)))
+    parts.append(_box((-0.35, 0.0, -0.05), (0.35, 0.185, 0.05), n(10)))
+    # chairs along both long sides
+    for side in (-1, 1):
+        for cx in np.linspace(-0.42, 0.42, 9):
+            cz = side * 0.25
+            parts.append(_box((cx - 0.035, 0.11, cz - 0.035), (cx + 0.035, 0.12, cz + 0.035), n(6)))      # seat
+            for sx in np.linspace(-0.03, 0.03, 5):                                                       # back slats
+                parts.append(_box((cx + sx - 0.004, 0.12, cz + side * 0.032), (cx + sx + 0.004, 0.24, cz + side * 0.037), n(3)))
+            parts.append(_box((cx - 0.035, 0.235, cz + side * 0.03), (cx + 0.035, 0.25, cz + side * 0.04), n(4)))
+            for ax in (-0.033, 0.033):                                                                     # arm rests
+                parts.append(_box((cx + ax - 0.004, 0.16, cz - 0.03), (cx + ax + 0.004, 0.165, cz + 0.03), n(3)))
+            for lx in (-0.03, 0.03):
+                for lz in (-0.03, 0.03):
+                    parts.append(_lathe(lambda v: (0.004 + 0.0015 * np.sin(5 * np.pi * v), 0.11 * v), cx + lx, cz + lz, 0.0, n(10), n(14)))
+    # ceiling lamps and a lectern
+    for lx in np.linspace(-0.5, 0.5, 5):
+        parts.append(_lathe(lambda v: (0.03 * np.sin(np.pi * v * 0.5) + 0.002, -0.03 * v), lx, 0.0, H - 0.02, n(28), n(16)))
+    parts.append(_box((0.62, 0.0, -0.06), (0.7, 0.22, 0.06), n(8)))
+    parts.append(_lathe(lambda v: (0.012 + 0.004 * rng.random(), 0.05 * v), 0.66, 0.0, 0.22, n(16), n(8)))
+    tv = np.concatenate(parts).astype(np.float32) + np.float32(0)
+    cam = look_at_camera((0.7, 0.3, -0.38), (-0.3, 0.12, 0.1), (0, 1, 0), 60, xres, yres)
+    return dict(name="conference-standin", tri_verts=tv, camera=cam, light=np.array([0, .5, 0], np.float32), maxdepth=1, spp=64,
+                note="PROCEDURAL STAND-IN for scenes/conference (geometry AND template absent from the reference tree), seed=%d "
+                     "detail=%g, %d triangles" % (seed, detail, len(tv)))
+
+
 def soup(n, seed=1, extent=10.0, size=0.5):
     """Random triangle soup (unit tests)."""
     rng = np.random.default_rng(seed)
