@@ -31,9 +31,12 @@ def main():
     b200rt.init(0)
     torch.zeros(1, device="cuda")
     st = torch.cuda.current_stream().cuda_stream
-    sc = scenes.sponza_standin() if scene == "sponza" else scenes.killeroo_simple()
+    sc = {"sponza": scenes.sponza_standin, "killeroo": scenes.killeroo_simple, "museum": scenes.museum_standin,
+          "conference": scenes.conference_standin, "living": scenes.living_room}[scene]()
+    maxdepth = int(os.environ.get("B200RT_AB_MAXDEPTH", sc.get("maxdepth", 5) if scene in ("museum", "conference") else 5))
     acc = b200rt.MakeAccelerator(accname, sc["tri_verts"])
-    integ = b200rt.WavefrontPathIntegrator(sc["camera"], spp=spp, maxdepth=5, light_pos=sc["light"], seed=1)
+    light = sc["light"] if "light" in sc else np.array([0.0, 1.5, 0.0], np.float32)   # (living-room: a point light stands in for its sky)
+    integ = b200rt.WavefrontPathIntegrator(sc["camera"], spp=spp, maxdepth=maxdepth, light_pos=light, seed=1)
     film = torch.zeros(integ.shape, dtype=torch.float32, device="cuda")
     wf.keep_queues(acc, True)
     integ.render_ptr(acc, film.data_ptr(), st)
