@@ -1,7 +1,7 @@
 """ncu target: one launch each of the production kernels on three real wavefront queues of the bench
 workload (q0 = camera rays, q4 = closest-hit queue at depth 2, q5 = shadow queue at depth 2).
 
-    ncu --set full -k regex:bvh_persistent -c 3 python scripts/prof_queue.py [spp]
+    ncu --set full -k regex:bvh_persistent -c 3 python scripts/prof_queue.py [spp] [bvh|kdtree] [sponza|museum|conference|killeroo]
 The render that produces the queues runs on the baseline kernel so that only the three launches of
 interest match the filter."""
 import os, sys
@@ -17,7 +17,9 @@ os.environ["B200RT_KERNEL"] = "baseline"
 b200rt.init(0)
 torch.zeros(1, device="cuda")
 st = torch.cuda.current_stream().cuda_stream
-sc = scenes.sponza_standin()
+scene = sys.argv[3] if len(sys.argv) > 3 else "sponza"
+sc = {"sponza": scenes.sponza_standin, "museum": scenes.museum_standin, "conference": scenes.conference_standin,
+      "killeroo": scenes.killeroo_simple}[scene]()
 acc = b200rt.MakeAccelerator(accname, sc["tri_verts"])
 integ = b200rt.WavefrontPathIntegrator(sc["camera"], spp=spp, maxdepth=5, light_pos=sc["light"], seed=1)
 film = torch.zeros(integ.shape, dtype=torch.float32, device="cuda")

@@ -48,6 +48,7 @@ int g_sm_count = 148;
 // tuning knobs (read once in b200rt_init): B200RT_KERNEL=baseline selects the one-ray-per-thread kernel
 // for A/B measurements; B200RT_THRESH = busy-lane count below which a persistent warp refills.
 static int g_use_baseline = 0;
+static int g_coherent_baseline = 1;   // B200RT_COHERENT_BASELINE=0: persistent kernel on every queue
 static uint32_t g_thresh = 14;
 static int g_pblocks[6][2];  // resident persistent blocks per SM, [kind][any]
 static int g_persist_bsp = 1;
@@ -99,6 +100,7 @@ extern "C" int b200rt_init(int device) {
     cudaDeviceProp p;
     CU(cudaGetDeviceProperties(&p, device));
     g_sm_count = p.multiProcessorCount;
+    if (const char *e = getenv("B200RT_COHERENT_BASELINE")) g_coherent_baseline = atoi(e);
     if (const char *e = getenv("B200RT_KERNEL")) g_use_baseline = std::strcmp(e, "baseline") == 0;
     if (const char *e = getenv("B200RT_THRESH")) g_thresh = (uint32_t)atoi(e);
     if (const char *e = getenv("B200RT_PIPE_CHUNK")) g_pipe_chunk = std::min<uint32_t>(B200RT_PIPE_CHUNK_MAX, std::max(1024, atoi(e)));
@@ -591,12 +593,16 @@ __global__ void miss_kernel(const float4 *__restrict__ rays, uint64_t n, b200rt_
 }
 
 int b200rt::launch_trace(const b200rt_scene *s, const float4 *rays, uint64_t n, const uint32_t *n_dev, b200rt_hit *hits,
-                         uint8_t *occ, bool any, Counters *counters, cudaStream_t st, uint4 *per_ray) {
+                         uint8_t *occ, bool any, Counters *counters, cudaStream_t st, uint4 *per_ray, bool coherent) {
     if (n == 0) return B200RT_OK;
     if (s->empty) {
         miss_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(rays, n, any ? nullptr : hits, any ? occ : nullptr);
         g_launches.fetch_add(1);
-    } else if (!counters && !g_use_baseline && (s->kind == B200RT_BVH || g_persist_bsp)) {
+    } else if (!counters && !g_use_baseline && (s->kind == B200RT_BVH || (g_persist_bsp && !(coherent && g_coherent_baseline)))) {
+        // (kd / RBSP / BSP trees on a COHERENT queue — the wavefront's camera rays and their shadow rays — go to the
+        // one-ray-per-thread kernel below: every lane is busy anyway, so the persistent kernel's votes are pure overhead there:
+        // museum kd camera 1.80 vs 2.46 ms, first shadow queue 1.17 vs 1.47 ms, conference kd camera +40 %
+        // (profiles/r02_ab_kd_queues.log); the BVH's persistent kernel is as fast on them, 4.31 vs 4.25 Grays/s)
         // production path: persistent warps (rt_persist.cuh); <= 2^30 rays per launch
         const uint64_t kMax = 1ull << 30;
         for (uint64_t off = 0; off < n; off += kMax) {

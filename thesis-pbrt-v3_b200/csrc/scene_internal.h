@@ -50,6 +50,6 @@ namespace b200rt {
 // Launches the traversal kernel on device-resident buffers.  n_dev (nullable): device-side ray count
 // (queue sizes produced by the wavefront stages) — the kernel traces min(n, *n_dev) rays.
 int launch_trace(const b200rt_scene *s, const float4 *rays, uint64_t n, const uint32_t *n_dev, b200rt_hit *hits,
-                 uint8_t *occ, bool any, Counters *counters, cudaStream_t st, uint4 *per_ray = nullptr);
+                 uint8_t *occ, bool any, Counters *counters, cudaStream_t st, uint4 *per_ray = nullptr, bool coherent = false);
 int set_error(int code, const char *fmt, ...);
 }  // namespace b200rt

@@ -668,7 +668,7 @@ static int render_impl(b200rt_scene *s, const b200rt_render_desc *d, float *film
             }
             cudaEvent_t a = timed ? ev(bs) : nullptr;
             rc = launch_trace(s, Q.rays[cur], nSlots, Q.counts + 2 * depth, Q.hits, nullptr, false,
-                              heat ? s->d_counters : nullptr, bs, heat ? w->perRay : nullptr);
+                              heat ? s->d_counters : nullptr, bs, heat ? w->perRay : nullptr, depth == 0);
             if (rc) return rc;
             if (timed) spans.push_back({a, ev(bs), false});
             if (heat) {
@@ -698,7 +698,7 @@ static int render_impl(b200rt_scene *s, const b200rt_render_desc *d, float *film
             }
             a = timed ? ev(bs) : nullptr;
             rc = launch_trace(s, Q.shRays, nSlots, Q.counts + 2 * depth + 1, nullptr, Q.occ, true,
-                              heat ? s->d_counters : nullptr, bs, heat ? w->perRay : nullptr);
+                              heat ? s->d_counters : nullptr, bs, heat ? w->perRay : nullptr, depth == 0);
             if (rc) return rc;
             if (timed) spans.push_back({a, ev(bs), true});
             if (heat) {
