@@ -483,7 +483,7 @@ def main():
                     "counters_checked_vs_oracle": bool(checked),
                     "note": "achieved = ALGORITHMIC bytes (reference traversal's node+triangle fetches) / kernel time; the "
                             "tree (~30 MB) is L1/L2-resident so DRAM traffic is far below it and the fraction can exceed 1; "
-                            "the kernel's real bounds are the L1 data pipe and SIMT divergence (ncu, profiles/r01_ncu_full_v6_summary.txt: l1tex throughput 83 % of peak, 13 of 32 lanes active per instruction)"}
+                            "the kernel's real bounds are the L1 data pipe and SIMT divergence (ncu, profiles/r02_ncu_full_bvh_summary.txt launch 1: l1tex throughput 83 % of peak, 13.2 of 32 lanes active per instruction, long-scoreboard 3.8 warps per issue)"}
         # ---- cpu_baseline: the reference's own code on the host cores, bounded sample ----------
         cpu = None
         if not args.no_cpu_baseline:
