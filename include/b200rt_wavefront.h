@@ -188,6 +188,19 @@ int b200rt_render_queue_paths(b200rt_scene *scene, uint32_t queue, uint32_t *pat
 int b200rt_camera_perspective(const float *lookat9, const float *w2c16, float fov, uint32_t xres, uint32_t yres,
                               b200rt_render_desc *desc);
 
+/* The one exchange step of a multi-process render (one process per GPU, ONE node): sums the films of all `world` ranks into
+ * rank 0's buffer, in rank order (deterministic).  Replaces what Film::MergeFilmTile (src/core/film.cpp:118-135) does for the
+ * reference's threads: each rank's film holds its own tiles, the boundary samples' contributions to the one-pixel halo around
+ * them, and zeros elsewhere, so the frame is the sum.  Rank 0 maps each peer's device buffer through CUDA IPC (NVLink / NVSwitch
+ * peer access between GPUs; also works for ranks sharing a GPU) and adds it with one kernel; there is no launcher on the C++
+ * side (`pbrt scene.pbrt` per rank), so the handles travel through files `film.<rank>` / `done.<rank>` in the directory
+ * `rendezvous`, which every rank must reach and which must not hold files of an earlier, aborted call.
+ * film: HOST or DEVICE, n_floats = 4 * pixels; heat: optional (NULL) B200RT_HEAT_PLANES planes of uint32, summed likewise.
+ * On rank 0 film / heat hold the frame afterwards; on other ranks they are unchanged.  Blocks until rank 0 has read this
+ * rank's buffer; timeout_s <= 0 means 120 s.  world <= 1 returns 0 at once. */
+int b200rt_film_reduce(const char *rendezvous, uint32_t rank, uint32_t world, float *film, uint64_t n_floats,
+                       uint32_t *heat, uint64_t n_heat, double timeout_s);
+
 #ifdef __cplusplus
 }
 #endif

@@ -20,11 +20,12 @@ def write_killeroo_geometry(path):
 
 
 def killeroo_simple(dirname, accelerator, integrator='Integrator "path" "integer maxdepth" [5]', xres=700, yres=700, spp=8,
-                    filename="killeroo-simple.pfm", extra_film=""):
+                    filename="killeroo-simple.pfm", extra_film="", scene_name="input.pbrt"):
     """scenes/killeroo-simple with its Accelerator line replaced by `accelerator` (a full directive) and, optionally, its
     Integrator line by `integrator`.  Returns the scene file's path."""
     geo = os.path.join(dirname, "killeroo.pbrt")
-    write_killeroo_geometry(geo)
+    if not os.path.exists(geo):
+        write_killeroo_geometry(geo)
     txt = '''LookAt 400 20 30   0 63 -110   0 0 1
 Rotate -5 0 0 1
 Camera "perspective" "float fov" [39]
@@ -74,7 +75,7 @@ Translate -200 0 0
 AttributeEnd
 WorldEnd
 ''' % (xres, yres, filename, extra_film, spp, accelerator, integrator, geo, geo)
-    path = os.path.join(dirname, "input.pbrt")
+    path = os.path.join(dirname, scene_name)
     with open(path, "w") as f:
         f.write(txt)
     return path

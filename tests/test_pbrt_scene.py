@@ -71,3 +71,39 @@ def test_parsed_scene_renders_on_the_b200(tmp_path, tree):
     print("\nparsed killeroo-simple, tree %s: %s" % (tree, st))
     assert img.shape == ref.shape == (700, 700, 3)
     assert st["rel_rmse_excl"] <= 1e-4 and st["frac_differing"] < 1e-3, st
+
+
+@pytest.mark.gpu
+def test_two_ranks_write_one_image(tmp_path):
+    """`Integrator "b200wavefront" "integer world" [2]`: two pbrt processes (here sharing the one GPU of the box), each rendering
+    the tiles t % 2 == rank; b200rt_film_reduce sums rank 1's film into rank 0's over CUDA IPC and rank 0 alone writes the
+    image, which equals the one-process image (boundary-sample halos are the only pixels summed in another order)."""
+    import pbrt_scenes as ps
+    d = str(tmp_path)
+    rdv = os.path.join(d, "rdv")
+    os.makedirs(rdv)
+    kw = dict(xres=256, yres=256, spp=4)
+    one = ps.killeroo_simple(d, 'Accelerator "b200" "string tree" "bvh"', integrator='Integrator "b200wavefront"', filename="one.pfm",
+                             scene_name="one.pbrt", **kw)
+    rc, out = _run(one, d)
+    assert rc == 0, out
+    procs = []
+    for r in (1, 0):
+        sc = ps.killeroo_simple(d, 'Accelerator "b200" "string tree" "bvh"',
+                                integrator='Integrator "b200wavefront" "integer rank" [%d] "integer world" [2] "string rendezvous" "%s"' % (r, rdv),
+                                filename="two_rank%d.pfm" % r, scene_name="two_rank%d.pbrt" % r, **kw)
+        procs.append(subprocess.Popen([PBRT, "--quiet", sc], cwd=d, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True))
+    outs = [p.communicate(timeout=300)[0] for p in procs]
+    assert all(p.returncode == 0 for p in procs), outs
+    assert os.path.exists(os.path.join(d, "two_rank0.pfm")) and not os.path.exists(os.path.join(d, "two_rank1.pfm")), outs
+    a, b = ps.read_pfm(os.path.join(d, "one.pfm")), ps.read_pfm(os.path.join(d, "two_rank0.pfm"))
+    same = np.all(a == b, axis=-1).mean()
+    print("\ntwo ranks vs one: %.5f of the pixels bit-identical, max abs diff %.3g" % (same, np.abs(a - b).max()))
+    assert same > 0.98 and np.allclose(a, b, rtol=2e-6, atol=1e-7)
+    assert os.listdir(rdv) == []     # the rendezvous files are consumed
+
+    # world > 1 without a rendezvous directory is an error, not a partial image
+    sc = ps.killeroo_simple(d, 'Accelerator "b200" "string tree" "bvh"', integrator='Integrator "b200wavefront" "integer world" [2]',
+                            filename="bad.pfm", scene_name="bad.pbrt", **kw)
+    rc, out = _run(sc, d, quiet=False)
+    assert "rendezvous" in out and not os.path.exists(os.path.join(d, "bad.pfm")), out

@@ -42,3 +42,20 @@ class FilmGather:
             return film
         dist.reduce(film, dst=0, op=dist.ReduceOp.SUM)
         return film if self.rank == 0 else None
+
+
+def film_reduce_ipc(film, rank, world, rendezvous, heat=None, timeout_s=0.0):
+    """The same sum without a communicator: b200rt_film_reduce (CUDA IPC peer memory, handles through files in `rendezvous`),
+    the call the C++ `Integrator "b200wavefront"` makes when `pbrt` is started once per rank.  film: CUDA or CPU float32
+    tensor / array of (yres, xres, 4); heat: optional uint32 planes.  Completed in place on rank 0."""
+    import ctypes as C
+    from . import api
+
+    def ptr(t):
+        return (t.data_ptr(), t.numel()) if hasattr(t, "data_ptr") else (t.ctypes.data, t.size)
+    fp, fn = ptr(film)
+    hp, hn = ptr(heat) if heat is not None else (None, 0)
+    L = api.lib()
+    L.b200rt_film_reduce.argtypes = [C.c_char_p, C.c_uint32, C.c_uint32, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64, C.c_double]
+    api._check(L.b200rt_film_reduce(str(rendezvous).encode(), rank, world, fp, fn, hp, hn, float(timeout_s)))
+    return film if rank == 0 else None

@@ -368,6 +368,15 @@ void B200WavefrontIntegrator::Render(const Scene &scene) {
         Error("b200wavefront: %s", b200rt_last_error());
         return;
     }
+    if (world > 1) {
+        // the frame is the sum of the ranks' films (each holds its own tiles + boundary-sample halos); rank 0 writes it
+        if (b200rt_film_reduce(rendezvous.c_str(), (uint32_t)rank, (uint32_t)world, rgbw.data(), rgbw.size(),
+                               generalStats ? heat.data() : nullptr, heat.size(), 0)) {
+            Error("b200wavefront: %s", b200rt_last_error());
+            return;
+        }
+        if (rank != 0) return;
+    }
     // Film: pixel = sum / weight (film.cpp:266-305); SetImage stores it with filterWeightSum = 1
     std::unique_ptr<Spectrum[]> img(new Spectrum[nPix]);
     for (size_t i = 0; i < nPix; ++i) {
@@ -407,7 +416,13 @@ B200WavefrontIntegrator *CreateB200WavefrontIntegrator(const ParamSet &params, s
     const int world = params.FindOneInt("world", 1);
     const int seed = params.FindOneInt("seed", 0);
     const bool generalStats = params.FindOneBool("generalstats", false);
-    return new B200WavefrontIntegrator(maxDepth, std::move(camera), std::move(sampler), rank, world, seed, generalStats);
+    const std::string rendezvous = params.FindOneString("rendezvous", "");
+    if (world > 1 && rendezvous.empty()) {
+        Error("b200wavefront: \"integer world\" > 1 needs \"string rendezvous\" (a directory every rank can write)");
+        return nullptr;
+    }
+    if (rank < 0 || rank >= std::max(world, 1)) { Error("b200wavefront: rank %d outside world %d", rank, world); return nullptr; }
+    return new B200WavefrontIntegrator(maxDepth, std::move(camera), std::move(sampler), rank, world, seed, generalStats, rendezvous);
 }
 
 }  // namespace pbrt

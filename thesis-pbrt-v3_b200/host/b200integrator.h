@@ -16,6 +16,7 @@
 #define B200RT_HOST_B200INTEGRATOR_H
 
 #include <memory>
+#include <string>
 
 #include "pbrt.h"
 #include "integrator.h"
@@ -26,11 +27,12 @@ namespace pbrt {
 class B200WavefrontIntegrator : public Integrator {
   public:
     // rank/world: this process renders the 16x16 tiles t with t % world == rank (integrator.cpp:237-239 tile grid);
-    // the other tiles' pixels stay black in this process's film (the host application gathers them).
+    // with world > 1 the ranks' films are summed into rank 0's through b200rt_film_reduce (CUDA IPC peer memory; `rendezvous`
+    // names the directory the handles travel through) and rank 0 alone writes the image and the statistic matrices.
     B200WavefrontIntegrator(int maxDepth, std::shared_ptr<const Camera> camera, std::shared_ptr<Sampler> sampler,
-                            int rank = 0, int world = 1, int seed = 0, bool generalStats = false)
+                            int rank = 0, int world = 1, int seed = 0, bool generalStats = false, std::string rendezvous = "")
         : maxDepth(maxDepth), camera(std::move(camera)), sampler(std::move(sampler)), rank(rank), world(world), seed(seed),
-          generalStats(generalStats) {}
+          generalStats(generalStats), rendezvous(std::move(rendezvous)) {}
     void Render(const Scene &scene);
     const b200rt_render_stats &stats() const { return lastStats; }
 
@@ -40,11 +42,13 @@ class B200WavefrontIntegrator : public Integrator {
     std::shared_ptr<Sampler> sampler;
     const int rank, world, seed;
     const bool generalStats;
+    const std::string rendezvous;
     b200rt_render_stats lastStats{};
 };
 
-// Parameters: "integer maxdepth" (path.cpp:209, default 5), "integer rank" / "integer world" (default: the RANK /
-// WORLD_SIZE environment of a torchrun-style launch, else 0 / 1), "integer seed", "bool generalstats" (default false:
+// Parameters: "integer maxdepth" (path.cpp:209, default 5), "integer rank" / "integer world" (explicit only, default 0 / 1;
+// world > 1 requires "string rendezvous", a directory all ranks of the node can write), "integer seed" (hash sampler only),
+// "bool generalstats" (default false:
 // true renders through the instrumented kernels, b200rt_render_heatmaps, fills the Film's per-pixel GeneralStats and
 // writes the thesis's statistic matrices with Film::WriteGeneralStats like SamplerIntegrator::Render does,
 // integrator.cpp:327-328,359).
