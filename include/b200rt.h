@@ -170,6 +170,26 @@ int b200rt_build_kdtree(const float *tri_verts, uint32_t n_prims, int isect_cost
                         float empty_bonus, int max_prims, int max_depth, void **out_nodes,
                         uint32_t *out_node_count, uint32_t **out_prim_indices, uint32_t *out_n_indices,
                         float out_bounds[6]);
+/* ---- device builder -------------------------------------------------------------------------- */
+/* RBSP::buildTree (rbsp.cpp:181-403) with kDOPMesh.h's cut / surface-area arithmetic, level-synchronous on the B200: every
+ * candidate plane of every node of a tree level is cut and measured in parallel (the reference: 38-319 s per tree on the CPU),
+ * then the nodes are numbered in the reference's depth-first order and emitted as 8-byte RBSPNodes (rbsp.cpp:15-135).
+ * Params = CreateRBSPTreeAccelerator's (rbsp.cpp:549-570): intersectcost 80, traversalcost 5, emptybonus 0, maxprims 1,
+ * maxdepth -1 (= round(2 + 1.6 log2 n), geometry.h:1845), nbDirections 3 | 7 | 9 | 13 (RBSPShared.h:50-71).
+ * The node array equals the reference's byte for byte; the order of the primitive indices inside a leaf (and, in the rare
+ * leaf where the reference's choice hangs on std::sort's order among equal keys, its members) may differ: csrc/rbsp_build.cuh.
+ * Triangles only.  out_directions: nb_directions x 3 floats.  Outputs are malloc'ed; free with b200rt_free.  stats may be NULL.
+ * No host path: B200RT_ENODEVICE without a CUDA device. */
+typedef struct b200rt_build_stats {
+    uint32_t levels;            /* tree levels processed (<= maxdepth + 1) */
+    uint64_t candidates;        /* bound edges examined: 2 n M summed over the levels (statNbSplitTests' upper bound) */
+    uint64_t kernel_launches;
+    float build_ms;             /* CUDA events around upload, build and download */
+} b200rt_build_stats;
+int b200rt_build_rbsp(const float *tri_verts, uint32_t n_prims, uint32_t nb_directions, int isect_cost, int traversal_cost,
+                      float empty_bonus, int max_prims, int max_depth, void **out_nodes, uint32_t *out_node_count,
+                      uint32_t **out_prim_indices, uint32_t *out_n_indices, float out_bounds[6], float *out_directions,
+                      b200rt_build_stats *stats);
 void b200rt_free(void *p);
 
 /* ---- wavefront driver (SamplerIntegrator::Render restructured, src/core/integrator.cpp:230-360

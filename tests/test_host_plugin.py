@@ -132,12 +132,13 @@ def test_plugin_matches_reference_accelerator(host, gpu, tree, builder, ip, refk
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("tree", ["bvh", "kdtree"])
-def test_plugin_with_this_repos_builders(host, gpu, tree):
+@pytest.mark.parametrize("tree,ip", [("bvh", {}), ("kdtree", {}), ("rbsp", {"nbDirections": 7})])
+def test_plugin_with_this_repos_builders(host, gpu, tree, ip):
+    """`"string builder" "b200"`: the library's own builders — BVH / kd-tree on the host, RBSP on the device."""
     rb, L = host
     sc = _scene(rb, L, spheres=False)
-    ref = rb.RefAccel(sc, tree)
-    acc = PluginAccel(rb, L, sc, tree, "b200")
+    ref = rb.RefAccel(sc, tree, ip)
+    acc = PluginAccel(rb, L, sc, tree, "b200", ip)
     assert acc.h
     rays = _rays(4000, seed=5)
     _same(acc.intersect_batch(rays), ref.intersect(rays))

@@ -143,6 +143,36 @@ def build_kdtree(tri_verts, intersectcost=80, traversalcost=1, emptybonus=0.0, m
                 n_prims=len(v))
 
 
+class BuildStats(C.Structure):
+    _fields_ = [("levels", C.c_uint32), ("candidates", C.c_uint64), ("kernel_launches", C.c_uint64), ("build_ms", C.c_float)]
+
+
+def build_rbsp(tri_verts, nbDirections=3, intersectcost=80, traversalcost=5, emptybonus=0.0, maxprims=1, maxdepth=-1):
+    """RBSP tree built ON THE DEVICE (csrc/build_rbsp.cu, level-synchronous: every candidate plane of a tree level cut and
+    measured in parallel), params of CreateRBSPTreeAccelerator (reference src/accelerators/rbsp.cpp:549-570).  The node
+    array equals the reference builder's byte for byte.  tree["build"] holds levels / candidates / launches / build_ms."""
+    v = np.ascontiguousarray(tri_verts, np.float32).reshape(-1, 9)
+    nodes, idx, nc, ni = C.c_void_p(), C.c_void_p(), C.c_uint32(), C.c_uint32()
+    b = (C.c_float * 6)()
+    dirs = np.zeros((16, 3), np.float32)
+    st = BuildStats()
+    L = lib()
+    L.b200rt_build_rbsp.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_int, C.c_int, C.c_float, C.c_int, C.c_int,
+                                    C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    _check(L.b200rt_build_rbsp(_p(v), len(v), int(nbDirections), int(intersectcost), int(traversalcost), float(emptybonus),
+                               int(maxprims), int(maxdepth), C.byref(nodes), C.byref(nc), C.byref(idx), C.byref(ni),
+                               C.byref(b), _p(dirs), C.byref(st)))
+    n = _take(nodes, nc.value, 2)
+    if ni.value:
+        i = _take(idx, ni.value, 1).reshape(-1)
+    else:
+        L.b200rt_free(idx)
+        i = np.zeros(0, np.uint32)
+    return dict(kind="rbsp", nodes=n, indices=i, directions=dirs[:int(nbDirections)].copy(), bounds=np.array(list(b), np.float32),
+                n_prims=len(v), build=dict(levels=st.levels, candidates=st.candidates, kernel_launches=st.kernel_launches,
+                                           build_ms=st.build_ms))
+
+
 class B200Accel:
     """Aggregate over a device-resident tree.  Mirrors pbrt's Aggregate (src/core/primitive.h:49-56,
     188-198) for ray BATCHES: WorldBound(), Intersect(rays) -> hits, IntersectP(rays) -> occluded."""
@@ -242,14 +272,15 @@ class B200Accel:
 
 _BVH_DEFAULTS = dict(maxnodeprims=4, intersectcost=8, traversalcost=1)
 _KD_DEFAULTS = dict(intersectcost=80, traversalcost=1, emptybonus=0.0, maxprims=1, maxdepth=-1)
+_RBSP_DEFAULTS = dict(nbDirections=3, intersectcost=80, traversalcost=5, emptybonus=0.0, maxprims=1, maxdepth=-1)
 _IGNORED = {"splitalpha", "alphatype", "axisselectiontype", "axisselectionamount", "nbDirections"}
 
 
 def MakeAccelerator(name, tri_verts, paramSet=None, tri_uvs=None, tree=None, tri_normals=None, prim_flags=None):
     """Mirror of MakeAccelerator(name, prims, paramSet) (reference src/core/api.cpp:790-1015) for
     the accelerators on the hot path.  `paramSet` uses the .pbrt parameter names.  "bvh" and
-    "kdtree" are built by this repo's host builders; "rbsp"/"rbspkd" take a host-built tree
-    (`tree=`, reference node format) because their builder is outside this round's scope.
+    "kdtree" are built by this repo's host builders, "rbsp" by the device builder (build_rbsp); "rbspkd" and the BSP
+    families take a host-built tree (`tree=`, reference node format).
     Unknown names return None after a warning, like the reference (api.cpp:1011-1012)."""
     ps = dict(paramSet or {})
     if tree is not None:
@@ -260,7 +291,10 @@ def MakeAccelerator(name, tri_verts, paramSet=None, tri_uvs=None, tree=None, tri
     elif name == "kdtree":
         args = {k: ps.pop(k, v) for k, v in _KD_DEFAULTS.items()}
         tree = build_kdtree(tri_verts, **args)
-    elif name in ("rbsp", "rbspkd"):
+    elif name == "rbsp":
+        args = {k: ps.pop(k, v) for k, v in _RBSP_DEFAULTS.items()}
+        tree = build_rbsp(tri_verts, **args)
+    elif name == "rbspkd":
         raise B200RTError(4, "accelerator %r needs a host-built tree (tree=...): its builder is not part of "
                              "this engine" % name)
     else:

@@ -1,0 +1,182 @@
+// b200rt_build_rbsp: the RBSP tree builder on the B200 (include/b200rt.h).  The algorithm and its kernels (functors) are in
+// rbsp_build.cuh, the level loop in rbsp_driver.h; this file is the CUDA backend — one grid per functor, CUB's radix sort and
+// scans for the two collective primitives, stream-ordered allocation — and the C entry point.  There is no host fallback:
+// without a device the call fails with B200RT_ENODEVICE.
+#include <cuda_runtime.h>
+
+#include <cub/device/device_radix_sort.cuh>
+#include <cub/device/device_scan.cuh>
+
+#include <algorithm>
+#include <atomic>
+#include <cstdlib>
+
+#include "../../include/b200rt.h"
+#include "rbsp_driver.h"
+#include "scene_internal.h"
+
+extern std::atomic<uint64_t> g_launches;   // b200rt.cu
+
+namespace {
+using namespace b200rt::rbsp;
+
+template <class F>
+__global__ void k_for_each(F f, size_t n) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) f(i);
+}
+// the k-DOP functors keep two meshes and the per-face cut points in local memory (~9 KB per thread): small blocks
+template <class F>
+__global__ void __launch_bounds__(64) k_for_each_heavy(F f, size_t n) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) f(i);
+}
+
+struct MaxU32 {
+    __host__ __device__ uint32_t operator()(uint32_t a, uint32_t b) const { return a > b ? a : b; }
+};
+
+struct CudaBackend {
+    cudaStream_t st = nullptr;
+    cudaError_t status = cudaSuccess;
+    uint64_t launches = 0;
+    void check(cudaError_t e) { if (e != cudaSuccess && status == cudaSuccess) status = e; }
+    template <class T> T *alloc(size_t n) {
+        void *p = nullptr;
+        check(cudaMallocAsync(&p, std::max<size_t>(n, 1) * sizeof(T), st));
+        return (T *)p;
+    }
+    void free(void *p) { if (p) check(cudaFreeAsync(p, st)); }
+    template <class T> void upload(T *dst, const T *src, size_t n) {
+        if (!n || status != cudaSuccess) return;
+        check(cudaMemcpyAsync(dst, src, n * sizeof(T), cudaMemcpyHostToDevice, st));
+        check(cudaStreamSynchronize(st));   // src may be a temporary of the caller
+    }
+    template <class T> void download(T *dst, const T *src, size_t n) {
+        if (!n || status != cudaSuccess) return;
+        check(cudaMemcpyAsync(dst, src, n * sizeof(T), cudaMemcpyDeviceToHost, st));
+        check(cudaStreamSynchronize(st));
+    }
+    template <class F> void for_each(size_t n, F f) {
+        if (!n || status != cudaSuccess) return;
+        k_for_each<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(f, n);
+        check(cudaGetLastError());
+        ++launches;
+    }
+    template <class F> void for_each_heavy(size_t n, F f) {
+        if (!n || status != cudaSuccess) return;
+        k_for_each_heavy<<<(unsigned)((n + 63) / 64), 64, 0, st>>>(f, n);
+        check(cudaGetLastError());
+        ++launches;
+    }
+    void sort_pairs(const uint64_t *kin, uint64_t *kout, const uint32_t *vin, uint32_t *vout, size_t n, int bits) {
+        if (!n || status != cudaSuccess) return;
+        size_t bytes = 0;
+        check(cub::DeviceRadixSort::SortPairs(nullptr, bytes, kin, kout, vin, vout, (int64_t)n, 0, bits, st));
+        void *tmp = alloc<uint8_t>(bytes);
+        check(cub::DeviceRadixSort::SortPairs(tmp, bytes, kin, kout, vin, vout, (int64_t)n, 0, bits, st));
+        free(tmp);
+        ++launches;
+    }
+    void exclusive_sum(const uint32_t *in, uint32_t *out, size_t n) {
+        if (!n || status != cudaSuccess) return;
+        size_t bytes = 0;
+        check(cub::DeviceScan::ExclusiveSum(nullptr, bytes, in, out, (int64_t)n, st));
+        void *tmp = alloc<uint8_t>(bytes);
+        check(cub::DeviceScan::ExclusiveSum(tmp, bytes, in, out, (int64_t)n, st));
+        free(tmp);
+        ++launches;
+    }
+    void inclusive_max(const uint32_t *in, uint32_t *out, size_t n) {
+        if (!n || status != cudaSuccess) return;
+        size_t bytes = 0;
+        check(cub::DeviceScan::InclusiveScan(nullptr, bytes, in, out, MaxU32(), (int64_t)n, st));
+        void *tmp = alloc<uint8_t>(bytes);
+        check(cub::DeviceScan::InclusiveScan(tmp, bytes, in, out, MaxU32(), (int64_t)n, st));
+        free(tmp);
+        ++launches;
+    }
+};
+
+}  // namespace
+
+extern "C" int b200rt_build_rbsp(const float *tri_verts, uint32_t n_prims, uint32_t nb_directions, int isect_cost,
+                                 int traversal_cost, float empty_bonus, int max_prims, int max_depth, void **out_nodes,
+                                 uint32_t *out_node_count, uint32_t **out_prim_indices, uint32_t *out_n_indices,
+                                 float out_bounds[6], float *out_directions, b200rt_build_stats *stats) {
+    using b200rt::set_error;
+    if (!tri_verts || !out_nodes || !out_node_count || !out_prim_indices || !out_n_indices || !out_bounds || !out_directions)
+        return set_error(B200RT_EINVAL, "b200rt_build_rbsp: null argument");
+    if (n_prims >= (1u << 27)) return set_error(B200RT_EUNSUPPORTED, "b200rt_build_rbsp: more than 2^27 primitives");
+    BuildParams P{};
+    P.M = make_directions(nb_directions, P.dirs);
+    if (!P.M) return set_error(B200RT_EINVAL, "b200rt_build_rbsp: nbDirections must be 3, 7, 9 or 13 (RBSPShared.h:50-71), got %u", nb_directions);
+    P.isectCost = (uint32_t)isect_cost;
+    P.traversalCost = (uint32_t)traversal_cost;
+    P.emptyBonus = empty_bonus;
+    P.maxPrims = (uint32_t)max_prims;
+    P.maxDepth = max_depth < 0 ? default_max_depth(n_prims) : (uint32_t)max_depth;
+    if (P.maxDepth > 63) return set_error(B200RT_EUNSUPPORTED, "b200rt_build_rbsp: maxdepth %u exceeds the traversal's 64-entry stack", P.maxDepth);
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        cudaGetLastError();
+        return set_error(B200RT_ENODEVICE, "b200rt_build_rbsp: no CUDA device (the builder has no host path)");
+    }
+    // `bounds = Union(bounds, prim->WorldBound())` (rbsp.cpp:192): plain min / max of the coordinates
+    float world[6] = {3.402823466e+38f, 3.402823466e+38f, 3.402823466e+38f, -3.402823466e+38f, -3.402823466e+38f, -3.402823466e+38f};
+    for (uint32_t p = 0; p < n_prims; ++p)
+        for (int v = 0; v < 3; ++v)
+            for (int c = 0; c < 3; ++c) {
+                world[c] = std::min(world[c], tri_verts[9 * (size_t)p + 3 * v + c]);
+                world[3 + c] = std::max(world[3 + c], tri_verts[9 * (size_t)p + 3 * v + c]);
+            }
+    CudaBackend be;
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    be.check(cudaStreamCreateWithFlags(&be.st, cudaStreamNonBlocking));
+    {   // keep freed blocks in the pool between levels
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaMemPool_t pool;
+        if (cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess) {
+            uint64_t thr = ~0ull;
+            cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr);
+        }
+    }
+    be.check(cudaEventCreate(&e0));
+    be.check(cudaEventCreate(&e1));
+    be.check(cudaEventRecord(e0, be.st));
+    float *dTris = be.alloc<float>((size_t)n_prims * 9);
+    be.upload(dTris, tri_verts, (size_t)n_prims * 9);
+    BuildResult r;
+    if (be.status == cudaSuccess) r = build(be, dTris, n_prims, P, world);
+    be.free(dTris);
+    be.check(cudaEventRecord(e1, be.st));
+    be.check(cudaStreamSynchronize(be.st));
+    float ms = 0;
+    if (be.status == cudaSuccess) cudaEventElapsedTime(&ms, e0, e1);
+    if (e0) cudaEventDestroy(e0);
+    if (e1) cudaEventDestroy(e1);
+    if (be.st) cudaStreamDestroy(be.st);
+    g_launches += be.launches;
+    if (be.status != cudaSuccess) return set_error(B200RT_ECUDA, "b200rt_build_rbsp: %s", cudaGetErrorString(be.status));
+    if (r.error) return set_error(B200RT_EUNSUPPORTED, "b200rt_build_rbsp: a node's k-DOP outgrew %d edges / %d cut points per face", kMaxEdges, kMaxFacePoints);
+    const size_t nNodes = r.nodes.size() / 2;
+    uint32_t *nodes = (uint32_t *)std::malloc(std::max<size_t>(r.nodes.size(), 1) * 4);
+    uint32_t *idx = (uint32_t *)std::malloc(std::max<size_t>(r.indices.size(), 1) * 4);
+    if (!nodes || !idx) { std::free(nodes); std::free(idx); return set_error(B200RT_ENOMEM, "b200rt_build_rbsp: out of host memory"); }
+    std::memcpy(nodes, r.nodes.data(), r.nodes.size() * 4);
+    std::memcpy(idx, r.indices.data(), r.indices.size() * 4);
+    *out_nodes = nodes;
+    *out_node_count = (uint32_t)nNodes;
+    *out_prim_indices = idx;
+    *out_n_indices = (uint32_t)r.indices.size();
+    std::memcpy(out_bounds, world, 24);
+    std::memcpy(out_directions, P.dirs, P.M * 12);
+    if (stats) {
+        stats->levels = r.levels;
+        stats->candidates = r.candidates;
+        stats->kernel_launches = be.launches;
+        stats->build_ms = ms;
+    }
+    return B200RT_OK;
+}
