@@ -190,6 +190,13 @@ int b200rt_build_rbsp(const float *tri_verts, uint32_t n_prims, uint32_t nb_dire
                       float empty_bonus, int max_prims, int max_depth, void **out_nodes, uint32_t *out_node_count,
                       uint32_t **out_prim_indices, uint32_t *out_n_indices, float out_bounds[6], float *out_directions,
                       b200rt_build_stats *stats);
+/* KdTreeAccel::buildTree (kdtreeaccel.cpp:208-379) through the same level-synchronous device builder (box areas in closed
+ * form instead of k-DOP cuts).  Same outputs and parameters as b200rt_build_kdtree; the node array is identical to it (and to
+ * the reference's), the order of the indices inside a leaf follows the stable radix sort instead of std::sort's. */
+int b200rt_build_kdtree_device(const float *tri_verts, uint32_t n_prims, int isect_cost, int traversal_cost,
+                               float empty_bonus, int max_prims, int max_depth, void **out_nodes, uint32_t *out_node_count,
+                               uint32_t **out_prim_indices, uint32_t *out_n_indices, float out_bounds[6],
+                               b200rt_build_stats *stats);
 void b200rt_free(void *p);
 
 /* ---- wavefront driver (SamplerIntegrator::Render restructured, src/core/integrator.cpp:230-360

@@ -35,11 +35,13 @@ struct HostBackend {
 };
 }  // namespace
 
+// nbDirections = 0 selects the kd-tree mode (KdTreeAccel::buildTree)
 extern "C" int hb_build_rbsp(const float *tris, uint32_t n, uint32_t nbDirections, int isectCost, int traversalCost,
                              float emptyBonus, int maxPrims, int maxDepth, uint32_t **nodes, uint32_t *nNodes,
                              uint32_t **indices, uint32_t *nIndices, float *dirsOut, float *boundsOut, uint64_t *candidates) {
     BuildParams P{};
-    P.M = make_directions(nbDirections, P.dirs);
+    P.kd = nbDirections == 0;
+    P.M = make_directions(P.kd ? 3 : nbDirections, P.dirs);
     if (!P.M) return 1;
     P.isectCost = (uint32_t)isectCost; P.traversalCost = (uint32_t)traversalCost; P.emptyBonus = emptyBonus;
     P.maxPrims = (uint32_t)maxPrims;

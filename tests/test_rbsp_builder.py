@@ -117,6 +117,22 @@ def test_parameters_against_a_fresh_reference_build(hb, params):
         compare_with_reference(t, ex["nodes"], ex["indices"], params["nbDirections"])
 
 
+def test_kd_mode_reproduces_the_reference_kdtree(hb, built_lib):
+    """The builder's kd mode (nbDirections = 0: box areas in closed form instead of k-DOP cuts, KdTreeAccel::buildTree) against
+    the reference-built golden and against this repo's host builder (itself byte-identical to the reference up to 2.9 M nodes,
+    tests/test_living_room.py)."""
+    g = load_golden("ref_small_kdtree.npz")
+    t = hb(g["tri_verts"], nbDirections=0, traversalcost=1)
+    assert np.array_equal(t["nodes"], g["nodes"]) and np.array_equal(t["indices"], g["indices"]) and np.array_equal(t["bounds"], g["bounds"])
+    from b200rt import scenes
+    tv = scenes.killeroo_simple()["tri_verts"][:20000]
+    for kw in (dict(), dict(maxprims=4, emptybonus=0.5), dict(maxdepth=9, intersectcost=20, traversalcost=3)):
+        h = built_lib.build_kdtree(tv, **{"traversalcost": 1, **kw})
+        t = hb(tv, nbDirections=0, **{"traversalcost": 1, **kw})
+        bad, n = compare_with_reference(t, h["nodes"], h["indices"], 3)
+        assert bad == 0
+
+
 def test_empty_and_tiny_inputs(hb):
     t = hb(np.zeros((0, 9), np.float32), nbDirections=7)
     assert t["nodes"].shape == (1, 2) and t["nodes"][0, 1] == 7 and len(t["indices"]) == 0      # one empty leaf: flags = M, np = 0
@@ -169,3 +185,25 @@ def test_device_build_rejects_what_it_does_not_do(gpu):
         gpu.build_rbsp(np.zeros((4, 9), np.float32), nbDirections=5)
     t = gpu.build_rbsp(np.zeros((0, 9), np.float32), nbDirections=7)
     assert t["nodes"].shape == (1, 2) and t["nodes"][0, 1] == 7
+
+
+@pytest.mark.gpu
+def test_device_kdtree_build(gpu, hb):
+    """b200rt_build_kdtree_device on scenes/killeroo-simple's 66 532 triangles: the host builder's (= the reference's) node
+    array, the same leaves, and the same answers on rays."""
+    from b200rt import scenes
+    sc = scenes.killeroo_simple()
+    tv = sc["tri_verts"]
+    h = gpu.build_kdtree(tv)
+    t = gpu.build_kdtree_device(tv)
+    bad, n = compare_with_reference(t, h["nodes"], h["indices"], 3)
+    assert bad == 0 and np.array_equal(t["bounds"], h["bounds"])
+    print("\nkilleroo-simple kd-tree on the B200: %d nodes in %.1f ms (%d levels, %d launches)"
+          % (len(t["nodes"]), t["build"]["build_ms"], t["build"]["levels"], t["build"]["kernel_launches"]))
+    g = load_golden("ref_small_kdtree.npz")
+    t = gpu.build_kdtree_device(g["tri_verts"])
+    assert np.array_equal(t["nodes"], g["nodes"]) and np.array_equal(t["indices"], g["indices"])
+    acc = gpu.B200Accel(t, g["tri_verts"])
+    hits = acc.Intersect(g["rays"])
+    assert np.array_equal(hits["prim"], np.where(g["hit_prim"] < 0, gpu.MISS, g["hit_prim"]).astype(np.uint32))
+    assert np.array_equal(hits["t"].view(np.uint32), g["hit_t"].view(np.uint32))

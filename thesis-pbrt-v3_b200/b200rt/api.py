@@ -143,6 +143,29 @@ def build_kdtree(tri_verts, intersectcost=80, traversalcost=1, emptybonus=0.0, m
                 n_prims=len(v))
 
 
+def build_kdtree_device(tri_verts, intersectcost=80, traversalcost=1, emptybonus=0.0, maxprims=1, maxdepth=-1):
+    """build_kdtree on the DEVICE (b200rt_build_kdtree_device: the level-synchronous builder of csrc/rbsp_build.cuh in its
+    kd mode).  Node array identical to build_kdtree's; the order of the indices inside a leaf may differ."""
+    v = np.ascontiguousarray(tri_verts, np.float32).reshape(-1, 9)
+    nodes, idx, nc, ni = C.c_void_p(), C.c_void_p(), C.c_uint32(), C.c_uint32()
+    b = (C.c_float * 6)()
+    st = BuildStats()
+    L = lib()
+    L.b200rt_build_kdtree_device.argtypes = [C.c_void_p, C.c_uint32, C.c_int, C.c_int, C.c_float, C.c_int, C.c_int,
+                                             C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    _check(L.b200rt_build_kdtree_device(_p(v), len(v), int(intersectcost), int(traversalcost), float(emptybonus), int(maxprims),
+                                        int(maxdepth), C.byref(nodes), C.byref(nc), C.byref(idx), C.byref(ni), C.byref(b), C.byref(st)))
+    n = _take(nodes, nc.value, 2)
+    if ni.value:
+        i = _take(idx, ni.value, 1).reshape(-1)
+    else:
+        L.b200rt_free(idx)
+        i = np.zeros(0, np.uint32)
+    return dict(kind="kdtree", nodes=n, indices=i, directions=np.eye(3, dtype=np.float32), bounds=np.array(list(b), np.float32),
+                n_prims=len(v), build=dict(levels=st.levels, candidates=st.candidates, kernel_launches=st.kernel_launches,
+                                           build_ms=st.build_ms))
+
+
 class BuildStats(C.Structure):
     _fields_ = [("levels", C.c_uint32), ("candidates", C.c_uint64), ("kernel_launches", C.c_uint64), ("build_ms", C.c_float)]
 

@@ -100,16 +100,18 @@ struct CudaBackend {
 
 }  // namespace
 
-extern "C" int b200rt_build_rbsp(const float *tri_verts, uint32_t n_prims, uint32_t nb_directions, int isect_cost,
-                                 int traversal_cost, float empty_bonus, int max_prims, int max_depth, void **out_nodes,
-                                 uint32_t *out_node_count, uint32_t **out_prim_indices, uint32_t *out_n_indices,
-                                 float out_bounds[6], float *out_directions, b200rt_build_stats *stats) {
+// nb_directions = 0: kd-tree mode
+static int build_on_device(const float *tri_verts, uint32_t n_prims, uint32_t nb_directions, int isect_cost,
+                           int traversal_cost, float empty_bonus, int max_prims, int max_depth, void **out_nodes,
+                           uint32_t *out_node_count, uint32_t **out_prim_indices, uint32_t *out_n_indices,
+                           float out_bounds[6], float *out_directions, b200rt_build_stats *stats) {
     using b200rt::set_error;
-    if (!tri_verts || !out_nodes || !out_node_count || !out_prim_indices || !out_n_indices || !out_bounds || !out_directions)
+    if (!tri_verts || !out_nodes || !out_node_count || !out_prim_indices || !out_n_indices || !out_bounds)
         return set_error(B200RT_EINVAL, "b200rt_build_rbsp: null argument");
     if (n_prims >= (1u << 27)) return set_error(B200RT_EUNSUPPORTED, "b200rt_build_rbsp: more than 2^27 primitives");
     BuildParams P{};
-    P.M = make_directions(nb_directions, P.dirs);
+    P.kd = nb_directions == 0;
+    P.M = make_directions(P.kd ? 3 : nb_directions, P.dirs);
     if (!P.M) return set_error(B200RT_EINVAL, "b200rt_build_rbsp: nbDirections must be 3, 7, 9 or 13 (RBSPShared.h:50-71), got %u", nb_directions);
     P.isectCost = (uint32_t)isect_cost;
     P.traversalCost = (uint32_t)traversal_cost;
@@ -171,7 +173,7 @@ extern "C" int b200rt_build_rbsp(const float *tri_verts, uint32_t n_prims, uint3
     *out_prim_indices = idx;
     *out_n_indices = (uint32_t)r.indices.size();
     std::memcpy(out_bounds, world, 24);
-    std::memcpy(out_directions, P.dirs, P.M * 12);
+    if (out_directions) std::memcpy(out_directions, P.dirs, P.M * 12);
     if (stats) {
         stats->levels = r.levels;
         stats->candidates = r.candidates;
@@ -179,4 +181,21 @@ extern "C" int b200rt_build_rbsp(const float *tri_verts, uint32_t n_prims, uint3
         stats->build_ms = ms;
     }
     return B200RT_OK;
+}
+
+extern "C" int b200rt_build_rbsp(const float *tri_verts, uint32_t n_prims, uint32_t nb_directions, int isect_cost,
+                                 int traversal_cost, float empty_bonus, int max_prims, int max_depth, void **out_nodes,
+                                 uint32_t *out_node_count, uint32_t **out_prim_indices, uint32_t *out_n_indices,
+                                 float out_bounds[6], float *out_directions, b200rt_build_stats *stats) {
+    if (!out_directions || nb_directions == 0) return b200rt::set_error(B200RT_EINVAL, "b200rt_build_rbsp: null argument / nbDirections 0");
+    return build_on_device(tri_verts, n_prims, nb_directions, isect_cost, traversal_cost, empty_bonus, max_prims, max_depth,
+                           out_nodes, out_node_count, out_prim_indices, out_n_indices, out_bounds, out_directions, stats);
+}
+
+extern "C" int b200rt_build_kdtree_device(const float *tri_verts, uint32_t n_prims, int isect_cost, int traversal_cost,
+                                          float empty_bonus, int max_prims, int max_depth, void **out_nodes,
+                                          uint32_t *out_node_count, uint32_t **out_prim_indices, uint32_t *out_n_indices,
+                                          float out_bounds[6], b200rt_build_stats *stats) {
+    return build_on_device(tri_verts, n_prims, 0, isect_cost, traversal_cost, empty_bonus, max_prims, max_depth, out_nodes,
+                           out_node_count, out_prim_indices, out_n_indices, out_bounds, nullptr, stats);
 }

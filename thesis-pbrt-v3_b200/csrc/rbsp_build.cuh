@@ -37,6 +37,10 @@ struct BuildParams {
     uint32_t M, isectCost, traversalCost, maxPrims, maxDepth;
     float emptyBonus;
     float dirs[kMaxDirs * 3];
+    // kd = 1: KdTreeAccel::buildTree (src/accelerators/kdtreeaccel.cpp:208-379) — the same sweep over the three axes with the
+    // node's BOX instead of a k-DOP: areas in closed form (:300-305), children's boxes by replacing one bound (:362-364),
+    // the same 8-byte node layout (M = 3: two flag bits, leaf = 3).  No meshes, no EvalAreas pass.
+    uint32_t kd;
 };
 
 enum : uint32_t { kLeaf = 0, kInterior = 1, kActive = 2 };
@@ -91,7 +95,13 @@ struct PrimBoundsF {   // allPrimBounds, rbsp.cpp:189-201
     WF_HD void operator()(size_t i) const {
         const size_t p = i / P.M, d = i % P.M;
         float mn, mx;
-        tri_extent(tris + 9 * p, P.dirs + 3 * d, mn, mx);
+        if (P.kd) {   // Triangle::WorldBound, triangle.cpp:180-186: Union(Bounds3f(p0, p1), p2), one axis of it
+            const float *v = tris + 9 * p + d;
+            mn = smin(smin(v[0], v[3]), v[6]);
+            mx = smax(smax(v[0], v[3]), v[6]);
+        } else {
+            tri_extent(tris + 9 * p, P.dirs + 3 * d, mn, mx);
+        }
         primB[2 * i] = mn;
         primB[2 * i + 1] = mx;
     }
@@ -125,6 +135,11 @@ struct InitNodeF {   // termination criteria, rbsp.cpp:258
     WF_HD void operator()(size_t k) const {
         L.kind[k] = (L.nPrims[k] <= P.maxPrims || L.depth[k] == 0) ? kLeaf : kActive;
         L.best[k] = ~0ull;
+        if (P.kd) {   // Bounds3::SurfaceArea, geometry.h:946-949
+            const float *b = L.bounds + (size_t)k * 6;
+            const float dx = b[1] - b[0], dy = b[3] - b[2], dz = b[5] - b[4];
+            L.area[k] = 2 * (dx * dy + dx * dz + dy * dz);
+        }
     }
 };
 
@@ -175,24 +190,36 @@ struct EvalAreasF {   // rbsp.cpp:301-311 for one distinct plane
     }
 };
 
-struct EvalCostF {   // rbsp.cpp:296-330 for one bound edge
+struct EvalCostF {   // rbsp.cpp:296-330 / kdtreeaccel.cpp:290-322 for one bound edge
     Level L;
     BuildParams P;
     uint32_t d;
     const uint64_t *skey;
-    const uint32_t *leader, *endsBefore;
-    const float *areaB, *areaA;
+    const uint32_t *sref, *leader, *endsBefore;
+    const float *areaB, *areaA, *primB;
     WF_HD void operator()(size_t i) const {
         const uint32_t k = (uint32_t)(skey[i] >> 33);
         if (L.kind[k] != kActive) return;
-        const uint32_t ld = leader[i];
-        const float aB = areaB[ld];
-        if (aB == -1.0f) return;   // the plane is not strictly inside the node
+        float aB, aA;
+        if (P.kd) {
+            const float t = primB[((size_t)L.refPrim[sref[i]] * 3 + d) * 2 + (skey[i] & 1)];
+            const float *b = L.bounds + (size_t)k * 6;
+            if (!(t > b[2 * d] && t < b[2 * d + 1])) return;
+            const uint32_t o0 = (d + 1) % 3, o1 = (d + 2) % 3;
+            const float d0 = b[2 * o0 + 1] - b[2 * o0], d1 = b[2 * o1 + 1] - b[2 * o1];
+            aB = 2 * (d0 * d1 + (t - b[2 * d]) * (d0 + d1));
+            aA = 2 * (d0 * d1 + (b[2 * d + 1] - t) * (d0 + d1));
+        } else {
+            const uint32_t ld = leader[i];
+            aB = areaB[ld];
+            if (aB == -1.0f) return;   // the plane is not strictly inside the node
+            aA = areaA[ld];
+        }
         const uint32_t s = 2 * L.refBase[k], il = (uint32_t)i - s, e = (uint32_t)(skey[i] & 1);
         const uint32_t eb = endsBefore[i] - endsBefore[s];
         const uint32_t nAbove = L.nPrims[k] - eb - e, nBelow = il - eb;
         const float invTotalSA = 1 / L.area[k];
-        const float cost = sah_cost(P.traversalCost, P.isectCost, P.emptyBonus, aB, areaA[ld], invTotalSA, nBelow, nAbove);
+        const float cost = sah_cost(P.traversalCost, P.isectCost, P.emptyBonus, aB, aA, invTotalSA, nBelow, nAbove);
         if (!(cost < wf_inf())) return;   // `cost < bestCost` is false for NaN and for +inf
         atomic_min_u64(L.best + k, ((uint64_t)float_order(cost + 0.0f) << 32) | ((uint64_t)d << 28) | il);
     }
@@ -233,6 +260,16 @@ struct SplitF {   // the winning cut again: children's meshes, areas, extents (r
         const uint32_t c = 2 * rank[k], d = L.bestD[k];
         const size_t pos = (size_t)2 * L.refBase[k] + L.bestOff[k];
         const float t = primB[((size_t)L.refPrim[S.ref[d][pos]] * P.M + d) * 2 + (S.key[d][pos] & 1)];
+        Nx.depth[c] = Nx.depth[c + 1] = L.depth[k] - 1;
+        Nx.bad[c] = Nx.bad[c + 1] = L.bad[k];
+        L.split[k] = t;
+        L.childBelow[k] = c;
+        if (P.kd) {
+            for (uint32_t j = 0; j < 6; ++j) Nx.bounds[(size_t)c * 6 + j] = Nx.bounds[(size_t)(c + 1) * 6 + j] = L.bounds[(size_t)k * 6 + j];
+            Nx.bounds[(size_t)c * 6 + 2 * d + 1] = t;         // bounds0.pMax[axis] = tSplit
+            Nx.bounds[(size_t)(c + 1) * 6 + 2 * d] = t;       // bounds1.pMin[axis] = tSplit
+            return;
+        }
         KdopMesh &left = Nx.mesh[c], &right = Nx.mesh[c + 1];
         FacePoints fp;
         if (!kdop_cut(L.mesh[k], P.M, t, P.dirs + 3 * d, d, left, right, fp)) *err = kErrMeshOverflow;
@@ -242,10 +279,6 @@ struct SplitF {   // the winning cut again: children's meshes, areas, extents (r
             kdop_extent(left, P.dirs + 3 * dd, Nx.bounds[((size_t)c * P.M + dd) * 2], Nx.bounds[((size_t)c * P.M + dd) * 2 + 1]);
             kdop_extent(right, P.dirs + 3 * dd, Nx.bounds[((size_t)(c + 1) * P.M + dd) * 2], Nx.bounds[((size_t)(c + 1) * P.M + dd) * 2 + 1]);
         }
-        Nx.depth[c] = Nx.depth[c + 1] = L.depth[k] - 1;
-        Nx.bad[c] = Nx.bad[c + 1] = L.bad[k];
-        L.split[k] = t;
-        L.childBelow[k] = c;
     }
 };
 

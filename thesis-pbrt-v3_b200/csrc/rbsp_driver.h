@@ -51,12 +51,12 @@ struct BuildResult {
 };
 
 template <class B>
-void alloc_level(B &be, Level &L, uint32_t K, uint32_t M) {
+void alloc_level(B &be, Level &L, uint32_t K, uint32_t M, bool meshes = true) {
     L.K = K;
     L.nPrims = be.template alloc<uint32_t>(K); L.depth = be.template alloc<uint32_t>(K);
     L.bad = be.template alloc<uint32_t>(K); L.refBase = be.template alloc<uint32_t>(K);
     L.area = be.template alloc<float>(K); L.bounds = be.template alloc<float>((size_t)K * M * 2);
-    L.mesh = be.template alloc<KdopMesh>(K);
+    L.mesh = be.template alloc<KdopMesh>(meshes ? K : 0);
     L.kind = be.template alloc<uint32_t>(K); L.bestD = be.template alloc<uint32_t>(K);
     L.bestOff = be.template alloc<uint32_t>(K); L.childBelow = be.template alloc<uint32_t>(K);
     L.split = be.template alloc<float>(K); L.best = be.template alloc<uint64_t>(K);
@@ -84,7 +84,7 @@ BuildResult build(B &be, const float *tris, uint32_t n, const BuildParams &P, co
     // root: extents of all primitives per direction, the world box as a k-DOP, its area (rbsp.cpp:183-229)
     std::vector<Level> levels(1);
     Level *cur = &levels[0];
-    alloc_level(be, *cur, 1, M);
+    alloc_level(be, *cur, 1, M, !P.kd);
     {
         uint32_t *ord = be.template alloc<uint32_t>(2 * M);
         std::vector<uint32_t> init(2 * M);
@@ -96,12 +96,15 @@ BuildResult build(B &be, const float *tris, uint32_t n, const BuildParams &P, co
         std::vector<float> rb(2 * M);
         for (uint32_t i = 0; i < 2 * M; ++i) rb[i] = float_unorder(init[i]);
         if (n == 0) for (uint32_t d = 0; d < M; ++d) { rb[2 * d] = 3.402823466e+38f; rb[2 * d + 1] = -3.402823466e+38f; }
+        if (P.kd) for (uint32_t d = 0; d < 3; ++d) { rb[2 * d] = world[d]; rb[2 * d + 1] = world[3 + d]; }   // the root's box
         be.upload(cur->bounds, rb.data(), 2 * M);
-        KdopMesh root;
-        kdop_from_box(world, root);
-        const float area = kdop_area(root, P.dirs, M);   // re-orients the root's edges, and the build keeps them so
-        be.upload(cur->mesh, &root, 1);
-        be.upload(cur->area, &area, 1);
+        if (!P.kd) {
+            KdopMesh root;
+            kdop_from_box(world, root);
+            const float area = kdop_area(root, P.dirs, M);   // re-orients the root's edges, and the build keeps them so
+            be.upload(cur->mesh, &root, 1);
+            be.upload(cur->area, &area, 1);
+        }
         const uint32_t one[4] = {n, P.maxDepth, 0u, 0u};
         be.upload(cur->nPrims, one + 0, 1); be.upload(cur->depth, one + 1, 1);
         be.upload(cur->bad, one + 2, 1); be.upload(cur->refBase, one + 3, 1);
@@ -133,9 +136,11 @@ BuildResult build(B &be, const float *tris, uint32_t n, const BuildParams &P, co
             be.sort_pairs(keyTmp, skey[d], valTmp, sref[d], E, 33 + nodeBits);
             be.for_each(E, EdgeFlagsF{skey[d], isEnd, lead});
             be.exclusive_sum(isEnd, endsBefore, E);
-            be.inclusive_max(lead, leader, E);
-            be.for_each_heavy(E, EvalAreasF{L, primB, P, d, skey[d], sref[d], leader, areaB, areaA, err});
-            be.for_each(E, EvalCostF{L, P, d, skey[d], leader, endsBefore, areaB, areaA});
+            if (!P.kd) {
+                be.inclusive_max(lead, leader, E);
+                be.for_each_heavy(E, EvalAreasF{L, primB, P, d, skey[d], sref[d], leader, areaB, areaA, err});
+            }
+            be.for_each(E, EvalCostF{L, P, d, skey[d], sref[d], leader, endsBefore, areaB, areaA, primB});
             out.candidates += E;
         }
         void *tmp[] = {keyTmp, valTmp, isEnd, lead, endsBefore, leader, areaB, areaA};
@@ -158,7 +163,7 @@ BuildResult build(B &be, const float *tris, uint32_t n, const BuildParams &P, co
         levels.emplace_back();
         Level &Lc = levels[levels.size() - 2];   // the vector may have moved
         Level &Nx = levels.back();
-        alloc_level(be, Nx, 2 * nInterior, M);
+        alloc_level(be, Nx, 2 * nInterior, M, !P.kd);
         SortedDirs S;
         for (uint32_t d = 0; d < kMaxDirs; ++d) { S.key[d] = d < M ? skey[d] : nullptr; S.ref[d] = d < M ? sref[d] : nullptr; }
         be.for_each_heavy(Lc.K, SplitF{Lc, Nx, primB, P, S, rank, err});

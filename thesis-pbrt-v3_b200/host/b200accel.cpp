@@ -184,10 +184,10 @@ B200Accel::B200Accel(std::vector<std::shared_ptr<Primitive>> p, const ParamSet &
             d.kind = B200RT_BVH;
             nIdx = (uint32_t)prims.size();
         } else if (tree == "kdtree") {  // CreateKdTreeAccelerator (kdtreeaccel.cpp:523-545)
-            rc = b200rt_build_kdtree(cap.verts.data(), (uint32_t)prims.size(), ps.FindOneInt("intersectcost", 80),
-                                     ps.FindOneInt("traversalcost", 1), ps.FindOneFloat("emptybonus", 0.f),
-                                     ps.FindOneInt("maxprims", 1), ps.FindOneInt("maxdepth", -1), &ownNodes, &nNodes,
-                                     &ownIdx, &nIdx, d.bounds);
+            rc = b200rt_build_kdtree_device(cap.verts.data(), (uint32_t)prims.size(), ps.FindOneInt("intersectcost", 80),
+                                            ps.FindOneInt("traversalcost", 1), ps.FindOneFloat("emptybonus", 0.f),
+                                            ps.FindOneInt("maxprims", 1), ps.FindOneInt("maxdepth", -1), &ownNodes, &nNodes,
+                                            &ownIdx, &nIdx, d.bounds, nullptr);
             d.kind = B200RT_KDTREE;
             d.n_directions = 3;
         } else if (tree == "rbsp") {    // CreateRBSPTreeAccelerator (rbsp.cpp:549-570), built on the device
