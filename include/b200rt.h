@@ -197,6 +197,12 @@ int b200rt_build_kdtree_device(const float *tri_verts, uint32_t n_prims, int ise
                                float empty_bonus, int max_prims, int max_depth, void **out_nodes, uint32_t *out_node_count,
                                uint32_t **out_prim_indices, uint32_t *out_n_indices, float out_bounds[6],
                                b200rt_build_stats *stats);
+/* BVHAccel's sweep-SAH build (bvh.cpp:155-352) on the device: every axis sorted once for the whole scene, then per tree level
+ * two segmented box scans per axis, one thread per candidate position, stable partitions that keep the runs sorted, and
+ * primitiveInfo permuted exactly as std::partition leaves it (csrc/bvh_build.cuh).  Outputs and parameters as
+ * b200rt_build_bvh; nodes AND primNumMapping equal its output (and the reference's) byte for byte. */
+int b200rt_build_bvh_device(const float *tri_verts, uint32_t n_prims, int max_node_prims, int isect_cost, int traversal_cost,
+                            void **out_nodes, uint32_t *out_node_count, uint32_t **out_prim_order, b200rt_build_stats *stats);
 void b200rt_free(void *p);
 
 /* ---- wavefront driver (SamplerIntegrator::Render restructured, src/core/integrator.cpp:230-360

@@ -6,6 +6,7 @@
 #include <numeric>
 
 #include "rbsp_driver.h"
+#include "bvh_driver.h"
 
 using namespace b200rt::rbsp;
 
@@ -27,6 +28,13 @@ struct HostBackend {
     void exclusive_sum(const uint32_t *in, uint32_t *out, size_t n) {
         uint32_t s = 0;
         for (size_t i = 0; i < n; ++i) { const uint32_t v = in[i]; out[i] = s; s += v; }
+    }
+    void scan_boxes(const uint32_t *keys, const b200rt::bvhb::Box6 *in, b200rt::bvhb::Box6 *out, size_t n, bool reverse) {
+        b200rt::bvhb::BoxUnion op;
+        for (size_t j = 0; j < n; ++j) {
+            const size_t i = reverse ? n - 1 - j : j, prev = reverse ? i + 1 : i - 1;
+            out[i] = (j > 0 && keys[prev] == keys[i]) ? op(out[prev], in[i]) : in[i];
+        }
     }
     void inclusive_max(const uint32_t *in, uint32_t *out, size_t n) {
         uint32_t m = 0;
@@ -68,3 +76,18 @@ extern "C" int hb_build_rbsp(const float *tris, uint32_t n, uint32_t nbDirection
     return 0;
 }
 extern "C" void hb_free(void *p) { std::free(p); }
+
+extern "C" int hb_build_bvh(const float *tris, uint32_t n, int maxNodePrims, int isectCost, int traversalCost,
+                            uint32_t **nodes, uint32_t *nNodes, uint32_t **order) {
+    using namespace b200rt::bvhb;
+    HostBackend be;
+    BvhParams P{std::min(255, maxNodePrims), isectCost, traversalCost};
+    BvhResult r = build_bvh(be, tris, n, P);
+    if (r.error) return 2;
+    *nNodes = (uint32_t)(r.nodes.size() / 8);
+    *nodes = (uint32_t *)std::malloc(std::max<size_t>(r.nodes.size(), 1) * 4);
+    *order = (uint32_t *)std::malloc(std::max<size_t>(r.order.size(), 1) * 4);
+    std::memcpy(*nodes, r.nodes.data(), r.nodes.size() * 4);
+    std::memcpy(*order, r.order.data(), r.order.size() * 4);
+    return 0;
+}

@@ -133,6 +133,42 @@ def test_kd_mode_reproduces_the_reference_kdtree(hb, built_lib):
         assert bad == 0
 
 
+@pytest.fixture(scope="module")
+def hb_bvh(hb):
+    L = C.CDLL(os.path.join(HB_DIR, "libhostbuild.so"))
+    L.hb_build_bvh.argtypes = [C.c_void_p, C.c_uint32, C.c_int, C.c_int, C.c_int, C.POINTER(C.POINTER(C.c_uint32)),
+                               C.POINTER(C.c_uint32), C.POINTER(C.POINTER(C.c_uint32))]
+
+    def build(tv, maxnodeprims=4, intersectcost=8, traversalcost=1):
+        tv = np.ascontiguousarray(tv, np.float32).reshape(-1, 9)
+        nodes, order, nn = C.POINTER(C.c_uint32)(), C.POINTER(C.c_uint32)(), C.c_uint32()
+        assert L.hb_build_bvh(tv.ctypes.data, len(tv), maxnodeprims, intersectcost, traversalcost, C.byref(nodes), C.byref(nn), C.byref(order)) == 0
+        N, O = np.ctypeslib.as_array(nodes, (nn.value, 8)).copy(), np.ctypeslib.as_array(order, (len(tv),)).copy()
+        L.hb_free(nodes)
+        L.hb_free(order)
+        return N, O
+    return build
+
+
+def test_level_synchronous_bvh_build_is_byte_identical(hb_bvh, built_lib):
+    """csrc/bvh_build.cuh (sorted once per axis, segmented box scans, std::partition's permutation from two scans) against the
+    reference-built golden and against the serial host builder on meshes and soups, several parameter sets: the 32-byte nodes
+    AND primNumMapping, byte for byte."""
+    g = load_golden("ref_small_bvh.npz")
+    N, O = hb_bvh(g["tri_verts"])
+    assert np.array_equal(N, g["nodes"]) and np.array_equal(O, g["indices"])
+    from b200rt import scenes
+    cases = [(scenes.soup(3000, seed=3), {}), (scenes.killeroo_simple()["tri_verts"][:25000], {}),
+             (scenes.killeroo_simple()["tri_verts"][:9000], dict(maxnodeprims=1)),
+             (scenes.sponza_standin(detail=0.1)["tri_verts"], dict(maxnodeprims=8, intersectcost=20, traversalcost=3)),
+             (np.tile(scenes.soup(1, seed=1), (40, 1)), {}),           # 40 identical triangles: every centroid ties, the primitive number decides
+             (scenes.soup(1, seed=2), {}), (scenes.soup(2, seed=2), {})]
+    for tv, kw in cases:
+        h = built_lib.build_bvh(tv, **kw)
+        N, O = hb_bvh(tv, **kw)
+        assert np.array_equal(N, h["nodes"]) and np.array_equal(O, h["indices"]), (len(tv), kw)
+
+
 def test_empty_and_tiny_inputs(hb):
     t = hb(np.zeros((0, 9), np.float32), nbDirections=7)
     assert t["nodes"].shape == (1, 2) and t["nodes"][0, 1] == 7 and len(t["indices"]) == 0      # one empty leaf: flags = M, np = 0
@@ -207,3 +243,23 @@ def test_device_kdtree_build(gpu, hb):
     hits = acc.Intersect(g["rays"])
     assert np.array_equal(hits["prim"], np.where(g["hit_prim"] < 0, gpu.MISS, g["hit_prim"]).astype(np.uint32))
     assert np.array_equal(hits["t"].view(np.uint32), g["hit_t"].view(np.uint32))
+
+
+@pytest.mark.gpu
+def test_device_bvh_build(gpu):
+    """b200rt_build_bvh_device: the host builder's (= the reference's) nodes and primNumMapping byte for byte, on the golden,
+    on scenes/killeroo-simple and on the headline sponza stand-in."""
+    from b200rt import scenes
+    g = load_golden("ref_small_bvh.npz")
+    t = gpu.build_bvh_device(g["tri_verts"])
+    assert np.array_equal(t["nodes"], g["nodes"]) and np.array_equal(t["indices"], g["indices"])
+    for name, tv, kw in [("killeroo-simple", scenes.killeroo_simple()["tri_verts"], {}),
+                         ("sponza stand-in", scenes.sponza_standin()["tri_verts"], {}),
+                         ("killeroo-simple, maxnodeprims 1", scenes.killeroo_simple()["tri_verts"], dict(maxnodeprims=1))]:
+        t0 = time.time()
+        h = gpu.build_bvh(tv, **kw)
+        host_s = time.time() - t0
+        t = gpu.build_bvh_device(tv, **kw)
+        assert np.array_equal(t["nodes"], h["nodes"]) and np.array_equal(t["indices"], h["indices"]), name
+        print("\n%s: %d triangles, %d nodes: %.1f ms on the B200 (%d levels, %d launches); serial host builder %.0f ms"
+              % (name, len(tv), len(t["nodes"]), t["build"]["build_ms"], t["build"]["levels"], t["build"]["kernel_launches"], 1e3 * host_s))

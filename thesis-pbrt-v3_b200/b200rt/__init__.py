@@ -9,9 +9,9 @@ The reference's interface for this path (paths relative to the reference tree):
 There is no CPU fallback: importing works anywhere (the library loads without a GPU so symbol
 checks can run), but every compute call raises B200RTError without a CUDA device."""
 from .api import (B200RTError, B200Accel, MakeAccelerator, RAY_DTYPE, HIT_DTYPE, MISS, lib, lib_path,
-                  build_bvh, build_kdtree, build_rbsp, build_kdtree_device, make_rays, init, launch_count, KINDS)
+                  build_bvh, build_kdtree, build_rbsp, build_kdtree_device, build_bvh_device, make_rays, init, launch_count, KINDS)
 
 from .wavefront import WavefrontPathIntegrator, film_to_rgb  # noqa: E402
 
 __all__ = ["WavefrontPathIntegrator", "film_to_rgb", "B200RTError", "B200Accel", "MakeAccelerator", "RAY_DTYPE", "HIT_DTYPE", "MISS", "lib", "lib_path",
-           "build_bvh", "build_kdtree", "build_rbsp", "build_kdtree_device", "make_rays", "init", "launch_count", "KINDS"]
+           "build_bvh", "build_kdtree", "build_rbsp", "build_kdtree_device", "build_bvh_device", "make_rays", "init", "launch_count", "KINDS"]

@@ -143,6 +143,23 @@ def build_kdtree(tri_verts, intersectcost=80, traversalcost=1, emptybonus=0.0, m
                 n_prims=len(v))
 
 
+def build_bvh_device(tri_verts, maxnodeprims=4, intersectcost=8, traversalcost=1):
+    """build_bvh on the DEVICE (b200rt_build_bvh_device, csrc/bvh_build.cuh): nodes and primNumMapping byte-identical to
+    build_bvh's."""
+    v = np.ascontiguousarray(tri_verts, np.float32).reshape(-1, 9)
+    nodes, order, nc = C.c_void_p(), C.c_void_p(), C.c_uint32()
+    st = BuildStats()
+    L = lib()
+    L.b200rt_build_bvh_device.argtypes = [C.c_void_p, C.c_uint32, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    _check(L.b200rt_build_bvh_device(_p(v), len(v), int(maxnodeprims), int(intersectcost), int(traversalcost),
+                                     C.byref(nodes), C.byref(nc), C.byref(order), C.byref(st)))
+    n = _take(nodes, nc.value, 8)
+    o = _take(order, len(v), 1).reshape(-1)
+    bounds = n[0, :6].view(np.float32).copy() if len(n) else np.zeros(6, np.float32)
+    return dict(kind="bvh", nodes=n, indices=o, directions=np.zeros((0, 3), np.float32), bounds=bounds, n_prims=len(v),
+                build=dict(levels=st.levels, candidates=st.candidates, kernel_launches=st.kernel_launches, build_ms=st.build_ms))
+
+
 def build_kdtree_device(tri_verts, intersectcost=80, traversalcost=1, emptybonus=0.0, maxprims=1, maxdepth=-1):
     """build_kdtree on the DEVICE (b200rt_build_kdtree_device: the level-synchronous builder of csrc/rbsp_build.cuh in its
     kd mode).  Node array identical to build_kdtree's; the order of the indices inside a leaf may differ."""
@@ -299,21 +316,21 @@ _RBSP_DEFAULTS = dict(nbDirections=3, intersectcost=80, traversalcost=5, emptybo
 _IGNORED = {"splitalpha", "alphatype", "axisselectiontype", "axisselectionamount", "nbDirections"}
 
 
-def MakeAccelerator(name, tri_verts, paramSet=None, tri_uvs=None, tree=None, tri_normals=None, prim_flags=None):
+def MakeAccelerator(name, tri_verts, paramSet=None, tri_uvs=None, tree=None, tri_normals=None, prim_flags=None, builder="device"):
     """Mirror of MakeAccelerator(name, prims, paramSet) (reference src/core/api.cpp:790-1015) for
-    the accelerators on the hot path.  `paramSet` uses the .pbrt parameter names.  "bvh" and
-    "kdtree" are built by this repo's host builders, "rbsp" by the device builder (build_rbsp); "rbspkd" and the BSP
-    families take a host-built tree (`tree=`, reference node format).
-    Unknown names return None after a warning, like the reference (api.cpp:1011-1012)."""
+    the accelerators on the hot path.  `paramSet` uses the .pbrt parameter names.  "bvh", "kdtree" and "rbsp" are built ON THE
+    DEVICE by the level-synchronous builders (build_bvh_device / build_kdtree_device / build_rbsp; `builder="host"` selects the
+    serial host builders for bvh / kdtree — same nodes); "rbspkd" and the BSP families take a host-built tree (`tree=`,
+    reference node format).  Unknown names return None after a warning, like the reference (api.cpp:1011-1012)."""
     ps = dict(paramSet or {})
     if tree is not None:
         return B200Accel(tree, tri_verts, tri_uvs, tri_normals=tri_normals, prim_flags=prim_flags)
     if name == "bvh":
         args = {k: ps.pop(k, v) for k, v in _BVH_DEFAULTS.items()}
-        tree = build_bvh(tri_verts, **args)
+        tree = (build_bvh_device if builder == "device" else build_bvh)(tri_verts, **args)
     elif name == "kdtree":
         args = {k: ps.pop(k, v) for k, v in _KD_DEFAULTS.items()}
-        tree = build_kdtree(tri_verts, **args)
+        tree = (build_kdtree_device if builder == "device" else build_kdtree)(tri_verts, **args)
     elif name == "rbsp":
         args = {k: ps.pop(k, v) for k, v in _RBSP_DEFAULTS.items()}
         tree = build_rbsp(tri_verts, **args)

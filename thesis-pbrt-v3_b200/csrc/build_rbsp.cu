@@ -12,6 +12,9 @@
 #include <cstdlib>
 
 #include "../../include/b200rt.h"
+#include <thrust/iterator/reverse_iterator.h>
+
+#include "bvh_driver.h"
 #include "rbsp_driver.h"
 #include "scene_internal.h"
 
@@ -87,6 +90,26 @@ struct CudaBackend {
         free(tmp);
         ++launches;
     }
+    void scan_boxes(const uint32_t *keys, const b200rt::bvhb::Box6 *in, b200rt::bvhb::Box6 *out, size_t n, bool reverse) {
+        if (!n || status != cudaSuccess) return;
+        using b200rt::bvhb::BoxUnion;
+        size_t bytes = 0;
+        if (!reverse) {
+            check(cub::DeviceScan::InclusiveScanByKey(nullptr, bytes, keys, in, out, BoxUnion(), (int64_t)n, cub::Equality(), st));
+            void *tmp = alloc<uint8_t>(bytes);
+            check(cub::DeviceScan::InclusiveScanByKey(tmp, bytes, keys, in, out, BoxUnion(), (int64_t)n, cub::Equality(), st));
+            free(tmp);
+        } else {
+            auto rk = thrust::make_reverse_iterator(keys + n);
+            auto ri = thrust::make_reverse_iterator(in + n);
+            auto ro = thrust::make_reverse_iterator(out + n);
+            check(cub::DeviceScan::InclusiveScanByKey(nullptr, bytes, rk, ri, ro, BoxUnion(), (int64_t)n, cub::Equality(), st));
+            void *tmp = alloc<uint8_t>(bytes);
+            check(cub::DeviceScan::InclusiveScanByKey(tmp, bytes, rk, ri, ro, BoxUnion(), (int64_t)n, cub::Equality(), st));
+            free(tmp);
+        }
+        ++launches;
+    }
     void inclusive_max(const uint32_t *in, uint32_t *out, size_t n) {
         if (!n || status != cudaSuccess) return;
         size_t bytes = 0;
@@ -99,6 +122,71 @@ struct CudaBackend {
 };
 
 }  // namespace
+
+static bool have_device() {
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { cudaGetLastError(); return false; }
+    return true;
+}
+static void open_backend(CudaBackend &be, cudaEvent_t *e0, cudaEvent_t *e1) {
+    be.check(cudaStreamCreateWithFlags(&be.st, cudaStreamNonBlocking));
+    int dev = 0;   // keep freed blocks in the pool between levels
+    cudaGetDevice(&dev);
+    cudaMemPool_t pool;
+    if (cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess) {
+        uint64_t thr = ~0ull;
+        cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr);
+    }
+    be.check(cudaEventCreate(e0));
+    be.check(cudaEventCreate(e1));
+    be.check(cudaEventRecord(*e0, be.st));
+}
+static float close_backend(CudaBackend &be, cudaEvent_t e0, cudaEvent_t e1) {
+    be.check(cudaEventRecord(e1, be.st));
+    be.check(cudaStreamSynchronize(be.st));
+    float ms = 0;
+    if (be.status == cudaSuccess) cudaEventElapsedTime(&ms, e0, e1);
+    if (e0) cudaEventDestroy(e0);
+    if (e1) cudaEventDestroy(e1);
+    if (be.st) cudaStreamDestroy(be.st);
+    g_launches += be.launches;
+    return ms;
+}
+
+// BVHAccel's sweep-SAH build on the device (bvh_build.cuh); outputs as b200rt_build_bvh
+extern "C" int b200rt_build_bvh_device(const float *tri_verts, uint32_t n_prims, int max_node_prims, int isect_cost,
+                                       int traversal_cost, void **out_nodes, uint32_t *out_node_count,
+                                       uint32_t **out_prim_order, b200rt_build_stats *stats) {
+    using b200rt::set_error;
+    using namespace b200rt::bvhb;
+    if (!tri_verts || !out_nodes || !out_node_count || !out_prim_order) return set_error(B200RT_EINVAL, "b200rt_build_bvh_device: null argument");
+    *out_nodes = nullptr; *out_node_count = 0; *out_prim_order = nullptr;
+    if (n_prims == 0) return B200RT_OK;
+    if (n_prims >= (1u << 28)) return set_error(B200RT_EUNSUPPORTED, "b200rt_build_bvh_device: more than 2^28 primitives");
+    if (!have_device()) return set_error(B200RT_ENODEVICE, "b200rt_build_bvh_device: no CUDA device (the builder has no host path)");
+    CudaBackend be;
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    open_backend(be, &e0, &e1);
+    float *dTris = be.alloc<float>((size_t)n_prims * 9);
+    be.upload(dTris, tri_verts, (size_t)n_prims * 9);
+    BvhResult r;
+    const BvhParams P{std::min(255, max_node_prims), isect_cost, traversal_cost};   // bvh.cpp:157
+    if (be.status == cudaSuccess) r = build_bvh(be, dTris, n_prims, P);
+    be.free(dTris);
+    const float ms = close_backend(be, e0, e1);
+    if (be.status != cudaSuccess) return set_error(B200RT_ECUDA, "b200rt_build_bvh_device: %s", cudaGetErrorString(be.status));
+    if (r.error) return set_error(B200RT_EUNSUPPORTED, "b200rt_build_bvh_device: the tree is deeper than 4096 levels");
+    uint32_t *nodes = (uint32_t *)std::malloc(std::max<size_t>(r.nodes.size(), 1) * 4);
+    uint32_t *order = (uint32_t *)std::malloc(std::max<size_t>(r.order.size(), 1) * 4);
+    if (!nodes || !order) { std::free(nodes); std::free(order); return set_error(B200RT_ENOMEM, "b200rt_build_bvh_device: out of host memory"); }
+    std::memcpy(nodes, r.nodes.data(), r.nodes.size() * 4);
+    std::memcpy(order, r.order.data(), r.order.size() * 4);
+    *out_nodes = nodes;
+    *out_node_count = (uint32_t)(r.nodes.size() / 8);
+    *out_prim_order = order;
+    if (stats) { stats->levels = r.levels; stats->candidates = r.candidates; stats->kernel_launches = be.launches; stats->build_ms = ms; }
+    return B200RT_OK;
+}
 
 // nb_directions = 0: kd-tree mode
 static int build_on_device(const float *tri_verts, uint32_t n_prims, uint32_t nb_directions, int isect_cost,
@@ -119,11 +207,7 @@ static int build_on_device(const float *tri_verts, uint32_t n_prims, uint32_t nb
     P.maxPrims = (uint32_t)max_prims;
     P.maxDepth = max_depth < 0 ? default_max_depth(n_prims) : (uint32_t)max_depth;
     if (P.maxDepth > 63) return set_error(B200RT_EUNSUPPORTED, "b200rt_build_rbsp: maxdepth %u exceeds the traversal's 64-entry stack", P.maxDepth);
-    int ndev = 0;
-    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
-        cudaGetLastError();
-        return set_error(B200RT_ENODEVICE, "b200rt_build_rbsp: no CUDA device (the builder has no host path)");
-    }
+    if (!have_device()) return set_error(B200RT_ENODEVICE, "b200rt_build_rbsp: no CUDA device (the builder has no host path)");
     // `bounds = Union(bounds, prim->WorldBound())` (rbsp.cpp:192): plain min / max of the coordinates
     float world[6] = {3.402823466e+38f, 3.402823466e+38f, 3.402823466e+38f, -3.402823466e+38f, -3.402823466e+38f, -3.402823466e+38f};
     for (uint32_t p = 0; p < n_prims; ++p)
@@ -134,32 +218,13 @@ static int build_on_device(const float *tri_verts, uint32_t n_prims, uint32_t nb
             }
     CudaBackend be;
     cudaEvent_t e0 = nullptr, e1 = nullptr;
-    be.check(cudaStreamCreateWithFlags(&be.st, cudaStreamNonBlocking));
-    {   // keep freed blocks in the pool between levels
-        int dev = 0;
-        cudaGetDevice(&dev);
-        cudaMemPool_t pool;
-        if (cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess) {
-            uint64_t thr = ~0ull;
-            cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr);
-        }
-    }
-    be.check(cudaEventCreate(&e0));
-    be.check(cudaEventCreate(&e1));
-    be.check(cudaEventRecord(e0, be.st));
+    open_backend(be, &e0, &e1);
     float *dTris = be.alloc<float>((size_t)n_prims * 9);
     be.upload(dTris, tri_verts, (size_t)n_prims * 9);
     BuildResult r;
     if (be.status == cudaSuccess) r = build(be, dTris, n_prims, P, world);
     be.free(dTris);
-    be.check(cudaEventRecord(e1, be.st));
-    be.check(cudaStreamSynchronize(be.st));
-    float ms = 0;
-    if (be.status == cudaSuccess) cudaEventElapsedTime(&ms, e0, e1);
-    if (e0) cudaEventDestroy(e0);
-    if (e1) cudaEventDestroy(e1);
-    if (be.st) cudaStreamDestroy(be.st);
-    g_launches += be.launches;
+    const float ms = close_backend(be, e0, e1);
     if (be.status != cudaSuccess) return set_error(B200RT_ECUDA, "b200rt_build_rbsp: %s", cudaGetErrorString(be.status));
     if (r.error) return set_error(B200RT_EUNSUPPORTED, "b200rt_build_rbsp: a node's k-DOP outgrew %d edges / %d cut points per face", kMaxEdges, kMaxFacePoints);
     const size_t nNodes = r.nodes.size() / 2;

@@ -178,9 +178,9 @@ B200Accel::B200Accel(std::vector<std::shared_ptr<Primitive>> p, const ParamSet &
         uint32_t nNodes = 0, nIdx = 0;
         int rc;
         if (tree == "bvh") {            // parameter names and defaults of CreateBVHAccelerator (bvh.cpp:529-535)
-            rc = b200rt_build_bvh(cap.verts.data(), (uint32_t)prims.size(), ps.FindOneInt("maxnodeprims", 4),
-                                  ps.FindOneInt("intersectcost", 8), ps.FindOneInt("traversalcost", 1), &ownNodes,
-                                  &nNodes, &ownIdx);
+            rc = b200rt_build_bvh_device(cap.verts.data(), (uint32_t)prims.size(), ps.FindOneInt("maxnodeprims", 4),
+                                         ps.FindOneInt("intersectcost", 8), ps.FindOneInt("traversalcost", 1), &ownNodes,
+                                         &nNodes, &ownIdx, nullptr);
             d.kind = B200RT_BVH;
             nIdx = (uint32_t)prims.size();
         } else if (tree == "kdtree") {  // CreateKdTreeAccelerator (kdtreeaccel.cpp:523-545)
