@@ -190,6 +190,12 @@ int b200rt_build_rbsp(const float *tri_verts, uint32_t n_prims, uint32_t nb_dire
                       float empty_bonus, int max_prims, int max_depth, void **out_nodes, uint32_t *out_node_count,
                       uint32_t **out_prim_indices, uint32_t *out_n_indices, float out_bounds[6], float *out_directions,
                       b200rt_build_stats *stats);
+/* RBSPKd::buildTree (rbspKd.cpp:187-470; CreateRBSPKdTreeAccelerator :640-665 adds "kdtraversalcost", default 1) through the
+ * same builder: axis-aligned planes are charged kd_traversal_cost, the others 0.1 * isect_cost * (n - 1) + kd_traversal_cost. */
+int b200rt_build_rbspkd(const float *tri_verts, uint32_t n_prims, uint32_t nb_directions, int isect_cost, int traversal_cost,
+                        int kd_traversal_cost, float empty_bonus, int max_prims, int max_depth, void **out_nodes,
+                        uint32_t *out_node_count, uint32_t **out_prim_indices, uint32_t *out_n_indices, float out_bounds[6],
+                        float *out_directions, b200rt_build_stats *stats);
 /* KdTreeAccel::buildTree (kdtreeaccel.cpp:208-379) through the same level-synchronous device builder (box areas in closed
  * form instead of k-DOP cuts).  Same outputs and parameters as b200rt_build_kdtree; the node array is identical to it (and to
  * the reference's), the order of the indices inside a leaf follows the stable radix sort instead of std::sort's. */

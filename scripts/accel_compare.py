@@ -3,6 +3,9 @@ comparison — BVH vs kd-tree vs RBSP with 3/7/9/13 directions (+ RBSPKd, BSPPap
 
     python scripts/accel_compare.py --build     # HERE (needs /root/reference): reference builders -> oracle/_ref/feet_trees.npz
     python scripts/accel_compare.py             # on the GPU box: Mrays/s + the thesis's per-ray statistics per accelerator
+    python scripts/accel_compare.py --device-build   # same, but BVH / kd-tree / RBSP / RBSPKd trees are BUILT on the B200 (round 2:
+                                                     # csrc/rbsp_build.cuh, bvh_build.cuh) and the build time is printed; the BSPPaper
+                                                     # families still come from the tree file when it is there
 
 The tree file is git-ignored (oracle/_ref/) but travels to the GPU box with the snapshot.  The full killeroo of the
 scene (33 264 triangles) is used; rays = the crop window's camera rays (1000 x 2000 px of the 5000^2 film) and the
@@ -64,23 +67,35 @@ def run():
     import torch
     import b200rt
     from b200rt import scenes
-    z = np.load(TREES)
-    tv = z["tri_verts"]
+    device_build = "--device-build" in sys.argv
+    z = np.load(TREES) if os.path.exists(TREES) else None
+    tv = z["tri_verts"] if z is not None else scenes.killeroo_feet()["tri_verts"]
     b200rt.init(0)
+    b200rt.build_bvh_device(tv[:64])   # load the module before timing anything
     torch.zeros(1, device="cuda")
     st = torch.cuda.current_stream().cuda_stream
     sc = scenes.killeroo_feet()
     x0, x1, y0, y1 = sc["crop"]
     cam = scenes.camera_rays(sc["camera"], x0=x0, x1=x1, y0=y0, y1=y1)   # the crop window at the scene's resolution
-    names = [n for n, _, _ in CASES if n + "_nodes" in z.files]
+    names = [n for n, k, _ in CASES if (device_build and k in ("bvh", "kdtree", "rbsp", "rbspkd")) or (z is not None and n + "_nodes" in z.files)]
     ref = None
     accs = {}
     print("killeroo-feet: %d triangles, %d camera rays (crop %s of 5000^2)" % (len(tv), len(cam), (x0, x1, y0, y1)))
     print("%-10s %9s | %-28s | %-28s | %-28s" % ("accel", "nodes", "camera closest", "bounce closest", "shadow any-hit"))
     print("%-10s %9s | %8s %8s %9s | %8s %8s %9s | %8s %8s %9s" % (("", "") + ("Mrays/s", "nodes/r", "tests/r") * 3))
+    builds = {}
     for name in names:
-        tree = dict(kind=str(z[name + "_kind"]), nodes=z[name + "_nodes"], indices=z[name + "_indices"],
-                    directions=z[name + "_directions"], bounds=z[name + "_bounds"], n_prims=len(tv))
+        kind, ip = [(k, p) for n_, k, p in CASES if n_ == name][0]
+        if device_build and kind in ("bvh", "kdtree", "rbsp", "rbspkd"):
+            tree = {"bvh": b200rt.build_bvh_device, "kdtree": b200rt.build_kdtree_device}[kind](tv) if kind in ("bvh", "kdtree") else \
+                b200rt.build_rbsp(tv, nbDirections=ip["nbDirections"], kdtraversalcost=1 if kind == "rbspkd" else None)
+            builds[name] = tree["build"]["build_ms"]
+            if z is not None and name + "_nodes" in z.files:   # the reference's own tree of the same scene: same node array
+                assert np.array_equal(tree["nodes"], z[name + "_nodes"]), name
+                builds[name] = (tree["build"]["build_ms"], float(z[name + "_build_s"]))
+        else:
+            tree = dict(kind=str(z[name + "_kind"]), nodes=z[name + "_nodes"], indices=z[name + "_indices"],
+                        directions=z[name + "_directions"], bounds=z[name + "_bounds"], n_prims=len(tv))
         acc = b200rt.B200Accel(tree, tv)
         hits = acc.Intersect(cam)
         if ref is None:
@@ -115,6 +130,10 @@ def run():
             row += " %8.0f %8.2f %9.2f |" % (n / ms / 1e3, (rs["interior_visits"] + rs["leaf_visits"]).mean(), rs["prim_tests"].mean())
         print(row, flush=True)
         accs[name] = acc
+    if builds:
+        print("\ntree builds on the B200 (ms)" + (" | the reference's builder on this container's CPU (s), node arrays asserted equal" if z is not None else "") + ":")
+        for name, b in builds.items():
+            print("%-10s %s" % (name, ("%9.1f ms | %7.1f s" % b) if isinstance(b, tuple) else "%9.1f ms" % b))
     # ---- the thesis's experiment itself: the scene file rendered per accelerator (scripts/run_rbsps.sh of the reference:
     # 5000^2 film, cropwindow [.3 .5 .4 .8], 8 spp, path maxdepth 5, distant light, plastic killeroo) ----
     from b200rt import wavefront as wf

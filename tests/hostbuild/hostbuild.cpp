@@ -43,12 +43,13 @@ struct HostBackend {
 };
 }  // namespace
 
-// nbDirections = 0 selects the kd-tree mode (KdTreeAccel::buildTree)
+// nbDirections = 0 selects the kd-tree mode (KdTreeAccel::buildTree); nbDirections + 100 the RBSPKd mode (kdtraversalcost 1)
 extern "C" int hb_build_rbsp(const float *tris, uint32_t n, uint32_t nbDirections, int isectCost, int traversalCost,
                              float emptyBonus, int maxPrims, int maxDepth, uint32_t **nodes, uint32_t *nNodes,
                              uint32_t **indices, uint32_t *nIndices, float *dirsOut, float *boundsOut, uint64_t *candidates) {
     BuildParams P{};
     P.kd = nbDirections == 0;
+    if (nbDirections >= 100) { P.rbspkd = 1; P.kdTraversalCost = 1; nbDirections -= 100; }
     P.M = make_directions(P.kd ? 3 : nbDirections, P.dirs);
     if (!P.M) return 1;
     P.isectCost = (uint32_t)isectCost; P.traversalCost = (uint32_t)traversalCost; P.emptyBonus = emptyBonus;

@@ -132,7 +132,7 @@ def test_plugin_matches_reference_accelerator(host, gpu, tree, builder, ip, refk
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("tree,ip", [("bvh", {}), ("kdtree", {}), ("rbsp", {"nbDirections": 7})])
+@pytest.mark.parametrize("tree,ip", [("bvh", {}), ("kdtree", {}), ("rbsp", {"nbDirections": 7}), ("rbspkd", {"nbDirections": 13})])
 def test_plugin_with_this_repos_builders(host, gpu, tree, ip):
     """`"string builder" "b200"`: the library's own builders — BVH / kd-tree on the host, RBSP on the device."""
     rb, L = host

@@ -54,6 +54,31 @@ def test_builders_reproduce_the_references_living_room_trees(built_lib, room, go
     assert _sha(t["indices"]) == str(golden[kind + "_indices_sha256"])
 
 
+@pytest.mark.gpu
+@pytest.mark.parametrize("kind", ["bvh", "kdtree"])
+def test_device_builders_reproduce_the_references_living_room_trees(gpu, room, golden, kind):
+    """The level-synchronous DEVICE builders on the reference's own 143 163 triangles: the node arrays hash to the reference's
+    SHA-256 (BVH: primNumMapping too; kd-tree: 2 941 789 nodes, leaves hold the same primitives, their order inside a leaf
+    follows the stable radix sort instead of std::sort's)."""
+    tv = room["tri_verts"]
+    t = gpu.build_bvh_device(tv) if kind == "bvh" else gpu.build_kdtree_device(tv)
+    assert len(t["nodes"]) == int(golden[kind + "_n_nodes"])
+    assert _sha(t["nodes"]) == str(golden[kind + "_nodes_sha256"])
+    assert len(t["indices"]) == int(golden[kind + "_n_indices"])
+    if kind == "bvh":
+        assert _sha(t["indices"]) == str(golden[kind + "_indices_sha256"])
+    else:
+        h = gpu.build_kdtree(tv)
+        w0, w1 = t["nodes"][:, 0].astype(np.int64), t["nodes"][:, 1].astype(np.int64)
+        leaf = ((w1 & 3) == 3) & ((w1 >> 2) > 1)
+        starts, counts = w0[leaf], (w1[leaf] >> 2)
+        seg = np.repeat(np.arange(len(starts)), counts)
+        at = np.repeat(starts, counts) + (np.arange(len(seg)) - np.repeat(np.cumsum(counts) - counts, counts))
+        a, b = t["indices"][at], h["indices"][at]
+        assert np.array_equal(a[np.lexsort((a, seg))], b[np.lexsort((b, seg))])      # every leaf: the same primitives
+    print("\nliving-room %s on the B200: %d nodes in %.1f ms (%d levels)" % (kind, len(t["nodes"]), t["build"]["build_ms"], t["build"]["levels"]))
+
+
 def _check_hits(hits, occ, g, kind):
     ref_prim = np.where(g[kind + "_prim"] < 0, ob.MISS, g[kind + "_prim"]).astype(np.uint32)
     assert np.array_equal(hits["prim"], ref_prim)

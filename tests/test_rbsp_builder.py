@@ -44,7 +44,7 @@ def hb():
         I = np.ctypeslib.as_array(idx, (max(ni.value, 1),)).copy()[:ni.value]
         L.hb_free(nodes)
         L.hb_free(idx)
-        return dict(kind="rbsp", nodes=N, indices=I, directions=dirs[:nbDirections].copy(), bounds=b, n_prims=len(tv),
+        return dict(kind="rbsp", nodes=N, indices=I, directions=dirs[:nbDirections % 100].copy(), bounds=b, n_prims=len(tv),
                     candidates=cand.value)
     return build
 
@@ -115,6 +115,17 @@ def test_parameters_against_a_fresh_reference_build(hb, params):
         ex = rb.RefAccel(S, "rbsp", ip, fp).export()
         t = hb(tv, **params)
         compare_with_reference(t, ex["nodes"], ex["indices"], params["nbDirections"])
+
+
+def test_rbspkd_mode_reproduces_the_reference_tree(hb):
+    """RBSPKd::buildTree (rbspKd.cpp:187-470): nbDirections + 100 in the host harness."""
+    g = load_golden("ref_small_rbspkd13.npz")
+    t = hb(g["tri_verts"], nbDirections=113)
+    assert np.array_equal(t["nodes"], g["nodes"]) and np.array_equal(t["indices"], g["indices"])
+    g = load_golden("ref_feet.npz")
+    t = hb(g["tri_verts"], nbDirections=113)
+    bad, n = compare_with_reference(t, g["rbspkd13_nodes"], g["rbspkd13_indices"], 13)
+    assert bad == 0
 
 
 def test_kd_mode_reproduces_the_reference_kdtree(hb, built_lib):
@@ -263,3 +274,16 @@ def test_device_bvh_build(gpu):
         assert np.array_equal(t["nodes"], h["nodes"]) and np.array_equal(t["indices"], h["indices"]), name
         print("\n%s: %d triangles, %d nodes: %.1f ms on the B200 (%d levels, %d launches); serial host builder %.0f ms"
               % (name, len(tv), len(t["nodes"]), t["build"]["build_ms"], t["build"]["levels"], t["build"]["kernel_launches"], 1e3 * host_s))
+
+
+@pytest.mark.gpu
+def test_device_rbspkd_build(gpu):
+    g = load_golden("ref_feet.npz")
+    t = gpu.build_rbsp(g["tri_verts"], nbDirections=13, kdtraversalcost=1)
+    bad, n = compare_with_reference(t, g["rbspkd13_nodes"], g["rbspkd13_indices"], 13)
+    assert bad == 0 and t["kind"] == "rbspkd"
+    acc = gpu.MakeAccelerator("rbspkd", g["tri_verts"], {"nbDirections": 13})
+    hits = acc.Intersect(g["rays"])
+    assert np.array_equal(hits["prim"], np.where(g["rbspkd13_prim"] < 0, gpu.MISS, g["rbspkd13_prim"]).astype(np.uint32))
+    assert np.array_equal(hits["t"].view(np.uint32), g["rbspkd13_t"].view(np.uint32))
+    assert np.array_equal(acc.IntersectP(g["rays"]), g["rbspkd13_occ"])

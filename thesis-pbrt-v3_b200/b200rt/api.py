@@ -187,10 +187,12 @@ class BuildStats(C.Structure):
     _fields_ = [("levels", C.c_uint32), ("candidates", C.c_uint64), ("kernel_launches", C.c_uint64), ("build_ms", C.c_float)]
 
 
-def build_rbsp(tri_verts, nbDirections=3, intersectcost=80, traversalcost=5, emptybonus=0.0, maxprims=1, maxdepth=-1):
+def build_rbsp(tri_verts, nbDirections=3, intersectcost=80, traversalcost=5, emptybonus=0.0, maxprims=1, maxdepth=-1,
+               kdtraversalcost=None):
     """RBSP tree built ON THE DEVICE (csrc/build_rbsp.cu, level-synchronous: every candidate plane of a tree level cut and
     measured in parallel), params of CreateRBSPTreeAccelerator (reference src/accelerators/rbsp.cpp:549-570).  The node
-    array equals the reference builder's byte for byte.  tree["build"] holds levels / candidates / launches / build_ms."""
+    array equals the reference builder's byte for byte.  tree["build"] holds levels / candidates / launches / build_ms.
+    kdtraversalcost not None selects RBSPKd::buildTree (rbspKd.cpp:187-470, CreateRBSPKdTreeAccelerator's default 1)."""
     v = np.ascontiguousarray(tri_verts, np.float32).reshape(-1, 9)
     nodes, idx, nc, ni = C.c_void_p(), C.c_void_p(), C.c_uint32(), C.c_uint32()
     b = (C.c_float * 6)()
@@ -199,16 +201,23 @@ def build_rbsp(tri_verts, nbDirections=3, intersectcost=80, traversalcost=5, emp
     L = lib()
     L.b200rt_build_rbsp.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_int, C.c_int, C.c_float, C.c_int, C.c_int,
                                     C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
-    _check(L.b200rt_build_rbsp(_p(v), len(v), int(nbDirections), int(intersectcost), int(traversalcost), float(emptybonus),
-                               int(maxprims), int(maxdepth), C.byref(nodes), C.byref(nc), C.byref(idx), C.byref(ni),
-                               C.byref(b), _p(dirs), C.byref(st)))
+    L.b200rt_build_rbspkd.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_int, C.c_int, C.c_int, C.c_float, C.c_int, C.c_int,
+                                      C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    if kdtraversalcost is None:
+        _check(L.b200rt_build_rbsp(_p(v), len(v), int(nbDirections), int(intersectcost), int(traversalcost), float(emptybonus),
+                                   int(maxprims), int(maxdepth), C.byref(nodes), C.byref(nc), C.byref(idx), C.byref(ni),
+                                   C.byref(b), _p(dirs), C.byref(st)))
+    else:
+        _check(L.b200rt_build_rbspkd(_p(v), len(v), int(nbDirections), int(intersectcost), int(traversalcost), int(kdtraversalcost),
+                                     float(emptybonus), int(maxprims), int(maxdepth), C.byref(nodes), C.byref(nc), C.byref(idx),
+                                     C.byref(ni), C.byref(b), _p(dirs), C.byref(st)))
     n = _take(nodes, nc.value, 2)
     if ni.value:
         i = _take(idx, ni.value, 1).reshape(-1)
     else:
         L.b200rt_free(idx)
         i = np.zeros(0, np.uint32)
-    return dict(kind="rbsp", nodes=n, indices=i, directions=dirs[:int(nbDirections)].copy(), bounds=np.array(list(b), np.float32),
+    return dict(kind="rbsp" if kdtraversalcost is None else "rbspkd", nodes=n, indices=i, directions=dirs[:int(nbDirections)].copy(), bounds=np.array(list(b), np.float32),
                 n_prims=len(v), build=dict(levels=st.levels, candidates=st.candidates, kernel_launches=st.kernel_launches,
                                            build_ms=st.build_ms))
 
@@ -318,9 +327,9 @@ _IGNORED = {"splitalpha", "alphatype", "axisselectiontype", "axisselectionamount
 
 def MakeAccelerator(name, tri_verts, paramSet=None, tri_uvs=None, tree=None, tri_normals=None, prim_flags=None, builder="device"):
     """Mirror of MakeAccelerator(name, prims, paramSet) (reference src/core/api.cpp:790-1015) for
-    the accelerators on the hot path.  `paramSet` uses the .pbrt parameter names.  "bvh", "kdtree" and "rbsp" are built ON THE
+    the accelerators on the hot path.  `paramSet` uses the .pbrt parameter names.  "bvh", "kdtree", "rbsp" and "rbspkd" are built ON THE
     DEVICE by the level-synchronous builders (build_bvh_device / build_kdtree_device / build_rbsp; `builder="host"` selects the
-    serial host builders for bvh / kdtree — same nodes); "rbspkd" and the BSP families take a host-built tree (`tree=`,
+    serial host builders for bvh / kdtree — same nodes); the general BSP families take a host-built tree (`tree=`,
     reference node format).  Unknown names return None after a warning, like the reference (api.cpp:1011-1012)."""
     ps = dict(paramSet or {})
     if tree is not None:
@@ -335,8 +344,8 @@ def MakeAccelerator(name, tri_verts, paramSet=None, tri_uvs=None, tree=None, tri
         args = {k: ps.pop(k, v) for k, v in _RBSP_DEFAULTS.items()}
         tree = build_rbsp(tri_verts, **args)
     elif name == "rbspkd":
-        raise B200RTError(4, "accelerator %r needs a host-built tree (tree=...): its builder is not part of "
-                             "this engine" % name)
+        args = {k: ps.pop(k, v) for k, v in _RBSP_DEFAULTS.items()}
+        tree = build_rbsp(tri_verts, kdtraversalcost=ps.pop("kdtraversalcost", 1), **args)
     else:
         import warnings
         warnings.warn('Accelerator "%s" unknown.' % name)

@@ -188,8 +188,8 @@ extern "C" int b200rt_build_bvh_device(const float *tri_verts, uint32_t n_prims,
     return B200RT_OK;
 }
 
-// nb_directions = 0: kd-tree mode
-static int build_on_device(const float *tri_verts, uint32_t n_prims, uint32_t nb_directions, int isect_cost,
+// nb_directions = 0: kd-tree mode; kd_traversal_cost >= 0: RBSPKd mode
+static int build_on_device(const float *tri_verts, uint32_t n_prims, uint32_t nb_directions, int kd_traversal_cost, int isect_cost,
                            int traversal_cost, float empty_bonus, int max_prims, int max_depth, void **out_nodes,
                            uint32_t *out_node_count, uint32_t **out_prim_indices, uint32_t *out_n_indices,
                            float out_bounds[6], float *out_directions, b200rt_build_stats *stats) {
@@ -199,6 +199,7 @@ static int build_on_device(const float *tri_verts, uint32_t n_prims, uint32_t nb
     if (n_prims >= (1u << 27)) return set_error(B200RT_EUNSUPPORTED, "b200rt_build_rbsp: more than 2^27 primitives");
     BuildParams P{};
     P.kd = nb_directions == 0;
+    if (kd_traversal_cost >= 0) { P.rbspkd = 1; P.kdTraversalCost = (uint32_t)kd_traversal_cost; }
     P.M = make_directions(P.kd ? 3 : nb_directions, P.dirs);
     if (!P.M) return set_error(B200RT_EINVAL, "b200rt_build_rbsp: nbDirections must be 3, 7, 9 or 13 (RBSPShared.h:50-71), got %u", nb_directions);
     P.isectCost = (uint32_t)isect_cost;
@@ -226,6 +227,8 @@ static int build_on_device(const float *tri_verts, uint32_t n_prims, uint32_t nb
     be.free(dTris);
     const float ms = close_backend(be, e0, e1);
     if (be.status != cudaSuccess) return set_error(B200RT_ECUDA, "b200rt_build_rbsp: %s", cudaGetErrorString(be.status));
+    if (r.error == kErrFixedOnly)
+        return set_error(B200RT_EUNSUPPORTED, "b200rt_build_rbspkd: a node has candidate planes only in the \"fixed\" search; the reference indexes edges[-1] there (rbspKd.cpp:417-428)");
     if (r.error) return set_error(B200RT_EUNSUPPORTED, "b200rt_build_rbsp: a node's k-DOP outgrew %d edges / %d cut points per face", kMaxEdges, kMaxFacePoints);
     const size_t nNodes = r.nodes.size() / 2;
     uint32_t *nodes = (uint32_t *)std::malloc(std::max<size_t>(r.nodes.size(), 1) * 4);
@@ -253,14 +256,23 @@ extern "C" int b200rt_build_rbsp(const float *tri_verts, uint32_t n_prims, uint3
                                  uint32_t *out_node_count, uint32_t **out_prim_indices, uint32_t *out_n_indices,
                                  float out_bounds[6], float *out_directions, b200rt_build_stats *stats) {
     if (!out_directions || nb_directions == 0) return b200rt::set_error(B200RT_EINVAL, "b200rt_build_rbsp: null argument / nbDirections 0");
-    return build_on_device(tri_verts, n_prims, nb_directions, isect_cost, traversal_cost, empty_bonus, max_prims, max_depth,
+    return build_on_device(tri_verts, n_prims, nb_directions, -1, isect_cost, traversal_cost, empty_bonus, max_prims, max_depth,
                            out_nodes, out_node_count, out_prim_indices, out_n_indices, out_bounds, out_directions, stats);
+}
+
+extern "C" int b200rt_build_rbspkd(const float *tri_verts, uint32_t n_prims, uint32_t nb_directions, int isect_cost,
+                                   int traversal_cost, int kd_traversal_cost, float empty_bonus, int max_prims, int max_depth,
+                                   void **out_nodes, uint32_t *out_node_count, uint32_t **out_prim_indices,
+                                   uint32_t *out_n_indices, float out_bounds[6], float *out_directions, b200rt_build_stats *stats) {
+    if (!out_directions || nb_directions == 0 || kd_traversal_cost < 0) return b200rt::set_error(B200RT_EINVAL, "b200rt_build_rbspkd: bad argument");
+    return build_on_device(tri_verts, n_prims, nb_directions, kd_traversal_cost, isect_cost, traversal_cost, empty_bonus, max_prims,
+                           max_depth, out_nodes, out_node_count, out_prim_indices, out_n_indices, out_bounds, out_directions, stats);
 }
 
 extern "C" int b200rt_build_kdtree_device(const float *tri_verts, uint32_t n_prims, int isect_cost, int traversal_cost,
                                           float empty_bonus, int max_prims, int max_depth, void **out_nodes,
                                           uint32_t *out_node_count, uint32_t **out_prim_indices, uint32_t *out_n_indices,
                                           float out_bounds[6], b200rt_build_stats *stats) {
-    return build_on_device(tri_verts, n_prims, 0, isect_cost, traversal_cost, empty_bonus, max_prims, max_depth, out_nodes,
+    return build_on_device(tri_verts, n_prims, 0, -1, isect_cost, traversal_cost, empty_bonus, max_prims, max_depth, out_nodes,
                            out_node_count, out_prim_indices, out_n_indices, out_bounds, nullptr, stats);
 }

@@ -41,7 +41,12 @@ struct BuildParams {
     // node's BOX instead of a k-DOP: areas in closed form (:300-305), children's boxes by replacing one bound (:362-364),
     // the same 8-byte node layout (M = 3: two flag bits, leaf = 3).  No meshes, no EvalAreas pass.
     uint32_t kd;
+    // rbspkd = 1: RBSPKd::buildTree (src/accelerators/rbspKd.cpp:187-470): the axis-aligned directions (d < 3) are charged
+    // kdTraversalCost instead of traversalCost; the others BSP_ALPHA * isectCost * (n - 1) + kdTraversalCost, and a second
+    // arg-min over them with the plain traversalCost ("fixed") only feeds the bad-refine and leaf rules (:403-406).
+    uint32_t rbspkd, kdTraversalCost;
 };
+enum : uint32_t { kErrFixedOnly = 2 };   // rbspKd.cpp:417-428 indexes edges[-1] when only the "fixed" search found a plane
 
 enum : uint32_t { kLeaf = 0, kInterior = 1, kActive = 2 };
 enum : uint32_t { kErrMeshOverflow = 1 };
@@ -76,7 +81,7 @@ struct Level {
     KdopMesh *mesh = nullptr;
     uint32_t *kind = nullptr, *bestD = nullptr, *bestOff = nullptr, *childBelow = nullptr;
     float *split = nullptr;
-    uint64_t *best = nullptr;
+    uint64_t *best = nullptr, *bestFixed = nullptr;
     uint32_t *size = nullptr, *idxCount = nullptr, *pre = nullptr, *off = nullptr;
     uint32_t *refPrim = nullptr, *refNode = nullptr;
 };
@@ -135,6 +140,7 @@ struct InitNodeF {   // termination criteria, rbsp.cpp:258
     WF_HD void operator()(size_t k) const {
         L.kind[k] = (L.nPrims[k] <= P.maxPrims || L.depth[k] == 0) ? kLeaf : kActive;
         L.best[k] = ~0ull;
+        L.bestFixed[k] = ~0ull;
         if (P.kd) {   // Bounds3::SurfaceArea, geometry.h:946-949
             const float *b = L.bounds + (size_t)k * 6;
             const float dx = b[1] - b[0], dy = b[3] - b[2], dz = b[5] - b[4];
@@ -219,7 +225,21 @@ struct EvalCostF {   // rbsp.cpp:296-330 / kdtreeaccel.cpp:290-322 for one bound
         const uint32_t eb = endsBefore[i] - endsBefore[s];
         const uint32_t nAbove = L.nPrims[k] - eb - e, nBelow = il - eb;
         const float invTotalSA = 1 / L.area[k];
-        const float cost = sah_cost(P.traversalCost, P.isectCost, P.emptyBonus, aB, aA, invTotalSA, nBelow, nAbove);
+        float cost;
+        if (!P.rbspkd) {
+            cost = sah_cost(P.traversalCost, P.isectCost, P.emptyBonus, aB, aA, invTotalSA, nBelow, nAbove);
+        } else if (d < 3) {   // rbspKd.cpp:326-330
+            cost = sah_cost(P.kdTraversalCost, P.isectCost, P.emptyBonus, aB, aA, invTotalSA, nBelow, nAbove);
+        } else {              // rbspKd.cpp:379-385
+            const float pBelow = aB * invTotalSA, pAbove = aA * invTotalSA;
+            const float eb = (nAbove == 0 || nBelow == 0) ? P.emptyBonus : 0;
+            const float costIntersection = P.isectCost * (1 - eb) * (pBelow * nBelow + pAbove * nAbove);
+            const float costFixed = P.traversalCost + costIntersection;
+            const float BSP_ALPHA = 0.1;
+            cost = BSP_ALPHA * P.isectCost * (L.nPrims[k] - 1) + P.kdTraversalCost + costIntersection;
+            if (costFixed < wf_inf())
+                atomic_min_u64(L.bestFixed + k, ((uint64_t)float_order(costFixed + 0.0f) << 32) | ((uint64_t)d << 28) | il);
+        }
         if (!(cost < wf_inf())) return;   // `cost < bestCost` is false for NaN and for +inf
         atomic_min_u64(L.best + k, ((uint64_t)float_order(cost + 0.0f) << 32) | ((uint64_t)d << 28) | il);
     }
@@ -229,6 +249,7 @@ struct DecideF {   // rbsp.cpp:335-344
     Level L;
     BuildParams P;
     uint32_t *interior;   // K + 1 flags (the last one 0) for the scan that numbers the children
+    uint32_t *err;
     WF_HD void operator()(size_t k) const {
         interior[k] = 0;
         if (k >= L.K || L.kind[k] != kActive) return;
@@ -238,8 +259,17 @@ struct DecideF {   // rbsp.cpp:335-344
         const float oldCost = P.isectCost * float(n);
         const float bestCost = none ? wf_inf() : float_unorder((uint32_t)(b >> 32));
         uint32_t bad = L.bad[k];
-        if (bestCost > oldCost) ++bad;
-        if ((bestCost > 4 * oldCost && n < 16) || none || bad == 3) { L.kind[k] = kLeaf; return; }
+        if (P.rbspkd) {   // rbspKd.cpp:403-411
+            const uint64_t bf = L.bestFixed[k];
+            const bool noneFixed = bf == ~0ull;
+            const float bestCostFixed = noneFixed ? wf_inf() : float_unorder((uint32_t)(bf >> 32));
+            if (bestCost > oldCost && bestCostFixed > oldCost) ++bad;
+            if ((bestCost > 4 * oldCost && bestCostFixed > 4 * oldCost && n < 16) || (none && noneFixed) || bad == 3) { L.kind[k] = kLeaf; return; }
+            if (none) { *err = kErrFixedOnly; L.kind[k] = kLeaf; return; }
+        } else {
+            if (bestCost > oldCost) ++bad;
+            if ((bestCost > 4 * oldCost && n < 16) || none || bad == 3) { L.kind[k] = kLeaf; return; }
+        }
         L.kind[k] = kInterior;
         L.bad[k] = bad;
         L.bestD[k] = (uint32_t)(b >> 28) & 15u;

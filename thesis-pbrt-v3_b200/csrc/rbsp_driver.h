@@ -59,14 +59,14 @@ void alloc_level(B &be, Level &L, uint32_t K, uint32_t M, bool meshes = true) {
     L.mesh = be.template alloc<KdopMesh>(meshes ? K : 0);
     L.kind = be.template alloc<uint32_t>(K); L.bestD = be.template alloc<uint32_t>(K);
     L.bestOff = be.template alloc<uint32_t>(K); L.childBelow = be.template alloc<uint32_t>(K);
-    L.split = be.template alloc<float>(K); L.best = be.template alloc<uint64_t>(K);
+    L.split = be.template alloc<float>(K); L.best = be.template alloc<uint64_t>(K); L.bestFixed = be.template alloc<uint64_t>(K);
     L.size = be.template alloc<uint32_t>(K); L.idxCount = be.template alloc<uint32_t>(K);
     L.pre = be.template alloc<uint32_t>(K); L.off = be.template alloc<uint32_t>(K);
 }
 template <class B>
 void free_level(B &be, Level &L) {
     void *ps[] = {L.nPrims, L.depth, L.bad, L.refBase, L.area, L.bounds, L.mesh, L.kind, L.bestD, L.bestOff, L.childBelow,
-                  L.split, L.best, L.size, L.idxCount, L.pre, L.off, L.refPrim, L.refNode};
+                  L.split, L.best, L.bestFixed, L.size, L.idxCount, L.pre, L.off, L.refPrim, L.refNode};
     for (void *p : ps) be.free(p);
     L = Level();
 }
@@ -148,7 +148,7 @@ BuildResult build(B &be, const float *tris, uint32_t n, const BuildParams &P, co
 
         // leaf / interior, children numbered by a scan over the interior flags
         uint32_t *interior = be.template alloc<uint32_t>((size_t)L.K + 1), *rank = be.template alloc<uint32_t>((size_t)L.K + 1);
-        be.for_each((size_t)L.K + 1, DecideF{L, P, interior});
+        be.for_each((size_t)L.K + 1, DecideF{L, P, interior, err});
         be.exclusive_sum(interior, rank, (size_t)L.K + 1);
         uint32_t nInterior = 0;
         be.download(&nInterior, rank + L.K, 1);

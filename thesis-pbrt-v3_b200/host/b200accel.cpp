@@ -190,18 +190,24 @@ B200Accel::B200Accel(std::vector<std::shared_ptr<Primitive>> p, const ParamSet &
                                             &ownIdx, &nIdx, d.bounds, nullptr);
             d.kind = B200RT_KDTREE;
             d.n_directions = 3;
-        } else if (tree == "rbsp") {    // CreateRBSPTreeAccelerator (rbsp.cpp:549-570), built on the device
+        } else if (tree == "rbsp" || tree == "rbspkd") {   // CreateRBSP(Kd)TreeAccelerator (rbsp.cpp:549-570, rbspKd.cpp:640-665)
             const int M = ps.FindOneInt("nbDirections", 3);
             dirs.assign(3 * 16, 0.f);
-            rc = b200rt_build_rbsp(cap.verts.data(), (uint32_t)prims.size(), (uint32_t)M, ps.FindOneInt("intersectcost", 80),
-                                   ps.FindOneInt("traversalcost", 5), ps.FindOneFloat("emptybonus", 0.f),
-                                   ps.FindOneInt("maxprims", 1), ps.FindOneInt("maxdepth", -1), &ownNodes, &nNodes, &ownIdx,
-                                   &nIdx, d.bounds, dirs.data(), nullptr);
-            d.kind = B200RT_RBSP;
+            if (tree == "rbsp")
+                rc = b200rt_build_rbsp(cap.verts.data(), (uint32_t)prims.size(), (uint32_t)M, ps.FindOneInt("intersectcost", 80),
+                                       ps.FindOneInt("traversalcost", 5), ps.FindOneFloat("emptybonus", 0.f),
+                                       ps.FindOneInt("maxprims", 1), ps.FindOneInt("maxdepth", -1), &ownNodes, &nNodes, &ownIdx,
+                                       &nIdx, d.bounds, dirs.data(), nullptr);
+            else
+                rc = b200rt_build_rbspkd(cap.verts.data(), (uint32_t)prims.size(), (uint32_t)M, ps.FindOneInt("intersectcost", 80),
+                                         ps.FindOneInt("traversalcost", 5), ps.FindOneInt("kdtraversalcost", 1),
+                                         ps.FindOneFloat("emptybonus", 0.f), ps.FindOneInt("maxprims", 1),
+                                         ps.FindOneInt("maxdepth", -1), &ownNodes, &nNodes, &ownIdx, &nIdx, d.bounds, dirs.data(), nullptr);
+            d.kind = tree == "rbsp" ? B200RT_RBSP : B200RT_RBSPKD;
             d.directions = dirs.data();
             d.n_directions = (uint32_t)M;
         } else {
-            Error("b200: builder \"b200\" knows \"bvh\", \"kdtree\" and \"rbsp\"; \"%s\" needs the reference's builder", tree.c_str());
+            Error("b200: builder \"b200\" knows \"bvh\", \"kdtree\", \"rbsp\" and \"rbspkd\"; \"%s\" needs the reference's builder", tree.c_str());
             return;
         }
         if (rc) { Error("b200: %s", b200rt_last_error()); return; }
