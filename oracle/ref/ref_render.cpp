@@ -35,6 +35,7 @@
 #include "materials/glass.h"
 #include "materials/metal.h"
 #include "materials/substrate.h"
+#include "materials/uber.h"
 #include "samplers/halton.h"
 #include "samplers/sobol.h"
 #include "samplers/random.h"
@@ -230,6 +231,12 @@ extern "C" int ref_render_get_camera_matrix(float *w2c16) {
     return g_camMatrix ? 1 : 0;
 }
 
+// floats per prim_mat record for the NEXT renders: 8 (default) or 20 (the device's long record, which adds Material "uber":
+// [0] = 6 (+32: remaproughness false), Kd 1-3, Ks 4-6, roughness 7, Kr 8-10, Kt 11-13, opacity 14-16, eta 17)
+static int g_matStride = 8;
+extern "C" void ref_render_set_mat_stride(int n) { g_matStride = n == 20 ? 20 : 8; }
+extern "C" int ref_render_get_mat_stride(void) { return g_matStride; }
+
 // Film "float cropwindow" [x0 x1 y0 y1] for the NEXT renders (NULL = whole frame); out_rgb / out_heat then hold the
 // window's pixels only (Film::croppedPixelBounds, film.cpp:49-57).
 static float g_crop[4] = {0.f, 1.f, 0.f, 1.f};
@@ -266,13 +273,13 @@ extern "C" int ref_render(ref_scene *s, const char *accel_kind, const float *cam
     MediumInterface mi;
     std::vector<std::shared_ptr<Primitive>> prims;
     std::shared_ptr<AreaLight> area;
-    std::map<std::array<float, 8>, std::shared_ptr<Material>> byKd;   // one Material per distinct record
+    std::map<std::array<float, 20>, std::shared_ptr<Material>> byKd;   // one Material per distinct record
     for (size_t i = 0; i < s->prims.size(); ++i) {
         auto *gp = static_cast<GeometricPrimitive *>(s->prims[i].get());
         std::shared_ptr<Material> m = matte;
         if (prim_mat) {
-            std::array<float, 8> k;
-            std::memcpy(k.data(), prim_mat + 8 * i, sizeof(float) * 8);
+            std::array<float, 20> k{};
+            std::memcpy(k.data(), prim_mat + (size_t)g_matStride * i, sizeof(float) * g_matStride);
             auto it = byKd.find(k);
             if (it == byKd.end()) {
                 Float c[3] = {k[1], k[2], k[3]}, cs[3] = {k[4], k[5], k[6]};
@@ -292,6 +299,15 @@ extern "C" int ref_render(ref_scene *s, const char *accel_kind, const float *cam
                     auto texS = std::make_shared<ConstantTexture<Spectrum>>(Spectrum::FromRGB(cs));
                     auto rough = std::make_shared<ConstantTexture<Float>>(k[7]);
                     mm = std::make_shared<SubstrateMaterial>(tex, texS, rough, rough, nullptr, remap);
+                } else if (kind == 6) {   // Material "uber" (materials/uber.cpp:102-128): constant textures, isotropic roughness
+                    Float cr[3] = {k[8], k[9], k[10]}, ct[3] = {k[11], k[12], k[13]}, co[3] = {k[14], k[15], k[16]};
+                    auto texS = std::make_shared<ConstantTexture<Spectrum>>(Spectrum::FromRGB(cs));
+                    auto texR = std::make_shared<ConstantTexture<Spectrum>>(Spectrum::FromRGB(cr));
+                    auto texT = std::make_shared<ConstantTexture<Spectrum>>(Spectrum::FromRGB(ct));
+                    auto texO = std::make_shared<ConstantTexture<Spectrum>>(Spectrum::FromRGB(co));
+                    auto rough = std::make_shared<ConstantTexture<Float>>(k[7]);
+                    auto eta = std::make_shared<ConstantTexture<Float>>(k[17]);
+                    mm = std::make_shared<UberMaterial>(tex, texS, texR, texT, rough, nullptr, nullptr, texO, eta, nullptr, remap);
                 } else if (kind == 2) {   // Material "mirror" "color Kr" (materials/mirror.cpp:58-63)
                     mm = std::make_shared<MirrorMaterial>(tex, nullptr);
                 } else if (kind == 3) {   // Material "glass" "color Kr" "color Kt" "float index" (materials/glass.cpp:97-110), roughness 0

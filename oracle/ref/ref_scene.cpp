@@ -121,6 +121,20 @@ extern "C" int ref_loopsubdiv_normals(float *out) {
     return (int)(g_lastSubdivN.size() / 3);
 }
 
+// Transform::operator()(Normal3f) of the Transform pbrtTransform builds from a row-major 4x4 (its inverse computed by the
+// reference's own Inverse()), i.e. what TriangleMesh's constructor applies to a plymesh's normals (triangle.cpp:61-64); and
+// Transform::SwapsHandedness (transform.cpp:238-243).  Used by tests/golden/make_living_room.py.
+extern "C" int ref_transform_normals(const float *m16, const float *N, int n, float *out) {
+    Matrix4x4 m(m16[0], m16[1], m16[2], m16[3], m16[4], m16[5], m16[6], m16[7], m16[8], m16[9], m16[10], m16[11], m16[12],
+                m16[13], m16[14], m16[15]);
+    Transform t(m);
+    for (int i = 0; i < n; ++i) {
+        const Normal3f r = t(Normal3f(N[3 * i], N[3 * i + 1], N[3 * i + 2]));
+        out[3 * i] = r.x; out[3 * i + 1] = r.y; out[3 * i + 2] = r.z;
+    }
+    return t.SwapsHandedness() ? 1 : 0;
+}
+
 extern "C" ref_accel *ref_accel_create(ref_scene *s, const char *kind, const char *const *int_names,
                                        const int *int_vals, const char *const *float_names,
                                        const float *float_vals) {

@@ -223,7 +223,13 @@ def render(scene, accel_kind, eye, look, up, fov, xres, yres, spp, maxdepth, lig
     out = np.zeros((ch_, cw_, 3), np.float32)
     nc, ns, secs = C.c_uint64(), C.c_uint64(), C.c_double()
     hm = np.zeros((6, ch_, cw_), np.uint32) if heat else None
-    pk = None if prim_mat is None else np.ascontiguousarray(prim_mat, np.float32).reshape(-1, 8)
+    pk = None if prim_mat is None else np.ascontiguousarray(prim_mat, np.float32)
+    if pk is not None:   # 8-float records, or the device's 20-float records (adds Material "uber")
+        assert pk.ndim == 2 and pk.shape[1] in (8, 20), pk.shape
+        if hasattr(scene.L, "ref_render_set_mat_stride"):
+            scene.L.ref_render_set_mat_stride(int(pk.shape[1]))
+        elif pk.shape[1] != 8:
+            raise RuntimeError("libpbrtref.so predates ref_render_set_mat_stride: rebuild oracle/ref")
     el = None if emitter_L is None else np.ascontiguousarray(emitter_L, np.float32)
     if hasattr(scene.L, "ref_render_set_distant"):   # distant=(from, to): LightSource "distant" with L = light_I
         scene.L.ref_render_set_distant.argtypes = [C.c_void_p]

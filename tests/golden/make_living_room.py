@@ -36,7 +36,7 @@ def read_ply(path):
         elif t and t[0] == "property":
             cur["props"].append(t[1:])
     off = end
-    P = UV = faces = None
+    P = UV = faces = N = None
     for e in elems:
         if e["name"] == "vertex":
             names = [p[-1] for p in e["props"]]
@@ -45,6 +45,7 @@ def read_ply(path):
             off += a.nbytes
             P = a[:, [names.index(c) for c in "xyz"]].copy()
             UV = a[:, [names.index("u"), names.index("v")]].copy() if "u" in names else np.zeros((e["n"], 2), np.float32)
+            N = a[:, [names.index(c) for c in ("nx", "ny", "nz")]].copy() if "nx" in names else None
         elif e["name"] == "face":
             assert e["props"] == [["list", "uint8", "int", "vertex_indices"]], e["props"]
             tris = []
@@ -59,7 +60,22 @@ def read_ply(path):
                     tris.append(f[[3, 0, 2]])
             faces = np.asarray(tris, np.int32)
     assert off == len(raw), (path, off, len(raw))
-    return P, UV, faces
+    return P, UV, faces, N
+
+
+def xform_normals(m, N):
+    """TriangleMesh's `n[i] = ObjectToWorld(N[i])` (triangle.cpp:61-64) through the reference's own Transform (its Inverse()
+    and operator()(Normal3f)); also returns Transform::SwapsHandedness()."""
+    import ctypes as C
+    sys.path.insert(0, os.path.dirname(os.path.dirname(HERE)))
+    from oracle import refbind as rb
+    L = rb.lib()
+    L.ref_transform_normals.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
+    m32 = np.ascontiguousarray(m, np.float32)
+    N = np.ascontiguousarray(N, np.float32)
+    out = np.zeros_like(N)
+    swaps = L.ref_transform_normals(m32.ctypes.data, N.ctypes.data, len(N), out.ctypes.data)
+    return out, bool(swaps)
 
 
 def xform32(m, P):
@@ -85,7 +101,7 @@ def main():
         mats[name] = dict(kind=kind, kd=[float(v) for v in kd.groups()] if kd else None, tex=tex.group(1) if tex else "")
         order.append(name)
     ctm, stack, cur = np.eye(4), [], None
-    Ps, UVs, Is, Ms, meshes = [], [], [], [], []
+    Ps, UVs, Is, Ms, meshes, Ns, Fl = [], [], [], [], [], [], []
     base = 0
     for ln in world.splitlines():
         t = ln.strip()
@@ -100,7 +116,11 @@ def main():
             cur = re.search(r'"([^"]+)"', t).group(1)
         elif t.startswith("Shape"):
             f = re.search(r'"string filename" \[ "([^"]+)" \]', t).group(1)
-            P, UV, F = read_ply(os.path.join(REF, f))
+            P, UV, F, N = read_ply(os.path.join(REF, f))
+            Nw, swaps = xform_normals(ctm, N if N is not None else np.zeros_like(P))
+            Ns.append(Nw if N is not None else np.zeros_like(P))
+            # bit 1: the mesh has normals; bit 0: transformSwapsHandedness (no ReverseOrientation in the file)
+            Fl.append(np.full(len(F), (2 if N is not None else 0) | (1 if swaps else 0), np.uint8))
             Ps.append(xform32(ctm, P))
             UVs.append(UV)
             Is.append(F + base)
@@ -108,10 +128,12 @@ def main():
             meshes.append(f)
             base += len(P)
     P, UV, I, M = np.concatenate(Ps), np.concatenate(UVs), np.concatenate(Is), np.concatenate(Ms)
+    Nall, flags = np.concatenate(Ns), np.concatenate(Fl)
+    print("meshes whose transform swaps handedness:", sum(int(f[0] & 1) for f in Fl), "of", len(Fl))
     print("meshes", len(meshes), "vertices", len(P), "triangles", len(I))
     assert len(I) == 143163, len(I)   # SURVEY.md §6.2 (the reference's own count for this scene)
     cam = re.search(r"^Transform \[([^\]]+)\]", txt, re.M).group(1).split()
-    np.savez_compressed(os.path.join(HERE, "living_room_mesh.npz"), P=P, UV=UV, idx=I, tri_material=M,
+    np.savez_compressed(os.path.join(HERE, "living_room_mesh.npz"), P=P, UV=UV, idx=I, tri_material=M, N=Nall, tri_flags=flags,
                         material_names=np.array(order), material_kinds=np.array([mats[n]["kind"] for n in order]),
                         material_kd=np.array([mats[n]["kd"] or [-1, -1, -1] for n in order], np.float32),
                         material_tex=np.array([mats[n]["tex"] for n in order]),

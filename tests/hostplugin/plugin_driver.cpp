@@ -106,6 +106,7 @@ extern "C" int plugin_intersect_p_batch(const ref_accel *a, const float *rays, u
 #include "materials/glass.h"
 #include "materials/metal.h"
 #include "materials/substrate.h"
+#include "materials/uber.h"
 #include "lights/diffuse.h"
 #include "lights/distant.h"
 #include "core/sampling.h"
@@ -120,6 +121,7 @@ extern "C" int ref_last_image(float *out_rgb, int *xres, int *yres);
 extern "C" int ref_render_get_distant(float *from_to);
 extern "C" int ref_render_get_infinite(float *L_rgb, float *l2w16);      // set through ref_render_set_infinite
 extern "C" int ref_render_get_camera_matrix(float *w2c16);             // set through ref_render_set_camera_matrix
+extern "C" int ref_render_get_mat_stride(void);             // set through ref_render_set_mat_stride: 8 or 20 floats per record
 extern "C" void ref_render_get_crop(float *cw);           // set through ref_render_set_crop   // set through ref_render_set_distant (oracle/ref/ref_render.cpp)
 std::shared_ptr<pbrt::Shape> shape_of(const pbrt::Primitive *p);   // plugin_shape_of.cpp (GeometricPrimitive::shape is private)
 
@@ -142,13 +144,14 @@ extern "C" int plugin_render(ref_scene *s, const char *tree, const float *cam, i
     MediumInterface mi;
     std::vector<std::shared_ptr<Primitive>> prims;
     std::shared_ptr<AreaLight> area;
-    std::map<std::array<float, 8>, std::shared_ptr<Material>> byRec;
+    std::map<std::array<float, 20>, std::shared_ptr<Material>> byRec;
+    const int stride = ref_render_get_mat_stride();
     for (size_t i = 0; i < s->prims.size(); ++i) {
         std::shared_ptr<Shape> shape = shape_of(s->prims[i].get());
         std::shared_ptr<Material> m = matte;
         if (prim_mat) {
-            std::array<float, 8> k;
-            std::memcpy(k.data(), prim_mat + 8 * i, sizeof(float) * 8);
+            std::array<float, 20> k{};
+            std::memcpy(k.data(), prim_mat + (size_t)stride * i, sizeof(float) * stride);
             auto it = byRec.find(k);
             if (it == byRec.end()) {
                 Float c[3] = {k[1], k[2], k[3]}, cs[3] = {k[4], k[5], k[6]};
@@ -162,7 +165,13 @@ extern "C" int plugin_render(ref_scene *s, const char *tree, const float *cam, i
                 else if (kind == 4) mm = std::make_shared<MetalMaterial>(tex, texS, rough, nullptr, nullptr, nullptr, remap);
                 else if (kind == 5) mm = std::make_shared<SubstrateMaterial>(tex, texS, rough, rough, nullptr, remap);
                 else if (kind == 2) mm = std::make_shared<MirrorMaterial>(tex, nullptr);
-                else if (kind == 3)
+                else if (kind == 6) {   // Material "uber": Kr 8-10, Kt 11-13, opacity 14-16, eta 17
+                    Float cr[3] = {k[8], k[9], k[10]}, ct[3] = {k[11], k[12], k[13]}, co[3] = {k[14], k[15], k[16]};
+                    mm = std::make_shared<UberMaterial>(tex, texS, std::make_shared<ConstantTexture<Spectrum>>(Spectrum::FromRGB(cr)),
+                                                        std::make_shared<ConstantTexture<Spectrum>>(Spectrum::FromRGB(ct)), rough, nullptr, nullptr,
+                                                        std::make_shared<ConstantTexture<Spectrum>>(Spectrum::FromRGB(co)),
+                                                        std::make_shared<ConstantTexture<Float>>(k[17]), nullptr, remap);
+                } else if (kind == 3)
                     mm = std::make_shared<GlassMaterial>(tex, std::make_shared<ConstantTexture<Spectrum>>(Spectrum::FromRGB(cs)),
                                                          std::make_shared<ConstantTexture<Float>>(0.f), std::make_shared<ConstantTexture<Float>>(0.f),
                                                          std::make_shared<ConstantTexture<Float>>(k[7]), nullptr, true);

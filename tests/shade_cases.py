@@ -57,9 +57,21 @@ def build(name, res=48):
             mats = scenes.metal_materials(sc)
         elif kind == "oren":
             mats = scenes.metal_materials(sc, oren_nayar=True)
+        elif kind == "uber":
+            # Material "uber" (materials/uber.cpp:45-100; scenes/living-room uses it): 20-float records.  Ground: every lobe at
+            # once (diffuse + glossy + specular reflection + specular transmission), opaque; first killeroo: opacity .6, so the
+            # pass-through SpecularTransmission(1 - opacity, 1, 1) lobe comes first and eta becomes 1; second: glossy + diffuse
+            # with "remaproughness" false
+            m20 = np.zeros((len(mats), 20), np.float32)
+            m20[:, :8] = mats
+            m20[0] = [6, .5, .5, .8, .25, .25, .25, .1, .1, .1, .1, .05, .05, .05, 1, 1, 1, 1.5, 0, 0]
+            m20[1] = [6, .4, .2, .2, .3, .3, .3, .05, 0, 0, 0, .3, .3, .3, .6, .6, .6, 1.3, 0, 0]
+            m20[2] = [6 + 32, .25, .25, .25, .25, .25, .25, .1, 0, 0, 0, 0, 0, 0, 1, 1, 1, 1.5, 0, 0]
+            mats = m20
+            out["maxdepth"] = 8
         tv = sc["tri_verts"]
         sl = sc["sphere_light"]
-        prim_mat = np.concatenate([mats[sc["prim_material"]], np.zeros((1, 8), np.float32)])
+        prim_mat = np.concatenate([mats[sc["prim_material"]], np.zeros((1, mats.shape[1]), np.float32)])
         spheres = np.array([list(sl["center"]) + [sl["radius"]]], np.float32)
         render = dict(eye=eye, look=look, up=up, fov=fov, light_pos=sl["center"], light_I=sl["L"], kd=(.5, .5, .5), prim_mat=prim_mat)
         integ = dict(camera=sc["camera"], light_pos=sl["center"], light_I=sl["L"], materials=mats, prim_material=pm)
@@ -106,6 +118,29 @@ def build(name, res=48):
                               distant_light=(sc["light_dir"], wf.world_radius(tv)), crop=sc["crop"]),
                    accel=(tv, {}), res=res * 4)
         return out
+    if name == "living_room":
+        # BASELINE config 5, scenes/living-room as the reference resolves it (b200rt.scenes.living_room): the file's camera CTM,
+        # its infinite light (constant: the sky map is absent), maxdepth 65, the file's matte / Oren-Nayar / substrate / metal /
+        # glass / mirror / uber materials and the PLY vertex normals.  The reference harness builds ONE mesh, so the 3 008
+        # triangles whose PLY has no normals carry zero normals on both sides (ns falls back to n, triangle.cpp:352-355).
+        import os
+        from b200rt import wavefront as wf
+        sc = scenes.living_room(res, res)
+        z = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "living_room_mesh.npz"))
+        tv = sc["tri_verts"]
+        il = sc["infinite_light"]
+        l2w = np.eye(4, dtype=np.float32)
+        l2w[:3, :3] = il["light_to_world"]
+        L = tuple(float(v) for v in il["L"])
+        out.update(ref=dict(P=z["P"], indices=z["idx"], uv=z["UV"], normals=z["N"]),
+                   render=dict(eye=(0, 0, 0), look=(0, 0, 1), up=(0, 1, 0), fov=sc["camera"]["fov"], light_pos=(0, 0, 0), light_I=L,
+                               kd=(.5, .5, .5), prim_mat=sc["materials"][sc["prim_material"]], infinite=(L, l2w),
+                               camera_matrix=sc["camera"]["world_to_camera"]),
+                   integ=dict(camera=sc["camera"], light_I=L, infinite_light=(il["light_to_world"], wf.world_radius(tv)),
+                              materials=sc["materials"], prim_material=sc["prim_material"]),
+                   accel=(tv, dict(tri_uvs=sc["tri_uvs"], tri_normals=sc["tri_normals"], prim_flags=np.full(len(tv), 2, np.uint8))),
+                   mis=True, infinite_scene=True, maxdepth=sc["maxdepth"])
+        return out
     if name in ("normals", "normals_flipped"):
         # vertex normals (interpolated shading normal, triangle.cpp:348-400), a real (u, v) parameterisation (dpdu frame) and,
         # for normals_flipped, `ReverseOrientation`; two-lobe plastic so that the frame matters for both lobes
@@ -128,5 +163,5 @@ def build(name, res=48):
     raise KeyError(name)
 
 
-CASES = ["sponza_point", "killeroo_plastic", "killeroo_normals", "killeroo_glass", "killeroo_metal", "killeroo_oren", "killeroo_infinite",
-         "feet_distant", "normals", "normals_flipped"]
+CASES = ["sponza_point", "killeroo_plastic", "killeroo_normals", "killeroo_glass", "killeroo_metal", "killeroo_oren", "killeroo_uber", "killeroo_infinite",
+         "feet_distant", "normals", "normals_flipped", "living_room"]

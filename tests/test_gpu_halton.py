@@ -42,9 +42,9 @@ def _device_queues(gpu, c, spp, sampler):
 
 
 @pytest.mark.parametrize("case,sampler", [("sponza_point", "halton"), ("killeroo_plastic", "halton"), ("killeroo_normals", "halton"), ("killeroo_glass", "halton"),
-                                          ("killeroo_metal", "halton"), ("killeroo_oren", "halton"), ("killeroo_infinite", "halton"),
+                                          ("killeroo_metal", "halton"), ("killeroo_oren", "halton"), ("killeroo_uber", "halton"), ("killeroo_infinite", "halton"),
                                           ("feet_distant", "halton"), ("normals", "halton"), ("normals_flipped", "halton"),
-                                          ("killeroo_metal", "sobol"), ("feet_distant", "sobol")])
+                                          ("killeroo_metal", "sobol"), ("feet_distant", "sobol"), ("living_room", "sobol")])
 def test_device_rays_are_the_references(gpu, case, sampler):
     import hostwf
     from b200rt import wavefront as wf
@@ -84,6 +84,10 @@ IMAGE_CASES = {
     "feet_distant": dict(res=320, spp=8),
     "killeroo_glass": dict(res=256, spp=8),
     "killeroo_metal": dict(res=256, spp=8),
+    "killeroo_uber": dict(res=256, spp=8),
+    # BASELINE config 5: scenes/living-room as the reference resolves it (the file's Sampler "sobol", maxdepth 65, infinite light,
+    # its material table incl. "uber", the PLY vertex normals), square frame
+    "living_room": dict(res=256, spp=16, sampler="sobol"),
 }
 
 
@@ -102,8 +106,8 @@ def test_image_is_the_references_halton_render(gpu, case):
     r = dict(c["render"])
     rres = c.get("res", p["res"])
     img, nc, ns = rb.render(S, "bvh", r.pop("eye"), r.pop("look"), r.pop("up"), r.pop("fov"), rres, rres, p["spp"], c["maxdepth"],
-                            r.pop("light_pos"), r.pop("light_I"), r.pop("kd"), sampler="halton", n_threads=0, **r)
-    integ = gpu.WavefrontPathIntegrator(spp=p["spp"], maxdepth=c["maxdepth"], sampler="halton", **c["integ"])
+                            r.pop("light_pos"), r.pop("light_I"), r.pop("kd"), sampler=p.get("sampler", "halton"), n_threads=0, **r)
+    integ = gpu.WavefrontPathIntegrator(spp=p["spp"], maxdepth=c["maxdepth"], sampler=p.get("sampler", "halton"), **c["integ"])
     film, st = integ.Render(_accel(gpu, c))
     im = hostwf.image_stats(wf.film_to_rgb(film), img)
     print("\n%s %dx%d @ %d spp: rays dev %d/%d ref %d/%d; %s" % (case, img.shape[1], img.shape[0], p["spp"], st["closest_rays"],

@@ -10,11 +10,12 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, os.path.join(ROOT, "thesis-pbrt-v3_b200"))
 from b200rt import scenes  # noqa: E402
 
-KINDS = {0: "matte", 1: "plastic", 2: "mirror", 3: "glass", 4: "metal", 5: "substrate"}
+KINDS = {0: "matte", 1: "plastic", 2: "mirror", 3: "glass", 4: "metal", 5: "substrate", 6: "uber"}
 
 
 def _check_records(m):
-    m = np.asarray(m, np.float32).reshape(-1, 8)
+    m = np.asarray(m, np.float32)
+    assert m.ndim == 2 and m.shape[1] in (8, 20)     # material_stride: the short record, or the long one "uber" needs
     for r in m:
         kf = int(r[0])
         assert kf == r[0] and 0 <= kf < 64 and (kf & 15) in KINDS, r
@@ -27,6 +28,8 @@ def _check_records(m):
             assert (r[1:4] >= 0).all() and (r[1:4] <= 1).all()
         if kind == 0:
             assert 0 <= r[4] <= 90   # sigma in degrees
+        if kind == 6:
+            assert len(r) == 20 and r[7] > 0 and r[17] > 0 and (r[8:17] >= 0).all() and (r[8:17] <= 1).all()   # Kr, Kt, opacity; eta
 
 
 def test_museum_standin_is_deterministic_and_holds_the_templates_camera():
@@ -64,8 +67,11 @@ def test_living_room_materials_are_the_files_kinds():
     kinds = dict(zip(lr["material_names"], lr["materials"][:, 0].astype(int)))
     assert kinds["Mirror"] == 2 and kinds["FireplaceGlass"] == 2 and kinds["Glass"] == 3
     assert kinds["BrushedStainlessSteel"] == 4 + 32 and kinds["Paneling"] == 5 + 32 and kinds["Floor"] == 5 + 32
-    assert kinds["Sofa"] == 0 and kinds["Leaves"] == 0
+    assert kinds["Sofa"] == 0 and kinds["Leaves"] == 6      # scene.pbrt:29 "string type" [ "uber" ]
     names = lr["material_names"]
+    # textures/wood.tga and wood5.tga are absent from the reference tree: the reference resolves their Kd to the constant 1
+    assert (lr["materials"][names.index("Floor"), 1:4] == 1).all() and (lr["materials"][names.index("TableWood"), 1:4] == 1).all()
+    assert lr["tri_normals"].shape == (143163, 9) and np.bincount(lr["prim_flags"]).tolist() == [3008, 0, 140155]
     assert lr["materials"][names.index("PlantPot"), 4] == 1          # scene.pbrt:26 "float sigma" [1]
     assert np.allclose(lr["materials"][names.index("BrushedStainlessSteel"), 1:8],
                        [1.657460, 0.880369, 0.521229, 9.223869, 6.269523, 4.837001, .02])   # scene.pbrt:21

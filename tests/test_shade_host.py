@@ -45,13 +45,13 @@ def test_camera_matrices_equal_the_reference_cameras(built_lib):
     assert np.array_equal(np.array(d.camera_to_world, np.float32).view(np.uint32), c2w.ravel().view(np.uint32))
 
 
-@pytest.mark.parametrize("case", ["sponza_point", "killeroo_plastic", "killeroo_normals", "killeroo_glass", "killeroo_metal", "killeroo_oren",
-                                  "killeroo_infinite", "feet_distant", "normals", "normals_flipped"])
+@pytest.mark.parametrize("case", ["sponza_point", "killeroo_plastic", "killeroo_normals", "killeroo_glass", "killeroo_metal", "killeroo_oren", "killeroo_uber",
+                                  "killeroo_infinite", "feet_distant", "normals", "normals_flipped", "living_room"])
 def test_every_sample_and_every_ray_is_the_references(built_lib, case):
     _check_case(built_lib, case, "halton")
 
 
-@pytest.mark.parametrize("case", ["sponza_point", "killeroo_metal", "feet_distant"])
+@pytest.mark.parametrize("case", ["sponza_point", "killeroo_metal", "feet_distant", "living_room"])
 def test_sobol_stream_is_the_references(built_lib, case):
     """Sampler "sobol" (scenes/living-room/scene.pbrt:3): SobolIntervalToIndex + SobolSampleFloat over the reference's
     generator matrices (b200rt/data/sobol_tables.npz), incl. the pixel-relative remap of dimensions 0 / 1 and a crop window."""

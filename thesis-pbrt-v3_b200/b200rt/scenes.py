@@ -290,46 +290,57 @@ def living_room(xres=1280, yres=720):
     Light: `LightSource "infinite" "string mapname" "textures/Sky 19.pfm"` under the file's rotation; the map is NOT in
     the reference tree, so the reference itself falls back to a constant radiance L = 1 (infinite.cpp:52-60) — that is
     what `infinite_light` describes.
-    Materials: the file uses matte (88 114 triangles), substrate, glass, metal, uber and mirror, some with image textures
-    (two of the four texture files are absent too).  `materials` follows the file's MakeNamedMaterial table
-    (scene.pbrt:13-31) with the shade stage's own kinds: matte keeps its Kd; substrate = "substrate" (its Kd, Ks .04,
-    u = v roughness, "remaproughness" false); "metal" with the file's eta / k and roughness .02 unremapped; "glass"
-    index 1.5 (Kr = Kt = 1, glass.cpp's defaults); "mirror" Kr .9 (mirror.cpp's default).  What stays SUBSTITUTED,
-    identically on the reference side of the parity test: texture-mapped Kd -> constant .5 (image textures are out of
-    scope and half the files are absent), "uber" Leaves (Ks 0, opacity texture) -> matte .5, and the PLY files' vertex normals are not used (geometric normals on both sides; for glass the outside
-    is the side the triangle's winding normal points to).  `legacy_materials` keeps the earlier matte + plastic table
-    (the numbers of profiles/r01_living_room_*.json).  The TRAVERSAL workload (tree, rays, hit parity) is the reference
-    scene's as shipped."""
+    Materials: the file uses matte (88 114 triangles), substrate, glass, metal, uber and mirror, some with image textures.
+    `materials` (20-float records) follows the file's MakeNamedMaterial table (scene.pbrt:13-31) with the shade stage's own
+    kinds: matte keeps its Kd (PlantPot: sigma 1, Oren-Nayar); substrate = "substrate" (its Kd, Ks .04, u = v roughness,
+    "remaproughness" false); "metal" with the file's eta / k and roughness .02 unremapped; "glass" index 1.5 (Kr = Kt = 1,
+    glass.cpp's defaults); "mirror" Kr .9 (mirror.cpp's default); "uber" (Leaves: Ks 0, uber.cpp's defaults for the rest).
+    Image textures (`imagemap` is not built): textures/wood.tga and wood5.tga are ABSENT from the reference tree, so the
+    reference itself resolves Floor's and TableWood's Kd to the constant 1 (imagemap.cpp:67-71) and so does this table; the
+    two files that are there (picture8.tga on the Painting's 2 triangles, leaf.tga as Kd and opacity of the Leaves' 3 264) are
+    SUBSTITUTED by the constants .5 (Kd) and 1 (opacity), identically on the reference side of the parity test.
+    `tri_normals` / `prim_flags`: the PLY files' vertex normals in world space (TriangleMesh applies ObjectToWorld to them,
+    triangle.cpp:61-64; 140 155 triangles have them, 3 008 do not), interpolated shading normals as triangle.cpp:348-400.
+    `legacy_materials` keeps the round-1 matte + plastic table (the numbers of profiles/r01_living_room_*.json).  The TRAVERSAL
+    workload (tree, rays, hit parity) is the reference scene's as shipped."""
     z = np.load(os.path.join(_GOLDEN, "living_room_mesh.npz"))
     P, UV, idx = z["P"], z["UV"], z["idx"]
     tv = P[idx].reshape(-1, 9).astype(np.float32) + np.float32(0)
     uv = UV[idx].reshape(-1, 6).astype(np.float32)
     kinds, kd = [str(k) for k in z["material_kinds"]], z["material_kd"]
     rough = {"Floor": .15, "TableWood": .05, "Paneling": .2}   # scene.pbrt:13,14,18 ("remaproughness" false in the file)
-    mats = np.zeros((len(kinds), 8), np.float32)
+    absent = {"Texture01", "Texture02"}   # textures/wood.tga, wood5.tga: not in the reference tree -> the constant 1
+    mats = np.zeros((len(kinds), 20), np.float32)
     legacy = np.zeros((len(kinds), 8), np.float32)
     for i, (k, name) in enumerate(zip(kinds, [str(n) for n in z["material_names"]])):
-        c = kd[i] if kd[i][0] >= 0 else np.array([.5, .5, .5], np.float32)
+        tex = str(z["material_tex"][i])
+        c = kd[i] if kd[i][0] >= 0 else np.array([1, 1, 1] if tex in absent else [.5, .5, .5], np.float32)
+        cl = kd[i] if kd[i][0] >= 0 else np.array([.5, .5, .5], np.float32)
         legacy[i] = [0, .5, .5, .5, 0, 0, 0, 0]
         if k == "substrate":
-            mats[i] = [5 + 32, c[0], c[1], c[2], .04, .04, .04, rough[name]]
-            legacy[i] = [1, c[0], c[1], c[2], .04, .04, .04, rough[name]]
+            mats[i, :8] = [5 + 32, c[0], c[1], c[2], .04, .04, .04, rough[name]]
+            legacy[i] = [1, cl[0], cl[1], cl[2], .04, .04, .04, rough[name]]
         elif k == "matte":
-            mats[i] = legacy[i] = [0, c[0], c[1], c[2], 0, 0, 0, 0]
+            mats[i, :8] = [0, c[0], c[1], c[2], 0, 0, 0, 0]
+            legacy[i] = [0, cl[0], cl[1], cl[2], 0, 0, 0, 0]
             if name == "PlantPot":   # scene.pbrt:26 "float sigma" [1]: Oren-Nayar
-                mats[i] = [0, c[0], c[1], c[2], 1, 0, 0, 0]
+                mats[i, :8] = [0, c[0], c[1], c[2], 1, 0, 0, 0]
         elif k == "metal":     # scene.pbrt:21 BrushedStainlessSteel
-            mats[i] = [4 + 32, 1.657460, 0.880369, 0.521229, 9.223869, 6.269523, 4.837001, .02]
+            mats[i, :8] = [4 + 32, 1.657460, 0.880369, 0.521229, 9.223869, 6.269523, 4.837001, .02]
         elif k == "glass":     # scene.pbrt:25
-            mats[i] = [3, 1, 1, 1, 1, 1, 1, 1.5]
+            mats[i, :8] = [3, 1, 1, 1, 1, 1, 1, 1.5]
         elif k == "mirror":    # scene.pbrt:20,27
-            mats[i] = [2, .9, .9, .9, 0, 0, 0, 0]
+            mats[i, :8] = [2, .9, .9, .9, 0, 0, 0, 0]
+        elif k == "uber":      # scene.pbrt:29 Leaves: Ks 0; uber.cpp:102-128 defaults Kr 0, Kt 0, roughness .1, eta 1.5, opacity 1
+            mats[i] = [6, c[0], c[1], c[2], 0, 0, 0, .1, 0, 0, 0, 0, 0, 0, 1, 1, 1, 1.5, 0, 0]
         else:
-            mats[i] = [0, .5, .5, .5, 0, 0, 0, 0]
+            raise ValueError("scenes/living-room material kind %r" % k)
     # TransformBegin Transform [-1 0 8.74228e-008 0  -8.74228e-008 0 -1 0  0 1 0 0  0 0 0 1] LightSource "infinite"
     # (scene.pbrt:163-166; column-major in the file) -> row-major LightToWorld rotation
     l2w = np.array([-1, 0, 8.74228e-008, 0, -8.74228e-008, 0, -1, 0, 0, 1, 0, 0, 0, 0, 0, 1], np.float64).reshape(4, 4).T[:3, :3]
-    return dict(name="living-room", tri_verts=tv, tri_uvs=uv, camera=matrix_camera(z["world_to_camera"], 58.715508, xres, yres),
+    tn = z["N"][idx].reshape(-1, 9).astype(np.float32)
+    return dict(name="living-room", tri_verts=tv, tri_uvs=uv, tri_normals=tn, prim_flags=z["tri_flags"].astype(np.uint8),
+                camera=matrix_camera(z["world_to_camera"], 58.715508, xres, yres),
                 materials=mats, legacy_materials=legacy, prim_material=z["tri_material"].astype(np.uint8), material_names=[str(n) for n in z["material_names"]],
                 material_kinds=kinds, infinite_light=dict(L=np.array([1, 1, 1], np.float32), light_to_world=l2w),
                 maxdepth=65, spp=64)
