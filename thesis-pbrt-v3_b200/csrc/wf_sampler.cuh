@@ -18,7 +18,19 @@ constexpr int kSobolMatrixSize = 52;     // sobolmatrices.h:48
 constexpr int kSobolDims = 1024;         // sobolmatrices.h:47
 constexpr int kHaltonDims = 1000;        // PrimeTableSize (lowdiscrepancy.h)
 
-struct HaltonDim { uint32_t prime, offset; };
+// magic / shift: floor(a / prime) for every 32-bit a as ((a - q) >> 1) + q) >> shift with q = mulhi(a, magic) — the
+// divisor-invariant multiplication of Granlund & Montgomery in its always-add form; integer results, so the digits (and every
+// sample value) are the ones `a / prime` gives.  A runtime division costs ~20 instructions on the SM and a path vertex takes
+// up to 8 dimensions x ~6 digits of them.
+struct HaltonDim { uint32_t prime, offset, magic, shift; };
+WF_HD uint32_t div_magic(uint32_t a, uint32_t magic, uint32_t shift) {
+#ifdef __CUDA_ARCH__
+    const uint32_t q = __umulhi(a, magic);
+#else
+    const uint32_t q = (uint32_t)(((uint64_t)a * magic) >> 32);
+#endif
+    return (((a - q) >> 1) + q) >> shift;
+}
 
 struct WfSampler {
     uint32_t kind, seed;
@@ -70,13 +82,15 @@ WF_HD uint64_t inverse_radical_inverse(uint32_t base, uint64_t inverse, uint32_t
 WF_HD uint64_t sampler_index(const WfSampler &S, int32_t px, int32_t py, uint32_t s) {
     if (S.kind == WF_SAMPLER_HALTON) {
         // HaltonSampler::GetIndexForSample (halton.cpp:96-116); kMaxResolution = 128
-        uint64_t offset = 0;
+        // sampleStride = baseScales[0] * baseScales[1] <= 128 * 243, so sampleStride / baseScales[i] is the other scale and
+        // both products stay below 2^23: the reference's 64-bit sum and modulo are exact in 32 bits
+        uint32_t offset = 0;
         if (S.stride > 1) {
             const uint32_t pmx = (uint32_t)(((px % 128) + 128) % 128), pmy = (uint32_t)(((py % 128) + 128) % 128);
-            const uint64_t d0 = inverse_radical_inverse(2, pmx, S.baseExp0);
-            const uint64_t d1 = inverse_radical_inverse(3, pmy, S.baseExp1);
-            offset += d0 * (S.stride / S.baseScale0) * S.multInv0;
-            offset += d1 * (S.stride / S.baseScale1) * S.multInv1;
+            const uint32_t d0 = (uint32_t)inverse_radical_inverse(2, pmx, S.baseExp0);
+            const uint32_t d1 = (uint32_t)inverse_radical_inverse(3, pmy, S.baseExp1);
+            offset += d0 * S.baseScale1 * S.multInv0;
+            offset += d1 * S.baseScale0 * S.multInv1;
             offset %= S.stride;
         }
         return offset + (uint64_t)s * S.stride;
@@ -120,7 +134,7 @@ WF_HD float radical_inverse(uint32_t base, uint64_t a) {
     return smin((float)rev * invBaseN, kOneMinusEps);
 }
 // ScrambledRadicalInverseSpecialized<base> (lowdiscrepancy.cpp:405-424)
-WF_HD float scrambled_radical_inverse(uint32_t base, const uint16_t *perm, uint64_t a) {
+WF_HD float scrambled_radical_inverse(uint32_t base, uint32_t magic, uint32_t shift, const uint16_t *perm, uint64_t a) {
     const float invBase = 1.f / (float)base;
     uint64_t rev = 0;
     float invBaseN = 1.f;
@@ -132,7 +146,7 @@ WF_HD float scrambled_radical_inverse(uint32_t base, const uint16_t *perm, uint6
     }
     uint32_t a32 = (uint32_t)a;
     while (a32) {
-        const uint32_t next = a32 / base, digit = a32 - next * base;
+        const uint32_t next = div_magic(a32, magic, shift), digit = a32 - next * base;
         rev = rev * base + perm[digit];
         invBaseN *= invBase;
         a32 = next;
@@ -148,7 +162,7 @@ WF_HD float sampler_dim(const WfSampler &S, uint64_t index, uint32_t dim, int32_
         if (dim == 1) return radical_inverse(3, index / S.baseScale1);
         if (dim >= S.nDims) dim = S.nDims - 1;   // host rejects frames that can get here (max_depth vs. table size)
         const HaltonDim di = S.dimInfo[dim];
-        return scrambled_radical_inverse(di.prime, S.perms + di.offset, index);
+        return scrambled_radical_inverse(di.prime, di.magic, di.shift, S.perms + di.offset, index);
     }
     if (S.kind == WF_SAMPLER_SOBOL) {
         // SobolSampler::SampleDimension (sobol.cpp:48-60) over SobolSampleFloat (lowdiscrepancy.h:252-266), scramble 0

@@ -63,7 +63,21 @@ const HaltonTables &halton_tables() {
         }
         size_t total = 0;
         T.dims.resize(primes.size());
-        for (size_t i = 0; i < primes.size(); ++i) { T.dims[i].prime = primes[i]; T.dims[i].offset = (uint32_t)total; total += primes[i]; }
+        for (size_t i = 0; i < primes.size(); ++i) {
+            T.dims[i].prime = primes[i];
+            T.dims[i].offset = (uint32_t)total;
+            total += primes[i];
+            // always-add invariant division (see div_magic): l = floor(log2 d), m = floor(2^(33 + l) / d) + 1 (low 32 bits).
+            // d = 2 is the one power of two among the primes: m = 2^32 does not fit, and dimension 0 never takes this path
+            // (HaltonSampler::SampleDimension reverses bits for base 2); give it a working pair anyway: a / 2 = (((a - 0) >> 1) + 0) >> 0
+            const uint32_t d = primes[i];
+            uint32_t l = 0;
+            while ((2u << l) <= d) ++l;
+            if (d == 2) { T.dims[i].magic = 0; T.dims[i].shift = 0; continue; }
+            const unsigned __int128 num = (unsigned __int128)1 << (33 + l);
+            T.dims[i].magic = (uint32_t)(uint64_t)(num / d + 1);
+            T.dims[i].shift = l;
+        }
         T.perms.resize(total);
         Pcg32 rng;
         uint16_t *p = T.perms.data();
