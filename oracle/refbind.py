@@ -253,10 +253,18 @@ def render(scene, accel_kind, eye, look, up, fov, xres, yres, spp, maxdepth, lig
         scene.L.ref_render_set_crop(_p(None if cropwindow is None else np.array(cropwindow, np.float32)))
     elif cropwindow is not None:
         raise RuntimeError("libpbrtref.so predates ref_render_set_crop: rebuild oracle/ref")
-    with tempfile.TemporaryDirectory() as td:   # the thesis's per-pixel stat dumps (film.cpp:170-264) land here
-        pre = (tmp_prefix or os.path.join(td, "ref")).encode()
-        rc = scene.L.ref_render(scene.h, accel_kind.encode(), _p(cam), xres, yres, spp, maxdepth, _p(lp), _p(li), _p(k),
-                                sampler.encode(), n_threads, pre, _p(out), C.byref(nc), C.byref(ns), _p(hm), _p(pk), _p(el), C.byref(secs))
+    try:
+        with tempfile.TemporaryDirectory() as td:   # the thesis's per-pixel stat dumps (film.cpp:170-264) land here
+            pre = (tmp_prefix or os.path.join(td, "ref")).encode()
+            rc = scene.L.ref_render(scene.h, accel_kind.encode(), _p(cam), xres, yres, spp, maxdepth, _p(lp), _p(li), _p(k),
+                                    sampler.encode(), n_threads, pre, _p(out), C.byref(nc), C.byref(ns), _p(hm), _p(pk), _p(el), C.byref(secs))
+    finally:
+        # the "for the NEXT renders" settings are process globals of the library (tests/hostplugin's driver reads them too):
+        # leave them at their defaults, so that a later render in the same process is not lit by this one's infinite light
+        for fn, args in (("ref_render_set_distant", (None,)), ("ref_render_set_infinite", (None, None)),
+                         ("ref_render_set_camera_matrix", (None,)), ("ref_render_set_crop", (None,)), ("ref_render_set_mat_stride", (8,))):
+            if hasattr(scene.L, fn):
+                getattr(scene.L, fn)(*args)
     if rc != 0:
         raise RuntimeError("ref_render failed (%d)" % rc)
     if timing:   # (rgb, n_closest, n_shadow, seconds spent inside Integrator::Render)

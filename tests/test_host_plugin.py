@@ -367,7 +367,9 @@ def test_cpp_integrator_writes_the_thesis_statistic_matrices(host, gpu, tree):
                 mats[n] = np.loadtxt(os.path.join(td, "img-%s.txt" % n), dtype=np.uint64).reshape(res, res)
     finally:
         L.plugin_set_generalstats(0)
-    acc = gpu.MakeAccelerator(tree, tv)
+    # builder "host": the any-hit counters depend on the order of the primitives INSIDE a kd leaf (IntersectP leaves at the first
+    # hit), which the host builder shares with the reference's and the device builder (stable radix sort) does not
+    acc = gpu.MakeAccelerator(tree, tv, builder="host")
     integ = gpu.WavefrontPathIntegrator(sc["camera"], spp=spp, maxdepth=maxdepth, light_pos=light, light_I=I, kd=kd, seed=9)
     _, heat, _ = wf.render_heatmaps(integ, acc)
     planes = {"primitiveIntersections": 0, "primitiveIntersectionsP": 1, "leafNodeTraversals": 4, "leafNodeTraversalsP": 5}
@@ -378,6 +380,7 @@ def test_cpp_integrator_writes_the_thesis_statistic_matrices(host, gpu, tree):
         assert mats["kdTreeNodeTraversals"].sum() == 0
     assert mats["bspTreeNodeTraversals"].sum() == 0
     ref = g["killeroo_heat"].astype(np.float64)
+    print("\n%s: rays C++ %d/%d; %s" % (tree, nc.value, ns.value, {n: (int(mats[n].sum()), int(heat[k].sum()), int(ref[k].sum())) for n, k in planes.items()}))
     for n, k in planes.items():
         a, b = mats[n].astype(np.float64), heat[k].astype(np.float64)
         assert np.array_equal(a, b), (n, a.sum(), b.sum())   # same description, same Halton stream: the same rays
