@@ -154,6 +154,17 @@ int b200rt_intersect_closest_stats(b200rt_scene *scene, const b200rt_ray *rays, 
                                    b200rt_ray_stats *per_ray, void *stream);
 int b200rt_intersect_any_stats(b200rt_scene *scene, const b200rt_ray *rays, uint64_t n, uint8_t *occluded,
                                b200rt_ray_stats *per_ray, void *stream);
+/* b200rt_intersect_closest for callers that cannot allocate.  NO COUNTERPART IN THE REFERENCE: added
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  rays / hits are
+ * HOST buffers of n records; the device-side staging the ordinary entry point cudaMalloc's on first use lives here in a
+ * file-scope static __device__ array (csrc/no_alloc.cu; 3.25 MiB, held by every GPU that loads the library until exit), so the
+ * call makes no cudaMalloc / cudaFree / allocating library call.  n > B200RT_NOALLOC_MAX_RAYS is rejected with B200RT_EINVAL.
+ * Same kernels, same results (bit for bit) as b200rt_intersect_closest, every tree kind.  The scene's device must be current.
+ * The array is shared by all calls and keeps the last call's contents (this call's hit records are cleared before the launch);
+ * calls that overlap on the GPU would race on it: the entry point serialises its callers on a mutex and returns only after
+ * `stream` has drained. */
+#define B200RT_NOALLOC_MAX_RAYS 65536u
+int b200rt_intersect_closest_noalloc(b200rt_scene *scene, const b200rt_ray *rays, uint64_t n, b200rt_hit *hits, void *stream);
 /* Number of kernel launches issued by this library since b200rt_init (bench.py's gpu_launches). */
 uint64_t b200rt_launch_count(void);
 
