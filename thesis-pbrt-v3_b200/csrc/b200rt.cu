@@ -52,6 +52,7 @@ static int g_coherent_baseline = 1;   // B200RT_COHERENT_BASELINE=0: persistent 
 static uint32_t g_thresh = 14;
 static int g_pblocks[6][2];  // resident persistent blocks per SM, [kind][any]
 static int g_persist_bsp = 1;
+static int g_kd_prefetch = 0;      // B200RT_KD_PREFETCH=1: kd persistent kernel fetches the below child together with each node
 static uint32_t g_bvh_steps = 4;
 static uint32_t g_sstack = 10;     // BVH stack entries kept in shared memory (B200RT_SSTACK; 0 = all in local memory)
 static uint32_t g_toplevels = 0;   // BVH levels staged in shared memory per block (B200RT_TOPLEVELS; 0 = none, the default):
@@ -138,7 +139,12 @@ extern "C" int b200rt_init(int device) {
             CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_pblocks[B200RT_BVH][a], fns[a], B200RT_PBLOCK, sm));
         }
     }
-    OCC(B200RT_KDTREE, 0, (bsp_persistent_kernel<B200RT_KDTREE, false>)); OCC(B200RT_KDTREE, 1, (bsp_persistent_kernel<B200RT_KDTREE, true>));
+    if (const char *e = getenv("B200RT_KD_PREFETCH")) g_kd_prefetch = atoi(e);
+    if (g_kd_prefetch) {
+        OCC(B200RT_KDTREE, 0, (bsp_persistent_kernel<B200RT_KDTREE, false, true>)); OCC(B200RT_KDTREE, 1, (bsp_persistent_kernel<B200RT_KDTREE, true, true>));
+    } else {
+        OCC(B200RT_KDTREE, 0, (bsp_persistent_kernel<B200RT_KDTREE, false>)); OCC(B200RT_KDTREE, 1, (bsp_persistent_kernel<B200RT_KDTREE, true>));
+    }
     OCC(B200RT_RBSP, 0, (bsp_persistent_kernel<B200RT_RBSP, false>)); OCC(B200RT_RBSP, 1, (bsp_persistent_kernel<B200RT_RBSP, true>));
     OCC(B200RT_RBSPKD, 0, (bsp_persistent_kernel<B200RT_RBSPKD, false>)); OCC(B200RT_RBSPKD, 1, (bsp_persistent_kernel<B200RT_RBSPKD, true>));
     OCC(B200RT_BSP, 0, (bsp_persistent_kernel<B200RT_BSP, false>)); OCC(B200RT_BSP, 1, (bsp_persistent_kernel<B200RT_BSP, true>));
@@ -464,7 +470,8 @@ static int build_bsp_scene(const b200rt_scene_desc *d, b200rt_scene *s) {
         CU(cudaMalloc(&s->d_nodes, wide.size() * sizeof(float4)));
         CU(cudaMemcpy(s->d_nodes, wide.data(), wide.size() * sizeof(float4), cudaMemcpyHostToDevice));
     } else {
-        CU(cudaMalloc(&s->d_nodes, (size_t)N * 8));
+        CU(cudaMalloc(&s->d_nodes, ((size_t)N + 1) * 8));   // + 1 record: the kd kernel's below-child prefetch may read nodes[N]
+        CU(cudaMemsetAsync((char *)s->d_nodes + (size_t)N * 8, 0, 8));
         CU(cudaMemcpy(s->d_nodes, ref, (size_t)N * 8, cudaMemcpyHostToDevice));
     }
     CU(cudaMalloc(&s->d_indices, std::max<size_t>(1, d->n_indices) * 4));
@@ -639,8 +646,14 @@ int b200rt::launch_trace(const b200rt_scene *s, const float4 *rays, uint64_t n, 
                     CU(cudaLaunchKernel(bvh_fn(any), dim3(blk), dim3(B200RT_PBLOCK), args, smem, st));
                     break;
                 }
-                case B200RT_KDTREE * 2: PL((bsp_persistent_kernel<B200RT_KDTREE, false>), s->bsp); break;
-                case B200RT_KDTREE * 2 + 1: PL((bsp_persistent_kernel<B200RT_KDTREE, true>), s->bsp); break;
+                case B200RT_KDTREE * 2:
+                    if (g_kd_prefetch) PL((bsp_persistent_kernel<B200RT_KDTREE, false, true>), s->bsp);
+                    else PL((bsp_persistent_kernel<B200RT_KDTREE, false>), s->bsp);
+                    break;
+                case B200RT_KDTREE * 2 + 1:
+                    if (g_kd_prefetch) PL((bsp_persistent_kernel<B200RT_KDTREE, true, true>), s->bsp);
+                    else PL((bsp_persistent_kernel<B200RT_KDTREE, true>), s->bsp);
+                    break;
                 case B200RT_RBSP * 2: PL((bsp_persistent_kernel<B200RT_RBSP, false>), s->bsp); break;
                 case B200RT_RBSP * 2 + 1: PL((bsp_persistent_kernel<B200RT_RBSP, true>), s->bsp); break;
                 case B200RT_RBSPKD * 2: PL((bsp_persistent_kernel<B200RT_RBSPKD, false>), s->bsp); break;

@@ -231,6 +231,19 @@ struct BspCodec {  // bit layout of the flags word
     static constexpr bool wide = KIND == B200RT_BSP || KIND == B200RT_BSPKD;
 };
 
+// Decode the two words of an 8-byte kd / RBSP / RBSPKd node and, for an interior node, intersect its split plane.
+template <int KIND>
+__device__ __forceinline__ BspStep bsp_decode(const BspView &S, const RayCtx &r, uint2 n, uint32_t off, uint32_t mask, uint32_t leafTag) {
+    BspStep st;
+    const uint32_t axis = n.y & mask;
+    st.w0 = n.x;
+    st.payload = n.y >> off;
+    st.leaf = axis == leafTag;
+    st.tPlane = 0.f; st.belowFirst = false;
+    if (!st.leaf) st.tPlane = bsp_interior<KIND>(S, r, axis, __uint_as_float(n.x), st.belowFirst);
+    return st;
+}
+
 // Fetch + decode node `cur` and, for an interior node, intersect its split plane.
 //   kd / RBSP / RBSPKd : kdtreeaccel.cpp:43-104, rbsp.cpp:15-80, rbspKd.cpp:68-92 (axis field `off` bits wide)
 //   BSP                : BSP.h:13-67 (bit 0 = leaf, payload << 1), treeIntersectInterior
@@ -239,16 +252,7 @@ template <int KIND>
 __device__ __forceinline__ BspStep bsp_fetch(const BspView &S, const RayCtx &r, uint32_t cur, uint32_t off, uint32_t mask,
                                              uint32_t leafTag) {
     BspStep st;
-    if (!BspCodec<KIND>::wide) {
-        const uint2 n = __ldg(S.nodes + cur);
-        const uint32_t axis = n.y & mask;
-        st.w0 = n.x;
-        st.payload = n.y >> off;
-        st.leaf = axis == leafTag;
-        st.tPlane = 0.f; st.belowFirst = false;
-        if (!st.leaf) st.tPlane = bsp_interior<KIND>(S, r, axis, __uint_as_float(n.x), st.belowFirst);
-        return st;
-    }
+    if (!BspCodec<KIND>::wide) return bsp_decode<KIND>(S, r, __ldg(S.nodes + cur), off, mask, leafTag);
     float4 lo, hi;
     asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
                  : "=f"(lo.x), "=f"(lo.y), "=f"(lo.z), "=f"(lo.w), "=f"(hi.x), "=f"(hi.y), "=f"(hi.z), "=f"(hi.w)

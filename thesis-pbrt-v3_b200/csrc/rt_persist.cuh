@@ -423,7 +423,10 @@ bvh4_persistent_kernel(const __grid_constant__ BvhView S, const float4 *__restri
 #define B200RT_ST_NODE 1u
 #define B200RT_ST_LEAF 2u
 
-template <int KIND, bool ANY>
+// PF (8-byte node kinds only): the below child is the next record (i + 1), so its words are fetched together with node i's —
+// two independent loads, usually of the same 32-byte sector — and a step that goes below costs no dependent load
+// (B200RT_KD_PREFETCH=1; A/B in profiles/r02_ab_kd_prefetch.log).  The node array is padded by one record for it.
+template <int KIND, bool ANY, bool PF = false>
 __global__ void __launch_bounds__(B200RT_PBLOCK, 8)
 bsp_persistent_kernel(const __grid_constant__ BspView S, const float4 *__restrict__ rays, uint64_t n64,
                       const uint32_t *__restrict__ n_dev, b200rt_hit *__restrict__ hits,
@@ -450,6 +453,8 @@ bsp_persistent_kernel(const __grid_constant__ BspView S, const float4 *__restric
     uint4 todo[64];              // (node, tMin, tMax, -): one 16-byte local store / load per push / pop
     int todoPos = 0;
     WarpQueue wq;
+    uint2 wPre = make_uint2(0u, 0u);   // PF: the words of node `cur` when havePre
+    bool havePre = false;
 
     for (;;) {
         const unsigned idle = __ballot_sync(FULL, state == B200RT_ST_DONE);
@@ -462,6 +467,7 @@ bsp_persistent_kernel(const __grid_constant__ BspView S, const float4 *__restric
                 hit = false;
                 todoPos = 0;
                 cur = 0;
+                havePre = false;
                 if (root_clip(r, S.bounds, tMin, tMax)) state = B200RT_ST_NODE;  // kdtreeaccel.cpp:385
                 else {
                     if (ANY) occluded[rayIdx] = 0;
@@ -486,11 +492,22 @@ bsp_persistent_kernel(const __grid_constant__ BspView S, const float4 *__restric
 #pragma unroll 1
                 for (uint32_t k = 0; k < steps && state == B200RT_ST_NODE; ++k) {
                     if (!ANY && r.tMax < tMin) { finished = true; break; }  // kdtreeaccel.cpp:400 (closest-hit only)
-                    const BspStep nd = bsp_fetch<KIND>(S, r, cur, off, mask, leafTag);
+                    BspStep nd;
+                    uint2 wBelow = make_uint2(0u, 0u);
+                    if (PF && !BspCodec<KIND>::wide) {
+                        const uint2 w = havePre ? wPre : __ldg(S.nodes + cur);
+                        wBelow = __ldg(S.nodes + cur + 1);
+                        nd = bsp_decode<KIND>(S, r, w, off, mask, leafTag);
+                        havePre = false;
+                    } else nd = bsp_fetch<KIND>(S, r, cur, off, mask, leafTag);
                     if (!nd.leaf) {
                         const float tPlane = nd.tPlane;
                         const uint32_t above = nd.payload;
                         const uint32_t first = nd.belowFirst ? cur + 1 : above, second = nd.belowFirst ? above : cur + 1;
+                        if (PF && !BspCodec<KIND>::wide) {   // the node visited next is the below child in these two cases
+                            const bool goesFirst = !(tPlane < tMin) || tPlane > tMax || tPlane <= 0;
+                            if ((goesFirst ? first : second) == cur + 1) { wPre = wBelow; havePre = true; }
+                        }
                         if (tPlane > tMax || tPlane <= 0) cur = first;
                         else if (tPlane < tMin) cur = second;
                         else {
