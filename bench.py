@@ -187,7 +187,7 @@ def run_reference(args):
                        "GeneralStats and all, %d threads) of the workload at %dx%d @ %d of its %d spp: %d rays/step, tree build not timed"
                        % (MAXDEPTH, threads, XRES, YRES, spp, SPP, tot_n // max(1, min(2, args.steps))))}
         # BASELINE config 5 beside it (not the headline): the reference's own render of scenes/living-room's geometry as
-        # scripts/living_room.py renders it on the B200 (path maxdepth 65, constant infinite light, substituted materials)
+        # scripts/living_room.py renders it on the B200 (path maxdepth 65, constant infinite light, the file's materials and image textures)
         try:
             lr = scenes.living_room(480, 270)
             ltv, il = lr["tri_verts"], lr["infinite_light"]
@@ -197,11 +197,11 @@ def run_reference(args):
             _, nc, ns, secs = rb.render(LS, "bvh", (0, 0, 0), (0, 0, 1), (0, 1, 0), 58.715508, 480, 270, 16, lr["maxdepth"], (0, 0, 0),
                                         il["L"], (.5, .5, .5), sampler="random", n_threads=0, timing=True,
                                         prim_mat=lr["materials"][lr["prim_material"]], infinite=(il["L"], l2w),
-                                        camera_matrix=lr["camera"]["world_to_camera"])
+                                        camera_matrix=lr["camera"]["world_to_camera"], textures=lr["texture_pixels"])
             extra["reference_render_living_room"] = {
                 "value": (nc + ns) / secs / 1e6, "unit": UNIT, "cores": threads, "kind": "reference", "seconds": secs,
                 "sample": "the reference's own whole render of scenes/living-room (143163 triangles, BVHAccel, path maxdepth 65, "
-                          "constant infinite light, substituted materials) at 480x270 @ 16 spp: %d rays, %d threads" % (nc + ns, threads)}
+                          "constant infinite light, the file's materials and image textures, box filter) at 480x270 @ 16 spp: %d rays, %d threads" % (nc + ns, threads)}
         except Exception as e:   # noqa: BLE001 — an extra, never the headline
             extra["reference_render_living_room"] = {"unavailable": str(e)[:200]}
     # traversal alone (the reference's BVHAccel::Intersect / IntersectP, or the oracle port, on path-like ray queues)

@@ -21,7 +21,7 @@
 extern "C" {
 #endif
 
-#define B200RT_VERSION 8
+#define B200RT_VERSION 9
 
 enum {
     B200RT_OK = 0,

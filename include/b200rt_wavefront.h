@@ -37,6 +37,16 @@ typedef struct {
     uint32_t xres, yres;
 } b200rt_camera;
 
+/* One image texture: the reference's MIPMap pyramid (b200rt_mipmap_build makes it from the image as ReadImage returns it; the
+ * C++ drop-in hands over the pyramid of the reference's own ImageTexture) and its UVMapping2D (core/texture.cpp).
+ * texels: HOST pointer, RGB floats, level 0 (width x height, both powers of two, row-major, s fastest, row 0 = t 0) followed by
+ * the coarser levels max(1, width >> l) x max(1, height >> l). */
+typedef struct {
+    const float *texels;
+    uint32_t width, height, n_levels;
+    float su, sv, du, dv;   /* "float uscale" / "vscale" / "udelta" / "vdelta": 1, 1, 0, 0 */
+} b200rt_texture;
+
 typedef struct {
     b200rt_camera camera;
     uint32_t spp;        /* Sampler "pixelsamples" */
@@ -99,7 +109,11 @@ typedef struct {
     const uint64_t *sobol_vdc_inv;    /* VdCSobolMatricesInv, sobol_vdc_rows x 52 */
     uint32_t sobol_vdc_rows;
     uint32_t material_stride; /* floats per material record: 0 or 8 = the v7 records; 20 = v8 records
-                              (kind, c0.rgb, c1.rgb, roughness, Kr.rgb, Kt.rgb, opacity.rgb, eta, -, -) which B200RT_MAT_UBER needs */
+                              (kind, c0.rgb, c1.rgb, roughness, Kr.rgb, Kt.rgb, opacity.rgb, eta, kdTex, opacityTex) which B200RT_MAT_UBER needs */
+    /* ---- ABI v9: `Texture "name" "spectrum" "imagemap" ... "bool trilinear" "true"` (textures/imagemap.cpp, core/mipmap.h) ---- */
+    const b200rt_texture *textures; /* HOST array; slot 18 of a 20-float material record = 1 + index of the texture its Kd reads
+                              (matte, plastic, substrate, uber), slot 19 = 1 + index of uber's opacity texture; 0 = the constant */
+    uint32_t n_textures;
 } b200rt_render_desc;
 enum { B200RT_SAMPLER_HASH = 0, B200RT_SAMPLER_HALTON = 1, B200RT_SAMPLER_SOBOL = 2 };
 enum { B200RT_LIGHT_POINT = 0, B200RT_LIGHT_SPHERE = 1, B200RT_LIGHT_DISTANT = 2, B200RT_LIGHT_INFINITE = 3 };
@@ -198,6 +212,13 @@ int b200rt_camera_perspective(const float *lookat9, const float *w2c16, float fo
  * film: HOST or DEVICE, n_floats = 4 * pixels; heat: optional (NULL) B200RT_HEAT_PLANES planes of uint32, summed likewise.
  * On rank 0 film / heat hold the frame afterwards; on other ranks they are unchanged.  Blocks until rank 0 has read this
  * rank's buffer; timeout_s <= 0 means 120 s.  world <= 1 returns 0 at once. */
+/* MIPMap::MIPMap (core/mipmap.h:113-209) + ImageTexture::GetTexture's y flip and convertIn (textures/imagemap.cpp:73-90) on the
+ * host: rgb = w x h x 3 floats as ReadImage returns them (row 0 = top of the image; 8-bit formats: byte / 255.f), gamma != 0 =
+ * InverseGammaCorrect (the default for .tga / .png), scale = "float scale".  b200rt_mipmap_dims gives the power-of-two level-0
+ * size, the level count and the total texel count; out = n_texels x 3 floats.  Texels equal the reference's bit for bit. */
+int b200rt_mipmap_dims(uint32_t w, uint32_t h, uint32_t *w0, uint32_t *h0, uint32_t *n_levels, uint64_t *n_texels);
+int b200rt_mipmap_build(const float *rgb, uint32_t w, uint32_t h, int gamma, float scale, float *out);
+
 int b200rt_film_reduce(const char *rendezvous, uint32_t rank, uint32_t world, float *film, uint64_t n_floats,
                        uint32_t *heat, uint64_t n_heat, double timeout_s);
 

@@ -11,6 +11,8 @@
 #include "core/camera.h"
 #include "core/primitive.h"
 #include "core/film.h"
+#include "core/mipmap.h"
+#include "textures/imagemap.h"
 #undef private
 #undef protected
 #include "core/api.h"
@@ -52,7 +54,7 @@ void WriteImage(const std::string &, const Float *rgb, const Bounds2i &outputBou
     g_lastRes = Point2i(res.x, res.y);
     g_lastImage.assign(rgb, rgb + 3 * (size_t)res.x * res.y);
 }
-std::unique_ptr<RGBSpectrum[]> ReadImage(const std::string &, Point2i *) { return nullptr; }
+// ReadImage is the reference's own (core/imageio.cpp compiled with its WriteImage renamed, oracle/ref/Makefile): image textures
 }  // namespace pbrt
 using namespace pbrt;
 
@@ -237,6 +239,70 @@ static int g_matStride = 8;
 extern "C" void ref_render_set_mat_stride(int n) { g_matStride = n == 20 ? 20 : 8; }
 extern "C" int ref_render_get_mat_stride(void) { return g_matStride; }
 
+// `Texture "t<i>" "spectrum" "imagemap" "string filename" <file> "bool trilinear" "true"` for the NEXT renders: slot 18 / 19 of a
+// 20-float prim_mat record name (1-based) the texture the material's Kd / uber's opacity reads.  The textures are made by the
+// reference's own CreateImageSpectrumTexture (textures/imagemap.cpp:146-188) -> ReadImage -> MIPMap.
+static std::vector<std::string> g_texFiles;
+static std::shared_ptr<Texture<Spectrum>> make_imagemap(const std::string &file) {
+    ParamSet ps;
+    std::unique_ptr<std::string[]> f(new std::string[1]);
+    f[0] = file;
+    ps.AddString("filename", std::move(f), 1);
+    std::unique_ptr<bool[]> tri(new bool[1]);
+    tri[0] = true;
+    ps.AddBool("trilinear", std::move(tri), 1);
+    std::map<std::string, std::shared_ptr<Texture<Float>>> ft;
+    std::map<std::string, std::shared_ptr<Texture<Spectrum>>> st;
+    TextureParams tp(ps, ps, ft, st);
+    // MIPMap's constructor runs ParallelFor loops; the thread pool is not up here (pbrtInit starts it before any texture is made):
+    // with one thread the loops run inline (parallel.cpp:186)
+    const int nThreads = PbrtOptions.nThreads;
+    PbrtOptions.nThreads = 1;
+    std::shared_ptr<Texture<Spectrum>> t(CreateImageSpectrumTexture(Transform(), tp));
+    PbrtOptions.nThreads = nThreads;
+    return t;
+}
+extern "C" void ref_render_set_textures(int n, const char *const *files) {
+    g_texFiles.clear();
+    ImageTexture<RGBSpectrum, Spectrum>::ClearCache();
+    for (int i = 0; i < n; ++i) g_texFiles.push_back(files[i]);
+}
+extern "C" int ref_render_get_textures(int i, char *out, int cap) {   // for tests/hostplugin's driver; returns the count
+    if (i >= 0 && i < (int)g_texFiles.size() && out) std::snprintf(out, cap, "%s", g_texFiles[i].c_str());
+    return (int)g_texFiles.size();
+}
+// The MIPMap the reference builds for `file`: level count and level-0 size; with out != NULL also the texels of `level`
+// (RGB, row-major, s fastest).  Returns the number of levels, 0 if the file cannot be read.
+extern "C" int ref_texture_pyramid(const char *file, int level, float *out, int *w, int *h) {
+    ImageTexture<RGBSpectrum, Spectrum>::ClearCache();
+    std::shared_ptr<Texture<Spectrum>> t = make_imagemap(file);
+    auto *it = static_cast<ImageTexture<RGBSpectrum, Spectrum> *>(t.get());
+    const MIPMap<RGBSpectrum> *mm = it->mipmap;
+    const int nL = mm->Levels();
+    if (level < 0 || level >= nL) return 0;
+    const BlockedArray<RGBSpectrum> &a = *mm->pyramid[level];
+    *w = a.uSize(); *h = a.vSize();
+    if (out)
+        for (int t2 = 0; t2 < a.vSize(); ++t2)
+            for (int s2 = 0; s2 < a.uSize(); ++s2) {
+                Float rgb[3];
+                a(s2, t2).ToRGB(rgb);
+                for (int c = 0; c < 3; ++c) out[3 * ((size_t)t2 * a.uSize() + s2) + c] = rgb[c];
+            }
+    return nL;
+}
+// MIPMap::Lookup(st, width) of the reference's texture for n (s, t, width) triples
+extern "C" int ref_texture_lookup(const char *file, const float *stw, int n, float *out) {
+    std::shared_ptr<Texture<Spectrum>> t = make_imagemap(file);
+    auto *it = static_cast<ImageTexture<RGBSpectrum, Spectrum> *>(t.get());
+    for (int i = 0; i < n; ++i) {
+        Float rgb[3];
+        it->mipmap->Lookup(Point2f(stw[3 * i], stw[3 * i + 1]), stw[3 * i + 2]).ToRGB(rgb);
+        for (int c = 0; c < 3; ++c) out[3 * i + c] = rgb[c];
+    }
+    return 0;
+}
+
 // Film "float cropwindow" [x0 x1 y0 y1] for the NEXT renders (NULL = whole frame); out_rgb / out_heat then hold the
 // window's pixels only (Film::croppedPixelBounds, film.cpp:49-57).
 static float g_crop[4] = {0.f, 1.f, 0.f, 1.f};
@@ -283,7 +349,8 @@ extern "C" int ref_render(ref_scene *s, const char *accel_kind, const float *cam
             auto it = byKd.find(k);
             if (it == byKd.end()) {
                 Float c[3] = {k[1], k[2], k[3]}, cs[3] = {k[4], k[5], k[6]};
-                auto tex = std::make_shared<ConstantTexture<Spectrum>>(Spectrum::FromRGB(c));
+                std::shared_ptr<Texture<Spectrum>> tex = std::make_shared<ConstantTexture<Spectrum>>(Spectrum::FromRGB(c));
+                if (g_matStride == 20 && k[18] > 0 && (size_t)k[18] <= g_texFiles.size()) tex = make_imagemap(g_texFiles[(size_t)k[18] - 1]);
                 std::shared_ptr<Material> mm;
                 const int kind = (int)k[0] & 15;
                 const bool remap = !((int)k[0] & 32);   // "bool remaproughness"
@@ -304,7 +371,8 @@ extern "C" int ref_render(ref_scene *s, const char *accel_kind, const float *cam
                     auto texS = std::make_shared<ConstantTexture<Spectrum>>(Spectrum::FromRGB(cs));
                     auto texR = std::make_shared<ConstantTexture<Spectrum>>(Spectrum::FromRGB(cr));
                     auto texT = std::make_shared<ConstantTexture<Spectrum>>(Spectrum::FromRGB(ct));
-                    auto texO = std::make_shared<ConstantTexture<Spectrum>>(Spectrum::FromRGB(co));
+                    std::shared_ptr<Texture<Spectrum>> texO = std::make_shared<ConstantTexture<Spectrum>>(Spectrum::FromRGB(co));
+                    if (k[19] > 0 && (size_t)k[19] <= g_texFiles.size()) texO = make_imagemap(g_texFiles[(size_t)k[19] - 1]);
                     auto rough = std::make_shared<ConstantTexture<Float>>(k[7]);
                     auto eta = std::make_shared<ConstantTexture<Float>>(k[17]);
                     mm = std::make_shared<UberMaterial>(tex, texS, texR, texT, rough, nullptr, nullptr, texO, eta, nullptr, remap);

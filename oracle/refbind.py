@@ -208,7 +208,7 @@ def camera_matrices(eye, look, up, fov, xres, yres, camera_matrix=None):
 
 def render(scene, accel_kind, eye, look, up, fov, xres, yres, spp, maxdepth, light_pos, light_I, kd,
            sampler="random", n_threads=0, tmp_prefix=None, heat=False, prim_mat=None, emitter_L=None, timing=False,
-           distant=None, cropwindow=None, infinite=None, camera_matrix=None):
+           distant=None, cropwindow=None, infinite=None, camera_matrix=None, textures=None):
     """The reference's OWN render (SamplerIntegrator::Render + PathIntegrator::Li + Film, oracle/ref/ref_render.cpp)
     of `scene` with a matte material and one point light.  Returns (rgb (yres,xres,3), n_closest, n_shadow)."""
     import tempfile
@@ -256,13 +256,22 @@ def render(scene, accel_kind, eye, look, up, fov, xres, yres, spp, maxdepth, lig
     try:
         with tempfile.TemporaryDirectory() as td:   # the thesis's per-pixel stat dumps (film.cpp:170-264) land here
             pre = (tmp_prefix or os.path.join(td, "ref")).encode()
+            if textures:
+                # textures: list of (h, w, 3) uint8 images (row 0 = top).  They become .tga files the reference reads with its own
+                # ReadImage; slots 18 / 19 of 20-float prim_mat records name them (1-based) as the Kd / opacity `imagemap`
+                files = []
+                for i, px in enumerate(textures):
+                    files.append(os.path.join(td, "tex%d.tga" % i))
+                    write_tga(files[-1], px)
+                set_textures(files, scene.L)
             rc = scene.L.ref_render(scene.h, accel_kind.encode(), _p(cam), xres, yres, spp, maxdepth, _p(lp), _p(li), _p(k),
                                     sampler.encode(), n_threads, pre, _p(out), C.byref(nc), C.byref(ns), _p(hm), _p(pk), _p(el), C.byref(secs))
     finally:
         # the "for the NEXT renders" settings are process globals of the library (tests/hostplugin's driver reads them too):
         # leave them at their defaults, so that a later render in the same process is not lit by this one's infinite light
         for fn, args in (("ref_render_set_distant", (None,)), ("ref_render_set_infinite", (None, None)),
-                         ("ref_render_set_camera_matrix", (None,)), ("ref_render_set_crop", (None,)), ("ref_render_set_mat_stride", (8,))):
+                         ("ref_render_set_camera_matrix", (None,)), ("ref_render_set_crop", (None,)), ("ref_render_set_mat_stride", (8,)),
+                         ("ref_render_set_textures", (0, None))):
             if hasattr(scene.L, fn):
                 getattr(scene.L, fn)(*args)
     if rc != 0:
@@ -270,3 +279,46 @@ def render(scene, accel_kind, eye, look, up, fov, xres, yres, spp, maxdepth, lig
     if timing:   # (rgb, n_closest, n_shadow, seconds spent inside Integrator::Render)
         return out, nc.value, ns.value, secs.value
     return (out, nc.value, ns.value, hm) if heat else (out, nc.value, ns.value)
+
+
+def texture_pyramid(path):
+    """The MIPMap the reference builds for the image file `path` (CreateImageSpectrumTexture, trilinear): list of (h, w, 3) levels."""
+    L = lib()
+    L.ref_texture_pyramid.argtypes = [C.c_char_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
+    w, h = C.c_int(), C.c_int()
+    n = L.ref_texture_pyramid(path.encode(), 0, None, C.byref(w), C.byref(h))
+    out = []
+    for l in range(n):
+        L.ref_texture_pyramid(path.encode(), l, None, C.byref(w), C.byref(h))
+        a = np.zeros((h.value, w.value, 3), np.float32)
+        L.ref_texture_pyramid(path.encode(), l, _p(a), C.byref(w), C.byref(h))
+        out.append(a)
+    return out
+
+
+def texture_lookup(path, stw):
+    """MIPMap::Lookup(st, width) of the reference's texture for (n, 3) rows (s, t, width)."""
+    L = lib()
+    L.ref_texture_lookup.argtypes = [C.c_char_p, C.c_void_p, C.c_int, C.c_void_p]
+    stw = np.ascontiguousarray(stw, np.float32).reshape(-1, 3)
+    out = np.zeros((len(stw), 3), np.float32)
+    L.ref_texture_lookup(path.encode(), _p(stw), len(stw), _p(out))
+    return out
+
+
+def set_textures(files, L=None):
+    """Image files the slots 18 / 19 of 20-float prim_mat records refer to (1-based) in the NEXT renders; [] clears."""
+    L = L or lib()
+    arr = (C.c_char_p * max(1, len(files)))(*[f.encode() for f in files])
+    L.ref_render_set_textures.argtypes = [C.c_int, C.c_void_p]
+    L.ref_render_set_textures(len(files), arr)
+
+
+def write_tga(path, rgb8):
+    """Uncompressed 24-bit TGA with top-to-bottom rows (descriptor 0x20) and BGR pixels, like the files of scenes/living-room."""
+    import struct
+    rgb8 = np.ascontiguousarray(rgb8, np.uint8)
+    h, w = rgb8.shape[:2]
+    with open(path, "wb") as f:
+        f.write(struct.pack("<BBBHHBHHHHBB", 0, 0, 2, 0, 0, 0, 0, 0, w, h, 24, 0x20))
+        f.write(np.ascontiguousarray(rgb8[..., ::-1]).tobytes())

@@ -52,11 +52,13 @@ def main():
     accel = b200rt.MakeAccelerator(args.accel, tv)
     il = sc["infinite_light"]
 
+    textures = scenes.living_room_textures(sc)
+
     def integrator(spp):
         return b200rt.WavefrontPathIntegrator(sc["camera"], spp=spp, maxdepth=args.maxdepth, light_I=il["L"],
                                               infinite_light=(il["light_to_world"], wf.world_radius(tv)),
                                               materials=sc["materials"], prim_material=sc["prim_material"],
-                                              rank=rank, world=world, seed=1)
+                                              textures=textures, rank=rank, world=world, seed=1)
     film = torch.zeros((args.yres, args.xres, 4), dtype=torch.float32, device=dev)
     gather = FilmGather(args.xres, args.yres, 16, rank, world, dev)
 

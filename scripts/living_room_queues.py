@@ -33,7 +33,8 @@ tv, il = sc["tri_verts"], sc["infinite_light"]
 acc = b200rt.MakeAccelerator(args.accel, tv)
 integ = b200rt.WavefrontPathIntegrator(sc["camera"], spp=args.spp, maxdepth=args.maxdepth, light_I=il["L"], seed=1,
                                        infinite_light=(il["light_to_world"], wf.world_radius(tv)),
-                                       materials=sc["materials"], prim_material=sc["prim_material"])
+                                       materials=sc["materials"], prim_material=sc["prim_material"],
+                                       textures=scenes.living_room_textures(sc))
 film = torch.zeros(integ.shape, dtype=torch.float32, device="cuda")
 wf.keep_queues(acc, True)
 stats = integ.render_ptr(acc, film.data_ptr(), st)

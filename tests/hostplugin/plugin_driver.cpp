@@ -107,6 +107,8 @@ extern "C" int plugin_intersect_p_batch(const ref_accel *a, const float *rays, u
 #include "materials/metal.h"
 #include "materials/substrate.h"
 #include "materials/uber.h"
+#include "textures/imagemap.h"
+#include "core/paramset.h"
 #include "lights/diffuse.h"
 #include "lights/distant.h"
 #include "core/sampling.h"
@@ -121,6 +123,7 @@ extern "C" int ref_last_image(float *out_rgb, int *xres, int *yres);
 extern "C" int ref_render_get_distant(float *from_to);
 extern "C" int ref_render_get_infinite(float *L_rgb, float *l2w16);      // set through ref_render_set_infinite
 extern "C" int ref_render_get_camera_matrix(float *w2c16);             // set through ref_render_set_camera_matrix
+extern "C" int ref_render_get_textures(int i, char *out, int cap);   // set through ref_render_set_textures: image files of slots 18 / 19
 extern "C" int ref_render_get_mat_stride(void);             // set through ref_render_set_mat_stride: 8 or 20 floats per record
 extern "C" void ref_render_get_crop(float *cw);           // set through ref_render_set_crop   // set through ref_render_set_distant (oracle/ref/ref_render.cpp)
 std::shared_ptr<pbrt::Shape> shape_of(const pbrt::Primitive *p);   // plugin_shape_of.cpp (GeometricPrimitive::shape is private)
@@ -155,7 +158,27 @@ extern "C" int plugin_render(ref_scene *s, const char *tree, const float *cam, i
             auto it = byRec.find(k);
             if (it == byRec.end()) {
                 Float c[3] = {k[1], k[2], k[3]}, cs[3] = {k[4], k[5], k[6]};
-                auto tex = std::make_shared<ConstantTexture<Spectrum>>(Spectrum::FromRGB(c));
+                std::shared_ptr<Texture<Spectrum>> tex = std::make_shared<ConstantTexture<Spectrum>>(Spectrum::FromRGB(c));
+                auto imagemap = [](int idx) -> std::shared_ptr<Texture<Spectrum>> {   // `Texture ... "imagemap" "bool trilinear" "true"`
+                    char file[1024];
+                    if (idx < 1 || idx > ref_render_get_textures(idx - 1, file, sizeof file)) return nullptr;
+                    ParamSet ps;
+                    std::unique_ptr<std::string[]> f(new std::string[1]);
+                    f[0] = file;
+                    ps.AddString("filename", std::move(f), 1);
+                    std::unique_ptr<bool[]> tri(new bool[1]);
+                    tri[0] = true;
+                    ps.AddBool("trilinear", std::move(tri), 1);
+                    std::map<std::string, std::shared_ptr<Texture<Float>>> ft;
+                    std::map<std::string, std::shared_ptr<Texture<Spectrum>>> st;
+                    TextureParams tp(ps, ps, ft, st);
+                    const int nThreads = PbrtOptions.nThreads;
+                    PbrtOptions.nThreads = 1;   // MIPMap's ParallelFor loops run inline: the pool is not up yet
+                    std::shared_ptr<Texture<Spectrum>> t(CreateImageSpectrumTexture(Transform(), tp));
+                    PbrtOptions.nThreads = nThreads;
+                    return t;
+                };
+                if (stride == 20 && k[18] > 0) if (auto t = imagemap((int)k[18])) tex = t;
                 std::shared_ptr<Material> mm;
                 const int kind = (int)k[0] & 15;
                 const bool remap = !((int)k[0] & 32);
@@ -167,9 +190,11 @@ extern "C" int plugin_render(ref_scene *s, const char *tree, const float *cam, i
                 else if (kind == 2) mm = std::make_shared<MirrorMaterial>(tex, nullptr);
                 else if (kind == 6) {   // Material "uber": Kr 8-10, Kt 11-13, opacity 14-16, eta 17
                     Float cr[3] = {k[8], k[9], k[10]}, ct[3] = {k[11], k[12], k[13]}, co[3] = {k[14], k[15], k[16]};
+                    std::shared_ptr<Texture<Spectrum>> texO = std::make_shared<ConstantTexture<Spectrum>>(Spectrum::FromRGB(co));
+                    if (k[19] > 0) if (auto t = imagemap((int)k[19])) texO = t;
                     mm = std::make_shared<UberMaterial>(tex, texS, std::make_shared<ConstantTexture<Spectrum>>(Spectrum::FromRGB(cr)),
                                                         std::make_shared<ConstantTexture<Spectrum>>(Spectrum::FromRGB(ct)), rough, nullptr, nullptr,
-                                                        std::make_shared<ConstantTexture<Spectrum>>(Spectrum::FromRGB(co)),
+                                                        texO,
                                                         std::make_shared<ConstantTexture<Float>>(k[17]), nullptr, remap);
                 } else if (kind == 3)
                     mm = std::make_shared<GlassMaterial>(tex, std::make_shared<ConstantTexture<Spectrum>>(Spectrum::FromRGB(cs)),

@@ -26,6 +26,7 @@ struct hs_ctx {
     std::vector<uint8_t> flags, isSphere, primMat;
     std::vector<uint32_t> sobol32;
     std::vector<uint64_t> vdc;
+    std::vector<WfTexture> tex;
 };
 
 extern "C" const char *hs_last_error() { return g_err; }
@@ -52,10 +53,25 @@ extern "C" hs_ctx *hs_create(const b200rt_render_desc *d, uint32_t n_prims, cons
         c->mats.resize((size_t)d->n_materials * kMatFloats);
         bool spec = false;
         for (uint32_t k = 0; k < d->n_materials; ++k)
-            if (!material_lobes(d->materials + (size_t)stride * k, stride, k, c->mats.data() + (size_t)k * kMatFloats, &spec)) { delete c; return nullptr; }
+            if (!material_lobes(d->materials + (size_t)stride * k, stride, k, c->mats.data() + (size_t)k * kMatFloats, &spec, d->textures ? d->n_textures : 0u)) { delete c; return nullptr; }
         P.has_specular = spec;
         c->primMat.assign(d->prim_material, d->prim_material + n_prims);
         P.mats = c->mats.data(); P.primMat = c->primMat.data();
+        if (d->textures && d->n_textures) {   // the caller's pyramids stay alive as long as the context
+            c->tex.resize(d->n_textures);
+            for (uint32_t k = 0; k < d->n_textures; ++k) {
+                const b200rt_texture &t = d->textures[k];
+                WfTexture &T = c->tex[k];
+                T.texels = t.texels; T.nLevels = t.n_levels; T.w0 = t.width; T.h0 = t.height;
+                T.su = t.su; T.sv = t.sv; T.du = t.du; T.dv = t.dv;
+                size_t off = 0;
+                for (uint32_t l = 0; l < 16; ++l) {
+                    T.levelOffset[l] = (uint32_t)off;
+                    if (l < t.n_levels) off += (size_t)std::max(1u, t.width >> l) * std::max(1u, t.height >> l);
+                }
+            }
+            P.tex = c->tex.data(); P.nTex = d->n_textures;
+        }
     }
     P.smp.kind = d->sampler; P.smp.seed = d->seed;
     if (d->sampler == B200RT_SAMPLER_HALTON) {
@@ -172,4 +188,25 @@ extern "C" uint64_t hs_sincos_check(uint32_t lo, uint32_t hi, uint32_t stride) {
             bad += (f2u(a) != f2u(b)) + (f2u(c) != f2u(d));
         }
     return bad;
+}
+
+// log_ref (wf_texture.cuh) against this machine's libm logf over the positive float bit patterns [lo, hi) with the given stride
+extern "C" uint64_t hs_log_check(uint32_t lo, uint32_t hi, uint32_t stride) {
+    uint64_t bad = 0;
+    for (uint32_t u = lo; u < hi; u += stride) {
+        const float x = u2f(u);
+        bad += f2u(logf(x)) != f2u(log_ref(x));
+    }
+    return bad;
+}
+// MIPMap::Lookup of one texture (tex_lookup) for a list of (s, t, width) triples: 3 floats out per lookup
+extern "C" void hs_tex_lookup(const b200rt_texture *t, const float *stw, uint32_t n, float *out) {
+    WfTexture T;
+    T.texels = t->texels; T.nLevels = t->n_levels; T.w0 = t->width; T.h0 = t->height; T.su = t->su; T.sv = t->sv; T.du = t->du; T.dv = t->dv;
+    size_t off = 0;
+    for (uint32_t l = 0; l < 16; ++l) { T.levelOffset[l] = (uint32_t)off; if (l < t->n_levels) off += (size_t)std::max(1u, t->width >> l) * std::max(1u, t->height >> l); }
+    for (uint32_t i = 0; i < n; ++i) {
+        const V3 v = tex_lookup(T, stw[3 * i], stw[3 * i + 1], stw[3 * i + 2]);
+        out[3 * i] = v.x; out[3 * i + 1] = v.y; out[3 * i + 2] = v.z;
+    }
 }

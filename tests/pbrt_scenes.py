@@ -20,12 +20,18 @@ def write_killeroo_geometry(path):
 
 
 def killeroo_simple(dirname, accelerator, integrator='Integrator "path" "integer maxdepth" [5]', xres=700, yres=700, spp=8,
-                    filename="killeroo-simple.pfm", extra_film="", scene_name="input.pbrt"):
+                    filename="killeroo-simple.pfm", extra_film="", scene_name="input.pbrt", ground_texture=None):
     """scenes/killeroo-simple with its Accelerator line replaced by `accelerator` (a full directive) and, optionally, its
     Integrator line by `integrator`.  Returns the scene file's path."""
     geo = os.path.join(dirname, "killeroo.pbrt")
     if not os.path.exists(geo):
         write_killeroo_geometry(geo)
+    ground = 'Material "matte" "color Kd" [.5 .5 .8]'
+    if ground_texture is not None:
+        # the ground (uv 0..5: five repeats) with an image texture on its Kd, the way scenes/sponza and scenes/living-room
+        # declare theirs: `Texture "name" "spectrum" "imagemap" "string filename" ... "bool trilinear" "true"`
+        ground = ('Texture "groundtex" "spectrum" "imagemap" "string filename" "%s" "bool trilinear" "true"\n'
+                  '  Material "matte" "texture Kd" "groundtex"' % ground_texture)
     txt = '''LookAt 400 20 30   0 63 -110   0 0 1
 Rotate -5 0 0 1
 Camera "perspective" "float fov" [39]
@@ -50,7 +56,7 @@ AttributeEnd
 
 
 AttributeBegin
-  Material "matte" "color Kd" [.5 .5 .8]
+  %s
   Translate 0 0 -140
 Shape "trianglemesh" "point P" [ -1000 -1000 0 1000 -1000 0 1000 1000 0 -1000 1000 0 ]
       "float uv" [ 0 0 5 0 5 5 0 5 ]
@@ -74,7 +80,7 @@ Translate -200 0 0
 
 AttributeEnd
 WorldEnd
-''' % (xres, yres, filename, extra_film, spp, accelerator, integrator, geo, geo)
+''' % (xres, yres, filename, extra_film, spp, accelerator, integrator, ground, geo, geo)
     path = os.path.join(dirname, scene_name)
     with open(path, "w") as f:
         f.write(txt)

@@ -118,14 +118,16 @@ def build(name, res=48):
                               distant_light=(sc["light_dir"], wf.world_radius(tv)), crop=sc["crop"]),
                    accel=(tv, {}), res=res * 4)
         return out
-    if name == "living_room":
+    if name in ("living_room", "living_room_tex"):
         # BASELINE config 5, scenes/living-room as the reference resolves it (b200rt.scenes.living_room): the file's camera CTM,
         # its infinite light (constant: the sky map is absent), maxdepth 65, the file's matte / Oren-Nayar / substrate / metal /
         # glass / mirror / uber materials and the PLY vertex normals.  The reference harness builds ONE mesh, so the 3 008
         # triangles whose PLY has no normals carry zero normals on both sides (ns falls back to n, triangle.cpp:352-355).
         import os
         from b200rt import wavefront as wf
-        sc = scenes.living_room(res, res)
+        # "living_room_tex": with the image textures of the files that are in the reference tree (leaf.tga: Kd and opacity of the
+        # Leaves; picture8.tga: Kd of the Painting) — the scene as the reference renders it, box filter aside
+        sc = scenes.living_room(res, res, textures=name == "living_room_tex")
         z = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "living_room_mesh.npz"))
         tv = sc["tri_verts"]
         il = sc["infinite_light"]
@@ -140,6 +142,10 @@ def build(name, res=48):
                               materials=sc["materials"], prim_material=sc["prim_material"]),
                    accel=(tv, dict(tri_uvs=sc["tri_uvs"], tri_normals=sc["tri_normals"], prim_flags=np.full(len(tv), 2, np.uint8))),
                    mis=True, infinite_scene=True, maxdepth=sc["maxdepth"])
+        if name == "living_room_tex":
+            from b200rt import textures as tx
+            out["render"]["textures"] = sc["texture_pixels"]
+            out["integ"]["textures"] = [tx.ImageTexture(rgb8=px) for px in sc["texture_pixels"]]
         return out
     if name in ("normals", "normals_flipped"):
         # vertex normals (interpolated shading normal, triangle.cpp:348-400), a real (u, v) parameterisation (dpdu frame) and,
@@ -164,4 +170,4 @@ def build(name, res=48):
 
 
 CASES = ["sponza_point", "killeroo_plastic", "killeroo_normals", "killeroo_glass", "killeroo_metal", "killeroo_oren", "killeroo_uber", "killeroo_infinite",
-         "feet_distant", "normals", "normals_flipped", "living_room"]
+         "feet_distant", "normals", "normals_flipped", "living_room", "living_room_tex"]

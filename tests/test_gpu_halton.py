@@ -44,7 +44,8 @@ def _device_queues(gpu, c, spp, sampler):
 @pytest.mark.parametrize("case,sampler", [("sponza_point", "halton"), ("killeroo_plastic", "halton"), ("killeroo_normals", "halton"), ("killeroo_glass", "halton"),
                                           ("killeroo_metal", "halton"), ("killeroo_oren", "halton"), ("killeroo_uber", "halton"), ("killeroo_infinite", "halton"),
                                           ("feet_distant", "halton"), ("normals", "halton"), ("normals_flipped", "halton"),
-                                          ("killeroo_metal", "sobol"), ("feet_distant", "sobol"), ("living_room", "sobol")])
+                                          ("killeroo_metal", "sobol"), ("feet_distant", "sobol"), ("living_room", "sobol"),
+                                          ("living_room_tex", "sobol")])
 def test_device_rays_are_the_references(gpu, case, sampler):
     import hostwf
     from b200rt import wavefront as wf
@@ -88,6 +89,9 @@ IMAGE_CASES = {
     # BASELINE config 5: scenes/living-room as the reference resolves it (the file's Sampler "sobol", maxdepth 65, infinite light,
     # its material table incl. "uber", the PLY vertex normals), square frame
     "living_room": dict(res=256, spp=16, sampler="sobol"),
+    # ... and with the image textures of the files that are in the reference tree (ABI v9: leaf.tga as Kd and opacity of the uber
+    # Leaves, picture8.tga on the Painting; MIP level from the camera rays' differentials)
+    "living_room_tex": dict(res=256, spp=16, sampler="sobol"),
 }
 
 

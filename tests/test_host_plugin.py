@@ -269,9 +269,17 @@ def test_cpp_integrator_renders_living_room(host, gpu):
                                 C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_char_p, C.c_void_p, C.POINTER(C.c_uint64),
                                 C.POINTER(C.c_uint64), C.c_void_p, C.c_void_p]
     xres, yres, spp, maxdepth = 160, 90, 16, 65
-    sc = scenes.living_room(xres, yres)
+    sc = scenes.living_room(xres, yres)          # with its image textures (ABI v9)
     z = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "living_room_mesh.npz"))
     tv, il = sc["tri_verts"], sc["infinite_light"]
+    from b200rt import textures as tx
+    import tempfile
+    texdir = tempfile.mkdtemp()
+    texfiles = []
+    for n, px in zip(sc["texture_names"], sc["texture_pixels"]):
+        texfiles.append(os.path.join(texdir, n + ".tga"))
+        tx.write_tga(texfiles[-1], px)
+    rb.set_textures(texfiles, L)
     S = rb.RefScene(z["P"], z["idx"], uv=z["UV"], normals=z["N"], L=L)
     l2w = np.eye(4, dtype=np.float32)
     l2w[:3, :3] = il["light_to_world"]
@@ -299,13 +307,15 @@ def test_cpp_integrator_renders_living_room(host, gpu):
         L.ref_render_set_camera_matrix(None)
         L.ref_render_set_mat_stride(8)
         L.plugin_set_sampler(b"halton")
+        rb.set_textures([], L)
     assert rc == 0
     # the Python mirror: same C ABI, same records (the harness's single mesh gives every triangle the has-normals flag)
     acc = gpu.B200Accel(gpu.build_bvh_device(tv), tv, tri_uvs=sc["tri_uvs"], tri_normals=sc["tri_normals"],
                         prim_flags=np.full(len(tv), 2, np.uint8))
     integ = gpu.WavefrontPathIntegrator(sc["camera"], spp=spp, maxdepth=maxdepth, light_I=il["L"], sampler="sobol",
                                         infinite_light=(il["light_to_world"], wf.world_radius(tv)),
-                                        materials=sc["materials"], prim_material=sc["prim_material"])
+                                        materials=sc["materials"], prim_material=sc["prim_material"],
+                                        textures=[tx.ImageTexture(rgb8=px) for px in sc["texture_pixels"]])
     film, st = integ.Render(acc)
     py = film_to_rgb(film)
     # Film::WriteImage converts XYZ -> RGB on the way out (film.cpp:266-305): a rounding of the last bit, nothing else
@@ -314,7 +324,7 @@ def test_cpp_integrator_renders_living_room(host, gpu):
     # the reference's own render of the same objects, same sample stream
     ref, rnc, rns = rb.render(S, "bvh", (0, 0, 0), (0, 0, 1), (0, 1, 0), 58.715508, xres, yres, spp, maxdepth, (0, 0, 0), il["L"],
                               (.5, .5, .5), sampler="sobol", n_threads=0, prim_mat=prim_mat, infinite=(il["L"], l2w),
-                              camera_matrix=sc["camera"]["world_to_camera"])
+                              camera_matrix=sc["camera"]["world_to_camera"], textures=sc["texture_pixels"])
     im = hostwf.image_stats(out, ref)
     print("\nliving-room through the C++ drop-in, %dx%d @ %d spp sobol: rays %d/%d ref %d/%d; %s" % (xres, yres, spp, nc.value, ns.value, rnc, rns, im))
     assert abs(nc.value - rnc) <= 1e-5 * rnc + 2 and abs(ns.value - rns) <= 1e-5 * rns + 2

@@ -109,12 +109,18 @@ def _blocks(img, k):
     return img[:h, :w].reshape(h // k, k, w // k, k, -1).mean((1, 3))
 
 
+def scenes_mod():
+    from b200rt import scenes
+    return scenes
+
+
 def _integrator(gpu, sc, spp, maxdepth, **kw):
     from b200rt import wavefront as wf
     il = sc["infinite_light"]
     return gpu.WavefrontPathIntegrator(sc["camera"], spp=spp, maxdepth=maxdepth, light_I=il["L"],
                                        infinite_light=(il["light_to_world"], wf.world_radius(sc["tri_verts"])),
-                                       materials=sc["materials"], prim_material=sc["prim_material"], **kw)
+                                       materials=sc["materials"], prim_material=sc["prim_material"],
+                                       textures=scenes_mod().living_room_textures(sc), **kw)
 
 
 @pytest.mark.gpu
@@ -127,7 +133,7 @@ def test_living_room_render_matches_the_references_render(gpu):
     from oracle import refbind as rb
     from b200rt.wavefront import film_to_rgb
     res, spp = 192, 16
-    c = shade_cases.build("living_room", res)
+    c = shade_cases.build("living_room_tex", res)      # the scene with its image textures (ABI v9)
     S = rb.RefScene(**c["ref"])
     r = dict(c["render"])
     ref, nc, ns = rb.render(S, "bvh", r.pop("eye"), r.pop("look"), r.pop("up"), r.pop("fov"), res, res, spp, c["maxdepth"],

@@ -107,3 +107,34 @@ def test_two_ranks_write_one_image(tmp_path):
                             filename="bad.pfm", scene_name="bad.pbrt", **kw)
     rc, out = _run(sc, d, quiet=False)
     assert "rendezvous" in out and not os.path.exists(os.path.join(d, "bad.pfm")), out
+
+
+@pytest.mark.gpu
+def test_parsed_scene_with_an_image_texture(tmp_path):
+    """`Texture ... "imagemap" ... "bool trilinear" "true"` + `Material "matte" "texture Kd"` through pbrtParseFile: the C++
+    integrator hands the reference's own MIPMap pyramid to the device (ABI v9), the MIP level comes from the camera rays'
+    differentials; against the stock run of the same file."""
+    import pbrt_scenes as ps
+    import hostwf
+    from conftest import load_golden
+    from b200rt import textures
+    d = str(tmp_path)
+    textures.write_tga(os.path.join(d, "leaf.tga"), load_golden("living_room_textures.npz")["leaf"])
+    kw = dict(xres=384, yres=384, spp=8, ground_texture="leaf.tga")
+    scene = ps.killeroo_simple(d, 'Accelerator "bvh"', filename="stock.pfm", **kw)
+    rc, out = _run(scene, d)
+    assert rc == 0, out
+    ref = ps.read_pfm(os.path.join(d, "stock.pfm"))
+    scene = ps.killeroo_simple(d, 'Accelerator "b200" "string tree" "bvh"', integrator='Integrator "b200wavefront" "integer maxdepth" [5]',
+                               filename="b200.pfm", **kw)
+    rc, out2 = _run(scene, d)
+    assert rc == 0 and os.path.exists(os.path.join(d, "b200.pfm")), out2
+    img = ps.read_pfm(os.path.join(d, "b200.pfm"))
+    st = hostwf.image_stats(img, ref)
+    plain = ps.read_pfm(os.path.join(d, "stock.pfm"))
+    print("\nparsed killeroo-simple with a textured ground: %s" % st)
+    assert st["rel_rmse_excl"] <= 1e-4 and st["frac_differing"] < 1e-3, st
+    # and the texture is really there: the ground of the plain scene is a constant (.5 .5 .8)
+    scene = ps.killeroo_simple(d, 'Accelerator "bvh"', filename="plain.pfm", xres=384, yres=384, spp=8)
+    rc, _ = _run(scene, d)
+    assert rc == 0 and np.abs(ps.read_pfm(os.path.join(d, "plain.pfm")) - ref).max() > 0.05

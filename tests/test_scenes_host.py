@@ -69,8 +69,15 @@ def test_living_room_materials_are_the_files_kinds():
     assert kinds["BrushedStainlessSteel"] == 4 + 32 and kinds["Paneling"] == 5 + 32 and kinds["Floor"] == 5 + 32
     assert kinds["Sofa"] == 0 and kinds["Leaves"] == 6      # scene.pbrt:29 "string type" [ "uber" ]
     names = lr["material_names"]
-    # textures/wood.tga and wood5.tga are absent from the reference tree: the reference resolves their Kd to the constant 1
-    assert (lr["materials"][names.index("Floor"), 1:4] == 1).all() and (lr["materials"][names.index("TableWood"), 1:4] == 1).all()
+    # textures/wood.tga and wood5.tga are absent from the reference tree: the reference resolves their Kd to one grey texel 0.5,
+    # gamma-decoded (imagemap.cpp:67-72; pinned against the reference in tests/test_texture.py)
+    grey = np.array([0x3e5b2d9a], np.uint32).view(np.float32)[0]
+    assert (lr["materials"][names.index("Floor"), 1:4] == grey).all() and (lr["materials"][names.index("TableWood"), 1:4] == grey).all()
+    # the files that are there: picture8.tga on the Painting's Kd, leaf.tga on the Leaves' Kd and opacity (ABI v9 slots 18 / 19)
+    assert lr["texture_names"] == ["leaf", "picture8"] and [p.shape for p in lr["texture_pixels"]] == [(271, 365, 3), (853, 1280, 3)]
+    assert lr["materials"][names.index("Painting"), 18] == 2 and tuple(lr["materials"][names.index("Leaves"), 18:20]) == (1, 1)
+    plain = scenes.living_room(64, 36, textures=False)
+    assert (plain["materials"][:, 18:20] == 0).all() and plain["texture_pixels"] is None
     assert lr["tri_normals"].shape == (143163, 9) and np.bincount(lr["prim_flags"]).tolist() == [3008, 0, 140155]
     assert lr["materials"][names.index("PlantPot"), 4] == 1          # scene.pbrt:26 "float sigma" [1]
     assert np.allclose(lr["materials"][names.index("BrushedStainlessSteel"), 1:8],

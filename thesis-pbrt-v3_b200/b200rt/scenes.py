@@ -281,7 +281,7 @@ def matrix_camera(world_to_camera, fov_deg, xres, yres):
                 w2c=np.asarray(world_to_camera, np.float32).reshape(16), fov=float(fov_deg))
 
 
-def living_room(xres=1280, yres=720):
+def living_room(xres=1280, yres=720, textures=True):
     """scenes/living-room/scene.pbrt (BASELINE config 5): the reference's OWN geometry — 65 `plymesh` shapes,
     143 163 triangles in file order, world space — from the committed fixture tests/golden/living_room_mesh.npz
     (made from the reference's scene by tests/golden/make_living_room.py); camera = the file's `Transform` + fov
@@ -295,10 +295,12 @@ def living_room(xres=1280, yres=720):
     kinds: matte keeps its Kd (PlantPot: sigma 1, Oren-Nayar); substrate = "substrate" (its Kd, Ks .04, u = v roughness,
     "remaproughness" false); "metal" with the file's eta / k and roughness .02 unremapped; "glass" index 1.5 (Kr = Kt = 1,
     glass.cpp's defaults); "mirror" Kr .9 (mirror.cpp's default); "uber" (Leaves: Ks 0, uber.cpp's defaults for the rest).
-    Image textures (`imagemap` is not built): textures/wood.tga and wood5.tga are ABSENT from the reference tree, so the
-    reference itself resolves Floor's and TableWood's Kd to the constant 1 (imagemap.cpp:67-71) and so does this table; the
-    two files that are there (picture8.tga on the Painting's 2 triangles, leaf.tga as Kd and opacity of the Leaves' 3 264) are
-    SUBSTITUTED by the constants .5 (Kd) and 1 (opacity), identically on the reference side of the parity test.
+    Image textures (scene.pbrt:8-12, all "bool trilinear" true): textures/wood.tga and wood5.tga are ABSENT from the reference tree,
+    so the reference itself replaces them by one grey texel 0.5 (imagemap.cpp:67-72) which ImageTexture's convertIn gamma-decodes:
+    Floor's and TableWood's Kd is the constant 0x3e5b2d9a = 0.21404114 here too.  The two files that are there — picture8.tga on
+    the Painting's 2 triangles, leaf.tga as Kd and opacity of the Leaves' 3 264 — are `textures` (tests/golden/
+    living_room_textures.npz holds their pixels), named by slots 18 / 19 of the material records; `textures=False` substitutes the
+    constants .5 (Kd) and 1 (opacity) for them (the round-2 per-pixel goldens before ABI v9).
     `tri_normals` / `prim_flags`: the PLY files' vertex normals in world space (TriangleMesh applies ObjectToWorld to them,
     triangle.cpp:61-64; 140 155 triangles have them, 3 008 do not), interpolated shading normals as triangle.cpp:348-400.
     `legacy_materials` keeps the round-1 matte + plastic table (the numbers of profiles/r01_living_room_*.json).  The TRAVERSAL
@@ -309,12 +311,15 @@ def living_room(xres=1280, yres=720):
     uv = UV[idx].reshape(-1, 6).astype(np.float32)
     kinds, kd = [str(k) for k in z["material_kinds"]], z["material_kd"]
     rough = {"Floor": .15, "TableWood": .05, "Paneling": .2}   # scene.pbrt:13,14,18 ("remaproughness" false in the file)
+    tex_files = ["leaf", "picture8"]   # textures/leaf.tga (Texture04, Texture05), textures/picture8.tga (Texture03)
+    tex_of = {"Texture03": "picture8", "Texture04": "leaf", "Texture05": "leaf"}
     absent = {"Texture01", "Texture02"}   # textures/wood.tga, wood5.tga: not in the reference tree -> the constant 1
     mats = np.zeros((len(kinds), 20), np.float32)
     legacy = np.zeros((len(kinds), 8), np.float32)
     for i, (k, name) in enumerate(zip(kinds, [str(n) for n in z["material_names"]])):
         tex = str(z["material_tex"][i])
-        c = kd[i] if kd[i][0] >= 0 else np.array([1, 1, 1] if tex in absent else [.5, .5, .5], np.float32)
+        grey = np.array([0x3e5b2d9a] * 3, np.uint32).view(np.float32)    # InverseGammaCorrect(0.5f): the reference's stand-in for a missing file
+        c = kd[i] if kd[i][0] >= 0 else (grey if tex in absent else np.array([.5, .5, .5], np.float32))
         cl = kd[i] if kd[i][0] >= 0 else np.array([.5, .5, .5], np.float32)
         legacy[i] = [0, .5, .5, .5, 0, 0, 0, 0]
         if k == "substrate":
@@ -322,6 +327,8 @@ def living_room(xres=1280, yres=720):
             legacy[i] = [1, cl[0], cl[1], cl[2], .04, .04, .04, rough[name]]
         elif k == "matte":
             mats[i, :8] = [0, c[0], c[1], c[2], 0, 0, 0, 0]
+            if textures and tex in tex_of:   # Painting: "texture Kd" Texture03
+                mats[i, 18] = 1 + tex_files.index(tex_of[tex])
             legacy[i] = [0, cl[0], cl[1], cl[2], 0, 0, 0, 0]
             if name == "PlantPot":   # scene.pbrt:26 "float sigma" [1]: Oren-Nayar
                 mats[i, :8] = [0, c[0], c[1], c[2], 1, 0, 0, 0]
@@ -333,17 +340,32 @@ def living_room(xres=1280, yres=720):
             mats[i, :8] = [2, .9, .9, .9, 0, 0, 0, 0]
         elif k == "uber":      # scene.pbrt:29 Leaves: Ks 0; uber.cpp:102-128 defaults Kr 0, Kt 0, roughness .1, eta 1.5, opacity 1
             mats[i] = [6, c[0], c[1], c[2], 0, 0, 0, .1, 0, 0, 0, 0, 0, 0, 1, 1, 1, 1.5, 0, 0]
+            if textures:       # "texture Kd" Texture04, "texture opacity" Texture05: both textures/leaf.tga
+                mats[i, 18] = mats[i, 19] = 1 + tex_files.index("leaf")
         else:
             raise ValueError("scenes/living-room material kind %r" % k)
     # TransformBegin Transform [-1 0 8.74228e-008 0  -8.74228e-008 0 -1 0  0 1 0 0  0 0 0 1] LightSource "infinite"
     # (scene.pbrt:163-166; column-major in the file) -> row-major LightToWorld rotation
     l2w = np.array([-1, 0, 8.74228e-008, 0, -8.74228e-008, 0, -1, 0, 0, 1, 0, 0, 0, 0, 0, 1], np.float64).reshape(4, 4).T[:3, :3]
     tn = z["N"][idx].reshape(-1, 9).astype(np.float32)
-    return dict(name="living-room", tri_verts=tv, tri_uvs=uv, tri_normals=tn, prim_flags=z["tri_flags"].astype(np.uint8),
+    tex_px = None
+    if textures:
+        zt = np.load(os.path.join(_GOLDEN, "living_room_textures.npz"))
+        tex_px = [zt[n] for n in tex_files]      # 8-bit RGB, row 0 = top (what ReadImageTGA returns before / 255.f)
+    return dict(name="living-room", texture_names=tex_files, texture_pixels=tex_px, tri_verts=tv, tri_uvs=uv, tri_normals=tn, prim_flags=z["tri_flags"].astype(np.uint8),
                 camera=matrix_camera(z["world_to_camera"], 58.715508, xres, yres),
                 materials=mats, legacy_materials=legacy, prim_material=z["tri_material"].astype(np.uint8), material_names=[str(n) for n in z["material_names"]],
                 material_kinds=kinds, infinite_light=dict(L=np.array([1, 1, 1], np.float32), light_to_world=l2w),
                 maxdepth=65, spp=64)
+
+
+def living_room_textures(sc):
+    """The `textures=` argument of WavefrontPathIntegrator for scenes.living_room(): the MIPMap pyramids of the scene's image
+    files (None when the scene was made with textures=False)."""
+    if not sc.get("texture_pixels"):
+        return None
+    from . import textures as tx
+    return [tx.ImageTexture(rgb8=px) for px in sc["texture_pixels"]]
 
 
 # ---- procedural stand-ins --------------------------------------------------------------------

@@ -20,7 +20,8 @@ class RenderDesc(C.Structure):
                 ("crop", C.c_uint32 * 4), ("light_to_world", C.c_float * 9),
                 ("sampler", C.c_uint32), ("camera_exact", C.c_uint32), ("raster_to_camera", C.c_float * 16),
                 ("camera_to_world", C.c_float * 16), ("sobol_matrices32", C.c_void_p), ("sobol_vdc", C.c_void_p),
-                ("sobol_vdc_inv", C.c_void_p), ("sobol_vdc_rows", C.c_uint32), ("material_stride", C.c_uint32)]
+                ("sobol_vdc_inv", C.c_void_p), ("sobol_vdc_rows", C.c_uint32), ("material_stride", C.c_uint32),
+                ("textures", C.c_void_p), ("n_textures", C.c_uint32)]
 
 
 SAMPLERS = {"hash": 0, "halton": 1, "sobol": 2}
@@ -59,7 +60,8 @@ class WavefrontPathIntegrator:
 
     def __init__(self, camera, spp=8, maxdepth=5, light_pos=(0, 0, 0), light_I=(1, 1, 1), kd=(.5, .5, .5),
                  rank=0, world=1, seed=0, tile_size=16, max_batch=0, sphere_light=None, materials=None,
-                 prim_material=None, distant_light=None, crop=None, infinite_light=None, sampler="halton", sobol_tables=None):
+                 prim_material=None, distant_light=None, crop=None, infinite_light=None, sampler="halton", sobol_tables=None,
+                 textures=None):
         """sphere_light=(radius, prim): `AreaLightSource "area" "color L" light_I` on the full sphere primitive number
         `prim` of the aggregate, centred at light_pos (sampled with MIS like EstimateDirect).  materials: (n, 8) rows
         (kind, Kd.rgb, Ks.rgb, roughness) + prim_material: (n_prims,) uint8 index per primitive.
@@ -74,7 +76,9 @@ class WavefrontPathIntegrator:
         reference camera's own matrices (b200rt_camera_perspective) and camera rays are bit-identical to the reference's.
         sampler: "hash" | "halton" | "sobol" (Sampler "halton" / "sobol" of the reference, same sample values and
         dimension order); sobol needs sobol_tables = (SobolMatrices32, VdCSobolMatrices, VdCSobolMatricesInv) arrays.
-        materials: (n, 8) rows, or (n, 20) rows (needed for "uber", kind 6)."""
+        materials: (n, 8) rows, or (n, 20) rows (needed for "uber", kind 6).
+        textures: list of b200rt.textures.ImageTexture (`Texture ... "imagemap"`, trilinear); slot 18 of a 20-float material row =
+        1 + index of the texture its Kd reads, slot 19 = 1 + index of uber's opacity texture."""
         d = RenderDesc()
         if "lookat" in camera or "w2c" in camera:
             la = None if camera.get("lookat") is None else np.ascontiguousarray(camera["lookat"], np.float32).reshape(9)
@@ -122,6 +126,11 @@ class WavefrontPathIntegrator:
             self._pm = np.ascontiguousarray(prim_material, np.uint8)
             d.materials, d.n_materials, d.material_stride = self._mats.ctypes.data, len(self._mats), stride
             d.prim_material = self._pm.ctypes.data
+        if textures:
+            from . import textures as tx
+            self._textures = list(textures)
+            self._tex_array = tx.texture_array(self._textures)
+            d.textures, d.n_textures = C.cast(self._tex_array, C.c_void_p), len(self._textures)
         self.desc = d
 
     @property

@@ -11,7 +11,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "b200rt", "libb200rt.so")
 OBJ = os.path.join(HERE, "_obj")
-SOURCES = ["b200rt.cu", "wavefront.cu", "film_reduce.cu", "build_rbsp.cu", "no_alloc.cu", "build_bvh.cpp", "build_kd.cpp", "wf_sampler_host.cpp", "wf_camera_host.cpp", "wf_setup_host.cpp"]
+SOURCES = ["b200rt.cu", "wavefront.cu", "film_reduce.cu", "build_rbsp.cu", "no_alloc.cu", "build_bvh.cpp", "build_kd.cpp", "wf_sampler_host.cpp", "wf_camera_host.cpp", "wf_setup_host.cpp", "wf_texture_host.cpp"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-fmad=false",
          "--shared", "-Xcompiler", "-fPIC,-ffp-contract=off,-fno-fast-math", "-cudart", "static"]

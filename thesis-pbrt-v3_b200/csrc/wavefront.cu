@@ -266,6 +266,10 @@ struct Workspace {
     float4 *misRays = nullptr, *misContrib = nullptr;   // lights with area only (EstimateDirect's BSDF-sampled rays)
     uint32_t *misPath = nullptr;
     float *mats = nullptr;      // kMatFloats per material
+    WfTexture *tex = nullptr;   // image textures (ABI v9) and their pyramids
+    float *texData = nullptr;
+    const void *texHost = nullptr, *texFirst = nullptr;
+    uint32_t texN = 0;
     uint8_t *primMat = nullptr;
     size_t mats_n = 0, primMat_n = 0;
     uint4 *perRay = nullptr;   // heat-map mode only
@@ -333,7 +337,7 @@ void free_ws(Workspace *w) {
     for (int i = 0; i < Workspace::kMaxSets - 1; ++i) free_alt(w, i);
     for (int k = 0; k < Workspace::kMaxSets; ++k) { if (w->side[k]) cudaStreamDestroy(w->side[k]); if (w->evJoin[k]) cudaEventDestroy(w->evJoin[k]); }
     if (w->evFork) cudaEventDestroy(w->evFork);
-    cudaFree(w->film); cudaFree(w->heat); cudaFree(w->mats); cudaFree(w->primMat);
+    cudaFree(w->film); cudaFree(w->heat); cudaFree(w->mats); cudaFree(w->primMat); cudaFree(w->tex); cudaFree(w->texData);
     cudaFree(w->splatCount); cudaFree(w->splatPix); cudaFree(w->splatVal);
     cudaFree(w->haltonPerms); cudaFree(w->haltonDims); cudaFree(w->sobol32); cudaFree(w->sobolVdc);
     if (w->hCounts) cudaFreeHost(w->hCounts);
@@ -526,7 +530,7 @@ static int render_impl(b200rt_scene *s, const b200rt_render_desc *d, float *film
         std::vector<float> dev((size_t)d->n_materials * kMatFloats);
         bool hasSpec = false;
         for (uint32_t k = 0; k < d->n_materials; ++k)
-            if (!material_lobes(d->materials + (size_t)mstride * k, mstride, k, dev.data() + (size_t)k * kMatFloats, &hasSpec)) return B200RT_EINVAL;
+            if (!material_lobes(d->materials + (size_t)mstride * k, mstride, k, dev.data() + (size_t)k * kMatFloats, &hasSpec, d->textures ? d->n_textures : 0u)) return B200RT_EINVAL;
         P.has_specular = hasSpec ? 1u : 0u;
         if (w->mats_n < d->n_materials) { cudaFree(w->mats); w->mats = nullptr; WCU(cudaMalloc(&w->mats, (size_t)d->n_materials * kMatFloats * 4)); w->mats_n = d->n_materials; }
         if (w->primMat_n < s->n_prims) { cudaFree(w->primMat); w->primMat = nullptr; WCU(cudaMalloc(&w->primMat, s->n_prims)); w->primMat_n = s->n_prims; }
@@ -535,6 +539,43 @@ static int render_impl(b200rt_scene *s, const b200rt_render_desc *d, float *film
         WCU(cudaMemcpy(w->mats, dev.data(), dev.size() * 4, cudaMemcpyHostToDevice));
         WCU(cudaMemcpy(w->primMat, d->prim_material, s->n_prims, cudaMemcpyHostToDevice));
         P.mats = w->mats; P.primMat = w->primMat;
+    }
+    P.tex = nullptr; P.nTex = 0;
+    if (d->materials && d->textures && d->n_textures) {
+        // image textures: the pyramids are uploaded when the host array (pointer, count, first texel pointer) changes
+        if (!P.cam_exact) return set_error(B200RT_EINVAL, "image textures need the exact camera (camera_exact): the ray differentials come from its matrices");
+        if (w->texHost != (const void *)d->textures || w->texN != d->n_textures || w->texFirst != (const void *)d->textures[0].texels) {
+            cudaFree(w->texData); cudaFree(w->tex); w->texData = nullptr; w->tex = nullptr;
+            std::vector<WfTexture> T(d->n_textures);
+            size_t total = 0;
+            for (uint32_t k = 0; k < d->n_textures; ++k) {
+                const b200rt_texture &t = d->textures[k];
+                if (!t.texels || !t.width || !t.height || (t.width & (t.width - 1)) || (t.height & (t.height - 1)) || t.n_levels == 0 || t.n_levels > 16)
+                    return set_error(B200RT_EINVAL, "texture %u: a pyramid with power-of-two level 0 and 1..16 levels is required (b200rt_mipmap_build)", k);
+                T[k].nLevels = t.n_levels; T[k].w0 = t.width; T[k].h0 = t.height;
+                T[k].su = t.su; T[k].sv = t.sv; T[k].du = t.du; T[k].dv = t.dv;
+                size_t off = 0;
+                for (uint32_t l = 0; l < 16; ++l) {
+                    T[k].levelOffset[l] = (uint32_t)off;
+                    if (l < t.n_levels) off += (size_t)std::max(1u, t.width >> l) * std::max(1u, t.height >> l);
+                }
+                total += off;
+            }
+            WCU(cudaMalloc(&w->texData, std::max<size_t>(total, 1) * 3 * sizeof(float)));
+            size_t base = 0;
+            for (uint32_t k = 0; k < d->n_textures; ++k) {
+                const b200rt_texture &t = d->textures[k];
+                size_t n = 0;
+                for (uint32_t l = 0; l < t.n_levels; ++l) n += (size_t)std::max(1u, t.width >> l) * std::max(1u, t.height >> l);
+                WCU(cudaMemcpy(w->texData + base * 3, t.texels, n * 3 * sizeof(float), cudaMemcpyHostToDevice));
+                T[k].texels = w->texData + base * 3;
+                base += n;
+            }
+            WCU(cudaMalloc(&w->tex, T.size() * sizeof(WfTexture)));
+            WCU(cudaMemcpy(w->tex, T.data(), T.size() * sizeof(WfTexture), cudaMemcpyHostToDevice));
+            w->texHost = d->textures; w->texN = d->n_textures; w->texFirst = d->textures[0].texels;
+        }
+        P.tex = w->tex; P.nTex = d->n_textures;
     }
     P.primUV = s->d_prim_uv; P.primN = s->d_prim_n; P.primFlags = s->d_prim_flags;
     // camera 5 + per bounce: light choice 1 + uLight 2 + uScattering 2 + BSDF 2 + Russian roulette 1

@@ -38,7 +38,7 @@ float clamp01inf(float v) { return v < 0.f ? 0.f : v; }   // Spectrum::Clamp(0, 
 
 }  // namespace
 
-bool material_lobes(const float *rec, uint32_t stride, uint32_t index, float *out, bool *hasSpecular) {
+bool material_lobes(const float *rec, uint32_t stride, uint32_t index, float *out, bool *hasSpecular, uint32_t nTextures) {
     std::memset(out, 0, sizeof(float) * kMatFloats);
     const float kf = rec[0];
     if (!(kf >= 0.f && kf < 64.f) || kf != (float)(uint32_t)kf) { set_error(B200RT_EUNSUPPORTED, "material %u: bad kind", index); return false; }
@@ -130,6 +130,43 @@ bool material_lobes(const float *rec, uint32_t stride, uint32_t index, float *ou
     }
     std::memcpy(out, &n, 4);
     out[1] = eta;
+    // ABI v9: image textures on Kd (slot 18) and on uber's opacity (slot 19), texture index + 1.  The lobes of such a material
+    // depend on the hit, so the record switches to the TEXTURED layout wf_shade.cuh's textured_lobes reads (the constant
+    // record above has served as the validation of the kind, the roughness and the constants).
+    if (stride >= 20 && (rec[18] != 0.f || rec[19] != 0.f)) {
+        const float kdT = rec[18], opT = rec[19];
+        if (!(kdT >= 0.f && opT >= 0.f && kdT == (float)(uint32_t)kdT && opT == (float)(uint32_t)opT && kdT <= (float)nTextures && opT <= (float)nTextures)) {
+            set_error(B200RT_EINVAL, "material %u: texture indices (%g, %g) outside the %u textures of the description", index, kdT, opT, nTextures);
+            return false;
+        }
+        if (!(kind == B200RT_MAT_MATTE || kind == B200RT_MAT_PLASTIC || kind == B200RT_MAT_SUBSTRATE || kind == B200RT_MAT_UBER) || (opT != 0.f && kind != B200RT_MAT_UBER)) {
+            set_error(B200RT_EUNSUPPORTED, "material %u: image textures are supported on the Kd of matte / plastic / substrate / uber and on uber's opacity", index);
+            return false;
+        }
+        const float alpha = (kind == B200RT_MAT_MATTE) ? 0.f : (remap ? roughness_to_alpha(rough) : rough);
+        if (kind != B200RT_MAT_MATTE && !(alpha > 0.f)) { set_error(B200RT_EINVAL, "material %u: roughness must be > 0", index); return false; }
+        std::memset(out, 0, sizeof(float) * kMatFloats);
+        const uint32_t kdI = (uint32_t)kdT, opI = (uint32_t)opT, k32 = kind;
+        std::memcpy(out + 2, &kdI, 4); std::memcpy(out + 3, &opI, 4);
+        std::memcpy(out + 4, &k32, 4);
+        for (int c = 0; c < 3; ++c) { out[5 + c] = c0[c]; out[8 + c] = c1[c]; }
+        out[11] = alpha;
+        if (kind == B200RT_MAT_UBER) {
+            for (int c = 0; c < 3; ++c) { out[12 + c] = clamp01inf(rec[8 + c]); out[15 + c] = clamp01inf(rec[11 + c]); out[18 + c] = clamp01inf(rec[14 + c]); }
+            out[21] = rec[17];
+            *hasSpecular = true;   // 1 - opacity may be non-black at some hit
+        } else {
+            out[18] = out[19] = out[20] = 1.f;
+        }
+        if (kind == B200RT_MAT_MATTE) {
+            const float sig = std::min(std::max(rec[4], 0.f), 90.f);
+            out[8] = out[9] = out[10] = 0.f;   // slot 4 of a matte record is sigma, not Ks
+            if (sig != 0) {
+                const float sr = (3.14159265358979323846f / 180.f) * sig, s2 = sr * sr;
+                out[22] = 1.f - (s2 / (2.f * (s2 + 0.33f))); out[23] = 0.45f * s2 / (s2 + 0.09f);
+            }
+        }
+    }
     return true;
 }
 

@@ -8,7 +8,7 @@ int set_error(int code, const char *fmt, ...);
 int tiling_of(const b200rt_render_desc *d, WfTiling *t);
 // One material record -> its lobes, in the order the material's ComputeScatteringFunctions adds BxDFs.
 // rec: `stride` floats (b200rt_wavefront.h).  out: kMatFloats floats.  Returns false (with the error set) on a bad record.
-bool material_lobes(const float *rec, uint32_t stride, uint32_t index, float *out, bool *hasSpecular);
+bool material_lobes(const float *rec, uint32_t stride, uint32_t index, float *out, bool *hasSpecular, uint32_t nTextures = 0);
 // Light block of WfParams from the description; returns an error code for unsupported / inconsistent lights.
 int light_of(const b200rt_render_desc *d, uint32_t n_prims, WfLight *Lt);
 }  // namespace b200rt

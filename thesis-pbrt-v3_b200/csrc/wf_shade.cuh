@@ -6,6 +6,7 @@
 #pragma once
 #include "../../include/b200rt_wavefront.h"
 #include "wf_bsdf.cuh"
+#include "wf_texture.cuh"
 #include "wf_sampler.cuh"
 
 namespace b200rt {
@@ -41,6 +42,8 @@ struct WfParams {
     const uint8_t *primFlags; // bit 0: reverseOrientation ^ transformSwapsHandedness; bit 1: the primitive has vertex normals
     uint32_t has_specular;    // some material has a specular lobe (path.cpp's specularBounce / etaScale bookkeeping is live)
     WfSampler smp;
+    const WfTexture *tex;     // imagemap textures (ABI v9) or nullptr; materials name them in their header words 2 / 3
+    uint32_t nTex;
 };
 
 // path slot -> (pixel x, y inside the crop window, sample); false when the slot lies outside the image (edge tiles)
@@ -97,6 +100,8 @@ constexpr uint32_t kCameraDims = 5;   // the first dimension PathIntegrator::Li 
 struct WfIsect {
     V3 p, pError, n, wo;   // Interaction::p, pError, n (geometric, oriented), wo = Normalize(-ray.d)
     V3 ns, dpdu;           // shading.n, shading.dpdu
+    V3 gdpdu, gdpdv;       // SurfaceInteraction::dpdu / dpdv (what ComputeDifferentials solves with)
+    float u, v;            // SurfaceInteraction::uv = b0 uv0 + b1 uv1 + b2 uv2 (triangle.cpp:331)
 };
 WF_HD void triangle_isect(const WfParams &P, uint32_t prim, V3 p0, V3 p1, V3 p2, float b0, float b1, float b2, V3 rayD, WfIsect &it) {
     float uv[6] = {0.f, 0.f, 1.f, 0.f, 1.f, 1.f};
@@ -144,6 +149,54 @@ WF_HD void triangle_isect(const WfParams &P, uint32_t prim, V3 p0, V3 p1, V3 p2,
         n = vneg(n); ns = n;
     }
     it.n = n; it.ns = ns; it.dpdu = sdpdu;
+    it.gdpdu = dpdu; it.gdpdv = dpdv;
+    it.u = b0 * uv[0] + b1 * uv[2] + b2 * uv[4];
+    it.v = b0 * uv[1] + b1 * uv[3] + b2 * uv[5];
+}
+
+// Lobes of a material whose Kd and / or opacity is an image texture, rebuilt per hit from the texture values (the constant-
+// texture materials get theirs once on the host, wf_setup_host.cpp material_lobes — same rules: matte.cpp:44-62,
+// plastic.cpp:44-70, substrate.cpp:45-66, uber.cpp:45-100).  m: the material's 64-float record in its TEXTURED layout:
+//   m[4] kind, m[5..7] Kd, m[8..10] Ks, m[11] alpha (already remapped), m[12..14] Kr, m[15..17] Kt, m[18..20] opacity,
+//   m[21] eta, m[22], m[23] Oren-Nayar A, B (sigma > 0) or 0, 0
+WF_HD void put_lobe(float *L, uint32_t &n, uint32_t kind, V3 c0, V3 c1, float a, float e0, float e1) {
+    float *l = L + n * kLobeFloats;
+    l[0] = u2f(kind);
+    l[1] = c0.x; l[2] = c0.y; l[3] = c0.z; l[4] = c1.x; l[5] = c1.y; l[6] = c1.z;
+    l[7] = a; l[8] = e0; l[9] = e1;
+    for (int i = 10; i < kLobeFloats; ++i) l[i] = 0.f;
+    ++n;
+}
+WF_HD V3 spec_clamp0(V3 c) { return v3(c.x < 0.f ? 0.f : c.x, c.y < 0.f ? 0.f : c.y, c.z < 0.f ? 0.f : c.z); }   // Spectrum::Clamp()
+WF_HD void textured_lobes(const float *m, bool haveKd, V3 kdTex, bool haveOp, V3 opTex, float *L, uint32_t &n, float &eta) {
+    const uint32_t kind = f2u(m[4]);
+    const V3 Kd = haveKd ? spec_clamp0(kdTex) : v3(m[5], m[6], m[7]);
+    const V3 Ks = v3(m[8], m[9], m[10]), zero = v3(0.f, 0.f, 0.f);
+    const float alpha = m[11];
+    n = 0;
+    eta = 1.f;
+    if (kind == B200RT_MAT_MATTE) {
+        if (!spec_black(Kd)) {
+            if (m[22] == 0.f && m[23] == 0.f) put_lobe(L, n, LOBE_LAMBERT, Kd, zero, 0, 0, 0);
+            else put_lobe(L, n, LOBE_OREN, Kd, zero, 0, m[22], m[23]);
+        }
+    } else if (kind == B200RT_MAT_PLASTIC) {
+        if (!spec_black(Kd)) put_lobe(L, n, LOBE_LAMBERT, Kd, zero, 0, 0, 0);
+        if (!spec_black(Ks)) put_lobe(L, n, LOBE_MICRO_DIEL, Ks, zero, alpha, 1.5f, 1.f);
+    } else if (kind == B200RT_MAT_SUBSTRATE) {
+        if (!spec_black(Kd) || !spec_black(Ks)) put_lobe(L, n, LOBE_BLEND, Kd, Ks, alpha, 0, 0);
+    } else {   // B200RT_MAT_UBER
+        const float e = m[21];
+        const V3 op = haveOp ? spec_clamp0(opTex) : v3(m[18], m[19], m[20]);
+        const V3 t = spec_clamp0(v3(-op.x + 1.f, -op.y + 1.f, -op.z + 1.f));
+        if (!spec_black(t)) { eta = 1.f; put_lobe(L, n, LOBE_SPEC_TRANS, t, zero, 0, 1.f, 1.f); }
+        else eta = e;
+        const V3 kd = spec_mul(op, Kd), ks = spec_mul(op, Ks), kr = spec_mul(op, v3(m[12], m[13], m[14])), kt = spec_mul(op, v3(m[15], m[16], m[17]));
+        if (!spec_black(kd)) put_lobe(L, n, LOBE_LAMBERT, kd, zero, 0, 0, 0);
+        if (!spec_black(ks)) put_lobe(L, n, LOBE_MICRO_DIEL, ks, zero, alpha, 1.f, e);
+        if (!spec_black(kr)) put_lobe(L, n, LOBE_SPEC_REFL_DIEL, kr, zero, 0, 1.f, e);
+        if (!spec_black(kt)) put_lobe(L, n, LOBE_SPEC_TRANS, kt, zero, 0, 1.f, e);
+    }
 }
 
 // ---- what one vertex produces ------------------------------------------------------------------------------------------
@@ -254,6 +307,26 @@ WF_HD float light_pdf(const WfLight &Lt, const WfIsect &it, V3 wi) {
     return 1.f / (2.f * kPiF * kPiF * sinTheta);
 }
 
+// The lobes of a textured material at this hit (out of line: it is rare and register-hungry).
+// ComputeScatteringFunctions -> ComputeDifferentials(ray): only the camera ray has differentials.
+WF_HD_NOINLINE void textured_material(const WfParams &P, const float *m, uint32_t depth, uint32_t x, uint32_t y, uint32_t s, V3 rayO, V3 rayD,
+                                      const WfIsect &it, float *L, uint32_t &n, float &eta) {
+    const uint32_t kdT = f2u(m[2]), opT = f2u(m[3]);
+    WfUVDiff D = {0.f, 0.f, 0.f, 0.f};
+    if (depth == 0 && P.cam_exact) {
+        PathSampler cs;
+        path_sampler_init(P, x, y, s, 0, cs);
+        const float u0 = get1d(P, cs), u1 = get1d(P, cs);
+        V3 rxO, rxD, ryO, ryD;
+        camera_ray_diff_ref(P.cm, (float)cs.px + u0, (float)cs.py + u1, 1.f / sqrtf((float)P.tl.spp), rayO, rayD, rxO, rxD, ryO, ryD);
+        D = compute_differentials(it.p, it.n, it.gdpdu, it.gdpdv, rxO, rxD, ryO, ryD);
+    }
+    V3 kdV = v3(0.f, 0.f, 0.f), opV = v3(0.f, 0.f, 0.f);
+    if (kdT) kdV = tex_evaluate(P.tex[kdT - 1], it.u, it.v, D);
+    if (opT) opV = tex_evaluate(P.tex[opT - 1], it.u, it.v, D);
+    textured_lobes(m, kdT != 0, kdV, opT != 0, opV, L, n, eta);
+}
+
 // One bounce of PathIntegrator::Li for a path whose ray (rayO, rayD) found `hit`.
 //   bt  : beta.xyz and the (specularBounce, etaScale) code in w
 //   dim : the path's next sample dimension
@@ -291,9 +364,14 @@ WF_HD void shade_vertex(const WfParams &P, uint32_t depth, uint32_t x, uint32_t 
     bs.ts = vcross(bs.ns, bs.ss);
     bs.leanKd = spec3(P.kd);
     bs.lobes = nullptr; bs.nLobes = spec_black(bs.leanKd) ? 0u : 1u; bs.eta = 1.f;
+    float texLobes[kMaxLobes * kLobeFloats];
     if (FULL && P.mats) {
         const float *m = P.mats + (size_t)P.primMat[prim] * kMatFloats;
         bs.nLobes = f2u(m[0]); bs.eta = m[1]; bs.lobes = m + 4;
+        if (P.tex && (f2u(m[2]) | f2u(m[3]))) {
+            textured_material(P, m, depth, x, y, s, rayO, rayD, it, texLobes, bs.nLobes, bs.eta);
+            bs.lobes = texLobes;
+        }
     }
     PathSampler ps;
     path_sampler_init(P, x, y, s, dim, ps);

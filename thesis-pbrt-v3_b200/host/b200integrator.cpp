@@ -39,6 +39,9 @@
 #include "materials/metal.h"
 #include "materials/substrate.h"
 #include "materials/uber.h"
+#include "core/texture.h"         // UVMapping2D::su / sv / du / dv
+#include "core/mipmap.h"          // MIPMap::pyramid / doTrilinear / wrapMode
+#include "textures/imagemap.h"    // ImageTexture::mapping / mipmap
 #include "core/film.h"   // Film::pixels / Pixel::stats for "bool generalstats" (no accessor either)
 #include "core/transform.h"       // AnimatedTransform::startTransform
 #include "core/camera.h"          // ProjectiveCamera::RasterToCamera / lensRadius
@@ -257,6 +260,43 @@ void B200WavefrontIntegrator::Render(const Scene &scene) {
     // (constant Kd / Ks / roughness, remaproughness true), one record per distinct Material object
     std::vector<float> mats;
     std::vector<uint8_t> primMat(accel->primitiveCount(), 0);
+    // `Texture ... "imagemap"` on a Kd or on uber's opacity: the pyramid of the reference's own MIPMap goes to the device as it is
+    // (ABI v9); trilinear filtering, UV mapping and Repeat wrap only — what scenes/living-room and scenes/sponza ask for
+    std::vector<std::vector<float>> texData;
+    std::vector<b200rt_texture> texRecs;
+    std::map<const void *, int> texSeen;
+    bool texBad = false;
+    auto textureIndex = [&](const std::shared_ptr<Texture<Spectrum>> &t) -> int {   // 1-based; 0 = not an image texture
+        const auto *im = dynamic_cast<const ImageTexture<RGBSpectrum, Spectrum> *>(t.get());
+        if (!im) return 0;
+        auto it = texSeen.find(im);
+        if (it != texSeen.end()) return it->second;
+        const UVMapping2D *uv = dynamic_cast<const UVMapping2D *>(im->mapping.get());
+        const MIPMap<RGBSpectrum> *mm = im->mipmap;
+        if (!uv || !mm || (!mm->doTrilinear && mm->Levels() > 1) || mm->wrapMode != ImageWrap::Repeat || mm->Levels() > 16) {
+            Error("b200wavefront: image textures are supported with \"uv\" mapping, \"bool trilinear\" \"true\" and \"repeat\" wrap only");
+            texBad = true;
+            return 0;
+        }
+        std::vector<float> px;
+        for (int l = 0; l < mm->Levels(); ++l) {
+            const BlockedArray<RGBSpectrum> &a = *mm->pyramid[l];
+            for (int tt = 0; tt < a.vSize(); ++tt)
+                for (int ss = 0; ss < a.uSize(); ++ss) {
+                    Float rgb[3];
+                    a(ss, tt).ToRGB(rgb);
+                    px.insert(px.end(), rgb, rgb + 3);
+                }
+        }
+        texData.push_back(std::move(px));
+        b200rt_texture r;
+        r.texels = nullptr;   // set below, once texData stops moving
+        r.width = (uint32_t)mm->pyramid[0]->uSize(); r.height = (uint32_t)mm->pyramid[0]->vSize(); r.n_levels = (uint32_t)mm->Levels();
+        r.su = uv->su; r.sv = uv->sv; r.du = uv->du; r.dv = uv->dv;
+        texRecs.push_back(r);
+        texSeen[im] = (int)texRecs.size();
+        return (int)texRecs.size();
+    };
     {
         // one record per distinct (Material object, orientation flag): glass needs to know on which side of a triangle the
         // shape's normal is (Shape::reverseOrientation ^ transformSwapsHandedness, triangle.cpp:421-424)
@@ -282,6 +322,7 @@ void B200WavefrontIntegrator::Render(const Scene &scene) {
                     rec[0] = (float)(B200RT_MAT_PLASTIC + (pm->remapRoughness ? 0 : B200RT_MAT_NO_REMAP));
                     for (int c = 0; c < 3; ++c) { rec[1 + c] = kd[c]; rec[4 + c] = ks[c]; }
                     rec[7] = pm->roughness->Evaluate(si);
+                    rec[18] = (float)textureIndex(pm->Kd);
                 } else if (const MetalMaterial *me = dynamic_cast<const MetalMaterial *>(m)) {
                     const Float ur = me->uRoughness ? me->uRoughness->Evaluate(si) : me->roughness->Evaluate(si);
                     const Float vr = me->vRoughness ? me->vRoughness->Evaluate(si) : me->roughness->Evaluate(si);
@@ -300,6 +341,7 @@ void B200WavefrontIntegrator::Render(const Scene &scene) {
                     rec[0] = (float)(B200RT_MAT_SUBSTRATE + (sm->remapRoughness ? 0 : B200RT_MAT_NO_REMAP));
                     for (int c = 0; c < 3; ++c) { rec[1 + c] = kd[c]; rec[4 + c] = ks[c]; }
                     rec[7] = sm->nu->Evaluate(si);
+                    rec[18] = (float)textureIndex(sm->Kd);
                 } else if (const UberMaterial *um = dynamic_cast<const UberMaterial *>(m)) {
                     // Material "uber" (uber.cpp:45-100): constant textures only, isotropic roughness
                     if (um->bumpMap || um->roughnessu || um->roughnessv) { Error("b200wavefront: only isotropic uber without a bump map is supported"); return; }
@@ -313,6 +355,8 @@ void B200WavefrontIntegrator::Render(const Scene &scene) {
                     for (int c = 0; c < 3; ++c) { rec[1 + c] = kd[c]; rec[4 + c] = ks[c]; rec[8 + c] = kr[c]; rec[11 + c] = kt[c]; rec[14 + c] = op[c]; }
                     rec[7] = um->roughness->Evaluate(si);
                     rec[17] = um->eta->Evaluate(si);
+                    rec[18] = (float)textureIndex(um->Kd);
+                    rec[19] = (float)textureIndex(um->opacity);
                 } else if (const MirrorMaterial *mm = dynamic_cast<const MirrorMaterial *>(m)) {
                     if (mm->bumpMap) { Error("b200wavefront: mirror with a bump map is not supported"); return; }
                     Float kr[3];
@@ -331,27 +375,32 @@ void B200WavefrontIntegrator::Render(const Scene &scene) {
                     for (int c = 0; c < 3; ++c) { rec[1 + c] = kr[c]; rec[4 + c] = kt[c]; }
                     rec[7] = gm->index->Evaluate(si);
                 } else if (const MatteMaterial *mt = dynamic_cast<const MatteMaterial *>(m);
-                           mt && !mt->bumpMap && mt->sigma->Evaluate(si) != 0) {
-                    // Material "matte" with "float sigma" > 0: an Oren-Nayar lobe (matte.cpp:55-61); sigma has no accessor
+                           mt && !mt->bumpMap && (mt->sigma->Evaluate(si) != 0 || dynamic_cast<const ImageTexture<RGBSpectrum, Spectrum> *>(mt->Kd.get()))) {
+                    // Material "matte" with "float sigma" > 0: an Oren-Nayar lobe (matte.cpp:55-61); sigma has no accessor.
+                    // Or with an image texture on Kd
                     Float kd[3];
                     Spectrum(mt->Kd->Evaluate(si).Clamp()).ToRGB(kd);
                     for (int c = 0; c < 3; ++c) rec[1 + c] = kd[c];
                     rec[4] = Clamp(mt->sigma->Evaluate(si), 0, 90);
+                    rec[18] = (float)textureIndex(mt->Kd);
                 } else {
                     Float kd[3];
                     if (!lambertianKd(m, kd)) { Error("b200wavefront: only \"matte\", \"plastic\", \"mirror\", smooth \"glass\", \"metal\", \"substrate\" and \"uber\" materials are supported"); return; }
                     for (int c = 0; c < 3; ++c) rec[1 + c] = kd[c];
                 }
+                if (texBad) return;
                 it = seen.emplace(std::make_pair(m, flip), (int)seen.size()).first;
                 mats.insert(mats.end(), rec, rec + 20);
             }
             primMat[i] = (uint8_t)it->second;
         }
-        if (mats.size() == 20 && mats[0] == 0.f && mats[4] == 0.f && d.light_kind == B200RT_LIGHT_POINT) {
+        if (mats.size() == 20 && mats[0] == 0.f && mats[4] == 0.f && mats[18] == 0.f && d.light_kind == B200RT_LIGHT_POINT) {
             for (int c = 0; c < 3; ++c) d.kd[c] = mats[1 + c];   // one Lambertian Kd (sigma 0): the lean kernel path
         } else {
             d.materials = mats.data(); d.n_materials = (uint32_t)(mats.size() / 20); d.prim_material = primMat.data();
             d.material_stride = 20;
+            for (size_t k = 0; k < texRecs.size(); ++k) texRecs[k].texels = texData[k].data();
+            if (!texRecs.empty()) { d.textures = texRecs.data(); d.n_textures = (uint32_t)texRecs.size(); }
         }
     }
     d.spp = (uint32_t)sampler->samplesPerPixel;
