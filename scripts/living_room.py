@@ -28,6 +28,9 @@ def main():
     ap.add_argument("--frames", type=int, default=1)
     ap.add_argument("--warm-spp", type=int, default=4, help="spp of the untimed warm-up frame")
     ap.add_argument("--out", default="", help="rank 0 writes the frame's RGB as .npy here")
+    ap.add_argument("--sampler", default="sobol", choices=["sobol", "halton", "hash"], help="the file asks for sobol")
+    ap.add_argument("--no-textures", action="store_true", help="constants instead of the two image files (A/B)")
+    ap.add_argument("--no-normals", action="store_true", help="geometric normals instead of the PLY vertex normals (A/B)")
     args = ap.parse_args()
 
     import numpy as np
@@ -47,9 +50,9 @@ def main():
     b200rt.init(local)
     dev = torch.device("cuda", local)
     stream = torch.cuda.current_stream().cuda_stream
-    sc = scenes.living_room(args.xres, args.yres)
+    sc = scenes.living_room(args.xres, args.yres, textures=not args.no_textures)
     tv = sc["tri_verts"]
-    accel = b200rt.MakeAccelerator(args.accel, tv)
+    accel = b200rt.MakeAccelerator(args.accel, tv, tri_uvs=sc["tri_uvs"], tri_normals=None if args.no_normals else sc["tri_normals"], prim_flags=None if args.no_normals else sc["prim_flags"])
     il = sc["infinite_light"]
 
     textures = scenes.living_room_textures(sc)
@@ -58,7 +61,7 @@ def main():
         return b200rt.WavefrontPathIntegrator(sc["camera"], spp=spp, maxdepth=args.maxdepth, light_I=il["L"],
                                               infinite_light=(il["light_to_world"], wf.world_radius(tv)),
                                               materials=sc["materials"], prim_material=sc["prim_material"],
-                                              textures=textures, rank=rank, world=world, seed=1)
+                                              textures=textures, rank=rank, world=world, sampler=args.sampler, seed=1)
     film = torch.zeros((args.yres, args.xres, 4), dtype=torch.float32, device=dev)
     gather = FilmGather(args.xres, args.yres, 16, rank, world, dev)
 
@@ -99,7 +102,9 @@ def main():
             np.save(args.out, rgb)
         print(json.dumps({
             "workload": "scenes/living-room (reference geometry, 143163 triangles, %s), %dx%d @ %d spp, path maxdepth %d, "
-                        "constant infinite light + MIS, the file's material kinds (matte, substrate, metal, glass, mirror) with constant textures" % (args.accel, args.xres, args.yres, args.spp, args.maxdepth),
+                        "Sampler %s, constant infinite light + MIS, the file's materials (matte, Oren-Nayar, substrate, metal, glass, mirror, uber)%s%s; "
+                        "box filter" % (args.accel, args.xres, args.yres, args.spp, args.maxdepth, args.sampler,
+                                        "" if args.no_textures else ", image textures", "" if args.no_normals else ", PLY vertex normals"),
             "n_gpus": world, "ms_per_frame": ms, "rays_per_frame": rays, "mrays_per_s": rays / ms / 1e3,
             "camera_rays": float(tsum[6]) / args.frames, "closest_rays": float(tsum[1]) / args.frames,
             "shadow_rays": float(tsum[2]) / args.frames, "mis_rays": float(tsum[5]) / args.frames,

@@ -32,6 +32,14 @@ WF_HD uint32_t div_magic(uint32_t a, uint32_t magic, uint32_t shift) {
     return (((a - q) >> 1) + q) >> shift;
 }
 
+WF_HD int lowest_bit(uint64_t a) {   // index of the lowest set bit, a != 0
+#ifdef __CUDA_ARCH__
+    return __ffsll((long long)a) - 1;
+#else
+    return __builtin_ctzll(a);
+#endif
+}
+
 struct WfSampler {
     uint32_t kind, seed;
     // halton
@@ -99,14 +107,14 @@ WF_HD uint64_t sampler_index(const WfSampler &S, int32_t px, int32_t py, uint32_
         // SobolIntervalToIndex(log2Resolution, sampleNum, currentPixel - sampleBounds.pMin) (lowdiscrepancy.h:229-250)
         const uint32_t m = S.log2Res;
         if (m == 0) return 0;
+        // the reference walks the bits from the lowest and XORs a matrix column for every set one: visiting only the set bits
+        // gives the same XOR (lowest_bit)
         uint64_t frame = s;
         uint64_t index = frame << (m << 1);
         uint64_t delta = 0;
-        for (int c = 0; frame; frame >>= 1, ++c)
-            if (frame & 1) delta ^= S.vdc[c];
+        for (; frame; frame &= frame - 1) delta ^= S.vdc[lowest_bit(frame)];
         uint64_t b = (((uint64_t)((uint32_t)(px - S.sbMinX)) << m) | ((uint32_t)(py - S.sbMinY))) ^ delta;
-        for (int c = 0; b; b >>= 1, ++c)
-            if (b & 1) index ^= S.vdcInv[c];
+        for (; b; b &= b - 1) index ^= S.vdcInv[lowest_bit(b)];
         return index;
     }
     return s;
@@ -168,9 +176,8 @@ WF_HD float sampler_dim(const WfSampler &S, uint64_t index, uint32_t dim, int32_
         // SobolSampler::SampleDimension (sobol.cpp:48-60) over SobolSampleFloat (lowdiscrepancy.h:252-266), scramble 0
         if (dim >= (uint32_t)kSobolDims) dim = kSobolDims - 1;
         uint32_t v = 0;
-        uint64_t a = index;
-        for (uint32_t i = dim * kSobolMatrixSize; a != 0; a >>= 1, i++)
-            if (a & 1) v ^= S.sobol32[i];
+        const uint32_t *col = S.sobol32 + dim * kSobolMatrixSize;
+        for (uint64_t a = index; a != 0; a &= a - 1) v ^= col[lowest_bit(a)];
         float sv = smin((float)v * 0x1p-32f, kOneMinusEps);
         if (dim < 2) {
             sv = sv * (float)(int32_t)S.res + (float)(dim == 0 ? S.sbMinX : S.sbMinY);

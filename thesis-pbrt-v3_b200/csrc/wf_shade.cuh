@@ -323,7 +323,7 @@ WF_HD_NOINLINE void textured_material(const WfParams &P, const float *m, uint32_
     }
     V3 kdV = v3(0.f, 0.f, 0.f), opV = v3(0.f, 0.f, 0.f);
     if (kdT) kdV = tex_evaluate(P.tex[kdT - 1], it.u, it.v, D);
-    if (opT) opV = tex_evaluate(P.tex[opT - 1], it.u, it.v, D);
+    if (opT) opV = (opT == kdT) ? kdV : tex_evaluate(P.tex[opT - 1], it.u, it.v, D);   // the same texture object: the same value
     textured_lobes(m, kdT != 0, kdV, opT != 0, opV, L, n, eta);
 }
 

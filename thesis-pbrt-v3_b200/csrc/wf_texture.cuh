@@ -32,7 +32,7 @@ WF_HD double u2d(uint64_t u) {
 // glibc 2.39 logf for finite x > 0 (the callers pass max(width, 1e-8))
 WF_HD float log_ref(float x) {
     // __logf_data: tab[16] = {invc, logc}, ln2, poly[3]
-    const uint64_t T[32] = {
+    static const uint64_t T[32] = {
         0x3ff661ec79f8f3beull, 0xbfd57bf7808caadeull, 0x3ff571ed4aaf883dull, 0xbfd2bef0a7c06ddbull, 0x3ff49539f0f010b0ull, 0xbfd01eae7f513a67ull,
         0x3ff3c995b0b80385ull, 0xbfcb31d8a68224e9ull, 0x3ff30d190c8864a5ull, 0xbfc6574f0ac07758ull, 0x3ff25e227b0b8ea0ull, 0xbfc1aa2bc79c8100ull,
         0x3ff1bb4a4a1a343full, 0xbfba4e76ce8c0e5eull, 0x3ff12358f08ae5baull, 0xbfb1973c5a611cccull, 0x3ff0953f419900a7ull, 0xbfa252f438e10c1eull,
