@@ -21,7 +21,7 @@
 extern "C" {
 #endif
 
-#define B200RT_VERSION 9
+#define B200RT_VERSION 10
 
 enum {
     B200RT_OK = 0,

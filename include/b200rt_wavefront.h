@@ -10,9 +10,10 @@
  * queue, bounce closest-hit queue) -> ... up to maxdepth, with warp-ballot queue compaction.
  *
  * Shading subset (what the config scenes' templates need around the traversal): perspective camera
- * (src/cameras/perspective.cpp), one point light (src/lights/point.cpp), one distant light (src/lights/distant.cpp), one
- * sphere area light (src/lights/diffuse.cpp, Sphere::Sample/Pdf) OR one constant infinite light (src/lights/infinite.cpp
- * with the 1x1 map) — the last two with multiple importance sampling (EstimateDirect's two strategies) —, "matte" and
+ * (src/cameras/perspective.cpp), point lights (src/lights/point.cpp), distant lights (src/lights/distant.cpp), sphere area
+ * lights (src/lights/diffuse.cpp, Sphere::Sample/Pdf) and constant infinite lights (src/lights/infinite.cpp with the 1x1
+ * map) — the last two with multiple importance sampling (EstimateDirect's two strategies); one of them through the
+ * description's own fields or several through its `lights` array (ABI v10, UniformSampleOneLight) —, "matte" and
  * "plastic", "mirror", smooth "glass", "metal" and "substrate" materials per primitive (src/materials/matte.cpp, plastic.cpp, mirror.cpp, glass.cpp, metal.cpp, substrate.cpp), box pixel filter, Russian roulette of
  * path.cpp:190-199, path depths up to 68 (scenes/living-room uses 65).  Samples come
  * from a counter-based hash of (pixel, sample, dimension), so the image does not depend on the
@@ -46,6 +47,18 @@ typedef struct {
     uint32_t width, height, n_levels;
     float su, sv, du, dv;   /* "float uscale" / "vscale" / "udelta" / "vdelta": 1, 1, 0, 0 */
 } b200rt_texture;
+
+/* One light of a scene with several (ABI v10; `n_lights` below).  The fields mean what the desc's single-light fields
+ * light_kind / light_pos / light_I / light_radius / light_prim / light_to_world mean for that kind. */
+typedef struct {
+    uint32_t kind;        /* B200RT_LIGHT_* */
+    uint32_t prim;        /* B200RT_LIGHT_SPHERE: the sphere's primitive number */
+    float pos[3];         /* point: "from"; sphere: centre; distant: unit direction TOWARDS the light */
+    float I[3];           /* point: "I"; the others: radiance "L" */
+    float radius;         /* sphere: its radius; distant / infinite: the scene's bounding-sphere radius */
+    float to_world[9];    /* infinite: rotation of LightToWorld, row-major; all zero = identity */
+    float weight;         /* this light's entry in the light-sampling distribution (below) */
+} b200rt_light;
 
 typedef struct {
     b200rt_camera camera;
@@ -114,7 +127,22 @@ typedef struct {
     const b200rt_texture *textures; /* HOST array; slot 18 of a 20-float material record = 1 + index of the texture its Kd reads
                               (matte, plastic, substrate, uber), slot 19 = 1 + index of uber's opacity texture; 0 = the constant */
     uint32_t n_textures;
+    /* ---- ABI v10: several lights, UniformSampleOneLight over a light distribution (integrator.cpp:86-107) ---- */
+    const b200rt_light *lights; /* HOST array of n_lights records, in the order of Scene::lights; when n_lights > 0 it REPLACES the
+                              single-light fields above (n_lights = 1 is the same render as those fields).  Per path vertex one
+                              light is chosen as Distribution1D::SampleDiscrete (sampling.h:90-100) chooses it from the sample
+                              the path integrator draws for the choice: the distribution is built, as the reference builds it
+                              (sampling.h:57-69), from the records' `weight`s — all equal = Integrator "path" "string
+                              lightsamplestrategy" "uniform" (UniformLightDistribution, lightdistrib.cpp:68-75), Light::Power().y()
+                              of each light = "power" (PowerLightDistribution).  The estimate is divided by the choice's
+                              probability; a light of weight 0 is never chosen.  "spatial" (the default when a scene has
+                              more than one light, a per-voxel distribution built lazily from 128 samples a voxel) is NOT
+                              built: the host mirrors refuse it.  Emitted radiance seen by camera rays and after specular
+                              bounces: the hit sphere's own light (path.cpp:100) and the SUM over every infinite light for rays
+                              that escape (path.cpp:103-104).  At most B200RT_MAX_LIGHTS. */
+    uint32_t n_lights;
 } b200rt_render_desc;
+#define B200RT_MAX_LIGHTS 64u
 enum { B200RT_SAMPLER_HASH = 0, B200RT_SAMPLER_HALTON = 1, B200RT_SAMPLER_SOBOL = 2 };
 enum { B200RT_LIGHT_POINT = 0, B200RT_LIGHT_SPHERE = 1, B200RT_LIGHT_DISTANT = 2, B200RT_LIGHT_INFINITE = 3 };
 enum {

@@ -215,6 +215,29 @@ extern "C" void ref_render_set_infinite(const float *L_rgb, const float *l2w16) 
     g_infinite = L_rgb != nullptr && l2w16 != nullptr;
     if (g_infinite) { std::memcpy(g_infL, L_rgb, sizeof(g_infL)); std::memcpy(g_infM, l2w16, sizeof(g_infM)); }
 }
+// More LightSource statements after the first one, for the NEXT renders (n = 0: off): Scene::lights = the render's own light
+// followed by these, in order.  A record is 24 floats: kind (0 "point": a = "from", rgb = "I"; 2 "distant": a = from - to,
+// rgb = "L"; 3 "infinite": rgb = "L", m = row-major 4x4 LightToWorld, constant map), a[3], rgb[3], m[16], unused.
+// strategy = Integrator "path" "string lightsamplestrategy" (path.cpp:218-219; lightdistrib.cpp:48-66).
+static std::vector<float> g_extraLights, g_lastPowers;
+static std::string g_lightStrategy = "spatial";
+extern "C" void ref_render_set_extra_lights(const float *recs, int n, const char *strategy) {
+    g_extraLights.assign(recs && n > 0 ? recs : nullptr, recs && n > 0 ? recs + (size_t)24 * n : nullptr);
+    g_lightStrategy = (strategy && n > 0) ? strategy : "spatial";
+}
+extern "C" int ref_render_get_extra_lights(float *recs, int cap, char *strategy, int strategy_cap) {   // for tests/hostplugin's driver
+    const int n = (int)(g_extraLights.size() / 24);
+    if (recs && n <= cap) std::memcpy(recs, g_extraLights.data(), g_extraLights.size() * sizeof(float));
+    if (strategy && strategy_cap > 0) { std::strncpy(strategy, g_lightStrategy.c_str(), (size_t)strategy_cap - 1); strategy[strategy_cap - 1] = 0; }
+    return n;
+}
+// Light::Power().y() of every light of the LAST render's scene, in Scene::lights order (after Scene's constructor ran their
+// Preprocess): what PowerLightDistribution weighs the lights by (integrator.cpp:219-227).
+extern "C" int ref_render_last_light_powers(float *out, int cap) {
+    const int n = (int)g_lastPowers.size();
+    for (int i = 0; i < n && i < cap; ++i) out[i] = g_lastPowers[(size_t)i];
+    return n;
+}
 // `Transform [16 floats]` before `Camera` (scenes/living-room/scene.pbrt:2): the world-to-camera CTM as a row-major
 // 4x4 for the NEXT renders instead of the LookAt in `cam` (NULL = LookAt again); cam[9] stays the fov.
 static bool g_camMatrix = false;
@@ -435,7 +458,21 @@ extern "C" int ref_render(ref_scene *s, const char *accel_kind, const float *cam
                                                         Point3f(g_from_to[0], g_from_to[1], g_from_to[2]) -
                                                             Point3f(g_from_to[3], g_from_to[4], g_from_to[5])));
     else lights.push_back(std::make_shared<PointLight>(l2w, mi, Spectrum::FromRGB(li)));
+    for (size_t k = 0; k + 24 <= g_extraLights.size(); k += 24) {
+        const float *r = g_extraLights.data() + k;
+        Float c[3] = {r[4], r[5], r[6]};
+        const int kind = (int)r[0];
+        if (kind == 0) lights.push_back(std::make_shared<PointLight>(Translate(Vector3f(r[1], r[2], r[3])), mi, Spectrum::FromRGB(c)));
+        else if (kind == 2) lights.push_back(std::make_shared<DistantLight>(Transform(), Spectrum::FromRGB(c), Vector3f(r[1], r[2], r[3])));
+        else if (kind == 3) {
+            const float *q = r + 7;
+            Matrix4x4 m(q[0], q[1], q[2], q[3], q[4], q[5], q[6], q[7], q[8], q[9], q[10], q[11], q[12], q[13], q[14], q[15]);
+            lights.push_back(std::make_shared<InfiniteAreaLight>(Transform(m), Spectrum::FromRGB(c), 1, std::string("")));
+        } else return 4;
+    }
     Scene scene(counting, lights);
+    g_lastPowers.clear();
+    for (const auto &l : scene.lights) g_lastPowers.push_back(l->Power().y());
 
     // Film "image" + PixelFilter "box" (film.cpp:307-351, filters/box.cpp) — defaults of every thesis template
     std::unique_ptr<Filter> filter(new BoxFilter(Vector2f(0.5f, 0.5f)));
@@ -463,7 +500,7 @@ extern "C" int ref_render(ref_scene *s, const char *accel_kind, const float *cam
         if (g_trace) sampler.reset(new TracingSampler<SobolSampler>(spp, film->GetSampleBounds()));
         else sampler.reset(new SobolSampler(spp, film->GetSampleBounds()));
     } else sampler.reset(new RandomSampler(spp));
-    PathIntegrator integ(maxdepth, camera, sampler, film->GetSampleBounds(), 1.f, "spatial");
+    PathIntegrator integ(maxdepth, camera, sampler, film->GetSampleBounds(), 1.f, g_lightStrategy);
 
     const auto t0 = std::chrono::steady_clock::now();
     integ.Render(scene);     // -> film->WriteImage() -> the WriteImage above

@@ -208,7 +208,8 @@ def camera_matrices(eye, look, up, fov, xres, yres, camera_matrix=None):
 
 def render(scene, accel_kind, eye, look, up, fov, xres, yres, spp, maxdepth, light_pos, light_I, kd,
            sampler="random", n_threads=0, tmp_prefix=None, heat=False, prim_mat=None, emitter_L=None, timing=False,
-           distant=None, cropwindow=None, infinite=None, camera_matrix=None, textures=None):
+           distant=None, cropwindow=None, infinite=None, camera_matrix=None, textures=None, extra_lights=None,
+           lightsamplestrategy="uniform"):
     """The reference's OWN render (SamplerIntegrator::Render + PathIntegrator::Li + Film, oracle/ref/ref_render.cpp)
     of `scene` with a matte material and one point light.  Returns (rgb (yres,xres,3), n_closest, n_shadow)."""
     import tempfile
@@ -253,6 +254,13 @@ def render(scene, accel_kind, eye, look, up, fov, xres, yres, spp, maxdepth, lig
         scene.L.ref_render_set_crop(_p(None if cropwindow is None else np.array(cropwindow, np.float32)))
     elif cropwindow is not None:
         raise RuntimeError("libpbrtref.so predates ref_render_set_crop: rebuild oracle/ref")
+    if extra_lights:
+        # more LightSource statements after the render's own light (dicts as b200rt.wavefront.make_light takes them: point /
+        # distant / infinite) and Integrator "path" "string lightsamplestrategy"
+        if not hasattr(scene.L, "ref_render_set_extra_lights"):
+            raise RuntimeError("libpbrtref.so predates ref_render_set_extra_lights: rebuild oracle/ref")
+        scene.L.ref_render_set_extra_lights.argtypes = [C.c_void_p, C.c_int, C.c_char_p]
+        scene.L.ref_render_set_extra_lights(_p(extra_light_records(extra_lights)), len(extra_lights), lightsamplestrategy.encode())
     try:
         with tempfile.TemporaryDirectory() as td:   # the thesis's per-pixel stat dumps (film.cpp:170-264) land here
             pre = (tmp_prefix or os.path.join(td, "ref")).encode()
@@ -271,7 +279,7 @@ def render(scene, accel_kind, eye, look, up, fov, xres, yres, spp, maxdepth, lig
         # leave them at their defaults, so that a later render in the same process is not lit by this one's infinite light
         for fn, args in (("ref_render_set_distant", (None,)), ("ref_render_set_infinite", (None, None)),
                          ("ref_render_set_camera_matrix", (None,)), ("ref_render_set_crop", (None,)), ("ref_render_set_mat_stride", (8,)),
-                         ("ref_render_set_textures", (0, None))):
+                         ("ref_render_set_textures", (0, None)), ("ref_render_set_extra_lights", (None, 0, None))):
             if hasattr(scene.L, fn):
                 getattr(scene.L, fn)(*args)
     if rc != 0:
@@ -279,6 +287,33 @@ def render(scene, accel_kind, eye, look, up, fov, xres, yres, spp, maxdepth, lig
     if timing:   # (rgb, n_closest, n_shadow, seconds spent inside Integrator::Render)
         return out, nc.value, ns.value, secs.value
     return (out, nc.value, ns.value, hm) if heat else (out, nc.value, ns.value)
+
+
+def extra_light_records(lights):
+    """24-float records of ref_render_set_extra_lights from make_light-style dicts."""
+    recs = np.zeros((len(lights), 24), np.float32)
+    for r, l in zip(recs, lights):
+        if l["kind"] == "point":
+            r[0], r[1:4], r[4:7] = 0, l["pos"], l["I"]
+        elif l["kind"] == "distant":
+            r[0], r[1:4], r[4:7] = 2, l["w"], l["L"]
+        elif l["kind"] == "infinite":
+            m = np.eye(4, dtype=np.float32)
+            if l.get("light_to_world") is not None:
+                m[:3, :3] = np.asarray(l["light_to_world"], np.float32)[:3, :3]
+            r[0], r[4:7], r[7:23] = 3, l["L"], m.ravel()
+        else:
+            raise ValueError("extra light kind %r" % (l["kind"],))
+    return recs
+
+
+def last_light_powers(L=None):
+    """Light::Power().y() of the lights of the last render's scene, in Scene::lights order."""
+    L = L or lib()
+    out = np.zeros(64, np.float32)
+    L.ref_render_last_light_powers.argtypes = [C.c_void_p, C.c_int]
+    n = L.ref_render_last_light_powers(_p(out), 64)
+    return out[:n].copy()
 
 
 def texture_pyramid(path):

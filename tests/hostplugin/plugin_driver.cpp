@@ -124,6 +124,7 @@ extern "C" int ref_render_get_distant(float *from_to);
 extern "C" int ref_render_get_infinite(float *L_rgb, float *l2w16);      // set through ref_render_set_infinite
 extern "C" int ref_render_get_camera_matrix(float *w2c16);             // set through ref_render_set_camera_matrix
 extern "C" int ref_render_get_textures(int i, char *out, int cap);   // set through ref_render_set_textures: image files of slots 18 / 19
+extern "C" int ref_render_get_extra_lights(float *recs, int cap, char *strategy, int strategy_cap);   // set through ref_render_set_extra_lights
 extern "C" int ref_render_get_mat_stride(void);             // set through ref_render_set_mat_stride: 8 or 20 floats per record
 extern "C" void ref_render_get_crop(float *cw);           // set through ref_render_set_crop   // set through ref_render_set_distant (oracle/ref/ref_render.cpp)
 std::shared_ptr<pbrt::Shape> shape_of(const pbrt::Primitive *p);   // plugin_shape_of.cpp (GeometricPrimitive::shape is private)
@@ -237,6 +238,25 @@ extern "C" int plugin_render(ref_scene *s, const char *tree, const float *cam, i
         lights.push_back(std::make_shared<DistantLight>(Transform(), Spectrum::FromRGB(li),
                                                         Point3f(ft[0], ft[1], ft[2]) - Point3f(ft[3], ft[4], ft[5])));
     else lights.push_back(std::make_shared<PointLight>(l2w, mi, Spectrum::FromRGB(li)));
+    // more LightSource statements (24-float records, oracle/ref/ref_render.cpp) and Integrator "string lightsamplestrategy"
+    std::vector<float> extra((size_t)24 * 64);
+    char strategy[32] = "spatial";
+    const int nExtra = ref_render_get_extra_lights(extra.data(), 64, strategy, sizeof strategy);
+    for (int k = 0; k < nExtra && k < 64; ++k) {
+        const float *r = extra.data() + (size_t)24 * k;
+        Float c[3] = {r[4], r[5], r[6]};
+        const int kind = (int)r[0];
+        if (kind == 0) lights.push_back(std::make_shared<PointLight>(Translate(Vector3f(r[1], r[2], r[3])), mi, Spectrum::FromRGB(c)));
+        else if (kind == 2) lights.push_back(std::make_shared<DistantLight>(Transform(), Spectrum::FromRGB(c), Vector3f(r[1], r[2], r[3])));
+        else if (kind == 3) {
+            const float *q = r + 7;
+            ParallelInit();
+            lights.push_back(std::make_shared<InfiniteAreaLight>(
+                Transform(Matrix4x4(q[0], q[1], q[2], q[3], q[4], q[5], q[6], q[7], q[8], q[9], q[10], q[11], q[12], q[13], q[14], q[15])),
+                Spectrum::FromRGB(c), 1, std::string("")));
+            ParallelCleanup();
+        } else return 4;
+    }
     Scene scene(accel, lights);
     std::unique_ptr<Filter> filter(new BoxFilter(Vector2f(0.5f, 0.5f)));
     float cw[4];
@@ -266,6 +286,7 @@ extern "C" int plugin_render(ref_scene *s, const char *tree, const float *cam, i
     auto addInt = [&](const char *name, int v) { std::unique_ptr<int[]> a(new int[1]); a[0] = v; ips.AddInt(name, std::move(a), 1); };
     addInt("maxdepth", maxdepth); addInt("seed", seed); addInt("rank", rank); addInt("world", world);
     if (g_generalStats) { std::unique_ptr<bool[]> b(new bool[1]); b[0] = true; ips.AddBool("generalstats", std::move(b), 1); }
+    if (nExtra > 0) { std::unique_ptr<std::string[]> v(new std::string[1]); v[0] = strategy; ips.AddString("lightsamplestrategy", std::move(v), 1); }
     std::unique_ptr<B200WavefrontIntegrator> integ(CreateB200WavefrontIntegrator(ips, sampler, camera));
     integ->Render(scene);
     int w = 0, h = 0;

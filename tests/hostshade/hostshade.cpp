@@ -27,6 +27,7 @@ struct hs_ctx {
     std::vector<uint32_t> sobol32;
     std::vector<uint64_t> vdc;
     std::vector<WfTexture> tex;
+    std::vector<WfLight> lights;
 };
 
 extern "C" const char *hs_last_error() { return g_err; }
@@ -41,7 +42,15 @@ extern "C" hs_ctx *hs_create(const b200rt_render_desc *d, uint32_t n_prims, cons
     std::memcpy(P.cm.r2c, d->raster_to_camera, 64); std::memcpy(P.cm.c2w, d->camera_to_world, 64);
     std::memcpy(P.kd, d->kd, 12);
     P.max_depth = d->max_depth;
-    if (light_of(d, n_prims, &P.light)) { delete c; return nullptr; }
+    if (lights_of(d, n_prims, c->lights)) { delete c; return nullptr; }
+    P.light = c->lights[0];
+    P.nLights = (uint32_t)c->lights.size();
+    P.lights = P.nLights > 1 ? c->lights.data() : nullptr;
+    bool notPoint = false;
+    for (const WfLight &l : c->lights) {
+        if (l.kind == B200RT_LIGHT_SPHERE || l.kind == B200RT_LIGHT_INFINITE) P.anyMis = 1;
+        notPoint = notPoint || l.kind != B200RT_LIGHT_POINT;
+    }
     c->tris.assign(tri_verts, tri_verts + 9 * (size_t)n_prims);
     if (tri_uvs) { c->uv.assign(tri_uvs, tri_uvs + 6 * (size_t)n_prims); P.primUV = c->uv.data(); }
     if (tri_normals) { c->normals.assign(tri_normals, tri_normals + 9 * (size_t)n_prims); P.primN = c->normals.data(); }
@@ -89,8 +98,7 @@ extern "C" hs_ctx *hs_create(const b200rt_render_desc *d, uint32_t n_prims, cons
         }
         P.smp.sobol32 = c->sobol32.data(); P.smp.vdc = c->vdc.data(); P.smp.vdcInv = c->vdc.data() + kSobolMatrixSize;
     }
-    const uint32_t lk = d->light_kind;
-    c->full = lk != B200RT_LIGHT_POINT || P.mats || P.primN || P.primUV || P.primFlags;
+    c->full = notPoint || P.nLights > 1 || P.mats || P.primN || P.primUV || P.primFlags;
     return c;
 }
 extern "C" void hs_destroy(hs_ctx *c) { delete c; }
@@ -169,7 +177,7 @@ extern "C" void hs_shade(const hs_ctx *c, uint32_t depth, uint64_t start, uint32
         if (o.wantMis) {
             float *q = misRays + 8 * (size_t)nMis;
             q[0] = o.mo.x; q[1] = o.mo.y; q[2] = o.mo.z; q[3] = wf_inf(); q[4] = o.md.x; q[5] = o.md.y; q[6] = o.md.z; q[7] = 0.f;
-            misContrib[4 * (size_t)nMis] = o.mcontrib.x; misContrib[4 * (size_t)nMis + 1] = o.mcontrib.y; misContrib[4 * (size_t)nMis + 2] = o.mcontrib.z; misContrib[4 * (size_t)nMis + 3] = 0.f;
+            misContrib[4 * (size_t)nMis] = o.mcontrib.x; misContrib[4 * (size_t)nMis + 1] = o.mcontrib.y; misContrib[4 * (size_t)nMis + 2] = o.mcontrib.z; std::memcpy(misContrib + 4 * (size_t)nMis + 3, &o.misPrim, 4);
             misPath[nMis++] = path;
         }
     }

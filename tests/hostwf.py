@@ -38,6 +38,15 @@ def _p(a):
     return None if a is None else a.ctypes.data_as(C.c_void_p)
 
 
+def desc_has_area_light(d):
+    """Some light of the description has area (sphere / infinite): EstimateDirect's BSDF-sampled rays exist."""
+    if d.n_lights:
+        from b200rt import wavefront as wf
+        recs = C.cast(d.lights, C.POINTER(wf.Light))
+        return any(recs[k].kind in (1, 3) for k in range(d.n_lights))
+    return d.light_kind in (1, 3)
+
+
 class HostWavefront:
     """The wavefront loop of csrc/wavefront.cu on the host: hs_camera / hs_shade are the kernels' bodies, `orc` (an
     oracle.orcbind.OracleAccel) traces the queues.  render() returns (film (yres, xres, 4), queues) with queues[q] =
@@ -81,7 +90,7 @@ class HostWavefront:
         L = lib()
         d = self.desc
         n = int(L.hs_n_paths(self.h))
-        mis = d.light_kind in (1, 3)
+        mis = desc_has_area_light(d)
         maxd = d.max_depth
         rays = np.zeros((n, 8), np.float32)
         qpath = np.zeros(n, np.uint32)
@@ -120,9 +129,11 @@ class HostWavefront:
                 stats["mis_rays"] += nm
                 if nm:
                     mh = self._trace(mr[:nm])
-                    want = MISS if d.light_kind == 3 else d.light_prim
+                    want = mc[:nm, 3].copy().view(np.uint32)   # the chosen light's primitive, or MISS for an infinite light
                     ok = mh[:, 0] == want
-                    np.add.at(Lp, (mp[:nm][ok],), mc[:nm][ok])
+                    add = mc[:nm].copy()
+                    add[:, 3] = 0
+                    np.add.at(Lp, (mp[:nm][ok],), add[ok])
             rays[:nn], qpath[:nn], cnt = nr[:nn], npth[:nn], nn
         # k_film: per pixel, samples summed in order
         from b200rt import wavefront as wf
@@ -259,6 +270,9 @@ def reference_trace(case, spp, res, sampler="halton"):
     rres = c.get("res", res)
     (img, nc, ns), rec = rb.trace_render(S, "bvh", r.pop("eye"), r.pop("look"), r.pop("up"), r.pop("fov"), rres, rres, spp,
                                          c["maxdepth"], r.pop("light_pos"), r.pop("light_I"), r.pop("kd"), sampler=sampler, **r)
+    if c.get("power"):   # "lightsamplestrategy" "power": the weights are the reference's own Light::Power().y()
+        for l, w in zip(c["integ"]["lights"], rb.last_light_powers(S.L)):
+            l["weight"] = float(w)
     return c, img, (nc, ns), parse_trace(rec)
 
 

@@ -20,9 +20,10 @@ def write_killeroo_geometry(path):
 
 
 def killeroo_simple(dirname, accelerator, integrator='Integrator "path" "integer maxdepth" [5]', xres=700, yres=700, spp=8,
-                    filename="killeroo-simple.pfm", extra_film="", scene_name="input.pbrt", ground_texture=None):
+                    filename="killeroo-simple.pfm", extra_film="", scene_name="input.pbrt", ground_texture=None, more_lights=""):
     """scenes/killeroo-simple with its Accelerator line replaced by `accelerator` (a full directive) and, optionally, its
-    Integrator line by `integrator`.  Returns the scene file's path."""
+    Integrator line by `integrator`; `more_lights` = LightSource directives placed right after WorldBegin (before the file's own
+    area light, so they come first in Scene::lights).  Returns the scene file's path."""
     geo = os.path.join(dirname, "killeroo.pbrt")
     if not os.path.exists(geo):
         write_killeroo_geometry(geo)
@@ -45,7 +46,7 @@ Sampler "halton" "integer pixelsamples" [%d]
 %s
 
 WorldBegin
-
+%s
 AttributeBegin
 Material "matte" "color Kd" [0 0 0]
 Translate 150 0  20
@@ -80,11 +81,21 @@ Translate -200 0 0
 
 AttributeEnd
 WorldEnd
-''' % (xres, yres, filename, extra_film, spp, accelerator, integrator, ground, geo, geo)
+''' % (xres, yres, filename, extra_film, spp, accelerator, integrator, more_lights, ground, geo, geo)
     path = os.path.join(dirname, scene_name)
     with open(path, "w") as f:
         f.write(txt)
     return path
+
+
+# a point, a distant and a constant infinite light next to killeroo-simple's sphere area light: every light kind in one scene
+MORE_LIGHTS = '''LightSource "point" "point from" [100 -150 200] "rgb I" [60000 50000 40000]
+LightSource "distant" "point from" [-0.3 0.4 1] "point to" [0 0 0] "rgb L" [1.5 1.5 1.2]
+AttributeBegin
+Rotate 40 0 0 1
+LightSource "infinite" "rgb L" [.3 .35 .5]
+AttributeEnd
+'''
 
 
 def read_pfm(path):

@@ -45,6 +45,18 @@ def build(name, res=48):
                    render=dict(eye=eye, look=look, up=up, fov=fov, light_pos=sc["light"], light_I=I, kd=kd),
                    integ=dict(camera=sc["camera"], light_pos=sc["light"], light_I=I, kd=kd), accel=(tv, {}))
         return out
+    if name == "sponza_two_points":
+        # two LightSource "point" (delta lights only): UniformSampleOneLight's choice and the division by its probability
+        sc = scenes.sponza_standin(detail=0.05, xres=res, yres=res)
+        tv = sc["tri_verts"]
+        eye, look, up, fov = _lookat(sc)
+        I, kd = (1.0, .9, .8), (.6, .5, .4)
+        second = dict(kind="point", pos=(-0.35, 0.3, 0.1), I=(.2, .5, .9))
+        out.update(ref=dict(P=tv.reshape(-1, 3), indices=np.arange(3 * len(tv), dtype=np.int32).reshape(-1, 3)),
+                   render=dict(eye=eye, look=look, up=up, fov=fov, light_pos=sc["light"], light_I=I, kd=kd, extra_lights=[second],
+                               lightsamplestrategy="uniform"),
+                   integ=dict(camera=sc["camera"], kd=kd, lights=[dict(kind="point", pos=sc["light"], I=I), second]), accel=(tv, {}))
+        return out
     if name.startswith("killeroo_"):
         sc = scenes.killeroo_simple(xres=res, yres=res)
         eye, look, up, fov = _lookat(sc)
@@ -87,6 +99,24 @@ def build(name, res=48):
             integ.update(light_I=(1.0, 0.9, 0.8), infinite_light=(l2w[:3, :3], wf.world_radius(verts)))
             out["mis"] = True
             out["infinite_scene"] = True
+        elif kind in ("lights", "lights_power"):
+            # Scene::lights = the file's sphere area light + a point, a distant and a constant infinite light: every light kind
+            # in one distribution ("uniform", or "power": weights = the reference's own Light::Power().y(), filled in by
+            # hostwf.reference_trace / the image test after the reference built its scene)
+            from b200rt import wavefront as wf
+            c, s_ = np.cos(0.7), np.sin(0.7)
+            l2w = (np.array([[c, 0, s_], [0, 1, 0], [-s_, 0, c]], np.float32) @ np.array([[1, 0, 0], [0, 0, -1], [0, 1, 0]], np.float32))
+            wr = wf.world_radius(verts)
+            extra = [dict(kind="point", pos=(100.0, -150.0, 200.0), I=(60000.0, 50000.0, 40000.0)),
+                     dict(kind="distant", w=(-0.3, 0.4, 1.0), L=(1.5, 1.5, 1.2), world_radius=wr),
+                     dict(kind="infinite", L=(0.3, 0.35, 0.5), light_to_world=l2w, world_radius=wr)]
+            strategy = "power" if kind == "lights_power" else "uniform"
+            render.update(emitter_L=sl["L"], extra_lights=extra, lightsamplestrategy=strategy)
+            del integ["light_pos"], integ["light_I"]
+            integ.update(lights=[dict(kind="sphere", center=sl["center"], L=sl["L"], radius=sl["radius"], prim=len(verts) - 1)] + extra,
+                         lightsamplestrategy=strategy)
+            out["mis"] = True
+            out["power"] = strategy == "power"
         else:
             render["emitter_L"] = sl["L"]
             integ["sphere_light"] = (sl["radius"], len(verts) - 1)
@@ -170,4 +200,5 @@ def build(name, res=48):
 
 
 CASES = ["sponza_point", "killeroo_plastic", "killeroo_normals", "killeroo_glass", "killeroo_metal", "killeroo_oren", "killeroo_uber", "killeroo_infinite",
-         "feet_distant", "normals", "normals_flipped", "living_room", "living_room_tex"]
+         "feet_distant", "normals", "normals_flipped", "living_room", "living_room_tex", "sponza_two_points", "killeroo_lights",
+         "killeroo_lights_power"]

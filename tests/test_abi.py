@@ -27,7 +27,7 @@ def test_exports_every_declared_symbol(built_lib):
 
 
 def test_version(built_lib):
-    assert built_lib.lib().b200rt_version() == 9
+    assert built_lib.lib().b200rt_version() == 10
 
 
 def test_no_cpu_fallback(built_lib):

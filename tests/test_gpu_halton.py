@@ -45,7 +45,8 @@ def _device_queues(gpu, c, spp, sampler):
                                           ("killeroo_metal", "halton"), ("killeroo_oren", "halton"), ("killeroo_uber", "halton"), ("killeroo_infinite", "halton"),
                                           ("feet_distant", "halton"), ("normals", "halton"), ("normals_flipped", "halton"),
                                           ("killeroo_metal", "sobol"), ("feet_distant", "sobol"), ("living_room", "sobol"),
-                                          ("living_room_tex", "sobol")])
+                                          ("living_room_tex", "sobol"), ("sponza_two_points", "halton"), ("killeroo_lights", "halton"),
+                                          ("killeroo_lights_power", "halton"), ("killeroo_lights", "sobol")])
 def test_device_rays_are_the_references(gpu, case, sampler):
     import hostwf
     from b200rt import wavefront as wf

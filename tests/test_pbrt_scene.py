@@ -138,3 +138,44 @@ def test_parsed_scene_with_an_image_texture(tmp_path):
     scene = ps.killeroo_simple(d, 'Accelerator "bvh"', filename="plain.pfm", xres=384, yres=384, spp=8)
     rc, _ = _run(scene, d)
     assert rc == 0 and np.abs(ps.read_pfm(os.path.join(d, "plain.pfm")) - ref).max() > 0.05
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("strategy", ["uniform", "power"])
+def test_parsed_scene_with_four_lights(tmp_path, strategy):
+    """Several LightSource statements (point, distant, constant infinite) next to the file's sphere area light, through
+    pbrtParseFile: UniformSampleOneLight over `"string lightsamplestrategy" "uniform"` / `"power"` (ABI v10: the C++ integrator
+    describes every light of Scene::lights and, for "power", weighs them by the reference's own Light::Power().y()) against the
+    stock run of the same file with the same strategy."""
+    import pbrt_scenes as ps
+    import hostwf
+    d = str(tmp_path)
+    kw = dict(xres=384, yres=384, spp=8, more_lights=ps.MORE_LIGHTS)
+    integ = '"integer maxdepth" [5] "string lightsamplestrategy" "%s"' % strategy
+    scene = ps.killeroo_simple(d, 'Accelerator "bvh"', integrator='Integrator "path" ' + integ, filename="stock.pfm", **kw)
+    rc, out = _run(scene, d)
+    assert rc == 0, out
+    ref = ps.read_pfm(os.path.join(d, "stock.pfm"))
+    scene = ps.killeroo_simple(d, 'Accelerator "b200" "string tree" "bvh"', integrator='Integrator "b200wavefront" ' + integ,
+                               filename="b200.pfm", **kw)
+    rc, out2 = _run(scene, d)
+    assert rc == 0 and os.path.exists(os.path.join(d, "b200.pfm")), out2
+    st = hostwf.image_stats(ps.read_pfm(os.path.join(d, "b200.pfm")), ref)
+    print("\nparsed killeroo-simple with four lights, %s: %s" % (strategy, st))
+    assert st["rel_rmse_excl"] <= 1e-4 and st["frac_differing"] < 1e-3, st
+    # the lights are really there: the file's own single light gives another picture
+    scene = ps.killeroo_simple(d, 'Accelerator "bvh"', filename="plain.pfm", xres=384, yres=384, spp=8)
+    rc, _ = _run(scene, d)
+    assert rc == 0 and np.abs(ps.read_pfm(os.path.join(d, "plain.pfm")) - ref).max() > 0.05
+
+
+@pytest.mark.gpu
+def test_spatial_light_distribution_is_refused(tmp_path):
+    """The reference's default for scenes with several lights, "spatial" (a lazily built per-voxel distribution), is not restated:
+    the integrator says so and renders nothing rather than something else."""
+    import pbrt_scenes as ps
+    d = str(tmp_path)
+    scene = ps.killeroo_simple(d, 'Accelerator "b200" "string tree" "bvh"', integrator='Integrator "b200wavefront" "integer maxdepth" [5]',
+                               filename="spatial.pfm", xres=64, yres=64, spp=1, more_lights=ps.MORE_LIGHTS)
+    rc, out = _run(scene, d, quiet=False)
+    assert "lightsamplestrategy" in out and not os.path.exists(os.path.join(d, "spatial.pfm")), out

@@ -11,6 +11,45 @@ class Camera(C.Structure):
                 ("xres", C.c_uint32), ("yres", C.c_uint32)]
 
 
+class Light(C.Structure):
+    """b200rt_light (include/b200rt_wavefront.h, ABI v10)."""
+    _fields_ = [("kind", C.c_uint32), ("prim", C.c_uint32), ("pos", C.c_float * 3), ("I", C.c_float * 3), ("radius", C.c_float),
+                ("to_world", C.c_float * 9), ("weight", C.c_float)]
+
+
+def _unit_to_light(w):
+    """wLight = Normalize(LightToWorld(from - to)) (lights/distant.cpp:44-47): v * (1 / Length), in float."""
+    w = np.asarray(w, np.float32)
+    inv = np.float32(1) / np.sqrt(w[0] * w[0] + w[1] * w[1] + w[2] * w[2], dtype=np.float32)
+    return (w * inv).astype(np.float32)
+
+
+def make_light(spec):
+    """One entry of `lights=`: a dict with "kind" and that kind's parameters, "weight" (default 1) its entry in the light
+    distribution:
+      point    : pos, I                                   LightSource "point" "from" "I"
+      sphere   : center, L, radius, prim                  AreaLightSource "area" "L" on the full Shape "sphere" number `prim`
+      distant  : w (= from - to), L, world_radius         LightSource "distant"
+      infinite : L, light_to_world (3x3 or None), world_radius   LightSource "infinite" without a readable map"""
+    l = Light()
+    kind = spec["kind"]
+    l.weight = float(spec.get("weight", 1.0))
+    f3 = lambda v: (C.c_float * 3)(*[float(x) for x in v])
+    if kind == "point":
+        l.kind, l.pos, l.I = 0, f3(spec["pos"]), f3(spec["I"])
+    elif kind == "sphere":
+        l.kind, l.pos, l.I, l.radius, l.prim = 1, f3(spec["center"]), f3(spec["L"]), float(spec["radius"]), int(spec["prim"])
+    elif kind == "distant":
+        l.kind, l.pos, l.I, l.radius = 2, f3(_unit_to_light(spec["w"])), f3(spec["L"]), float(spec["world_radius"])
+    elif kind == "infinite":
+        m = np.eye(3) if spec.get("light_to_world") is None else np.asarray(spec["light_to_world"], np.float64)[:3, :3]
+        l.kind, l.I, l.radius = 3, f3(spec["L"]), float(spec["world_radius"])
+        l.to_world = (C.c_float * 9)(*[float(x) for x in m.ravel()])
+    else:
+        raise ValueError("unknown light kind %r" % (kind,))
+    return l
+
+
 class RenderDesc(C.Structure):
     _fields_ = [("camera", Camera), ("spp", C.c_uint32), ("max_depth", C.c_uint32), ("light_pos", C.c_float * 3),
                 ("light_I", C.c_float * 3), ("kd", C.c_float * 3), ("tile_size", C.c_uint32), ("rank", C.c_uint32),
@@ -21,7 +60,7 @@ class RenderDesc(C.Structure):
                 ("sampler", C.c_uint32), ("camera_exact", C.c_uint32), ("raster_to_camera", C.c_float * 16),
                 ("camera_to_world", C.c_float * 16), ("sobol_matrices32", C.c_void_p), ("sobol_vdc", C.c_void_p),
                 ("sobol_vdc_inv", C.c_void_p), ("sobol_vdc_rows", C.c_uint32), ("material_stride", C.c_uint32),
-                ("textures", C.c_void_p), ("n_textures", C.c_uint32)]
+                ("textures", C.c_void_p), ("n_textures", C.c_uint32), ("lights", C.c_void_p), ("n_lights", C.c_uint32)]
 
 
 SAMPLERS = {"hash": 0, "halton": 1, "sobol": 2}
@@ -61,7 +100,7 @@ class WavefrontPathIntegrator:
     def __init__(self, camera, spp=8, maxdepth=5, light_pos=(0, 0, 0), light_I=(1, 1, 1), kd=(.5, .5, .5),
                  rank=0, world=1, seed=0, tile_size=16, max_batch=0, sphere_light=None, materials=None,
                  prim_material=None, distant_light=None, crop=None, infinite_light=None, sampler="halton", sobol_tables=None,
-                 textures=None):
+                 textures=None, lights=None, lightsamplestrategy="uniform"):
         """sphere_light=(radius, prim): `AreaLightSource "area" "color L" light_I` on the full sphere primitive number
         `prim` of the aggregate, centred at light_pos (sampled with MIS like EstimateDirect).  materials: (n, 8) rows
         (kind, Kd.rgb, Ks.rgb, roughness) + prim_material: (n_prims,) uint8 index per primitive.
@@ -78,7 +117,12 @@ class WavefrontPathIntegrator:
         dimension order); sobol needs sobol_tables = (SobolMatrices32, VdCSobolMatrices, VdCSobolMatricesInv) arrays.
         materials: (n, 8) rows, or (n, 20) rows (needed for "uber", kind 6).
         textures: list of b200rt.textures.ImageTexture (`Texture ... "imagemap"`, trilinear); slot 18 of a 20-float material row =
-        1 + index of the texture its Kd reads, slot 19 = 1 + index of uber's opacity texture."""
+        1 + index of the texture its Kd reads, slot 19 = 1 + index of uber's opacity texture.
+        lights: a list of make_light() dicts = Scene::lights in the scene's order, REPLACING light_pos / light_I / sphere_light /
+        distant_light / infinite_light; one of them is chosen per path vertex as UniformSampleOneLight does (integrator.cpp:86-107)
+        from the distribution over their "weight"s: lightsamplestrategy "uniform" (all 1, the default here) or "power" (the
+        caller's weights = Light::Power().y()).  The reference's own default for scenes with several lights, "spatial", is not
+        built and is refused."""
         d = RenderDesc()
         if "lookat" in camera or "w2c" in camera:
             la = None if camera.get("lookat") is None else np.ascontiguousarray(camera["lookat"], np.float32).reshape(9)
@@ -110,9 +154,7 @@ class WavefrontPathIntegrator:
             d.crop = (C.c_uint32 * 4)(*[int(c) for c in crop])
         if distant_light is not None:
             # wLight = Normalize(LightToWorld(from - to)) (lights/distant.cpp:44-47): v * (1 / Length), in float
-            w = np.asarray(distant_light[0], np.float32)
-            inv = np.float32(1) / np.sqrt(w[0] * w[0] + w[1] * w[1] + w[2] * w[2], dtype=np.float32)
-            w = (w * inv).astype(np.float32)
+            w = _unit_to_light(distant_light[0])
             d.light_kind, d.light_radius = 2, float(distant_light[1])
             d.light_pos = (C.c_float * 3)(*[float(x) for x in w])
         if infinite_light is not None:
@@ -131,6 +173,12 @@ class WavefrontPathIntegrator:
             self._textures = list(textures)
             self._tex_array = tx.texture_array(self._textures)
             d.textures, d.n_textures = C.cast(self._tex_array, C.c_void_p), len(self._textures)
+        if lights:
+            if lightsamplestrategy not in ("uniform", "power"):
+                raise ValueError("lightsamplestrategy %r: only \"uniform\" and \"power\" are built" % (lightsamplestrategy,))
+            recs = [make_light(dict(l, weight=1.0) if lightsamplestrategy == "uniform" else l) for l in lights]
+            self._lights = (Light * len(recs))(*recs)
+            d.lights, d.n_lights = C.cast(self._lights, C.c_void_p), len(recs)
         self.desc = d
 
     @property

@@ -81,7 +81,7 @@ __global__ void k_shade(const __grid_constant__ WfParams P, uint32_t depth, uint
                         float4 *L, float4 *misRays, uint32_t *misPath, float4 *misContrib, uint32_t *nMis) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     const uint32_t n = *nCur;
-    const bool mis = FULL && (P.light.kind == B200RT_LIGHT_SPHERE || P.light.kind == B200RT_LIGHT_INFINITE);
+    const bool mis = FULL && P.anyMis;
     ShadeOut o;
     o.wantShadow = o.wantNext = o.wantMis = false;
     uint32_t path = 0;
@@ -131,18 +131,20 @@ __global__ void k_shade(const __grid_constant__ WfParams P, uint32_t depth, uint
             misRays[2 * (size_t)mj] = make_float4(o.mo.x, o.mo.y, o.mo.z, __int_as_float(0x7f800000));
             misRays[2 * (size_t)mj + 1] = make_float4(o.md.x, o.md.y, o.md.z, 0.f);
             misPath[mj] = path;
-            misContrib[mj] = make_float4(o.mcontrib.x, o.mcontrib.y, o.mcontrib.z, 0.f);
+            misContrib[mj] = make_float4(o.mcontrib.x, o.mcontrib.y, o.mcontrib.z, __uint_as_float(o.misPrim));
         }
     }
 }
 
 // The BSDF-sampled ray of EstimateDirect (integrator.cpp:196-212): it contributes when its closest hit is the emitter
-// (`lightIsect.primitive->GetAreaLight() == &light`, Li = lightIsect.Le(-wi); seen from outside the sphere is front-facing).
-__global__ void k_mis_resolve(const uint32_t *__restrict__ nMis, const b200rt_hit *__restrict__ hits, uint32_t lightPrim,
+// (`lightIsect.primitive->GetAreaLight() == &light`, Li = lightIsect.Le(-wi); seen from outside the sphere is front-facing),
+// or, for an infinite light, when it escapes (`light.Le(ray)`): misContrib.w holds the primitive number the chosen light asks for.
+__global__ void k_mis_resolve(const uint32_t *__restrict__ nMis, const b200rt_hit *__restrict__ hits,
                               const uint32_t *__restrict__ misPath, const float4 *__restrict__ misContrib, float4 *L) {
     const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
-    if (j >= *nMis || hits[j].prim != lightPrim) return;
+    if (j >= *nMis) return;
     const float4 c = misContrib[j];
+    if (hits[j].prim != __float_as_uint(c.w)) return;
     float4 l = L[misPath[j]];   // one MIS ray per path and depth: no two threads share a path
     l.x += c.x; l.y += c.y; l.z += c.z;
     L[misPath[j]] = l;
@@ -272,6 +274,7 @@ struct Workspace {
     uint32_t texN = 0;
     uint8_t *primMat = nullptr;
     size_t mats_n = 0, primMat_n = 0;
+    WfLight *lights = nullptr;   // B200RT_MAX_LIGHTS records (ABI v10), allocated on the first render with more than one light
     uint4 *perRay = nullptr;   // heat-map mode only
     uint32_t *heat = nullptr;
     size_t heat_px = 0;
@@ -337,7 +340,7 @@ void free_ws(Workspace *w) {
     for (int i = 0; i < Workspace::kMaxSets - 1; ++i) free_alt(w, i);
     for (int k = 0; k < Workspace::kMaxSets; ++k) { if (w->side[k]) cudaStreamDestroy(w->side[k]); if (w->evJoin[k]) cudaEventDestroy(w->evJoin[k]); }
     if (w->evFork) cudaEventDestroy(w->evFork);
-    cudaFree(w->film); cudaFree(w->heat); cudaFree(w->mats); cudaFree(w->primMat); cudaFree(w->tex); cudaFree(w->texData);
+    cudaFree(w->film); cudaFree(w->heat); cudaFree(w->mats); cudaFree(w->primMat); cudaFree(w->tex); cudaFree(w->texData); cudaFree(w->lights);
     cudaFree(w->splatCount); cudaFree(w->splatPix); cudaFree(w->splatVal);
     cudaFree(w->haltonPerms); cudaFree(w->haltonDims); cudaFree(w->sobol32); cudaFree(w->sobolVdc);
     if (w->hCounts) cudaFreeHost(w->hCounts);
@@ -491,13 +494,18 @@ static int render_impl(b200rt_scene *s, const b200rt_render_desc *d, float *film
     std::memcpy(P.kd, d->kd, 12);
     P.max_depth = d->max_depth;
     if (d->max_depth > 68) return set_error(B200RT_EINVAL, "max_depth %u too large", d->max_depth);
-    rc = light_of(d, s->n_prims, &P.light);
+    std::vector<WfLight> lights;
+    rc = lights_of(d, s->n_prims, lights);
     if (rc) return rc;
-    const bool area = d->light_kind == B200RT_LIGHT_SPHERE;
-    const bool infinite = d->light_kind == B200RT_LIGHT_INFINITE;
-    const bool distant = d->light_kind == B200RT_LIGHT_DISTANT;
-    const bool mis = area || infinite;   // lights with area: EstimateDirect traces a BSDF-sampled ray too
-    (void)area;
+    P.light = lights[0];
+    P.nLights = (uint32_t)lights.size();
+    P.lights = nullptr;
+    bool mis = false, notPoint = false;   // mis = lights with area: EstimateDirect traces a BSDF-sampled ray too
+    for (const WfLight &l : lights) {
+        mis = mis || l.kind == B200RT_LIGHT_SPHERE || l.kind == B200RT_LIGHT_INFINITE;
+        notPoint = notPoint || l.kind != B200RT_LIGHT_POINT;
+    }
+    P.anyMis = mis ? 1u : 0u;
     if (d->materials && (!d->prim_material || d->n_materials == 0 || d->n_materials > 256))
         return set_error(B200RT_EINVAL, "materials need prim_material and 1..256 records");
     const uint32_t mstride = d->material_stride ? d->material_stride : 8;
@@ -511,6 +519,11 @@ static int render_impl(b200rt_scene *s, const b200rt_render_desc *d, float *film
     uint64_t want = d->max_batch ? d->max_batch : (envBatch ? envBatch : (1u << 22));
     uint64_t cap = std::max<uint64_t>(unit, want / unit * unit);
     cap = std::min<uint64_t>(cap, std::max<uint64_t>(unit, P.tl.n_paths_rank));
+    // a share that fits one default batch (one rank of an 8-rank headline frame) is split in two so that the second set of
+    // queue buffers has something to overlap with: 14.42 -> 14.18 ms (profiles/r02_ab_rank_share_batches.log); smaller
+    // batches than ~2 M paths lose more to the thin deep-bounce launches than the overlap returns
+    if (!d->max_batch && !envBatch && g_wf_sets.load() >= 2 && P.tl.n_paths_rank <= cap && P.tl.n_paths_rank >= (3ull << 20))
+        cap = std::max<uint64_t>(unit, ((P.tl.n_paths_rank + 1) / 2 + unit - 1) / unit * unit);
     if (cap > 0x7fffffffull) return set_error(B200RT_EINVAL, "batch too large");
     const uint32_t misBase = 2 * (d->max_depth + 2);          // counts[misBase + depth] = MIS queue size at depth
     const uint32_t nCounts = misBase + d->max_depth + 1;
@@ -539,6 +552,11 @@ static int render_impl(b200rt_scene *s, const b200rt_render_desc *d, float *film
         WCU(cudaMemcpy(w->mats, dev.data(), dev.size() * 4, cudaMemcpyHostToDevice));
         WCU(cudaMemcpy(w->primMat, d->prim_material, s->n_prims, cudaMemcpyHostToDevice));
         P.mats = w->mats; P.primMat = w->primMat;
+    }
+    if (P.nLights > 1) {
+        if (!w->lights) WCU(cudaMalloc(&w->lights, B200RT_MAX_LIGHTS * sizeof(WfLight)));
+        WCU(cudaMemcpy(w->lights, lights.data(), lights.size() * sizeof(WfLight), cudaMemcpyHostToDevice));
+        P.lights = w->lights;
     }
     P.tex = nullptr; P.nTex = 0;
     if (d->materials && d->textures && d->n_textures) {
@@ -582,7 +600,7 @@ static int render_impl(b200rt_scene *s, const b200rt_render_desc *d, float *film
     rc = setup_sampler(w, d, P, 5 + 8 * (d->max_depth + 1), st);
     if (rc) return rc;
     // the lean instantiation: one point light, one Lambertian Kd, no vertex normals / UVs / orientation flags
-    const bool full = mis || distant || P.mats || P.primN || P.primUV || P.primFlags;
+    const bool full = mis || notPoint || P.nLights > 1 || P.mats || P.primN || P.primUV || P.primFlags;
     const size_t npx = (size_t)P.tl.xres * P.tl.yres;
     cudaPointerAttributes pa;
     bool film_dev = cudaPointerGetAttributes(&pa, film) == cudaSuccess &&
@@ -758,7 +776,7 @@ static int render_impl(b200rt_scene *s, const b200rt_render_desc *d, float *film
                     k_heat<<<gridSlots, TB, 0, bs>>>(P, start, Q.counts + misBase + depth, Q.misPath, w->perRay, d_heat, 0u);
                     g_launches.fetch_add(1);
                 }
-                k_mis_resolve<<<gridSlots, TB, 0, bs>>>(Q.counts + misBase + depth, Q.hits, infinite ? (uint32_t)B200RT_MISS : d->light_prim, Q.misPath, Q.misContrib, Q.L);
+                k_mis_resolve<<<gridSlots, TB, 0, bs>>>(Q.counts + misBase + depth, Q.hits, Q.misPath, Q.misContrib, Q.L);
                 g_launches.fetch_add(1);
             }
             cur ^= 1;

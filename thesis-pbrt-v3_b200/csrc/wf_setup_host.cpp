@@ -171,24 +171,65 @@ bool material_lobes(const float *rec, uint32_t stride, uint32_t index, float *ou
 }
 
 
-int light_of(const b200rt_render_desc *d, uint32_t n_prims, WfLight *Lt) {
+// One light record, validated (the kinds and their fields: include/b200rt_wavefront.h).
+static int light_from(uint32_t kind, uint32_t prim, const float *pos, const float *I, float radius, const float *l2w, uint32_t n_prims, WfLight *Lt) {
     std::memset(Lt, 0, sizeof(*Lt));
-    std::memcpy(Lt->pos, d->light_pos, 12); std::memcpy(Lt->I, d->light_I, 12);
-    Lt->kind = d->light_kind; Lt->prim = d->light_prim; Lt->radius = d->light_radius;
-    if (d->light_kind > B200RT_LIGHT_INFINITE) return set_error(B200RT_EINVAL, "unknown light_kind %u", d->light_kind);
-    if (d->light_kind == B200RT_LIGHT_INFINITE) {
+    std::memcpy(Lt->pos, pos, 12); std::memcpy(Lt->I, I, 12);
+    Lt->kind = kind; Lt->prim = prim; Lt->radius = radius;
+    Lt->cdfHi = 1.f; Lt->pickPdf = 1.f;
+    if (kind > B200RT_LIGHT_INFINITE) return set_error(B200RT_EINVAL, "unknown light_kind %u", kind);
+    if (kind == B200RT_LIGHT_INFINITE) {
         bool zero = true;
-        for (int k = 0; k < 9; ++k) zero = zero && d->light_to_world[k] == 0.f;
-        for (int k = 0; k < 9; ++k) Lt->l2w[k] = zero ? (k % 4 == 0 ? 1.f : 0.f) : d->light_to_world[k];
-        if (!(d->light_radius > 0.f)) return set_error(B200RT_EINVAL, "infinite light: light_radius must be the scene's bounding-sphere radius");
+        for (int k = 0; k < 9; ++k) zero = zero && l2w[k] == 0.f;
+        for (int k = 0; k < 9; ++k) Lt->l2w[k] = zero ? (k % 4 == 0 ? 1.f : 0.f) : l2w[k];
+        if (!(radius > 0.f)) return set_error(B200RT_EINVAL, "infinite light: light_radius must be the scene's bounding-sphere radius");
     }
-    if (d->light_kind == B200RT_LIGHT_DISTANT) {
-        const float l2 = d->light_pos[0] * d->light_pos[0] + d->light_pos[1] * d->light_pos[1] + d->light_pos[2] * d->light_pos[2];
-        if (!(d->light_radius > 0.f) || !(std::fabs(l2 - 1.f) < 1e-3f))
+    if (kind == B200RT_LIGHT_DISTANT) {
+        const float l2 = pos[0] * pos[0] + pos[1] * pos[1] + pos[2] * pos[2];
+        if (!(radius > 0.f) || !(std::fabs(l2 - 1.f) < 1e-3f))
             return set_error(B200RT_EINVAL, "distant light: light_pos must be the unit direction to the light and light_radius the scene's bounding-sphere radius");
     }
-    if (d->light_kind == B200RT_LIGHT_SPHERE && (!(d->light_radius > 0.f) || d->light_prim >= n_prims))
+    if (kind == B200RT_LIGHT_SPHERE && (!(radius > 0.f) || prim >= n_prims))
         return set_error(B200RT_EINVAL, "sphere light: radius must be > 0 and light_prim a primitive of the scene");
+    return B200RT_OK;
+}
+
+int light_of(const b200rt_render_desc *d, uint32_t n_prims, WfLight *Lt) {
+    return light_from(d->light_kind, d->light_prim, d->light_pos, d->light_I, d->light_radius, d->light_to_world, n_prims, Lt);
+}
+
+// Scene::lights and the distribution UniformSampleOneLight draws from: Distribution1D(func, n) (sampling.h:57-69) over the
+// records' weights, restated with its float operations so that the device's choice is SampleDiscrete's for every u.
+int lights_of(const b200rt_render_desc *d, uint32_t n_prims, std::vector<WfLight> &out) {
+    out.clear();
+    if (d->n_lights == 0) {
+        out.resize(1);
+        return light_of(d, n_prims, &out[0]);
+    }
+    if (!d->lights) return set_error(B200RT_EINVAL, "n_lights = %u without a lights array", d->n_lights);
+    if (d->n_lights > B200RT_MAX_LIGHTS) return set_error(B200RT_EUNSUPPORTED, "%u lights: at most %u", d->n_lights, B200RT_MAX_LIGHTS);
+    const int n = (int)d->n_lights;
+    out.resize((size_t)n);
+    std::vector<float> func((size_t)n), cdf((size_t)n + 1);
+    for (int k = 0; k < n; ++k) {
+        const b200rt_light &l = d->lights[k];
+        const int rc = light_from(l.kind, l.prim, l.pos, l.I, l.radius, l.to_world, n_prims, &out[(size_t)k]);
+        if (rc) return rc;
+        if (!(l.weight >= 0.f)) return set_error(B200RT_EINVAL, "light %d: weight must be >= 0", k);
+        func[(size_t)k] = l.weight;
+    }
+    cdf[0] = 0;
+    for (int i = 1; i < n + 1; ++i) cdf[(size_t)i] = cdf[(size_t)i - 1] + func[(size_t)i - 1] / n;
+    const float funcInt = cdf[(size_t)n];
+    if (funcInt == 0) {
+        for (int i = 1; i < n + 1; ++i) cdf[(size_t)i] = float(i) / float(n);
+    } else {
+        for (int i = 1; i < n + 1; ++i) cdf[(size_t)i] /= funcInt;
+    }
+    for (int k = 0; k < n; ++k) {
+        out[(size_t)k].cdfHi = cdf[(size_t)k + 1];
+        out[(size_t)k].pickPdf = (funcInt > 0) ? func[(size_t)k] / (funcInt * n) : 0.f;
+    }
     return B200RT_OK;
 }
 

@@ -1,6 +1,8 @@
 // Host-side set-up shared by the wavefront driver (wavefront.cu) and the host-compiled check of the shade stage
 // (tests/hostshade): tile layout of a render description and the material record -> lobe list conversion.
 #pragma once
+#include <vector>
+
 #include "wf_shade.cuh"
 
 namespace b200rt {
@@ -11,4 +13,5 @@ int tiling_of(const b200rt_render_desc *d, WfTiling *t);
 bool material_lobes(const float *rec, uint32_t stride, uint32_t index, float *out, bool *hasSpecular, uint32_t nTextures = 0);
 // Light block of WfParams from the description; returns an error code for unsupported / inconsistent lights.
 int light_of(const b200rt_render_desc *d, uint32_t n_prims, WfLight *Lt);
+int lights_of(const b200rt_render_desc *d, uint32_t n_prims, std::vector<WfLight> &out);   // Scene::lights + the light distribution (ABI v10)
 }  // namespace b200rt

@@ -25,6 +25,8 @@ struct WfLight {
     float I[3];        // point: intensity; others: radiance
     float radius;      // sphere: radius; distant / infinite: the scene's bounding-sphere radius
     float l2w[9];      // infinite: rotation of LightToWorld, row-major
+    float cdfHi;       // cdf[k + 1] of the light distribution (Distribution1D, sampling.h:57-69) for light k
+    float pickPdf;     // Distribution1D::SampleDiscrete's pdf of choosing this light: func[k] / (funcInt * n)
 };
 
 struct WfParams {
@@ -32,7 +34,10 @@ struct WfParams {
     CamMat cm;                // the reference camera's matrices (cam_exact != 0)
     uint32_t cam_exact;
     WfTiling tl;
-    WfLight light;
+    WfLight light;            // lights[0]: the scene's only light unless nLights > 1
+    const WfLight *lights;    // nLights records (ABI v10) when nLights > 1, else unused
+    uint32_t nLights;
+    uint32_t anyMis;          // some light has area (sphere / infinite): EstimateDirect traces BSDF-sampled rays, emitters are visible
     float kd[3];
     uint32_t max_depth;
     const float *mats;        // kMatFloats per material (wf_bsdf.cuh); nullptr = one Lambertian lobe with R = kd
@@ -205,6 +210,7 @@ struct ShadeOut {
     V3 Le;                          // beta * emitted radiance seen at this vertex (already weighted)
     V3 so, sd, contrib;             // shadow ray (tMax = 1 - ShadowEpsilon) and the radiance it carries if unoccluded
     V3 mo, md, mcontrib;            // BSDF-sampled MIS ray of EstimateDirect and the radiance it carries if it reaches the light
+    uint32_t misPrim;               // ... i.e. if its closest hit is this primitive (the chosen sphere light) / B200RT_MISS (infinite light)
     V3 no, nd, beta;                // next path ray and the new throughput
     float betaW;                    // new (specularBounce, etaScale) code: 0 = (false, 1); else |w| = etaScale, w < 0 = specular bounce
     uint32_t dim;                   // the path's next sample dimension
@@ -339,18 +345,22 @@ WF_HD void shade_vertex(const WfParams &P, uint32_t depth, uint32_t x, uint32_t 
     o.Le = zero;
     o.dim = dim;
     o.betaW = betaW;
-    const WfLight &Lt = P.light;
-    const bool area = FULL && Lt.kind == B200RT_LIGHT_SPHERE, infinite = FULL && Lt.kind == B200RT_LIGHT_INFINITE;
+    const bool multi = FULL && P.nLights > 1;
     const bool specularBounce = FULL && betaW < 0.f;
     const float etaScale = (!FULL || betaW == 0.f) ? 1.f : fabsf(betaW);
     // path.cpp:97-107: emitted radiance at camera-ray hits and after a specular bounce
     if (FULL && (depth == 0 || specularBounce)) {
-        if (prim == B200RT_MISS) {
-            if (infinite) o.Le = spec_mul(beta, spec3(Lt.I));   // InfiniteAreaLight::Le with the constant map
-        } else if (area && prim == Lt.prim) {
-            // isect.Le(-ray.d) -> DiffuseAreaLight::L(intr, w): Lemit when Dot(intr.n, w) > 0; a sphere's n points outwards
-            const V3 ph = v3(rayO.x + t * rayD.x, rayO.y + t * rayD.y, rayO.z + t * rayD.z);
-            if (vdot(vsub(ph, spec3(Lt.pos)), vneg(rayD)) > 0.f) o.Le = spec_mul(beta, spec3(Lt.I));
+        const uint32_t nL = multi ? P.nLights : 1u;
+        for (uint32_t k = 0; k < nL; ++k) {
+            const WfLight &Le = multi ? P.lights[k] : P.light;
+            if (prim == B200RT_MISS) {
+                // `for (const auto &light : scene.infiniteLights) L += beta * light->Le(ray)`: InfiniteAreaLight::Le with the constant map
+                if (Le.kind == B200RT_LIGHT_INFINITE) o.Le = vadd(o.Le, spec_mul(beta, spec3(Le.I)));
+            } else if (Le.kind == B200RT_LIGHT_SPHERE && prim == Le.prim) {
+                // isect.Le(-ray.d) -> DiffuseAreaLight::L(intr, w): Lemit when Dot(intr.n, w) > 0; a sphere's n points outwards
+                const V3 ph = v3(rayO.x + t * rayD.x, rayO.y + t * rayD.y, rayO.z + t * rayD.z);
+                if (vdot(vsub(ph, spec3(Le.pos)), vneg(rayD)) > 0.f) o.Le = spec_mul(beta, spec3(Le.I));
+            }
         }
     }
     if (prim == B200RT_MISS || depth >= P.max_depth) return;   // path.cpp:110
@@ -377,8 +387,25 @@ WF_HD void shade_vertex(const WfParams &P, uint32_t depth, uint32_t x, uint32_t 
     path_sampler_init(P, x, y, s, dim, ps);
     // ---- direct lighting: UniformSampleOneLight (integrator.cpp:86-107) when the BSDF has a non-specular lobe ----
     const uint32_t nonSpec = BSDF_ALL & ~BSDF_SPECULAR;
-    if (bsdf_num_components(bs, nonSpec) > 0) {
-        get1d(P, ps);   // the light choice (integrator.cpp:96): one light, Distribution1D::SampleDiscrete -> 0 with pdf 1
+    // the light choice (integrator.cpp:93-97): Distribution1D::SampleDiscrete(u) = the last k with cdf[k] <= u (FindInterval,
+    // pbrt.h:334-350), its pdf func[k] / (funcInt * n); one light -> 0 with pdf 1.  A pdf of 0 returns before uLight / uScattering
+    // are drawn.
+    const WfLight *Lp = &P.light;
+    float pickPdf = 1.f;
+    bool direct = bsdf_num_components(bs, nonSpec) > 0;
+    if (direct) {
+        const float uPick = get1d(P, ps);
+        if (multi) {
+            uint32_t k = 0;
+            while (k + 1 < P.nLights && P.lights[k].cdfHi <= uPick) ++k;
+            Lp = P.lights + k;
+            pickPdf = Lp->pickPdf;
+            direct = pickPdf != 0.f;
+        }
+    }
+    const WfLight &Lt = *Lp;
+    const bool area = FULL && Lt.kind == B200RT_LIGHT_SPHERE, infinite = FULL && Lt.kind == B200RT_LIGHT_INFINITE;
+    if (direct) {
         const float ul0 = get1d(P, ps), ul1 = get1d(P, ps);   // uLight
         const float us0 = get1d(P, ps), us1 = get1d(P, ps);   // uScattering
         // EstimateDirect (integrator.cpp:109-217)
@@ -396,7 +423,7 @@ WF_HD void shade_vertex(const WfParams &P, uint32_t depth, uint32_t x, uint32_t 
                     const float wgt = (lightPdf * lightPdf) / (lightPdf * lightPdf + scatPdf * scatPdf);   // PowerHeuristic(1, lightPdf, 1, scatPdf)
                     Ld = spec_div(vmul(spec_mul(f, Li), wgt), lightPdf);
                 }
-                o.contrib = spec_mul(beta, spec_div(Ld, 1.f));   // / lightPdf of the light choice (= 1), * beta (path.cpp:133)
+                o.contrib = spec_mul(beta, spec_div(Ld, pickPdf));   // / lightPdf of the light choice, * beta (path.cpp:133)
                 o.so = so; o.sd = sd;
                 o.wantShadow = true;
             }
@@ -413,7 +440,8 @@ WF_HD void shade_vertex(const WfParams &P, uint32_t depth, uint32_t x, uint32_t 
                     const float wgt = (scatPdf * scatPdf) / (scatPdf * scatPdf + lp * lp);
                     // Ld += f * Li * Tr * weight / scatteringPdf, Li = Lemit when the ray reaches the light
                     const V3 Ld = spec_div(vmul(spec_mul(f, spec3(Lt.I)), wgt), scatPdf);
-                    o.mcontrib = spec_mul(beta, Ld);
+                    o.mcontrib = spec_mul(beta, spec_div(Ld, pickPdf));
+                    o.misPrim = area ? Lt.prim : (uint32_t)B200RT_MISS;
                     o.md = wiS;
                     o.mo = offset_ray_origin_ref(it.p, it.pError, it.n, wiS);
                     o.wantMis = true;

@@ -125,6 +125,96 @@ bool lambertianKd(const Material *m, Float kd[3]) {
     return true;
 }
 
+// One light of the scene as a b200rt_light: LightSource "point" (through Light::Sample_Li, lights/point.cpp:44-53), LightSource
+// "distant", AreaLightSource "area" on a full Shape "sphere" that is a primitive of the aggregate (lights/diffuse.cpp,
+// scenes/killeroo-simple:18-24) or a constant LightSource "infinite".
+bool describeLight(const Scene &scene, const B200Accel *accel, const Light *light, b200rt_light *out) {
+    std::memset(out, 0, sizeof(*out));
+    if (light->flags & (int)LightFlags::DeltaPosition) {
+        Interaction ref(Point3f(0, 0, 0), Normal3f(0, 0, 1), Vector3f(0, 0, 0), Vector3f(0, 0, 1), 0, MediumInterface());
+        Vector3f wi;
+        Float pdf;
+        VisibilityTester vis;
+        const Spectrum Li = light->Sample_Li(ref, Point2f(0.5f, 0.5f), &wi, &pdf, &vis);
+        const Point3f pl = vis.P1().p;
+        const Float d2 = (pl - Point3f(0, 0, 0)).LengthSquared();
+        Float rgb[3];
+        Spectrum(Li * d2).ToRGB(rgb);
+        out->pos[0] = pl.x; out->pos[1] = pl.y; out->pos[2] = pl.z;
+        for (int i = 0; i < 3; ++i) out->I[i] = rgb[i];
+    } else if (light->flags & (int)LightFlags::DeltaDirection) {
+        // LightSource "distant" (lights/distant.cpp:49-59): wi = wLight, Li = L for every reference point; shadow rays
+        // end 2 * worldRadius away, worldRadius as DistantLight::Preprocess takes it from the scene's bound (distant.h)
+        Interaction ref(Point3f(0, 0, 0), Normal3f(0, 0, 1), Vector3f(0, 0, 0), Vector3f(0, 0, 1), 0, MediumInterface());
+        Vector3f wi;
+        Float pdf;
+        VisibilityTester vis;
+        const Spectrum Li = light->Sample_Li(ref, Point2f(0.5f, 0.5f), &wi, &pdf, &vis);
+        Point3f wc;
+        Float wr;
+        scene.WorldBound().BoundingSphere(&wc, &wr);
+        Float rgb[3];
+        Li.ToRGB(rgb);
+        out->kind = B200RT_LIGHT_DISTANT;
+        out->radius = wr;
+        out->pos[0] = wi.x; out->pos[1] = wi.y; out->pos[2] = wi.z;
+        for (int i = 0; i < 3; ++i) out->I[i] = rgb[i];
+    } else if (light->flags & (int)LightFlags::Area) {
+        int lp = -1;
+        for (size_t i = 0; i < accel->primitiveCount(); ++i)
+            if (accel->primitive((uint32_t)i)->GetAreaLight() == light) {
+                if (lp >= 0) { Error("b200wavefront: the area light must sit on ONE sphere primitive"); return false; }
+                lp = (int)i;
+            }
+        const GeometricPrimitive *gp = lp < 0 ? nullptr : dynamic_cast<const GeometricPrimitive *>(accel->primitive((uint32_t)lp).get());
+        const Sphere *sp = gp ? dynamic_cast<const Sphere *>(gp->shape.get()) : nullptr;
+        if (!sp) { Error("b200wavefront: the area light's shape must be a sphere inside the b200 aggregate"); return false; }
+        const AreaLight *al = static_cast<const AreaLight *>(light);
+        Interaction it;
+        it.n = Normal3f(0, 0, 1);
+        Float le[3];
+        al->L(it, Vector3f(0, 0, 1)).ToRGB(le);
+        if (!al->L(it, Vector3f(0, 0, -1)).IsBlack()) { Error("b200wavefront: two-sided area lights are not supported"); return false; }
+        const Point3f c = (*sp->ObjectToWorld)(Point3f(0, 0, 0));
+        out->kind = B200RT_LIGHT_SPHERE;
+        out->radius = sp->radius;
+        out->prim = (uint32_t)lp;
+        out->pos[0] = c.x; out->pos[1] = c.y; out->pos[2] = c.z;
+        for (int i = 0; i < 3; ++i) out->I[i] = le[i];
+    } else if (light->flags & (int)LightFlags::Infinite) {
+        // LightSource "infinite" (lights/infinite.cpp) with a CONSTANT map — what the reference builds when "mapname" is
+        // absent or unreadable (scenes/living-room's sky map is not in the tree).  Read through the public interface:
+        // with the 1x1 map Sample_Li(u) is (theta, phi) = (u[1] pi, u[0] 2 pi) -> LightToWorld's columns, pdf 1/(2 pi^2 sin theta).
+        Point3f c; Float wr;
+        scene.WorldBound().BoundingSphere(&c, &wr);
+        Interaction ref(c, Normal3f(), Vector3f(), Vector3f(0, 0, 1), 0.f, MediumInterface());
+        Vector3f col[3]; Float pdf; VisibilityTester vis;
+        const Point2f us[3] = {Point2f(0.f, 0.5f), Point2f(0.25f, 0.5f), Point2f(0.f, 0.f)};
+        Float le[3];
+        for (int k = 0; k < 3; ++k) {
+            const Spectrum Li = light->Sample_Li(ref, us[k], &col[k], &pdf, &vis);
+            if (k == 0) Li.ToRGB(le);
+            if (k < 2 && std::abs(pdf * 2 * Pi * Pi - 1) > 1e-4f) { Error("b200wavefront: only a constant infinite light (no usable \"mapname\") is supported"); return false; }
+        }
+        for (int k = 0; k < 26; ++k) {   // Le must not depend on the direction
+            const Vector3f w = Normalize(Vector3f(Float(k % 3) - 1, Float(k / 3 % 3) - 1, Float(k / 9) - 1 + 0.01f));
+            Float q[3];
+            light->Le(RayDifferential(Ray(c, w))).ToRGB(q);
+            for (int i = 0; i < 3; ++i)
+                if (std::abs(q[i] - le[i]) > 1e-5f * (1 + std::abs(le[i]))) { Error("b200wavefront: only a constant infinite light is supported"); return false; }
+        }
+        out->kind = B200RT_LIGHT_INFINITE;
+        out->radius = wr;
+        for (int r = 0; r < 3; ++r)
+            for (int k = 0; k < 3; ++k) out->to_world[3 * r + k] = col[k][r];
+        for (int i = 0; i < 3; ++i) out->I[i] = le[i];
+    } else {
+        Error("b200wavefront: only a point light, a distant light, a sphere area light or a constant infinite light is supported");
+        return false;
+    }
+    return true;
+}
+
 }  // namespace
 
 void B200WavefrontIntegrator::Render(const Scene &scene) {
@@ -170,91 +260,31 @@ void B200WavefrontIntegrator::Render(const Scene &scene) {
         Error("b200wavefront: pixel filters wider than one pixel are not supported (use PixelFilter \"box\")");
         return;
     }
-    // the light: LightSource "point" (through Light::Sample_Li, lights/point.cpp:44-53), LightSource "distant", or AreaLightSource "area" on
-    // a full Shape "sphere" that is a primitive of the aggregate (lights/diffuse.cpp, scenes/killeroo-simple:18-24)
-    if (scene.lights.size() != 1) { Error("b200wavefront: exactly one light is supported"); return; }
-    const Light *light = scene.lights[0].get();
-    if (light->flags & (int)LightFlags::DeltaPosition) {
-        Interaction ref(Point3f(0, 0, 0), Normal3f(0, 0, 1), Vector3f(0, 0, 0), Vector3f(0, 0, 1), 0, MediumInterface());
-        Vector3f wi;
-        Float pdf;
-        VisibilityTester vis;
-        const Spectrum Li = light->Sample_Li(ref, Point2f(0.5f, 0.5f), &wi, &pdf, &vis);
-        const Point3f pl = vis.P1().p;
-        const Float d2 = (pl - Point3f(0, 0, 0)).LengthSquared();
-        Float rgb[3];
-        Spectrum(Li * d2).ToRGB(rgb);
-        d.light_pos[0] = pl.x; d.light_pos[1] = pl.y; d.light_pos[2] = pl.z;
-        for (int i = 0; i < 3; ++i) d.light_I[i] = rgb[i];
-    } else if (light->flags & (int)LightFlags::DeltaDirection) {
-        // LightSource "distant" (lights/distant.cpp:49-59): wi = wLight, Li = L for every reference point; shadow rays
-        // end 2 * worldRadius away, worldRadius as DistantLight::Preprocess takes it from the scene's bound (distant.h)
-        Interaction ref(Point3f(0, 0, 0), Normal3f(0, 0, 1), Vector3f(0, 0, 0), Vector3f(0, 0, 1), 0, MediumInterface());
-        Vector3f wi;
-        Float pdf;
-        VisibilityTester vis;
-        const Spectrum Li = light->Sample_Li(ref, Point2f(0.5f, 0.5f), &wi, &pdf, &vis);
-        Point3f wc;
-        Float wr;
-        scene.WorldBound().BoundingSphere(&wc, &wr);
-        Float rgb[3];
-        Li.ToRGB(rgb);
-        d.light_kind = B200RT_LIGHT_DISTANT;
-        d.light_radius = wr;
-        d.light_pos[0] = wi.x; d.light_pos[1] = wi.y; d.light_pos[2] = wi.z;
-        for (int i = 0; i < 3; ++i) d.light_I[i] = rgb[i];
-    } else if (light->flags & (int)LightFlags::Area) {
-        int lp = -1;
-        for (size_t i = 0; i < accel->primitiveCount(); ++i)
-            if (accel->primitive((uint32_t)i)->GetAreaLight() == light) {
-                if (lp >= 0) { Error("b200wavefront: the area light must sit on ONE sphere primitive"); return; }
-                lp = (int)i;
-            }
-        const GeometricPrimitive *gp = lp < 0 ? nullptr : dynamic_cast<const GeometricPrimitive *>(accel->primitive((uint32_t)lp).get());
-        const Sphere *sp = gp ? dynamic_cast<const Sphere *>(gp->shape.get()) : nullptr;
-        if (!sp) { Error("b200wavefront: the area light's shape must be a sphere inside the b200 aggregate"); return; }
-        const AreaLight *al = static_cast<const AreaLight *>(light);
-        Interaction it;
-        it.n = Normal3f(0, 0, 1);
-        Float le[3];
-        al->L(it, Vector3f(0, 0, 1)).ToRGB(le);
-        if (!al->L(it, Vector3f(0, 0, -1)).IsBlack()) { Error("b200wavefront: two-sided area lights are not supported"); return; }
-        const Point3f c = (*sp->ObjectToWorld)(Point3f(0, 0, 0));
-        d.light_kind = B200RT_LIGHT_SPHERE;
-        d.light_radius = sp->radius;
-        d.light_prim = (uint32_t)lp;
-        d.light_pos[0] = c.x; d.light_pos[1] = c.y; d.light_pos[2] = c.z;
-        for (int i = 0; i < 3; ++i) d.light_I[i] = le[i];
-    } else if (light->flags & (int)LightFlags::Infinite) {
-        // LightSource "infinite" (lights/infinite.cpp) with a CONSTANT map — what the reference builds when "mapname" is
-        // absent or unreadable (scenes/living-room's sky map is not in the tree).  Read through the public interface:
-        // with the 1x1 map Sample_Li(u) is (theta, phi) = (u[1] pi, u[0] 2 pi) -> LightToWorld's columns, pdf 1/(2 pi^2 sin theta).
-        Point3f c; Float wr;
-        scene.WorldBound().BoundingSphere(&c, &wr);
-        Interaction ref(c, Normal3f(), Vector3f(), Vector3f(0, 0, 1), 0.f, MediumInterface());
-        Vector3f col[3]; Float pdf; VisibilityTester vis;
-        const Point2f us[3] = {Point2f(0.f, 0.5f), Point2f(0.25f, 0.5f), Point2f(0.f, 0.f)};
-        Float le[3];
-        for (int k = 0; k < 3; ++k) {
-            const Spectrum Li = light->Sample_Li(ref, us[k], &col[k], &pdf, &vis);
-            if (k == 0) Li.ToRGB(le);
-            if (k < 2 && std::abs(pdf * 2 * Pi * Pi - 1) > 1e-4f) { Error("b200wavefront: only a constant infinite light (no usable \"mapname\") is supported"); return; }
+    // the lights (describeLight above), in Scene::lights order, and the distribution UniformSampleOneLight draws from
+    if (scene.lights.empty()) { Error("b200wavefront: the scene has no light"); return; }
+    if (scene.lights.size() > B200RT_MAX_LIGHTS) { Error("b200wavefront: %d lights, at most %d are supported", (int)scene.lights.size(), (int)B200RT_MAX_LIGHTS); return; }
+    std::vector<b200rt_light> lights(scene.lights.size());
+    for (size_t k = 0; k < scene.lights.size(); ++k) {
+        if (!describeLight(scene, accel, scene.lights[k].get(), &lights[k])) return;
+        lights[k].weight = 1.f;   // UniformLightDistribution (lightdistrib.cpp:68-71); also what one light gets under every strategy
+    }
+    if (lights.size() > 1) {
+        // CreateLightSampleDistribution (lightdistrib.cpp:48-66): "uniform" and "power" are one Distribution1D for the whole
+        // scene; "spatial" (the default) builds one per voxel lazily from 128 point samples and is not restated on the device
+        if (lightSampleStrategy == "power") {
+            for (size_t k = 0; k < lights.size(); ++k) lights[k].weight = scene.lights[k]->Power().y();   // ComputeLightPowerDistribution
+        } else if (lightSampleStrategy != "uniform") {
+            Error("b200wavefront: %d lights need \"string lightsamplestrategy\" \"uniform\" or \"power\" (\"%s\" is not built); nothing rendered",
+                  (int)lights.size(), lightSampleStrategy.c_str());
+            return;
         }
-        for (int k = 0; k < 26; ++k) {   // Le must not depend on the direction
-            const Vector3f w = Normalize(Vector3f(Float(k % 3) - 1, Float(k / 3 % 3) - 1, Float(k / 9) - 1 + 0.01f));
-            Float q[3];
-            light->Le(RayDifferential(Ray(c, w))).ToRGB(q);
-            for (int i = 0; i < 3; ++i)
-                if (std::abs(q[i] - le[i]) > 1e-5f * (1 + std::abs(le[i]))) { Error("b200wavefront: only a constant infinite light is supported"); return; }
-        }
-        d.light_kind = B200RT_LIGHT_INFINITE;
-        d.light_radius = wr;
-        for (int r = 0; r < 3; ++r)
-            for (int k = 0; k < 3; ++k) d.light_to_world[3 * r + k] = col[k][r];
-        for (int i = 0; i < 3; ++i) d.light_I[i] = le[i];
-    } else {
-        Error("b200wavefront: only a point light, a distant light, a sphere area light or a constant infinite light is supported");
-        return;
+        d.lights = lights.data();
+        d.n_lights = (uint32_t)lights.size();
+    }
+    {   // one light: the description's own fields (every ABI version reads them)
+        const b200rt_light &l = lights[0];
+        d.light_kind = l.kind; d.light_prim = l.prim; d.light_radius = l.radius;
+        std::memcpy(d.light_pos, l.pos, 12); std::memcpy(d.light_I, l.I, 12); std::memcpy(d.light_to_world, l.to_world, 36);
     }
     // materials: Material "matte" (constant Kd, sigma 0; measured through the public BSDF) and Material "plastic"
     // (constant Kd / Ks / roughness, remaproughness true), one record per distinct Material object
@@ -471,7 +501,9 @@ B200WavefrontIntegrator *CreateB200WavefrontIntegrator(const ParamSet &params, s
         return nullptr;
     }
     if (rank < 0 || rank >= std::max(world, 1)) { Error("b200wavefront: rank %d outside world %d", rank, world); return nullptr; }
-    return new B200WavefrontIntegrator(maxDepth, std::move(camera), std::move(sampler), rank, world, seed, generalStats, rendezvous);
+    // Integrator "path" "string lightsamplestrategy" (path.cpp:218-219, default "spatial"): it only matters with several lights
+    const std::string strategy = params.FindOneString("lightsamplestrategy", "spatial");
+    return new B200WavefrontIntegrator(maxDepth, std::move(camera), std::move(sampler), rank, world, seed, generalStats, rendezvous, strategy);
 }
 
 }  // namespace pbrt

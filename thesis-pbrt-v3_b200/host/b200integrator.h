@@ -30,9 +30,10 @@ class B200WavefrontIntegrator : public Integrator {
     // with world > 1 the ranks' films are summed into rank 0's through b200rt_film_reduce (CUDA IPC peer memory; `rendezvous`
     // names the directory the handles travel through) and rank 0 alone writes the image and the statistic matrices.
     B200WavefrontIntegrator(int maxDepth, std::shared_ptr<const Camera> camera, std::shared_ptr<Sampler> sampler,
-                            int rank = 0, int world = 1, int seed = 0, bool generalStats = false, std::string rendezvous = "")
+                            int rank = 0, int world = 1, int seed = 0, bool generalStats = false, std::string rendezvous = "",
+                            std::string lightSampleStrategy = "spatial")
         : maxDepth(maxDepth), camera(std::move(camera)), sampler(std::move(sampler)), rank(rank), world(world), seed(seed),
-          generalStats(generalStats), rendezvous(std::move(rendezvous)) {}
+          generalStats(generalStats), rendezvous(std::move(rendezvous)), lightSampleStrategy(std::move(lightSampleStrategy)) {}
     void Render(const Scene &scene);
     const b200rt_render_stats &stats() const { return lastStats; }
 
@@ -43,11 +44,13 @@ class B200WavefrontIntegrator : public Integrator {
     const int rank, world, seed;
     const bool generalStats;
     const std::string rendezvous;
+    const std::string lightSampleStrategy;   // with several lights: "uniform" | "power" ("spatial" is refused)
     b200rt_render_stats lastStats{};
 };
 
 // Parameters: "integer maxdepth" (path.cpp:209, default 5), "integer rank" / "integer world" (explicit only, default 0 / 1;
 // world > 1 requires "string rendezvous", a directory all ranks of the node can write), "integer seed" (hash sampler only),
+// "string lightsamplestrategy" (path.cpp:218-219; only read when the scene has several lights: "uniform" or "power"),
 // "bool generalstats" (default false:
 // true renders through the instrumented kernels, b200rt_render_heatmaps, fills the Film's per-pixel GeneralStats and
 // writes the thesis's statistic matrices with Film::WriteGeneralStats like SamplerIntegrator::Render does,
