@@ -54,6 +54,7 @@ static int g_pblocks[6][2];  // resident persistent blocks per SM, [kind][any]
 static int g_persist_bsp = 1;
 static int g_kd_prefetch = 0;      // B200RT_KD_PREFETCH=1: kd persistent kernel fetches the below child together with each node
 static uint32_t g_bvh_steps = 4;
+static uint32_t g_bvh_vote[2] = {1, 1}, g_bsp_vote[2] = {1, 1};   // the vote's weights (interior, leaf): B200RT_BVH_VOTE=wI,wL / B200RT_BSP_VOTE=wI,wL
 static uint32_t g_sstack = 10;     // BVH stack entries kept in shared memory (B200RT_SSTACK; 0 = all in local memory)
 static uint32_t g_toplevels = 0;   // BVH levels staged in shared memory per block (B200RT_TOPLEVELS; 0 = none, the default):
                                    // north-star item (3), built and measured — neutral at 3-6 levels, -1 % at 8
@@ -107,6 +108,8 @@ extern "C" int b200rt_init(int device) {
     if (const char *e = getenv("B200RT_PIPE_CHUNK")) g_pipe_chunk = std::min<uint32_t>(B200RT_PIPE_CHUNK_MAX, std::max(1024, atoi(e)));
     if (const char *e = getenv("B200RT_PIPE_RAMP")) g_pipe_ramp = atoi(e);
     if (const char *e = getenv("B200RT_BVH_STEPS")) g_bvh_steps = std::max(1, atoi(e));
+    if (const char *e = getenv("B200RT_BVH_VOTE")) { unsigned a = 1, b = 1; if (sscanf(e, "%u,%u", &a, &b) >= 1) { g_bvh_vote[0] = std::max(1u, a); g_bvh_vote[1] = std::max(1u, b); } }
+    if (const char *e = getenv("B200RT_BSP_VOTE")) { unsigned a = 1, b = 1; if (sscanf(e, "%u,%u", &a, &b) >= 1) { g_bsp_vote[0] = std::max(1u, a); g_bsp_vote[1] = std::max(1u, b); } }
     if (const char *e = getenv("B200RT_PERSIST_BSP")) g_persist_bsp = atoi(e);
     if (const char *e = getenv("B200RT_BSP_STEPS_N")) g_bsp_steps = (uint32_t)std::max(1, atoi(e));
     if (const char *e = getenv("B200RT_SSTACK_BSP")) g_sstack_bsp = (uint32_t)std::min(64, std::max(0, atoi(e)));
@@ -625,7 +628,9 @@ int b200rt::launch_trace(const b200rt_scene *s, const float4 *rays, uint64_t n, 
             b200rt_hit *ho = any ? nullptr : hits + off;
             uint8_t *oo = any ? occ + off : nullptr;
             const float4 *ri = rays + 2 * off;
-#define PL(fn, view) fn<<<blocks, B200RT_PBLOCK, (size_t)g_sstack_bsp * 12 * B200RT_PBLOCK, st>>>(view, ri, m, n_dev, ho, oo, pc, g_thresh, chunk, g_sstack_bsp, g_bsp_steps)
+            const uint32_t bspStepsW = pack_steps(g_bsp_steps, g_bsp_vote[0], g_bsp_vote[1]);
+            uint32_t bvhStepsW = pack_steps(g_bvh_steps, g_bvh_vote[0], g_bvh_vote[1]);
+#define PL(fn, view) fn<<<blocks, B200RT_PBLOCK, (size_t)g_sstack_bsp * 12 * B200RT_PBLOCK, st>>>(view, ri, m, n_dev, ho, oo, pc, g_thresh, chunk, g_sstack_bsp, bspStepsW)
             switch (s->kind * 2 + (any ? 1 : 0)) {
                 case B200RT_BVH * 2: case B200RT_BVH * 2 + 1: {
                     uint32_t topN = (g_toplevels && !g_bvh4) ? s->bvh.topCount[g_toplevels] : 0u;
@@ -642,7 +647,7 @@ int b200rt::launch_trace(const b200rt_scene *s, const float4 *rays, uint64_t n, 
                         blk = (unsigned)std::min<uint64_t>((m + chunk * wpb - 1) / (chunk * wpb), (uint64_t)g_sm_count * std::max(1, per));
                     }
                     void *args[] = {(void *)&s->bvh, (void *)&ri, (void *)&m, (void *)&n_dev, (void *)&ho, (void *)&oo, (void *)&pc,
-                                    (void *)&g_thresh, (void *)&chunk, (void *)&g_bvh_steps, (void *)&g_sstack, (void *)&topN};
+                                    (void *)&g_thresh, (void *)&chunk, (void *)&bvhStepsW, (void *)&g_sstack, (void *)&topN};
                     CU(cudaLaunchKernel(bvh_fn(any), dim3(blk), dim3(B200RT_PBLOCK), args, smem, st));
                     break;
                 }

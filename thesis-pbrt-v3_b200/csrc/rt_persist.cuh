@@ -22,6 +22,13 @@
 
 namespace b200rt {
 
+// The persistent kernels' per-round vote: the warp runs an interior round when nInterior * wI >= nLeaf * wL, else a primitive
+// round (one triangle per lane).  wI = wL = 1 is the plain majority; wI > 1 keeps the cheap interior rounds going until most
+// lanes wait at a leaf, so that the expensive primitive rounds run fuller.  Schedules only: every lane still sees its own
+// nodes and primitives in the reference's order.
+inline uint32_t pack_steps(uint32_t steps, uint32_t wI, uint32_t wL) { return (steps & 0xffu) | ((wI & 0xffu) << 8) | ((wL & 0xffu) << 16); }
+
+
 #define B200RT_DONE 0x7FFFFFFFu  // "no node": an interior ref that no tree can contain
 #define B200RT_PBLOCK 128
 
@@ -96,7 +103,7 @@ bvh_persistent_kernel(const __grid_constant__ BvhView S, const float4 *__restric
                       const uint32_t *__restrict__ n_dev, b200rt_hit *__restrict__ hits,
                       uint8_t *__restrict__ occluded, PersistCounters *pc, uint32_t thresh,
                       uint32_t chunk /* rays a warp claims per global atomic */,
-                      uint32_t steps /* interior steps a lane may take per vote */,
+                      uint32_t stepsW /* bits 0-7: interior steps a lane may take per vote; 8-15 / 16-23: the vote's weights (pack_steps) */,
                       uint32_t sdepth /* stack entries [0, sdepth) live in shared memory, the rest in local */,
                       uint32_t topN /* the first topN node records (= the top levels, BvhView::topCount) are staged in shared memory */) {
     // Shared-memory bottom of the traversal stack: entry d of thread t sits at sst[d * blockDim + t], i.e. in bank
@@ -175,9 +182,9 @@ bvh_persistent_kernel(const __grid_constant__ BvhView S, const float4 *__restric
             const unsigned mL = __ballot_sync(FULL, (cur & B200RT_LEAF_BIT) != 0);
             const uint32_t nI = __popc(mI), nL = __popc(mL);
             if (nI + nL == 0 || (!wq.drained && nI + nL < thresh)) break;
-            if (nI >= nL) {
+            if (nI * ((stepsW >> 8) & 0xffu) >= nL * (stepsW >> 16)) {
 #pragma unroll 1
-                for (uint32_t k = 0; k < steps && !(cur & B200RT_LEAF_BIT) && cur != B200RT_DONE; ++k) {
+                for (uint32_t k = 0; k < (stepsW & 0xffu) && !(cur & B200RT_LEAF_BIT) && cur != B200RT_DONE; ++k) {
                     const BvhNode2 *nd = S.nodes + cur;
                     float4 a, b, c, mf;
                     if (TOP && cur < topN) { const float4 *q = stop + 4 * (size_t)cur; a = q[0]; b = q[1]; c = q[2]; mf = q[3]; }
@@ -265,7 +272,7 @@ __global__ void __launch_bounds__(B200RT_PBLOCK, MINB)
 bvh4_persistent_kernel(const __grid_constant__ BvhView S, const float4 *__restrict__ rays, uint64_t n64,
                        const uint32_t *__restrict__ n_dev, b200rt_hit *__restrict__ hits,
                        uint8_t *__restrict__ occluded, PersistCounters *pc, uint32_t thresh, uint32_t chunk,
-                       uint32_t steps, uint32_t sdepth, uint32_t /*topN: unused*/) {
+                       uint32_t stepsW, uint32_t sdepth, uint32_t /*topN: unused*/) {
     extern __shared__ uint2 sst[];
     uint32_t n = (uint32_t)n64;
     if (n_dev) { const uint32_t m = *n_dev; n = m < n ? m : n; }
@@ -334,9 +341,9 @@ bvh4_persistent_kernel(const __grid_constant__ BvhView S, const float4 *__restri
             const unsigned mL = __ballot_sync(FULL, (cur & B200RT_LEAF_BIT) != 0);
             const uint32_t nI = __popc(mI), nL = __popc(mL);
             if (nI + nL == 0 || (!wq.drained && nI + nL < thresh)) break;
-            if (nI >= nL) {
+            if (nI * ((stepsW >> 8) & 0xffu) >= nL * (stepsW >> 16)) {
 #pragma unroll 1
-                for (uint32_t k = 0; k < steps && !(cur & B200RT_LEAF_BIT) && cur != B200RT_DONE; ++k) {
+                for (uint32_t k = 0; k < (stepsW & 0xffu) && !(cur & B200RT_LEAF_BIT) && cur != B200RT_DONE; ++k) {
                     const float4 *nd = S.nodes4[cur].q;
                     float4 a0, b0, c0, m0, a1, b1, c1, m1;
                     ldg256(nd, a0, b0); ldg256(nd + 2, c0, m0); ldg256(nd + 4, a1, b1); ldg256(nd + 6, c1, m1);
@@ -432,7 +439,7 @@ bsp_persistent_kernel(const __grid_constant__ BspView S, const float4 *__restric
                       const uint32_t *__restrict__ n_dev, b200rt_hit *__restrict__ hits,
                       uint8_t *__restrict__ occluded, PersistCounters *pc, uint32_t thresh, uint32_t chunk,
                       uint32_t sdepth /* todo entries [0, sdepth) live in shared memory (see bvh_persistent_kernel) */,
-                      uint32_t steps /* interior steps a lane may take per vote */) {
+                      uint32_t stepsW /* bits 0-7: interior steps a lane may take per vote; 8-15 / 16-23: the vote's weights (pack_steps) */) {
     extern __shared__ uint32_t sst32[];  // 3 planes (node, tMin, tMax) of sdepth x blockDim words: bank = lane
     uint32_t n = (uint32_t)n64;
     if (n_dev) { const uint32_t m = *n_dev; n = m < n ? m : n; }
@@ -488,9 +495,9 @@ bsp_persistent_kernel(const __grid_constant__ BspView S, const float4 *__restric
             const uint32_t nN = __popc(mN), nL = __popc(mL);
             if (nN + nL == 0 || (!wq.drained && nN + nL < thresh)) break;
             bool finished = false;
-            if (nN >= nL) {
+            if (nN * ((stepsW >> 8) & 0xffu) >= nL * (stepsW >> 16)) {
 #pragma unroll 1
-                for (uint32_t k = 0; k < steps && state == B200RT_ST_NODE; ++k) {
+                for (uint32_t k = 0; k < (stepsW & 0xffu) && state == B200RT_ST_NODE; ++k) {
                     if (!ANY && r.tMax < tMin) { finished = true; break; }  // kdtreeaccel.cpp:400 (closest-hit only)
                     BspStep nd;
                     uint2 wBelow = make_uint2(0u, 0u);
