@@ -389,12 +389,27 @@ def main():
     outs = {q: (torch.empty((len(b), 5), dtype=torch.int32).pin_memory() if q % 2 == 0
                 else torch.empty(len(b), dtype=torch.uint8).pin_memory()) for q, b in hq.items()}
 
-    def e2e_pass():
+    def e2e_pass_sync():   # one blocking call per queue (the pipeline drains after every queue)
         for q, b in hq.items():
             if q % 2 == 0:
                 accel.intersect_ptr(b.data_ptr(), len(b), outs[q].data_ptr(), stream)
             else:
                 accel.intersect_p_ptr(b.data_ptr(), len(b), outs[q].data_ptr(), stream)
+
+    def e2e_pass():
+        # as a host-side wavefront integrator issues them: the camera rays, then per bounce d the two queues it has in hand after
+        # shading bounce d's hits — the shadow rays of d (queue 2d+1) and the rays of bounce d+1 (queue 2d+2) — enqueued together
+        # (b200rt_intersect_*_async) and waited for before the next bounce
+        for d in range(-1, MAXDEPTH + 1):
+            pair = [q for q in (2 * d + 1, 2 * d + 2) if q >= 0 and q in hq]
+            for q in pair:
+                b = hq[q]
+                if q % 2 == 0:
+                    accel.intersect_ptr_async(b.data_ptr(), len(b), outs[q].data_ptr(), stream)
+                else:
+                    accel.intersect_p_ptr_async(b.data_ptr(), len(b), outs[q].data_ptr(), stream)
+            if pair:
+                accel.wait()
 
     # the copies alone (same bytes, H2D and D2H on two streams at once): the ceiling the host links put on e2e
     dbuf = {q: torch.empty_like(b, device=dev) for q, b in hq.items()}
@@ -423,6 +438,7 @@ def main():
         barrier()
         return max(a.elapsed_time(b_), 0.0) / reps, (time.perf_counter() - t0) * 1e3 / reps
     e2e_ms, _ = timed(e2e_pass)
+    e2e_sync_ms, _ = timed(e2e_pass_sync)
     _, copy_ms = timed(copy_pass)   # (the copies run on side streams: wall clock between barriers)
     del dbuf, dout
     n_e2e = sum(len(b) for b in hq.values())
@@ -430,19 +446,23 @@ def main():
     d2h = sum(len(b) * (20 if q % 2 == 0 else 1) for q, b in hq.items())
     per_rank = {"h2d_gbs": h2d / (e2e_ms * 1e-3) / 1e9, "d2h_gbs": d2h / (e2e_ms * 1e-3) / 1e9}
     if world > 1:  # every rank pushes its share through its own PCIe link at the same time
-        tm = torch.tensor([e2e_ms, copy_ms], dtype=torch.float64, device=dev)
+        tm = torch.tensor([e2e_ms, copy_ms, e2e_sync_ms], dtype=torch.float64, device=dev)
         dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+        e2e_sync_ms = float(tm[2])
         ts = torch.tensor([float(n_e2e), float(h2d), float(d2h)], dtype=torch.float64, device=dev)
         dist.all_reduce(ts, op=dist.ReduceOp.SUM)
         e2e_ms, copy_ms, n_e2e, h2d, d2h = float(tm[0]), float(tm[1]), int(ts[0]), int(ts[1]), int(ts[2])
     e2e = {"value": n_e2e / (e2e_ms * 1e-3) / 1e6, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
            "rays_per_step": n_e2e, "ms_per_step": e2e_ms,
+           "one_blocking_call_per_queue_mrays_s": n_e2e / (e2e_sync_ms * 1e-3) / 1e6,
            "copies_only_ms": copy_ms, "copies_only_mrays_s": n_e2e / (copy_ms * 1e-3) / 1e6,
            "h2d_gbs_all_ranks": h2d / (e2e_ms * 1e-3) / 1e9, "d2h_gbs_all_ranks": d2h / (e2e_ms * 1e-3) / 1e9,
            "rank0_link": per_rank, "cpu_affinity_rank0": affinity,
            "what": "FIXED workload at every N: the closest + shadow queues of the whole %dx%d frame at %d spp (tiles sharded by rank "
-                   "like the render's), b200rt_intersect_closest/any with pinned HOST rays in and HOST hits out on every rank at once "
-                   "(sum of rays / max-over-ranks time); copies_only = the same bytes moved by plain cudaMemcpyAsync (H2D and D2H "
+                   "like the render's), through the C ABI with pinned HOST rays in and HOST hits out on every rank at once (sum of rays / "
+                   "max-over-ranks time), issued the way a host-side wavefront integrator has them: camera rays, then per bounce its "
+                   "shadow queue and the next bounce's queue enqueued together (b200rt_intersect_any_async / _closest_async) and one "
+                   "b200rt_intersect_wait per bounce; one_blocking_call_per_queue = b200rt_intersect_closest / _any on each queue in turn; copies_only = the same bytes moved by plain cudaMemcpyAsync (H2D and D2H "
                    "streams together, no kernel): what the host links allow" % (XRES, YRES, E2E_SPP)}
     if rank == 0:
         from oracle import orcbind as ob

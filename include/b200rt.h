@@ -135,6 +135,18 @@ int b200rt_intersect_closest(b200rt_scene *scene, const b200rt_ray *rays, uint64
 /* Aggregate::IntersectP over a batch (bvh.cpp:398, kdtreeaccel.cpp:454, rbsp.cpp:479): occluded[i] = 0/1. */
 int b200rt_intersect_any(b200rt_scene *scene, const b200rt_ray *rays, uint64_t n, uint8_t *occluded,
                          void *stream);
+
+/* The two calls above split into enqueue + wait, for HOST rays and HOST results only.  The reference has no counterpart
+ * (Aggregate::Intersect returns its answer); a host-side wavefront integrator has, after shading one bounce, two independent
+ * queues in hand — that bounce's shadow rays (IntersectP) and the next bounce's rays (Intersect) — and these calls let it keep
+ * both in flight: every call appends its chunks to the scene's copy / kernel / copy pipeline (three streams, a ring of staging
+ * slots) and returns; the pipeline does not drain between calls.  `rays` is read from the moment of the call on (work pending on
+ * `stream` is NOT waited for); `rays` and the result buffer must stay alive and untouched
+ * until b200rt_intersect_wait(scene) returns (or until `stream`, which is made to wait for the results, has been synchronised).
+ * Results are those of the synchronous calls, bit for bit (same kernels, same chunks). */
+int b200rt_intersect_closest_async(b200rt_scene *scene, const b200rt_ray *rays, uint64_t n, b200rt_hit *hits, void *stream);
+int b200rt_intersect_any_async(b200rt_scene *scene, const b200rt_ray *rays, uint64_t n, uint8_t *occluded, void *stream);
+int b200rt_intersect_wait(b200rt_scene *scene);
 /* Instrumented variants (slower; counters accumulate into *counters, a HOST struct). */
 int b200rt_intersect_closest_counted(b200rt_scene *scene, const b200rt_ray *rays, uint64_t n,
                                      b200rt_hit *hits, b200rt_counters *counters, void *stream);

@@ -61,6 +61,9 @@ def lib():
         L.b200rt_scene_bounds.argtypes = [vp, C.POINTER(C.c_float * 6)]
         L.b200rt_intersect_closest.argtypes = [vp, vp, u64, vp, vp]
         L.b200rt_intersect_any.argtypes = [vp, vp, u64, vp, vp]
+        L.b200rt_intersect_closest_async.argtypes = [vp, vp, u64, vp, vp]
+        L.b200rt_intersect_any_async.argtypes = [vp, vp, u64, vp, vp]
+        L.b200rt_intersect_wait.argtypes = [vp]
         L.b200rt_intersect_closest_counted.argtypes = [vp, vp, u64, vp, C.POINTER(CountersStruct), vp]
         L.b200rt_intersect_any_counted.argtypes = [vp, vp, u64, vp, C.POINTER(CountersStruct), vp]
         L.b200rt_intersect_closest_stats.argtypes = [vp, vp, u64, vp, vp, vp]
@@ -306,6 +309,17 @@ class B200Accel:
 
     def intersect_p_ptr(self, rays_ptr, n, occ_ptr, stream=None):
         _check(lib().b200rt_intersect_any(self._h, rays_ptr, n, occ_ptr, stream))
+
+    # -- enqueue + wait (HOST buffers that stay alive and untouched until wait() returns): several queues in flight at once,
+    #    e.g. the shadow queue and the next closest-hit queue of one bounce
+    def intersect_ptr_async(self, rays_ptr, n, hits_ptr, stream=None):
+        _check(lib().b200rt_intersect_closest_async(self._h, rays_ptr, n, hits_ptr, stream))
+
+    def intersect_p_ptr_async(self, rays_ptr, n, occ_ptr, stream=None):
+        _check(lib().b200rt_intersect_any_async(self._h, rays_ptr, n, occ_ptr, stream))
+
+    def wait(self):
+        _check(lib().b200rt_intersect_wait(self._h))
 
     def close(self):
         if getattr(self, "_h", None):

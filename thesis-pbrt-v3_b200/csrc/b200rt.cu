@@ -83,6 +83,8 @@ static const void *bvh_fn(bool any) {
     return (const void *)f;
 }  // kd/RBSP/BSP todo entries kept in shared memory (B200RT_SSTACK_BSP)
 #define B200RT_PIPE_CHUNK_MAX (1024u * 1024u)
+static uint32_t g_pipe_kstreams = 2;          // B200RT_PIPE_KSTREAMS: kernel streams of the host-buffer pipeline (1 .. 4)
+static int g_pipe_nokernel = 0;               // B200RT_PIPE_NOKERNEL=1 (measurement only): the pipeline's copies and events without the kernels
 static int g_pipe_ramp = 1;                   // B200RT_PIPE_RAMP=0: uniform chunks (A/B)
 static uint32_t g_pipe_chunk = 256u * 1024u;  // rays per pipeline stage (B200RT_PIPE_CHUNK overrides, <= 1 Mi)
 
@@ -107,6 +109,8 @@ extern "C" int b200rt_init(int device) {
     if (const char *e = getenv("B200RT_THRESH")) g_thresh = (uint32_t)atoi(e);
     if (const char *e = getenv("B200RT_PIPE_CHUNK")) g_pipe_chunk = std::min<uint32_t>(B200RT_PIPE_CHUNK_MAX, std::max(1024, atoi(e)));
     if (const char *e = getenv("B200RT_PIPE_RAMP")) g_pipe_ramp = atoi(e);
+    if (const char *e = getenv("B200RT_PIPE_NOKERNEL")) g_pipe_nokernel = atoi(e);
+    if (const char *e = getenv("B200RT_PIPE_KSTREAMS")) g_pipe_kstreams = (uint32_t)std::min(4, std::max(1, atoi(e)));
     if (const char *e = getenv("B200RT_BVH_STEPS")) g_bvh_steps = std::max(1, atoi(e));
     if (const char *e = getenv("B200RT_BVH_VOTE")) { unsigned a = 1, b = 1; if (sscanf(e, "%u,%u", &a, &b) >= 1) { g_bvh_vote[0] = std::max(1u, a); g_bvh_vote[1] = std::max(1u, b); } }
     if (const char *e = getenv("B200RT_BSP_VOTE")) { unsigned a = 1, b = 1; if (sscanf(e, "%u,%u", &a, &b) >= 1) { g_bsp_vote[0] = std::max(1u, a); g_bsp_vote[1] = std::max(1u, b); } }
@@ -552,11 +556,12 @@ extern "C" void b200rt_scene_destroy(b200rt_scene *s) {
     cudaFree(s->d_nodes); cudaFree(s->d_indices); cudaFree(s->d_tris); cudaFree(s->d_spheres);
     cudaFree(s->d_prim_uv); cudaFree(s->d_prim_n); cudaFree(s->d_prim_flags); cudaFree(s->d_nodes4);
     cudaFree(s->d_stage_in); cudaFree(s->d_stage_out); cudaFree(s->d_counters); cudaFree(s->d_pc);
-    for (auto &l : s->lanes) {
-        cudaFree(l.d_in); cudaFree(l.d_out);
-        if (l.done) cudaEventDestroy(l.done);
-        if (l.st) cudaStreamDestroy(l.st);
+    for (auto &q : s->slots) {
+        cudaFree(q.d_in); cudaFree(q.d_out);
+        for (cudaEvent_t e : {q.evIn, q.evK, q.evOut}) if (e) cudaEventDestroy(e);
     }
+    for (cudaStream_t st : {s->sIn, s->sK[0], s->sK[1], s->sK[2], s->sK[3], s->sOut}) if (st) cudaStreamDestroy(st);
+    if (s->ev_end) cudaEventDestroy(s->ev_end);
     if (s->ev_start) cudaEventDestroy(s->ev_start);
     delete s;
 }
@@ -694,26 +699,32 @@ static int ensure(void **p, size_t *have, size_t want) {
 
 // Host-buffer batches: chunked 3-stage pipeline (H2D | trace | D2H) over three streams.
 
-static int run_pipelined(b200rt_scene *s, const b200rt_ray *rays, uint64_t n, void *out, bool any, cudaStream_t user) {
+// Host rays in, host results out, in chunks through the scene's three-stream pipeline (scene_internal.h).  `wait`: block until
+// the results are in `out` (the synchronous entry points); otherwise `user` is made to wait for them and the call returns.
+static int run_pipelined(b200rt_scene *s, const b200rt_ray *rays, uint64_t n, void *out, bool any, cudaStream_t user, bool wait) {
     const size_t out_elem = any ? 1 : sizeof(b200rt_hit);
     if (!s->lanes_ready) {
-        for (auto &l : s->lanes) {
-            CU(cudaStreamCreateWithFlags(&l.st, cudaStreamNonBlocking));
-            CU(cudaEventCreateWithFlags(&l.done, cudaEventDisableTiming));
-            CU(cudaMalloc(&l.d_in, (size_t)B200RT_PIPE_CHUNK_MAX * sizeof(b200rt_ray)));
-            CU(cudaMalloc(&l.d_out, (size_t)B200RT_PIPE_CHUNK_MAX * sizeof(b200rt_hit)));
+        for (cudaStream_t *st : {&s->sIn, &s->sK[0], &s->sK[1], &s->sK[2], &s->sK[3], &s->sOut}) CU(cudaStreamCreateWithFlags(st, cudaStreamNonBlocking));
+        for (auto &q : s->slots) {
+            for (cudaEvent_t *e : {&q.evIn, &q.evK, &q.evOut}) CU(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
+            CU(cudaMalloc(&q.d_in, (size_t)B200RT_PIPE_CHUNK_MAX * sizeof(b200rt_ray)));
+            CU(cudaMalloc(&q.d_out, (size_t)B200RT_PIPE_CHUNK_MAX * sizeof(b200rt_hit)));
         }
         CU(cudaEventCreateWithFlags(&s->ev_start, cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&s->ev_end, cudaEventDisableTiming));
         s->lanes_ready = true;
     }
-    CU(cudaEventRecord(s->ev_start, user));
-    for (auto &l : s->lanes) CU(cudaStreamWaitEvent(l.st, s->ev_start, 0));
+    if (wait) {   // the blocking calls start after whatever the caller queued on its stream
+        CU(cudaEventRecord(s->ev_start, user));
+        CU(cudaStreamWaitEvent(s->sIn, s->ev_start, 0));
+    }   // the enqueue calls read `rays` from the moment they are called: waiting for `user` here would chain every call behind
+        // the previous one's results (the stream is made to wait for those below) and the queues would not overlap
     // Chunk schedule: a short head (c/4, c/2) so the first kernel starts after 1/4 of a chunk's copy time, full chunks
     // in the middle, and the last chunk split in two so the un-overlapped tail (last kernel + last D2H) is short too.
-    int k = 0, idx = 0;
+    int idx = 0;
     uint64_t m = 0;
-    for (uint64_t off = 0; off < n; off += m, k = (k + 1) % 3, ++idx) {
-        b200rt_scene::Lane &l = s->lanes[k];
+    for (uint64_t off = 0; off < n; off += m, ++idx) {
+        b200rt_scene::Slot &q = s->slots[s->slot_next++ % b200rt_scene::kSlots];
         const uint64_t rem = n - off, c = g_pipe_chunk;
         m = std::min<uint64_t>(c, rem);
         if (g_pipe_ramp) {
@@ -721,22 +732,31 @@ static int run_pipelined(b200rt_scene *s, const b200rt_ray *rays, uint64_t n, vo
             else if (idx == 1) m = std::min<uint64_t>(rem, std::max<uint64_t>(c / 2, 1024));
             else if (rem <= c && rem > c / 2) m = rem / 2;
         }
-        CU(cudaMemcpyAsync(l.d_in, rays + off, m * sizeof(b200rt_ray), cudaMemcpyHostToDevice, l.st));
-        int rc = launch_trace(s, (const float4 *)l.d_in, m, nullptr, any ? nullptr : (b200rt_hit *)l.d_out,
-                              any ? (uint8_t *)l.d_out : nullptr, any, nullptr, l.st);
+        cudaStream_t sK = s->sK[s->chunk_next++ % g_pipe_kstreams];
+        if (q.used) {   // the slot's previous chunk: its kernel has read d_in, its D2H has drained d_out
+            CU(cudaStreamWaitEvent(s->sIn, q.evK, 0));
+            CU(cudaStreamWaitEvent(sK, q.evOut, 0));
+        }
+        CU(cudaMemcpyAsync(q.d_in, rays + off, m * sizeof(b200rt_ray), cudaMemcpyHostToDevice, s->sIn));
+        CU(cudaEventRecord(q.evIn, s->sIn));
+        CU(cudaStreamWaitEvent(sK, q.evIn, 0));
+        int rc = g_pipe_nokernel ? 0 : launch_trace(s, (const float4 *)q.d_in, m, nullptr, any ? nullptr : (b200rt_hit *)q.d_out,
+                                                    any ? (uint8_t *)q.d_out : nullptr, any, nullptr, sK);
         if (rc) return rc;
-        CU(cudaMemcpyAsync((char *)out + off * out_elem, l.d_out, m * out_elem, cudaMemcpyDeviceToHost, l.st));
+        CU(cudaEventRecord(q.evK, sK));
+        CU(cudaStreamWaitEvent(s->sOut, q.evK, 0));
+        CU(cudaMemcpyAsync((char *)out + off * out_elem, q.d_out, m * out_elem, cudaMemcpyDeviceToHost, s->sOut));
+        CU(cudaEventRecord(q.evOut, s->sOut));
+        q.used = true;
     }
-    for (auto &l : s->lanes) {
-        CU(cudaEventRecord(l.done, l.st));
-        CU(cudaStreamWaitEvent(user, l.done, 0));
-    }
-    CU(cudaStreamSynchronize(user));
+    CU(cudaEventRecord(s->ev_end, s->sOut));   // D2H copies complete in order: the last one done = all done
+    CU(cudaStreamWaitEvent(user, s->ev_end, 0));
+    if (wait) CU(cudaEventSynchronize(s->ev_end));
     return B200RT_OK;
 }
 
 static int run(b200rt_scene *s, const b200rt_ray *rays, uint64_t n, b200rt_hit *hits, uint8_t *occ, bool any,
-               b200rt_counters *counters, void *stream, b200rt_ray_stats *per_ray = nullptr) {
+               b200rt_counters *counters, void *stream, b200rt_ray_stats *per_ray = nullptr, bool async = false) {
     if (!s) return fail(B200RT_EINVAL, "null scene");
     b200rt_counters dummy;
     if (per_ray && !counters) counters = &dummy;  // per-ray stats come from the instrumented kernels
@@ -759,8 +779,9 @@ static int run(b200rt_scene *s, const b200rt_ray *rays, uint64_t n, b200rt_hit *
     const float4 *d_rays = (const float4 *)rays;
     void *d_out = (void *)outp;
     if (!rays_dev || !out_dev || counters) lock.lock();
-    if (!rays_dev && !out_dev && !counters && n > g_pipe_chunk)
-        return run_pipelined(s, rays, n, (void *)outp, any, st);
+    if (!rays_dev && !out_dev && !counters && (async || n > g_pipe_chunk))
+        return run_pipelined(s, rays, n, (void *)outp, any, st, !async);
+    if (async) return fail(B200RT_EINVAL, "the asynchronous calls take HOST rays and HOST results (device buffers are asynchronous through the plain calls)");
     if (!rays_dev) {
         int rc = ensure(&s->d_stage_in, &s->stage_in_bytes, n * sizeof(b200rt_ray));
         if (rc) return rc;
@@ -798,6 +819,18 @@ extern "C" int b200rt_intersect_closest(b200rt_scene *s, const b200rt_ray *rays,
 }
 extern "C" int b200rt_intersect_any(b200rt_scene *s, const b200rt_ray *rays, uint64_t n, uint8_t *occ, void *stream) {
     return run(s, rays, n, nullptr, occ, true, nullptr, stream);
+}
+extern "C" int b200rt_intersect_closest_async(b200rt_scene *s, const b200rt_ray *rays, uint64_t n, b200rt_hit *hits, void *stream) {
+    return run(s, rays, n, hits, nullptr, false, nullptr, stream, nullptr, true);
+}
+extern "C" int b200rt_intersect_any_async(b200rt_scene *s, const b200rt_ray *rays, uint64_t n, uint8_t *occ, void *stream) {
+    return run(s, rays, n, nullptr, occ, true, nullptr, stream, nullptr, true);
+}
+extern "C" int b200rt_intersect_wait(b200rt_scene *s) {
+    if (!s) return fail(B200RT_EINVAL, "null scene");
+    std::lock_guard<std::mutex> lock(s->mu);
+    if (s->lanes_ready) CU(cudaEventSynchronize(s->ev_end));
+    return B200RT_OK;
 }
 extern "C" int b200rt_intersect_closest_counted(b200rt_scene *s, const b200rt_ray *rays, uint64_t n, b200rt_hit *hits,
                                                 b200rt_counters *c, void *stream) {

@@ -26,15 +26,20 @@ struct b200rt_scene {
     void *d_stage_in = nullptr, *d_stage_out = nullptr;
     size_t stage_in_bytes = 0, stage_out_bytes = 0;
     b200rt::Counters *d_counters = nullptr;
-    // host-pointer calls are pipelined in chunks over B200RT_LANES streams: H2D of chunk i+1 overlaps the
-    // kernel of chunk i and the D2H of chunk i-1 (both copy engines + SMs busy at once)
-    struct Lane {
-        cudaStream_t st = nullptr;
+    // host-pointer calls are pipelined in chunks over three streams BY FUNCTION — host-to-device copies, kernels, device-to-host
+    // copies — and a ring of staging slots: the H2D engine runs ahead of the kernels by up to the ring's depth and never waits
+    // for a D2H of its own chunk; consecutive (asynchronous) calls continue the same pipeline without draining it
+    struct Slot {
         void *d_in = nullptr, *d_out = nullptr;
-        cudaEvent_t done = nullptr;
+        cudaEvent_t evIn = nullptr, evK = nullptr, evOut = nullptr;   // H2D done, kernel done (d_in free), D2H done (d_out free)
+        bool used = false;
     };
-    Lane lanes[3];
-    cudaEvent_t ev_start = nullptr;
+    static constexpr int kSlots = 6, kKernelStreams = 4;
+    Slot slots[kSlots];
+    uint32_t slot_next = 0;
+    cudaStream_t sIn = nullptr, sK[kKernelStreams] = {nullptr, nullptr, nullptr, nullptr}, sOut = nullptr;   // kernels of consecutive chunks alternate over g_pipe_kstreams streams: their tails overlap
+    uint32_t chunk_next = 0;
+    cudaEvent_t ev_start = nullptr, ev_end = nullptr;
     bool lanes_ready = false;
     // persistent kernels: ring of work-counter slots (one per in-flight launch; each slot is re-armed by
     // the last warp of the launch that used it)

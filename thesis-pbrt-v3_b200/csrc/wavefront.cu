@@ -522,7 +522,7 @@ static int render_impl(b200rt_scene *s, const b200rt_render_desc *d, float *film
     // a share that fits one default batch (one rank of an 8-rank headline frame) is split in two so that the second set of
     // queue buffers has something to overlap with: 14.42 -> 14.18 ms (profiles/r02_ab_rank_share_batches.log); smaller
     // batches than ~2 M paths lose more to the thin deep-bounce launches than the overlap returns
-    if (!d->max_batch && !envBatch && g_wf_sets.load() >= 2 && P.tl.n_paths_rank <= cap && P.tl.n_paths_rank >= (3ull << 20))
+    if (!d->max_batch && !envBatch && g_wf_sets.load() >= 2 && !heat && !w->keep && P.tl.n_paths_rank <= cap && P.tl.n_paths_rank >= (3ull << 20))
         cap = std::max<uint64_t>(unit, ((P.tl.n_paths_rank + 1) / 2 + unit - 1) / unit * unit);
     if (cap > 0x7fffffffull) return set_error(B200RT_EINVAL, "batch too large");
     const uint32_t misBase = 2 * (d->max_depth + 2);          // counts[misBase + depth] = MIS queue size at depth
