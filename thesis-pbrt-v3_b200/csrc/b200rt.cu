@@ -85,6 +85,7 @@ static const void *bvh_fn(bool any) {
 #define B200RT_PIPE_CHUNK_MAX (1024u * 1024u)
 static uint32_t g_pipe_kstreams = 2;          // B200RT_PIPE_KSTREAMS: kernel streams of the host-buffer pipeline (1 .. 4)
 static int g_pipe_nokernel = 0;               // B200RT_PIPE_NOKERNEL=1 (measurement only): the pipeline's copies and events without the kernels
+static int g_pipe_zerocopy = 0;               // B200RT_PIPE_ZEROCOPY=1 (experiment): kernels read PINNED host rays over PCIe themselves, no H2D stage
 static int g_pipe_ramp = 1;                   // B200RT_PIPE_RAMP=0: uniform chunks (A/B)
 static uint32_t g_pipe_chunk = 256u * 1024u;  // rays per pipeline stage (B200RT_PIPE_CHUNK overrides, <= 1 Mi)
 
@@ -109,6 +110,7 @@ extern "C" int b200rt_init(int device) {
     if (const char *e = getenv("B200RT_THRESH")) g_thresh = (uint32_t)atoi(e);
     if (const char *e = getenv("B200RT_PIPE_CHUNK")) g_pipe_chunk = std::min<uint32_t>(B200RT_PIPE_CHUNK_MAX, std::max(1024, atoi(e)));
     if (const char *e = getenv("B200RT_PIPE_RAMP")) g_pipe_ramp = atoi(e);
+    if (const char *e = getenv("B200RT_PIPE_ZEROCOPY")) g_pipe_zerocopy = atoi(e);
     if (const char *e = getenv("B200RT_PIPE_NOKERNEL")) g_pipe_nokernel = atoi(e);
     if (const char *e = getenv("B200RT_PIPE_KSTREAMS")) g_pipe_kstreams = (uint32_t)std::min(4, std::max(1, atoi(e)));
     if (const char *e = getenv("B200RT_BVH_STEPS")) g_bvh_steps = std::max(1, atoi(e));
@@ -719,6 +721,12 @@ static int run_pipelined(b200rt_scene *s, const b200rt_ray *rays, uint64_t n, vo
         CU(cudaStreamWaitEvent(s->sIn, s->ev_start, 0));
     }   // the enqueue calls read `rays` from the moment they are called: waiting for `user` here would chain every call behind
         // the previous one's results (the stream is made to wait for those below) and the queues would not overlap
+    const b200rt_ray *mapped = nullptr;   // zero-copy experiment: the device's view of pinned host rays
+    if (g_pipe_zerocopy) {
+        cudaPointerAttributes a;
+        if (cudaPointerGetAttributes(&a, rays) == cudaSuccess && a.type == cudaMemoryTypeHost && a.devicePointer) mapped = (const b200rt_ray *)a.devicePointer;
+        else cudaGetLastError();
+    }
     // Chunk schedule: a short head (c/4, c/2) so the first kernel starts after 1/4 of a chunk's copy time, full chunks
     // in the middle, and the last chunk split in two so the un-overlapped tail (last kernel + last D2H) is short too.
     int idx = 0;
@@ -737,10 +745,12 @@ static int run_pipelined(b200rt_scene *s, const b200rt_ray *rays, uint64_t n, vo
             CU(cudaStreamWaitEvent(s->sIn, q.evK, 0));
             CU(cudaStreamWaitEvent(sK, q.evOut, 0));
         }
-        CU(cudaMemcpyAsync(q.d_in, rays + off, m * sizeof(b200rt_ray), cudaMemcpyHostToDevice, s->sIn));
-        CU(cudaEventRecord(q.evIn, s->sIn));
-        CU(cudaStreamWaitEvent(sK, q.evIn, 0));
-        int rc = g_pipe_nokernel ? 0 : launch_trace(s, (const float4 *)q.d_in, m, nullptr, any ? nullptr : (b200rt_hit *)q.d_out,
+        if (!mapped) {
+            CU(cudaMemcpyAsync(q.d_in, rays + off, m * sizeof(b200rt_ray), cudaMemcpyHostToDevice, s->sIn));
+            CU(cudaEventRecord(q.evIn, s->sIn));
+            CU(cudaStreamWaitEvent(sK, q.evIn, 0));
+        }
+        int rc = g_pipe_nokernel ? 0 : launch_trace(s, mapped ? (const float4 *)(mapped + off) : (const float4 *)q.d_in, m, nullptr, any ? nullptr : (b200rt_hit *)q.d_out,
                                                     any ? (uint8_t *)q.d_out : nullptr, any, nullptr, sK);
         if (rc) return rc;
         CU(cudaEventRecord(q.evK, sK));
