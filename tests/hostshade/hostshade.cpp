@@ -158,8 +158,8 @@ extern "C" void hs_shade(const hs_ctx *c, uint32_t depth, uint64_t start, uint32
         path_pixel(P.tl, start + path, x, y, s);
         ShadeOut o;
         const V3 bt = v3(beta[4 * path], beta[4 * path + 1], beta[4 * path + 2]);
-        if (c->full) shade_vertex<true>(P, depth, x, y, s, pdim[path], v3(r[0], r[1], r[2]), v3(r[4], r[5], r[6]), prim, u2f(h[1]), u2f(h[2]), u2f(h[3]), u2f(h[4]), p0, p1, p2, sph, bt, beta[4 * path + 3], o);
-        else shade_vertex<false>(P, depth, x, y, s, pdim[path], v3(r[0], r[1], r[2]), v3(r[4], r[5], r[6]), prim, u2f(h[1]), u2f(h[2]), u2f(h[3]), u2f(h[4]), p0, p1, p2, sph, bt, beta[4 * path + 3], o);
+        if (c->full) shade_vertex<true>(P, depth, x, y, s, path_sample_index(P, x, y, s), pdim[path], v3(r[0], r[1], r[2]), v3(r[4], r[5], r[6]), prim, u2f(h[1]), u2f(h[2]), u2f(h[3]), u2f(h[4]), p0, p1, p2, sph, bt, beta[4 * path + 3], o);
+        else shade_vertex<false>(P, depth, x, y, s, path_sample_index(P, x, y, s), pdim[path], v3(r[0], r[1], r[2]), v3(r[4], r[5], r[6]), prim, u2f(h[1]), u2f(h[2]), u2f(h[3]), u2f(h[4]), p0, p1, p2, sph, bt, beta[4 * path + 3], o);
         L[4 * path] += o.Le.x; L[4 * path + 1] += o.Le.y; L[4 * path + 2] += o.Le.z;
         if (o.wantNext) {
             beta[4 * path] = o.beta.x; beta[4 * path + 1] = o.beta.y; beta[4 * path + 2] = o.beta.z; beta[4 * path + 3] = o.betaW;

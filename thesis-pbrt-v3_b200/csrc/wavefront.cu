@@ -46,11 +46,37 @@ __device__ __forceinline__ uint32_t warp_append(bool pred, uint32_t *counter) {
     return base + __popc(m & ((1u << lane) - 1u));
 }
 
+// Block-aggregated append to up to three queues at once: one atomic per queue per BLOCK.  Every warp of a launch appends to the
+// same two or three counters; with one atomic per warp the shade kernel spent 18 % of its stall samples waiting for them
+// (same-address atomics serialise in L2).  All threads of the block must call it.  slot[q] is only meaningful where pred[q].
+#define B200RT_WF_TB 256
+__device__ __forceinline__ void block_append3(bool p0, bool p1, bool p2, uint32_t *c0, uint32_t *c1, uint32_t *c2,
+                                              uint32_t &s0, uint32_t &s1, uint32_t &s2) {
+    __shared__ uint32_t wcount[3][B200RT_WF_TB / 32], wbase[3][B200RT_WF_TB / 32];
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+    const unsigned m0 = __ballot_sync(0xFFFFFFFFu, p0), m1 = __ballot_sync(0xFFFFFFFFu, p1), m2 = __ballot_sync(0xFFFFFFFFu, p2);
+    if (lane == 0) { wcount[0][warp] = __popc(m0); wcount[1][warp] = __popc(m1); wcount[2][warp] = __popc(m2); }
+    __syncthreads();
+    if (threadIdx.x < 3) {
+        const uint32_t q = threadIdx.x;
+        uint32_t total = 0;
+        for (uint32_t w = 0; w < nw; ++w) { wbase[q][w] = total; total += wcount[q][w]; }
+        uint32_t *c = q == 0 ? c0 : (q == 1 ? c1 : c2);
+        const uint32_t base = total ? atomicAdd(c, total) : 0u;
+        for (uint32_t w = 0; w < nw; ++w) wbase[q][w] += base;
+    }
+    __syncthreads();
+    const uint32_t below = (1u << lane) - 1u;
+    s0 = wbase[0][warp] + __popc(m0 & below);
+    s1 = wbase[1][warp] + __popc(m1 & below);
+    s2 = wbase[2][warp] + __popc(m2 & below);
+}
+
 // ---- stage kernels ------------------------------------------------------------------------------
 // Camera rays for path slots [batchStart, batchStart + nSlots) (Sampler::GetCameraSample + PerspectiveCamera::
 // GenerateRayDifferential, src/cameras/perspective.cpp:97-143, pinhole; wf_shade.cuh camera_ray).
 __global__ void k_camera(const __grid_constant__ WfParams P, uint64_t batchStart, uint32_t nSlots, float4 *rays,
-                         uint32_t *qPath, uint32_t *count, float4 *beta, float4 *L, uint32_t *pdim) {
+                         uint32_t *qPath, uint32_t *count, float4 *beta, float4 *L, uint32_t *pdim, uint4 *pinfo) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     bool active = false;
     uint32_t x = 0, y = 0, s = 0;
@@ -59,6 +85,10 @@ __global__ void k_camera(const __grid_constant__ WfParams P, uint64_t batchStart
         beta[i] = make_float4(1.f, 1.f, 1.f, 0.f);
         L[i] = make_float4(0.f, 0.f, 0.f, active ? 1.f : 0.f);
         pdim[i] = kCameraDims;
+        // the path's pixel, sample number and global sample index: the same at every bounce, so k_shade reads them back
+        // instead of redoing path_pixel's divisions and GetIndexForSample
+        const uint64_t idx = active ? path_sample_index(P, x, y, s) : 0ull;
+        pinfo[i] = make_uint4(x | (y << 16), s, (uint32_t)idx, (uint32_t)(idx >> 32));
     }
     const uint32_t slot = warp_append(active, count);
     if (!active) return;
@@ -76,7 +106,8 @@ template <bool FULL>
 __global__ void k_shade(const __grid_constant__ WfParams P, uint32_t depth, uint64_t batchStart,
                         const uint32_t *__restrict__ nCur, const float4 *__restrict__ rays,
                         const uint32_t *__restrict__ qPath, const b200rt_hit *__restrict__ hits,
-                        const float4 *__restrict__ primTris, float4 *beta, uint32_t *pdim, float4 *nextRays, uint32_t *nextPath,
+                        const float4 *__restrict__ primTris, float4 *beta, uint32_t *pdim, const uint4 *__restrict__ pinfo,
+                        float4 *nextRays, uint32_t *nextPath,
                         uint32_t *nNext, float4 *shRays, uint32_t *shPath, float4 *shContrib, uint32_t *nShadow,
                         float4 *L, float4 *misRays, uint32_t *misPath, float4 *misContrib, uint32_t *nMis) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -98,9 +129,9 @@ __global__ void k_shade(const __grid_constant__ WfParams P, uint32_t depth, uint
             p0 = v3(a.x, a.y, a.z); p1 = v3(b.x, b.y, b.z); p2 = v3(c.x, c.y, c.z);
             isSphere = (__float_as_uint(b.w) & B200RT_PRIM_SPHERE) != 0;
         }
-        uint32_t x, y, s;
-        path_pixel(P.tl, batchStart + path, x, y, s);
-        shade_vertex<FULL>(P, depth, x, y, s, pdim[path], v3(ro.x, ro.y, ro.z), v3(rd.x, rd.y, rd.z), h.prim, h.t, h.b0, h.b1, h.b2,
+        const uint4 pi = pinfo[path];
+        const uint32_t x = pi.x & 0xffffu, y = pi.x >> 16, s = pi.y;
+        shade_vertex<FULL>(P, depth, x, y, s, (uint64_t)pi.z | ((uint64_t)pi.w << 32), pdim[path], v3(ro.x, ro.y, ro.z), v3(rd.x, rd.y, rd.z), h.prim, h.t, h.b0, h.b1, h.b2,
                            p0, p1, p2, isSphere, v3(bt.x, bt.y, bt.z), bt.w, o);
         if (FULL && (o.Le.x != 0.f || o.Le.y != 0.f || o.Le.z != 0.f)) {
             float4 l = L[path];
@@ -112,21 +143,20 @@ __global__ void k_shade(const __grid_constant__ WfParams P, uint32_t depth, uint
             pdim[path] = o.dim;
         }
     }
-    const uint32_t sj = warp_append(o.wantShadow, nShadow);
+    uint32_t sj, nj, mj;
+    block_append3(o.wantShadow, o.wantNext, mis && o.wantMis, nShadow, nNext, nMis, sj, nj, mj);
     if (o.wantShadow) {
         shRays[2 * (size_t)sj] = make_float4(o.so.x, o.so.y, o.so.z, 1.f - kShadowEps);
         shRays[2 * (size_t)sj + 1] = make_float4(o.sd.x, o.sd.y, o.sd.z, 0.f);
         shPath[sj] = path;
         shContrib[sj] = make_float4(o.contrib.x, o.contrib.y, o.contrib.z, 0.f);
     }
-    const uint32_t nj = warp_append(o.wantNext, nNext);
     if (o.wantNext) {
         nextRays[2 * (size_t)nj] = make_float4(o.no.x, o.no.y, o.no.z, __int_as_float(0x7f800000));
         nextRays[2 * (size_t)nj + 1] = make_float4(o.nd.x, o.nd.y, o.nd.z, 0.f);
         nextPath[nj] = path;
     }
-    if (mis) {  // warp-uniform
-        const uint32_t mj = warp_append(o.wantMis, nMis);
+    if (mis) {  // launch-uniform
         if (o.wantMis) {
             misRays[2 * (size_t)mj] = make_float4(o.mo.x, o.mo.y, o.mo.z, __int_as_float(0x7f800000));
             misRays[2 * (size_t)mj + 1] = make_float4(o.md.x, o.md.y, o.md.z, 0.f);
@@ -250,6 +280,7 @@ __global__ void k_heat(const __grid_constant__ WfParams P, uint64_t batchStart, 
 struct QSet {
     float4 *rays[2], *shRays, *shContrib, *beta, *L, *misRays, *misContrib;
     uint32_t *qPath[2], *shPath, *counts, *pdim, *misPath;
+    uint4 *pinfo;   // per path: pixel, sample number, global sample index (k_camera)
     b200rt_hit *hits;
     uint8_t *occ;
 };
@@ -280,6 +311,7 @@ struct Workspace {
     size_t heat_px = 0;
     float4 *rays[2] = {nullptr, nullptr}, *shRays = nullptr, *shContrib = nullptr, *beta = nullptr, *L = nullptr;
     uint32_t *qPath[2] = {nullptr, nullptr}, *shPath = nullptr, *counts = nullptr, *pdim = nullptr;
+    uint4 *pinfo = nullptr;
     b200rt_hit *hits = nullptr;
     uint8_t *occ = nullptr;
     float4 *film = nullptr;
@@ -318,7 +350,7 @@ void free_kept(Workspace *w) {
 }
 void free_queues(Workspace *w) {
     for (int k = 0; k < 2; ++k) { cudaFree(w->rays[k]); cudaFree(w->qPath[k]); w->rays[k] = nullptr; w->qPath[k] = nullptr; }
-    cudaFree(w->shRays); cudaFree(w->shContrib); cudaFree(w->beta); cudaFree(w->L); cudaFree(w->shPath); cudaFree(w->pdim);
+    cudaFree(w->shRays); cudaFree(w->shContrib); cudaFree(w->beta); cudaFree(w->L); cudaFree(w->shPath); cudaFree(w->pdim); cudaFree(w->pinfo); w->pinfo = nullptr;
     cudaFree(w->counts); cudaFree(w->hits); cudaFree(w->occ); cudaFree(w->perRay);
     cudaFree(w->misRays); cudaFree(w->misContrib); cudaFree(w->misPath);
     w->shRays = w->shContrib = w->beta = w->L = w->misRays = w->misContrib = nullptr;
@@ -331,7 +363,7 @@ void free_alt(Workspace *w, int i) {
     QSet &a = w->alt[i];
     for (int k = 0; k < 2; ++k) { cudaFree(a.rays[k]); cudaFree(a.qPath[k]); }
     cudaFree(a.shRays); cudaFree(a.shContrib); cudaFree(a.beta); cudaFree(a.L); cudaFree(a.misRays); cudaFree(a.misContrib);
-    cudaFree(a.shPath); cudaFree(a.counts); cudaFree(a.pdim); cudaFree(a.misPath); cudaFree(a.hits); cudaFree(a.occ);
+    cudaFree(a.shPath); cudaFree(a.counts); cudaFree(a.pdim); cudaFree(a.pinfo); cudaFree(a.misPath); cudaFree(a.hits); cudaFree(a.occ);
     a = QSet{};
     w->altCap[i] = 0; w->altMis[i] = false;
 }
@@ -494,6 +526,7 @@ static int render_impl(b200rt_scene *s, const b200rt_render_desc *d, float *film
     std::memcpy(P.kd, d->kd, 12);
     P.max_depth = d->max_depth;
     if (d->max_depth > 68) return set_error(B200RT_EINVAL, "max_depth %u too large", d->max_depth);
+    if (P.tl.xres > 65000u || P.tl.yres > 65000u) return set_error(B200RT_EUNSUPPORTED, "film window %u x %u: at most 65000 pixels a side (a path's pixel is kept in 16 + 16 bits)", P.tl.xres, P.tl.yres);
     std::vector<WfLight> lights;
     rc = lights_of(d, s->n_prims, lights);
     if (rc) return rc;
@@ -531,7 +564,7 @@ static int render_impl(b200rt_scene *s, const b200rt_render_desc *d, float *film
         free_queues(w);
         for (int k = 0; k < 2; ++k) { WCU(cudaMalloc(&w->rays[k], cap * 32)); WCU(cudaMalloc(&w->qPath[k], cap * 4)); }
         WCU(cudaMalloc(&w->shRays, cap * 32)); WCU(cudaMalloc(&w->shContrib, cap * 16)); WCU(cudaMalloc(&w->shPath, cap * 4));
-        WCU(cudaMalloc(&w->beta, cap * 16)); WCU(cudaMalloc(&w->L, cap * 16)); WCU(cudaMalloc(&w->pdim, cap * 4));
+        WCU(cudaMalloc(&w->beta, cap * 16)); WCU(cudaMalloc(&w->L, cap * 16)); WCU(cudaMalloc(&w->pdim, cap * 4)); WCU(cudaMalloc(&w->pinfo, cap * 16));
         WCU(cudaMalloc(&w->hits, cap * sizeof(b200rt_hit))); WCU(cudaMalloc(&w->occ, cap));
         WCU(cudaMalloc(&w->counts, 4 * 3 * 72));
         w->cap = cap;
@@ -690,7 +723,7 @@ static int render_impl(b200rt_scene *s, const b200rt_render_desc *d, float *film
             const size_t c = w->cap;
             for (int k = 0; k < 2; ++k) { WCU(cudaMalloc(&q.rays[k], c * 32)); WCU(cudaMalloc(&q.qPath[k], c * 4)); }
             WCU(cudaMalloc(&q.shRays, c * 32)); WCU(cudaMalloc(&q.shContrib, c * 16)); WCU(cudaMalloc(&q.shPath, c * 4));
-            WCU(cudaMalloc(&q.beta, c * 16)); WCU(cudaMalloc(&q.L, c * 16)); WCU(cudaMalloc(&q.pdim, c * 4));
+            WCU(cudaMalloc(&q.beta, c * 16)); WCU(cudaMalloc(&q.L, c * 16)); WCU(cudaMalloc(&q.pdim, c * 4)); WCU(cudaMalloc(&q.pinfo, c * 16));
             WCU(cudaMalloc(&q.hits, c * sizeof(b200rt_hit))); WCU(cudaMalloc(&q.occ, c));
             WCU(cudaMalloc(&q.counts, 4 * 3 * 72));
             if (mis) { WCU(cudaMalloc(&q.misRays, c * 32)); WCU(cudaMalloc(&q.misContrib, c * 16)); WCU(cudaMalloc(&q.misPath, c * 4)); w->altMis[i] = true; }
@@ -699,7 +732,7 @@ static int render_impl(b200rt_scene *s, const b200rt_render_desc *d, float *film
     }
     QSet prim;
     prim.rays[0] = w->rays[0]; prim.rays[1] = w->rays[1]; prim.qPath[0] = w->qPath[0]; prim.qPath[1] = w->qPath[1];
-    prim.shRays = w->shRays; prim.shContrib = w->shContrib; prim.shPath = w->shPath; prim.beta = w->beta; prim.L = w->L; prim.pdim = w->pdim;
+    prim.shRays = w->shRays; prim.shContrib = w->shContrib; prim.shPath = w->shPath; prim.beta = w->beta; prim.L = w->L; prim.pdim = w->pdim; prim.pinfo = w->pinfo;
     prim.hits = w->hits; prim.occ = w->occ; prim.counts = w->counts;
     prim.misRays = w->misRays; prim.misContrib = w->misContrib; prim.misPath = w->misPath;
     cudaEvent_t t0 = timed ? ev(st) : nullptr;
@@ -707,7 +740,7 @@ static int render_impl(b200rt_scene *s, const b200rt_render_desc *d, float *film
         WCU(cudaEventRecord(w->evFork, st));
         for (int k = 0; k < nSets; ++k) WCU(cudaStreamWaitEvent(w->side[k], w->evFork, 0));
     }
-    const unsigned TB = 256;
+    const unsigned TB = B200RT_WF_TB;
     uint64_t batch = 0;
     for (uint64_t start = 0; start < P.tl.n_paths_rank; start += cap, ++batch) {
         const uint32_t nSlots = (uint32_t)std::min<uint64_t>(cap, P.tl.n_paths_rank - start);
@@ -717,7 +750,7 @@ static int render_impl(b200rt_scene *s, const b200rt_render_desc *d, float *film
         const unsigned gridSlots = (nSlots + TB - 1) / TB;
         WCU(cudaMemsetAsync(Q.counts, 0, 4 * nCounts, bs));
         // counts[2*depth] = closest queue size at depth, counts[2*depth+1] = shadow queue size at depth
-        k_camera<<<gridSlots, TB, 0, bs>>>(P, start, nSlots, Q.rays[0], Q.qPath[0], Q.counts, Q.beta, Q.L, Q.pdim);
+        k_camera<<<gridSlots, TB, 0, bs>>>(P, start, nSlots, Q.rays[0], Q.qPath[0], Q.counts, Q.beta, Q.L, Q.pdim, Q.pinfo);
         g_launches.fetch_add(1);
         int cur = 0;
         for (uint32_t depth = 0; depth <= d->max_depth; ++depth) {
@@ -738,7 +771,7 @@ static int render_impl(b200rt_scene *s, const b200rt_render_desc *d, float *film
             // bounce may still see there (path.cpp:97-107): one more shade launch, which only adds Le
             if (depth == d->max_depth && !(P.has_specular && mis)) break;
             (full ? k_shade<true> : k_shade<false>)<<<gridSlots, TB, 0, bs>>>(P, depth, start, Q.counts + 2 * depth, Q.rays[cur], Q.qPath[cur], Q.hits,
-                                              s->d_prim_tris, Q.beta, Q.pdim, Q.rays[cur ^ 1], Q.qPath[cur ^ 1],
+                                              s->d_prim_tris, Q.beta, Q.pdim, Q.pinfo, Q.rays[cur ^ 1], Q.qPath[cur ^ 1],
                                               Q.counts + 2 * (depth + 1), Q.shRays, Q.shPath, Q.shContrib,
                                               Q.counts + 2 * depth + 1, Q.L, Q.misRays, Q.misPath, Q.misContrib,
                                               Q.counts + misBase + depth);

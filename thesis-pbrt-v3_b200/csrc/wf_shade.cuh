@@ -77,6 +77,16 @@ WF_HD void path_sampler_init(const WfParams &P, uint32_t x, uint32_t y, uint32_t
     ps.s = s; ps.dim = dim;
     ps.index = sampler_index(P.smp, ps.px, ps.py, s);
 }
+// ... with the sample's global index already known (k_camera stores it per path: the index is the same at every bounce)
+WF_HD void path_sampler_init(const WfParams &P, uint32_t x, uint32_t y, uint32_t s, uint32_t dim, uint64_t index, PathSampler &ps) {
+    ps.px = (int32_t)(x + P.tl.x0); ps.py = (int32_t)(y + P.tl.y0);
+    ps.pixOrd = (uint32_t)ps.py * P.cam.xres + (uint32_t)ps.px;
+    ps.s = s; ps.dim = dim;
+    ps.index = index;
+}
+WF_HD uint64_t path_sample_index(const WfParams &P, uint32_t x, uint32_t y, uint32_t s) {
+    return sampler_index(P.smp, (int32_t)(x + P.tl.x0), (int32_t)(y + P.tl.y0), s);
+}
 WF_HD float get1d(const WfParams &P, PathSampler &ps) { return sampler_dim(P.smp, ps.index, ps.dim++, ps.px, ps.py, ps.pixOrd, ps.s); }
 
 // ---- camera ray of one path slot -------------------------------------------------------------------------------------
@@ -337,7 +347,8 @@ WF_HD_NOINLINE void textured_material(const WfParams &P, const float *m, uint32_
 //   bt  : beta.xyz and the (specularBounce, etaScale) code in w
 //   dim : the path's next sample dimension
 template <bool FULL>
-WF_HD void shade_vertex(const WfParams &P, uint32_t depth, uint32_t x, uint32_t y, uint32_t s, uint32_t dim, V3 rayO, V3 rayD,
+WF_HD void shade_vertex(const WfParams &P, uint32_t depth, uint32_t x, uint32_t y, uint32_t s, uint64_t sidx /* path_sample_index(x, y, s) */,
+                        uint32_t dim, V3 rayO, V3 rayD,
                         uint32_t prim, float t, float b0, float b1, float b2, V3 p0, V3 p1, V3 p2, bool isSphere,
                         V3 beta, float betaW, ShadeOut &o) {
     const V3 zero = v3(0.f, 0.f, 0.f);
@@ -384,7 +395,7 @@ WF_HD void shade_vertex(const WfParams &P, uint32_t depth, uint32_t x, uint32_t 
         }
     }
     PathSampler ps;
-    path_sampler_init(P, x, y, s, dim, ps);
+    path_sampler_init(P, x, y, s, dim, sidx, ps);
     // ---- direct lighting: UniformSampleOneLight (integrator.cpp:86-107) when the BSDF has a non-specular lobe ----
     const uint32_t nonSpec = BSDF_ALL & ~BSDF_SPECULAR;
     // the light choice (integrator.cpp:93-97): Distribution1D::SampleDiscrete(u) = the last k with cdf[k] <= u (FindInterval,
