@@ -136,12 +136,20 @@ typedef struct {
                               lightsamplestrategy" "uniform" (UniformLightDistribution, lightdistrib.cpp:68-75), Light::Power().y()
                               of each light = "power" (PowerLightDistribution).  The estimate is divided by the choice's
                               probability; a light of weight 0 is never chosen.  "spatial" (the default when a scene has
-                              more than one light, a per-voxel distribution built lazily from 128 samples a voxel) is NOT
-                              built: the host mirrors refuse it.  Emitted radiance seen by camera rays and after specular
+                              more than one light): light_strategy below.  Emitted radiance seen by camera rays and after specular
                               bounces: the hit sphere's own light (path.cpp:100) and the SUM over every infinite light for rays
                               that escape (path.cpp:103-104).  At most B200RT_MAX_LIGHTS. */
     uint32_t n_lights;
+    uint32_t light_strategy; /* with n_lights > 1: B200RT_LIGHTS_WEIGHTS (0) = the one distribution over the records' weights described
+                              above; B200RT_LIGHTS_SPATIAL (1) = "lightsamplestrategy" "spatial", the path integrator's default
+                              (SpatialLightDistribution, lightdistrib.cpp:95-300): the scene's bound is cut into voxels (64 along its
+                              widest side), each voxel gets its own Distribution1D from 128 Halton points inside it at which every
+                              light is sampled (Li.y() / pdf, floored at 0.1 % of the average), and a path vertex chooses from the
+                              distribution of the voxel it lies in.  The reference fills its hash table of voxels lazily; here every
+                              voxel's distribution is computed on the device before the frame (a voxel's values do not depend on when
+                              it is computed).  The weights are ignored. */
 } b200rt_render_desc;
+enum { B200RT_LIGHTS_WEIGHTS = 0, B200RT_LIGHTS_SPATIAL = 1 };
 #define B200RT_MAX_LIGHTS 64u
 enum { B200RT_SAMPLER_HASH = 0, B200RT_SAMPLER_HALTON = 1, B200RT_SAMPLER_SOBOL = 2 };
 enum { B200RT_LIGHT_POINT = 0, B200RT_LIGHT_SPHERE = 1, B200RT_LIGHT_DISTANT = 2, B200RT_LIGHT_INFINITE = 3 };

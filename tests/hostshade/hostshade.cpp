@@ -6,6 +6,8 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <algorithm>
+#include <thread>
 #include <vector>
 #include "../../thesis-pbrt-v3_b200/csrc/wf_setup_host.h"
 #include "../../thesis-pbrt-v3_b200/csrc/wf_sampler_host.h"
@@ -28,12 +30,14 @@ struct hs_ctx {
     std::vector<uint64_t> vdc;
     std::vector<WfTexture> tex;
     std::vector<WfLight> lights;
+    std::vector<float> vox;   // "spatial": cdfHi then pickPdf of every voxel
 };
 
 extern "C" const char *hs_last_error() { return g_err; }
 
 extern "C" hs_ctx *hs_create(const b200rt_render_desc *d, uint32_t n_prims, const float *tri_verts, const float *tri_uvs,
-                             const float *tri_normals, const uint8_t *prim_flags, const uint8_t *prim_is_sphere) {
+                             const float *tri_normals, const uint8_t *prim_flags, const uint8_t *prim_is_sphere,
+                             const float *scene_bounds /* 6 floats: Scene::WorldBound(), needed by the spatial light distribution */) {
     hs_ctx *c = new hs_ctx;
     WfParams &P = c->P;
     std::memset(&P, 0, sizeof(P));
@@ -46,6 +50,26 @@ extern "C" hs_ctx *hs_create(const b200rt_render_desc *d, uint32_t n_prims, cons
     P.light = c->lights[0];
     P.nLights = (uint32_t)c->lights.size();
     P.lights = P.nLights > 1 ? c->lights.data() : nullptr;
+    if (P.nLights > 1 && d->light_strategy == B200RT_LIGHTS_SPATIAL) {
+        // every voxel's distribution (the device computes them with k_light_voxels), here on a few host threads
+        std::memcpy(P.wb, scene_bounds, sizeof(P.wb));
+        spatial_voxel_counts(P.wb, 64, P.nVox);
+        const size_t nv = (size_t)P.nVox[0] * P.nVox[1] * P.nVox[2], per = nv * P.nLights;
+        c->vox.resize(2 * per);
+        float halton[640];
+        spatial_halton_table(halton);
+        const unsigned nt = std::max(1u, std::min(16u, std::thread::hardware_concurrency()));
+        std::vector<std::thread> th;
+        for (unsigned t = 0; t < nt; ++t)
+            th.emplace_back([&, t] {
+                std::vector<float> contrib(P.nLights);
+                for (size_t v = t; v < nv; v += nt)
+                    spatial_voxel_distribution(c->lights.data(), P.nLights, P.wb, P.nVox, (uint32_t)v, halton, contrib.data(),
+                                               c->vox.data() + v * P.nLights, c->vox.data() + per + v * P.nLights);
+            });
+        for (auto &x : th) x.join();
+        P.voxCdf = c->vox.data(); P.voxPdf = c->vox.data() + per;
+    }
     bool notPoint = false;
     for (const WfLight &l : c->lights) {
         if (l.kind == B200RT_LIGHT_SPHERE || l.kind == B200RT_LIGHT_INFINITE) P.anyMis = 1;

@@ -21,7 +21,7 @@ def lib():
         L = C.CDLL(os.path.join(HS_DIR, "libhostshade.so"))
         vp = C.c_void_p
         L.hs_create.restype = vp
-        L.hs_create.argtypes = [vp, C.c_uint32, vp, vp, vp, vp, vp]
+        L.hs_create.argtypes = [vp, C.c_uint32, vp, vp, vp, vp, vp, vp]
         L.hs_destroy.argtypes = [vp]
         L.hs_last_error.restype = C.c_char_p
         L.hs_n_paths.restype = C.c_uint64
@@ -61,7 +61,8 @@ class HostWavefront:
             prim_flags = np.full(len(self.tv), 2, np.uint8)
         self.pf = None if prim_flags is None else np.ascontiguousarray(prim_flags, np.uint8)
         self.sph = None if prim_is_sphere is None else np.ascontiguousarray(prim_is_sphere, np.uint8)
-        self.h = lib().hs_create(C.byref(desc), len(self.tv), _p(self.tv), _p(self.uv), _p(self.tn), _p(self.pf), _p(self.sph))
+        self.bounds = np.ascontiguousarray(orc.bounds, np.float32)   # Scene::WorldBound() = the aggregate's
+        self.h = lib().hs_create(C.byref(desc), len(self.tv), _p(self.tv), _p(self.uv), _p(self.tn), _p(self.pf), _p(self.sph), _p(self.bounds))
         if not self.h:
             raise RuntimeError(lib().hs_last_error().decode())
 

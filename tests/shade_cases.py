@@ -99,7 +99,7 @@ def build(name, res=48):
             integ.update(light_I=(1.0, 0.9, 0.8), infinite_light=(l2w[:3, :3], wf.world_radius(verts)))
             out["mis"] = True
             out["infinite_scene"] = True
-        elif kind in ("lights", "lights_power"):
+        elif kind in ("lights", "lights_power", "lights_spatial"):
             # Scene::lights = the file's sphere area light + a point, a distant and a constant infinite light: every light kind
             # in one distribution ("uniform", or "power": weights = the reference's own Light::Power().y(), filled in by
             # hostwf.reference_trace / the image test after the reference built its scene)
@@ -110,7 +110,7 @@ def build(name, res=48):
             extra = [dict(kind="point", pos=(100.0, -150.0, 200.0), I=(60000.0, 50000.0, 40000.0)),
                      dict(kind="distant", w=(-0.3, 0.4, 1.0), L=(1.5, 1.5, 1.2), world_radius=wr),
                      dict(kind="infinite", L=(0.3, 0.35, 0.5), light_to_world=l2w, world_radius=wr)]
-            strategy = "power" if kind == "lights_power" else "uniform"
+            strategy = {"lights": "uniform", "lights_power": "power", "lights_spatial": "spatial"}[kind]
             render.update(emitter_L=sl["L"], extra_lights=extra, lightsamplestrategy=strategy)
             del integ["light_pos"], integ["light_I"]
             integ.update(lights=[dict(kind="sphere", center=sl["center"], L=sl["L"], radius=sl["radius"], prim=len(verts) - 1)] + extra,
@@ -201,4 +201,4 @@ def build(name, res=48):
 
 CASES = ["sponza_point", "killeroo_plastic", "killeroo_normals", "killeroo_glass", "killeroo_metal", "killeroo_oren", "killeroo_uber", "killeroo_infinite",
          "feet_distant", "normals", "normals_flipped", "living_room", "living_room_tex", "sponza_two_points", "killeroo_lights",
-         "killeroo_lights_power"]
+         "killeroo_lights_power", "killeroo_lights_spatial"]

@@ -141,17 +141,18 @@ def test_parsed_scene_with_an_image_texture(tmp_path):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("strategy", ["uniform", "power"])
+@pytest.mark.parametrize("strategy", ["uniform", "power", "spatial", None])
 def test_parsed_scene_with_four_lights(tmp_path, strategy):
     """Several LightSource statements (point, distant, constant infinite) next to the file's sphere area light, through
     pbrtParseFile: UniformSampleOneLight over `"string lightsamplestrategy" "uniform"` / `"power"` (ABI v10: the C++ integrator
-    describes every light of Scene::lights and, for "power", weighs them by the reference's own Light::Power().y()) against the
-    stock run of the same file with the same strategy."""
+    describes every light of Scene::lights and, for "power", weighs them by the reference's own Light::Power().y()), `"spatial"`
+    and no strategy at all (= "spatial", the path integrator's default: one distribution per voxel of the scene's bound) against
+    the stock run of the same file with the same strategy."""
     import pbrt_scenes as ps
     import hostwf
     d = str(tmp_path)
     kw = dict(xres=384, yres=384, spp=8, more_lights=ps.MORE_LIGHTS)
-    integ = '"integer maxdepth" [5] "string lightsamplestrategy" "%s"' % strategy
+    integ = '"integer maxdepth" [5]' + ('' if strategy is None else ' "string lightsamplestrategy" "%s"' % strategy)
     scene = ps.killeroo_simple(d, 'Accelerator "bvh"', integrator='Integrator "path" ' + integ, filename="stock.pfm", **kw)
     rc, out = _run(scene, d)
     assert rc == 0, out
@@ -167,15 +168,3 @@ def test_parsed_scene_with_four_lights(tmp_path, strategy):
     scene = ps.killeroo_simple(d, 'Accelerator "bvh"', filename="plain.pfm", xres=384, yres=384, spp=8)
     rc, _ = _run(scene, d)
     assert rc == 0 and np.abs(ps.read_pfm(os.path.join(d, "plain.pfm")) - ref).max() > 0.05
-
-
-@pytest.mark.gpu
-def test_spatial_light_distribution_is_refused(tmp_path):
-    """The reference's default for scenes with several lights, "spatial" (a lazily built per-voxel distribution), is not restated:
-    the integrator says so and renders nothing rather than something else."""
-    import pbrt_scenes as ps
-    d = str(tmp_path)
-    scene = ps.killeroo_simple(d, 'Accelerator "b200" "string tree" "bvh"', integrator='Integrator "b200wavefront" "integer maxdepth" [5]',
-                               filename="spatial.pfm", xres=64, yres=64, spp=1, more_lights=ps.MORE_LIGHTS)
-    rc, out = _run(scene, d, quiet=False)
-    assert "lightsamplestrategy" in out and not os.path.exists(os.path.join(d, "spatial.pfm")), out

@@ -47,7 +47,7 @@ def test_camera_matrices_equal_the_reference_cameras(built_lib):
 
 @pytest.mark.parametrize("case", ["sponza_point", "killeroo_plastic", "killeroo_normals", "killeroo_glass", "killeroo_metal", "killeroo_oren", "killeroo_uber",
                                   "killeroo_infinite", "feet_distant", "normals", "normals_flipped", "living_room", "living_room_tex",
-                                  "sponza_two_points", "killeroo_lights", "killeroo_lights_power"])
+                                  "sponza_two_points", "killeroo_lights", "killeroo_lights_power", "killeroo_lights_spatial"])
 def test_every_sample_and_every_ray_is_the_references(built_lib, case):
     _check_case(built_lib, case, "halton")
 

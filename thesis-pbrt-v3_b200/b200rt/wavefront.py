@@ -60,7 +60,8 @@ class RenderDesc(C.Structure):
                 ("sampler", C.c_uint32), ("camera_exact", C.c_uint32), ("raster_to_camera", C.c_float * 16),
                 ("camera_to_world", C.c_float * 16), ("sobol_matrices32", C.c_void_p), ("sobol_vdc", C.c_void_p),
                 ("sobol_vdc_inv", C.c_void_p), ("sobol_vdc_rows", C.c_uint32), ("material_stride", C.c_uint32),
-                ("textures", C.c_void_p), ("n_textures", C.c_uint32), ("lights", C.c_void_p), ("n_lights", C.c_uint32)]
+                ("textures", C.c_void_p), ("n_textures", C.c_uint32), ("lights", C.c_void_p), ("n_lights", C.c_uint32),
+                ("light_strategy", C.c_uint32)]
 
 
 SAMPLERS = {"hash": 0, "halton": 1, "sobol": 2}
@@ -121,8 +122,8 @@ class WavefrontPathIntegrator:
         lights: a list of make_light() dicts = Scene::lights in the scene's order, REPLACING light_pos / light_I / sphere_light /
         distant_light / infinite_light; one of them is chosen per path vertex as UniformSampleOneLight does (integrator.cpp:86-107)
         from the distribution over their "weight"s: lightsamplestrategy "uniform" (all 1, the default here) or "power" (the
-        caller's weights = Light::Power().y()).  The reference's own default for scenes with several lights, "spatial", is not
-        built and is refused."""
+        caller's weights = Light::Power().y()) — or from the voxel's own distribution under "spatial", the reference's default
+        for scenes with several lights (SpatialLightDistribution)."""
         d = RenderDesc()
         if "lookat" in camera or "w2c" in camera:
             la = None if camera.get("lookat") is None else np.ascontiguousarray(camera["lookat"], np.float32).reshape(9)
@@ -174,8 +175,9 @@ class WavefrontPathIntegrator:
             self._tex_array = tx.texture_array(self._textures)
             d.textures, d.n_textures = C.cast(self._tex_array, C.c_void_p), len(self._textures)
         if lights:
-            if lightsamplestrategy not in ("uniform", "power"):
-                raise ValueError("lightsamplestrategy %r: only \"uniform\" and \"power\" are built" % (lightsamplestrategy,))
+            if lightsamplestrategy not in ("uniform", "power", "spatial"):
+                raise ValueError("lightsamplestrategy %r: \"uniform\", \"power\" or \"spatial\"" % (lightsamplestrategy,))
+            d.light_strategy = 1 if lightsamplestrategy == "spatial" and len(lights) > 1 else 0
             recs = [make_light(dict(l, weight=1.0) if lightsamplestrategy == "uniform" else l) for l in lights]
             self._lights = (Light * len(recs))(*recs)
             d.lights, d.n_lights = C.cast(self._lights, C.c_void_p), len(recs)

@@ -73,6 +73,17 @@ __device__ __forceinline__ void block_append3(bool p0, bool p1, bool p2, uint32_
     s2 = wbase[2][warp] + __popc(m2 & below);
 }
 
+// SpatialLightDistribution: one thread computes one voxel's Distribution1D (wf_shade.cuh spatial_voxel_distribution)
+__global__ void k_light_voxels(const WfLight *__restrict__ lights, uint32_t nLights, const float *__restrict__ wb6, const uint32_t *__restrict__ nVox3,
+                               uint32_t nVoxels, const float *__restrict__ halton5, float *cdfHi, float *pickPdf) {
+    const uint32_t v = blockIdx.x * blockDim.x + threadIdx.x;
+    if (v >= nVoxels) return;
+    float contrib[B200RT_MAX_LIGHTS];
+    const float wb[6] = {wb6[0], wb6[1], wb6[2], wb6[3], wb6[4], wb6[5]};
+    const uint32_t nVox[3] = {nVox3[0], nVox3[1], nVox3[2]};
+    spatial_voxel_distribution(lights, nLights, wb, nVox, v, halton5, contrib, cdfHi + (size_t)v * nLights, pickPdf + (size_t)v * nLights);
+}
+
 // ---- stage kernels ------------------------------------------------------------------------------
 // Camera rays for path slots [batchStart, batchStart + nSlots) (Sampler::GetCameraSample + PerspectiveCamera::
 // GenerateRayDifferential, src/cameras/perspective.cpp:97-143, pinhole; wf_shade.cuh camera_ray).
@@ -323,6 +334,8 @@ struct Workspace {
     uint8_t *primMat = nullptr;
     size_t mats_n = 0, primMat_n = 0;
     WfLight *lights = nullptr;   // B200RT_MAX_LIGHTS records (ABI v10), allocated on the first render with more than one light
+    float *voxTable = nullptr;   // "spatial": cdfHi then pickPdf of every voxel's distribution, + 640 Halton floats + bound + counts
+    size_t voxFloats = 0;
     uint4 *perRay = nullptr;   // heat-map mode only
     uint32_t *heat = nullptr;
     size_t heat_px = 0;
@@ -389,7 +402,7 @@ void free_ws(Workspace *w) {
     for (int i = 0; i < Workspace::kMaxSets - 1; ++i) free_alt(w, i);
     for (int k = 0; k < Workspace::kMaxSets; ++k) { if (w->side[k]) cudaStreamDestroy(w->side[k]); if (w->evJoin[k]) cudaEventDestroy(w->evJoin[k]); }
     if (w->evFork) cudaEventDestroy(w->evFork);
-    cudaFree(w->film); cudaFree(w->heat); cudaFree(w->mats); cudaFree(w->primMat); cudaFree(w->tex); cudaFree(w->texData); cudaFree(w->lights);
+    cudaFree(w->film); cudaFree(w->heat); cudaFree(w->mats); cudaFree(w->primMat); cudaFree(w->tex); cudaFree(w->texData); cudaFree(w->lights); cudaFree(w->voxTable);
     cudaFree(w->splatCount); cudaFree(w->splatPix); cudaFree(w->splatVal);
     cudaFree(w->haltonPerms); cudaFree(w->haltonDims); cudaFree(w->sobol32); cudaFree(w->sobolVdc);
     if (w->hCounts) cudaFreeHost(w->hCounts);
@@ -611,6 +624,30 @@ static int render_impl(b200rt_scene *s, const b200rt_render_desc *d, float *film
         if (!w->lights) WCU(cudaMalloc(&w->lights, B200RT_MAX_LIGHTS * sizeof(WfLight)));
         WCU(cudaMemcpy(w->lights, lights.data(), lights.size() * sizeof(WfLight), cudaMemcpyHostToDevice));
         P.lights = w->lights;
+        if (d->light_strategy == B200RT_LIGHTS_SPATIAL) {
+            // every voxel's distribution, before the frame (the reference computes a voxel's the first time a path lands in it;
+            // the values are the same): nv threads x 128 points x nLights light samples
+            std::memcpy(P.wb, s->bounds, sizeof(P.wb));
+            spatial_voxel_counts(P.wb, 64, P.nVox);
+            const size_t nv = (size_t)P.nVox[0] * P.nVox[1] * P.nVox[2], per = nv * P.nLights;
+            if (per > (48u << 20)) return set_error(B200RT_EUNSUPPORTED, "spatial light distribution: %zu voxels x %u lights is too large a table", nv, P.nLights);
+            const size_t need = 2 * per + 640 + 16;
+            if (w->voxFloats < need) {
+                cudaFree(w->voxTable); w->voxTable = nullptr; w->voxFloats = 0;
+                WCU(cudaMalloc(&w->voxTable, need * sizeof(float)));
+                w->voxFloats = need;
+            }
+            float host[640 + 16];
+            spatial_halton_table(host);
+            std::memcpy(host + 640, P.wb, 24);
+            std::memcpy(host + 640 + 6, P.nVox, 12);
+            float *aux = w->voxTable + 2 * per;
+            WCU(cudaMemcpy(aux, host, sizeof(host), cudaMemcpyHostToDevice));
+            k_light_voxels<<<(unsigned)((nv + 63) / 64), 64, 0, st>>>(w->lights, P.nLights, aux + 640, (const uint32_t *)(aux + 640 + 6), (uint32_t)nv,
+                                                                  aux, w->voxTable, w->voxTable + per);
+            g_launches.fetch_add(1);
+            P.voxCdf = w->voxTable; P.voxPdf = w->voxTable + per;
+        } else if (d->light_strategy != B200RT_LIGHTS_WEIGHTS) return set_error(B200RT_EINVAL, "unknown light_strategy %u", d->light_strategy);
     }
     P.tex = nullptr; P.nTex = 0;
     if (d->materials && d->textures && d->n_textures) {

@@ -233,4 +233,12 @@ int lights_of(const b200rt_render_desc *d, uint32_t n_prims, std::vector<WfLight
     return B200RT_OK;
 }
 
+void spatial_halton_table(float *out) {
+    static const uint32_t bases[5] = {2, 3, 5, 7, 11};
+    for (uint32_t i = 0; i < 128; ++i) {
+        out[5 * i] = (float)((double)reverse_bits64(i) * 0x1p-64);   // RadicalInverse(0, a) (lowdiscrepancy.cpp:430-435)
+        for (int b = 1; b < 5; ++b) out[5 * i + b] = radical_inverse(bases[b], i);
+    }
+}
+
 }  // namespace b200rt

@@ -14,4 +14,7 @@ bool material_lobes(const float *rec, uint32_t stride, uint32_t index, float *ou
 // Light block of WfParams from the description; returns an error code for unsupported / inconsistent lights.
 int light_of(const b200rt_render_desc *d, uint32_t n_prims, WfLight *Lt);
 int lights_of(const b200rt_render_desc *d, uint32_t n_prims, std::vector<WfLight> &out);   // Scene::lights + the light distribution (ABI v10)
+// RadicalInverse(0..4, i), i < 128: the 3-D Halton points and 2-D light samples of SpatialLightDistribution::ComputeDistribution
+// (lightdistrib.cpp:248-257); 5 floats per i.
+void spatial_halton_table(float *out640);
 }  // namespace b200rt

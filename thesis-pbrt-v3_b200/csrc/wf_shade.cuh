@@ -37,6 +37,12 @@ struct WfParams {
     WfLight light;            // lights[0]: the scene's only light unless nLights > 1
     const WfLight *lights;    // nLights records (ABI v10) when nLights > 1, else unused
     uint32_t nLights;
+    // "lightsamplestrategy" "spatial" (SpatialLightDistribution, lightdistrib.cpp:95-300): one Distribution1D per voxel of the scene's
+    // bound, all of them computed before the frame (k_light_voxels); voxCdf / voxPdf hold cdfHi / pickPdf of light k of voxel v at
+    // [v * nLights + k], v = (ix * nVox[1] + iy) * nVox[2] + iz.  nullptr = the lights' own cdfHi / pickPdf (uniform, power)
+    const float *voxCdf, *voxPdf;
+    uint32_t nVox[3];
+    float wb[6];              // Scene::WorldBound(): pMin, pMax
     uint32_t anyMis;          // some light has area (sphere / infinite): EstimateDirect traces BSDF-sampled rays, emitters are visible
     float kd[3];
     uint32_t max_depth;
@@ -324,6 +330,71 @@ WF_HD float light_pdf(const WfLight &Lt, const WfIsect &it, V3 wi) {
     return 1.f / (2.f * kPiF * kPiF * sinTheta);
 }
 
+// ---- SpatialLightDistribution (lightdistrib.cpp:95-300) ------------------------------------------------------------------
+// nVoxels (:101-110): the widest side of the scene's bound gets maxVoxels voxels, the others in proportion.
+WF_HD void spatial_voxel_counts(const float *wb, int maxVoxels, uint32_t *nVox) {
+    const float d[3] = {wb[3] - wb[0], wb[4] - wb[1], wb[5] - wb[2]};
+    const int widest = (d[0] > d[1] && d[0] > d[2]) ? 0 : (d[1] > d[2] ? 1 : 2);   // Bounds3::MaximumExtent
+    const float bmax = d[widest];
+    for (int i = 0; i < 3; ++i) {
+        const int v = (int)roundf(d[i] / bmax * (float)maxVoxels);
+        nVox[i] = (uint32_t)(v > 1 ? v : 1);
+    }
+}
+// Lookup's voxel of a point (:133-142): Bounds3::Offset, then Clamp(int(offset * nVoxels), 0, nVoxels - 1)
+WF_HD uint32_t spatial_voxel_of(const float *wb, const uint32_t *nVox, V3 p) {
+    float o[3] = {p.x - wb[0], p.y - wb[1], p.z - wb[2]};
+    uint32_t pi[3];
+    for (int i = 0; i < 3; ++i) {
+        if (wb[3 + i] > wb[i]) o[i] /= wb[3 + i] - wb[i];
+        const int v = (int)(o[i] * (float)(int)nVox[i]);
+        pi[i] = (uint32_t)(v < 0 ? 0 : (v > (int)nVox[i] - 1 ? (int)nVox[i] - 1 : v));
+    }
+    return (pi[0] * nVox[1] + pi[1]) * nVox[2] + pi[2];
+}
+WF_HD float lerp_ref(float t, float v1, float v2) { return (1 - t) * v1 + t * v2; }   // pbrt::Lerp (pbrt.h:417)
+// ComputeDistribution (:229-300) of voxel v: 128 points of the 3-D Halton sequence inside the voxel, every light sampled from
+// each with the next two Halton dimensions, Li.y() / pdf accumulated per light, floored at a thousandth of the average, and the
+// Distribution1D over that.  halton5: RadicalInverse(0..4, i) for i < 128 (5 floats per i).  contrib: nLights floats of scratch.
+WF_HD void spatial_voxel_distribution(const WfLight *lights, uint32_t nLights, const float *wb, const uint32_t *nVox, uint32_t v,
+                                      const float *halton5, float *contrib, float *cdfHi, float *pickPdf) {
+    const uint32_t iz = v % nVox[2], iy = (v / nVox[2]) % nVox[1], ix = v / (nVox[2] * nVox[1]);
+    const uint32_t pi[3] = {ix, iy, iz};
+    float lo[3], hi[3];
+    for (int i = 0; i < 3; ++i) {
+        const float t0 = (float)(int)pi[i] / (float)(int)nVox[i], t1 = (float)(int)(pi[i] + 1) / (float)(int)nVox[i];
+        const float a = lerp_ref(t0, wb[i], wb[3 + i]), b = lerp_ref(t1, wb[i], wb[3 + i]);
+        lo[i] = a < b ? a : b; hi[i] = a < b ? b : a;   // Bounds3(p1, p2): per-component min / max
+    }
+    for (uint32_t j = 0; j < nLights; ++j) contrib[j] = 0.f;
+    WfIsect it;
+    it.n = v3(0.f, 0.f, 0.f); it.pError = v3(0.f, 0.f, 0.f);
+    for (int i = 0; i < 128; ++i) {
+        const float *h = halton5 + 5 * i;
+        it.p = v3(lerp_ref(h[0], lo[0], hi[0]), lerp_ref(h[1], lo[1], hi[1]), lerp_ref(h[2], lo[2], hi[2]));
+        for (uint32_t j = 0; j < nLights; ++j) {
+            V3 wi, so, sd;
+            float pdf = 0.f;
+            const V3 Li = light_sample<true>(lights[j], it, h[3], h[4], wi, pdf, so, sd);
+            if (pdf > 0) contrib[j] += (0.212671f * Li.x + 0.715160f * Li.y + 0.072169f * Li.z) / pdf;   // RGBSpectrum::y()
+        }
+    }
+    float sum = 0.f;
+    for (uint32_t j = 0; j < nLights; ++j) sum += contrib[j];
+    const float avg = sum / (float)(128 * (int)nLights);
+    const float minContrib = (avg > 0) ? (float)(.001 * (double)avg) : 1.f;
+    for (uint32_t j = 0; j < nLights; ++j) contrib[j] = contrib[j] > minContrib ? contrib[j] : minContrib;   // std::max(a, b): a < b ? b : a
+    // Distribution1D (sampling.h:57-69)
+    const int n = (int)nLights;
+    float c = 0.f;
+    for (int j = 0; j < n; ++j) { c = c + contrib[j] / n; cdfHi[j] = c; }
+    const float funcInt = c;
+    for (int j = 0; j < n; ++j) {
+        cdfHi[j] = (funcInt == 0) ? (float)(j + 1) / (float)n : cdfHi[j] / funcInt;
+        pickPdf[j] = (funcInt > 0) ? contrib[j] / (funcInt * n) : 0.f;
+    }
+}
+
 // The lobes of a textured material at this hit (out of line: it is rare and register-hungry).
 // ComputeScatteringFunctions -> ComputeDifferentials(ray): only the camera ray has differentials.
 WF_HD_NOINLINE void textured_material(const WfParams &P, const float *m, uint32_t depth, uint32_t x, uint32_t y, uint32_t s, V3 rayO, V3 rayD,
@@ -409,9 +480,15 @@ WF_HD void shade_vertex(const WfParams &P, uint32_t depth, uint32_t x, uint32_t 
         const float uPick = get1d(P, ps);
         if (multi) {
             uint32_t k = 0;
-            while (k + 1 < P.nLights && P.lights[k].cdfHi <= uPick) ++k;
+            if (P.voxCdf) {   // lightDistribution->Lookup(isect.p) (path.cpp:125): this point's voxel
+                const size_t v = (size_t)spatial_voxel_of(P.wb, P.nVox, it.p) * P.nLights;
+                while (k + 1 < P.nLights && P.voxCdf[v + k] <= uPick) ++k;
+                pickPdf = P.voxPdf[v + k];
+            } else {
+                while (k + 1 < P.nLights && P.lights[k].cdfHi <= uPick) ++k;
+                pickPdf = P.lights[k].pickPdf;
+            }
             Lp = P.lights + k;
-            pickPdf = Lp->pickPdf;
             direct = pickPdf != 0.f;
         }
     }

@@ -270,13 +270,14 @@ void B200WavefrontIntegrator::Render(const Scene &scene) {
     }
     if (lights.size() > 1) {
         // CreateLightSampleDistribution (lightdistrib.cpp:48-66): "uniform" and "power" are one Distribution1D for the whole
-        // scene; "spatial" (the default) builds one per voxel lazily from 128 point samples and is not restated on the device
+        // scene; "spatial" (the default, and what an unknown name falls back to) is one per voxel of the scene's bound, which the
+        // device computes for every voxel before the frame (include/b200rt_wavefront.h light_strategy)
         if (lightSampleStrategy == "power") {
             for (size_t k = 0; k < lights.size(); ++k) lights[k].weight = scene.lights[k]->Power().y();   // ComputeLightPowerDistribution
         } else if (lightSampleStrategy != "uniform") {
-            Error("b200wavefront: %d lights need \"string lightsamplestrategy\" \"uniform\" or \"power\" (\"%s\" is not built); nothing rendered",
-                  (int)lights.size(), lightSampleStrategy.c_str());
-            return;
+            if (lightSampleStrategy != "spatial")
+                Error("Light sample distribution type \"%s\" unknown. Using \"spatial\".", lightSampleStrategy.c_str());   // lightdistrib.cpp:59-64
+            d.light_strategy = B200RT_LIGHTS_SPATIAL;
         }
         d.lights = lights.data();
         d.n_lights = (uint32_t)lights.size();

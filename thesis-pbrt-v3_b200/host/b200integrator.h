@@ -44,13 +44,13 @@ class B200WavefrontIntegrator : public Integrator {
     const int rank, world, seed;
     const bool generalStats;
     const std::string rendezvous;
-    const std::string lightSampleStrategy;   // with several lights: "uniform" | "power" ("spatial" is refused)
+    const std::string lightSampleStrategy;   // with several lights: "spatial" (default) | "uniform" | "power"
     b200rt_render_stats lastStats{};
 };
 
 // Parameters: "integer maxdepth" (path.cpp:209, default 5), "integer rank" / "integer world" (explicit only, default 0 / 1;
 // world > 1 requires "string rendezvous", a directory all ranks of the node can write), "integer seed" (hash sampler only),
-// "string lightsamplestrategy" (path.cpp:218-219; only read when the scene has several lights: "uniform" or "power"),
+// "string lightsamplestrategy" (path.cpp:218-219, default "spatial"; it only matters when the scene has several lights),
 // "bool generalstats" (default false:
 // true renders through the instrumented kernels, b200rt_render_heatmaps, fills the Film's per-pixel GeneralStats and
 // writes the thesis's statistic matrices with Film::WriteGeneralStats like SamplerIntegrator::Render does,
