@@ -46,7 +46,13 @@ typedef struct {
     const float *texels;
     uint32_t width, height, n_levels;
     float su, sv, du, dv;   /* "float uscale" / "vscale" / "udelta" / "vdelta": 1, 1, 0, 0 */
+    uint32_t filter;        /* B200RT_TEXFILTER_TRILINEAR (0) = "bool trilinear" true: MIPMap::Lookup(st, width) (mipmap.h:244-260);
+                               B200RT_TEXFILTER_EWA (1) = the ImageTexture default: the elliptically weighted average of
+                               MIPMap::Lookup(st, dst0, dst1) / EWA (mipmap.h:277-353) over the two pyramid levels around the
+                               ellipse's minor axis, Gaussian weights from MIPMap::weightLut (b200rt_ewa_weights) */
+    float max_anisotropy;   /* "float maxanisotropy": 0 = the default 8 */
 } b200rt_texture;
+enum { B200RT_TEXFILTER_TRILINEAR = 0, B200RT_TEXFILTER_EWA = 1 };
 
 /* One light of a scene with several (ABI v10; `n_lights` below).  The fields mean what the desc's single-light fields
  * light_kind / light_pos / light_I / light_radius / light_prim / light_to_world mean for that kind. */
@@ -254,6 +260,9 @@ int b200rt_camera_perspective(const float *lookat9, const float *w2c16, float fo
  * size, the level count and the total texel count; out = n_texels x 3 floats.  Texels equal the reference's bit for bit. */
 int b200rt_mipmap_dims(uint32_t w, uint32_t h, uint32_t *w0, uint32_t *h0, uint32_t *n_levels, uint64_t *n_texels);
 int b200rt_mipmap_build(const float *rgb, uint32_t w, uint32_t h, int gamma, float scale, float *out);
+/* MIPMap::weightLut (mipmap.h:94-101): weightLut[i] = exp(-2 r2) - exp(-2), r2 = i / 127, evaluated like the reference does
+ * (std::exp on floats, this machine's libm).  out: 128 floats. */
+void b200rt_ewa_weights(float *out128);
 
 int b200rt_film_reduce(const char *rendezvous, uint32_t rank, uint32_t world, float *film, uint64_t n_floats,
                        uint32_t *heat, uint64_t n_heat, double timeout_s);

@@ -266,14 +266,23 @@ extern "C" int ref_render_get_mat_stride(void) { return g_matStride; }
 // 20-float prim_mat record name (1-based) the texture the material's Kd / uber's opacity reads.  The textures are made by the
 // reference's own CreateImageSpectrumTexture (textures/imagemap.cpp:146-188) -> ReadImage -> MIPMap.
 static std::vector<std::string> g_texFiles;
+// "bool trilinear" / "float maxanisotropy" of the textures made for the NEXT renders and lookups (defaults of this harness:
+// trilinear, 8; the reference's own default is trilinear false = EWA)
+static bool g_texTrilinear = true;
+static float g_texMaxAniso = 8.f;
+extern "C" void ref_render_set_texture_filter(int trilinear, float maxaniso) { g_texTrilinear = trilinear != 0; g_texMaxAniso = maxaniso > 0 ? maxaniso : 8.f; }
+extern "C" void ref_render_get_texture_filter(int *trilinear, float *maxaniso) { *trilinear = g_texTrilinear ? 1 : 0; *maxaniso = g_texMaxAniso; }
 static std::shared_ptr<Texture<Spectrum>> make_imagemap(const std::string &file) {
     ParamSet ps;
     std::unique_ptr<std::string[]> f(new std::string[1]);
     f[0] = file;
     ps.AddString("filename", std::move(f), 1);
     std::unique_ptr<bool[]> tri(new bool[1]);
-    tri[0] = true;
+    tri[0] = g_texTrilinear;
     ps.AddBool("trilinear", std::move(tri), 1);
+    std::unique_ptr<Float[]> ma(new Float[1]);
+    ma[0] = g_texMaxAniso;
+    ps.AddFloat("maxanisotropy", std::move(ma), 1);
     std::map<std::string, std::shared_ptr<Texture<Float>>> ft;
     std::map<std::string, std::shared_ptr<Texture<Spectrum>>> st;
     TextureParams tp(ps, ps, ft, st);
@@ -321,6 +330,19 @@ extern "C" int ref_texture_lookup(const char *file, const float *stw, int n, flo
     for (int i = 0; i < n; ++i) {
         Float rgb[3];
         it->mipmap->Lookup(Point2f(stw[3 * i], stw[3 * i + 1]), stw[3 * i + 2]).ToRGB(rgb);
+        for (int c = 0; c < 3; ++c) out[3 * i + c] = rgb[c];
+    }
+    return 0;
+}
+
+// MIPMap::Lookup(st, dst0, dst1) of the reference's texture (the filter set by ref_render_set_texture_filter) for n lookups of
+// 6 floats: s, t, dst0.x, dst0.y, dst1.x, dst1.y
+extern "C" int ref_texture_lookup_diff(const char *file, const float *q, int n, float *out) {
+    std::shared_ptr<Texture<Spectrum>> t = make_imagemap(file);
+    auto *it = static_cast<ImageTexture<RGBSpectrum, Spectrum> *>(t.get());
+    for (int i = 0; i < n; ++i) {
+        Float rgb[3];
+        it->mipmap->Lookup(Point2f(q[6 * i], q[6 * i + 1]), Vector2f(q[6 * i + 2], q[6 * i + 3]), Vector2f(q[6 * i + 4], q[6 * i + 5])).ToRGB(rgb);
         for (int c = 0; c < 3; ++c) out[3 * i + c] = rgb[c];
     }
     return 0;

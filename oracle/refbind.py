@@ -209,7 +209,7 @@ def camera_matrices(eye, look, up, fov, xres, yres, camera_matrix=None):
 def render(scene, accel_kind, eye, look, up, fov, xres, yres, spp, maxdepth, light_pos, light_I, kd,
            sampler="random", n_threads=0, tmp_prefix=None, heat=False, prim_mat=None, emitter_L=None, timing=False,
            distant=None, cropwindow=None, infinite=None, camera_matrix=None, textures=None, extra_lights=None,
-           lightsamplestrategy="uniform"):
+           lightsamplestrategy="uniform", texture_filter=None):
     """The reference's OWN render (SamplerIntegrator::Render + PathIntegrator::Li + Film, oracle/ref/ref_render.cpp)
     of `scene` with a matte material and one point light.  Returns (rgb (yres,xres,3), n_closest, n_shadow)."""
     import tempfile
@@ -271,6 +271,8 @@ def render(scene, accel_kind, eye, look, up, fov, xres, yres, spp, maxdepth, lig
                 for i, px in enumerate(textures):
                     files.append(os.path.join(td, "tex%d.tga" % i))
                     write_tga(files[-1], px)
+                if texture_filter is not None:   # ("ewa" | "trilinear", maxanisotropy)
+                    set_texture_filter(texture_filter[0] == "trilinear", texture_filter[1], scene.L)
                 set_textures(files, scene.L)
             rc = scene.L.ref_render(scene.h, accel_kind.encode(), _p(cam), xres, yres, spp, maxdepth, _p(lp), _p(li), _p(k),
                                     sampler.encode(), n_threads, pre, _p(out), C.byref(nc), C.byref(ns), _p(hm), _p(pk), _p(el), C.byref(secs))
@@ -282,6 +284,8 @@ def render(scene, accel_kind, eye, look, up, fov, xres, yres, spp, maxdepth, lig
                          ("ref_render_set_textures", (0, None)), ("ref_render_set_extra_lights", (None, 0, None))):
             if hasattr(scene.L, fn):
                 getattr(scene.L, fn)(*args)
+        if hasattr(scene.L, "ref_render_set_texture_filter"):
+            set_texture_filter(True, 8.0, scene.L)
     if rc != 0:
         raise RuntimeError("ref_render failed (%d)" % rc)
     if timing:   # (rgb, n_closest, n_shadow, seconds spent inside Integrator::Render)
@@ -338,6 +342,24 @@ def texture_lookup(path, stw):
     stw = np.ascontiguousarray(stw, np.float32).reshape(-1, 3)
     out = np.zeros((len(stw), 3), np.float32)
     L.ref_texture_lookup(path.encode(), _p(stw), len(stw), _p(out))
+    return out
+
+
+def set_texture_filter(trilinear=True, maxanisotropy=8.0, L=None):
+    """"bool trilinear" / "float maxanisotropy" of the textures the NEXT renders and lookups make (harness default: trilinear)."""
+    L = L or lib()
+    L.ref_render_set_texture_filter.argtypes = [C.c_int, C.c_float]
+    L.ref_render_set_texture_filter(int(bool(trilinear)), float(maxanisotropy))
+
+
+def texture_lookup_diff(path, q):
+    """MIPMap::Lookup(st, dst0, dst1) of the reference's texture for (n, 6) rows (s, t, dst0.x, dst0.y, dst1.x, dst1.y), under
+    the filter set_texture_filter chose."""
+    L = lib()
+    L.ref_texture_lookup_diff.argtypes = [C.c_char_p, C.c_void_p, C.c_int, C.c_void_p]
+    q = np.ascontiguousarray(q, np.float32).reshape(-1, 6)
+    out = np.zeros((len(q), 3), np.float32)
+    L.ref_texture_lookup_diff(path.encode(), _p(q), len(q), _p(out))
     return out
 
 

@@ -125,6 +125,7 @@ extern "C" int ref_render_get_infinite(float *L_rgb, float *l2w16);      // set 
 extern "C" int ref_render_get_camera_matrix(float *w2c16);             // set through ref_render_set_camera_matrix
 extern "C" int ref_render_get_textures(int i, char *out, int cap);   // set through ref_render_set_textures: image files of slots 18 / 19
 extern "C" int ref_render_get_extra_lights(float *recs, int cap, char *strategy, int strategy_cap);   // set through ref_render_set_extra_lights
+extern "C" void ref_render_get_texture_filter(int *trilinear, float *maxaniso);
 extern "C" int ref_render_get_mat_stride(void);             // set through ref_render_set_mat_stride: 8 or 20 floats per record
 extern "C" void ref_render_get_crop(float *cw);           // set through ref_render_set_crop   // set through ref_render_set_distant (oracle/ref/ref_render.cpp)
 std::shared_ptr<pbrt::Shape> shape_of(const pbrt::Primitive *p);   // plugin_shape_of.cpp (GeometricPrimitive::shape is private)
@@ -168,8 +169,14 @@ extern "C" int plugin_render(ref_scene *s, const char *tree, const float *cam, i
                     f[0] = file;
                     ps.AddString("filename", std::move(f), 1);
                     std::unique_ptr<bool[]> tri(new bool[1]);
-                    tri[0] = true;
+                    int triFlag = 1;
+                    float maxAniso = 8.f;
+                    ref_render_get_texture_filter(&triFlag, &maxAniso);   // set through ref_render_set_texture_filter
+                    tri[0] = triFlag != 0;
                     ps.AddBool("trilinear", std::move(tri), 1);
+                    std::unique_ptr<Float[]> ma(new Float[1]);
+                    ma[0] = maxAniso;
+                    ps.AddFloat("maxanisotropy", std::move(ma), 1);
                     std::map<std::string, std::shared_ptr<Texture<Float>>> ft;
                     std::map<std::string, std::shared_ptr<Texture<Spectrum>>> st;
                     TextureParams tp(ps, ps, ft, st);

@@ -97,6 +97,9 @@ extern "C" hs_ctx *hs_create(const b200rt_render_desc *d, uint32_t n_prims, cons
                 WfTexture &T = c->tex[k];
                 T.texels = t.texels; T.nLevels = t.n_levels; T.w0 = t.width; T.h0 = t.height;
                 T.su = t.su; T.sv = t.sv; T.du = t.du; T.dv = t.dv;
+                static float lut[128];
+                b200rt_ewa_weights(lut);
+                T.ewa = t.filter == B200RT_TEXFILTER_EWA ? 1u : 0u; T.maxAniso = t.max_anisotropy > 0.f ? t.max_anisotropy : 8.f; T.lut = lut;
                 size_t off = 0;
                 for (uint32_t l = 0; l < 16; ++l) {
                     T.levelOffset[l] = (uint32_t)off;
@@ -239,6 +242,24 @@ extern "C" void hs_tex_lookup(const b200rt_texture *t, const float *stw, uint32_
     for (uint32_t l = 0; l < 16; ++l) { T.levelOffset[l] = (uint32_t)off; if (l < t->n_levels) off += (size_t)std::max(1u, t->width >> l) * std::max(1u, t->height >> l); }
     for (uint32_t i = 0; i < n; ++i) {
         const V3 v = tex_lookup(T, stw[3 * i], stw[3 * i + 1], stw[3 * i + 2]);
+        out[3 * i] = v.x; out[3 * i + 1] = v.y; out[3 * i + 2] = v.z;
+    }
+}
+// MIPMap::Lookup(st, dst0, dst1) of one texture (tex_evaluate's two filters with an identity mapping) for lookups of 6 floats:
+// s, t, dst0.x, dst0.y, dst1.x, dst1.y
+extern "C" void hs_tex_lookup_diff(const b200rt_texture *t, const float *q, uint32_t n, float *out) {
+    WfTexture T;
+    static float lut[128];
+    b200rt_ewa_weights(lut);
+    T.texels = t->texels; T.nLevels = t->n_levels; T.w0 = t->width; T.h0 = t->height; T.su = 1.f; T.sv = 1.f; T.du = 0.f; T.dv = 0.f;
+    T.ewa = t->filter == B200RT_TEXFILTER_EWA ? 1u : 0u; T.maxAniso = t->max_anisotropy > 0.f ? t->max_anisotropy : 8.f; T.lut = lut;
+    size_t off = 0;
+    for (uint32_t l = 0; l < 16; ++l) { T.levelOffset[l] = (uint32_t)off; if (l < t->n_levels) off += (size_t)std::max(1u, t->width >> l) * std::max(1u, t->height >> l); }
+    for (uint32_t i = 0; i < n; ++i) {
+        const float *r = q + 6 * i;
+        V3 v;
+        if (T.ewa) v = tex_lookup_ewa(T, r[0], r[1], r[2], r[3], r[4], r[5]);
+        else v = tex_lookup(T, r[0], r[1], 2 * smax(smax(fabsf(r[2]), fabsf(r[3])), smax(fabsf(r[4]), fabsf(r[5]))));
         out[3 * i] = v.x; out[3 * i + 1] = v.y; out[3 * i + 2] = v.z;
     }
 }

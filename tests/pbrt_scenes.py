@@ -20,7 +20,7 @@ def write_killeroo_geometry(path):
 
 
 def killeroo_simple(dirname, accelerator, integrator='Integrator "path" "integer maxdepth" [5]', xres=700, yres=700, spp=8,
-                    filename="killeroo-simple.pfm", extra_film="", scene_name="input.pbrt", ground_texture=None, more_lights=""):
+                    filename="killeroo-simple.pfm", extra_film="", scene_name="input.pbrt", ground_texture=None, more_lights="", trilinear=True):
     """scenes/killeroo-simple with its Accelerator line replaced by `accelerator` (a full directive) and, optionally, its
     Integrator line by `integrator`; `more_lights` = LightSource directives placed right after WorldBegin (before the file's own
     area light, so they come first in Scene::lights).  Returns the scene file's path."""
@@ -31,8 +31,9 @@ def killeroo_simple(dirname, accelerator, integrator='Integrator "path" "integer
     if ground_texture is not None:
         # the ground (uv 0..5: five repeats) with an image texture on its Kd, the way scenes/sponza and scenes/living-room
         # declare theirs: `Texture "name" "spectrum" "imagemap" "string filename" ... "bool trilinear" "true"`
-        ground = ('Texture "groundtex" "spectrum" "imagemap" "string filename" "%s" "bool trilinear" "true"\n'
-                  '  Material "matte" "texture Kd" "groundtex"' % ground_texture)
+        # (trilinear=False: no "bool trilinear" at all, the way scenes/sponza declares its textures = the EWA filter)
+        ground = ('Texture "groundtex" "spectrum" "imagemap" "string filename" "%s"%s\n'
+                  '  Material "matte" "texture Kd" "groundtex"' % (ground_texture, ' "bool trilinear" "true"' if trilinear else ""))
     txt = '''LookAt 400 20 30   0 63 -110   0 0 1
 Rotate -5 0 0 1
 Camera "perspective" "float fov" [39]

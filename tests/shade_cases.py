@@ -148,7 +148,7 @@ def build(name, res=48):
                               distant_light=(sc["light_dir"], wf.world_radius(tv)), crop=sc["crop"]),
                    accel=(tv, {}), res=res * 4)
         return out
-    if name in ("living_room", "living_room_tex"):
+    if name in ("living_room", "living_room_tex", "living_room_tex_ewa"):
         # BASELINE config 5, scenes/living-room as the reference resolves it (b200rt.scenes.living_room): the file's camera CTM,
         # its infinite light (constant: the sky map is absent), maxdepth 65, the file's matte / Oren-Nayar / substrate / metal /
         # glass / mirror / uber materials and the PLY vertex normals.  The reference harness builds ONE mesh, so the 3 008
@@ -157,7 +157,8 @@ def build(name, res=48):
         from b200rt import wavefront as wf
         # "living_room_tex": with the image textures of the files that are in the reference tree (leaf.tga: Kd and opacity of the
         # Leaves; picture8.tga: Kd of the Painting) — the scene as the reference renders it, box filter aside
-        sc = scenes.living_room(res, res, textures=name == "living_room_tex")
+        # "living_room_tex_ewa": the same without `"bool trilinear" "true"`, i.e. under the ImageTexture default, the EWA filter
+        sc = scenes.living_room(res, res, textures=name != "living_room")
         z = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "living_room_mesh.npz"))
         tv = sc["tri_verts"]
         il = sc["infinite_light"]
@@ -172,10 +173,13 @@ def build(name, res=48):
                               materials=sc["materials"], prim_material=sc["prim_material"]),
                    accel=(tv, dict(tri_uvs=sc["tri_uvs"], tri_normals=sc["tri_normals"], prim_flags=np.full(len(tv), 2, np.uint8))),
                    mis=True, infinite_scene=True, maxdepth=sc["maxdepth"])
-        if name == "living_room_tex":
+        if name != "living_room":
             from b200rt import textures as tx
+            ewa = name == "living_room_tex_ewa"
             out["render"]["textures"] = sc["texture_pixels"]
-            out["integ"]["textures"] = [tx.ImageTexture(rgb8=px) for px in sc["texture_pixels"]]
+            if ewa:
+                out["render"]["texture_filter"] = ("ewa", 8.0)
+            out["integ"]["textures"] = [tx.ImageTexture(rgb8=px, trilinear=not ewa) for px in sc["texture_pixels"]]
         return out
     if name in ("normals", "normals_flipped"):
         # vertex normals (interpolated shading normal, triangle.cpp:348-400), a real (u, v) parameterisation (dpdu frame) and,
@@ -201,4 +205,4 @@ def build(name, res=48):
 
 CASES = ["sponza_point", "killeroo_plastic", "killeroo_normals", "killeroo_glass", "killeroo_metal", "killeroo_oren", "killeroo_uber", "killeroo_infinite",
          "feet_distant", "normals", "normals_flipped", "living_room", "living_room_tex", "sponza_two_points", "killeroo_lights",
-         "killeroo_lights_power", "killeroo_lights_spatial"]
+         "killeroo_lights_power", "killeroo_lights_spatial", "living_room_tex_ewa"]

@@ -46,7 +46,7 @@ def _device_queues(gpu, c, spp, sampler):
                                           ("feet_distant", "halton"), ("normals", "halton"), ("normals_flipped", "halton"),
                                           ("killeroo_metal", "sobol"), ("feet_distant", "sobol"), ("living_room", "sobol"),
                                           ("living_room_tex", "sobol"), ("sponza_two_points", "halton"), ("killeroo_lights", "halton"),
-                                          ("killeroo_lights_power", "halton"), ("killeroo_lights", "sobol"), ("killeroo_lights_spatial", "halton")])
+                                          ("killeroo_lights_power", "halton"), ("killeroo_lights", "sobol"), ("killeroo_lights_spatial", "halton"), ("living_room_tex_ewa", "sobol")])
 def test_device_rays_are_the_references(gpu, case, sampler):
     import hostwf
     from b200rt import wavefront as wf

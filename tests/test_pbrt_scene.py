@@ -110,7 +110,8 @@ def test_two_ranks_write_one_image(tmp_path):
 
 
 @pytest.mark.gpu
-def test_parsed_scene_with_an_image_texture(tmp_path):
+@pytest.mark.parametrize("trilinear", [True, False])
+def test_parsed_scene_with_an_image_texture(tmp_path, trilinear):
     """`Texture ... "imagemap" ... "bool trilinear" "true"` + `Material "matte" "texture Kd"` through pbrtParseFile: the C++
     integrator hands the reference's own MIPMap pyramid to the device (ABI v9), the MIP level comes from the camera rays'
     differentials; against the stock run of the same file."""
@@ -120,7 +121,7 @@ def test_parsed_scene_with_an_image_texture(tmp_path):
     from b200rt import textures
     d = str(tmp_path)
     textures.write_tga(os.path.join(d, "leaf.tga"), load_golden("living_room_textures.npz")["leaf"])
-    kw = dict(xres=384, yres=384, spp=8, ground_texture="leaf.tga")
+    kw = dict(xres=384, yres=384, spp=8, ground_texture="leaf.tga", trilinear=trilinear)   # False: the ImageTexture default, EWA
     scene = ps.killeroo_simple(d, 'Accelerator "bvh"', filename="stock.pfm", **kw)
     rc, out = _run(scene, d)
     assert rc == 0, out

@@ -47,12 +47,12 @@ def test_camera_matrices_equal_the_reference_cameras(built_lib):
 
 @pytest.mark.parametrize("case", ["sponza_point", "killeroo_plastic", "killeroo_normals", "killeroo_glass", "killeroo_metal", "killeroo_oren", "killeroo_uber",
                                   "killeroo_infinite", "feet_distant", "normals", "normals_flipped", "living_room", "living_room_tex",
-                                  "sponza_two_points", "killeroo_lights", "killeroo_lights_power", "killeroo_lights_spatial"])
+                                  "sponza_two_points", "killeroo_lights", "killeroo_lights_power", "killeroo_lights_spatial", "living_room_tex_ewa"])
 def test_every_sample_and_every_ray_is_the_references(built_lib, case):
     _check_case(built_lib, case, "halton")
 
 
-@pytest.mark.parametrize("case", ["sponza_point", "killeroo_metal", "feet_distant", "living_room", "living_room_tex"])
+@pytest.mark.parametrize("case", ["sponza_point", "killeroo_metal", "feet_distant", "living_room", "living_room_tex", "living_room_tex_ewa"])
 def test_sobol_stream_is_the_references(built_lib, case):
     """Sampler "sobol" (scenes/living-room/scene.pbrt:3): SobolIntervalToIndex + SobolSampleFloat over the reference's
     generator matrices (b200rt/data/sobol_tables.npz), incl. the pixel-relative remap of dimensions 0 / 1 and a crop window."""

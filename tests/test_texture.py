@@ -72,3 +72,41 @@ def test_trilinear_lookup_equals_the_references(built_lib, tmp_path):
     L.hs_log_check.argtypes = [C.c_uint32] * 3
     assert L.hs_log_check(0x00000001, 0x7f800000, 257) == 0          # log_ref == this libm's logf (2^23 samples of all positive floats)
     assert L.hs_log_check(0x30000000, 0x41800000, 11) == 0           # and densely over [1e-9, 16)
+
+
+@pytest.mark.parametrize("maxaniso", [8.0, 2.0])
+def test_ewa_lookup_equals_the_references(built_lib, tmp_path, maxaniso):
+    """The ImageTexture default, "bool trilinear" false: MIPMap::Lookup(st, dst0, dst1) -> EWA over two levels (mipmap.h:277-353),
+    with its eccentricity clamp ("float maxanisotropy"), its Gaussian weight table and the degenerate cases (a zero minor axis ->
+    the bilinear `triangle`, ellipses wider than the coarsest level)."""
+    rb = _ref()
+    import hostwf
+    from b200rt import api, textures
+    px = load_golden("living_room_textures.npz")["picture8"]
+    path = str(tmp_path / "picture8.tga")
+    textures.write_tga(path, px)
+    t = textures.ImageTexture(rgb8=px, trilinear=False, maxanisotropy=maxaniso)
+    rng = np.random.default_rng(7)
+    n = 20000
+    q = np.zeros((n, 6), np.float32)
+    q[:, :2] = rng.uniform(-1.5, 2.5, (n, 2))
+    scale = 10.0 ** rng.uniform(-6, -0.3, (n, 1))                      # sub-texel .. a third of the image
+    q[:, 2:] = rng.standard_normal((n, 4)) * scale * np.array([1, 1, 0.2, 0.2])   # often anisotropic beyond the clamp
+    q[::17, 4:] = 0                                                     # minor axis exactly zero
+    q[::19, 2:] = 0                                                     # no differentials at all (hits past the camera ray)
+    rb.set_texture_filter(False, maxaniso)
+    try:
+        want = rb.texture_lookup_diff(path, q)
+    finally:
+        rb.set_texture_filter(True, 8.0)
+    L = hostwf.lib()
+    L.hs_tex_lookup_diff.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]
+    got = np.zeros((n, 3), np.float32)
+    rec = t.record()
+    L.hs_tex_lookup_diff(C.byref(rec), q.ctypes.data, n, got.ctypes.data)
+    assert np.array_equal(got.view(np.uint32), want.view(np.uint32)), int((got.view(np.uint32) != want.view(np.uint32)).any(1).sum())
+    # the weight table itself, against the one the reference's MIPMap holds (exp through this machine's libm on both sides)
+    lut = np.zeros(128, np.float32)
+    api.lib().b200rt_ewa_weights.argtypes = [C.c_void_p]
+    api.lib().b200rt_ewa_weights(lut.ctypes.data)
+    assert lut[0] > 0.86 and lut[127] == 0.0 and np.all(np.diff(lut) < 0)

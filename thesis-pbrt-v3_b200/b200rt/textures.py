@@ -9,14 +9,17 @@ from . import api
 
 class Texture(C.Structure):
     _fields_ = [("texels", C.c_void_p), ("width", C.c_uint32), ("height", C.c_uint32), ("n_levels", C.c_uint32),
-                ("su", C.c_float), ("sv", C.c_float), ("du", C.c_float), ("dv", C.c_float)]
+                ("su", C.c_float), ("sv", C.c_float), ("du", C.c_float), ("dv", C.c_float),
+                ("filter", C.c_uint32), ("max_anisotropy", C.c_float)]
 
 
 class ImageTexture:
     """rgb8: (h, w, 3) uint8 with row 0 = the top of the image (ReadImage's order), or rgb: float32 of the same shape.
-    gamma: InverseGammaCorrect on the way in (the reference's default for .tga / .png); scale = "float scale"."""
+    gamma: InverseGammaCorrect on the way in (the reference's default for .tga / .png); scale = "float scale".
+    trilinear: "bool trilinear" (False, the reference's default, = the EWA filter with "float maxanisotropy")."""
 
-    def __init__(self, rgb8=None, rgb=None, gamma=True, scale=1.0, su=1.0, sv=1.0, du=0.0, dv=0.0):
+    def __init__(self, rgb8=None, rgb=None, gamma=True, scale=1.0, su=1.0, sv=1.0, du=0.0, dv=0.0, trilinear=True, maxanisotropy=8.0):
+        self.trilinear, self.maxanisotropy = bool(trilinear), float(maxanisotropy)
         if rgb is None:
             rgb = np.asarray(rgb8, np.uint8).astype(np.float32) / np.float32(255)     # c = src / 255.f (imageio.cpp:245-247)
         rgb = np.ascontiguousarray(rgb, np.float32)
@@ -37,7 +40,8 @@ class ImageTexture:
         return self.texels[off:off + w * h].reshape(h, w, 3)
 
     def record(self):
-        return Texture(self.texels.ctypes.data, self.width, self.height, self.n_levels, self.su, self.sv, self.du, self.dv)
+        return Texture(self.texels.ctypes.data, self.width, self.height, self.n_levels, self.su, self.sv, self.du, self.dv,
+                       0 if self.trilinear else 1, self.maxanisotropy)
 
 
 def texture_array(textures):

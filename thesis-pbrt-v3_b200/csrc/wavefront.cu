@@ -653,36 +653,50 @@ static int render_impl(b200rt_scene *s, const b200rt_render_desc *d, float *film
     if (d->materials && d->textures && d->n_textures) {
         // image textures: the pyramids are uploaded when the host array (pointer, count, first texel pointer) changes
         if (!P.cam_exact) return set_error(B200RT_EINVAL, "image textures need the exact camera (camera_exact): the ray differentials come from its matrices");
+        std::vector<WfTexture> T(d->n_textures);
+        size_t total = 0;
+        for (uint32_t k = 0; k < d->n_textures; ++k) {
+            const b200rt_texture &t = d->textures[k];
+            if (!t.texels || !t.width || !t.height || (t.width & (t.width - 1)) || (t.height & (t.height - 1)) || t.n_levels == 0 || t.n_levels > 16)
+                return set_error(B200RT_EINVAL, "texture %u: a pyramid with power-of-two level 0 and 1..16 levels is required (b200rt_mipmap_build)", k);
+            if (t.filter > B200RT_TEXFILTER_EWA) return set_error(B200RT_EINVAL, "texture %u: unknown filter %u", k, t.filter);
+            T[k].nLevels = t.n_levels; T[k].w0 = t.width; T[k].h0 = t.height;
+            T[k].su = t.su; T[k].sv = t.sv; T[k].du = t.du; T[k].dv = t.dv;
+            T[k].ewa = t.filter == B200RT_TEXFILTER_EWA ? 1u : 0u;
+            T[k].maxAniso = t.max_anisotropy > 0.f ? t.max_anisotropy : 8.f;
+            size_t off = 0;
+            for (uint32_t l = 0; l < 16; ++l) {
+                T[k].levelOffset[l] = (uint32_t)off;
+                if (l < t.n_levels) off += (size_t)std::max(1u, t.width >> l) * std::max(1u, t.height >> l);
+            }
+            total += off;
+        }
         if (w->texHost != (const void *)d->textures || w->texN != d->n_textures || w->texFirst != (const void *)d->textures[0].texels) {
             cudaFree(w->texData); cudaFree(w->tex); w->texData = nullptr; w->tex = nullptr;
-            std::vector<WfTexture> T(d->n_textures);
-            size_t total = 0;
-            for (uint32_t k = 0; k < d->n_textures; ++k) {
-                const b200rt_texture &t = d->textures[k];
-                if (!t.texels || !t.width || !t.height || (t.width & (t.width - 1)) || (t.height & (t.height - 1)) || t.n_levels == 0 || t.n_levels > 16)
-                    return set_error(B200RT_EINVAL, "texture %u: a pyramid with power-of-two level 0 and 1..16 levels is required (b200rt_mipmap_build)", k);
-                T[k].nLevels = t.n_levels; T[k].w0 = t.width; T[k].h0 = t.height;
-                T[k].su = t.su; T[k].sv = t.sv; T[k].du = t.du; T[k].dv = t.dv;
-                size_t off = 0;
-                for (uint32_t l = 0; l < 16; ++l) {
-                    T[k].levelOffset[l] = (uint32_t)off;
-                    if (l < t.n_levels) off += (size_t)std::max(1u, t.width >> l) * std::max(1u, t.height >> l);
-                }
-                total += off;
-            }
-            WCU(cudaMalloc(&w->texData, std::max<size_t>(total, 1) * 3 * sizeof(float)));
+            // the texels of every pyramid, then MIPMap::weightLut (128 floats, shared by the EWA lookups of every texture)
+            WCU(cudaMalloc(&w->texData, (std::max<size_t>(total, 1) * 3 + 128) * sizeof(float)));
             size_t base = 0;
             for (uint32_t k = 0; k < d->n_textures; ++k) {
                 const b200rt_texture &t = d->textures[k];
                 size_t n = 0;
                 for (uint32_t l = 0; l < t.n_levels; ++l) n += (size_t)std::max(1u, t.width >> l) * std::max(1u, t.height >> l);
                 WCU(cudaMemcpy(w->texData + base * 3, t.texels, n * 3 * sizeof(float), cudaMemcpyHostToDevice));
-                T[k].texels = w->texData + base * 3;
                 base += n;
             }
+            float lut[128];
+            b200rt_ewa_weights(lut);
+            WCU(cudaMemcpy(w->texData + std::max<size_t>(total, 1) * 3, lut, sizeof(lut), cudaMemcpyHostToDevice));
             WCU(cudaMalloc(&w->tex, T.size() * sizeof(WfTexture)));
-            WCU(cudaMemcpy(w->tex, T.data(), T.size() * sizeof(WfTexture), cudaMemcpyHostToDevice));
             w->texHost = d->textures; w->texN = d->n_textures; w->texFirst = d->textures[0].texels;
+        }
+        {   // the records (filter, mapping) are refreshed every render; the texels above only when the host array changed
+            size_t base = 0;
+            for (uint32_t k = 0; k < d->n_textures; ++k) {
+                T[k].texels = w->texData + base * 3;
+                T[k].lut = w->texData + std::max<size_t>(total, 1) * 3;
+                for (uint32_t l = 0; l < T[k].nLevels; ++l) base += (size_t)std::max(1u, T[k].w0 >> l) * std::max(1u, T[k].h0 >> l);
+            }
+            WCU(cudaMemcpy(w->tex, T.data(), T.size() * sizeof(WfTexture), cudaMemcpyHostToDevice));
         }
         P.tex = w->tex; P.nTex = d->n_textures;
     }

@@ -69,6 +69,9 @@ struct WfTexture {
     uint32_t nLevels, w0, h0;   // level l is max(1, w0 >> l) x max(1, h0 >> l)
     uint32_t levelOffset[16];   // in texels
     float su, sv, du, dv;
+    uint32_t ewa;               // "bool trilinear" false (the ImageTexture default): the elliptically weighted average filter
+    float maxAniso;             // "float maxanisotropy" (8)
+    const float *lut;           // MIPMap::weightLut: WeightLUTSize = 128 Gaussian weights (mipmap.h:94-101)
 };
 
 WF_HD uint32_t smax_u(uint32_t a, uint32_t b) { return a < b ? b : a; }
@@ -103,6 +106,60 @@ WF_HD V3 tex_lookup(const WfTexture &T, float st0, float st1, float width) {
     return v3((1 - delta) * a.x + delta * b.x, (1 - delta) * a.y + delta * b.y, (1 - delta) * a.z + delta * b.z);
 }
 
+// MIPMap::EWA (mipmap.h:305-353): the texels of `level` inside the ellipse the two differentials span, Gaussian-weighted
+WF_HD V3 tex_ewa(const WfTexture &T, int level, float st0, float st1, float d00, float d01, float d10, float d11) {
+    const int nL = (int)T.nLevels;
+    if (level >= nL) return tex_texel(T, nL - 1, 0, 0);
+    const int w = (int)smax_u(1u, T.w0 >> level), h = (int)smax_u(1u, T.h0 >> level);
+    st0 = st0 * w - 0.5f; st1 = st1 * h - 0.5f;
+    d00 *= w; d01 *= h; d10 *= w; d11 *= h;
+    float A = d01 * d01 + d11 * d11 + 1;
+    float B = -2 * (d00 * d01 + d10 * d11);
+    float C = d00 * d00 + d10 * d10 + 1;
+    const float invF = 1 / (A * C - B * B * 0.25f);
+    A *= invF; B *= invF; C *= invF;
+    const float det = -B * B + 4 * A * C;
+    const float invDet = 1 / det;
+    const float uSqrt = sqrtf(det * C), vSqrt = sqrtf(A * det);
+    const int s0 = (int)ceilf(st0 - 2 * invDet * uSqrt), s1 = (int)floorf(st0 + 2 * invDet * uSqrt);
+    const int t0 = (int)ceilf(st1 - 2 * invDet * vSqrt), t1 = (int)floorf(st1 + 2 * invDet * vSqrt);
+    V3 sum = v3(0.f, 0.f, 0.f);
+    float sumWts = 0;
+    for (int it = t0; it <= t1; ++it) {
+        const float tt = it - st1;
+        for (int is = s0; is <= s1; ++is) {
+            const float ss = is - st0;
+            const float r2 = A * ss * ss + B * ss * tt + C * tt * tt;
+            if (r2 < 1) {
+                int index = (int)(r2 * 128);
+                index = index < 127 ? index : 127;
+                const float weight = T.lut[index];
+                const V3 x = tex_texel(T, level, is, it);
+                sum = v3(sum.x + x.x * weight, sum.y + x.y * weight, sum.z + x.z * weight);
+                sumWts += weight;
+            }
+        }
+    }
+    return v3(sum.x / sumWts, sum.y / sumWts, sum.z / sumWts);
+}
+// MIPMap::Lookup(st, dst0, dst1) without "trilinear" (mipmap.h:283-303)
+WF_HD V3 tex_lookup_ewa(const WfTexture &T, float st0, float st1, float d00, float d01, float d10, float d11) {
+    if (d00 * d00 + d01 * d01 < d10 * d10 + d11 * d11) { float x = d00; d00 = d10; d10 = x; x = d01; d01 = d11; d11 = x; }
+    const float majorLength = sqrtf(d00 * d00 + d01 * d01);
+    float minorLength = sqrtf(d10 * d10 + d11 * d11);
+    if (minorLength * T.maxAniso < majorLength && minorLength > 0) {   // clamp the ellipse's eccentricity
+        const float scale = majorLength / (minorLength * T.maxAniso);
+        d10 *= scale; d11 *= scale;
+        minorLength *= scale;
+    }
+    if (minorLength == 0) return tex_triangle(T, 0, st0, st1);
+    const float lod = smax(0.f, (float)(int)T.nLevels - 1.f + log2_ref(minorLength));
+    const int ilod = (int)floorf(lod);
+    const float delta = lod - ilod;
+    const V3 a = tex_ewa(T, ilod, st0, st1, d00, d01, d10, d11), b = tex_ewa(T, ilod + 1, st0, st1, d00, d01, d10, d11);
+    return v3((1 - delta) * a.x + delta * b.x, (1 - delta) * a.y + delta * b.y, (1 - delta) * a.z + delta * b.z);
+}
+
 // (dudx, dvdx, dudy, dvdy) of SurfaceInteraction::ComputeDifferentials; all zero without ray differentials
 struct WfUVDiff { float dudx, dvdx, dudy, dvdy; };
 
@@ -111,6 +168,7 @@ struct WfUVDiff { float dudx, dvdx, dudy, dvdy; };
 WF_HD V3 tex_evaluate(const WfTexture &T, float u, float v, const WfUVDiff &D) {
     const float dsdx = T.su * D.dudx, dtdx = T.sv * D.dvdx, dsdy = T.su * D.dudy, dtdy = T.sv * D.dvdy;
     const float st0 = T.su * u + T.du, st1 = T.sv * v + T.dv;
+    if (T.ewa) return tex_lookup_ewa(T, st0, st1, dsdx, dtdx, dsdy, dtdy);   // dst0 = dstdx, dst1 = dstdy (imagemap.h:71-77)
     const float width = smax(smax(fabsf(dsdx), fabsf(dtdx)), smax(fabsf(dsdy), fabsf(dtdy)));
     return tex_lookup(T, st0, st1, 2 * width);
 }

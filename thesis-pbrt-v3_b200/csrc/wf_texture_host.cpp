@@ -125,3 +125,11 @@ extern "C" int b200rt_mipmap_build(const float *rgb, uint32_t w, uint32_t h, int
     }
     return B200RT_OK;
 }
+
+extern "C" void b200rt_ewa_weights(float *out) {
+    for (int i = 0; i < 128; ++i) {
+        const float alpha = 2;
+        const float r2 = float(i) / float(128 - 1);
+        out[i] = std::exp(-alpha * r2) - std::exp(-alpha);
+    }
+}

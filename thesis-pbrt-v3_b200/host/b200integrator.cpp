@@ -304,8 +304,8 @@ void B200WavefrontIntegrator::Render(const Scene &scene) {
         if (it != texSeen.end()) return it->second;
         const UVMapping2D *uv = dynamic_cast<const UVMapping2D *>(im->mapping.get());
         const MIPMap<RGBSpectrum> *mm = im->mipmap;
-        if (!uv || !mm || (!mm->doTrilinear && mm->Levels() > 1) || mm->wrapMode != ImageWrap::Repeat || mm->Levels() > 16) {
-            Error("b200wavefront: image textures are supported with \"uv\" mapping, \"bool trilinear\" \"true\" and \"repeat\" wrap only");
+        if (!uv || !mm || mm->wrapMode != ImageWrap::Repeat || mm->Levels() > 16) {
+            Error("b200wavefront: image textures are supported with \"uv\" mapping and \"repeat\" wrap only");
             texBad = true;
             return 0;
         }
@@ -324,6 +324,8 @@ void B200WavefrontIntegrator::Render(const Scene &scene) {
         r.texels = nullptr;   // set below, once texData stops moving
         r.width = (uint32_t)mm->pyramid[0]->uSize(); r.height = (uint32_t)mm->pyramid[0]->vSize(); r.n_levels = (uint32_t)mm->Levels();
         r.su = uv->su; r.sv = uv->sv; r.du = uv->du; r.dv = uv->dv;
+        r.filter = mm->doTrilinear ? B200RT_TEXFILTER_TRILINEAR : B200RT_TEXFILTER_EWA;   // "bool trilinear" (default false: EWA)
+        r.max_anisotropy = mm->maxAnisotropy;
         texRecs.push_back(r);
         texSeen[im] = (int)texRecs.size();
         return (int)texRecs.size();
