@@ -76,7 +76,7 @@ typedef struct {
     uint32_t tile_size;  /* 16 in the reference (integrator.cpp:237) */
     uint32_t rank, world; /* this process renders tiles t with t % world == rank */
     uint32_t seed;
-    uint32_t max_batch;  /* paths in flight per wavefront (0 = default 1<<22) */
+    uint32_t max_batch;  /* paths in flight per wavefront batch (0 = default 1<<25; about 250 bytes of queue buffers per path and batch in flight) */
     /* ---- appended in ABI v4; all-zero = the v3 behaviour (one point light, one Kd for every primitive) ---- */
     uint32_t light_kind;   /* B200RT_LIGHT_POINT, or B200RT_LIGHT_SPHERE = AreaLightSource "area" on a full `Shape "sphere"`
                               (lights/diffuse.cpp:68-87 + Sphere::Sample / Pdf, shapes/sphere.cpp:232-305; one-sided),

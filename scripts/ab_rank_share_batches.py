@@ -1,5 +1,5 @@
 """A/B on ONE B200: the share of the headline frame that one rank of an N-rank run renders (tiles t % N == 0), at several
-wavefront batch sizes.  At N = 8 a rank's 3.9 M paths fit ONE default batch (2^22 paths), so the second set of queue buffers
+wavefront batch sizes.  At N = 8 a rank's 3.9 M paths fit ONE batch of the then default size (2^22 paths), so the second set of queue buffers
 (two batches in flight) has nothing to overlap with; this measures whether splitting the share into 2-4 smaller
 batches buys the overlap back.
 
@@ -53,7 +53,7 @@ def main():
             if ref is None:
                 ref = f
             rays = st["closest_rays"] + st["shadow_rays"]
-            print(json.dumps({"world": world, "rank": 0, "max_batch": max_batch or "default (2^22)", "ms_per_frame": ms,
+            print(json.dumps({"world": world, "rank": 0, "max_batch": max_batch or "default", "ms_per_frame": ms,
                               "rays": rays, "mrays_per_s": rays / ms / 1e3, "film_equals_default": bool(torch.equal(f, ref))}),
                   flush=True)
 

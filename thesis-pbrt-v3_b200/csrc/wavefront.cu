@@ -579,12 +579,15 @@ static int render_impl(b200rt_scene *s, const b200rt_render_desc *d, float *film
     const uint32_t tp = P.tl.tile * P.tl.tile;
     const uint64_t unit = (uint64_t)tp * P.tl.spp;  // batches hold whole tiles so a pixel's samples never split
     static const uint64_t envBatch = [] { const char *e = getenv("B200RT_WF_BATCH"); return e ? (uint64_t)atoll(e) : 0ull; }();
-    uint64_t want = d->max_batch ? d->max_batch : (envBatch ? envBatch : (1u << 22));
+    // 2^25 paths per batch (about 8 GB of queue buffers per batch in flight: the card has 180): the deep, thin bounces of a batch
+    // cost launches whatever their size, so fewer, larger batches pay — scenes/living-room (maxdepth 65) 1 312 ms at 2^22,
+    // 1 022 at 2^23, 873 at 2^24, 789 at 2^25; the headline frame 104.6 -> 101.1 ms (profiles/r02_ab_wf_batch.log)
+    uint64_t want = d->max_batch ? d->max_batch : (envBatch ? envBatch : (1u << 25));
     uint64_t cap = std::max<uint64_t>(unit, want / unit * unit);
     cap = std::min<uint64_t>(cap, std::max<uint64_t>(unit, P.tl.n_paths_rank));
-    // a share that fits one default batch (one rank of an 8-rank headline frame) is split in two so that the second set of
-    // queue buffers has something to overlap with: 14.42 -> 14.18 ms (profiles/r02_ab_rank_share_batches.log); smaller
-    // batches than ~2 M paths lose more to the thin deep-bounce launches than the overlap returns
+    // a share that fits one batch is split in two so that the second set of queue buffers has something to overlap with (one
+    // rank of an 8-rank headline frame: 14.42 -> 14.18 ms, profiles/r02_ab_rank_share_batches.log); batches smaller than ~2 M
+    // paths lose more to the thin deep-bounce launches than the overlap returns
     if (!d->max_batch && !envBatch && g_wf_sets.load() >= 2 && !heat && !w->keep && P.tl.n_paths_rank <= cap && P.tl.n_paths_rank >= (3ull << 20))
         cap = std::max<uint64_t>(unit, ((P.tl.n_paths_rank + 1) / 2 + unit - 1) / unit * unit);
     if (cap > 0x7fffffffull) return set_error(B200RT_EINVAL, "batch too large");
