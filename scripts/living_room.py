@@ -76,7 +76,10 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    frame(integrator(args.warm_spp))
+    # the warm-up frame must be large enough to make the library allocate its full-size wavefront buffers (2^25 paths per batch,
+    # two batches in flight: several GB), or that allocation lands in the timed frame
+    warm = min(args.spp, max(args.warm_spp, -(-(1 << 26) // max(1, args.xres * args.yres // world))))
+    frame(integrator(warm))
     integ = integrator(args.spp)
     barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)

@@ -112,6 +112,9 @@ bvh_persistent_kernel(const __grid_constant__ BvhView S, const float4 *__restric
     extern __shared__ uint2 sst[];
     uint32_t n = (uint32_t)n64;
     if (n_dev) { const uint32_t m = *n_dev; n = m < n ? m : n; }
+    // the host sized `chunk` for the queue's CAPACITY; a queue that cannot give every warp one chunk is handed out in 32-ray
+    // chunks, so that a thin deep-bounce queue spreads over the machine instead of running 128 rays a warp, four after another
+    if (chunk > 32u && n < gridDim.x * (blockDim.x >> 5) * chunk) chunk = 32u;
     const unsigned FULL = 0xFFFFFFFFu;
     const int lane = threadIdx.x & 31;
     // Top of the tree in shared memory (north-star item (3)): one cooperative copy per block, behind the stack area.
@@ -276,6 +279,9 @@ bvh4_persistent_kernel(const __grid_constant__ BvhView S, const float4 *__restri
     extern __shared__ uint2 sst[];
     uint32_t n = (uint32_t)n64;
     if (n_dev) { const uint32_t m = *n_dev; n = m < n ? m : n; }
+    // the host sized `chunk` for the queue's CAPACITY; a queue that cannot give every warp one chunk is handed out in 32-ray
+    // chunks, so that a thin deep-bounce queue spreads over the machine instead of running 128 rays a warp, four after another
+    if (chunk > 32u && n < gridDim.x * (blockDim.x >> 5) * chunk) chunk = 32u;
     const unsigned FULL = 0xFFFFFFFFu;
     const int lane = threadIdx.x & 31;
     RayCtx r;
@@ -443,6 +449,9 @@ bsp_persistent_kernel(const __grid_constant__ BspView S, const float4 *__restric
     extern __shared__ uint32_t sst32[];  // 3 planes (node, tMin, tMax) of sdepth x blockDim words: bank = lane
     uint32_t n = (uint32_t)n64;
     if (n_dev) { const uint32_t m = *n_dev; n = m < n ? m : n; }
+    // the host sized `chunk` for the queue's CAPACITY; a queue that cannot give every warp one chunk is handed out in 32-ray
+    // chunks, so that a thin deep-bounce queue spreads over the machine instead of running 128 rays a warp, four after another
+    if (chunk > 32u && n < gridDim.x * (blockDim.x >> 5) * chunk) chunk = 32u;
     const unsigned FULL = 0xFFFFFFFFu;
     const int lane = threadIdx.x & 31;
     const uint32_t off = KIND == B200RT_KDTREE ? 2u : S.bitOffset;

@@ -114,6 +114,11 @@ __global__ void k_camera(const __grid_constant__ WfParams P, uint64_t batchStart
 // Shade one wavefront: PathIntegrator::Li's body for one bounce (wf_shade.cuh shade_vertex), then the queue appends.
 // FULL = false: the lean instantiation for one point light + one matte Kd (the bench workload); FULL = true adds the
 // area / distant / infinite lights with MIS, the per-primitive material table and the specular bookkeeping.
+// No __launch_bounds__ on purpose.  k_shade<true> waits for instructions and for its slowest warps (ncu on scenes/living-room:
+// 15 no_instruction and 6.6 barrier stalls per issue at 16 resident warps), so 3 and 4 resident blocks per SM were tried: 80 / 64
+// registers with spills, no faster (741 / 751 ms against 720 in a run whose frames still included the buffer allocation,
+// profiles/r02_ab_shade_full.log); and the mere bound (256, 1) on the lean
+// instantiation changed its code enough (84 registers) to cost the headline frame 5 %, 106.3 against 101.3 ms on the same box.
 template <bool FULL>
 __global__ void k_shade(const __grid_constant__ WfParams P, uint32_t depth, uint64_t batchStart,
                         const uint32_t *__restrict__ nCur, const float4 *__restrict__ rays,
@@ -816,6 +821,12 @@ static int render_impl(b200rt_scene *s, const b200rt_render_desc *d, float *film
         for (int k = 0; k < nSets; ++k) WCU(cudaStreamWaitEvent(w->side[k], w->evFork, 0));
     }
     const unsigned TB = B200RT_WF_TB;
+    // k_shade<true>'s block size (B200RT_WF_TB_FULL: 64 | 128 | 256).  Smaller blocks were tried because its warps take very
+    // different times and a block holds its registers until its slowest warp is done: living-room 699 ms at 256, 871 at 128,
+    // 938 at 64 (profiles/r02_ab_shade_tb.log) — 256 stays
+    static const unsigned envTbFull = [] { const char *e = getenv("B200RT_WF_TB_FULL"); const int v = e ? atoi(e) : 256; return (unsigned)(v == 64 || v == 128 || v == 256 ? v : 256); }();
+    const unsigned tbFull = P.sortShade ? B200RT_WF_TB : envTbFull;   // the block-wide sort is written for B200RT_WF_TB threads
+    auto shadeFull = k_shade<true>;
     uint64_t batch = 0;
     for (uint64_t start = 0; start < P.tl.n_paths_rank; start += cap, ++batch) {
         const uint32_t nSlots = (uint32_t)std::min<uint64_t>(cap, P.tl.n_paths_rank - start);
@@ -845,7 +856,7 @@ static int render_impl(b200rt_scene *s, const b200rt_render_desc *d, float *film
             // path.cpp:110: the last intersection is found, then the path ends — after the emitted radiance a specular
             // bounce may still see there (path.cpp:97-107): one more shade launch, which only adds Le
             if (depth == d->max_depth && !(P.has_specular && mis)) break;
-            (full ? k_shade<true> : k_shade<false>)<<<gridSlots, TB, 0, bs>>>(P, depth, start, Q.counts + 2 * depth, Q.rays[cur], Q.qPath[cur], Q.hits,
+            (full ? shadeFull : k_shade<false>)<<<full ? (nSlots + tbFull - 1) / tbFull : gridSlots, full ? tbFull : TB, 0, bs>>>(P, depth, start, Q.counts + 2 * depth, Q.rays[cur], Q.qPath[cur], Q.hits,
                                               s->d_prim_tris, Q.beta, Q.pdim, Q.pinfo, Q.rays[cur ^ 1], Q.qPath[cur ^ 1],
                                               Q.counts + 2 * (depth + 1), Q.shRays, Q.shPath, Q.shContrib,
                                               Q.counts + 2 * depth + 1, Q.L, Q.misRays, Q.misPath, Q.misContrib,

@@ -353,7 +353,17 @@ WF_HD uint32_t bsdf_num_components(const WfBsdf &b, uint32_t flags) {
     for (uint32_t i = 0; i < b.nLobes; ++i) n += type_matches(lobe_type(bsdf_lobe(b, i).kind), flags) ? 1u : 0u;
     return n;
 }
+// The three per-lobe switches out of line: k_shade<true> evaluates BSDFs at three places (the light sample's f / Pdf, EstimateDirect's
+// BSDF sample, the path's next direction); inlined, every place carries its own copy of every lobe's code, and a kernel of warps
+// that diverge over materials then waits for instructions (ncu: 15 no_instruction stalls per issue on scenes/living-room).
+// OUT = false keeps them inline (the lean kernel has one Lambert lobe and nothing to share).
+WF_HD_NOINLINE V3 lobe_f_out(const WfLobe &l, V3 wo, V3 wi) { return lobe_f(l, wo, wi); }
+WF_HD_NOINLINE float lobe_pdf_out(const WfLobe &l, V3 wo, V3 wi) { return lobe_pdf(l, wo, wi); }
+WF_HD_NOINLINE V3 lobe_sample_out(const WfLobe &l, V3 wo, float u0, float u1, V3 &wi, float &pdf, uint32_t &sampledType) {
+    return lobe_sample(l, wo, u0, u1, wi, pdf, sampledType);
+}
 // BSDF::f (reflection.cpp:670-683)
+template <bool OUT = false>
 WF_HD V3 bsdf_f(const WfBsdf &b, V3 woW, V3 wiW, uint32_t flags) {
     const V3 wi = bsdf_to_local(b, wiW), wo = bsdf_to_local(b, woW);
     V3 f = v3(0.f, 0.f, 0.f);
@@ -362,11 +372,12 @@ WF_HD V3 bsdf_f(const WfBsdf &b, V3 woW, V3 wiW, uint32_t flags) {
     for (uint32_t i = 0; i < b.nLobes; ++i) {
         const WfLobe l = bsdf_lobe(b, i);
         const uint32_t t = lobe_type(l.kind);
-        if (type_matches(t, flags) && ((reflect && (t & BSDF_REFLECTION)) || (!reflect && (t & BSDF_TRANSMISSION)))) f = vadd(f, lobe_f(l, wo, wi));
+        if (type_matches(t, flags) && ((reflect && (t & BSDF_REFLECTION)) || (!reflect && (t & BSDF_TRANSMISSION)))) f = vadd(f, OUT ? lobe_f_out(l, wo, wi) : lobe_f(l, wo, wi));
     }
     return f;
 }
 // BSDF::Pdf (reflection.cpp:770-785)
+template <bool OUT = false>
 WF_HD float bsdf_pdf(const WfBsdf &b, V3 woW, V3 wiW, uint32_t flags) {
     if (b.nLobes == 0) return 0.f;
     const V3 wo = bsdf_to_local(b, woW), wi = bsdf_to_local(b, wiW);
@@ -375,11 +386,12 @@ WF_HD float bsdf_pdf(const WfBsdf &b, V3 woW, V3 wiW, uint32_t flags) {
     int matching = 0;
     for (uint32_t i = 0; i < b.nLobes; ++i) {
         const WfLobe l = bsdf_lobe(b, i);
-        if (type_matches(lobe_type(l.kind), flags)) { ++matching; pdf += lobe_pdf(l, wo, wi); }
+        if (type_matches(lobe_type(l.kind), flags)) { ++matching; pdf += OUT ? lobe_pdf_out(l, wo, wi) : lobe_pdf(l, wo, wi); }
     }
     return matching > 0 ? pdf / matching : 0.f;
 }
 // BSDF::Sample_f (reflection.cpp:703-768).  Returns f (black with pdf = 0 when nothing was sampled).
+template <bool OUT = false>
 WF_HD V3 bsdf_sample(const WfBsdf &b, V3 woW, float u0, float u1, uint32_t flags, V3 &wiW, float &pdf, uint32_t &sampledType) {
     const V3 zero = v3(0.f, 0.f, 0.f);
     pdf = 0.f; sampledType = 0;
@@ -398,14 +410,14 @@ WF_HD V3 bsdf_sample(const WfBsdf &b, V3 woW, float u0, float u1, uint32_t flags
     if (wo.z == 0) return zero;
     V3 wi;
     sampledType = ltype;
-    V3 f = lobe_sample(l, wo, ur, u1, wi, pdf, sampledType);
+    V3 f = OUT ? lobe_sample_out(l, wo, ur, u1, wi, pdf, sampledType) : lobe_sample(l, wo, ur, u1, wi, pdf, sampledType);
     if (pdf == 0) { sampledType = 0; return zero; }
     wiW = bsdf_to_world(b, wi);
     if (!(ltype & BSDF_SPECULAR) && matching > 1)
         for (uint32_t i = 0; i < b.nLobes; ++i) {
             if (i == chosen) continue;
             const WfLobe o = bsdf_lobe(b, i);
-            if (type_matches(lobe_type(o.kind), flags)) pdf += lobe_pdf(o, wo, wi);
+            if (type_matches(lobe_type(o.kind), flags)) pdf += OUT ? lobe_pdf_out(o, wo, wi) : lobe_pdf(o, wo, wi);
         }
     if (matching > 1) pdf /= matching;
     if (!(ltype & BSDF_SPECULAR)) {
@@ -414,7 +426,7 @@ WF_HD V3 bsdf_sample(const WfBsdf &b, V3 woW, float u0, float u1, uint32_t flags
         for (uint32_t i = 0; i < b.nLobes; ++i) {
             const WfLobe o = bsdf_lobe(b, i);
             const uint32_t t = lobe_type(o.kind);
-            if (type_matches(t, flags) && ((reflect && (t & BSDF_REFLECTION)) || (!reflect && (t & BSDF_TRANSMISSION)))) f = vadd(f, lobe_f(o, wo, wi));
+            if (type_matches(t, flags) && ((reflect && (t & BSDF_REFLECTION)) || (!reflect && (t & BSDF_TRANSMISSION)))) f = vadd(f, OUT ? lobe_f_out(o, wo, wi) : lobe_f(o, wo, wi));
         }
     }
     return f;

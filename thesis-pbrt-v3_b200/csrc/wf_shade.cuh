@@ -9,6 +9,10 @@
 #include "wf_texture.cuh"
 #include "wf_sampler.cuh"
 
+#ifndef B200RT_SHADE_OUTLINE
+#define B200RT_SHADE_OUTLINE 1   // 0: every BSDF evaluation of k_shade<true> inlines the lobe code (A/B)
+#endif
+
 namespace b200rt {
 
 struct WfTiling {
@@ -503,8 +507,8 @@ WF_HD void shade_vertex(const WfParams &P, uint32_t depth, uint32_t x, uint32_t 
         const V3 Li = light_sample<FULL>(Lt, it, ul0, ul1, wi, lightPdf, so, sd);
         const bool delta = !area && !infinite;
         if (lightPdf > 0 && !spec_black(Li)) {
-            const V3 f = vmul(bsdf_f(bs, it.wo, wi, nonSpec), fabsf(vdot(wi, it.ns)));
-            scatPdf = bsdf_pdf(bs, it.wo, wi, nonSpec);
+            const V3 f = vmul(bsdf_f<FULL && B200RT_SHADE_OUTLINE>(bs, it.wo, wi, nonSpec), fabsf(vdot(wi, it.ns)));
+            scatPdf = bsdf_pdf<FULL && B200RT_SHADE_OUTLINE>(bs, it.wo, wi, nonSpec);
             if (!spec_black(f)) {
                 V3 Ld;
                 if (delta) Ld = spec_div(spec_mul(f, Li), lightPdf);
@@ -521,7 +525,7 @@ WF_HD void shade_vertex(const WfParams &P, uint32_t depth, uint32_t x, uint32_t 
             // the BSDF-sampled strategy (integrator.cpp:166-214)
             V3 wiS;
             uint32_t st;
-            V3 f = bsdf_sample(bs, it.wo, us0, us1, nonSpec, wiS, scatPdf, st);
+            V3 f = bsdf_sample<FULL && B200RT_SHADE_OUTLINE>(bs, it.wo, us0, us1, nonSpec, wiS, scatPdf, st);
             f = vmul(f, fabsf(vdot(wiS, it.ns)));
             if (!spec_black(f) && scatPdf > 0) {
                 const float lp = light_pdf(Lt, it, wiS);
@@ -545,7 +549,7 @@ WF_HD void shade_vertex(const WfParams &P, uint32_t depth, uint32_t x, uint32_t 
     float pdf;
     uint32_t flags;
     const V3 woPath = vneg(rayD);   // path.cpp:143 `Vector3f wo = -ray.d`: NOT isect.wo, i.e. not renormalised
-    const V3 f = bsdf_sample(bs, woPath, ub0, ub1, BSDF_ALL, wi, pdf, flags);
+    const V3 f = bsdf_sample<FULL && B200RT_SHADE_OUTLINE>(bs, woPath, ub0, ub1, BSDF_ALL, wi, pdf, flags);
     if (spec_black(f) || pdf == 0.f) return;
     V3 nb = spec_mul(beta, spec_div(vmul(f, fabsf(vdot(wi, it.ns))), pdf));
     float es = etaScale;
