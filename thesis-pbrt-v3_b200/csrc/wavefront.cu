@@ -8,7 +8,6 @@
 // warp ballots + one atomic per warp.  The arithmetic of a path vertex is wf_shade.cuh (host/device, pinned against
 // the compiled reference on the CPU by tests/hostshade); this file holds the kernels around it and the host driver.
 #include <cuda_runtime.h>
-#include <cub/block/block_radix_sort.cuh>
 #include <algorithm>
 #include <atomic>
 #include <cmath>
@@ -53,7 +52,7 @@ __device__ __forceinline__ uint32_t warp_append(bool pred, uint32_t *counter) {
 #define B200RT_WF_TB 256
 __device__ __forceinline__ void block_append3(bool p0, bool p1, bool p2, uint32_t *c0, uint32_t *c1, uint32_t *c2,
                                               uint32_t &s0, uint32_t &s1, uint32_t &s2) {
-    __shared__ uint32_t wcount[3][B200RT_WF_TB / 32], wbase[3][B200RT_WF_TB / 32];
+    __shared__ uint32_t wcount[3][32], wbase[3][32];   // up to 1024 threads a block
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
     const unsigned m0 = __ballot_sync(0xFFFFFFFFu, p0), m1 = __ballot_sync(0xFFFFFFFFu, p1), m2 = __ballot_sync(0xFFFFFFFFu, p2);
     if (lane == 0) { wcount[0][warp] = __popc(m0); wcount[1][warp] = __popc(m1); wcount[2][warp] = __popc(m2); }
@@ -127,25 +126,10 @@ __global__ void k_shade(const __grid_constant__ WfParams P, uint32_t depth, uint
                         float4 *nextRays, uint32_t *nextPath,
                         uint32_t *nNext, float4 *shRays, uint32_t *shPath, float4 *shContrib, uint32_t *nShadow,
                         float4 *L, float4 *misRays, uint32_t *misPath, float4 *misContrib, uint32_t *nMis) {
-    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     const uint32_t n = *nCur;
     if (blockIdx.x * blockDim.x >= n) return;   // the launch covers the batch's capacity, the queue is usually shorter (block-uniform)
     const bool mis = FULL && P.anyMis;
-    if (FULL && P.mats && P.sortShade) {   // launch-uniform
-        // The threads of a block trade their queue entries so that a warp shades ONE material where it can: a block-wide sort
-        // of (material of the entry's hit, entry).  The lobes, textures and light strategies a lane runs follow the material,
-        // and a warp of mixed materials runs them one after the other.  Which thread shades an entry does not change what it
-        // computes; only the order of the output queues differs.
-        typedef cub::BlockRadixSort<uint32_t, B200RT_WF_TB, 1> Sort;
-        __shared__ typename Sort::TempStorage sortTmp;
-        uint32_t key[1] = {0xFF00u | threadIdx.x};   // entries past the queue's end and rays that escaped: last
-        if (i < n) {
-            const uint32_t prim = hits[i].prim;
-            if (prim != B200RT_MISS) key[0] = ((uint32_t)P.primMat[prim] << 8) | threadIdx.x;
-        }
-        Sort(sortTmp).Sort(key, 0, 16);
-        i = blockIdx.x * blockDim.x + (key[0] & 0xFFu);
-    }
     ShadeOut o;
     o.wantShadow = o.wantNext = o.wantMis = false;
     uint32_t path = 0;
@@ -616,10 +600,6 @@ static int render_impl(b200rt_scene *s, const b200rt_render_desc *d, float *film
         for (uint32_t k = 0; k < d->n_materials; ++k)
             if (!material_lobes(d->materials + (size_t)mstride * k, mstride, k, dev.data() + (size_t)k * kMatFloats, &hasSpec, d->textures ? d->n_textures : 0u)) return B200RT_EINVAL;
         P.has_specular = hasSpec ? 1u : 0u;
-        // off by default: on scenes/living-room (20 materials) the sorted blocks shade no faster than the sort costs,
-        // 1 328 against 1 308 ms per 1280x720 @ 64 spp frame (DESIGN.md §7 experiments)
-        static const int envSort = [] { const char *e = getenv("B200RT_WF_SORT_SHADE"); return e ? atoi(e) : 0; }();
-        P.sortShade = (envSort && d->n_materials > 2) ? 1u : 0u;
         if (w->mats_n < d->n_materials) { cudaFree(w->mats); w->mats = nullptr; WCU(cudaMalloc(&w->mats, (size_t)d->n_materials * kMatFloats * 4)); w->mats_n = d->n_materials; }
         if (w->primMat_n < s->n_prims) { cudaFree(w->primMat); w->primMat = nullptr; WCU(cudaMalloc(&w->primMat, s->n_prims)); w->primMat_n = s->n_prims; }
         for (uint32_t k = 0; k < s->n_prims; ++k)
@@ -821,11 +801,13 @@ static int render_impl(b200rt_scene *s, const b200rt_render_desc *d, float *film
         for (int k = 0; k < nSets; ++k) WCU(cudaStreamWaitEvent(w->side[k], w->evFork, 0));
     }
     const unsigned TB = B200RT_WF_TB;
-    // k_shade<true>'s block size (B200RT_WF_TB_FULL: 64 | 128 | 256).  Smaller blocks were tried because its warps take very
-    // different times and a block holds its registers until its slowest warp is done: living-room 699 ms at 256, 871 at 128,
-    // 938 at 64 (profiles/r02_ab_shade_tb.log) — 256 stays
-    static const unsigned envTbFull = [] { const char *e = getenv("B200RT_WF_TB_FULL"); const int v = e ? atoi(e) : 256; return (unsigned)(v == 64 || v == 128 || v == 256 ? v : 256); }();
-    const unsigned tbFull = P.sortShade ? B200RT_WF_TB : envTbFull;   // the block-wide sort is written for B200RT_WF_TB threads
+    // k_shade<true>'s block size (B200RT_WF_TB_FULL: 64 | 128 | 256 | 512).  The kernel is 23 k instructions long and its warps wait
+    // for instructions more than for anything else (ncu: 15 no_instruction stalls per issue); the warps of ONE block start together
+    // and run the same stretch of code at about the same time, warps of different blocks do not — so the larger the block, the
+    // better the instruction cache is shared: living-room 1280x720 @ 64 spp 938 ms at 64 threads, 871 at 128, 699 at 256,
+    // 557 at 512 (one block of 16 warps per SM at 114 registers; profiles/r02_ab_shade_tb.log)
+    static const unsigned envTbFull = [] { const char *e = getenv("B200RT_WF_TB_FULL"); const int v = e ? atoi(e) : 512; return (unsigned)(v == 64 || v == 128 || v == 256 || v == 512 ? v : 512); }();
+    const unsigned tbFull = envTbFull;
     auto shadeFull = k_shade<true>;
     uint64_t batch = 0;
     for (uint64_t start = 0; start < P.tl.n_paths_rank; start += cap, ++batch) {

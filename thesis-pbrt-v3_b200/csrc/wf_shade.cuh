@@ -55,7 +55,6 @@ struct WfParams {
     const float *primUV;      // 6 floats per primitive or nullptr = (0,0) (1,0) (1,1) (triangle.h:109-121)
     const float *primN;       // 9 floats per primitive (world-space vertex normals, TriangleMesh::n) or nullptr
     const uint8_t *primFlags; // bit 0: reverseOrientation ^ transformSwapsHandedness; bit 1: the primitive has vertex normals
-    uint32_t sortShade;       // k_shade sorts each block's entries by material (B200RT_WF_SORT_SHADE=1; off by default)
     uint32_t has_specular;    // some material has a specular lobe (path.cpp's specularBounce / etaScale bookkeeping is live)
     WfSampler smp;
     const WfTexture *tex;     // imagemap textures (ABI v9) or nullptr; materials name them in their header words 2 / 3
