@@ -50,6 +50,9 @@ __device__ __forceinline__ uint32_t warp_append(bool pred, uint32_t *counter) {
 // same two or three counters; with one atomic per warp the shade kernel spent 18 % of its stall samples waiting for them
 // (same-address atomics serialise in L2).  All threads of the block must call it.  slot[q] is only meaningful where pred[q].
 #define B200RT_WF_TB 256
+#ifndef B200RT_SHADE_PHASES
+#define B200RT_SHADE_PHASES 1   // k_shade<true>: a block-wide barrier between the two halves of the vertex (0: one call, A/B)
+#endif
 __device__ __forceinline__ void block_append3(bool p0, bool p1, bool p2, uint32_t *c0, uint32_t *c1, uint32_t *c2,
                                               uint32_t &s0, uint32_t &s1, uint32_t &s2) {
     __shared__ uint32_t wcount[3][32], wbase[3][32];   // up to 1024 threads a block
@@ -133,23 +136,58 @@ __global__ void k_shade(const __grid_constant__ WfParams P, uint32_t depth, uint
     ShadeOut o;
     o.wantShadow = o.wantNext = o.wantMis = false;
     uint32_t path = 0;
-    if (i < n) {
-        const b200rt_hit h = hits[i];
-        path = qPath[i];
-        const float4 ro = rays[2 * (size_t)i], rd = rays[2 * (size_t)i + 1];
-        const float4 bt = beta[path];
-        V3 p0 = v3(0.f, 0.f, 0.f), p1 = p0, p2 = p0;
-        bool isSphere = false;
-        if (h.prim != B200RT_MISS) {
-            const float4 a = __ldg(primTris + 3 * (size_t)h.prim), b = __ldg(primTris + 3 * (size_t)h.prim + 1),
-                         c = __ldg(primTris + 3 * (size_t)h.prim + 2);
-            p0 = v3(a.x, a.y, a.z); p1 = v3(b.x, b.y, b.z); p2 = v3(c.x, c.y, c.z);
-            isSphere = (__float_as_uint(b.w) & B200RT_PRIM_SPHERE) != 0;
+    if (!FULL || !B200RT_SHADE_PHASES) {
+        if (i < n) {
+            const b200rt_hit h = hits[i];
+            path = qPath[i];
+            const float4 ro = rays[2 * (size_t)i], rd = rays[2 * (size_t)i + 1];
+            const float4 bt = beta[path];
+            V3 p0 = v3(0.f, 0.f, 0.f), p1 = p0, p2 = p0;
+            bool isSphere = false;
+            if (h.prim != B200RT_MISS) {
+                const float4 a = __ldg(primTris + 3 * (size_t)h.prim), b = __ldg(primTris + 3 * (size_t)h.prim + 1),
+                             c = __ldg(primTris + 3 * (size_t)h.prim + 2);
+                p0 = v3(a.x, a.y, a.z); p1 = v3(b.x, b.y, b.z); p2 = v3(c.x, c.y, c.z);
+                isSphere = (__float_as_uint(b.w) & B200RT_PRIM_SPHERE) != 0;
+            }
+            const uint4 pi = pinfo[path];
+            const uint32_t x = pi.x & 0xffffu, y = pi.x >> 16, s = pi.y;
+            shade_vertex<FULL>(P, depth, x, y, s, (uint64_t)pi.z | ((uint64_t)pi.w << 32), pdim[path], v3(ro.x, ro.y, ro.z), v3(rd.x, rd.y, rd.z), h.prim, h.t, h.b0, h.b1, h.b2,
+                               p0, p1, p2, isSphere, v3(bt.x, bt.y, bt.z), bt.w, o);
         }
-        const uint4 pi = pinfo[path];
-        const uint32_t x = pi.x & 0xffffu, y = pi.x >> 16, s = pi.y;
-        shade_vertex<FULL>(P, depth, x, y, s, (uint64_t)pi.z | ((uint64_t)pi.w << 32), pdim[path], v3(ro.x, ro.y, ro.z), v3(rd.x, rd.y, rd.z), h.prim, h.t, h.b0, h.b1, h.b2,
-                           p0, p1, p2, isSphere, v3(bt.x, bt.y, bt.z), bt.w, o);
+    } else {
+        // the four quarters of the vertex with block-wide barriers between them: the warps of the block then run the same quarter of
+        // this long kernel at the same time and share the instruction cache (see the block size of its launches)
+        ShadeMid mid;
+        bool more = false;
+        V3 rayD = v3(0.f, 0.f, 0.f), bta = rayD;
+        if (i < n) {
+            const b200rt_hit h = hits[i];
+            path = qPath[i];
+            const float4 ro = rays[2 * (size_t)i], rd = rays[2 * (size_t)i + 1];
+            const float4 bt = beta[path];
+            V3 p0 = v3(0.f, 0.f, 0.f), p1 = p0, p2 = p0;
+            bool isSphere = false;
+            if (h.prim != B200RT_MISS) {
+                const float4 a = __ldg(primTris + 3 * (size_t)h.prim), b = __ldg(primTris + 3 * (size_t)h.prim + 1),
+                             c = __ldg(primTris + 3 * (size_t)h.prim + 2);
+                p0 = v3(a.x, a.y, a.z); p1 = v3(b.x, b.y, b.z); p2 = v3(c.x, c.y, c.z);
+                isSphere = (__float_as_uint(b.w) & B200RT_PRIM_SPHERE) != 0;
+            }
+            const uint4 pi = pinfo[path];
+            const uint32_t x = pi.x & 0xffffu, y = pi.x >> 16, s = pi.y;
+            rayD = v3(rd.x, rd.y, rd.z); bta = v3(bt.x, bt.y, bt.z);
+            more = shade_vertex_setup<FULL>(P, depth, x, y, s, (uint64_t)pi.z | ((uint64_t)pi.w << 32), pdim[path], v3(ro.x, ro.y, ro.z), rayD, h.prim, h.t,
+                                            h.b0, h.b1, h.b2, p0, p1, p2, isSphere, bta, bt.w, o, mid);
+        }
+        __syncthreads();
+        if (more) shade_vertex_light<FULL>(P, bta, mid, o);
+        __syncthreads();
+        if (more) shade_vertex_mis<FULL>(P, bta, mid, o);
+        __syncthreads();
+        if (more) shade_vertex_bounce<FULL>(P, depth, rayD, bta, mid, o);
+    }
+    if (i < n) {
         if (FULL && (o.Le.x != 0.f || o.Le.y != 0.f || o.Le.z != 0.f)) {
             float4 l = L[path];
             l.x += o.Le.x; l.y += o.Le.y; l.z += o.Le.z;

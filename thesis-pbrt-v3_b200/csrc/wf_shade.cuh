@@ -421,11 +421,30 @@ WF_HD_NOINLINE void textured_material(const WfParams &P, const float *m, uint32_
 // One bounce of PathIntegrator::Li for a path whose ray (rayO, rayD) found `hit`.
 //   bt  : beta.xyz and the (specularBounce, etaScale) code in w
 //   dim : the path's next sample dimension
+// The vertex in two halves, so that k_shade<true> can put a block-wide barrier between them (its warps then run the same stretch of
+// this long code at the same time and share the instruction cache): shade_vertex_direct = emitted radiance, the triangle's
+// interaction, the BSDF and UniformSampleOneLight; it returns false when the path ends there.  shade_vertex_bounce = the next
+// direction and Russian roulette.  What the second half needs of the first lives in ShadeMid.
+struct ShadeMid {
+    WfIsect it;
+    WfBsdf bs;
+    PathSampler ps;
+    float etaScale;
+    float texLobes[kMaxLobes * kLobeFloats];
+    // UniformSampleOneLight's choice and draws (shade_vertex_setup), for the two strategies of EstimateDirect
+    const WfLight *Lp;
+    float pickPdf, ul0, ul1, us0, us1;
+    bool direct;
+};
 template <bool FULL>
-WF_HD void shade_vertex(const WfParams &P, uint32_t depth, uint32_t x, uint32_t y, uint32_t s, uint64_t sidx /* path_sample_index(x, y, s) */,
-                        uint32_t dim, V3 rayO, V3 rayD,
-                        uint32_t prim, float t, float b0, float b1, float b2, V3 p0, V3 p1, V3 p2, bool isSphere,
-                        V3 beta, float betaW, ShadeOut &o) {
+WF_HD bool shade_vertex_setup(const WfParams &P, uint32_t depth, uint32_t x, uint32_t y, uint32_t s, uint64_t sidx /* path_sample_index(x, y, s) */,
+                               uint32_t dim, V3 rayO, V3 rayD,
+                               uint32_t prim, float t, float b0, float b1, float b2, V3 p0, V3 p1, V3 p2, bool isSphere,
+                               V3 beta, float betaW, ShadeOut &o, ShadeMid &M) {
+    WfIsect &it = M.it;
+    WfBsdf &bs = M.bs;
+    PathSampler &ps = M.ps;
+    float *texLobes = M.texLobes;
     const V3 zero = v3(0.f, 0.f, 0.f);
     o.wantShadow = o.wantNext = o.wantMis = false;
     o.Le = zero;
@@ -449,18 +468,16 @@ WF_HD void shade_vertex(const WfParams &P, uint32_t depth, uint32_t x, uint32_t 
             }
         }
     }
-    if (prim == B200RT_MISS || depth >= P.max_depth) return;   // path.cpp:110
-    if (isSphere) return;   // sphere primitives are emitters with Material "matte" Kd 0 here: no BxDF, the path ends (path.cpp:147)
-    WfIsect it;
+    if (prim == B200RT_MISS || depth >= P.max_depth) return false;   // path.cpp:110
+    if (isSphere) return false;   // sphere primitives are emitters with Material "matte" Kd 0 here: no BxDF, the path ends (path.cpp:147)
+    M.etaScale = etaScale;
     triangle_isect(P, prim, p0, p1, p2, b0, b1, b2, rayD, it);
     // the material's BSDF (ComputeScatteringFunctions -> BSDF(si, eta), reflection.h:170-175)
-    WfBsdf bs;
     bs.ns = it.ns; bs.ng = it.n;
     bs.ss = vnormalize(it.dpdu);
     bs.ts = vcross(bs.ns, bs.ss);
     bs.leanKd = spec3(P.kd);
     bs.lobes = nullptr; bs.nLobes = spec_black(bs.leanKd) ? 0u : 1u; bs.eta = 1.f;
-    float texLobes[kMaxLobes * kLobeFloats];
     if (FULL && P.mats) {
         const float *m = P.mats + (size_t)P.primMat[prim] * kMatFloats;
         bs.nLobes = f2u(m[0]); bs.eta = m[1]; bs.lobes = m + 4;
@@ -469,7 +486,6 @@ WF_HD void shade_vertex(const WfParams &P, uint32_t depth, uint32_t x, uint32_t 
             bs.lobes = texLobes;
         }
     }
-    PathSampler ps;
     path_sampler_init(P, x, y, s, dim, sidx, ps);
     // ---- direct lighting: UniformSampleOneLight (integrator.cpp:86-107) when the BSDF has a non-specular lobe ----
     const uint32_t nonSpec = BSDF_ALL & ~BSDF_SPECULAR;
@@ -495,12 +511,27 @@ WF_HD void shade_vertex(const WfParams &P, uint32_t depth, uint32_t x, uint32_t 
             direct = pickPdf != 0.f;
         }
     }
-    const WfLight &Lt = *Lp;
-    const bool area = FULL && Lt.kind == B200RT_LIGHT_SPHERE, infinite = FULL && Lt.kind == B200RT_LIGHT_INFINITE;
+    M.Lp = Lp; M.pickPdf = pickPdf; M.direct = direct;
+    M.ul0 = M.ul1 = M.us0 = M.us1 = 0.f;
     if (direct) {
-        const float ul0 = get1d(P, ps), ul1 = get1d(P, ps);   // uLight
-        const float us0 = get1d(P, ps), us1 = get1d(P, ps);   // uScattering
-        // EstimateDirect (integrator.cpp:109-217)
+        M.ul0 = get1d(P, ps); M.ul1 = get1d(P, ps);   // uLight
+        M.us0 = get1d(P, ps); M.us1 = get1d(P, ps);   // uScattering
+    }
+    o.dim = ps.dim;
+    return true;
+}
+
+// EstimateDirect (integrator.cpp:109-217), the light-sampled strategy: the shadow ray and what it carries
+template <bool FULL>
+WF_HD void shade_vertex_light(const WfParams &P, V3 beta, const ShadeMid &M, ShadeOut &o) {
+    if (!M.direct) return;
+    const WfIsect &it = M.it;
+    const WfBsdf &bs = M.bs;
+    const uint32_t nonSpec = BSDF_ALL & ~BSDF_SPECULAR;
+    const WfLight &Lt = *M.Lp;
+    const float pickPdf = M.pickPdf, ul0 = M.ul0, ul1 = M.ul1;
+    const bool area = FULL && Lt.kind == B200RT_LIGHT_SPHERE, infinite = FULL && Lt.kind == B200RT_LIGHT_INFINITE;
+    {
         V3 wi, so, sd;
         float lightPdf = 0.f, scatPdf = 0.f;
         const V3 Li = light_sample<FULL>(Lt, it, ul0, ul1, wi, lightPdf, so, sd);
@@ -520,8 +551,23 @@ WF_HD void shade_vertex(const WfParams &P, uint32_t depth, uint32_t x, uint32_t 
                 o.wantShadow = true;
             }
         }
-        if (FULL && !delta) {
-            // the BSDF-sampled strategy (integrator.cpp:166-214)
+    }
+}
+
+// ... and its BSDF-sampled strategy (integrator.cpp:166-214), for lights with area: the MIS ray and what it carries
+template <bool FULL>
+WF_HD void shade_vertex_mis(const WfParams &P, V3 beta, const ShadeMid &M, ShadeOut &o) {
+    if (!FULL || !M.direct) return;
+    const WfIsect &it = M.it;
+    const WfBsdf &bs = M.bs;
+    const uint32_t nonSpec = BSDF_ALL & ~BSDF_SPECULAR;
+    const WfLight &Lt = *M.Lp;
+    const float pickPdf = M.pickPdf, us0 = M.us0, us1 = M.us1;
+    const bool area = Lt.kind == B200RT_LIGHT_SPHERE, infinite = Lt.kind == B200RT_LIGHT_INFINITE;
+    const bool delta = !area && !infinite;
+    float scatPdf = 0.f;
+    {
+        if (!delta) {
             V3 wiS;
             uint32_t st;
             V3 f = bsdf_sample<FULL && B200RT_SHADE_OUTLINE>(bs, it.wo, us0, us1, nonSpec, wiS, scatPdf, st);
@@ -541,6 +587,25 @@ WF_HD void shade_vertex(const WfParams &P, uint32_t depth, uint32_t x, uint32_t 
             }
         }
     }
+}
+
+// The first three quarters in one call (the lean kernel and the host build)
+template <bool FULL>
+WF_HD bool shade_vertex_direct(const WfParams &P, uint32_t depth, uint32_t x, uint32_t y, uint32_t s, uint64_t sidx, uint32_t dim, V3 rayO, V3 rayD,
+                               uint32_t prim, float t, float b0, float b1, float b2, V3 p0, V3 p1, V3 p2, bool isSphere,
+                               V3 beta, float betaW, ShadeOut &o, ShadeMid &M) {
+    if (!shade_vertex_setup<FULL>(P, depth, x, y, s, sidx, dim, rayO, rayD, prim, t, b0, b1, b2, p0, p1, p2, isSphere, beta, betaW, o, M)) return false;
+    shade_vertex_light<FULL>(P, beta, M, o);
+    shade_vertex_mis<FULL>(P, beta, M, o);
+    return true;
+}
+
+template <bool FULL>
+WF_HD void shade_vertex_bounce(const WfParams &P, uint32_t depth, V3 rayD, V3 beta, ShadeMid &M, ShadeOut &o) {
+    const WfIsect &it = M.it;
+    const WfBsdf &bs = M.bs;
+    PathSampler &ps = M.ps;
+    const float etaScale = M.etaScale;
     // ---- the path's next direction (path.cpp:142-164) ----
     const float ub0 = get1d(P, ps), ub1 = get1d(P, ps);
     o.dim = ps.dim;
@@ -572,6 +637,18 @@ WF_HD void shade_vertex(const WfParams &P, uint32_t depth, uint32_t x, uint32_t 
     o.nd = wi;
     o.no = offset_ray_origin_ref(it.p, it.pError, it.n, wi);
     o.wantNext = true;
+}
+
+
+// One bounce of PathIntegrator::Li for a path whose ray (rayO, rayD) found `hit` (both halves, as the host build and the lean
+// kernel run them).
+template <bool FULL>
+WF_HD void shade_vertex(const WfParams &P, uint32_t depth, uint32_t x, uint32_t y, uint32_t s, uint64_t sidx, uint32_t dim, V3 rayO, V3 rayD,
+                        uint32_t prim, float t, float b0, float b1, float b2, V3 p0, V3 p1, V3 p2, bool isSphere,
+                        V3 beta, float betaW, ShadeOut &o) {
+    ShadeMid M;
+    if (shade_vertex_direct<FULL>(P, depth, x, y, s, sidx, dim, rayO, rayD, prim, t, b0, b1, b2, p0, p1, p2, isSphere, beta, betaW, o, M))
+        shade_vertex_bounce<FULL>(P, depth, rayD, beta, M, o);
 }
 
 }  // namespace b200rt
