@@ -32,6 +32,13 @@ WF_HD uint32_t div_magic(uint32_t a, uint32_t magic, uint32_t shift) {
     return (((a - q) >> 1) + q) >> shift;
 }
 
+WF_HD uint32_t lowest_bit32(uint32_t a) {   // index of the lowest set bit, a != 0
+#ifdef __CUDA_ARCH__
+    return (uint32_t)(__ffs((int)a) - 1);
+#else
+    return (uint32_t)__builtin_ctz(a);
+#endif
+}
 WF_HD int lowest_bit(uint64_t a) {   // index of the lowest set bit, a != 0
 #ifdef __CUDA_ARCH__
     return __ffsll((long long)a) - 1;
@@ -177,7 +184,11 @@ WF_HD float sampler_dim(const WfSampler &S, uint64_t index, uint32_t dim, int32_
         if (dim >= (uint32_t)kSobolDims) dim = kSobolDims - 1;
         uint32_t v = 0;
         const uint32_t *col = S.sobol32 + dim * kSobolMatrixSize;
-        for (uint64_t a = index; a != 0; a &= a - 1) v ^= col[lowest_bit(a)];
+        // (the index of every frame this library is asked for fits 32 bits: 2 * log2(resolution) + log2(spp) bits — the 32-bit
+        // find-first-set is one instruction, the 64-bit one several, and this loop is a quarter of k_shade<true>'s instructions)
+        uint32_t lo = (uint32_t)index;
+        for (; lo != 0; lo &= lo - 1) v ^= col[lowest_bit32(lo)];
+        for (uint64_t a = index >> 32; a != 0; a &= a - 1) v ^= col[32 + lowest_bit(a)];
         float sv = smin((float)v * 0x1p-32f, kOneMinusEps);
         if (dim < 2) {
             sv = sv * (float)(int32_t)S.res + (float)(dim == 0 ? S.sbMinX : S.sbMinY);
