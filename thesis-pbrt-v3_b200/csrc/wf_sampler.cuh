@@ -169,6 +169,27 @@ WF_HD float scrambled_radical_inverse(uint32_t base, uint32_t magic, uint32_t sh
     return smin(invBaseN * ((float)rev + invBase * (float)perm[0] / (1.f - invBase)), kOneMinusEps);
 }
 
+// SobolSampler::SampleDimension (sobol.cpp:48-60) over SobolSampleFloat (lowdiscrepancy.h:252-266), scramble 0.  Out of line: the
+// shade kernels draw at ten places, and the lean instantiation (Halton in every thesis template) proved sensitive to what is
+// inlined around its hot path — the 32-bit loop below, inlined, cost the HEADLINE frame 6 % (107.4 against 101.3 ms, same box).
+WF_HD_NOINLINE float sobol_dim(const WfSampler &S, uint64_t index, uint32_t dim, int32_t px, int32_t py) {
+    // SobolSampler::SampleDimension (sobol.cpp:48-60) over SobolSampleFloat (lowdiscrepancy.h:252-266), scramble 0
+    if (dim >= (uint32_t)kSobolDims) dim = kSobolDims - 1;
+    uint32_t v = 0;
+    const uint32_t *col = S.sobol32 + dim * kSobolMatrixSize;
+    // (the index of every frame this library is asked for fits 32 bits: 2 * log2(resolution) + log2(spp) bits — the 32-bit
+    // find-first-set is one instruction, the 64-bit one several, and this loop is a quarter of k_shade<true>'s instructions)
+    uint32_t lo = (uint32_t)index;
+    for (; lo != 0; lo &= lo - 1) v ^= col[lowest_bit32(lo)];
+    for (uint64_t a = index >> 32; a != 0; a &= a - 1) v ^= col[32 + lowest_bit(a)];
+    float sv = smin((float)v * 0x1p-32f, kOneMinusEps);
+    if (dim < 2) {
+        sv = sv * (float)(int32_t)S.res + (float)(dim == 0 ? S.sbMinX : S.sbMinY);
+        sv = clampf(sv - (float)(dim == 0 ? px : py), 0.f, kOneMinusEps);
+    }
+    return sv;
+}
+
 // GlobalSampler::SampleDimension of the sample with global index `index` at full-frame pixel (px, py).
 WF_HD float sampler_dim(const WfSampler &S, uint64_t index, uint32_t dim, int32_t px, int32_t py, uint32_t pixOrd, uint32_t s) {
     if (S.kind == WF_SAMPLER_HALTON) {
@@ -179,23 +200,7 @@ WF_HD float sampler_dim(const WfSampler &S, uint64_t index, uint32_t dim, int32_
         const HaltonDim di = S.dimInfo[dim];
         return scrambled_radical_inverse(di.prime, di.magic, di.shift, S.perms + di.offset, index);
     }
-    if (S.kind == WF_SAMPLER_SOBOL) {
-        // SobolSampler::SampleDimension (sobol.cpp:48-60) over SobolSampleFloat (lowdiscrepancy.h:252-266), scramble 0
-        if (dim >= (uint32_t)kSobolDims) dim = kSobolDims - 1;
-        uint32_t v = 0;
-        const uint32_t *col = S.sobol32 + dim * kSobolMatrixSize;
-        // (the index of every frame this library is asked for fits 32 bits: 2 * log2(resolution) + log2(spp) bits — the 32-bit
-        // find-first-set is one instruction, the 64-bit one several, and this loop is a quarter of k_shade<true>'s instructions)
-        uint32_t lo = (uint32_t)index;
-        for (; lo != 0; lo &= lo - 1) v ^= col[lowest_bit32(lo)];
-        for (uint64_t a = index >> 32; a != 0; a &= a - 1) v ^= col[32 + lowest_bit(a)];
-        float sv = smin((float)v * 0x1p-32f, kOneMinusEps);
-        if (dim < 2) {
-            sv = sv * (float)(int32_t)S.res + (float)(dim == 0 ? S.sbMinX : S.sbMinY);
-            sv = clampf(sv - (float)(dim == 0 ? px : py), 0.f, kOneMinusEps);
-        }
-        return sv;
-    }
+    if (S.kind == WF_SAMPLER_SOBOL) return sobol_dim(S, index, dim, px, py);
     return hash_sample(S.seed, pixOrd, s, dim);
 }
 
