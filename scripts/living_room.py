@@ -78,7 +78,8 @@ def main():
 
     # the warm-up frame must be large enough to make the library allocate its full-size wavefront buffers (2^25 paths per batch,
     # two batches in flight: several GB), or that allocation lands in the timed frame
-    warm = min(args.spp, max(args.warm_spp, -(-(1 << 26) // max(1, args.xres * args.yres // world))))
+    warm = max(args.warm_spp, -(-(1 << 26) // max(1, args.xres * args.yres // world)))
+    warm = min(args.spp, 1 << (warm - 1).bit_length())   # Sampler "sobol" wants a power of two
     frame(integrator(warm))
     integ = integrator(args.spp)
     barrier()
