@@ -620,6 +620,17 @@ static int render_impl(b200rt_scene *s, const b200rt_render_desc *d, float *film
     if (cap > 0x7fffffffull) return set_error(B200RT_EINVAL, "batch too large");
     const uint32_t misBase = 2 * (d->max_depth + 2);          // counts[misBase + depth] = MIS queue size at depth
     const uint32_t nCounts = misBase + d->max_depth + 1;
+    if (w->cap < cap && !d->max_batch) {
+        // the default batch is sized for a B200's 180 GB; on a card (or a shared one) with less free memory the batch shrinks to
+        // what fits rather than failing: about 200 bytes of queue buffers per path (+ 52 with MIS rays) and batch in flight
+        size_t freeB = 0, totalB = 0;
+        if (cudaMemGetInfo(&freeB, &totalB) == cudaSuccess) {
+            const size_t perPath = 2 * 32 + 2 * 4 + 32 + 16 + 4 + 16 + 16 + 4 + 16 + sizeof(b200rt_hit) + 1 + (mis ? 52 : 0);
+            const size_t sets = (heat || w->keep) ? 1 : (size_t)g_wf_sets.load();
+            while (cap > unit && (double)cap * perPath * sets > 0.8 * (double)freeB) cap = std::max<uint64_t>(unit, cap / 2 / unit * unit);
+            if (cap < w->cap) cap = w->cap / unit * unit;   // never below what an earlier frame already holds (its buffers are part of what is not free)
+        } else cudaGetLastError();
+    }
     if (w->cap < cap) {
         free_queues(w);
         for (int k = 0; k < 2; ++k) { WCU(cudaMalloc(&w->rays[k], cap * 32)); WCU(cudaMalloc(&w->qPath[k], cap * 4)); }
