@@ -75,6 +75,20 @@ __device__ __forceinline__ void block_append3(bool p0, bool p1, bool p2, uint32_
     s2 = wbase[2][warp] + __popc(m2 & below);
 }
 
+// Sampler "sobol": SobolSampleFloat XORs one matrix column per set bit of the sample index (lowdiscrepancy.h:252-266).  The same
+// XOR by bytes: T[dim][b][x] = XOR of the columns 8 b + i over the set bits i of x, so that a 32-bit index costs four table reads
+// instead of a loop over its set bits (a quarter of k_shade<true>'s instructions on scenes/living-room).
+__global__ void k_sobol_bytes(const uint32_t *__restrict__ sobol32, uint32_t *__restrict__ T) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (uint32_t)kSobolDims * 1024u) return;
+    const uint32_t dim = i >> 10, b = (i >> 8) & 3u, x = i & 255u;
+    const uint32_t *col = sobol32 + dim * kSobolMatrixSize + 8u * b;
+    uint32_t v = 0;
+    for (uint32_t k = 0; k < 8; ++k)
+        if ((x >> k) & 1u) v ^= col[k];
+    T[i] = v;
+}
+
 // SpatialLightDistribution: one thread computes one voxel's Distribution1D (wf_shade.cuh spatial_voxel_distribution)
 __global__ void k_light_voxels(const WfLight *__restrict__ lights, uint32_t nLights, const float *__restrict__ wb6, const uint32_t *__restrict__ nVox3,
                                uint32_t nVoxels, const float *__restrict__ halton5, float *cdfHi, float *pickPdf) {
@@ -381,6 +395,7 @@ struct Workspace {
     uint16_t *haltonPerms = nullptr;
     HaltonDim *haltonDims = nullptr;
     uint32_t *sobol32 = nullptr;
+    uint32_t *sobolBytes = nullptr;   // per dimension, 4 x 256 words: the XOR of the matrix columns a byte of the index selects
     uint64_t *sobolVdc = nullptr;   // 2 x 52: the VdC row and its inverse for the current resolution
     const void *sobolHost = nullptr;
     uint32_t sobolRow = ~0u;
@@ -431,7 +446,7 @@ void free_ws(Workspace *w) {
     if (w->evFork) cudaEventDestroy(w->evFork);
     cudaFree(w->film); cudaFree(w->heat); cudaFree(w->mats); cudaFree(w->primMat); cudaFree(w->tex); cudaFree(w->texData); cudaFree(w->lights); cudaFree(w->voxTable);
     cudaFree(w->splatCount); cudaFree(w->splatPix); cudaFree(w->splatVal);
-    cudaFree(w->haltonPerms); cudaFree(w->haltonDims); cudaFree(w->sobol32); cudaFree(w->sobolVdc);
+    cudaFree(w->haltonPerms); cudaFree(w->haltonDims); cudaFree(w->sobol32); cudaFree(w->sobolBytes); cudaFree(w->sobolVdc);
     if (w->hCounts) cudaFreeHost(w->hCounts);
     for (cudaEvent_t e : w->events) cudaEventDestroy(e);
 }
@@ -553,9 +568,14 @@ static int setup_sampler(Workspace *w, const b200rt_render_desc *d, WfParams &P,
             return set_error(B200RT_EINVAL, "Sampler \"sobol\": pixelsamples must be a power of two (the reference rounds it up, samplers/sobol.h; do that in the caller)");
         sobol_setup((int)P.tl.xres, (int)P.tl.yres, (int)P.tl.x0, (int)P.tl.y0, &P.smp);
         if (P.smp.log2Res > 0 && P.smp.log2Res > d->sobol_vdc_rows) return set_error(B200RT_EINVAL, "sobol_vdc_rows %u < log2(resolution) %u", d->sobol_vdc_rows, P.smp.log2Res);
-        if (!w->sobol32) { WCU(cudaMalloc(&w->sobol32, (size_t)kSobolDims * kSobolMatrixSize * 4)); WCU(cudaMalloc(&w->sobolVdc, 2 * kSobolMatrixSize * 8)); }
+        if (!w->sobol32) {
+            WCU(cudaMalloc(&w->sobol32, (size_t)kSobolDims * kSobolMatrixSize * 4)); WCU(cudaMalloc(&w->sobolVdc, 2 * kSobolMatrixSize * 8));
+            WCU(cudaMalloc(&w->sobolBytes, (size_t)kSobolDims * 1024 * 4));
+        }
         if (w->sobolHost != d->sobol_matrices32) {
             WCU(cudaMemcpyAsync(w->sobol32, d->sobol_matrices32, (size_t)kSobolDims * kSobolMatrixSize * 4, cudaMemcpyHostToDevice, st));
+            k_sobol_bytes<<<(kSobolDims * 1024 + 255) / 256, 256, 0, st>>>(w->sobol32, w->sobolBytes);
+            g_launches.fetch_add(1);
             w->sobolHost = d->sobol_matrices32; w->sobolRow = ~0u;
         }
         if (P.smp.log2Res > 0 && w->sobolRow != P.smp.log2Res - 1) {
@@ -564,6 +584,7 @@ static int setup_sampler(Workspace *w, const b200rt_render_desc *d, WfParams &P,
             WCU(cudaMemcpyAsync(w->sobolVdc + kSobolMatrixSize, d->sobol_vdc_inv + row, kSobolMatrixSize * 8, cudaMemcpyHostToDevice, st));
             w->sobolRow = P.smp.log2Res - 1;
         }
+        P.smp.sobolBytes = w->sobolBytes;
         P.smp.sobol32 = w->sobol32; P.smp.vdc = w->sobolVdc; P.smp.vdcInv = w->sobolVdc + kSobolMatrixSize;
         return B200RT_OK;
     }

@@ -54,6 +54,7 @@ struct WfSampler {
     const HaltonDim *dimInfo;    // per dimension: (prime, offset of its permutation = PrimeSums[dim])
     uint32_t baseScale0, baseScale1, baseExp0, baseExp1, stride, multInv0, multInv1, nDims;
     // sobol
+    const uint32_t *sobolBytes;  // device only (k_sobol_bytes), else nullptr: kSobolDims x 4 x 256 byte-wise XOR tables of sobol32
     const uint32_t *sobol32;     // kSobolDims x 52
     const uint64_t *vdc, *vdcInv;   // row log2Res - 1 of VdCSobolMatrices / VdCSobolMatricesInv (52 entries each)
     uint32_t log2Res, res;
@@ -180,6 +181,11 @@ WF_HD_NOINLINE float sobol_dim(const WfSampler &S, uint64_t index, uint32_t dim,
     // (the index of every frame this library is asked for fits 32 bits: 2 * log2(resolution) + log2(spp) bits — the 32-bit
     // find-first-set is one instruction, the 64-bit one several, and this loop is a quarter of k_shade<true>'s instructions)
     uint32_t lo = (uint32_t)index;
+    if (S.sobolBytes) {   // the same XOR, a byte of the index at a time
+        const uint32_t *T = S.sobolBytes + (size_t)dim * 1024u;
+        v = T[lo & 255u] ^ T[256u + ((lo >> 8) & 255u)] ^ T[512u + ((lo >> 16) & 255u)] ^ T[768u + (lo >> 24)];
+        lo = 0;
+    }
     for (; lo != 0; lo &= lo - 1) v ^= col[lowest_bit32(lo)];
     for (uint64_t a = index >> 32; a != 0; a &= a - 1) v ^= col[32 + lowest_bit(a)];
     float sv = smin((float)v * 0x1p-32f, kOneMinusEps);
