@@ -21,6 +21,10 @@
 extern "C" {
 #endif
 
+/* ABI history (b200rt_version()): 8 the reference's sample streams, camera matrices and the triangle tail's inputs; 9 image textures
+ * (trilinear); 10 several lights (b200rt_light, light_strategy: uniform / power / spatial), the EWA texture filter
+ * (b200rt_texture::filter, max_anisotropy), b200rt_intersect_closest_async / _any_async / _wait, b200rt_ewa_weights.
+ * Structures only grow at their end; zero in a new field means the previous version's behaviour. */
 #define B200RT_VERSION 10
 
 enum {
