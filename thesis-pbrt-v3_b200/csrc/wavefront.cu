@@ -878,6 +878,7 @@ static int render_impl(b200rt_scene *s, const b200rt_render_desc *d, float *film
     // 557 at 512 (one block of 16 warps per SM at 114 registers; profiles/r02_ab_shade_tb.log)
     static const unsigned envTbFull = [] { const char *e = getenv("B200RT_WF_TB_FULL"); const int v = e ? atoi(e) : 512; return (unsigned)(v == 64 || v == 128 || v == 256 || v == 512 ? v : 512); }();
     const unsigned tbFull = envTbFull;
+    static const unsigned tbLean = [] { const char *e = getenv("B200RT_WF_TB_LEAN"); const int v = e ? atoi(e) : 64; return (unsigned)(v == 32 || v == 64 || v == 128 || v == 256 || v == 512 ? v : 64); }();
     auto shadeFull = k_shade<true>;
     uint64_t batch = 0;
     for (uint64_t start = 0; start < P.tl.n_paths_rank; start += cap, ++batch) {
@@ -908,7 +909,7 @@ static int render_impl(b200rt_scene *s, const b200rt_render_desc *d, float *film
             // path.cpp:110: the last intersection is found, then the path ends — after the emitted radiance a specular
             // bounce may still see there (path.cpp:97-107): one more shade launch, which only adds Le
             if (depth == d->max_depth && !(P.has_specular && mis)) break;
-            (full ? shadeFull : k_shade<false>)<<<full ? (nSlots + tbFull - 1) / tbFull : gridSlots, full ? tbFull : TB, 0, bs>>>(P, depth, start, Q.counts + 2 * depth, Q.rays[cur], Q.qPath[cur], Q.hits,
+            (full ? shadeFull : k_shade<false>)<<<full ? (nSlots + tbFull - 1) / tbFull : (nSlots + tbLean - 1) / tbLean, full ? tbFull : tbLean, 0, bs>>>(P, depth, start, Q.counts + 2 * depth, Q.rays[cur], Q.qPath[cur], Q.hits,
                                               s->d_prim_tris, Q.beta, Q.pdim, Q.pinfo, Q.rays[cur ^ 1], Q.qPath[cur ^ 1],
                                               Q.counts + 2 * (depth + 1), Q.shRays, Q.shPath, Q.shContrib,
                                               Q.counts + 2 * depth + 1, Q.L, Q.misRays, Q.misPath, Q.misContrib,
